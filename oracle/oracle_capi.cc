@@ -1,0 +1,194 @@
+// TEST INFRASTRUCTURE (CPU oracle) -- flat C entry points over orb_oracle.h / cvprim.h for
+// ctypes (tests/, __graft_entry__.smoke(), bench.py cpu_baseline / --impl reference only).
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "orb_oracle.h"
+
+using namespace orbo;
+
+extern "C" {
+
+void orbo_resize_linear_u8(const uint8_t* src, int sw, int sh, size_t ss, uint8_t* dst, int dw,
+                           int dh, size_t ds) {
+  resize_linear_u8(src, sw, sh, ss, dst, dw, dh, ds);
+}
+void orbo_resize_axis_table(int S, int D, int* ofs, int16_t* a0, int16_t* a1) {
+  resize_axis_table(S, D, ofs, a0, a1);
+}
+void orbo_gaussian_blur7_u8(const uint8_t* src, int w, int h, size_t ss, uint8_t* dst, size_t ds) {
+  gaussian_blur7_u8(src, w, h, ss, dst, ds);
+}
+void orbo_copy_make_border_u8(const uint8_t* src, int w, int h, size_t ss, uint8_t* dst, size_t ds,
+                              int t, int b, int l, int r) {
+  copy_make_border_reflect101_u8(src, w, h, ss, dst, ds, t, b, l, r);
+}
+// returns the number of keypoints found (may exceed cap; only cap are written), xys = x,y,score
+int orbo_fast9_nms(const uint8_t* img, int w, int h, size_t stride, int threshold, int32_t* xys,
+                   int cap) {
+  std::vector<FastPoint> v;
+  fast9_nms(img, w, h, stride, threshold, v);
+  for (int i = 0; i < (int)v.size() && i < cap; ++i) {
+    xys[3 * i] = v[i].x; xys[3 * i + 1] = v[i].y; xys[3 * i + 2] = v[i].score;
+  }
+  return (int)v.size();
+}
+float orbo_fast_atan2(float y, float x) { return fast_atan2_deg(y, x); }
+void orbo_fast_atan2_n(const float* y, const float* x, float* out, int n) {
+  for (int i = 0; i < n; ++i) out[i] = fast_atan2_deg(y[i], x[i]);
+}
+int orbo_cv_round(double v) { return cv_round(v); }
+
+struct OrboExtractor {
+  Extractor ex;
+  std::vector<KeyPoint> kps;
+  std::vector<uint8_t> desc;
+  OrboExtractor(int n, float s, int l, int a, int b) : ex(n, s, l, a, b) {}
+};
+
+OrboExtractor* orbo_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniTh,
+                                     int minTh) {
+  return new OrboExtractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+}
+void orbo_extractor_destroy(OrboExtractor* e) { delete e; }
+// runs the extractor; returns the keypoint count (results are held by the handle)
+int orbo_extractor_run(OrboExtractor* e, const uint8_t* gray, int w, int h, size_t stride) {
+  e->ex.extract(gray, w, h, stride, e->kps, e->desc);
+  return (int)e->kps.size();
+}
+void orbo_extractor_results(OrboExtractor* e, KeyPoint* kps, uint8_t* desc) {
+  if (!e->kps.empty()) {
+    std::memcpy(kps, e->kps.data(), e->kps.size() * sizeof(KeyPoint));
+    std::memcpy(desc, e->desc.data(), e->desc.size());
+  }
+}
+void orbo_extractor_tables(OrboExtractor* e, float* scale, float* inv_scale, float* sigma2,
+                           float* inv_sigma2, int* quota, int* umax16) {
+  const Extractor& x = e->ex;
+  for (int i = 0; i < x.nlevels; ++i) {
+    scale[i] = x.scale[i]; inv_scale[i] = x.inv_scale[i];
+    sigma2[i] = x.sigma2[i]; inv_sigma2[i] = x.inv_sigma2[i]; quota[i] = x.quota[i];
+  }
+  for (int i = 0; i < 16; ++i) umax16[i] = x.umax[i];
+}
+void orbo_extractor_level_size(OrboExtractor* e, int level, int* w, int* h) {
+  *w = e->ex.pyramid[level].w; *h = e->ex.pyramid[level].h;
+}
+void orbo_extractor_level_image(OrboExtractor* e, int level, int blurred, uint8_t* dst) {
+  const Image& im = blurred ? e->ex.blurred[level] : e->ex.pyramid[level];
+  if (!im.px.empty()) std::memcpy(dst, im.px.data(), im.px.size());
+}
+int orbo_extractor_level_has_blur(OrboExtractor* e, int level) {
+  return !e->ex.blurred[level].px.empty();
+}
+int orbo_extractor_num_candidates(OrboExtractor* e, int level) {
+  return (int)e->ex.candidates[level].size();
+}
+void orbo_extractor_candidates(OrboExtractor* e, int level, float* xyr) {
+  const auto& c = e->ex.candidates[level];
+  for (size_t i = 0; i < c.size(); ++i) {
+    xyr[3 * i] = c[i].x; xyr[3 * i + 1] = c[i].y; xyr[3 * i + 2] = c[i].response;
+  }
+}
+int orbo_extractor_num_level_kps(OrboExtractor* e, int level) {
+  return (int)e->ex.level_kps[level].size();
+}
+void orbo_extractor_level_kps(OrboExtractor* e, int level, KeyPoint* out) {
+  const auto& c = e->ex.level_kps[level];
+  if (!c.empty()) std::memcpy(out, c.data(), c.size() * sizeof(KeyPoint));
+}
+void orbo_extractor_stage_seconds(OrboExtractor* e, double* out6) {
+  for (int i = 0; i < 6; ++i) out6[i] = e->ex.stage_s[i];
+}
+// standalone quadtree on a candidate list (x,y,response triples); returns count, writes indices
+int orbo_distribute_quadtree(const float* xyr, int n, int minX, int maxX, int minY, int maxY, int N,
+                             int32_t* out_idx, int cap) {
+  std::vector<LevelCandidate> keys(n);
+  for (int i = 0; i < n; ++i) keys[i] = {xyr[3 * i], xyr[3 * i + 1], xyr[3 * i + 2]};
+  std::vector<int> sel = Extractor::distribute_quadtree(keys, minX, maxX, minY, maxY, N);
+  for (int i = 0; i < (int)sel.size() && i < cap; ++i) out_idx[i] = sel[i];
+  return (int)sel.size();
+}
+
+// Batched extraction on `threads` host threads (frames are independent; the reference already
+// runs two extractors in parallel, src/Frame.cc:78-81).  counts[f] = keypoints of frame f;
+// kps/desc (optional) receive up to cap per frame.  Returns total keypoints.
+long orbo_extract_batch(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh,
+                        const uint8_t* frames, int nframes, int w, int h, size_t stride,
+                        size_t frame_stride, int threads, int* counts, KeyPoint* kps,
+                        uint8_t* desc, int cap) {
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  std::vector<long> totals(threads, 0);
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      Extractor ex(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+      std::vector<KeyPoint> k;
+      std::vector<uint8_t> d;
+      for (int f = t; f < nframes; f += threads) {
+        ex.extract(frames + (size_t)f * frame_stride, w, h, stride, k, d);
+        if (counts) counts[f] = (int)k.size();
+        totals[t] += (long)k.size();
+        const int n = std::min<int>((int)k.size(), cap);
+        if (kps && n) std::memcpy(kps + (size_t)f * cap, k.data(), (size_t)n * sizeof(KeyPoint));
+        if (desc && n) std::memcpy(desc + (size_t)f * cap * 32, d.data(), (size_t)n * 32);
+      }
+    });
+  for (auto& th : pool) th.join();
+  long total = 0;
+  for (long v : totals) total += v;
+  return total;
+}
+
+int orbo_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptor_distance(a, b); }
+
+// out: idx[nq], best[nq], second[nq]; `threads` host threads split the queries.
+void orbo_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int32_t* idx,
+                           int32_t* best, int32_t* second, int threads) {
+  std::vector<BruteResult> r(nq);
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      const int lo = (int)((int64_t)nq * t / threads), hi = (int)((int64_t)nq * (t + 1) / threads);
+      if (hi > lo) match_bruteforce(q + (size_t)lo * 32, hi - lo, db, ndb, r.data() + lo);
+    });
+  for (auto& th : pool) th.join();
+  for (int i = 0; i < nq; ++i) { idx[i] = r[i].idx; best[i] = r[i].best; second[i] = r[i].second; }
+}
+
+int orbo_search_by_projection(const ProjQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
+                              const uint8_t* kdesc, const float* u_right, int nk, float minX,
+                              float minY, float invW, float invH, const float* scale_factors,
+                              float th, float nnratio, int th_high, uint8_t* kp_blocked,
+                              int32_t* match_of_kp) {
+  FrameGrid g;
+  g.minX = minX; g.minY = minY; g.invW = invW; g.invH = invH;
+  g.build(kps, nk);
+  return search_by_projection(q, qdesc, nq, kps, kdesc, u_right, nk, g, scale_factors, th, nnratio,
+                              th_high, kp_blocked, match_of_kp);
+}
+
+// candidate list of one GetFeaturesInArea query, in the reference's order
+int orbo_features_in_area(const KeyPoint* kps, int nk, float minX, float minY, float invW,
+                          float invH, float x, float y, float r, int minLevel, int maxLevel,
+                          int32_t* out, int cap) {
+  FrameGrid g;
+  g.minX = minX; g.minY = minY; g.invW = invW; g.invH = invH;
+  g.build(kps, nk);
+  std::vector<int> v;
+  g.features_in_area(kps, x, y, r, minLevel, maxLevel, v);
+  for (int i = 0; i < (int)v.size() && i < cap; ++i) out[i] = v[i];
+  return (int)v.size();
+}
+
+void orbo_stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint* kr,
+                       const uint8_t* dr, int nr, int n_rows, const float* scale_factors,
+                       float min_d, float max_d, int th_high, int32_t* best_idx_r,
+                       int32_t* best_dist) {
+  stereo_match(kl, dl, nl, kr, dr, nr, n_rows, scale_factors, min_d, max_d, th_high, best_idx_r,
+               best_dist);
+}
+
+}  // extern "C"

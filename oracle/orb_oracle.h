@@ -1,0 +1,110 @@
+// TEST INFRASTRUCTURE (CPU oracle) -- not part of the shipped product path.
+//
+// CPU restatement of the reference's ORB front-end (ORB-SLAM2, /root/reference):
+//   extractor  src/ORBextractor.cc:72-147, 410-853, 1034-1132; include/ORBextractor.h:32-111
+//   matcher    src/ORBmatcher.cc:37-137, 1601-1663 (+ variant bodies); src/Frame.cc:230-245,
+//              327-392, 466-549
+// Pixel arithmetic (resize/blur/FAST/fastAtan2) comes from cvprim.h, pinned to cv2 4.13.0
+// because the reference neither vendors nor pins OpenCV ("parity unpinned by the reference
+// itself"; pinned here against cv2 outputs, see tests/golden/ and tests/test_oracle_vs_cv2.py).
+// The quadtree's equal-size tie-break follows the canonical creation-sequence rule of
+// SURVEY.md Appendix C (the reference's own order depends on heap addresses, :684).
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+// use this code.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "cvprim.h"
+
+namespace orbo {
+
+struct KeyPoint {  // layout == cv::KeyPoint (28 bytes)
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+};
+
+struct Image {
+  int w = 0, h = 0;
+  std::vector<uint8_t> px;  // w*h, dense
+  const uint8_t* row(int y) const { return px.data() + (size_t)y * w; }
+  uint8_t* row(int y) { return px.data() + (size_t)y * w; }
+};
+
+struct LevelCandidate { float x, y, response; };  // coords relative to the 16-px border
+
+class Extractor {
+ public:
+  Extractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+
+  // ORBextractor::operator() (src/ORBextractor.cc:1043-1105); mask is ignored there too.
+  void extract(const uint8_t* gray, int w, int h, size_t stride, std::vector<KeyPoint>& kps,
+               std::vector<uint8_t>& desc);
+
+  // tables of the constructor (:410-470)
+  int nfeatures, nlevels, iniTh, minTh;
+  double scaleFactorD;
+  std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+  std::vector<int> quota;
+  int umax[16];
+
+  // stage outputs of the last extract() call (for stage-by-stage parity tests)
+  std::vector<Image> pyramid;                          // mvImagePyramid ROIs (no 19-px pad)
+  std::vector<Image> blurred;                          // per-level GaussianBlur (empty if no kps)
+  std::vector<std::vector<LevelCandidate>> candidates;  // vToDistributeKeys per level
+  std::vector<std::vector<KeyPoint>> level_kps;         // after distribute + orientation
+
+  // per-stage wall clock of the last call, seconds: pyramid, fast, quadtree, orient, blur, desc
+  double stage_s[6] = {0, 0, 0, 0, 0, 0};
+
+  void compute_pyramid(const uint8_t* gray, int w, int h, size_t stride);
+  void detect_level(int level, std::vector<LevelCandidate>& out) const;
+  // DistributeOctTree (:539-763).  Returns indices into `keys` in output (list) order.
+  static std::vector<int> distribute_quadtree(const std::vector<LevelCandidate>& keys, int minX,
+                                              int maxX, int minY, int maxY, int N);
+  float ic_angle(const Image& img, int cx, int cy) const;
+  static void brief_descriptor(const Image& blurred, const KeyPoint& kp, uint8_t* out32);
+};
+
+// ------------------------------- matcher ------------------------------------------------
+// ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663), SWAR popcount as there.
+int descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+struct BruteResult { int32_t idx; int32_t best, second; };
+// M9 (defined in SURVEY 8(a)): ascending scan with the update rule of ORBmatcher.cc:216-225,
+// best=second=256 initially, idx=-1 if the database is empty.
+void match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, BruteResult* out);
+
+struct FrameGrid {  // Frame::AssignFeaturesToGrid / GetFeaturesInArea (src/Frame.cc:230-245,327-392)
+  float minX, minY, invW, invH;  // mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv
+  static const int COLS = 64, ROWS = 48;  // include/Frame.h:37-38
+  std::vector<std::vector<int>> cells;    // [ix*ROWS+iy]
+  void build(const KeyPoint* kps, int n);
+  void features_in_area(const KeyPoint* kps, float x, float y, float r, int minLevel,
+                        int maxLevel, std::vector<int>& out) const;
+};
+
+struct ProjQuery {   // the MapPoint fields SearchByProjection reads (ORBmatcher.cc:52-66)
+  float u, v, ur;    // mTrackProjX, mTrackProjY, mTrackProjXR
+  int32_t level;     // mnTrackScaleLevel
+  float view_cos;    // mTrackViewCos
+  uint8_t valid;     // mbTrackInView && !isBad()
+  uint8_t has_obs;   // Observations() > 0 (what a claim by this point means for later points)
+};
+// M2: ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (:45-129).
+// kp_blocked[i] in/out: keypoint already holds a MapPoint with Observations()>0 (:87-89).
+// match_of_kp[i] out: index of the query assigned to keypoint i in this call, else -1.
+int search_by_projection(const ProjQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
+                         const uint8_t* kdesc, const float* u_right, int nk,
+                         const FrameGrid& grid, const float* scale_factors, float th,
+                         float nnratio, int th_high, uint8_t* kp_blocked, int32_t* match_of_kp);
+
+// M10: Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549).
+// best_idx_r[i] = right index or -1; best_dist[i] = distance (TH_HIGH if none).
+void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint* kr,
+                  const uint8_t* dr, int nr, int n_rows, const float* scale_factors,
+                  float min_d, float max_d, int th_high, int32_t* best_idx_r,
+                  int32_t* best_dist);
+
+}  // namespace orbo

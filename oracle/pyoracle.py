@@ -1,0 +1,326 @@
+"""ctypes front of the CPU oracle (oracle/liborb_oracle.so) and, when built, of the reference's
+own ORBextractor.cc compiled verbatim (oracle/_ref/libref_orb.so).
+
+TEST INFRASTRUCTURE: imported only by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs.  Never imported by c_orb_slam_b200.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liborb_oracle.so")
+REF_PATH = os.path.join(HERE, "_ref", "libref_orb.so")
+REF_SEQ_PATH = os.path.join(HERE, "_ref", "libref_orb_seq.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("level", "<i4"),
+                       ("view_cos", "<f4"), ("valid", "u1"), ("has_obs", "u1")], align=True)
+assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24
+
+
+def build(force=False):
+    """(Re)build the oracle with oracle/Makefile (gcc only; no GPU, no reference build system)."""
+    need = force or not os.path.exists(LIB_PATH)
+    if os.path.isdir("/root/reference") and not os.path.exists(REF_PATH):
+        need = True
+    if need:
+        subprocess.check_call(["make", "-s", "-C", HERE, "all"])
+
+
+_lib = None
+_ref = None
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        L.orbo_fast_atan2.restype = C.c_float
+        L.orbo_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orbo_extractor_create.restype = C.c_void_p
+        L.orbo_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orbo_extract_batch.restype = C.c_long
+        L.orbo_cv_round.argtypes = [C.c_double]
+        _lib = L
+    return _lib
+
+
+def u8c(a):
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+def resize_linear(src, dw, dh):
+    src = u8c(src)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orbo_resize_linear_u8(_p(src), src.shape[1], src.shape[0], C.c_size_t(src.strides[0]),
+                                _p(dst), dw, dh, C.c_size_t(dw))
+    return dst
+
+
+def resize_axis_table(S, D):
+    ofs = np.empty(D, np.int32)
+    a0 = np.empty(D, np.int16)
+    a1 = np.empty(D, np.int16)
+    lib().orbo_resize_axis_table(S, D, _p(ofs), _p(a0), _p(a1))
+    return ofs, a0, a1
+
+
+def gaussian_blur7(src):
+    src = u8c(src)
+    dst = np.empty_like(src)
+    h, w = src.shape
+    lib().orbo_gaussian_blur7_u8(_p(src), w, h, C.c_size_t(w), _p(dst), C.c_size_t(w))
+    return dst
+
+
+def copy_make_border(src, t, b, l, r):
+    src = u8c(src)
+    h, w = src.shape
+    dst = np.empty((h + t + b, w + l + r), np.uint8)
+    lib().orbo_copy_make_border_u8(_p(src), w, h, C.c_size_t(w), _p(dst), C.c_size_t(dst.shape[1]),
+                                   t, b, l, r)
+    return dst
+
+
+def fast9_nms(img, threshold):
+    """-> int32 array [n,3] of (x, y, score) in row-major emission order."""
+    img = u8c(img)
+    h, w = img.shape
+    cap = max(16, w * h // 4 + 16)
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orbo_fast9_nms(_p(img), w, h, C.c_size_t(w), threshold, _p(out), cap)
+    return out[:n].copy()
+
+
+def fast_atan2(y, x):
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(y)
+    lib().orbo_fast_atan2_n(_p(y), _p(x), _p(out), int(y.size))
+    return out
+
+
+class Extractor:
+    """Restated ORBextractor (oracle/orb_oracle.cc)."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nlevels = nlevels
+        self.args = (nfeatures, float(scale_factor), nlevels, ini_th, min_th)
+        self._h = C.c_void_p(lib().orbo_extractor_create(nfeatures, C.c_float(scale_factor), nlevels,
+                                                         ini_th, min_th))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orbo_extractor_destroy(self._h)
+            self._h = None
+
+    def tables(self):
+        n = self.nlevels
+        f = [np.empty(n, np.float32) for _ in range(4)]
+        quota = np.empty(n, np.int32)
+        umax = np.empty(16, np.int32)
+        lib().orbo_extractor_tables(self._h, _p(f[0]), _p(f[1]), _p(f[2]), _p(f[3]), _p(quota), _p(umax))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3], quota=quota, umax=umax)
+
+    def __call__(self, img):
+        img = u8c(img)
+        h, w = img.shape
+        n = lib().orbo_extractor_run(self._h, _p(img), w, h, C.c_size_t(img.strides[0]))
+        kps = np.empty(n, KP_DTYPE)
+        desc = np.empty((n, 32), np.uint8)
+        lib().orbo_extractor_results(self._h, _p(kps), _p(desc))
+        return kps, desc
+
+    def level_image(self, level, blurred=False):
+        w = C.c_int()
+        h = C.c_int()
+        lib().orbo_extractor_level_size(self._h, level, C.byref(w), C.byref(h))
+        if blurred and not lib().orbo_extractor_level_has_blur(self._h, level):
+            return None
+        out = np.empty((h.value, w.value), np.uint8)
+        lib().orbo_extractor_level_image(self._h, level, int(blurred), _p(out))
+        return out
+
+    def candidates(self, level):
+        n = lib().orbo_extractor_num_candidates(self._h, level)
+        out = np.empty((n, 3), np.float32)
+        lib().orbo_extractor_candidates(self._h, level, _p(out))
+        return out
+
+    def level_kps(self, level):
+        n = lib().orbo_extractor_num_level_kps(self._h, level)
+        out = np.empty(n, KP_DTYPE)
+        lib().orbo_extractor_level_kps(self._h, level, _p(out))
+        return out
+
+    def stage_seconds(self):
+        out = np.empty(6, np.float64)
+        lib().orbo_extractor_stage_seconds(self._h, _p(out))
+        return dict(zip(["pyramid", "fast", "quadtree", "orient", "blur", "desc"], out.tolist()))
+
+
+def distribute_quadtree(xyr, minX, maxX, minY, maxY, N):
+    xyr = np.ascontiguousarray(xyr, np.float32)
+    cap = max(16, len(xyr))
+    out = np.empty(cap, np.int32)
+    n = lib().orbo_distribute_quadtree(_p(xyr), len(xyr), minX, maxX, minY, maxY, N, _p(out), cap)
+    return out[:n].copy()
+
+
+def extract_batch(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, threads=1, cap=None,
+                  want_output=True):
+    """frames: uint8 [B,H,W] contiguous.  -> counts[B], kps[B,cap], desc[B,cap,32]"""
+    frames = u8c(frames)
+    B, H, W = frames.shape
+    cap = cap or (nfeatures + 3 * nlevels)
+    counts = np.zeros(B, np.int32)
+    kps = np.zeros((B, cap), KP_DTYPE) if want_output else None
+    desc = np.zeros((B, cap, 32), np.uint8) if want_output else None
+    lib().orbo_extract_batch(nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th, _p(frames),
+                             B, W, H, C.c_size_t(W), C.c_size_t(W * H), threads, _p(counts),
+                             _p(kps), _p(desc), cap)
+    return counts, kps, desc
+
+
+def descriptor_distance(a, b):
+    a = u8c(a)
+    b = u8c(b)
+    return lib().orbo_descriptor_distance(_p(a), _p(b))
+
+
+def match_bruteforce(q, db, threads=1):
+    q = u8c(q)
+    db = u8c(db)
+    nq = len(q)
+    idx = np.empty(nq, np.int32)
+    best = np.empty(nq, np.int32)
+    second = np.empty(nq, np.int32)
+    lib().orbo_match_bruteforce(_p(q), nq, _p(db), C.c_int64(len(db)), _p(idx), _p(best), _p(second),
+                                threads)
+    return idx, best, second
+
+
+def search_by_projection(queries, qdesc, kps, kdesc, u_right, grid, scale_factors, th, nnratio,
+                         th_high=100, blocked=None):
+    """grid = (minX, minY, invW, invH).  -> nmatches, match_of_kp[nk], blocked_after[nk]"""
+    queries = np.ascontiguousarray(queries, PROJ_DTYPE)
+    qdesc = u8c(qdesc)
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    kdesc = u8c(kdesc)
+    nk = len(kps)
+    blocked = np.zeros(nk, np.uint8) if blocked is None else np.array(blocked, np.uint8)
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    out = np.empty(nk, np.int32)
+    n = lib().orbo_search_by_projection(_p(queries), _p(qdesc), len(queries), _p(kps), _p(kdesc),
+                                        _p(ur), nk,
+                                        C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
+                                        C.c_float(grid[3]), _p(sf), C.c_float(th), C.c_float(nnratio),
+                                        th_high, _p(blocked), _p(out))
+    return n, out, blocked
+
+
+def features_in_area(kps, grid, x, y, r, min_level, max_level):
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    out = np.empty(len(kps) + 1, np.int32)
+    n = lib().orbo_features_in_area(_p(kps), len(kps), C.c_float(grid[0]), C.c_float(grid[1]),
+                                    C.c_float(grid[2]), C.c_float(grid[3]), C.c_float(x), C.c_float(y),
+                                    C.c_float(r), min_level, max_level, _p(out), len(out))
+    return out[:n].copy()
+
+
+def stereo_match(kl, dl, kr, dr, n_rows, scale_factors, min_d, max_d, th_high=100):
+    kl = np.ascontiguousarray(kl, KP_DTYPE)
+    kr = np.ascontiguousarray(kr, KP_DTYPE)
+    dl = u8c(dl)
+    dr = u8c(dr)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    bi = np.empty(len(kl), np.int32)
+    bd = np.empty(len(kl), np.int32)
+    lib().orbo_stereo_match(_p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), n_rows, _p(sf),
+                            C.c_float(min_d), C.c_float(max_d), th_high, _p(bi), _p(bd))
+    return bi, bd
+
+
+# ------------------------------------------------------------------------------------------------
+# The reference's own ORBextractor.cc, compiled verbatim over oracle/opencv_shim (oracle/_ref).
+# ------------------------------------------------------------------------------------------------
+def have_ref():
+    if not os.path.exists(REF_PATH) and os.path.isdir("/root/reference"):
+        try:
+            build()
+        except Exception:
+            return False
+    return os.path.exists(REF_PATH)
+
+
+_refs = {}
+
+
+def ref(seq=False):
+    """seq=False: the reference as built (heap-address tie-break).  seq=True: same objects with a
+    bump arena for list nodes, so address order == creation order (see ref_wrapper.cc)."""
+    if seq not in _refs:
+        R = C.CDLL(REF_SEQ_PATH if seq else REF_PATH)
+        R.ref_extractor_create.restype = C.c_void_p
+        R.ref_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        R.ref_extract_batch.restype = C.c_long
+        _refs[seq] = R
+    return _refs[seq]
+
+
+class RefExtractor:
+    """ORB_SLAM2::ORBextractor from /root/reference/src/ORBextractor.cc, unmodified."""
+
+    def __init__(self, nfeatures=1000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7, seq=False):
+        self.nlevels = nlevels
+        self._R = ref(seq)
+        self._h = C.c_void_p(self._R.ref_extractor_create(nfeatures, C.c_float(scale_factor), nlevels,
+                                                        ini_th, min_th))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._R.ref_extractor_destroy(self._h)
+            self._h = None
+
+    def __call__(self, img):
+        img = u8c(img)
+        h, w = img.shape
+        n = self._R.ref_extractor_run(self._h, _p(img), w, h, C.c_size_t(img.strides[0]))
+        kps = np.empty(n, KP_DTYPE)
+        desc = np.empty((n, 32), np.uint8)
+        self._R.ref_extractor_results(self._h, _p(kps), _p(desc))
+        return kps, desc
+
+    def tables(self):
+        n = self.nlevels
+        f = [np.empty(n, np.float32) for _ in range(4)]
+        self._R.ref_extractor_tables(self._h, _p(f[0]), _p(f[1]), _p(f[2]), _p(f[3]))
+        return dict(scale=f[0], inv_scale=f[1], sigma2=f[2], inv_sigma2=f[3])
+
+    def level_image(self, level):
+        w = C.c_int()
+        h = C.c_int()
+        self._R.ref_extractor_level_size(self._h, level, C.byref(w), C.byref(h))
+        out = np.empty((h.value, w.value), np.uint8)
+        self._R.ref_extractor_level_image(self._h, level, _p(out))
+        return out
+
+
+def ref_extract_batch(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, threads=1):
+    frames = u8c(frames)
+    B, H, W = frames.shape
+    counts = np.zeros(B, np.int32)
+    ref().ref_extract_batch(nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th, _p(frames),
+                            B, W, H, C.c_size_t(W), C.c_size_t(W * H), threads, _p(counts))
+    return counts
