@@ -1,0 +1,300 @@
+"""Python host side of the C ABI (include/orb_gpu.h), mirroring the reference's two classes:
+
+  ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)   include/ORBextractor.h:45-111
+      __call__(image) -> (keypoints, descriptors)                        src/ORBextractor.cc:1043-1105
+      GetLevels / GetScaleFactor / GetScaleFactors / GetInverseScaleFactors /
+      GetScaleSigmaSquares / GetInverseScaleSigmaSquares, mvImagePyramid
+  ORBmatcher(nnratio=0.6, checkOri=True)                                  include/ORBmatcher.h:37-102
+      DescriptorDistance, SearchByProjection (Frame, MapPoints, th), TH_HIGH/TH_LOW/HISTO_LENGTH
+
+Everything computes in liborb_gpu.so (hand-written sm_100a kernels).  There is no CPU path: if the
+library cannot be loaded or no CUDA device is present, calls raise OrbGpuError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "liborb_gpu.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("level", "<i4"),
+                       ("view_cos", "<f4"), ("valid", "u1"), ("has_obs", "u1"), ("pad", "u1", (2,))])
+assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24
+
+EXPORTS = [
+    "orb_gpu_create", "orb_gpu_destroy", "orb_gpu_extract", "orb_gpu_extract_batch",
+    "orb_gpu_extract_batch_device", "orb_gpu_get_levels", "orb_gpu_get_scale_factor",
+    "orb_gpu_get_scale_tables", "orb_gpu_get_features_per_level", "orb_gpu_get_pyramid",
+    "orb_gpu_get_candidates", "orb_gpu_hamming_pairs_device", "orb_gpu_match_bruteforce_device",
+    "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
+    "orb_gpu_search_by_projection", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
+    "orb_gpu_launch_count", "orb_gpu_popc_peak",
+]
+
+STATUS = {0: "OK", -1: "ERR_ARG", -2: "ERR_CAPACITY", -3: "ERR_CUDA", -4: "ERR_STATE"}
+
+
+class OrbGpuError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        msg = "%s failed: %s (%d)" % (where, STATUS.get(code, "?"), code)
+        try:
+            detail = lib().orb_gpu_last_error().decode()
+            if detail:
+                msg += " -- " + detail
+        except Exception:
+            pass
+        super().__init__(msg)
+
+
+class _Grid(C.Structure):
+    _fields_ = [("min_x", C.c_float), ("min_y", C.c_float), ("inv_w", C.c_float), ("inv_h", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded C-ABI library.  Raises if liborb_gpu.so has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OrbGpuError(-3, "loading %s (run `python -m c_orb_slam_b200.build` / __graft_entry__.build())" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.orb_gpu_version.restype = C.c_char_p
+        L.orb_gpu_last_error.restype = C.c_char_p
+        L.orb_gpu_launch_count.restype = C.c_int64
+        L.orb_gpu_get_scale_factor.restype = C.c_float
+        L.orb_gpu_get_scale_factor.argtypes = [C.c_void_p]
+        L.orb_gpu_get_levels.argtypes = [C.c_void_p]
+        L.orb_gpu_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.orb_gpu_destroy.argtypes = [C.c_void_p]
+        L.orb_gpu_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t,
+                                            C.c_size_t, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orb_gpu_extract_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                                   C.c_size_t, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,
+                                                   C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orb_gpu_get_scale_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 4
+        L.orb_gpu_get_features_per_level.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orb_gpu_get_pyramid.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
+                                          C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orb_gpu_get_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.orb_gpu_hamming_pairs_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orb_gpu_match_bruteforce_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32,
+                                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orb_gpu_match_bruteforce.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orb_gpu_merge_top2_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orb_gpu_ratio_test_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
+                                                C.c_void_p, C.c_void_p]
+        L.orb_gpu_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                   C.c_void_p, C.c_int, _Grid, C.c_void_p, C.c_int, C.c_float,
+                                                   C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                   C.POINTER(C.c_int)]
+        L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                           C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
+                                           C.c_void_p, C.c_void_p]
+        L.orb_gpu_popc_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+        L.orb_gpu_set_bruteforce_variant.argtypes = [C.c_int, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _check(code, where):
+    if code != 0:
+        raise OrbGpuError(code, where)
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def launch_count():
+    return int(lib().orb_gpu_launch_count())
+
+
+def popc_peak(device=0):
+    v = C.c_double()
+    _check(lib().orb_gpu_popc_peak(device, C.byref(v)), "orb_gpu_popc_peak")
+    return v.value
+
+
+class ORBextractor:
+    """Drop-in for ORB_SLAM2::ORBextractor (include/ORBextractor.h:45-111)."""
+
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                 max_width=1920, max_height=1200, max_batch=1, device=0):
+        self._h = C.c_void_p()
+        self.nfeatures, self.nlevels, self.device = nfeatures, nlevels, device
+        self.capacity = nfeatures + 3 * nlevels
+        _check(lib().orb_gpu_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_width,
+                                    max_height, max_batch, device, C.byref(self._h)), "orb_gpu_create")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().orb_gpu_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    # -- getters (ORBextractor.h:63-83) --
+    def GetLevels(self):
+        return lib().orb_gpu_get_levels(self._h)
+
+    def GetScaleFactor(self):
+        return lib().orb_gpu_get_scale_factor(self._h)
+
+    def _tables(self):
+        t = [np.empty(self.nlevels, np.float32) for _ in range(4)]
+        _check(lib().orb_gpu_get_scale_tables(self._h, *[_p(a) for a in t]), "orb_gpu_get_scale_tables")
+        return t
+
+    def GetScaleFactors(self):
+        return self._tables()[0]
+
+    def GetInverseScaleFactors(self):
+        return self._tables()[1]
+
+    def GetScaleSigmaSquares(self):
+        return self._tables()[2]
+
+    def GetInverseScaleSigmaSquares(self):
+        return self._tables()[3]
+
+    def features_per_level(self):
+        q = np.empty(self.nlevels, np.int32)
+        u = np.empty(16, np.int32)
+        _check(lib().orb_gpu_get_features_per_level(self._h, _p(q), _p(u)), "orb_gpu_get_features_per_level")
+        return q, u
+
+    # -- operator() --
+    def __call__(self, image, mask=None):
+        """-> (keypoints[K] as KP_DTYPE, descriptors[K,32] uint8).  `mask` is ignored, as in the
+        reference (ORBextractor.h:58).  An empty image returns empty outputs (:1046)."""
+        image = np.asarray(image)
+        if image.size == 0:
+            return np.empty(0, KP_DTYPE), np.empty((0, 32), np.uint8)
+        n, kps, desc = self.extract_batch(image[None])
+        return kps[0, :n[0]].copy(), desc[0, :n[0]].copy()
+
+    def extract_batch(self, frames):
+        """frames uint8 [B,H,W] (host) -> counts[B], kps[B,cap], desc[B,cap,32]."""
+        frames = np.asarray(frames)
+        if frames.dtype != np.uint8 or frames.ndim != 3:
+            raise TypeError("expected uint8 [B,H,W] (the reference asserts CV_8UC1, ORBextractor.cc:1050)")
+        if frames.strides[2] != 1 or frames.strides[1] < frames.shape[2]:
+            frames = np.ascontiguousarray(frames)
+        B, H, W = frames.shape
+        cap = self.capacity
+        n = np.zeros(B, np.int32)
+        kps = np.zeros((B, cap), KP_DTYPE)
+        desc = np.zeros((B, cap, 32), np.uint8)
+        _check(lib().orb_gpu_extract_batch(self._h, _p(frames), B, W, H, frames.strides[1], frames.strides[0],
+                                           _p(kps), _p(desc), cap, _p(n)), "orb_gpu_extract_batch")
+        return n, kps, desc
+
+    def extract_batch_device(self, d_frames_ptr, B, W, H, stride, frame_stride, d_kps_ptr, d_desc_ptr,
+                             d_n_ptr, d_status_ptr=None, stream=None, capacity=None):
+        """All pointers are device addresses (ints); asynchronous on `stream` (cudaStream_t int)."""
+        _check(lib().orb_gpu_extract_batch_device(self._h, d_frames_ptr, B, W, H, stride, frame_stride,
+                                                  d_kps_ptr, d_desc_ptr, capacity or self.capacity, d_n_ptr,
+                                                  d_status_ptr, stream), "orb_gpu_extract_batch_device")
+
+    def pyramid_level(self, level, frame=0, blurred=False):
+        """mvImagePyramid[level] of the last call (ORBextractor.h:85)."""
+        w, h = C.c_int(), C.c_int()
+        _check(lib().orb_gpu_get_pyramid(self._h, frame, level, int(blurred), None, 0, C.byref(w), C.byref(h)),
+               "orb_gpu_get_pyramid")
+        out = np.empty((h.value, w.value), np.uint8)
+        _check(lib().orb_gpu_get_pyramid(self._h, frame, level, int(blurred), _p(out), w.value, C.byref(w),
+                                         C.byref(h)), "orb_gpu_get_pyramid")
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        return [self.pyramid_level(l) for l in range(self.nlevels)]
+
+    def candidates(self, level, frame=0):
+        n = C.c_int()
+        _check(lib().orb_gpu_get_candidates(self._h, frame, level, None, 0, C.byref(n)), "orb_gpu_get_candidates")
+        out = np.empty((n.value, 3), np.float32)
+        if n.value:
+            _check(lib().orb_gpu_get_candidates(self._h, frame, level, _p(out), n.value, C.byref(n)),
+                   "orb_gpu_get_candidates")
+        return out
+
+
+class ORBmatcher:
+    """Drop-in for the Hamming-matching surface of ORB_SLAM2::ORBmatcher (include/ORBmatcher.h)."""
+
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30  # src/ORBmatcher.cc:37-39
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio, self.mbCheckOrientation, self.device = float(nnratio), bool(checkOri), device
+
+    @staticmethod
+    def DescriptorDistance(a, b):
+        """src/ORBmatcher.cc:1647-1663 for one pair (host inline: one 256-bit pair is not worth a
+        launch); the batched device form is orb_gpu_hamming_pairs_device."""
+        a = np.ascontiguousarray(a, np.uint8).view(np.uint64)
+        b = np.ascontiguousarray(b, np.uint8).view(np.uint64)
+        return int(sum(bin(int(x) ^ int(y)).count("1") for x, y in zip(a, b)))
+
+    def match_bruteforce(self, queries, database):
+        """query x database top-2 (BASELINE config 5): -> idx, best, second (int32 arrays)."""
+        q = np.ascontiguousarray(queries, np.uint8)
+        db = np.ascontiguousarray(database, np.uint8)
+        nq = len(q)
+        idx = np.empty(nq, np.int32); best = np.empty(nq, np.int32); second = np.empty(nq, np.int32)
+        _check(lib().orb_gpu_match_bruteforce(_p(q), nq, _p(db), len(db), self.device, _p(idx), _p(best),
+                                              _p(second)), "orb_gpu_match_bruteforce")
+        return idx, best, second
+
+    def accept(self, best, second, th=None):
+        """best <= th && best < nnratio*second (ORBmatcher.cc:228-230), evaluated like the kernel."""
+        th = self.TH_LOW if th is None else th
+        b = np.asarray(best); s = np.asarray(second)
+        return (b <= th) & (b.astype(np.float32) < np.float32(self.mfNNratio) * s.astype(np.float32))
+
+    def SearchByProjection(self, frame, map_points, th=3.0):
+        """ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (ORBmatcher.cc:45-129).
+        frame: dict(kps KP_DTYPE (undistorted), desc [N,32], u_right [N] or None, grid (minX,minY,invW,invH),
+                    scale_factors [L], blocked uint8 [N] (keypoint holds a MapPoint with observations)).
+        map_points: dict(proj PROJ_DTYPE [M], desc [M,32]).
+        -> nmatches, match_of_kp [N] (map-point index or -1); frame['blocked'] is updated in place."""
+        kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
+        kd = np.ascontiguousarray(frame["desc"], np.uint8)
+        ur = frame.get("u_right")
+        ur = None if ur is None else np.ascontiguousarray(ur, np.float32)
+        sf = np.ascontiguousarray(frame["scale_factors"], np.float32)
+        blocked = frame.get("blocked")
+        if blocked is None:
+            blocked = frame["blocked"] = np.zeros(len(kps), np.uint8)
+        proj = np.ascontiguousarray(map_points["proj"], PROJ_DTYPE)
+        qd = np.ascontiguousarray(map_points["desc"], np.uint8)
+        g = _Grid(*[float(v) for v in frame["grid"]])
+        out = np.empty(len(kps), np.int32)
+        n = C.c_int()
+        _check(lib().orb_gpu_search_by_projection(_p(proj), _p(qd), len(proj), _p(kps), _p(kd), _p(ur), len(kps),
+                                                  g, _p(sf), len(sf), th, self.mfNNratio, self.TH_HIGH,
+                                                  self.device, _p(blocked), _p(out), C.byref(n)),
+               "orb_gpu_search_by_projection")
+        return n.value, out
+
+    def stereo_match(self, kps_l, desc_l, kps_r, desc_r, n_rows, scale_factors, min_d, max_d):
+        """Hamming stage of Frame::ComputeStereoMatches (Frame.cc:466-549) -> best_idx_r, best_dist."""
+        kl = np.ascontiguousarray(kps_l, KP_DTYPE); kr = np.ascontiguousarray(kps_r, KP_DTYPE)
+        dl = np.ascontiguousarray(desc_l, np.uint8); dr = np.ascontiguousarray(desc_r, np.uint8)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        bi = np.empty(len(kl), np.int32); bd = np.empty(len(kl), np.int32)
+        _check(lib().orb_gpu_stereo_match(_p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), n_rows, _p(sf),
+                                          len(sf), min_d, max_d, self.TH_HIGH, self.device, _p(bi), _p(bd)),
+               "orb_gpu_stereo_match")
+        return bi, bd

@@ -1,0 +1,94 @@
+// Shared declarations of the B200-native ORB front-end (device plan, error plumbing).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orb_gpu.h"
+
+namespace orbgpu {
+
+constexpr int kMaxLevels = ORB_GPU_MAX_LEVELS;
+constexpr int kEdge = 19;          // EDGE_THRESHOLD, reference src/ORBextractor.cc:74
+constexpr int kBorder = kEdge - 3; // FAST region starts 16 px inside the image (:773-776)
+constexpr int kHalfPatch = 15;     // HALF_PATCH_SIZE (:73)
+constexpr int kCodeDepth = 12;     // quadtree path digits kept per key (boxes up to 4096 px)
+constexpr int kMaxDim = 4096;
+
+// Geometry of one pyramid level for one (width,height); built on the host (plan.cc logic in
+// orb_gpu.cu), passed to kernels by value inside Plan.
+struct LevelGeom {
+  int w, h;                 // level image size, cvRound((float)W * invScale[l]) (:1112)
+  int pitch;                // bytes per row of img/blur
+  long long frame_stride;   // bytes between consecutive frames of this level
+  uint8_t* img;             // [B][h][pitch] (level 0 may alias caller memory)
+  uint8_t* blur;            // [B][h][bpitch] (always handle-owned)
+  int bpitch;               // bytes per row of blur
+  long long bframe_stride;  // bytes between frames of blur
+  // resize tables (level >= 1): source taps and 11-bit weights per destination column/row
+  const int* xofs; const short* ax0; const short* ax1;
+  const int* yofs; const short* ay0; const short* ay1;
+  // FAST cell grid (:778-806)
+  int ncols, nrows, wcell, hcell;
+  int max_bx, max_by;       // maxBorderX/Y = w-16, h-16
+  int cell_base;            // first cell of this level inside a frame's cell arrays
+  // quadtree (:539-563)
+  int n_ini;                // number of root nodes
+  float hx;                 // root width, (float)(W')/nIni
+  int box_w, box_h;         // W' = maxBorderX-minBorderX, H'
+  int quota;                // mnFeaturesPerLevel[l]
+  int key_cap;              // capacity (power of two) of the candidate/key arrays of this level
+  long long key_base;       // offset of this level inside a frame's key scratch (elements)
+  int slot_base;            // first output slot of this level inside a frame (quota+3 slots)
+  float scale;              // mvScaleFactor[l]
+  float patch_size;         // (float)(int)(31 * scale)  (:837)
+};
+
+struct Plan {
+  int nlevels;
+  int width, height;
+  int cells_per_frame;      // sum over levels of nrows*ncols
+  int cell_cap;             // slots per cell (upper bound of NMS survivors in one cell)
+  long long keys_per_frame; // sum of key_cap
+  int slots_per_frame;      // sum of quota+3
+  int ini_th, min_th;
+  int umax[16];
+  LevelGeom lv[kMaxLevels];
+};
+
+// Per-batch device scratch shared by the extraction kernels.
+struct Scratch {
+  uint32_t* cell_kp;   // [B][cells_per_frame][cell_cap]  lx | ly<<8 | score<<16
+  uint32_t* cell_cnt;  // [B][cells_per_frame]            all | hi<<16
+  uint64_t* keys;      // [B][keys_per_frame]             quadtree sort keys (global fallback)
+  uint32_t* pay;       // [B][keys_per_frame]             x | y<<12 | response<<24 by arrival
+  uint32_t* sel;       // [B][slots_per_frame]            selected keypoints, list order
+  int* sel_cnt;        // [B][nlevels]
+  int* cand_cnt;       // [B][nlevels]                    candidates per level (diagnostics/tests)
+  int* status;         // [1] sticky device-side status (0 or ORB_GPU_ERR_CAPACITY)
+};
+
+void count_launch(int n = 1);
+void set_last_error(const char* what, cudaError_t e);
+
+#define ORB_CUDA_TRY(expr)                                  \
+  do {                                                      \
+    cudaError_t e__ = (expr);                               \
+    if (e__ != cudaSuccess) {                               \
+      ::orbgpu::set_last_error(#expr, e__);                 \
+      return ORB_GPU_ERR_CUDA;                              \
+    }                                                       \
+  } while (0)
+
+// ---- launchers implemented in extract_kernels.cu -------------------------------------------
+int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s);
+int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);
+int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);
+int launch_blur(const Plan& p, int nframes, cudaStream_t s);
+int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
+                       uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s);
+int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int level, float* d_xyr,
+                             int cap, cudaStream_t s);
+int upload_constants();
+size_t quadtree_smem_bytes(const Plan& p, int level);
+
+}  // namespace orbgpu

@@ -1,0 +1,768 @@
+// Extraction kernels of the B200-native ORB front-end (sm_100a).
+//
+// Stages (reference: /root/reference/src/ORBextractor.cc):
+//   resize_level_kernel   ComputePyramid :1107-1132   (cv::resize INTER_LINEAR, 11-bit fixed point)
+//   fast_cells_kernel     per-cell FAST-9 + NMS + iniTh/minTh retry  :765-829
+//   quadtree_kernel       DistributeOctTree :539-763 as sort + node-level list simulation
+//   blur_kernel           GaussianBlur 7x7 sigma 2, REFLECT_101  :1085-1086
+//   orient_desc_kernel    IC_Angle :77-104, computeOrbDescriptor :106-147, output fix-ups
+// Integer stages are bit-exact with the CPU oracle; float stages use explicit _rn intrinsics
+// (the TU is compiled with -fmad=false) so every operation rounds as in the oracle.
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace orbgpu {
+
+__constant__ int8_t c_pattern[256 * 4];
+static const int8_t h_pattern[256 * 4] = {
+#include "brief_pattern.inc"
+};
+
+int upload_constants() {
+  ORB_CUDA_TRY(cudaMemcpyToSymbol(c_pattern, h_pattern, sizeof(h_pattern)));
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// 1. pyramid level l from level l-1
+// =============================================================================================
+// One thread produces 4 consecutive destination pixels of one row (one 32-bit store).
+__global__ void __launch_bounds__(256)
+resize_level_kernel(LevelGeom src, LevelGeom dst) {
+  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y = blockIdx.y * 8 + threadIdx.y;
+  const int f = blockIdx.z;
+  if (x4 >= dst.w || y >= dst.h) return;
+  const int sy0 = dst.yofs[y];
+  const int sy1 = min(sy0 + 1, src.h - 1);
+  const int b0 = dst.ay0[y], b1 = dst.ay1[y];
+  const uint8_t* s0 = src.img + (size_t)f * src.frame_stride + (size_t)sy0 * src.pitch;
+  const uint8_t* s1 = src.img + (size_t)f * src.frame_stride + (size_t)sy1 * src.pitch;
+  uint32_t packed = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int x = min(x4 + k, dst.w - 1);
+    const int x0 = dst.xofs[x];
+    const int x1 = min(x0 + 1, src.w - 1);
+    const int a0 = dst.ax0[x], a1 = dst.ax1[x];
+    const int r0 = (int)s0[x0] * a0 + (int)s0[x1] * a1;
+    const int r1 = (int)s1[x0] * a0 + (int)s1[x1] * a1;
+    const int v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
+    packed |= (uint32_t)(v & 0xff) << (8 * k);
+  }
+  uint8_t* d = dst.img + (size_t)f * dst.frame_stride + (size_t)y * dst.pitch + x4;
+  *reinterpret_cast<uint32_t*>(d) = packed;  // pitch is a multiple of 4; the row tail is padding
+}
+
+int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
+  const LevelGeom& d = p.lv[level];
+  dim3 block(32, 8);
+  dim3 grid((d.w + 127) / 128, (d.h + 7) / 8, nframes);
+  resize_level_kernel<<<grid, block, 0, s>>>(p.lv[level - 1], d);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// 2. FAST-9/16 per cell, 3x3 NMS inside the cell, threshold retry
+// =============================================================================================
+// One warp per cell.  score(p) = max over the 16 contiguous 9-arcs of max(min(d), -max(d)),
+// d_k = I(p) - I(circle_k); p is a corner at t iff score > t, response = score - 1.
+// NMS survivors above iniTh are exactly the survivors above minTh that exceed iniTh (a pixel
+// above iniTh beats every neighbour <= iniTh at either threshold), so one NMS pass serves both
+// thresholds; the cell emits the iniTh set if it is non-empty, else the minTh set (:809-816).
+constexpr int kFastWarps = 8;
+
+__device__ __forceinline__ int fast_score(const uint8_t* t, int pitch) {
+  const int v = t[0];
+  int d[16];
+  d[0] = v - t[3 * pitch];          d[1] = v - t[3 * pitch + 1];
+  d[2] = v - t[2 * pitch + 2];      d[3] = v - t[pitch + 3];
+  d[4] = v - t[3];                  d[5] = v - t[-pitch + 3];
+  d[6] = v - t[-2 * pitch + 2];     d[7] = v - t[-3 * pitch + 1];
+  d[8] = v - t[-3 * pitch];         d[9] = v - t[-3 * pitch - 1];
+  d[10] = v - t[-2 * pitch - 2];    d[11] = v - t[-pitch - 3];
+  d[12] = v - t[-3];                d[13] = v - t[pitch - 3];
+  d[14] = v - t[2 * pitch - 2];     d[15] = v - t[3 * pitch - 1];
+  // min/max over every 9-arc via 3-wide then 3x3-wide windows
+  int mn3[16], mx3[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    mn3[k] = min(d[k], min(d[(k + 1) & 15], d[(k + 2) & 15]));
+    mx3[k] = max(d[k], max(d[(k + 1) & 15], d[(k + 2) & 15]));
+  }
+  int best = -255, worst = 255;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    best = max(best, min(mn3[k], min(mn3[(k + 3) & 15], mn3[(k + 6) & 15])));
+    worst = min(worst, max(mx3[k], max(mx3[(k + 3) & 15], mx3[(k + 6) & 15])));
+  }
+  return max(best, -worst);
+}
+
+__global__ void __launch_bounds__(kFastWarps * 32)
+fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows, int score_pitch,
+                  int score_rows) {
+  extern __shared__ uint8_t smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
+  if (gcell >= (long long)nframes * p.cells_per_frame) return;
+  const int f = (int)(gcell / p.cells_per_frame);
+  const int cell = (int)(gcell - (long long)f * p.cells_per_frame);
+  int level = 0;
+  while (level + 1 < p.nlevels && cell >= p.lv[level + 1].cell_base) ++level;
+  const LevelGeom& g = p.lv[level];
+  const int ci = cell - g.cell_base;
+  const int i = ci / g.ncols, j = ci - i * g.ncols;
+
+  uint8_t* tile = smem + (size_t)warp * (tile_pitch * tile_rows + score_pitch * score_rows);
+  uint8_t* score = tile + tile_pitch * tile_rows;
+
+  // cell ROI (:789-806)
+  const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
+  const int max_y = min(ini_y + g.hcell + 6, g.max_by), max_x = min(ini_x + g.wcell + 6, g.max_bx);
+  const int cw = max_x - ini_x, ch = max_y - ini_y;
+  uint32_t* out = sc.cell_kp + ((size_t)f * p.cells_per_frame + cell) * p.cell_cap;
+  uint32_t* out_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + cell;
+  if (ini_y >= g.max_by - 3 || ini_x >= g.max_bx - 6 || cw < 7 || ch < 7) {
+    if (lane == 0) *out_cnt = 0;
+    return;
+  }
+  const int iw = cw - 6, ih = ch - 6;  // detectable interior
+
+  const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)ini_y * g.pitch + ini_x;
+  for (int y = 0; y < ch; ++y)
+    for (int x = lane; x < cw; x += 32) tile[y * tile_pitch + x] = img[(size_t)y * g.pitch + x];
+  // score tile with a 1-px zero frame (neighbours outside the interior count as 0)
+  for (int k = lane; k < score_pitch * (ih + 2); k += 32) score[k] = 0;
+  __syncwarp();
+
+  const int npx = iw * ih;
+  for (int k = lane; k < npx; k += 32) {
+    const int y = k / iw, x = k - y * iw;
+    const int s = fast_score(tile + (y + 3) * tile_pitch + (x + 3), tile_pitch);
+    score[(y + 1) * score_pitch + (x + 1)] = (uint8_t)(s > p.min_th ? s : 0);
+  }
+  __syncwarp();
+
+  int n_all = 0, n_hi = 0;
+  for (int k0 = 0; k0 < npx; k0 += 32) {
+    const int k = k0 + lane;
+    bool keep = false;
+    int s = 0, x = 0, y = 0;
+    if (k < npx) {
+      y = k / iw; x = k - y * iw;
+      const uint8_t* c = score + (y + 1) * score_pitch + (x + 1);
+      s = c[0];
+      if (s > 0) {
+        const int m = max(max(max(c[-score_pitch - 1], c[-score_pitch]), max(c[-score_pitch + 1], c[-1])),
+                          max(max(c[1], c[score_pitch - 1]), max(c[score_pitch], c[score_pitch + 1])));
+        keep = s > m;
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    const unsigned hi = __ballot_sync(0xffffffffu, keep && s > p.ini_th);
+    if (keep) {
+      const int pos = n_all + __popc(mask & ((1u << lane) - 1));
+      // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
+      out[pos] = (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(s - 1) << 16);
+    }
+    n_all += __popc(mask);
+    n_hi += __popc(hi);
+  }
+  if (lane == 0) *out_cnt = (uint32_t)n_all | ((uint32_t)n_hi << 16);
+}
+
+static void fast_smem_layout(const Plan& p, int* tile_pitch, int* tile_rows, int* score_pitch,
+                             int* score_rows) {
+  int mw = 0, mh = 0;
+  for (int l = 0; l < p.nlevels; ++l) {
+    mw = max(mw, p.lv[l].wcell + 6);
+    mh = max(mh, p.lv[l].hcell + 6);
+  }
+  *tile_pitch = (mw + 3) & ~3;
+  *tile_rows = mh;
+  *score_pitch = ((mw - 6 + 2) + 3) & ~3;
+  *score_rows = mh - 6 + 2;
+}
+
+int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
+  int tp, tr, sp, sr;
+  fast_smem_layout(p, &tp, &tr, &sp, &sr);
+  const size_t smem = (size_t)kFastWarps * (tp * tr + sp * sr);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+    configured = smem;
+  }
+  const long long cells = (long long)nframes * p.cells_per_frame;
+  const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
+  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, tp, tr, sp, sr);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// 3. quadtree distribution
+// =============================================================================================
+// The reference splits std::list nodes 4 ways until it holds >= N nodes, then keeps the best
+// response per node (:539-763).  Node boxes depend only on the path of quadrant choices from a
+// root, so every candidate gets a PATH CODE (root id, then 2 bits per depth: bit0 = right of
+// the split column, bit1 = below the split row, i.e. children n1..n4 = 0..3).  After sorting the
+// keys by (code, arrival index) every node is a contiguous key range and a split is three
+// binary searches.  The list itself (order, creation sequence, the "careful" last rounds that
+// split the largest nodes first and stop at N) is then simulated on node records only, with
+// scans instead of pointer chasing.  Equal-size ties use the creation sequence.
+constexpr int kQtThreads = 256;
+constexpr int kQtSmemKeys = 4096;   // keys sorted in shared memory up to this many, else global
+
+struct QtNode { int start, end; uint32_t prefix; int depth_new; int seq; };  // depth | isnew<<8
+
+__device__ __forceinline__ int block_exclusive_scan(int* a, int n, int* s_warp /*>=33 ints*/) {
+  // in-place exclusive scan of a[0..n) by the whole block; returns the total
+  const int T = blockDim.x, t = threadIdx.x;
+  const int chunk = (n + T - 1) / T;
+  const int lo = min(t * chunk, n), hi = min(lo + chunk, n);
+  int sum = 0;
+  for (int k = lo; k < hi; ++k) sum += a[k];
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((t & 31) >= o) incl += v;
+  }
+  if ((t & 31) == 31) s_warp[t >> 5] = incl;
+  __syncthreads();
+  if (t < 32) {
+    const int nw = T >> 5;
+    int w = t < nw ? s_warp[t] : 0, wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, wi, o);
+      if (t >= o) wi += v;
+    }
+    if (t < nw) s_warp[t] = wi - w;
+    if (t == nw - 1) s_warp[32] = wi;
+  }
+  __syncthreads();
+  int run = s_warp[t >> 5] + incl - sum;
+  for (int k = lo; k < hi; ++k) { const int v = a[k]; a[k] = run; run += v; }
+  const int total = s_warp[32];
+  __syncthreads();
+  return total;
+}
+
+__device__ __forceinline__ void block_bitonic_sort(uint64_t* a, int n /*pow2*/) {
+  for (int k = 2; k <= n; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int l = i | j;
+        const uint64_t x = a[i], y = a[l];
+        const bool up = (i & k) == 0;
+        if ((x > y) == up) { a[i] = y; a[l] = x; }
+      }
+      __syncthreads();
+    }
+}
+
+__device__ __forceinline__ int lower_bound_code(const uint64_t* keys, int lo, int hi, uint32_t code) {
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if ((uint32_t)(keys[mid] >> 32) < code) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// child boundaries of a node: b[0]=start, b[1..3] = first key of child 1..3, b[4]=end
+__device__ __forceinline__ void child_bounds(const uint64_t* keys, const QtNode& nd, int b[5]) {
+  const int depth = nd.depth_new & 0xff;
+  const int shift = 24 - 2 * (depth + 1);
+  b[0] = nd.start; b[4] = nd.end;
+  b[2] = lower_bound_code(keys, nd.start, nd.end, nd.prefix + (2u << shift));
+  b[1] = lower_bound_code(keys, nd.start, b[2], nd.prefix + (1u << shift));
+  b[3] = lower_bound_code(keys, b[2], nd.end, nd.prefix + (3u << shift));
+}
+
+__global__ void __launch_bounds__(kQtThreads)
+quadtree_kernel(Plan p, Scratch sc, int level, int ncap, int sort_cap) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const LevelGeom& g = p.lv[level];
+  const int f = blockIdx.x, t = threadIdx.x, T = kQtThreads;
+  const int ncells = g.nrows * g.ncols;
+  const int N = g.quota;
+
+  // shared memory carve-up
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* s_sort = s_keys + kQtSmemKeys;                       // [sort_cap]
+  QtNode* list_a = reinterpret_cast<QtNode*>(s_sort + sort_cap); // [ncap]
+  QtNode* list_b = list_a + ncap;                                // [ncap]
+  int* s_nch = reinterpret_cast<int*>(list_b + ncap);            // [ncap] children per split node
+  int* s_cb = s_nch + ncap;                                      // [ncap] creation base
+  int* s_sv = s_cb + ncap;                                       // [ncap] survivor flags/ranks
+  int* s_bnd = s_sv + ncap;                                      // [3*ncap] rank-ordered scratch
+  int* s_cell = s_bnd + 3 * ncap;                                // [ncells+1]
+  int* s_warp = s_cell + ncells + 1;                             // [40]
+  __shared__ int s_misc[8];
+
+  const uint32_t* cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
+  const uint32_t* cell_kp = sc.cell_kp + ((size_t)f * p.cells_per_frame + g.cell_base) * p.cell_cap;
+  uint32_t* pay = sc.pay + (size_t)f * p.keys_per_frame + g.key_base;
+  uint32_t* sel = sc.sel + (size_t)f * p.slots_per_frame + g.slot_base;
+
+  // ---- gather candidates in arrival order (cell row-major, then FAST row-major) -------------
+  for (int c = t; c < ncells; c += T) {
+    const uint32_t cc = cell_cnt[c];
+    s_cell[c] = (cc >> 16) ? (int)(cc >> 16) : (int)(cc & 0xffff);
+  }
+  if (t == 0) s_cell[ncells] = 0;
+  __syncthreads();
+  const int C = block_exclusive_scan(s_cell, ncells, s_warp);
+  if (t == 0) sc.cand_cnt[f * p.nlevels + level] = C;
+  if (C > g.key_cap) {  // uniform branch
+    if (t == 0) { *sc.status = ORB_GPU_ERR_CAPACITY; sc.sel_cnt[f * p.nlevels + level] = 0; }
+    return;
+  }
+  int cpad = 1;
+  while (cpad < C) cpad <<= 1;
+  uint64_t* keys = (cpad <= kQtSmemKeys) ? s_keys
+                                         : sc.keys + (size_t)f * p.keys_per_frame + g.key_base;
+  for (int c = t; c < ncells; c += T) {
+    const uint32_t cc = cell_cnt[c];
+    const int n_all = cc & 0xffff;
+    const bool hi_only = (cc >> 16) != 0;
+    const int ci = c / g.ncols, cj = c - ci * g.ncols;
+    const uint32_t* src = cell_kp + (size_t)c * p.cell_cap;
+    int arrival = s_cell[c];
+    for (int k = 0; k < n_all; ++k) {
+      const uint32_t e = src[k];
+      const int resp = (e >> 16) & 0xff;
+      if (hi_only && resp < p.ini_th) continue;  // score > iniTh  <=>  response >= iniTh
+      const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
+      // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
+      int root = (int)__fdiv_rn((float)x, g.hx);
+      root = min(root, g.n_ini - 1);
+      int ulx = (int)__fmul_rn(g.hx, (float)root), brx = (int)__fmul_rn(g.hx, (float)(root + 1));
+      int uly = 0, bry = g.box_h;
+      uint32_t code = (uint32_t)root << 24;
+#pragma unroll
+      for (int d = 0; d < kCodeDepth; ++d) {
+        const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+        const int right = x >= mx, below = y >= my;
+        code |= (uint32_t)(right | (below << 1)) << (22 - 2 * d);
+        if (right) ulx = mx; else brx = mx;
+        if (below) uly = my; else bry = my;
+      }
+      pay[arrival] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)resp << 24);
+      keys[arrival] = ((uint64_t)code << 32) | (uint32_t)arrival;
+      ++arrival;
+    }
+  }
+  for (int k = C + t; k < cpad; k += T) keys[k] = ~0ull;
+  __syncthreads();
+  block_bitonic_sort(keys, cpad);
+
+  // ---- initial list: non-empty roots (:543-585) --------------------------------------------
+  QtNode* cur = list_a;
+  QtNode* nxt = list_b;
+  if (t == 0) {
+    int n = 0;
+    for (int r = 0; r < g.n_ini; ++r) {
+      const int s = lower_bound_code(keys, 0, C, (uint32_t)r << 24);
+      const int e = lower_bound_code(keys, s, C, (uint32_t)(r + 1) << 24);
+      if (e > s) cur[n++] = QtNode{s, e, (uint32_t)r << 24, 0, r};
+    }
+    s_misc[0] = n;        // list size
+    s_misc[1] = g.n_ini;  // next creation sequence number
+  }
+  __syncthreads();
+  int n = s_misc[0];
+  int seq_base = s_misc[1];
+  bool careful = false;
+
+  while (true) {
+    const int prev_n = n;
+    // -- choose the nodes to split and their creation bases --
+    for (int i = t; i < n; i += T) { s_nch[i] = 0; s_cb[i] = 0; s_sv[i] = 1; }
+    __syncthreads();
+    int K = 0;
+    if (!careful) {
+      for (int i = t; i < n; i += T) {
+        const QtNode nd = cur[i];
+        if (nd.end - nd.start > 1 && (nd.depth_new & 0xff) < kCodeDepth) {
+          int b[5];
+          child_bounds(keys, nd, b);
+          s_nch[i] = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
+          s_sv[i] = 0;
+        }
+      }
+      __syncthreads();
+      for (int i = t; i < n; i += T) s_cb[i] = s_nch[i];
+      __syncthreads();
+      K = block_exclusive_scan(s_cb, n, s_warp);
+    } else {
+      // expandable nodes of the previous round, largest first, newest first among equals
+      if (t == 0) s_misc[2] = 0;
+      __syncthreads();
+      for (int i = t; i < n; i += T) {
+        const QtNode nd = cur[i];
+        if ((nd.depth_new >> 8) && nd.end - nd.start > 1 && (nd.depth_new & 0xff) < kCodeDepth) {
+          const int slot = atomicAdd(&s_misc[2], 1);
+          const uint64_t key = ((uint64_t)(nd.end - nd.start) << 40) | ((uint64_t)nd.seq << 16) | (uint64_t)i;
+          s_sort[slot] = ~key;  // ascending sort of ~key == descending (count, seq)
+        }
+      }
+      __syncthreads();
+      const int m = s_misc[2];
+      int mpad = 1;
+      while (mpad < m) mpad <<= 1;
+      for (int k = m + t; k < mpad; k += T) s_sort[k] = ~0ull;
+      __syncthreads();
+      block_bitonic_sort(s_sort, mpad);
+      // rank-ordered child counts; s_cb[j] (by rank) = children, s_sv reused later
+      int* r_nch = s_bnd + 0;
+      for (int j = t; j < m; j += T) {
+        const int pos = (int)((~s_sort[j]) & 0xffff);
+        int b[5];
+        child_bounds(keys, cur[pos], b);
+        r_nch[j] = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
+      }
+      __syncthreads();
+      // inclusive growth scan -> first rank at which the list reaches N (:730-731)
+      int* r_scan = s_bnd + ncap;
+      for (int j = t; j < m; j += T) r_scan[j] = r_nch[j];
+      __syncthreads();
+      block_exclusive_scan(r_scan, m, s_warp);  // r_scan[j] = children created before rank j
+      if (t == 0) s_misc[3] = m - 1;
+      __syncthreads();
+      for (int j = t; j < m; j += T) {
+        const int size_after = n + (r_scan[j] + r_nch[j]) - (j + 1);
+        if (size_after >= N) atomicMin(&s_misc[3], j);
+      }
+      __syncthreads();
+      const int jstar = s_misc[3];
+      int* r_pos = s_bnd + 2 * ncap;
+      for (int j = t; j < m; j += T) r_pos[j] = (int)((~s_sort[j]) & 0xffff);
+      __syncthreads();
+      if (m > 0) K = r_scan[jstar] + r_nch[jstar];
+      for (int j = t; j <= jstar && j < m; j += T) {
+        const int pos = r_pos[j];
+        s_nch[pos] = r_nch[j];
+        s_cb[pos] = r_scan[j];
+        s_sv[pos] = 0;
+      }
+    }
+    __syncthreads();
+    // -- survivors keep their order behind the new children --
+    const int nsurv = block_exclusive_scan(s_sv, n, s_warp);
+    if (t == 0) s_misc[4] = 0;
+    __syncthreads();
+    int n_exp_local = 0;
+    for (int i = t; i < n; i += T) {
+      const QtNode nd = cur[i];
+      const bool split = (i + 1 < n ? s_sv[i + 1] : nsurv) == s_sv[i];  // flag was 0
+      if (!split) {
+        QtNode keep = nd;
+        keep.depth_new &= 0xff;
+        nxt[K + s_sv[i]] = keep;
+      } else {
+        int b[5];
+        child_bounds(keys, nd, b);
+        const int depth = (nd.depth_new & 0xff) + 1;
+        const int shift = 24 - 2 * depth;
+        int m_idx = s_cb[i];
+        for (int k = 0; k < 4; ++k) {
+          if (b[k + 1] > b[k]) {
+            QtNode ch{b[k], b[k + 1], nd.prefix + ((uint32_t)k << shift), depth | 0x100, seq_base + m_idx};
+            nxt[K - 1 - m_idx] = ch;  // push_front: the last created child ends up first
+            n_exp_local += (b[k + 1] - b[k]) > 1;
+            ++m_idx;
+          }
+        }
+      }
+    }
+    if (n_exp_local) atomicAdd(&s_misc[4], n_exp_local);
+    __syncthreads();
+    const int n_exp = s_misc[4];
+    n = K + nsurv;
+    seq_base += K;
+    QtNode* tmp = cur; cur = nxt; nxt = tmp;
+    __syncthreads();
+    if (n >= N || n == prev_n) break;
+    if (!careful && n + 3 * n_exp > N) careful = true;
+  }
+
+  // ---- best response per node, list order (:741-760) ----------------------------------------
+  const int warp = t >> 5, lane = t & 31;
+  for (int i = warp; i < n; i += T / 32) {
+    const QtNode nd = cur[i];
+    // max response, earliest arrival among equals: maximise (resp << 32) | ~arrival
+    unsigned long long best = 0;
+    for (int k = nd.start + lane; k < nd.end; k += 32) {
+      const uint32_t arrival = (uint32_t)keys[k];
+      const uint32_t pv = pay[arrival];
+      const unsigned long long cand = ((unsigned long long)(pv >> 24) << 32) | (uint32_t)(~arrival);
+      best = cand > best ? cand : best;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
+      best = v > best ? v : best;
+    }
+    if (lane == 0) sel[i] = pay[~(uint32_t)best];
+  }
+  if (t == 0) sc.sel_cnt[f * p.nlevels + level] = n;
+}
+
+static int qt_ncap(const LevelGeom& g) { return max(g.quota + 4, 4 * g.n_ini) + 4; }
+static int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+size_t quadtree_smem_bytes(const Plan& p, int level) {
+  const LevelGeom& g = p.lv[level];
+  const int ncap = qt_ncap(g);
+  const int ncells = g.nrows * g.ncols;
+  return (size_t)kQtSmemKeys * 8 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
+         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 40) * 4 + 64;
+}
+
+int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
+  static size_t configured = 0;
+  for (int l = 0; l < p.nlevels; ++l) {
+    const size_t smem = quadtree_smem_bytes(p, l);
+    if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
+    if (smem > 48 * 1024 && smem > configured) {
+      ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)smem));
+      configured = smem;
+    }
+    const int ncap = qt_ncap(p.lv[l]);
+    quadtree_kernel<<<nframes, kQtThreads, smem, s>>>(p, sc, l, ncap, pow2ceil(ncap));
+    count_launch();
+  }
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// 4. GaussianBlur 7x7 sigma 2 (separable integer kernel, REFLECT_101 of the w x h image)
+// =============================================================================================
+constexpr int kBlurTW = 128, kBlurTH = 32;  // output tile; 256 threads
+
+__device__ __forceinline__ int reflect101(int p, int len) {
+  // valid for -len < p < 2*len-1 (3-px halo; len >= 4 guaranteed by the plan)
+  p = p < 0 ? -p : p;
+  return p >= len ? 2 * (len - 1) - p : p;
+}
+
+__global__ void __launch_bounds__(256)
+blur_kernel(Plan p, int tiles_total) {
+  __shared__ uint8_t s_raw[(kBlurTH + 6) * (kBlurTW + 8)];
+  __shared__ uint16_t s_h[(kBlurTH + 6) * kBlurTW];
+  // tile -> (level, tx, ty); tiles of all levels are laid out consecutively per frame
+  int tile = blockIdx.x;
+  const int f = blockIdx.y;
+  int level = 0, tiles_x = 0;
+  for (;; ++level) {
+    const LevelGeom& g = p.lv[level];
+    tiles_x = (g.w + kBlurTW - 1) / kBlurTW;
+    const int nt = tiles_x * ((g.h + kBlurTH - 1) / kBlurTH);
+    if (tile < nt || level + 1 == p.nlevels) break;
+    tile -= nt;
+  }
+  const LevelGeom& g = p.lv[level];
+  const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+  const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
+  const uint8_t* img = g.img + (size_t)f * g.frame_stride;
+  constexpr int RP = kBlurTW + 8;
+  for (int k = threadIdx.x; k < (kBlurTH + 6) * (kBlurTW + 6); k += 256) {
+    const int r = k / (kBlurTW + 6), c = k - r * (kBlurTW + 6);
+    const int sy = reflect101(min(y0 + r - 3, g.h + 2), g.h), sx = reflect101(min(x0 + c - 3, g.w + 2), g.w);
+    s_raw[r * RP + c] = img[(size_t)sy * g.pitch + sx];
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < (kBlurTH + 6) * kBlurTW; k += 256) {
+    const int r = k / kBlurTW, c = k - r * kBlurTW;
+    const uint8_t* s = s_raw + r * RP + c;
+    s_h[k] = (uint16_t)(18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3]);
+  }
+  __syncthreads();
+  uint8_t* out = g.blur + (size_t)f * g.bframe_stride;
+  for (int k = threadIdx.x; k < kBlurTH * (kBlurTW / 4); k += 256) {
+    const int r = k / (kBlurTW / 4), c4 = (k - r * (kBlurTW / 4)) * 4;
+    const int y = y0 + r, x = x0 + c4;
+    if (y >= g.h || x >= g.w) continue;
+    uint32_t packed = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint16_t* h = s_h + r * kBlurTW + c4 + q;
+      const uint32_t v = 18u * (h[0] + h[6 * kBlurTW]) + 34u * (h[kBlurTW] + h[5 * kBlurTW]) +
+                         48u * (h[2 * kBlurTW] + h[4 * kBlurTW]) + 56u * h[3 * kBlurTW];
+      packed |= ((v + 32768u) >> 16) << (8 * q);
+    }
+    *reinterpret_cast<uint32_t*>(out + (size_t)y * g.bpitch + x) = packed;
+  }
+}
+
+int launch_blur(const Plan& p, int nframes, cudaStream_t s) {
+  int tiles = 0;
+  for (int l = 0; l < p.nlevels; ++l)
+    tiles += ((p.lv[l].w + kBlurTW - 1) / kBlurTW) * ((p.lv[l].h + kBlurTH - 1) / kBlurTH);
+  blur_kernel<<<dim3(tiles, nframes), 256, 0, s>>>(p, tiles);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// 5. orientation (IC_Angle), steered BRIEF, keypoint fix-ups and per-frame concatenation
+// =============================================================================================
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  // cv::fastAtan2 (OpenCV 4.13): odd 7th-order polynomial, every op rounded to float32.
+  const float s = 57.295779513082323f;  // (float)(180/pi)
+  const float p1 = __fmul_rn(0.9997878412794807f, s), p3 = __fmul_rn(-0.3258083974640975f, s);
+  const float p5 = __fmul_rn(0.1555786518463281f, s), p7 = __fmul_rn(-0.04432655554792128f, s);
+  const float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0) a = __fsub_rn(180.f, a);
+  if (y < 0) a = __fsub_rn(360.f, a);
+  return a;
+}
+
+constexpr int kOdWarps = 8;
+
+// One warp per output slot (frame, level, rank in the level's selection).
+__global__ void __launch_bounds__(kOdWarps * 32)
+orient_desc_kernel(Plan p, Scratch sc, int nframes, OrbKeyPoint* __restrict__ kps,
+                   uint8_t* __restrict__ desc, int capacity, int* __restrict__ n_out) {
+  __shared__ char4 s_pat[256];
+  for (int k = threadIdx.x; k < 256; k += blockDim.x)
+    s_pat[k] = make_char4(c_pattern[4 * k], c_pattern[4 * k + 1], c_pattern[4 * k + 2], c_pattern[4 * k + 3]);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long gslot = (long long)blockIdx.x * kOdWarps + warp;
+  if (gslot >= (long long)nframes * p.slots_per_frame) return;
+  const int f = (int)(gslot / p.slots_per_frame);
+  const int slot = (int)(gslot - (long long)f * p.slots_per_frame);
+  int level = 0;
+  while (level + 1 < p.nlevels && slot >= p.lv[level + 1].slot_base) ++level;
+  const LevelGeom& g = p.lv[level];
+  const int rank = slot - g.slot_base;
+  const int* cnt = sc.sel_cnt + f * p.nlevels;
+  int before = 0, total = 0;
+  for (int l = 0; l < p.nlevels; ++l) {
+    const int c = cnt[l];
+    if (l < level) before += c;
+    total += c;
+  }
+  if (slot == 0 && lane == 0) n_out[f] = min(total, capacity);
+  if (rank >= cnt[level]) return;
+  const int out_idx = before + rank;
+  if (out_idx >= capacity) {
+    if (lane == 0) *sc.status = ORB_GPU_ERR_CAPACITY;
+    return;
+  }
+  const uint32_t pv = sc.sel[(size_t)f * p.slots_per_frame + slot];
+  const int cx = (int)(pv & 0xfff) + kBorder, cy = (int)((pv >> 12) & 0xfff) + kBorder;
+  const int resp = (int)(pv >> 24);
+
+  // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc; lane = column u+15
+  const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)cy * g.pitch + cx;
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {
+    const int u = lane - kHalfPatch;
+    const int au = u < 0 ? -u : u;
+#pragma unroll 1
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+      if (au <= p.umax[v < 0 ? -v : v]) {
+        const int val = img[v * g.pitch + u];
+        m10 += u * val;
+        m01 += v * val;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+  }
+  const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+  // steered BRIEF on the blurred level (:106-147)
+  const float rad = __fmul_rn(angle, 0.017453292519943295f);  // (float)(CV_PI/180.f)
+  const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+  const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride + (size_t)cy * g.bpitch + cx;
+  uint32_t* drow = reinterpret_cast<uint32_t*>(desc + ((size_t)f * capacity + out_idx) * 32);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const char4 t = s_pat[32 * k + lane];
+    const float x0 = (float)t.x, y0 = (float)t.y, x1 = (float)t.z, y1 = (float)t.w;
+    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+    const int t0 = bl[r0 * g.bpitch + c0], t1 = bl[r1 * g.bpitch + c1];
+    const unsigned word = __ballot_sync(0xffffffffu, t0 < t1);  // bit = test 32k+lane, LSB first
+    if (lane == 0) drow[k] = word;
+  }
+  if (lane == 0) {
+    OrbKeyPoint kp;
+    const float fx = (float)cx, fy = (float)cy;
+    kp.x = level ? __fmul_rn(fx, g.scale) : fx;  // keypoint->pt *= scale (:1095-1101)
+    kp.y = level ? __fmul_rn(fy, g.scale) : fy;
+    kp.size = g.patch_size;
+    kp.angle = angle;
+    kp.response = (float)resp;
+    kp.octave = level;
+    kp.class_id = -1;
+    kps[(size_t)f * capacity + out_idx] = kp;
+  }
+}
+
+int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
+                       uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
+  const long long slots = (long long)nframes * p.slots_per_frame;
+  const unsigned grid = (unsigned)((slots + kOdWarps - 1) / kOdWarps);
+  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, nframes, d_kps, d_desc, capacity, d_n_out);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// test hook: candidates of one (frame, level) in arrival order as floats
+// =============================================================================================
+__global__ void export_candidates_kernel(Plan p, Scratch sc, int f, int level, float* xyr, int cap) {
+  const LevelGeom& g = p.lv[level];
+  const int n = min(sc.cand_cnt[f * p.nlevels + level], cap);
+  const uint32_t* pay = sc.pay + (size_t)f * p.keys_per_frame + g.key_base;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const uint32_t v = pay[k];
+    xyr[3 * k] = (float)(v & 0xfff);
+    xyr[3 * k + 1] = (float)((v >> 12) & 0xfff);
+    xyr[3 * k + 2] = (float)(v >> 24);
+  }
+}
+
+int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int level, float* d_xyr,
+                             int cap, cudaStream_t s) {
+  export_candidates_kernel<<<32, 256, 0, s>>>(p, sc, frame, level, d_xyr, cap);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+}  // namespace orbgpu

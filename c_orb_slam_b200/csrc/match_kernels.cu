@@ -1,0 +1,355 @@
+// Hamming matching kernels of the B200-native ORB front-end (sm_100a).
+//
+// Reference: ORBmatcher::DescriptorDistance src/ORBmatcher.cc:1647-1663 (256-bit XOR+popcount),
+// top-2 update rule :216-225, SearchByProjection :45-129 with Frame::GetFeaturesInArea
+// src/Frame.cc:327-380, Frame::ComputeStereoMatches Hamming stage src/Frame.cc:466-549.
+// Everything is integer work on the LOP3/POPC pipes; results are bit-exact with the CPU oracle.
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace orbgpu {
+
+__device__ __forceinline__ int hamming256(const uint32_t q[8], const uint4 lo, const uint4 hi) {
+  return __popc(q[0] ^ lo.x) + __popc(q[1] ^ lo.y) + __popc(q[2] ^ lo.z) + __popc(q[3] ^ lo.w) +
+         __popc(q[4] ^ hi.x) + __popc(q[5] ^ hi.y) + __popc(q[6] ^ hi.z) + __popc(q[7] ^ hi.w);
+}
+
+// Carry-save (Harley-Seal) form: 4 POPC + LOP3 adders instead of 8 POPC.
+__device__ __forceinline__ int hamming256_csa(const uint32_t q[8], const uint4 lo, const uint4 hi) {
+  const uint32_t w0 = q[0] ^ lo.x, w1 = q[1] ^ lo.y, w2 = q[2] ^ lo.z, w3 = q[3] ^ lo.w;
+  const uint32_t w4 = q[4] ^ hi.x, w5 = q[5] ^ hi.y, w6 = q[6] ^ hi.z, w7 = q[7] ^ hi.w;
+  const uint32_t sa = w0 ^ w1 ^ w2, ca = (w0 & w1) | (w2 & (w0 | w1));
+  const uint32_t sb = w3 ^ w4 ^ w5, cb = (w3 & w4) | (w5 & (w3 | w4));
+  const uint32_t sc = sa ^ sb ^ w6, cc = (sa & sb) | (w6 & (sa | sb));
+  const uint32_t ones = sc ^ w7, cd = sc & w7;
+  const uint32_t se = ca ^ cb ^ cc, ce = (ca & cb) | (cc & (ca | cb));
+  const uint32_t twos = se ^ cd, cf = se & cd;
+  const uint32_t fours = ce ^ cf, eights = ce & cf;
+  return __popc(ones) + 2 * __popc(twos) + 4 * __popc(fours) + 8 * __popc(eights);
+}
+
+// ---------------------------------------------------------------------------------------------
+// DescriptorDistance for n independent pairs
+// ---------------------------------------------------------------------------------------------
+__global__ void hamming_pairs_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
+                                     int32_t* __restrict__ dist) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 a0 = a[2 * i], a1 = a[2 * i + 1];
+  const uint32_t q[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+  dist[i] = hamming256(q, b[2 * i], b[2 * i + 1]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// brute-force query x database top-2
+// ---------------------------------------------------------------------------------------------
+// Thread t of a block owns QPT queries in registers; the block streams its slice of the
+// database through shared memory in tiles (cp.async double buffer); every row is an LDS.128
+// broadcast shared by all threads.  Per (query,row): 8 LOP3 + 8 POPC (or 4 POPC in the
+// carry-save form) + adds, then a branch-free top-2 update on packed keys (dist << 23 | row),
+// which keeps the lowest row among equal distances exactly like the ascending scan with strict
+// '<' of the reference (:216-225).  Partial results of the database slices are merged by
+// merge_top2_kernel, the same kernel that merges per-GPU shards after the NCCL all-gather.
+constexpr int kBfThreads = 128;
+constexpr int kBfTile = 256;              // database rows per shared-memory tile (8 KB)
+constexpr int kBfSliceMax = 1 << 22;      // rows per slice (row index must fit 23 bits)
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+
+template <int QPT, bool CSA>
+__global__ void __launch_bounds__(kBfThreads)
+bruteforce_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
+                  long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
+                  int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
+  __shared__ __align__(16) uint4 tile[2][kBfTile * 2];
+  const int slice = blockIdx.y;
+  const long long row0 = (long long)slice * slice_rows;
+  const long long rows = min(slice_rows, ndb - row0);
+  uint32_t qr[QPT][8];
+  unsigned best[QPT], second[QPT];
+#pragma unroll
+  for (int k = 0; k < QPT; ++k) {
+    const int qi = min((blockIdx.x * QPT + k) * kBfThreads + threadIdx.x, nq - 1);
+    const uint4 a0 = q[2 * qi], a1 = q[2 * qi + 1];
+    qr[k][0] = a0.x; qr[k][1] = a0.y; qr[k][2] = a0.z; qr[k][3] = a0.w;
+    qr[k][4] = a1.x; qr[k][5] = a1.y; qr[k][6] = a1.z; qr[k][7] = a1.w;
+    best[k] = second[k] = (256u << 23) | 0x7fffffu;
+  }
+  const uint4* src = db + row0 * 2;
+  const int ntiles = (int)((rows + kBfTile - 1) / kBfTile);
+  auto issue = [&](int t, int buf) {
+    const long long base = (long long)t * kBfTile * 2;
+    const long long lim = rows * 2;
+    for (int v = threadIdx.x; v < kBfTile * 2; v += kBfThreads)
+      if (base + v < lim) cp_async16(&tile[buf][v], src + base + v);
+    cp_async_commit();
+  };
+  if (ntiles > 0) issue(0, 0);
+  for (int t = 0; t < ntiles; ++t) {
+    if (t + 1 < ntiles) { issue(t + 1, (t + 1) & 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const uint4* tl = tile[t & 1];
+    const int nr = (int)min((long long)kBfTile, rows - (long long)t * kBfTile);
+    const unsigned rbase = (unsigned)(t * kBfTile);
+#pragma unroll 4
+    for (int r = 0; r < nr; ++r) {
+      const uint4 lo = tl[2 * r], hi = tl[2 * r + 1];
+#pragma unroll
+      for (int k = 0; k < QPT; ++k) {
+        const int d = CSA ? hamming256_csa(qr[k], lo, hi) : hamming256(qr[k], lo, hi);
+        const unsigned key = ((unsigned)d << 23) | (rbase + r);
+        second[k] = min(second[k], max(best[k], key));
+        best[k] = min(best[k], key);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < QPT; ++k) {
+    const int qi = (blockIdx.x * QPT + k) * kBfThreads + threadIdx.x;
+    if (qi >= nq) continue;
+    const size_t o = (size_t)slice * nq + qi;
+    const int bd = (int)(best[k] >> 23);
+    o_best[o] = bd;
+    o_second[o] = (int)(second[k] >> 23);
+    o_idx[o] = bd < 256 ? (int32_t)(idx_base + row0 + (best[k] & 0x7fffffu)) : -1;  // 256 never beats the initial 256
+  }
+}
+
+// Exact merge of top-2 partials of disjoint ascending index ranges: scanning
+// shards in ascending order with the reference's update rule applied to (best, second) pairs.
+__global__ void merge_top2_kernel(const int32_t* __restrict__ idx, const int32_t* __restrict__ best,
+                                  const int32_t* __restrict__ second, int nshards, int nq,
+                                  int32_t* __restrict__ o_idx, int32_t* __restrict__ o_best,
+                                  int32_t* __restrict__ o_second) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  int b = 256, s = 256, id = -1;
+  for (int k = 0; k < nshards; ++k) {
+    const int bk = best[(size_t)k * nq + i], sk = second[(size_t)k * nq + i], ik = idx[(size_t)k * nq + i];
+    if (ik < 0) continue;  // empty shard
+    if (bk < b) { s = min(b, sk); b = bk; id = ik; }
+    else s = min(s, bk);
+  }
+  o_idx[i] = id; o_best[i] = b; o_second[i] = s;
+}
+
+__global__ void ratio_test_kernel(const int32_t* __restrict__ best, const int32_t* __restrict__ second,
+                                  int nq, int th, float nnratio, uint8_t* __restrict__ accept) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  const int b = best[i], s = second[i];
+  accept[i] = (b <= th) && ((float)b < __fmul_rn(nnratio, (float)s));  // ORBmatcher.cc:228-230
+}
+
+// ---------------------------------------------------------------------------------------------
+// integer-pipe peak probe: dependent-free POPC stream
+// ---------------------------------------------------------------------------------------------
+__global__ void popc_peak_kernel(uint32_t seed, int iters, uint32_t* out) {
+  uint32_t a[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = seed * (threadIdx.x + 1 + k) + blockIdx.x;
+  uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      acc[k] += __popc(a[k]);
+      a[k] += 0x9e3779b9u;  // keeps the operand changing so POPC cannot be hoisted
+    }
+  }
+  uint32_t r = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) r += acc[k];
+  if (r == 0xffffffffu) out[0] = r;
+}
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+// =============================================================================================
+// C ABI (matcher part)
+// =============================================================================================
+extern "C" {
+
+int orb_gpu_hamming_pairs_device(const uint8_t* d_a, const uint8_t* d_b, int n, int32_t* d_dist,
+                                 void* stream) {
+  if (n < 0 || (n > 0 && (!d_a || !d_b || !d_dist))) return ORB_GPU_ERR_ARG;
+  if (n == 0) return ORB_GPU_OK;
+  hamming_pairs_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const uint4*)d_a, (const uint4*)d_b, n, d_dist);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_merge_top2_device(const int32_t* d_idx, const int32_t* d_best, const int32_t* d_second,
+                              int nshards, int nq, int32_t* d_out_idx, int32_t* d_out_best,
+                              int32_t* d_out_second, void* stream) {
+  if (nq < 0 || nshards < 1 || (nq > 0 && (!d_idx || !d_best || !d_second || !d_out_idx || !d_out_best || !d_out_second)))
+    return ORB_GPU_ERR_ARG;
+  if (nq == 0) return ORB_GPU_OK;
+  merge_top2_kernel<<<(nq + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_idx, d_best, d_second, nshards, nq,
+                                                                    d_out_idx, d_out_best, d_out_second);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_ratio_test_device(const int32_t* d_best, const int32_t* d_second, int nq, int th,
+                              float nnratio, uint8_t* d_accept, void* stream) {
+  if (nq < 0 || (nq > 0 && (!d_best || !d_second || !d_accept))) return ORB_GPU_ERR_ARG;
+  if (nq == 0) return ORB_GPU_OK;
+  ratio_test_kernel<<<(nq + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_best, d_second, nq, th, nnratio, d_accept);
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================
+// brute force: launcher, host wrapper, POPC probe
+// =============================================================================================
+namespace orbgpu {
+
+struct TmpDev {  // RAII for call-scoped device scratch
+  void* p = nullptr;
+  ~TmpDev() { if (p) cudaFree(p); }
+  int alloc(size_t bytes) { ORB_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return ORB_GPU_OK; }
+  template <class T> T* as() { return (T*)p; }
+};
+
+static int g_bf_variant = 1;   // 0: 8-POPC form, 1: carry-save form (default)
+static int g_bf_qpt = 2;
+
+template <int QPT, bool CSA>
+static void bf_launch(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
+                      long long slice_rows, int32_t base, int32_t* i, int32_t* b, int32_t* sec) {
+  bruteforce_kernel<QPT, CSA><<<grid, kBfThreads, 0, s>>>(q, nq, db, ndb, slice_rows, base, i, b, sec);
+}
+
+}  // namespace orbgpu
+
+extern "C" {
+
+// test/bench knob: choose the inner-loop form (0 = 8 POPC, 1 = carry-save) and queries per thread
+int orb_gpu_set_bruteforce_variant(int csa, int qpt) {
+  if (qpt != 1 && qpt != 2 && qpt != 4) return ORB_GPU_ERR_ARG;
+  g_bf_variant = csa ? 1 : 0;
+  g_bf_qpt = qpt;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                    int32_t idx_base, int32_t* d_idx, int32_t* d_best, int32_t* d_second,
+                                    void* stream) {
+  if (nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_idx || !d_best || !d_second)) || (ndb > 0 && !d_db))
+    return ORB_GPU_ERR_ARG;
+  if (nq == 0) return ORB_GPU_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  int dev = 0, sms = 148;
+  ORB_CUDA_TRY(cudaGetDevice(&dev));
+  ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int qpt = g_bf_qpt;
+  const int qblocks = (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
+  // enough database slices to put ~4 waves of blocks on the chip, each slice a whole number of tiles
+  long long nslices = std::max<long long>(1, (4LL * sms * 4 + qblocks - 1) / qblocks);
+  long long slice_rows = (ndb + nslices - 1) / nslices;
+  slice_rows = std::max<long long>(kBfTile, (slice_rows + kBfTile - 1) / kBfTile * kBfTile);
+  slice_rows = std::min<long long>(slice_rows, kBfSliceMax);
+  nslices = std::max<long long>(1, (ndb + slice_rows - 1) / slice_rows);
+  if (nslices > 65535) return ORB_GPU_ERR_CAPACITY;
+  TmpDev part;
+  int32_t *pi = d_idx, *pb = d_best, *ps = d_second;
+  if (nslices > 1) {
+    int rc = part.alloc((size_t)nslices * nq * 3 * sizeof(int32_t));
+    if (rc) return rc;
+    pi = part.as<int32_t>(); pb = pi + (size_t)nslices * nq; ps = pb + (size_t)nslices * nq;
+  }
+  dim3 grid(qblocks, (unsigned)nslices);
+  const uint4* q4 = (const uint4*)d_q; const uint4* db4 = (const uint4*)d_db;
+  const int key = qpt * 2 + g_bf_variant;
+  switch (key) {
+    case 2: bf_launch<1, false>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+    case 3: bf_launch<1, true>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+    case 4: bf_launch<2, false>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+    case 5: bf_launch<2, true>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+    case 8: bf_launch<4, false>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+    default: bf_launch<4, true>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
+  }
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  if (nslices > 1) {
+    merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pi, pb, ps, (int)nslices, nq, d_idx, d_best, d_second);
+    count_launch();
+    ORB_CUDA_TRY(cudaGetLastError());
+    ORB_CUDA_TRY(cudaStreamSynchronize(s));  // `part` is freed on return
+  }
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int device,
+                             int32_t* idx, int32_t* best, int32_t* second) {
+  if (nq < 0 || ndb < 0 || (nq > 0 && (!q || !idx || !best || !second)) || (ndb > 0 && !db))
+    return ORB_GPU_ERR_ARG;
+  if (nq == 0) return ORB_GPU_OK;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  TmpDev dq, ddb, dout;
+  int rc;
+  if ((rc = dq.alloc((size_t)nq * 32)) || (rc = ddb.alloc((size_t)ndb * 32)) ||
+      (rc = dout.alloc((size_t)nq * 3 * sizeof(int32_t))))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice));
+  if (ndb) ORB_CUDA_TRY(cudaMemcpy(ddb.p, db, (size_t)ndb * 32, cudaMemcpyHostToDevice));
+  int32_t* o = dout.as<int32_t>();
+  if ((rc = orb_gpu_match_bruteforce_device(dq.as<uint8_t>(), nq, ddb.as<uint8_t>(), ndb, 0, o, o + nq,
+                                            o + 2 * (size_t)nq, nullptr)))
+    return rc;
+  ORB_CUDA_TRY(cudaDeviceSynchronize());
+  ORB_CUDA_TRY(cudaMemcpy(idx, o, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(best, o + nq, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(second, o + 2 * (size_t)nq, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_popc_peak(int device, double* popc_per_s) {
+  if (!popc_per_s) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int sms = 148;
+  ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  TmpDev out;
+  int rc = out.alloc(16);
+  if (rc) return rc;
+  cudaEvent_t e0, e1;
+  ORB_CUDA_TRY(cudaEventCreate(&e0));
+  ORB_CUDA_TRY(cudaEventCreate(&e1));
+  const int iters = 1 << 14, blocks = sms * 8, threads = 256;
+  popc_peak_kernel<<<blocks, threads>>>(12345u, 256, out.as<uint32_t>());  // warm-up
+  double bestv = 0;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0);
+    popc_peak_kernel<<<blocks, threads>>>(12345u + rep, iters, out.as<uint32_t>());
+    cudaEventRecord(e1);
+    ORB_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    bestv = std::max(bestv, (double)blocks * threads * iters * 8.0 / (ms * 1e-3));
+  }
+  count_launch(4);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  ORB_CUDA_TRY(cudaGetLastError());
+  *popc_per_s = bestv;
+  return ORB_GPU_OK;
+}
+
+}  // extern "C"

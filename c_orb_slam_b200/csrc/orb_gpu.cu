@@ -1,0 +1,431 @@
+// C ABI of the B200-native ORB front-end: handle management, host-side tables and the
+// extraction pipeline.  See include/orb_gpu.h for the contract and the reference citations.
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace orbgpu {
+
+static std::atomic<long long> g_launches{0};
+static thread_local std::string g_last_error;
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+void set_last_error(const char* what, cudaError_t e) {
+  g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
+}
+
+static inline int cv_round(double v) { return (int)std::lrint(v); }  // round-half-even, like cvRound
+static inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
+static inline int cv_ceil(double v) { int i = (int)v; return i + (i < v); }
+static inline int pow2ceil(long long v) { int p = 1; while (p < v) p <<= 1; return p; }
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// cv::resize INTER_LINEAR coefficient table of one axis (OpenCV 4.13 8U path): 11-bit weights.
+static void resize_axis_table(int S, int D, int* ofs, short* a0, short* a1) {
+  const double scale = 1.0 / ((double)D / (double)S);
+  for (int d = 0; d < D; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = cv_floor(f);
+    f -= (float)s;
+    if (s < 0) { f = 0.f; s = 0; }
+    if (s >= S - 1) { f = 0.f; s = S - 1; }
+    ofs[d] = s;
+    a0[d] = (short)std::lrintf((1.f - f) * 2048.f);
+    a1[d] = (short)std::lrintf(f * 2048.f);
+  }
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  int ensure(size_t need) {
+    if (need <= bytes) return ORB_GPU_OK;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    ORB_CUDA_TRY(cudaMalloc(&p, need));
+    bytes = need;
+    return ORB_GPU_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+struct OrbGpuExtractor {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  // constructor arguments and tables (reference src/ORBextractor.cc:410-470)
+  int nfeatures = 0, nlevels = 0, ini_th = 0, min_th = 0;
+  float scale_factor_f = 0;
+  double scale_factor = 0;  // the reference keeps a double member (include/ORBextractor.h:98)
+  std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+  std::vector<int> quota;
+  int umax[16];
+  int max_w = 0, max_h = 0, max_batch = 0;
+  // plan of the current geometry
+  Plan plan;
+  int plan_w = 0, plan_h = 0, plan_batch = 0;
+  std::vector<size_t> lvl_off;  // byte offset of each level inside pyr/blur (per batch capacity)
+  DevBuf pyr, blur, tables, cell_kp, cell_cnt, keys, pay, sel, sel_cnt, cand_cnt, status;
+  DevBuf out_kps, out_desc, out_n;
+  Scratch sc;
+  int last_nframes = 0;
+  bool have_result = false;
+  // level 0 of the last call (handle-owned copy, or the caller's device frames)
+  const uint8_t* last_l0 = nullptr;
+  int last_l0_pitch = 0;
+  long long last_l0_stride = 0;
+};
+
+static int build_tables(OrbGpuExtractor* h) {
+  const int L = h->nlevels;
+  h->scale.assign(L, 1.0f);
+  h->sigma2.assign(L, 1.0f);
+  for (int i = 1; i < L; ++i) {
+    h->scale[i] = (float)((double)h->scale[i - 1] * h->scale_factor);  // float * double member
+    h->sigma2[i] = h->scale[i] * h->scale[i];
+  }
+  h->inv_scale.resize(L);
+  h->inv_sigma2.resize(L);
+  for (int i = 0; i < L; ++i) {
+    h->inv_scale[i] = 1.0f / h->scale[i];
+    h->inv_sigma2[i] = 1.0f / h->sigma2[i];
+  }
+  h->quota.assign(L, 0);
+  const float factor = (float)(1.0 / h->scale_factor);
+  float desired = (float)h->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)L));
+  int sum = 0;
+  for (int l = 0; l < L - 1; ++l) {
+    h->quota[l] = cv_round(desired);
+    sum += h->quota[l];
+    desired *= factor;
+  }
+  h->quota[L - 1] = std::max(h->nfeatures - sum, 0);
+  // rows of the circular patch (:454-469)
+  const int vmax = cv_floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+  const int vmin = cv_ceil(kHalfPatch * std::sqrt(2.f) / 2);
+  const double hp2 = kHalfPatch * kHalfPatch;
+  for (int v = 0; v < 16; ++v) h->umax[v] = 0;
+  for (int v = 0; v <= vmax; ++v) h->umax[v] = cv_round(std::sqrt(hp2 - v * v));
+  for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+    while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+    h->umax[v] = v0;
+    ++v0;
+  }
+  return ORB_GPU_OK;
+}
+
+// Builds the plan for (w, h, batch): level geometry, resize tables, scratch layout; grows the
+// device buffers when needed.  Level 0 of the plan points at the handle's own level-0 buffer;
+// the device-input entry point overrides it with the caller's frames.
+static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
+  if (h->plan_w == w && h->plan_h == ht && batch <= h->plan_batch) return ORB_GPU_OK;
+  const int L = h->nlevels;
+  Plan p;
+  std::memset(&p, 0, sizeof(p));
+  p.nlevels = L; p.width = w; p.height = ht;
+  p.ini_th = h->ini_th; p.min_th = h->min_th;
+  for (int v = 0; v < 16; ++v) p.umax[v] = h->umax[v];
+  size_t table_bytes = 0, pyr_bytes = 0;
+  int cells = 0, slots = 0, cell_cap = 1;
+  long long keys = 0;
+  h->lvl_off.assign(L, 0);
+  std::vector<size_t> tab_off(L, 0);
+  for (int l = 0; l < L; ++l) {
+    LevelGeom& g = p.lv[l];
+    g.w = cv_round((float)w * h->inv_scale[l]);
+    g.h = cv_round((float)ht * h->inv_scale[l]);
+    g.pitch = (int)align_up((size_t)g.w, 64);
+    g.frame_stride = (long long)g.pitch * g.h;
+    g.bpitch = g.pitch; g.bframe_stride = g.frame_stride;
+    g.max_bx = g.w - kBorder; g.max_by = g.h - kBorder;
+    g.box_w = g.max_bx - kBorder; g.box_h = g.max_by - kBorder;
+    if (g.box_w < 30 || g.box_h < 30) return ORB_GPU_ERR_ARG;  // nCols/nRows would be 0 (:781-782)
+    const float width = (float)g.box_w, height = (float)g.box_h;
+    g.ncols = (int)(width / 30.f); g.nrows = (int)(height / 30.f);
+    g.wcell = (int)std::ceil(width / g.ncols); g.hcell = (int)std::ceil(height / g.nrows);
+    if (g.wcell + 6 > 250 || g.hcell + 6 > 250) return ORB_GPU_ERR_ARG;
+    g.cell_base = cells;
+    cells += g.ncols * g.nrows;
+    cell_cap = std::max(cell_cap, ((g.wcell + 1) / 2) * ((g.hcell + 1) / 2));
+    g.n_ini = (int)std::round(width / height);  // :543
+    if (g.n_ini < 1 || g.n_ini > 255) return ORB_GPU_ERR_ARG;  // portrait shapes: nIni == 0
+    g.hx = width / (float)g.n_ini;
+    g.quota = h->quota[l];
+    g.key_cap = pow2ceil(std::min<long long>(32768, std::max<long long>(1024, (long long)g.w * g.h / 16)));
+    g.key_base = keys;
+    keys += g.key_cap;
+    g.slot_base = slots;
+    slots += g.quota + 3;
+    g.scale = h->scale[l];
+    g.patch_size = (float)(int)(31.f * h->scale[l]);  // const int scaledPatchSize = 31*scale (:837)
+    h->lvl_off[l] = pyr_bytes;
+    pyr_bytes += align_up((size_t)g.frame_stride * batch, 256);
+    tab_off[l] = table_bytes;
+    table_bytes += align_up((size_t)g.w * 8 + (size_t)g.h * 8, 16);
+    if (quadtree_smem_bytes(p, l) > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
+  }
+  p.cells_per_frame = cells;
+  p.cell_cap = cell_cap;
+  p.keys_per_frame = keys;
+  p.slots_per_frame = slots;
+
+  cudaStreamSynchronize(h->stream);
+  int rc;
+  if ((rc = h->pyr.ensure(pyr_bytes)) || (rc = h->blur.ensure(pyr_bytes)) ||
+      (rc = h->tables.ensure(table_bytes)) ||
+      (rc = h->cell_kp.ensure((size_t)batch * cells * cell_cap * 4)) ||
+      (rc = h->cell_cnt.ensure((size_t)batch * cells * 4)) ||
+      (rc = h->keys.ensure((size_t)batch * keys * 8)) || (rc = h->pay.ensure((size_t)batch * keys * 4)) ||
+      (rc = h->sel.ensure((size_t)batch * slots * 4)) || (rc = h->sel_cnt.ensure((size_t)batch * L * 4)) ||
+      (rc = h->cand_cnt.ensure((size_t)batch * L * 4)) || (rc = h->status.ensure(16)))
+    return rc;
+
+  // resize tables: per level [xofs int][yofs int][ax0,ax1 short][ay0,ay1 short]
+  std::vector<uint8_t> tab(table_bytes, 0);
+  for (int l = 0; l < L; ++l) {
+    LevelGeom& g = p.lv[l];
+    g.img = (uint8_t*)h->pyr.p + h->lvl_off[l];
+    g.blur = (uint8_t*)h->blur.p + h->lvl_off[l];
+    uint8_t* base = tab.data() + tab_off[l];
+    int* xofs = (int*)base; int* yofs = xofs + g.w;
+    short* ax0 = (short*)(yofs + g.h); short* ax1 = ax0 + g.w;
+    short* ay0 = ax1 + g.w; short* ay1 = ay0 + g.h;
+    if (l > 0) {
+      resize_axis_table(p.lv[l - 1].w, g.w, xofs, ax0, ax1);
+      resize_axis_table(p.lv[l - 1].h, g.h, yofs, ay0, ay1);
+    }
+    uint8_t* dbase = (uint8_t*)h->tables.p + tab_off[l];
+    g.xofs = (const int*)dbase; g.yofs = g.xofs + g.w;
+    g.ax0 = (const short*)(g.yofs + g.h); g.ax1 = g.ax0 + g.w;
+    g.ay0 = g.ax1 + g.w; g.ay1 = g.ay0 + g.h;
+  }
+  ORB_CUDA_TRY(cudaMemcpyAsync(h->tables.p, tab.data(), table_bytes, cudaMemcpyHostToDevice, h->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(h->stream));  // `tab` dies at scope exit
+  h->sc.cell_kp = (uint32_t*)h->cell_kp.p; h->sc.cell_cnt = (uint32_t*)h->cell_cnt.p;
+  h->sc.keys = (uint64_t*)h->keys.p; h->sc.pay = (uint32_t*)h->pay.p;
+  h->sc.sel = (uint32_t*)h->sel.p; h->sc.sel_cnt = (int*)h->sel_cnt.p;
+  h->sc.cand_cnt = (int*)h->cand_cnt.p; h->sc.status = (int*)h->status.p;
+  h->plan = p;
+  h->plan_w = w; h->plan_h = ht; h->plan_batch = batch;
+  h->have_result = false;
+  return ORB_GPU_OK;
+}
+
+// Runs all stages for `nframes` frames whose level-0 images are described by plan.lv[0].
+static int run_pipeline(OrbGpuExtractor* h, const Plan& p, int nframes, OrbKeyPoint* d_kps,
+                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
+  int rc;
+  ORB_CUDA_TRY(cudaMemsetAsync(h->sc.status, 0, sizeof(int), s));
+  for (int l = 1; l < p.nlevels; ++l)
+    if ((rc = launch_resize_level(p, l, nframes, s))) return rc;
+  if ((rc = launch_fast_cells(p, h->sc, nframes, s))) return rc;
+  if ((rc = launch_quadtree(p, h->sc, nframes, s))) return rc;
+  if ((rc = launch_blur(p, nframes, s))) return rc;
+  if ((rc = launch_orient_desc(p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  return ORB_GPU_OK;
+}
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char* orb_gpu_version(void) { return "orb-b200 0.1 (sm_100a)"; }
+const char* orb_gpu_last_error(void) { return g_last_error.c_str(); }
+int64_t orb_gpu_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int orb_gpu_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                   int max_width, int max_height, int max_batch, int device, OrbGpuExtractor** out) {
+  if (!out) return ORB_GPU_ERR_ARG;
+  *out = nullptr;
+  if (nfeatures < 1 || nfeatures > 60000 || nlevels < 1 || nlevels > kMaxLevels || !(scaleFactor > 1.0f) ||
+      iniThFAST < 1 || iniThFAST > 254 || minThFAST < 1 || minThFAST > iniThFAST || max_width < 1 ||
+      max_height < 1 || max_width > kMaxDim || max_height > kMaxDim || max_batch < 1)
+    return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  OrbGpuExtractor* h = new OrbGpuExtractor();
+  h->device = device;
+  h->nfeatures = nfeatures; h->nlevels = nlevels; h->ini_th = iniThFAST; h->min_th = minThFAST;
+  h->scale_factor_f = scaleFactor; h->scale_factor = (double)scaleFactor;
+  h->max_w = max_width; h->max_h = max_height; h->max_batch = max_batch;
+  build_tables(h);
+  cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { set_last_error("cudaStreamCreate", e); delete h; return ORB_GPU_ERR_CUDA; }
+  int rc = upload_constants();
+  if (rc) { cudaStreamDestroy(h->stream); delete h; return rc; }
+  *out = h;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_destroy(OrbGpuExtractor* h) {
+  if (!h) return ORB_GPU_OK;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
+                    &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n};
+  for (DevBuf* b : bufs) b->release();
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_get_levels(const OrbGpuExtractor* h) { return h ? h->nlevels : ORB_GPU_ERR_ARG; }
+float orb_gpu_get_scale_factor(const OrbGpuExtractor* h) { return h ? (float)h->scale_factor : 0.f; }
+int orb_gpu_get_scale_tables(const OrbGpuExtractor* h, float* scale, float* inv_scale, float* sigma2,
+                             float* inv_sigma2) {
+  if (!h) return ORB_GPU_ERR_ARG;
+  for (int i = 0; i < h->nlevels; ++i) {
+    if (scale) scale[i] = h->scale[i];
+    if (inv_scale) inv_scale[i] = h->inv_scale[i];
+    if (sigma2) sigma2[i] = h->sigma2[i];
+    if (inv_sigma2) inv_sigma2[i] = h->inv_sigma2[i];
+  }
+  return ORB_GPU_OK;
+}
+int orb_gpu_get_features_per_level(const OrbGpuExtractor* h, int* quota, int* umax16) {
+  if (!h) return ORB_GPU_ERR_ARG;
+  if (quota) for (int i = 0; i < h->nlevels; ++i) quota[i] = h->quota[i];
+  if (umax16) for (int i = 0; i < 16; ++i) umax16[i] = h->umax[i];
+  return ORB_GPU_OK;
+}
+
+static int plan_batch_for(const OrbGpuExtractor* h, int w, int ht, int nb) {
+  return std::max(nb, (h->plan_w == w && h->plan_h == ht) ? h->plan_batch : 0);
+}
+
+int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, int nframes, int width,
+                                 int height, size_t stride, size_t frame_stride, OrbKeyPoint* d_kps,
+                                 uint8_t* d_desc, int capacity, int* d_n_out, int* d_status,
+                                 void* stream) {
+  if (!h || !d_frames || !d_kps || !d_desc || !d_n_out || nframes < 1 || capacity < 1)
+    return ORB_GPU_ERR_ARG;
+  if (width < 1 || height < 1 || width > h->max_w || height > h->max_h || nframes > h->max_batch ||
+      stride < (size_t)width || frame_stride < stride * (size_t)height)
+    return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  int rc = ensure_plan(h, width, height, plan_batch_for(h, width, height, nframes));
+  if (rc) return rc;
+  cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+  Plan p = h->plan;
+  p.lv[0].img = const_cast<uint8_t*>(d_frames);  // level 0 aliases the caller's frames
+  p.lv[0].pitch = (int)stride;
+  p.lv[0].frame_stride = (long long)frame_stride;
+  if ((rc = run_pipeline(h, p, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  if (d_status)
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToDevice, s));
+  h->last_nframes = nframes;
+  h->have_result = true;
+  h->last_l0 = d_frames; h->last_l0_pitch = (int)stride; h->last_l0_stride = (long long)frame_stride;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes, int width, int height,
+                          size_t stride, size_t frame_stride, OrbKeyPoint* kps, uint8_t* desc,
+                          int capacity, int* n_out) {
+  if (!h || !n_out || nframes < 0 || capacity < 0) return ORB_GPU_ERR_ARG;
+  for (int f = 0; f < nframes; ++f) n_out[f] = 0;
+  if (nframes == 0 || width == 0 || height == 0 || !frames) return ORB_GPU_OK;  // empty image (:1046)
+  if (!kps || !desc || capacity < 1) return ORB_GPU_ERR_ARG;
+  if (width < 0 || height < 0 || width > h->max_w || height > h->max_h || stride < (size_t)width)
+    return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  cudaStream_t s = h->stream;
+  int status_all = ORB_GPU_OK;
+  for (int f0 = 0; f0 < nframes; f0 += h->max_batch) {
+    const int nb = std::min(h->max_batch, nframes - f0);
+    int rc = ensure_plan(h, width, height, plan_batch_for(h, width, height, nb));
+    if (rc) return rc;
+    if ((rc = h->out_kps.ensure((size_t)h->plan_batch * capacity * sizeof(OrbKeyPoint))) ||
+        (rc = h->out_desc.ensure((size_t)h->plan_batch * capacity * 32)) ||
+        (rc = h->out_n.ensure((size_t)h->plan_batch * sizeof(int))))
+      return rc;
+    const Plan& p = h->plan;
+    const LevelGeom& l0 = p.lv[0];
+    const uint8_t* src = frames + (size_t)f0 * frame_stride;
+    if (frame_stride == stride * (size_t)height) {
+      ORB_CUDA_TRY(cudaMemcpy2DAsync(l0.img, l0.pitch, src, stride, width, (size_t)height * nb,
+                                     cudaMemcpyHostToDevice, s));
+    } else {
+      for (int f = 0; f < nb; ++f)
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(l0.img + (size_t)f * l0.frame_stride, l0.pitch,
+                                       src + (size_t)f * frame_stride, stride, width, height,
+                                       cudaMemcpyHostToDevice, s));
+    }
+    if ((rc = run_pipeline(h, p, nb, (OrbKeyPoint*)h->out_kps.p, (uint8_t*)h->out_desc.p, capacity,
+                           (int*)h->out_n.p, s)))
+      return rc;
+    int dev_status = 0;
+    ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0, h->out_n.p, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, s));
+    ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)f0 * capacity, h->out_kps.p,
+                                 (size_t)nb * capacity * sizeof(OrbKeyPoint), cudaMemcpyDeviceToHost, s));
+    ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)f0 * capacity * 32, h->out_desc.p, (size_t)nb * capacity * 32,
+                                 cudaMemcpyDeviceToHost, s));
+    ORB_CUDA_TRY(cudaMemcpyAsync(&dev_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToHost, s));
+    ORB_CUDA_TRY(cudaStreamSynchronize(s));
+    if (dev_status) status_all = dev_status;
+    h->last_nframes = nb;
+    h->have_result = true;
+    h->last_l0 = l0.img; h->last_l0_pitch = l0.pitch; h->last_l0_stride = l0.frame_stride;
+  }
+  return status_all;
+}
+
+int orb_gpu_extract(OrbGpuExtractor* h, const uint8_t* gray, int width, int height, size_t stride,
+                    OrbKeyPoint* kps, uint8_t* desc, int capacity, int* n_out) {
+  return orb_gpu_extract_batch(h, gray, 1, width, height, stride, stride * (size_t)height, kps, desc,
+                               capacity, n_out);
+}
+
+int orb_gpu_get_pyramid(OrbGpuExtractor* h, int frame, int level, int blurred, uint8_t* dst,
+                        size_t dst_stride, int* width, int* height) {
+  if (!h || level < 0 || level >= h->nlevels) return ORB_GPU_ERR_ARG;
+  if (!h->have_result) return ORB_GPU_ERR_STATE;
+  if (frame < 0 || frame >= h->last_nframes) return ORB_GPU_ERR_ARG;
+  const LevelGeom& g = h->plan.lv[level];
+  if (width) *width = g.w;
+  if (height) *height = g.h;
+  if (!dst) return ORB_GPU_OK;
+  if (dst_stride < (size_t)g.w) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  const uint8_t* src;
+  size_t spitch;
+  if (blurred) { src = g.blur + (size_t)frame * g.bframe_stride; spitch = (size_t)g.bpitch; }
+  else if (level == 0) { src = h->last_l0 + (size_t)frame * h->last_l0_stride; spitch = (size_t)h->last_l0_pitch; }
+  else { src = g.img + (size_t)frame * g.frame_stride; spitch = (size_t)g.pitch; }
+  ORB_CUDA_TRY(cudaDeviceSynchronize());
+  ORB_CUDA_TRY(cudaMemcpy2D(dst, dst_stride, src, spitch, g.w, g.h, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_get_candidates(OrbGpuExtractor* h, int frame, int level, float* xyr, int cap, int* n) {
+  if (!h || !n || level < 0 || level >= h->nlevels) return ORB_GPU_ERR_ARG;
+  if (!h->have_result) return ORB_GPU_ERR_STATE;
+  if (frame < 0 || frame >= h->last_nframes) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  ORB_CUDA_TRY(cudaDeviceSynchronize());
+  int cnt = 0;
+  ORB_CUDA_TRY(cudaMemcpy(&cnt, h->sc.cand_cnt + frame * h->nlevels + level, sizeof(int), cudaMemcpyDeviceToHost));
+  *n = cnt;
+  const int m = std::min(cnt, cap);
+  if (m <= 0 || !xyr) return ORB_GPU_OK;
+  float* d = nullptr;
+  ORB_CUDA_TRY(cudaMalloc(&d, (size_t)m * 3 * sizeof(float)));
+  int rc = launch_export_candidates(h->plan, h->sc, frame, level, d, m, h->stream);
+  if (!rc) {
+    cudaError_t e = cudaMemcpyAsync(xyr, d, (size_t)m * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) { set_last_error("get_candidates copy", e); rc = ORB_GPU_ERR_CUDA; }
+  }
+  cudaFree(d);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,356 @@
+// Windowed (guided) matching kernels: SearchByProjection-style search and the stereo row-band
+// search.  Reference: ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)
+// src/ORBmatcher.cc:45-129; Frame::AssignFeaturesToGrid / GetFeaturesInArea / PosInGrid
+// src/Frame.cc:230-245, 327-392; Frame::ComputeStereoMatches Hamming stage src/Frame.cc:466-549.
+//
+// The reference walks the map points in order and lets a point claim a keypoint, which hides it
+// from later points (:87-89, :123).  Here the per-query candidate lists (in GetFeaturesInArea
+// order) and all Hamming distances are computed in parallel, and the claims are found as the
+// fixpoint of "query i sees the claims of queries j < i": each round re-evaluates every query
+// against the previous round's claims; query i is final after at most i+1 rounds and the loop
+// ends when a round changes nothing, at which point the state equals the sequential result.
+#include <climits>
+
+#include "common.cuh"
+
+namespace orbgpu {
+
+constexpr int kGridCols = 64, kGridRows = 48;  // FRAME_GRID_COLS/ROWS, include/Frame.h:37-38
+constexpr int kCells = kGridCols * kGridRows;
+
+struct TmpDevW {
+  void* p = nullptr;
+  ~TmpDevW() { if (p) cudaFree(p); }
+  int alloc(size_t bytes) { ORB_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return ORB_GPU_OK; }
+  template <class T> T* as() { return (T*)p; }
+};
+
+__device__ __forceinline__ int hamming_rows(const uint4* a, const uint4* b) {
+  const uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// ---- grid: keypoint indices sorted by (cell, index); cell = ix*48 + iy (mGrid[ix][iy]) --------
+__global__ void __launch_bounds__(1024)
+grid_build_kernel(const OrbKeyPoint* __restrict__ kps, int nk, int nkpad, OrbFrameGrid g,
+                  uint32_t* __restrict__ sorted /*[nkpad]*/, int* __restrict__ cell_start /*[kCells+1]*/) {
+  extern __shared__ uint32_t s_key[];
+  for (int i = threadIdx.x; i < nkpad; i += blockDim.x) {
+    uint32_t key = 0xffffffffu;
+    if (i < nk) {
+      const int px = (int)roundf(__fmul_rn(__fsub_rn(kps[i].x, g.min_x), g.inv_w));  // PosInGrid
+      const int py = (int)roundf(__fmul_rn(__fsub_rn(kps[i].y, g.min_y), g.inv_h));
+      if (px >= 0 && px < kGridCols && py >= 0 && py < kGridRows)
+        key = ((uint32_t)(px * kGridRows + py) << 16) | (uint32_t)i;
+    }
+    s_key[i] = key;
+  }
+  __syncthreads();
+  for (int k = 2; k <= nkpad; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (nkpad >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int l = i | j;
+        const uint32_t x = s_key[i], y = s_key[l];
+        if ((x > y) == ((i & k) == 0)) { s_key[i] = y; s_key[l] = x; }
+      }
+      __syncthreads();
+    }
+  for (int i = threadIdx.x; i < nkpad; i += blockDim.x) sorted[i] = s_key[i];
+  for (int c = threadIdx.x; c <= kCells; c += blockDim.x) {
+    const uint32_t target = (uint32_t)c << 16;
+    int lo = 0, hi = nkpad;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (s_key[mid] < target) lo = mid + 1; else hi = mid;
+    }
+    cell_start[c] = lo;
+  }
+}
+
+// ---- candidates of every query, in GetFeaturesInArea order -----------------------------------
+// FILL == false: count only.  Entry = kp index | dist << 16 | octave << 25.
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+window_candidates_kernel(const OrbProjQuery* __restrict__ q, const uint4* __restrict__ qdesc, int nq,
+                         const OrbKeyPoint* __restrict__ kps, const uint4* __restrict__ kdesc,
+                         const float* __restrict__ u_right, OrbFrameGrid g,
+                         const float* __restrict__ sf, int nlevels, float th,
+                         const uint32_t* __restrict__ sorted, const int* __restrict__ cell_start,
+                         int* __restrict__ counts, const int* __restrict__ offsets,
+                         uint32_t* __restrict__ entries) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= nq) return;
+  const OrbProjQuery p = q[warp];
+  int n = 0;
+  if (p.valid && p.level >= 0 && p.level < nlevels) {
+    float r = (double)p.view_cos > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos (:131-137)
+    if (th != 1.0f) r = __fmul_rn(r, th);
+    const float rad = __fmul_rn(r, sf[p.level]);
+    const int min_level = p.level - 1, max_level = p.level;
+    const float bx = __fsub_rn(p.u, g.min_x), by = __fsub_rn(p.v, g.min_y);
+    const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(bx, rad), g.inv_w)));
+    const int c1 = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(bx, rad), g.inv_w)));
+    const int r0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(by, rad), g.inv_h)));
+    const int r1 = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(by, rad), g.inv_h)));
+    if (c0 < kGridCols && c1 >= 0 && r0 < kGridRows && r1 >= 0) {
+      uint32_t* dst = FILL ? entries + offsets[warp] : nullptr;
+      for (int ix = c0; ix <= c1; ++ix) {
+        // cells (ix, r0..r1) are contiguous in the sorted array
+        const int beg = cell_start[ix * kGridRows + r0], end = cell_start[ix * kGridRows + r1 + 1];
+        for (int e0 = beg; e0 < end; e0 += 32) {
+          const int e = e0 + lane;
+          bool ok = false;
+          int idx = 0, oct = 0;
+          if (e < end) {
+            idx = (int)(sorted[e] & 0xffffu);
+            const OrbKeyPoint kp = kps[idx];
+            oct = kp.octave;
+            ok = oct >= min_level && oct <= max_level &&
+                 fabsf(__fsub_rn(kp.x, p.u)) < rad && fabsf(__fsub_rn(kp.y, p.v)) < rad;
+            if (ok && u_right) {
+              const float ur = u_right[idx];
+              if (ur > 0 && fabsf(__fsub_rn(p.ur, ur)) > rad) ok = false;  // stereo gate (:91-96)
+            }
+          }
+          const unsigned m = __ballot_sync(0xffffffffu, ok);
+          if (FILL && ok) {
+            const int d = hamming_rows(qdesc + 2 * (size_t)warp, kdesc + 2 * (size_t)idx);
+            dst[n + __popc(m & ((1u << lane) - 1))] = (uint32_t)idx | ((uint32_t)d << 16) | ((uint32_t)oct << 25);
+          }
+          n += __popc(m);
+        }
+      }
+    }
+  }
+  if (!FILL && lane == 0) counts[warp] = n;
+}
+
+__global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int n, int* out /*[n+1]*/) {
+  __shared__ int s_part[1024];
+  const int T = blockDim.x, t = threadIdx.x;
+  const int chunk = (n + T - 1) / T, lo = min(t * chunk, n), hi = min(lo + chunk, n);
+  int sum = 0;
+  for (int k = lo; k < hi; ++k) sum += in[k];
+  s_part[t] = sum;
+  __syncthreads();
+  if (t == 0) {
+    int run = 0;
+    for (int k = 0; k < T; ++k) { const int v = s_part[k]; s_part[k] = run; run += v; }
+    out[n] = run;
+  }
+  __syncthreads();
+  int run = s_part[t];
+  for (int k = lo; k < hi; ++k) { out[k] = run; run += in[k]; }
+}
+
+// ---- ordered claim resolution as a fixpoint ---------------------------------------------------
+__global__ void __launch_bounds__(1024)
+window_resolve_kernel(const OrbProjQuery* __restrict__ q, int nq, int nk, const int* __restrict__ offsets,
+                      const uint32_t* __restrict__ entries, float nnratio, int th_high,
+                      uint8_t* __restrict__ blocked /*in/out [nk]*/, int* __restrict__ claim_a,
+                      int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
+                      int32_t* __restrict__ match_of_kp, int* __restrict__ nmatches) {
+  __shared__ int s_changed, s_count;
+  const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
+  int* prev = claim_a;
+  int* cur = claim_b;
+  for (int i = t; i < nq; i += T) prev[i] = -1;
+  __syncthreads();
+  for (int round = 0; round <= nq; ++round) {
+    for (int k = t; k < nk; k += T) minclaim[k] = INT_MAX;
+    if (t == 0) s_changed = 0;
+    __syncthreads();
+    for (int i = t; i < nq; i += T)
+      if (prev[i] >= 0 && q[i].has_obs) atomicMin(&minclaim[prev[i]], i);
+    __syncthreads();
+    for (int i = warp; i < nq; i += nwarps) {
+      const int beg = offsets[i], end = offsets[i + 1];
+      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position)
+      for (int e = beg + lane; e < end; e += 32) {
+        const uint32_t en = entries[e];
+        const int idx = (int)(en & 0xffffu);
+        if (blocked[idx] || minclaim[idx] < i) continue;  // keypoint already taken (:87-89)
+        const unsigned key = (((en >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
+        if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const unsigned lo = min(k1, o1), hi = max(k1, o1);
+        k2 = min(hi, min(k2, o2));
+        k1 = lo;
+      }
+      if (lane == 0) {
+        int result = -1;
+        if (k1 != 0xffffffffu) {
+          const int best_dist = (int)(k1 >> 20);
+          const uint32_t e1 = entries[beg + (k1 & 0xfffffu)];
+          int best_dist2 = 256, level2 = -1;
+          if (k2 != 0xffffffffu) {
+            best_dist2 = (int)(k2 >> 20);
+            level2 = (int)(entries[beg + (k2 & 0xfffffu)] >> 25);
+          }
+          const int level1 = (int)(e1 >> 25);
+          if (best_dist <= th_high &&
+              !(level1 == level2 && (float)best_dist > __fmul_rn(nnratio, (float)best_dist2)))
+            result = (int)(e1 & 0xffffu);
+        }
+        cur[i] = result;
+        if (result != prev[i]) s_changed = 1;
+      }
+    }
+    __syncthreads();
+    int* tmp = prev; prev = cur; cur = tmp;
+    const int changed = s_changed;
+    __syncthreads();
+    if (!changed) break;
+  }
+  // final state: last claimer per keypoint, blocked flags, match count
+  for (int k = t; k < nk; k += T) { match_of_kp[k] = -1; }
+  if (t == 0) s_count = 0;
+  __syncthreads();
+  int local = 0;
+  for (int i = t; i < nq; i += T)
+    if (prev[i] >= 0) {
+      atomicMax(&match_of_kp[prev[i]], i);
+      if (q[i].has_obs) blocked[prev[i]] = 1;
+      ++local;
+    }
+  if (local) atomicAdd(&s_count, local);
+  __syncthreads();
+  if (t == 0) *nmatches = s_count;
+}
+
+// ---- stereo row-band search -------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+stereo_match_kernel(const OrbKeyPoint* __restrict__ kl, const uint4* __restrict__ dl, int nl,
+                    const OrbKeyPoint* __restrict__ kr, const uint4* __restrict__ dr, int nr, int n_rows,
+                    const float* __restrict__ sf, float min_d, float max_d, int th_high,
+                    int32_t* __restrict__ best_idx_r, int32_t* __restrict__ best_dist) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= nl) return;
+  const OrbKeyPoint L = kl[warp];
+  const int row = (int)L.y;  // vRowIndices[vL] (Frame.cc:511)
+  const float min_u = __fsub_rn(L.x, max_d), max_u = __fsub_rn(L.x, min_d);
+  unsigned best = 0xffffffffu;
+  if (row >= 0 && row < n_rows && !(max_u < 0)) {
+    for (int i = lane; i < nr; i += 32) {
+      const OrbKeyPoint R = kr[i];
+      const float r = __fmul_rn(2.0f, sf[R.octave]);
+      const int maxr = (int)ceilf(__fadd_rn(R.y, r)), minr = (int)floorf(__fsub_rn(R.y, r));
+      if (row < minr || row > maxr) continue;
+      if (R.octave < L.octave - 1 || R.octave > L.octave + 1) continue;
+      if (!(R.x >= min_u && R.x <= max_u)) continue;
+      const unsigned d = (unsigned)hamming_rows(dl + 2 * (size_t)warp, dr + 2 * (size_t)i);
+      best = min(best, (d << 16) | (unsigned)i);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (lane == 0) {
+    const int d = best == 0xffffffffu ? 1 << 20 : (int)(best >> 16);
+    const bool ok = d < th_high;  // bestDist starts at TH_HIGH, strict '<' (:522,:543)
+    best_idx_r[warp] = ok ? (int)(best & 0xffffu) : -1;
+    best_dist[warp] = ok ? d : th_high;
+  }
+}
+
+}  // namespace orbgpu
+
+using namespace orbgpu;
+
+extern "C" {
+
+int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
+                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
+                                 float th, float nnratio, int th_high, int device, uint8_t* kp_blocked,
+                                 int32_t* match_of_kp, int* nmatches) {
+  if (nq < 0 || nk < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
+      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  *nmatches = 0;
+  for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
+  if (nq == 0 || nk == 0) return ORB_GPU_OK;
+  if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int nkpad = 2;
+  while (nkpad < nk) nkpad <<= 1;
+  TmpDevW dq, dqd, dk, dkd, dur, dsf, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn;
+  int rc;
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbProjQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
+      (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) || (rc = dkd.alloc((size_t)nk * 32)) ||
+      (rc = dur.alloc((size_t)nk * 4)) || (rc = dsf.alloc((size_t)nlevels * 4)) ||
+      (rc = dsorted.alloc((size_t)nkpad * 4)) || (rc = dcell.alloc((size_t)(kCells + 1) * 4)) ||
+      (rc = dcnt.alloc((size_t)nq * 4)) || (rc = doff.alloc((size_t)(nq + 1) * 4)) ||
+      (rc = dblk.alloc((size_t)nk)) || (rc = dca.alloc((size_t)nq * 4)) || (rc = dcb.alloc((size_t)nq * 4)) ||
+      (rc = dmin.alloc((size_t)nk * 4)) || (rc = dmatch.alloc((size_t)nk * 4)) || (rc = dn.alloc(4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbProjQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dqd.p, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk.p, kps, (size_t)nk * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dkd.p, kdesc, (size_t)nk * 32, cudaMemcpyHostToDevice));
+  if (u_right) ORB_CUDA_TRY(cudaMemcpy(dur.p, u_right, (size_t)nk * 4, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dsf.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dblk.p, kp_blocked, (size_t)nk, cudaMemcpyHostToDevice));
+
+  const size_t smem = (size_t)nkpad * 4;
+  if (smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grid_build_kernel<<<1, 1024, smem>>>(dk.as<OrbKeyPoint>(), nk, nkpad, grid, dsorted.as<uint32_t>(), dcell.as<int>());
+  const int blocks = (nq * 32 + 255) / 256;
+  const float* ur = u_right ? dur.as<float>() : nullptr;
+  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbProjQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), ur, grid, dsf.as<float>(), nlevels, th, dsorted.as<uint32_t>(), dcell.as<int>(),
+      dcnt.as<int>(), nullptr, nullptr);
+  exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
+  int total = 0;
+  ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
+  if ((rc = dent.alloc((size_t)total * 4))) return rc;
+  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbProjQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), ur, grid, dsf.as<float>(), nlevels, th, dsorted.as<uint32_t>(), dcell.as<int>(),
+      nullptr, doff.as<int>(), dent.as<uint32_t>());
+  window_resolve_kernel<<<1, 1024>>>(dq.as<OrbProjQuery>(), nq, nk, doff.as<int>(), dent.as<uint32_t>(), nnratio,
+      th_high, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(), dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+  count_launch(5);
+  ORB_CUDA_TRY(cudaGetLastError());
+  ORB_CUDA_TRY(cudaMemcpy(match_of_kp, dmatch.p, (size_t)nk * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(kp_blocked, dblk.p, (size_t)nk, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const OrbKeyPoint* kr,
+                         const uint8_t* dr, int nr, int n_rows, const float* scale_factors, int nlevels,
+                         float min_d, float max_d, int th_high, int device, int32_t* best_idx_r,
+                         int32_t* best_dist) {
+  if (nl < 0 || nr < 0 || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
+      (nl > 0 && (!kl || !dl || !best_idx_r || !best_dist)) || (nr > 0 && (!kr || !dr)) || nr > 65535)
+    return ORB_GPU_ERR_ARG;
+  if (nl == 0) return ORB_GPU_OK;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  TmpDevW a, b, c, d, e, f, g;
+  int rc;
+  if ((rc = a.alloc((size_t)nl * sizeof(OrbKeyPoint))) || (rc = b.alloc((size_t)nl * 32)) ||
+      (rc = c.alloc((size_t)nr * sizeof(OrbKeyPoint))) || (rc = d.alloc((size_t)nr * 32)) ||
+      (rc = e.alloc((size_t)nlevels * 4)) || (rc = f.alloc((size_t)nl * 4)) || (rc = g.alloc((size_t)nl * 4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(a.p, kl, (size_t)nl * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(b.p, dl, (size_t)nl * 32, cudaMemcpyHostToDevice));
+  if (nr) {
+    ORB_CUDA_TRY(cudaMemcpy(c.p, kr, (size_t)nr * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(d.p, dr, (size_t)nr * 32, cudaMemcpyHostToDevice));
+  }
+  ORB_CUDA_TRY(cudaMemcpy(e.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice));
+  stereo_match_kernel<<<(nl * 32 + 255) / 256, 256>>>(a.as<OrbKeyPoint>(), b.as<uint4>(), nl, c.as<OrbKeyPoint>(),
+      d.as<uint4>(), nr, n_rows, e.as<float>(), min_d, max_d, th_high, f.as<int32_t>(), g.as<int32_t>());
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  ORB_CUDA_TRY(cudaMemcpy(best_idx_r, f.p, (size_t)nl * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(best_dist, g.p, (size_t)nl * 4, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
+}
+
+}  // extern "C"

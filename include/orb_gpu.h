@@ -1,0 +1,179 @@
+/* orb_gpu.h -- C ABI of the B200-native ORB front-end (liborb_gpu.so).
+ *
+ * Drop-in boundary for ORB-SLAM2's (reference: junejunejune/c_orb_slam)
+ *   ORB_SLAM2::ORBextractor::operator()   include/ORBextractor.h:59-61, src/ORBextractor.cc:1043-1105
+ *   ORB_SLAM2::ORBmatcher Hamming matching include/ORBmatcher.h:37-102, src/ORBmatcher.cc
+ *   Frame::ComputeStereoMatches (Hamming) src/Frame.cc:466-549
+ * The reference has no FFI layer of its own; the C++ adapter classes in
+ * c_orb_slam_b200/csrc/adapter/ reproduce the two reference classes on top of these calls
+ * (INTEGRATION.md shows the binding a maintainer adds).
+ *
+ * Conventions: every function returns ORB_GPU_OK (0) or a negative OrbGpuStatus; nothing throws;
+ * there is NO CPU fallback -- without a CUDA device every compute call fails with
+ * ORB_GPU_ERR_CUDA.  Pointers named d_* are device pointers, all others are host pointers.
+ * `stream` arguments are cudaStream_t values passed as void* (NULL = the handle's own stream).
+ * A handle is single-caller; different handles may be used concurrently from different threads
+ * (the reference runs two extractors from two std::threads, src/Frame.cc:78-81).
+ */
+#ifndef ORB_GPU_H_
+#define ORB_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  ORB_GPU_OK = 0,
+  ORB_GPU_ERR_ARG = -1,      /* null pointer, bad size, unsupported shape (e.g. portrait: nIni == 0) */
+  ORB_GPU_ERR_CAPACITY = -2, /* caller buffer or an internal candidate pool too small */
+  ORB_GPU_ERR_CUDA = -3,     /* CUDA runtime error (no device, launch failure, OOM) */
+  ORB_GPU_ERR_STATE = -4     /* call order violated (e.g. pyramid requested before any extract) */
+} OrbGpuStatus;
+
+/* Layout-compatible with cv::KeyPoint (28 bytes): pt.x, pt.y, size, angle, response, octave,
+ * class_id.  Replaces std::vector<cv::KeyPoint> at include/ORBextractor.h:60. */
+typedef struct {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} OrbKeyPoint;
+
+typedef struct OrbGpuExtractor OrbGpuExtractor; /* owns one device, one stream, pyramids, scratch */
+
+#define ORB_GPU_MAX_LEVELS 16
+/* upper bound of keypoints per frame: nfeatures + 3 per level (the quadtree may overshoot its
+ * per-level quota by up to 3, src/ORBextractor.cc:730-731). */
+#define ORB_GPU_CAPACITY(nfeatures, nlevels) ((nfeatures) + 3 * (nlevels))
+
+/* ---- extractor ------------------------------------------------------------------------- */
+
+/* ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * (include/ORBextractor.h:51-52, src/ORBextractor.cc:410-470).  max_width/max_height/max_batch
+ * size the device buffers once; device = CUDA ordinal. */
+int orb_gpu_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                   int max_width, int max_height, int max_batch, int device,
+                   OrbGpuExtractor** out);
+int orb_gpu_destroy(OrbGpuExtractor* h);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors) (src/ORBextractor.cc:1043-1105);
+ * the mask is ignored by the reference (include/ORBextractor.h:58) and has no parameter here.
+ * gray: host, 8-bit single channel, `stride` bytes per row.  kps[capacity], desc[capacity*32].
+ * An empty image (width or height 0) returns OK with *n_out = 0 (:1046). */
+int orb_gpu_extract(OrbGpuExtractor* h, const uint8_t* gray, int width, int height, size_t stride,
+                    OrbKeyPoint* kps, uint8_t* desc, int capacity, int* n_out);
+
+/* Batched form (config 3 of BASELINE.json; no reference function -- defined as the call above
+ * applied independently to each frame).  Host frames: frame f starts at frames + f*frame_stride.
+ * Outputs are [nframes][capacity] / [nframes][capacity*32] / n_out[nframes]. */
+int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes, int width,
+                          int height, size_t stride, size_t frame_stride, OrbKeyPoint* kps,
+                          uint8_t* desc, int capacity, int* n_out);
+
+/* Same with every buffer resident in device memory; asynchronous on `stream`.  Level 0 of the
+ * pyramid aliases d_frames (no copy), so d_frames must stay valid until the stream has drained.
+ * d_status (optional, int[1]) receives 0 or ORB_GPU_ERR_CAPACITY from the device side. */
+int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, int nframes,
+                                 int width, int height, size_t stride, size_t frame_stride,
+                                 OrbKeyPoint* d_kps, uint8_t* d_desc, int capacity, int* d_n_out,
+                                 int* d_status, void* stream);
+
+/* Getters of include/ORBextractor.h:63-83 (values bit-identical to the reference's float/double
+ * mix) plus mnFeaturesPerLevel and umax for tests.  Arrays hold nlevels entries (umax: 16). */
+int orb_gpu_get_levels(const OrbGpuExtractor* h);
+float orb_gpu_get_scale_factor(const OrbGpuExtractor* h);
+int orb_gpu_get_scale_tables(const OrbGpuExtractor* h, float* scale, float* inv_scale,
+                             float* sigma2, float* inv_sigma2);
+int orb_gpu_get_features_per_level(const OrbGpuExtractor* h, int* quota, int* umax16);
+
+/* mvImagePyramid[level] of the last extract call (include/ORBextractor.h:85; read by stereo
+ * matching, src/Frame.cc:473,563,575,580).  frame = index inside the last batch.  blurred != 0
+ * returns the 7x7 sigma-2 blurred level used for the descriptors (:1085-1086) instead.
+ * dst may be NULL to query the size only. */
+int orb_gpu_get_pyramid(OrbGpuExtractor* h, int frame, int level, int blurred, uint8_t* dst,
+                        size_t dst_stride, int* width, int* height);
+
+/* Stage access for parity tests: FAST candidates of one level of one frame in the reference's
+ * arrival order (vToDistributeKeys, src/ORBextractor.cc:778-829): xyr[3*i] = x, y (relative to
+ * the 16-px border), response.  Returns count through *n (only min(*n, cap) are written). */
+int orb_gpu_get_candidates(OrbGpuExtractor* h, int frame, int level, float* xyr, int cap, int* n);
+
+/* ---- matcher --------------------------------------------------------------------------- */
+
+#define ORB_GPU_TH_HIGH 100 /* ORBmatcher::TH_HIGH, src/ORBmatcher.cc:37 */
+#define ORB_GPU_TH_LOW 50   /* ORBmatcher::TH_LOW,  src/ORBmatcher.cc:38 */
+#define ORB_GPU_HISTO_LENGTH 30
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663) for n pairs: dist[i] =
+ * hamming(a[i], b[i]), 32-byte rows, device pointers. */
+int orb_gpu_hamming_pairs_device(const uint8_t* d_a, const uint8_t* d_b, int n, int32_t* d_dist,
+                                 void* stream);
+
+/* Brute-force query x database top-2 (config 5; defined from ORBmatcher.cc:216-225,228-230):
+ * for each query, ascending scan of the database keeping best / lowest best index / second.
+ * idx = index + idx_base (int32; -1 if ndb == 0), best/second in 0..256.  Device pointers. */
+int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                    int32_t idx_base, int32_t* d_idx, int32_t* d_best,
+                                    int32_t* d_second, void* stream);
+/* Host-pointer form (copies in, computes on `device`, copies out). */
+int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int device,
+                             int32_t* idx, int32_t* best, int32_t* second);
+/* Exact merge of per-shard results of disjoint ascending index ranges (shard s holds rows
+ * [base_s, base_s + n_s) with base_s increasing in s): inputs are [nshards][nq].  This is the
+ * step that follows the NCCL all-gather when the database is sharded across GPUs. */
+int orb_gpu_merge_top2_device(const int32_t* d_idx, const int32_t* d_best, const int32_t* d_second,
+                              int nshards, int nq, int32_t* d_out_idx, int32_t* d_out_best,
+                              int32_t* d_out_second, void* stream);
+/* accept flags of ORBmatcher.cc:228-230: best <= th && (float)best < nnratio*(float)second */
+int orb_gpu_ratio_test_device(const int32_t* d_best, const int32_t* d_second, int nq, int th,
+                              float nnratio, uint8_t* d_accept, void* stream);
+
+/* The MapPoint fields ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) reads
+ * (src/ORBmatcher.cc:52-66). */
+typedef struct {
+  float u, v, ur;   /* mTrackProjX, mTrackProjY, mTrackProjXR */
+  int32_t level;    /* mnTrackScaleLevel */
+  float view_cos;   /* mTrackViewCos */
+  uint8_t valid;    /* mbTrackInView && !isBad() */
+  uint8_t has_obs;  /* Observations() > 0 */
+  uint8_t pad_[2];
+} OrbProjQuery;
+
+/* Frame grid parameters (src/Frame.cc:230-245,327-392; include/Frame.h:37-38: 64 x 48 cells). */
+typedef struct {
+  float min_x, min_y, inv_w, inv_h; /* mnMinX, mnMinY, mfGridElementWidthInv, ...HeightInv */
+} OrbFrameGrid;
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (src/ORBmatcher.cc:45-129)
+ * including GetFeaturesInArea candidate order and the in-order claim of keypoints.  Host
+ * pointers.  u_right may be NULL (monocular).  kp_blocked[nk] in/out: keypoint already holds a
+ * MapPoint with Observations()>0.  match_of_kp[nk] out: query index assigned or -1. */
+int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
+                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
+                                 float th, float nnratio, int th_high, int device,
+                                 uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches);
+
+/* Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): for each left keypoint
+ * the best right keypoint in its row band within the disparity and octave gates.
+ * best_idx_r[nl] = right index or -1, best_dist[nl] = distance (th_high when none). */
+int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const OrbKeyPoint* kr,
+                         const uint8_t* dr, int nr, int n_rows, const float* scale_factors,
+                         int nlevels, float min_d, float max_d, int th_high, int device,
+                         int32_t* best_idx_r, int32_t* best_dist);
+
+/* ---- diagnostics ----------------------------------------------------------------------- */
+const char* orb_gpu_version(void);
+/* last CUDA error string seen by this thread inside the library ("" if none) */
+const char* orb_gpu_last_error(void);
+/* number of kernels this library has launched in this process (for bench.py gpu_launches) */
+int64_t orb_gpu_launch_count(void);
+/* dependent-free POPC stream on all SMs: returns achieved 32-bit POPC/s (integer-pipe peak
+ * denominator for the Hamming roofline; MEASURED_PEAKS.json has no integer figure). */
+int orb_gpu_popc_peak(int device, double* popc_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORB_GPU_H_ */

@@ -1,0 +1,113 @@
+"""GPU parity of the extractor against the CPU oracle, through the C ABI (pytest -m gpu).
+
+Bar: pyramid pixels, FAST candidates (order included), keypoint set/order/octave/response,
+descriptors: bit-exact.  Angles: bit-exact in practice (same float ops), asserted <= 1e-3 deg.
+"""
+import numpy as np
+import pytest
+
+from c_orb_slam_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [("tum", 1000), ("euroc", 1200), ("kitti", 2000)]
+
+
+def _compare_frame(ex_o, ex_g, img, frame=0, kps_g=None, desc_g=None):
+    ko, do = ex_o(img)
+    if kps_g is None:
+        kps_g, desc_g = ex_g(img)
+    for l in range(8):
+        assert np.array_equal(ex_o.level_image(l), ex_g.pyramid_level(l, frame)), "pyramid level %d" % l
+        co, cg = ex_o.candidates(l), ex_g.candidates(l, frame)
+        assert co.shape == cg.shape and np.array_equal(co, cg), "FAST candidates level %d" % l
+        bo = ex_o.level_image(l, blurred=True)
+        if bo is not None:
+            assert np.array_equal(bo, ex_g.pyramid_level(l, frame, blurred=True)), "blur level %d" % l
+    assert len(ko) == len(kps_g)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(ko[f], kps_g[f]), f
+    dang = np.abs(ko["angle"].astype(np.float64) - kps_g["angle"].astype(np.float64))
+    assert dang.max() <= 1e-3, "angle tolerance 1e-3 deg (north_star)"
+    nbad = int((do != desc_g).any(axis=1).sum())
+    return dict(n=len(ko), angle_bitdiff=int((ko["angle"] != kps_g["angle"]).sum()), desc_rows_diff=nbad)
+
+
+@pytest.mark.parametrize("shape,nfeat", CONFIGS)
+def test_single_frame_parity(gpu, oracle, shape, nfeat):
+    W, H = synth.SHAPES[shape]
+    ex_o = oracle.Extractor(nfeat, 1.2, 8, 20, 7)
+    ex_g = gpu.ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=W, max_height=H)
+    t = ex_o.tables()
+    assert np.array_equal(t["scale"], ex_g.GetScaleFactors())
+    assert np.array_equal(t["inv_scale"], ex_g.GetInverseScaleFactors())
+    assert np.array_equal(t["sigma2"], ex_g.GetScaleSigmaSquares())
+    assert np.array_equal(t["inv_sigma2"], ex_g.GetInverseScaleSigmaSquares())
+    q, u = ex_g.features_per_level()
+    assert np.array_equal(q, t["quota"]) and np.array_equal(u, t["umax"])
+    assert ex_g.GetLevels() == 8 and abs(ex_g.GetScaleFactor() - 1.2) < 1e-6
+    for seed in (1000, 1001):
+        r = _compare_frame(ex_o, ex_g, synth.make_frame(W, H, seed))
+        assert r["desc_rows_diff"] == 0 and r["angle_bitdiff"] == 0, r
+
+
+def test_batch_matches_single(gpu, oracle):
+    W, H = synth.SHAPES["euroc"]
+    B = 6
+    frames = synth.make_frames(W, H, B, seed0=2000)
+    ex_g = gpu.ORBextractor(1200, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=4)  # forces 2 chunks
+    n, kps, desc = ex_g.extract_batch(frames)
+    ex_o = oracle.Extractor(1200, 1.2, 8, 20, 7)
+    for f in range(B):
+        ko, do = ex_o(frames[f])
+        assert n[f] == len(ko)
+        assert np.array_equal(kps[f, :n[f]], ko) and np.array_equal(desc[f, :n[f]], do)
+
+
+def test_strided_input_and_reuse(gpu, oracle):
+    W, H = 640, 480
+    big = np.zeros((H, W + 37), np.uint8)
+    big[:, :W] = synth.make_frame(W, H, 77)
+    ex_g = gpu.ORBextractor(1000, 1.2, 8, 20, 7, max_width=800, max_height=600)
+    ex_o = oracle.Extractor(1000, 1.2, 8, 20, 7)
+    k1, d1 = ex_g(big[:, :W])
+    ko, do = ex_o(np.ascontiguousarray(big[:, :W]))
+    assert np.array_equal(k1, ko) and np.array_equal(d1, do)
+    # same handle, different geometry, then back
+    small = synth.make_frame(400, 300, 5)
+    k2, d2 = ex_g(small)
+    ko2, do2 = ex_o(small)
+    assert np.array_equal(k2, ko2) and np.array_equal(d2, do2)
+    k3, d3 = ex_g(big[:, :W])
+    assert np.array_equal(k3, ko) and np.array_equal(d3, do)
+
+
+def test_edge_cases(gpu, oracle):
+    ex_g = gpu.ORBextractor(500, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    k, d = ex_g(np.empty((0, 0), np.uint8))            # empty image: silent return (:1046)
+    assert len(k) == 0 and d.shape == (0, 32)
+    flat = np.full((480, 640), 128, np.uint8)           # no corners anywhere
+    k, d = ex_g(flat)
+    assert len(k) == 0
+    ko, _ = oracle.Extractor(500, 1.2, 8, 20, 7)(flat)
+    assert len(ko) == 0
+    with pytest.raises(gpu.OrbGpuError):                # level 7 would have no FAST cell
+        ex_g(np.zeros((100, 100), np.uint8))
+    with pytest.raises(gpu.OrbGpuError):                # larger than max_width
+        ex_g(np.zeros((480, 700), np.uint8))
+    # low-texture image: exercises the minThFAST retry and under-full quotas
+    rng = np.random.default_rng(3)
+    soft = (128 + 12 * rng.standard_normal((480, 640))).clip(0, 255).astype(np.uint8)
+    k, d = ex_g(soft)
+    ko, do = oracle.Extractor(500, 1.2, 8, 20, 7)(soft)
+    assert np.array_equal(k, ko) and np.array_equal(d, do)
+
+
+def test_non_default_parameters(gpu, oracle):
+    img = synth.make_frame(752, 480, 4242)
+    for args in ((300, 1.5, 4, 30, 10), (3000, 1.1, 10, 15, 5)):
+        ex_g = gpu.ORBextractor(*args, max_width=752, max_height=480)
+        ex_o = oracle.Extractor(*args)
+        k, d = ex_g(img)
+        ko, do = ex_o(img)
+        assert np.array_equal(k, ko) and np.array_equal(d, do), args

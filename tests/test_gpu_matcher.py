@@ -1,0 +1,101 @@
+"""GPU parity of the Hamming matchers against the CPU oracle (pytest -m gpu): bit-exact."""
+import numpy as np
+import pytest
+
+from c_orb_slam_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nq,ndb", [(1, 1), (7, 300), (512, 20000), (1000, 70001)])
+@pytest.mark.parametrize("variant", [(0, 1), (1, 2), (1, 4)])
+def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
+    q, db = synth.make_match_set(nq, ndb, seed=11)
+    gpu.lib().orb_gpu_set_bruteforce_variant(*variant)
+    m = gpu.ORBmatcher(0.9)
+    idx, best, second = m.match_bruteforce(q, db)
+    oi, ob, os_ = oracle.match_bruteforce(q, db, threads=8)
+    assert np.array_equal(best, ob) and np.array_equal(second, os_) and np.array_equal(idx, oi)
+    acc = m.accept(best, second, th=m.TH_HIGH)
+    ref = (ob <= 100) & (ob.astype(np.float32) < np.float32(0.9) * os_.astype(np.float32))
+    assert np.array_equal(acc, ref)
+    gpu.lib().orb_gpu_set_bruteforce_variant(1, 2)
+
+
+def test_bruteforce_empty_and_ties(gpu, oracle):
+    m = gpu.ORBmatcher()
+    q = synth.random_descriptors(5, 1)
+    idx, best, second = m.match_bruteforce(q, np.empty((0, 32), np.uint8))
+    assert (idx == -1).all() and (best == 256).all() and (second == 256).all()
+    db = np.repeat(q[:1], 9, axis=0)                      # nine identical rows: lowest index wins
+    idx, best, second = m.match_bruteforce(q[:1], db)
+    assert idx[0] == 0 and best[0] == 0 and second[0] == 0
+    inv = (~q[:1]).astype(np.uint8)                       # distance 256 never beats the initial 256
+    idx, best, second = m.match_bruteforce(q[:1], inv)
+    oi, ob, os_ = oracle.match_bruteforce(q[:1], inv)
+    assert idx[0] == oi[0] == -1 and best[0] == ob[0] == 256
+
+
+def _frame_from_extractor(oracle, W, H, seed, nfeat):
+    ex = oracle.Extractor(nfeat, 1.2, 8, 20, 7)
+    kps, desc = ex(synth.make_frame(W, H, seed))
+    return ex, kps, desc
+
+
+def _projection_case(oracle, seed, th, stereo):
+    W, H = 640, 480
+    ex, kps, desc = _frame_from_extractor(oracle, W, H, seed, 2000)
+    rng = np.random.default_rng(seed)
+    nk = len(kps)
+    sf = ex.tables()["scale"]
+    M = 2000
+    proj = np.zeros(M, oracle.PROJ_DTYPE)
+    qdesc = np.empty((M, 32), np.uint8)
+    src = rng.integers(0, nk, M)
+    near = rng.random(M) < 0.75
+    proj["u"] = np.where(near, kps["x"][src] + rng.normal(0, 2, M), rng.uniform(0, W, M)).astype(np.float32)
+    proj["v"] = np.where(near, kps["y"][src] + rng.normal(0, 2, M), rng.uniform(0, H, M)).astype(np.float32)
+    proj["level"] = np.clip(kps["octave"][src] + rng.integers(0, 2, M), 0, 7)
+    proj["view_cos"] = rng.uniform(0.99, 1.0, M).astype(np.float32)
+    proj["valid"] = rng.random(M) < 0.95
+    proj["has_obs"] = rng.random(M) < 0.9
+    qdesc[:] = synth.flip_bits(desc[src], rng.integers(0, 61, M), rng)
+    # duplicates: several map points aimed at the same keypoint -> ordered claims matter
+    dup = rng.integers(0, M, 300)
+    proj[dup] = proj[(dup + 1) % M]
+    qdesc[dup] = qdesc[(dup + 1) % M]
+    u_right = None
+    if stereo:
+        u_right = np.where(rng.random(nk) < 0.6, kps["x"] - rng.uniform(1, 40, nk), -1).astype(np.float32)
+        proj["ur"] = (proj["u"] - rng.uniform(1, 40, M)).astype(np.float32)
+    blocked = (rng.random(nk) < 0.05).astype(np.uint8)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(W), np.float32(48) / np.float32(H))
+    return kps, desc, proj, qdesc, u_right, blocked, grid, sf
+
+
+@pytest.mark.parametrize("th,stereo,seed", [(1.0, False, 1), (3.0, False, 2), (5.0, True, 3), (15.0, True, 4)])
+def test_search_by_projection(gpu, oracle, th, stereo, seed):
+    kps, desc, proj, qdesc, u_right, blocked, grid, sf = _projection_case(oracle, seed, th, stereo)
+    n_o, match_o, blocked_o = oracle.search_by_projection(proj, qdesc, kps, desc, u_right, grid, sf, th, 0.9,
+                                                          100, blocked.copy())
+    frame = dict(kps=kps, desc=desc, u_right=u_right, grid=grid, scale_factors=sf, blocked=blocked.copy())
+    pg = np.zeros(len(proj), gpu.PROJ_DTYPE)
+    for f in ("u", "v", "ur", "level", "view_cos", "valid", "has_obs"):
+        pg[f] = proj[f]
+    n_g, match_g = gpu.ORBmatcher(0.9).SearchByProjection(frame, dict(proj=pg, desc=qdesc), th)
+    assert n_o > 100
+    assert n_g == n_o and np.array_equal(match_g, match_o) and np.array_equal(frame["blocked"], blocked_o)
+
+
+def test_stereo_match(gpu, oracle):
+    W, H = synth.SHAPES["kitti"]
+    left, right = synth.make_stereo_pair(W, H, 31)
+    exl = oracle.Extractor(2000, 1.2, 8, 20, 7)
+    kl, dl = exl(left)
+    kr, dr = oracle.Extractor(2000, 1.2, 8, 20, 7)(right)
+    sf = exl.tables()["scale"]
+    max_d = np.float32(718.856)  # bf/mb = fx (KITTI00-02.yaml; Frame.cc:496-498)
+    bi_o, bd_o = oracle.stereo_match(kl, dl, kr, dr, H, sf, 0.0, max_d)
+    bi_g, bd_g = gpu.ORBmatcher().stereo_match(kl, dl, kr, dr, H, sf, 0.0, max_d)
+    assert (bi_o >= 0).sum() > 200
+    assert np.array_equal(bi_g, bi_o) and np.array_equal(bd_g, bd_o)
