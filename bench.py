@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""Benchmark of the ORB front-end hot path (BASELINE.json metric: "ORB extract frames/s (TUM 640x480,
+1000 kp); Hamming Gpairs/s").
+
+  python bench.py --gpus N --steps K --warmup W            # this repo (CUDA, sm_100a)
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU code on host cores
+
+One step = ORBextractor::operator() over one batch of synthetic TUM-shaped frames (TUM1.yaml
+settings: 1000 features, 8 levels, 1.2, iniThFAST 20, minThFAST 7).  `value` is frames/s with the
+frames resident in HBM (device C-ABI, CUDA events on the launching stream); `e2e` is the same work
+through the host-pointer C-ABI call with pinned host buffers, H2D/D2H inside the timed region.
+Frames shard across ranks (independent units, no collective): weak scaling.  A secondary object
+`hamming` reports the brute-force 4096 x 10M top-2 matcher (database sharded across ranks, one NCCL
+all-gather of the per-rank top-2, exact merge).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SETTINGS = dict(nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7)  # Examples/Monocular/TUM1.yaml:30-43
+W, H = 640, 480
+ALGO_BYTES_PER_FRAME = 4481474      # pyramid r/w + FAST read + blur r/w + K*60
+P_PIXELS = 950532                   # sum of level pixels, TUM
+METRIC = "ORB extract frames/s (TUM 640x480, 1000 kp); Hamming Gpairs/s @1-8 GPU"
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs (NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+            while not self.stop_flag:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.02)
+        except Exception as e:  # NVML missing: report nothing rather than guess
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_reference_extract(frames, threads):
+    """Times the reference's CPU extractor on `frames` with `threads` host threads.
+    Returns (seconds, kind, total_keypoints)."""
+    from oracle import pyoracle as O
+    O.lib()
+    s = SETTINGS
+    if os.path.exists(O.REF_PATH):
+        t0 = time.perf_counter()
+        counts = O.ref_extract_batch(frames, s["nfeatures"], s["scale"], s["nlevels"], s["ini_th"], s["min_th"], threads)
+        return time.perf_counter() - t0, "reference", int(counts.sum())
+    t0 = time.perf_counter()
+    counts, _, _ = O.extract_batch(frames, s["nfeatures"], s["scale"], s["nlevels"], s["ini_th"], s["min_th"],
+                                   threads, want_output=False)
+    return time.perf_counter() - t0, "port", int(counts.sum())
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from c_orb_slam_b200 import synth
+    cores = os.cpu_count() or 1
+    sample = args.cpu_frames
+    frames = synth.make_frames_fast(W, H, sample, seed0=1000)
+    for _ in range(args.warmup):
+        cpu_reference_extract(frames[:max(cores, 8)], cores)
+    t = 0.0
+    kind = "port"
+    for _ in range(args.steps):
+        dt, kind, _ = cpu_reference_extract(frames, cores)
+        t += dt
+    fps = sample * args.steps / t
+    desc = ("%d synthetic TUM frames per step, ORBextractor.cc %s, %d host threads (frames in parallel)"
+            % (sample, "compiled verbatim over oracle/opencv_shim (OpenCV primitives restated, pinned to cv2 4.13.0)"
+               if kind == "reference" else "restated (oracle port)", cores))
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "TUM 640x480, 1000 features, 8 levels, 1.2, FAST 20/7 (configs[0]); CPU sample of %d frames/step" % sample},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": desc},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import c_orb_slam_b200 as orb
+    from c_orb_slam_b200 import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    # a real (non-legacy) stream, so the C-ABI launches and the torch events share one stream
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    s = SETTINGS
+    B = args.batch
+    cap = s["nfeatures"] + 3 * s["nlevels"]
+    frames_np = synth.make_frames_fast(W, H, B, seed0=1000 + 100000 * rank)
+    h_frames = torch.from_numpy(frames_np).pin_memory()
+    d_frames = h_frames.to(dev)
+    d_kps = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev)
+    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(B, dtype=torch.int32, device=dev)
+    d_status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ex = orb.ORBextractor(s["nfeatures"], s["scale"], s["nlevels"], s["ini_th"], s["min_th"], max_width=W,
+                          max_height=H, max_batch=B, device=local)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device():
+        ex.extract_batch_device(d_frames.data_ptr(), B, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(),
+                                d_n.data_ptr(), d_status.data_ptr(), stream)
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    if int(d_status.item()) != 0:
+        raise SystemExit("device-side capacity error during warm-up")
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = orb.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    launches = orb.launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.result()
+    kp_total = int(d_n.sum().item())
+    value = world * B * args.steps / (ms * 1e-3)
+
+    # per-stage device times (same inputs, K more steps; each readout synchronises, so these steps are
+    # outside the timed region above)
+    ex.set_stage_timing(True)
+    acc = {}
+    for _ in range(args.steps):
+        step_device()
+        for k, v in ex.stage_ms().items():
+            acc[k] = acc.get(k, 0.0) + v / args.steps
+    ex.set_stage_timing(False)
+    peaks, peak_kind = measured_peaks()
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    top = max(acc, key=acc.get)
+    # algorithmic bytes per frame of each stage (DESIGN.md "Kernels"): pyramid reads l0..l6 + writes l1..l7,
+    # FAST reads P, blur reads+writes P, quadtree/orient touch O(candidates)/O(K*60) only
+    stage_bytes = {"pyramid": 926546 + 643332, "fast": P_PIXELS, "blur": 2 * P_PIXELS,
+                   "quadtree": 9000 * 12, "orient_desc": 60 * s["nfeatures"]}
+    achieved = stage_bytes[top] * B / (acc[top] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                "frac": achieved / hbm, "traffic": None, "peak_kind": peak_kind,
+                "stage_ms": acc, "launches_per_step": launches / max(1, args.steps)}
+    pipe_gbs = ALGO_BYTES_PER_FRAME * B * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    roofline["pipeline"] = {"achieved": pipe_gbs, "frac": pipe_gbs / hbm, "bytes_per_frame": ALGO_BYTES_PER_FRAME}
+
+    # ---- end to end through the host-pointer C-ABI (pinned host buffers, H2D + D2H inside) ----
+    h_kps = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    h_desc = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    h_n = torch.zeros(B, dtype=torch.int32).pin_memory()
+    L = orb.lib()
+
+    def step_host():
+        rc = L.orb_gpu_extract_batch(ex._h, h_frames.data_ptr(), B, W, H, W, W * H, h_kps.data_ptr(),
+                                     h_desc.data_ptr(), cap, h_n.data_ptr())
+        if rc:
+            raise SystemExit("orb_gpu_extract_batch failed: %d" % rc)
+
+    for _ in range(2):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_host()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e = {"value": world * B * args.steps / e2e_s, "unit": "frames/s",
+           "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 4)),
+           "ms_per_step": 1e3 * e2e_s / args.steps}
+    assert int(h_n.sum().item()) == kp_total, "host and device paths disagree"
+
+    # ---- Hamming brute force: 4096 queries x 10M rows, database sharded by rank -----------------
+    hamming = None
+    if not args.skip_hamming:
+        nq, ndb_total = 4096, args.db_rows
+        lo = ndb_total * rank // world
+        hi = ndb_total * (rank + 1) // world
+        g = torch.Generator(device=dev)
+        g.manual_seed(7 + rank)
+        db = torch.randint(0, 256, (hi - lo, 32), dtype=torch.uint8, device=dev, generator=g)
+        g.manual_seed(99)
+        q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)
+        part = torch.empty((3, nq), dtype=torch.int32, device=dev)
+        gathered = torch.empty((world, 3, nq), dtype=torch.int32, device=dev)
+        merged = torch.empty((3, nq), dtype=torch.int32, device=dev)
+
+        def step_match():
+            rc = L.orb_gpu_match_bruteforce_device(q.data_ptr(), nq, db.data_ptr(), hi - lo, lo, part[0].data_ptr(),
+                                                   part[1].data_ptr(), part[2].data_ptr(), stream)
+            if rc:
+                raise SystemExit("orb_gpu_match_bruteforce_device failed: %d" % rc)
+            if world > 1:
+                dist.all_gather_into_tensor(gathered, part)  # 48 KB per rank over NVLink
+                gt = gathered.permute(1, 0, 2).contiguous()  # [3][world][nq]
+                rc = L.orb_gpu_merge_top2_device(gt[0].data_ptr(), gt[1].data_ptr(), gt[2].data_ptr(), world, nq,
+                                                 merged[0].data_ptr(), merged[1].data_ptr(), merged[2].data_ptr(), stream)
+                if rc:
+                    raise SystemExit("orb_gpu_merge_top2_device failed: %d" % rc)
+
+        for _ in range(2):
+            step_match()
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        hsteps = max(1, min(args.steps, 5))
+        h0.record()
+        for _ in range(hsteps):
+            step_match()
+        h1.record()
+        barrier()
+        hms = max_over_ranks(h0.elapsed_time(h1))
+        gpairs = nq * ndb_total * hsteps / (hms * 1e-3) / 1e9
+        popc = orb.popc_peak(local)
+        hamming = {"value": gpairs, "unit": "Gpairs/s", "scaling": "strong", "ms_per_step": hms / hsteps,
+                   "config": {"workload": "brute-force top-2, %d queries x %d database rows, database sharded over %d GPU(s), "
+                                          "top-2 all-gather + exact merge" % (nq, ndb_total, world)},
+                   "roofline": {"bound": "int-pipe (POPC)", "achieved": gpairs * 8 / world, "peak": popc / 1e9,
+                                "unit": "GPOPC-equivalents/s per GPU (8 per pair)", "frac": gpairs * 8 / world / (popc / 1e9),
+                                "peak_kind": "measured here: dependent-free POPC stream, orb_gpu_popc_peak"}}
+
+    # ---- CPU baseline (rank 0, N=1 only): the reference's CPU extractor on a bounded sample -----
+    cpu = None
+    if world == 1 and not args.skip_cpu:
+        cores = os.cpu_count() or 1
+        sample = args.cpu_frames
+        cpu_reference_extract(frames_np[:max(8, cores)], cores)
+        dt, kind, nkp = cpu_reference_extract(frames_np[:sample], cores)
+        dt1, _, _ = cpu_reference_extract(frames_np[:max(4, sample // 16)], 1)
+        cpu = {"value": sample / dt, "unit": "frames/s", "cores": cores, "kind": kind,
+               "sample": "%d of the %d bench frames, %d host threads (frames in parallel); single-thread rate %.1f frames/s"
+                         % (sample, B, cores, max(4, sample // 16) / dt1),
+               "note": "ORBextractor.cc verbatim over oracle/opencv_shim (restated OpenCV primitives, not OpenCV's SIMD)"
+                       if kind == "reference" else "oracle port"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "TUM 640x480 (configs[0]: 1000 features, 8 levels, 1.2, FAST 20/7), "
+                                       "batch of %d frames per GPU per step" % B,
+                           "frames_per_gpu": B, "l2": "inputs larger than L2 (%.0f MB of frames, %.0f MB of pyramids per step)"
+                                                      % (B * W * H / 1e6, B * 1158012 / 1e6),
+                           "keypoints_per_frame": kp_total / B},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks, "hamming": hamming}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=512, help="frames per GPU per step")
+    ap.add_argument("--db-rows", type=int, default=10_000_000)
+    ap.add_argument("--cpu-frames", type=int, default=256, help="frames in the bounded CPU sample")
+    ap.add_argument("--skip-hamming", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -99,6 +99,8 @@ def lib():
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
+        L.orb_gpu_set_stage_timing.argtypes = [C.c_void_p, C.c_int]
+        L.orb_gpu_get_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
         L.orb_gpu_popc_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
         L.orb_gpu_set_bruteforce_variant.argtypes = [C.c_int, C.c_int]
         _lib = L
@@ -206,6 +208,15 @@ class ORBextractor:
         _check(lib().orb_gpu_extract_batch_device(self._h, d_frames_ptr, B, W, H, stride, frame_stride,
                                                   d_kps_ptr, d_desc_ptr, capacity or self.capacity, d_n_ptr,
                                                   d_status_ptr, stream), "orb_gpu_extract_batch_device")
+
+    def set_stage_timing(self, enable=True):
+        _check(lib().orb_gpu_set_stage_timing(self._h, int(enable)), "orb_gpu_set_stage_timing")
+
+    def stage_ms(self):
+        """Device ms of the last call: dict(pyramid, fast, quadtree, blur, orient_desc)."""
+        ms = np.empty(5, np.float32)
+        _check(lib().orb_gpu_get_stage_ms(self._h, _p(ms)), "orb_gpu_get_stage_ms")
+        return dict(zip(["pyramid", "fast", "quadtree", "blur", "orient_desc"], ms.tolist()))
 
     def pyramid_level(self, level, frame=0, blurred=False):
         """mvImagePyramid[level] of the last call (ORBextractor.h:85)."""

@@ -82,6 +82,9 @@ struct OrbGpuExtractor {
   const uint8_t* last_l0 = nullptr;
   int last_l0_pitch = 0;
   long long last_l0_stride = 0;
+  // optional per-stage CUDA-event timing (bench/roofline)
+  bool timing = false;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 static int build_tables(OrbGpuExtractor* h) {
@@ -224,12 +227,19 @@ static int run_pipeline(OrbGpuExtractor* h, const Plan& p, int nframes, OrbKeyPo
                         uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
   int rc;
   ORB_CUDA_TRY(cudaMemsetAsync(h->sc.status, 0, sizeof(int), s));
+  const bool tm = h->timing;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[0], s));
   for (int l = 1; l < p.nlevels; ++l)
     if ((rc = launch_resize_level(p, l, nframes, s))) return rc;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[1], s));
   if ((rc = launch_fast_cells(p, h->sc, nframes, s))) return rc;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[2], s));
   if ((rc = launch_quadtree(p, h->sc, nframes, s))) return rc;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[3], s));
   if ((rc = launch_blur(p, nframes, s))) return rc;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[4], s));
   if ((rc = launch_orient_desc(p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[5], s));
   return ORB_GPU_OK;
 }
 
@@ -272,8 +282,28 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
                     &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n};
   for (DevBuf* b : bufs) b->release();
+  for (int i = 0; i < 6; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   cudaStreamDestroy(h->stream);
   delete h;
+  return ORB_GPU_OK;
+}
+
+// Per-stage device times of the LAST extract call on this handle: pyramid, fast, quadtree, blur,
+// orient+descriptor (milliseconds, CUDA events on the stream the kernels ran on).
+int orb_gpu_set_stage_timing(OrbGpuExtractor* h, int enable) {
+  if (!h) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  if (enable && !h->ev[0])
+    for (int i = 0; i < 6; ++i) ORB_CUDA_TRY(cudaEventCreate(&h->ev[i]));
+  h->timing = enable != 0;
+  return ORB_GPU_OK;
+}
+int orb_gpu_get_stage_ms(OrbGpuExtractor* h, float* ms5) {
+  if (!h || !ms5) return ORB_GPU_ERR_ARG;
+  if (!h->timing || !h->have_result) return ORB_GPU_ERR_STATE;
+  ORB_CUDA_TRY(cudaSetDevice(h->device));
+  ORB_CUDA_TRY(cudaEventSynchronize(h->ev[5]));
+  for (int i = 0; i < 5; ++i) ORB_CUDA_TRY(cudaEventElapsedTime(&ms5[i], h->ev[i], h->ev[i + 1]));
   return ORB_GPU_OK;
 }
 

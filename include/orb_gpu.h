@@ -163,6 +163,15 @@ int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const
                          int nlevels, float min_d, float max_d, int th_high, int device,
                          int32_t* best_idx_r, int32_t* best_dist);
 
+/* test/bench knob for the brute-force inner loop: csa = 0 (8 POPC per pair) or 1 (carry-save,
+ * 4 POPC per pair; default); qpt = queries per thread (1, 2 or 4). */
+int orb_gpu_set_bruteforce_variant(int csa, int qpt);
+
+/* Per-stage device time of the last extract call on this handle (CUDA events on the stream the
+ * kernels ran on): ms5 = pyramid, FAST, quadtree, blur, orientation+descriptors. */
+int orb_gpu_set_stage_timing(OrbGpuExtractor* h, int enable);
+int orb_gpu_get_stage_ms(OrbGpuExtractor* h, float* ms5);
+
 /* ---- diagnostics ----------------------------------------------------------------------- */
 const char* orb_gpu_version(void);
 /* last CUDA error string seen by this thread inside the library ("" if none) */
