@@ -154,12 +154,28 @@ void fast9_nms(const uint8_t* img, int w, int h, size_t stride, int threshold,
   out.clear();
   if (w < 7 || h < 7) return;
   // score map (0 = not a corner at this threshold), then strict 8-neighbour maximum.
-  std::vector<int> sc((size_t)w * h, 0);
-  for (int y = 3; y < h - 3; ++y)
+  static thread_local std::vector<int> sc;
+  sc.assign((size_t)w * h, 0);
+  const ptrdiff_t st = (ptrdiff_t)stride;
+  for (int y = 3; y < h - 3; ++y) {
+    const uint8_t* row = img + (size_t)y * stride;
     for (int x = 3; x < w - 3; ++x) {
-      int b = fast9_best(img + (size_t)y * stride + x, stride);
+      // Any 9 contiguous circle pixels contain one of each opposite pair (0,8), (4,12), (2,10),
+      // (6,14): reject unless all four pairs have a member brighter (or all darker) than +-t.
+      const uint8_t* p = row + x;
+      const int v = p[0], lo = v - threshold, hi = v + threshold;
+      const int c0 = p[3 * st], c8 = p[-3 * st], c4 = p[3], c12 = p[-3];
+      const bool dark = (c0 < lo || c8 < lo) && (c4 < lo || c12 < lo);
+      const bool bright = (c0 > hi || c8 > hi) && (c4 > hi || c12 > hi);
+      if (!dark && !bright) continue;
+      const int c2 = p[2 * st + 2], c10 = p[-2 * st - 2], c6 = p[-2 * st + 2], c14 = p[2 * st - 2];
+      const bool dark2 = dark && (c2 < lo || c10 < lo) && (c6 < lo || c14 < lo);
+      const bool bright2 = bright && (c2 > hi || c10 > hi) && (c6 > hi || c14 > hi);
+      if (!dark2 && !bright2) continue;
+      int b = fast9_best(p, stride);
       if (b > threshold) sc[(size_t)y * w + x] = b - 1;
     }
+  }
   for (int y = 3; y < h - 3; ++y)
     for (int x = 3; x < w - 3; ++x) {
       const int s = sc[(size_t)y * w + x];
