@@ -102,10 +102,15 @@ __device__ __forceinline__ int fast_score(const uint8_t* t, int pitch) {
   return max(best, -worst);
 }
 
+// One warp per cell.  Per threshold T (iniTh first, minTh only if the cell kept nothing, :809-816):
+//   1. 4-point reject test on every interior pixel (any 9-arc contains one of each opposite
+//      compass pair), survivors compacted in row-major order into a candidate list;
+//   2. exact arc score for the candidates only, written into a zero-framed score tile;
+//   3. strict 3x3 NMS over the candidates, emitted in row-major order.
 __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows, int score_pitch,
-                  int score_rows) {
-  extern __shared__ uint8_t smem[];
+                  int score_rows, int cand_cap) {
+  extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
   if (gcell >= (long long)nframes * p.cells_per_frame) return;
@@ -117,8 +122,10 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows
   const int ci = cell - g.cell_base;
   const int i = ci / g.ncols, j = ci - i * g.ncols;
 
-  uint8_t* tile = smem + (size_t)warp * (tile_pitch * tile_rows + score_pitch * score_rows);
+  const int per_warp = tile_pitch * tile_rows + score_pitch * score_rows + 2 * cand_cap;
+  uint8_t* tile = smem + (size_t)warp * per_warp;
   uint8_t* score = tile + tile_pitch * tile_rows;
+  uint16_t* cand = reinterpret_cast<uint16_t*>(score + score_pitch * score_rows);
 
   // cell ROI (:789-806)
   const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
@@ -131,67 +138,105 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows
     return;
   }
   const int iw = cw - 6, ih = ch - 6;  // detectable interior
-
-  const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)ini_y * g.pitch + ini_x;
-  for (int y = 0; y < ch; ++y)
-    for (int x = lane; x < cw; x += 32) tile[y * tile_pitch + x] = img[(size_t)y * g.pitch + x];
-  // score tile with a 1-px zero frame (neighbours outside the interior count as 0)
-  for (int k = lane; k < score_pitch * (ih + 2); k += 32) score[k] = 0;
-  __syncwarp();
-
   const int npx = iw * ih;
-  for (int k = lane; k < npx; k += 32) {
-    const int y = k / iw, x = k - y * iw;
-    const int s = fast_score(tile + (y + 3) * tile_pitch + (x + 3), tile_pitch);
-    score[(y + 1) * score_pitch + (x + 1)] = (uint8_t)(s > p.min_th ? s : 0);
-  }
-  __syncwarp();
+  const unsigned inv_iw = ((1u << 20) + iw - 1) / iw;  // k / iw == (k * inv_iw) >> 20 for k < 2^20 / iw
 
-  int n_all = 0, n_hi = 0;
-  for (int k0 = 0; k0 < npx; k0 += 32) {
-    const int k = k0 + lane;
-    bool keep = false;
-    int s = 0, x = 0, y = 0;
-    if (k < npx) {
-      y = k / iw; x = k - y * iw;
-      const uint8_t* c = score + (y + 1) * score_pitch + (x + 1);
-      s = c[0];
-      if (s > 0) {
-        const int m = max(max(max(c[-score_pitch - 1], c[-score_pitch]), max(c[-score_pitch + 1], c[-1])),
-                          max(max(c[1], c[score_pitch - 1]), max(c[score_pitch], c[score_pitch + 1])));
-        keep = s > m;
-      }
+  // tile load with aligned 32-bit words (rows are 4-byte aligned: pitch % 4 == 0, base % 4 == 0)
+  const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)ini_y * g.pitch + ini_x;
+  const int off = (int)(reinterpret_cast<uintptr_t>(img) & 3);
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(tile);
+    const int nw = (off + cw + 3) >> 2, wpitch = g.pitch >> 2, tp4 = tile_pitch >> 2;
+    const unsigned inv_nw = ((1u << 20) + nw - 1) / nw;
+    for (int k = lane; k < nw * ch; k += 32) {
+      const int r = (int)(((unsigned)k * inv_nw) >> 20), c = k - r * nw;
+      dst[r * tp4 + c] = __ldg(src + (size_t)r * wpitch + c);
     }
-    const unsigned mask = __ballot_sync(0xffffffffu, keep);
-    const unsigned hi = __ballot_sync(0xffffffffu, keep && s > p.ini_th);
-    if (keep) {
-      const int pos = n_all + __popc(mask & ((1u << lane) - 1));
-      // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
-      out[pos] = (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(s - 1) << 16);
-    }
-    n_all += __popc(mask);
-    n_hi += __popc(hi);
   }
-  if (lane == 0) *out_cnt = (uint32_t)n_all | ((uint32_t)n_hi << 16);
+  const uint8_t* t0 = tile + 3 * tile_pitch + off + 3;  // interior pixel (0,0)
+  const int tp = tile_pitch;
+  int n_kept = 0;
+  int T = p.ini_th;
+  for (int pass = 0; pass < 2; ++pass) {
+    // 1. reject test + ordered compaction; also clears the score tile
+    {
+      uint32_t* z = reinterpret_cast<uint32_t*>(score);
+      for (int k = lane; k < (score_pitch * (ih + 2)) >> 2; k += 32) z[k] = 0;
+    }
+    __syncwarp();
+    int ncand = 0;
+    for (int k0 = 0; k0 < npx; k0 += 32) {
+      const int k = k0 + lane;
+      bool ok = false;
+      if (k < npx) {
+        const int y = (int)(((unsigned)k * inv_iw) >> 20), x = k - y * iw;
+        const uint8_t* c = t0 + y * tp + x;
+        const int v = c[0], c0 = c[3 * tp], c8 = c[-3 * tp], c4 = c[3], c12 = c[-3];
+        const int brightest = min(max(c0, c8), max(c4, c12));  // > v+T needed for a dark-centre corner
+        const int darkest = max(min(c0, c8), min(c4, c12));    // < v-T needed for a bright-centre corner
+        ok = (brightest > v + T) || (darkest < v - T);
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, ok);
+      if (ok) cand[ncand + __popc(m & ((1u << lane) - 1))] = (uint16_t)k;
+      ncand += __popc(m);
+    }
+    __syncwarp();
+    // 2. exact score of the candidates
+    for (int q = lane; q < ncand; q += 32) {
+      const int k = cand[q];
+      const int y = (int)(((unsigned)k * inv_iw) >> 20), x = k - y * iw;
+      const int s = fast_score(t0 + y * tp + x, tp);
+      if (s > T) score[(y + 1) * score_pitch + (x + 1)] = (uint8_t)s;
+    }
+    __syncwarp();
+    // 3. NMS + ordered emission
+    for (int q0 = 0; q0 < ncand; q0 += 32) {
+      const int q = q0 + lane;
+      bool keep = false;
+      int s = 0, x = 0, y = 0;
+      if (q < ncand) {
+        const int k = cand[q];
+        y = (int)(((unsigned)k * inv_iw) >> 20); x = k - y * iw;
+        const uint8_t* c = score + (y + 1) * score_pitch + (x + 1);
+        s = c[0];
+        if (s > 0) {
+          const int mx = max(max(max(c[-score_pitch - 1], c[-score_pitch]), max(c[-score_pitch + 1], c[-1])),
+                             max(max(c[1], c[score_pitch - 1]), max(c[score_pitch], c[score_pitch + 1])));
+          keep = s > mx;
+        }
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      if (keep)  // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
+        out[n_kept + __popc(m & ((1u << lane) - 1))] =
+            (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(s - 1) << 16);
+      n_kept += __popc(m);
+    }
+    if (n_kept > 0 || T == p.min_th) break;
+    T = p.min_th;  // empty at iniThFAST: rerun the cell at minThFAST (:812-816)
+    __syncwarp();
+  }
+  if (lane == 0) *out_cnt = (uint32_t)n_kept;  // hi field 0: the list is already the final one
 }
 
 static void fast_smem_layout(const Plan& p, int* tile_pitch, int* tile_rows, int* score_pitch,
-                             int* score_rows) {
+                             int* score_rows, int* cand_cap) {
   int mw = 0, mh = 0;
   for (int l = 0; l < p.nlevels; ++l) {
     mw = max(mw, p.lv[l].wcell + 6);
     mh = max(mh, p.lv[l].hcell + 6);
   }
-  *tile_pitch = (mw + 3) & ~3;
+  *tile_pitch = (mw + 3 + 3 + 3) & ~3;  // + alignment offset (<= 3) + word-load overhang
   *tile_rows = mh;
   *score_pitch = ((mw - 6 + 2) + 3) & ~3;
   *score_rows = mh - 6 + 2;
+  *cand_cap = ((mw - 6) * (mh - 6) + 7) & ~7;
 }
 
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
-  int tp, tr, sp, sr;
-  fast_smem_layout(p, &tp, &tr, &sp, &sr);
-  const size_t smem = (size_t)kFastWarps * (tp * tr + sp * sr);
+  int tp, tr, sp, sr, cc;
+  fast_smem_layout(p, &tp, &tr, &sp, &sr, &cc);
+  const size_t smem = (size_t)kFastWarps * (tp * tr + sp * sr + 2 * cc);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
     ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -200,7 +245,7 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
   }
   const long long cells = (long long)nframes * p.cells_per_frame;
   const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, tp, tr, sp, sr);
+  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, tp, tr, sp, sr, cc);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;

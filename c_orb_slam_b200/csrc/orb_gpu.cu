@@ -345,15 +345,23 @@ int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, in
   if (rc) return rc;
   cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
   Plan p = h->plan;
-  p.lv[0].img = const_cast<uint8_t*>(d_frames);  // level 0 aliases the caller's frames
-  p.lv[0].pitch = (int)stride;
-  p.lv[0].frame_stride = (long long)frame_stride;
+  if ((stride & 3) == 0 && (frame_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(d_frames) & 3) == 0) {
+    p.lv[0].img = const_cast<uint8_t*>(d_frames);  // level 0 aliases the caller's frames
+    p.lv[0].pitch = (int)stride;
+    p.lv[0].frame_stride = (long long)frame_stride;
+  } else {
+    // rows not 4-byte aligned (e.g. 1241-px KITTI rows): repack into the handle's level-0 buffer
+    for (int f = 0; f < nframes; ++f)
+      ORB_CUDA_TRY(cudaMemcpy2DAsync(p.lv[0].img + (size_t)f * p.lv[0].frame_stride, p.lv[0].pitch,
+                                     d_frames + (size_t)f * frame_stride, stride, width, height,
+                                     cudaMemcpyDeviceToDevice, s));
+  }
   if ((rc = run_pipeline(h, p, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
   if (d_status)
     ORB_CUDA_TRY(cudaMemcpyAsync(d_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToDevice, s));
   h->last_nframes = nframes;
   h->have_result = true;
-  h->last_l0 = d_frames; h->last_l0_pitch = (int)stride; h->last_l0_stride = (long long)frame_stride;
+  h->last_l0 = p.lv[0].img; h->last_l0_pitch = p.lv[0].pitch; h->last_l0_stride = p.lv[0].frame_stride;
   return ORB_GPU_OK;
 }
 

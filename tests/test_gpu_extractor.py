@@ -111,3 +111,32 @@ def test_non_default_parameters(gpu, oracle):
         k, d = ex_g(img)
         ko, do = ex_o(img)
         assert np.array_equal(k, ko) and np.array_equal(d, do), args
+
+
+def test_device_api_aliased_and_unaligned(gpu, oracle):
+    """orb_gpu_extract_batch_device: level 0 aliases aligned caller frames, repacks unaligned ones."""
+    import torch
+    for (W, H), nf in (((640, 480), 1000), ((1241, 376), 2000)):   # 1241-px rows are not 4-byte aligned
+        B = 3
+        frames = synth.make_frames(W, H, B, seed0=500)
+        d_frames = torch.from_numpy(frames).cuda()
+        cap = nf + 24
+        d_kps = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda")
+        d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+        d_n = torch.zeros(B, dtype=torch.int32, device="cuda")
+        d_st = torch.ones(1, dtype=torch.int32, device="cuda")
+        ex = gpu.ORBextractor(nf, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=B)
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            ex.extract_batch_device(d_frames.data_ptr(), B, W, H, W, W * H, d_kps.data_ptr(), d_desc.data_ptr(),
+                                    d_n.data_ptr(), d_st.data_ptr(), s.cuda_stream)
+        s.synchronize()
+        assert int(d_st.item()) == 0
+        n = d_n.cpu().numpy()
+        kps = d_kps.cpu().numpy().view(gpu.KP_DTYPE).reshape(B, cap)
+        desc = d_desc.cpu().numpy()
+        ex_o = oracle.Extractor(nf, 1.2, 8, 20, 7)
+        for f in range(B):
+            ko, do = ex_o(frames[f])
+            assert n[f] == len(ko) and np.array_equal(kps[f, :n[f]], ko) and np.array_equal(desc[f, :n[f]], do)
+        assert np.array_equal(ex.pyramid_level(0, 1), frames[1])
