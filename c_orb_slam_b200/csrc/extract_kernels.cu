@@ -595,7 +595,13 @@ int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t 
 // =============================================================================================
 // 4. GaussianBlur 7x7 sigma 2 (separable integer kernel, REFLECT_101 of the w x h image)
 // =============================================================================================
-constexpr int kBlurTW = 128, kBlurTH = 32;  // output tile; 256 threads
+// Tile 64x64 per block (256 threads).  Raw tile (+3 px halo, word-aligned loads, REFLECT_101 applied
+// to row indices at load time and to the <=3 halo columns in shared memory), horizontal pass with two
+// IDP4A per pixel on funnel-shifted words (8.8 fixed point, u16), vertical pass with a 10-row register
+// window per 4x4 output patch (16.16), one 32-bit store per 4 pixels.
+constexpr int kBlurTW = 64, kBlurTH = 64;
+constexpr int kBlurRawPitch = kBlurTW + 8;     // bytes: [x0-4, x0+TW+4)
+constexpr int kBlurHPitch = kBlurTW + 4;       // u16 elements (+4 pad against bank conflicts)
 
 __device__ __forceinline__ int reflect101(int p, int len) {
   // valid for -len < p < 2*len-1 (3-px halo; len >= 4 guaranteed by the plan)
@@ -605,8 +611,8 @@ __device__ __forceinline__ int reflect101(int p, int len) {
 
 __global__ void __launch_bounds__(256)
 blur_kernel(Plan p, int tiles_total) {
-  __shared__ uint8_t s_raw[(kBlurTH + 6) * (kBlurTW + 8)];
-  __shared__ uint16_t s_h[(kBlurTH + 6) * kBlurTW];
+  __shared__ __align__(16) uint8_t s_raw[(kBlurTH + 6) * kBlurRawPitch];
+  __shared__ __align__(16) uint16_t s_h[(kBlurTH + 6) * kBlurHPitch];
   // tile -> (level, tx, ty); tiles of all levels are laid out consecutively per frame
   int tile = blockIdx.x;
   const int f = blockIdx.y;
@@ -622,33 +628,84 @@ blur_kernel(Plan p, int tiles_total) {
   const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
   const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
   const uint8_t* img = g.img + (size_t)f * g.frame_stride;
-  constexpr int RP = kBlurTW + 8;
-  for (int k = threadIdx.x; k < (kBlurTH + 6) * (kBlurTW + 6); k += 256) {
-    const int r = k / (kBlurTW + 6), c = k - r * (kBlurTW + 6);
-    const int sy = reflect101(min(y0 + r - 3, g.h + 2), g.h), sx = reflect101(min(x0 + c - 3, g.w + 2), g.w);
-    s_raw[r * RP + c] = img[(size_t)sy * g.pitch + sx];
-  }
-  __syncthreads();
-  for (int k = threadIdx.x; k < (kBlurTH + 6) * kBlurTW; k += 256) {
-    const int r = k / kBlurTW, c = k - r * kBlurTW;
-    const uint8_t* s = s_raw + r * RP + c;
-    s_h[k] = (uint16_t)(18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3]);
-  }
-  __syncthreads();
-  uint8_t* out = g.blur + (size_t)f * g.bframe_stride;
-  for (int k = threadIdx.x; k < kBlurTH * (kBlurTW / 4); k += 256) {
-    const int r = k / (kBlurTW / 4), c4 = (k - r * (kBlurTW / 4)) * 4;
-    const int y = y0 + r, x = x0 + c4;
-    if (y >= g.h || x >= g.w) continue;
-    uint32_t packed = 0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const uint16_t* h = s_h + r * kBlurTW + c4 + q;
-      const uint32_t v = 18u * (h[0] + h[6 * kBlurTW]) + 34u * (h[kBlurTW] + h[5 * kBlurTW]) +
-                         48u * (h[2 * kBlurTW] + h[4 * kBlurTW]) + 56u * h[3 * kBlurTW];
-      packed |= ((v + 32768u) >> 16) << (8 * q);
+  const int t = threadIdx.x;
+
+  // ---- raw tile: 18 words per row, rows reflected ----
+  {
+    const int words_in_row = (g.w + 3) >> 2;  // readable words of an image row
+    constexpr int WPR = kBlurRawPitch / 4;
+    for (int k = t; k < (kBlurTH + 6) * WPR; k += 256) {
+      const int r = k / WPR, c = k - r * WPR;
+      const int sy = reflect101(min(y0 + r - 3, g.h + 2), g.h);
+      const int wi = (x0 >> 2) - 1 + c;
+      uint32_t v = 0;
+      if (wi >= 0 && wi < words_in_row) v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)sy * g.pitch) + wi);
+      reinterpret_cast<uint32_t*>(s_raw)[r * WPR + c] = v;
     }
-    *reinterpret_cast<uint32_t*>(out + (size_t)y * g.bpitch + x) = packed;
+  }
+  __syncthreads();
+  // column halo by reflection (tile column c holds image x = x0 - 4 + c)
+  if (x0 == 0 || x0 + kBlurTW + 3 > g.w - 1) {
+    for (int k = t; k < (kBlurTH + 6) * 6; k += 256) {
+      const int r = k / 6, j = k - r * 6;
+      int x;
+      if (j < 3) { if (x0 != 0) continue; x = -1 - j; }
+      else { x = g.w + (j - 3); if (x - (x0 - 4) >= kBlurRawPitch || x < x0 - 4) continue; }
+      const int sx = reflect101(x, g.w);
+      if (sx - (x0 - 4) < 0 || sx - (x0 - 4) >= kBlurRawPitch) continue;
+      s_raw[r * kBlurRawPitch + (x - (x0 - 4))] = s_raw[r * kBlurRawPitch + (sx - (x0 - 4))];
+    }
+    __syncthreads();
+  }
+  // ---- horizontal: 4 output pixels per item from 3 words, 2 dp4a each ----
+  {
+    const uint32_t K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps 0..3
+    const uint32_t K1 = 48u | (34u << 8) | (18u << 16);                // taps 4..6
+    constexpr int GPR = kBlurTW / 4;
+    for (int k = t; k < (kBlurTH + 6) * GPR; k += 256) {
+      const int r = k / GPR, gq = k - r * GPR;
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(s_raw + r * kBlurRawPitch) + gq;
+      const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];  // bytes x-4..x-1 | x..x+3 | x+4..x+7
+      uint32_t h0 = __dp4a(__funnelshift_r(w0, w1, 8), K0, 0u);
+      h0 = __dp4a(__funnelshift_r(w1, w2, 8), K1, h0);
+      uint32_t h1 = __dp4a(__funnelshift_r(w0, w1, 16), K0, 0u);
+      h1 = __dp4a(__funnelshift_r(w1, w2, 16), K1, h1);
+      uint32_t h2 = __dp4a(__funnelshift_r(w0, w1, 24), K0, 0u);
+      h2 = __dp4a(__funnelshift_r(w1, w2, 24), K1, h2);
+      uint32_t h3 = __dp4a(w1, K0, 0u);
+      h3 = __dp4a(w2, K1, h3);
+      uint2 o;
+      o.x = h0 | (h1 << 16);
+      o.y = h2 | (h3 << 16);
+      *reinterpret_cast<uint2*>(s_h + r * kBlurHPitch + gq * 4) = o;
+    }
+  }
+  __syncthreads();
+  // ---- vertical: thread = 4 columns x 4 rows, 10-row window ----
+  {
+    const int cg = t & 15, slab = t >> 4;  // 16 column groups x 16 row slabs
+    const int x = x0 + cg * 4, yb = y0 + slab * 4;
+    if (x < g.w && yb < g.h) {
+      uint32_t col[10][4];
+#pragma unroll
+      for (int r = 0; r < 10; ++r) {
+        const uint2 v = *reinterpret_cast<const uint2*>(s_h + (slab * 4 + r) * kBlurHPitch + cg * 4);
+        col[r][0] = v.x & 0xffffu; col[r][1] = v.x >> 16; col[r][2] = v.y & 0xffffu; col[r][3] = v.y >> 16;
+      }
+      uint8_t* out = g.blur + (size_t)f * g.bframe_stride + (size_t)yb * g.bpitch + x;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        if (yb + r >= g.h) break;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t v = 18u * (col[r][q] + col[r + 6][q]) + 34u * (col[r + 1][q] + col[r + 5][q]) +
+                             48u * (col[r + 2][q] + col[r + 4][q]) + 56u * col[r + 3][q];
+          packed |= ((v + 32768u) >> 16) << (8 * q);
+        }
+        *reinterpret_cast<uint32_t*>(out + (size_t)r * g.bpitch) = packed;
+      }
+    }
   }
 }
 
@@ -730,14 +787,15 @@ orient_desc_kernel(Plan p, Scratch sc, int nframes, OrbKeyPoint* __restrict__ kp
   if (lane < 31) {
     const int u = lane - kHalfPatch;
     const int au = u < 0 ? -u : u;
-#pragma unroll 1
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-      if (au <= p.umax[v < 0 ? -v : v]) {
-        const int val = img[v * g.pitch + u];
-        m10 += u * val;
-        m01 += v * val;
-      }
-    }
+    int vals[31];
+#pragma unroll
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v)  // 31 independent loads in flight
+      vals[v + kHalfPatch] = au <= p.umax[v < 0 ? -v : v] ? (int)__ldg(img + v * g.pitch + u) : 0;
+    int sv = 0, s1 = 0;
+#pragma unroll
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) { sv += vals[v + kHalfPatch]; s1 += v * vals[v + kHalfPatch]; }
+    m10 = u * sv;
+    m01 = s1;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -748,21 +806,30 @@ orient_desc_kernel(Plan p, Scratch sc, int nframes, OrbKeyPoint* __restrict__ kp
 
   // steered BRIEF on the blurred level (:106-147)
   const float rad = __fmul_rn(angle, 0.017453292519943295f);  // (float)(CV_PI/180.f)
-  const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+  double sd, cd;
+  sincos((double)rad, &sd, &cd);
+  const float a = (float)cd, b = (float)sd;
   const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride + (size_t)cy * g.bpitch + cx;
   uint32_t* drow = reinterpret_cast<uint32_t*>(desc + ((size_t)f * capacity + out_idx) * 32);
+  int t0[8], t1[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < 8; ++k) {  // 16 independent gathers per lane
     const char4 t = s_pat[32 * k + lane];
     const float x0 = (float)t.x, y0 = (float)t.y, x1 = (float)t.z, y1 = (float)t.w;
     const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
     const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
     const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
     const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-    const int t0 = bl[r0 * g.bpitch + c0], t1 = bl[r1 * g.bpitch + c1];
-    const unsigned word = __ballot_sync(0xffffffffu, t0 < t1);  // bit = test 32k+lane, LSB first
-    if (lane == 0) drow[k] = word;
+    t0[k] = __ldg(bl + r0 * g.bpitch + c0);
+    t1[k] = __ldg(bl + r1 * g.bpitch + c1);
   }
+  uint32_t words[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) words[k] = __ballot_sync(0xffffffffu, t0[k] < t1[k]);  // bit = test 32k+lane
+  uint32_t mine = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) mine = lane == k ? words[k] : mine;
+  if (lane < 8) drow[lane] = mine;  // one coalesced 32-byte store
   if (lane == 0) {
     OrbKeyPoint kp;
     const float fx = (float)cx, fy = (float)cy;
