@@ -301,18 +301,43 @@ __device__ __forceinline__ int block_exclusive_scan(int* a, int n, int* s_warp /
   return total;
 }
 
+__device__ __forceinline__ void bitonic_step(uint64_t* a, int i, int j, int k) {
+  const int l = i | j;
+  const uint64_t x = a[i], y = a[l];
+  const bool up = (i & k) == 0;
+  if ((x > y) == up) { a[i] = y; a[l] = x; }
+}
+
+// Bitonic sort of a[0..n) (n a power of two) by the whole block.  Every warp owns an aligned chunk
+// of n / nwarps elements: sub-stages whose partner distance stays inside a chunk only need a
+// __syncwarp, so only the few widest sub-stages pay for a block barrier.
 __device__ __forceinline__ void block_bitonic_sort(uint64_t* a, int n /*pow2*/) {
-  for (int k = 2; k <= n; k <<= 1)
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x) {
-        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-        const int l = i | j;
-        const uint64_t x = a[i], y = a[l];
-        const bool up = (i & k) == 0;
-        if ((x > y) == up) { a[i] = y; a[l] = x; }
+  const int nwarps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int chunk = n / nwarps;  // nwarps is a power of two
+  if (chunk < 2) {               // tiny input: plain block-wide network
+    for (int k = 2; k <= n; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x)
+          bitonic_step(a, ((t & ~(j - 1)) << 1) | (t & (j - 1)), j, k);
+        __syncthreads();
       }
+    return;
+  }
+  const int half = chunk >> 1, base = warp * chunk;
+  for (int k = 2; k <= n; k <<= 1) {
+    int j = k >> 1;
+    for (; 2 * j > chunk; j >>= 1) {  // partners in different chunks
+      for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x)
+        bitonic_step(a, ((t & ~(j - 1)) << 1) | (t & (j - 1)), j, k);
       __syncthreads();
     }
+    for (; j > 0; j >>= 1) {          // warp-local sub-stages
+      for (int t = lane; t < half; t += 32)
+        bitonic_step(a, base + (((t & ~(j - 1)) << 1) | (t & (j - 1))), j, k);
+      __syncwarp();
+    }
+    if (2 * k > chunk) __syncthreads();  // the next k starts with (or ends the sort before) a cross-chunk read
+  }
 }
 
 __device__ __forceinline__ int lower_bound_code(const uint64_t* keys, int lo, int hi, uint32_t code) {
@@ -333,11 +358,20 @@ __device__ __forceinline__ void child_bounds(const uint64_t* keys, const QtNode&
   b[3] = lower_bound_code(keys, b[2], nd.end, nd.prefix + (3u << shift));
 }
 
+__host__ __device__ __forceinline__ int qt_ncap(int quota, int n_ini) {
+  const int a = quota + 4, b = 4 * n_ini;
+  return (a > b ? a : b) + 4;
+}
+__device__ __forceinline__ int pow2ceil_dev(int v) { return v <= 1 ? 1 : 1 << (32 - __clz(v - 1)); }
+
 __global__ void __launch_bounds__(kQtThreads)
-quadtree_kernel(Plan p, Scratch sc, int level, int ncap, int sort_cap) {
+quadtree_kernel(Plan p, Scratch sc, int nframes) {
   extern __shared__ __align__(16) uint8_t smem[];
+  // one block per (level, frame); the big levels are scheduled first so the small ones fill the tail
+  const int level = blockIdx.x / nframes;
   const LevelGeom& g = p.lv[level];
-  const int f = blockIdx.x, t = threadIdx.x, T = kQtThreads;
+  const int f = blockIdx.x - level * nframes, t = threadIdx.x, T = kQtThreads;
+  const int ncap = qt_ncap(g.quota, g.n_ini), sort_cap = pow2ceil_dev(ncap);
   const int ncells = g.nrows * g.ncols;
   const int N = g.quota;
 
@@ -360,14 +394,11 @@ quadtree_kernel(Plan p, Scratch sc, int level, int ncap, int sort_cap) {
   uint32_t* sel = sc.sel + (size_t)f * p.slots_per_frame + g.slot_base;
 
   // ---- gather candidates in arrival order (cell row-major, then FAST row-major) -------------
-  for (int c = t; c < ncells; c += T) {
-    const uint32_t cc = cell_cnt[c];
-    s_cell[c] = (cc >> 16) ? (int)(cc >> 16) : (int)(cc & 0xffff);
-  }
+  for (int c = t; c < ncells; c += T) s_cell[c] = (int)cell_cnt[c];
   if (t == 0) s_cell[ncells] = 0;
   __syncthreads();
   const int C = block_exclusive_scan(s_cell, ncells, s_warp);
-  if (t == 0) sc.cand_cnt[f * p.nlevels + level] = C;
+  if (t == 0) { sc.cand_cnt[f * p.nlevels + level] = C; s_cell[ncells] = C; }
   if (C > g.key_cap) {  // uniform branch
     if (t == 0) { *sc.status = ORB_GPU_ERR_CAPACITY; sc.sel_cnt[f * p.nlevels + level] = 0; }
     return;
@@ -376,36 +407,35 @@ quadtree_kernel(Plan p, Scratch sc, int level, int ncap, int sort_cap) {
   while (cpad < C) cpad <<= 1;
   uint64_t* keys = (cpad <= kQtSmemKeys) ? s_keys
                                          : sc.keys + (size_t)f * p.keys_per_frame + g.key_base;
-  for (int c = t; c < ncells; c += T) {
-    const uint32_t cc = cell_cnt[c];
-    const int n_all = cc & 0xffff;
-    const bool hi_only = (cc >> 16) != 0;
-    const int ci = c / g.ncols, cj = c - ci * g.ncols;
-    const uint32_t* src = cell_kp + (size_t)c * p.cell_cap;
-    int arrival = s_cell[c];
-    for (int k = 0; k < n_all; ++k) {
-      const uint32_t e = src[k];
-      const int resp = (e >> 16) & 0xff;
-      if (hi_only && resp < p.ini_th) continue;  // score > iniTh  <=>  response >= iniTh
-      const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
-      // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
-      int root = (int)__fdiv_rn((float)x, g.hx);
-      root = min(root, g.n_ini - 1);
-      int ulx = (int)__fmul_rn(g.hx, (float)root), brx = (int)__fmul_rn(g.hx, (float)(root + 1));
-      int uly = 0, bry = g.box_h;
-      uint32_t code = (uint32_t)root << 24;
-#pragma unroll
-      for (int d = 0; d < kCodeDepth; ++d) {
-        const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
-        const int right = x >= mx, below = y >= my;
-        code |= (uint32_t)(right | (below << 1)) << (22 - 2 * d);
-        if (right) ulx = mx; else brx = mx;
-        if (below) uly = my; else bry = my;
-      }
-      pay[arrival] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)resp << 24);
-      keys[arrival] = ((uint64_t)code << 32) | (uint32_t)arrival;
-      ++arrival;
+  __syncthreads();
+  // one thread per candidate: its cell is the last one whose arrival base is <= the arrival index
+  for (int arrival = t; arrival < C; arrival += T) {
+    int lo = 0, hi = ncells - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_cell[mid] <= arrival) lo = mid; else hi = mid - 1;
     }
+    const int c = lo;
+    const int ci = c / g.ncols, cj = c - ci * g.ncols;
+    const uint32_t e = cell_kp[(size_t)c * p.cell_cap + (arrival - s_cell[c])];
+    const int resp = (e >> 16) & 0xff;
+    const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
+    // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
+    int root = (int)__fdiv_rn((float)x, g.hx);
+    root = min(root, g.n_ini - 1);
+    int ulx = (int)__fmul_rn(g.hx, (float)root), brx = (int)__fmul_rn(g.hx, (float)(root + 1));
+    int uly = 0, bry = g.box_h;
+    uint32_t code = (uint32_t)root << 24;
+#pragma unroll
+    for (int d = 0; d < kCodeDepth; ++d) {
+      const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+      const int right = x >= mx, below = y >= my;
+      code |= (uint32_t)(right | (below << 1)) << (22 - 2 * d);
+      if (right) ulx = mx; else brx = mx;
+      if (below) uly = my; else bry = my;
+    }
+    pay[arrival] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)resp << 24);
+    keys[arrival] = ((uint64_t)code << 32) | (uint32_t)arrival;
   }
   for (int k = C + t; k < cpad; k += T) keys[k] = ~0ull;
   __syncthreads();
@@ -563,12 +593,11 @@ quadtree_kernel(Plan p, Scratch sc, int level, int ncap, int sort_cap) {
   if (t == 0) sc.sel_cnt[f * p.nlevels + level] = n;
 }
 
-static int qt_ncap(const LevelGeom& g) { return max(g.quota + 4, 4 * g.n_ini) + 4; }
 static int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 size_t quadtree_smem_bytes(const Plan& p, int level) {
   const LevelGeom& g = p.lv[level];
-  const int ncap = qt_ncap(g);
+  const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
   return (size_t)kQtSmemKeys * 8 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
          (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 40) * 4 + 64;
@@ -576,18 +605,16 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
   static size_t configured = 0;
-  for (int l = 0; l < p.nlevels; ++l) {
-    const size_t smem = quadtree_smem_bytes(p, l);
-    if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
-    if (smem > 48 * 1024 && smem > configured) {
-      ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)smem));
-      configured = smem;
-    }
-    const int ncap = qt_ncap(p.lv[l]);
-    quadtree_kernel<<<nframes, kQtThreads, smem, s>>>(p, sc, l, ncap, pow2ceil(ncap));
-    count_launch();
+  size_t smem = 0;
+  for (int l = 0; l < p.nlevels; ++l) smem = max(smem, quadtree_smem_bytes(p, l));
+  if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
+  if (smem > 48 * 1024 && smem > configured) {
+    ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+    configured = smem;
   }
+  quadtree_kernel<<<nframes * p.nlevels, kQtThreads, smem, s>>>(p, sc, nframes);
+  count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
 }
