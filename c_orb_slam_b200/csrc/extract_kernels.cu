@@ -68,48 +68,60 @@ int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
 // =============================================================================================
 // 2. FAST-9/16 per cell, 3x3 NMS inside the cell, threshold retry
 // =============================================================================================
-// One warp per cell.  score(p) = max over the 16 contiguous 9-arcs of max(min(d), -max(d)),
-// d_k = I(p) - I(circle_k); p is a corner at t iff score > t, response = score - 1.
-// NMS survivors above iniTh are exactly the survivors above minTh that exceed iniTh (a pixel
-// above iniTh beats every neighbour <= iniTh at either threshold), so one NMS pass serves both
-// thresholds; the cell emits the iniTh set if it is non-empty, else the minTh set (:809-816).
+// One warp per 30-px cell (:789-829).  score(p) = max over the 16 contiguous 9-arcs of
+// max(min(d), -max(d)), d_k = I(p) - I(circle_k); p is a corner at t iff score > t and
+// response = score - 1 (the largest threshold at which p is still a corner).
+// Per threshold T (iniTh first, minTh only if the cell kept nothing, :809-816):
+//   1. word-wide necessary test on 4 pixels at a time: a 9-arc contains one pixel of each antipodal
+//      pair, so both (|v-c0|>T or |v-c8|>T) and (|v-c4|>T or |v-c12|>T) must hold (VABSDIFF4 +
+//      SWAR compares).  Every lane scans a run of consecutive words and keeps the 4-bit results in
+//      registers; one warp scan turns them into a row-major candidate list.
+//   2. exact arc score of the candidates, two signs at once in s16x2 lanes (VIMNMX3.S16x2);
+//   3. strict 3x3 NMS over the candidates, emitted in row-major order (cv::FAST's order).
 constexpr int kFastWarps = 8;
 
-__device__ __forceinline__ int fast_score(const uint8_t* t, int pitch) {
-  const int v = t[0];
-  int d[16];
-  d[0] = v - t[3 * pitch];          d[1] = v - t[3 * pitch + 1];
-  d[2] = v - t[2 * pitch + 2];      d[3] = v - t[pitch + 3];
-  d[4] = v - t[3];                  d[5] = v - t[-pitch + 3];
-  d[6] = v - t[-2 * pitch + 2];     d[7] = v - t[-3 * pitch + 1];
-  d[8] = v - t[-3 * pitch];         d[9] = v - t[-3 * pitch - 1];
-  d[10] = v - t[-2 * pitch - 2];    d[11] = v - t[-pitch - 3];
-  d[12] = v - t[-3];                d[13] = v - t[pitch - 3];
-  d[14] = v - t[2 * pitch - 2];     d[15] = v - t[3 * pitch - 1];
-  // min/max over every 9-arc via 3-wide then 3x3-wide windows
-  int mn3[16], mx3[16];
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    mn3[k] = min(d[k], min(d[(k + 1) & 15], d[(k + 2) & 15]));
-    mx3[k] = max(d[k], max(d[(k + 1) & 15], d[(k + 2) & 15]));
-  }
-  int best = -255, worst = 255;
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    best = max(best, min(mn3[k], min(mn3[(k + 3) & 15], mn3[(k + 6) & 15])));
-    worst = min(worst, max(mx3[k], max(mx3[(k + 3) & 15], mx3[(k + 6) & 15])));
-  }
-  return max(best, -worst);
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit_wait_all() {
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 }
 
-// One warp per cell.  Per threshold T (iniTh first, minTh only if the cell kept nothing, :809-816):
-//   1. 4-point reject test on every interior pixel (any 9-arc contains one of each opposite
-//      compass pair), survivors compacted in row-major order into a candidate list;
-//   2. exact arc score for the candidates only, written into a zero-framed score tile;
-//   3. strict 3x3 NMS over the candidates, emitted in row-major order.
+// exact FAST score of the pixel at t (tile pitch in bytes): lo lane = v - c + 256, hi lane = c - v + 256
+__device__ __forceinline__ int fast_score(const uint8_t* t, int pitch) {
+  const unsigned vb = (unsigned)t[0] + 256u + ((256u - (unsigned)t[0]) << 16);
+  unsigned e[16];
+#define ORB_E(k, off) e[k] = (unsigned)t[off] * 0xffffu + vb
+  ORB_E(0, 3 * pitch);       ORB_E(1, 3 * pitch + 1);   ORB_E(2, 2 * pitch + 2);   ORB_E(3, pitch + 3);
+  ORB_E(4, 3);               ORB_E(5, -pitch + 3);      ORB_E(6, -2 * pitch + 2);  ORB_E(7, -3 * pitch + 1);
+  ORB_E(8, -3 * pitch);      ORB_E(9, -3 * pitch - 1);  ORB_E(10, -2 * pitch - 2); ORB_E(11, -pitch - 3);
+  ORB_E(12, -3);             ORB_E(13, pitch - 3);      ORB_E(14, 2 * pitch - 2);  ORB_E(15, 3 * pitch - 1);
+#undef ORB_E
+  unsigned m3[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+  unsigned m9[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+  unsigned a = __vimax3_s16x2(m9[0], m9[1], m9[2]), b = __vimax3_s16x2(m9[3], m9[4], m9[5]);
+  unsigned c = __vimax3_s16x2(m9[6], m9[7], m9[8]), d = __vimax3_s16x2(m9[9], m9[10], m9[11]);
+  unsigned f = __vimax3_s16x2(m9[12], m9[13], m9[14]);
+  a = __vimax3_s16x2(a, b, c);
+  d = __vimax3_s16x2(d, f, m9[15]);
+  a = __vmaxs2(a, d);
+  return max((int)(a & 0xffffu), (int)(a >> 16)) - 256;
+}
+
+// sign bits of (x > T) per byte for T < 127: x > T  <=>  x >= 128 or (x & 127) + (127 - T) >= 128
+__device__ __forceinline__ unsigned gt_bytes(unsigned x, unsigned k127mT) {
+  return ((x & 0x7f7f7f7fu) + k127mT) | x;
+}
+
+struct FastLayout { int tp4, tile_rows, score_pitch, score_rows, cand_cap, per_warp; };
+
 __global__ void __launch_bounds__(kFastWarps * 32)
-fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows, int score_pitch,
-                  int score_rows, int cand_cap) {
+fast_cells_kernel(Plan p, Scratch sc, int nframes, FastLayout L) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
@@ -122,10 +134,9 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows
   const int ci = cell - g.cell_base;
   const int i = ci / g.ncols, j = ci - i * g.ncols;
 
-  const int per_warp = tile_pitch * tile_rows + score_pitch * score_rows + 2 * cand_cap;
-  uint8_t* tile = smem + (size_t)warp * per_warp;
-  uint8_t* score = tile + tile_pitch * tile_rows;
-  uint16_t* cand = reinterpret_cast<uint16_t*>(score + score_pitch * score_rows);
+  uint8_t* tile = smem + (size_t)warp * L.per_warp;
+  uint8_t* score = tile + L.tp4 * 4 * L.tile_rows;
+  uint16_t* cand = reinterpret_cast<uint16_t*>(score + L.score_pitch * L.score_rows);
 
   // cell ROI (:789-806)
   const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
@@ -138,106 +149,157 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, int tile_pitch, int tile_rows
     return;
   }
   const int iw = cw - 6, ih = ch - 6;  // detectable interior
-  const int npx = iw * ih;
-  const unsigned inv_iw = ((1u << 20) + iw - 1) / iw;  // k / iw == (k * inv_iw) >> 20 for k < 2^20 / iw
 
   // tile load with aligned 32-bit words (rows are 4-byte aligned: pitch % 4 == 0, base % 4 == 0)
   const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)ini_y * g.pitch + ini_x;
   const int off = (int)(reinterpret_cast<uintptr_t>(img) & 3);
+  uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(tile);
-    const int nw = (off + cw + 3) >> 2, wpitch = g.pitch >> 2, tp4 = tile_pitch >> 2;
+    const int nw = (off + cw + 3) >> 2, wpitch = g.pitch >> 2;
     const unsigned inv_nw = ((1u << 20) + nw - 1) / nw;
     for (int k = lane; k < nw * ch; k += 32) {
       const int r = (int)(((unsigned)k * inv_nw) >> 20), c = k - r * nw;
-      dst[r * tp4 + c] = __ldg(src + (size_t)r * wpitch + c);
+      cp_async4(tile32 + r * L.tp4 + c, src + (size_t)r * wpitch + c);
     }
+    uint32_t* z = reinterpret_cast<uint32_t*>(score);
+    for (int k = lane; k < (L.score_pitch * (ih + 2)) >> 2; k += 32) z[k] = 0;
+    cp_async_commit_wait_all();
   }
-  const uint8_t* t0 = tile + 3 * tile_pitch + off + 3;  // interior pixel (0,0)
-  const int tp = tile_pitch;
+  __syncwarp();
+  const int tp = L.tp4 * 4;
+  const int xs = off + 3;                         // tile byte column of interior pixel x = 0
+  const uint8_t* t0 = tile + 3 * tp + xs;         // interior pixel (0,0)
+  const int gw0 = xs >> 2;                        // first word group that holds interior pixels
+  const int ng = ((xs + iw - 1) >> 2) - gw0 + 1;  // word groups per interior row
+  const unsigned m_first = 0x80808080u << (8 * (xs & 3));
+  const unsigned m_last = 0x80808080u >> (8 * (4 * (gw0 + ng) - (xs + iw)));
+  const int nitems = ih * ng;
+  const unsigned inv_ng = ((1u << 20) + ng - 1) / ng;  // k / ng == (k * inv_ng) >> 20 (k < 2^20 / ng)
+
   int n_kept = 0;
   int T = p.ini_th;
   for (int pass = 0; pass < 2; ++pass) {
-    // 1. reject test + ordered compaction; also clears the score tile
-    {
-      uint32_t* z = reinterpret_cast<uint32_t*>(score);
-      for (int k = lane; k < (score_pitch * (ih + 2)) >> 2; k += 32) z[k] = 0;
-    }
-    __syncwarp();
+    const unsigned kT = (unsigned)(127 - min(T, 126)) * 0x01010101u;
+    // ---- 1. necessary test, 4 pixels per word, up to 16 consecutive words per lane and round ----
     int ncand = 0;
-    for (int k0 = 0; k0 < npx; k0 += 32) {
-      const int k = k0 + lane;
-      bool ok = false;
-      if (k < npx) {
-        const int y = (int)(((unsigned)k * inv_iw) >> 20), x = k - y * iw;
-        const uint8_t* c = t0 + y * tp + x;
-        const int v = c[0], c0 = c[3 * tp], c8 = c[-3 * tp], c4 = c[3], c12 = c[-3];
-        const int brightest = min(max(c0, c8), max(c4, c12));  // > v+T needed for a dark-centre corner
-        const int darkest = max(min(c0, c8), min(c4, c12));    // < v-T needed for a bright-centre corner
-        ok = (brightest > v + T) || (darkest < v - T);
+    for (int k0 = 0; k0 < nitems; k0 += 512) {
+      const int nr = min(512, nitems - k0);
+      int m = (nr + 31) >> 5;
+      if (!(m & 1) && m < 16) ++m;  // odd run length: lanes start on different banks
+      const int a = k0 + min(lane * m, nr);
+      const int cnt = min(m, k0 + nr - a);
+      int row = (int)(((unsigned)a * inv_ng) >> 20), gi = a - row * ng;
+      unsigned acc0 = 0, acc1 = 0;
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        if (it < cnt) {
+          const uint32_t* rp = tile32 + (row + 3) * L.tp4 + gw0 + gi;
+          const unsigned wm = rp[-1], wc = rp[0], wp = rp[1];
+          const unsigned up = rp[-3 * L.tp4], dn = rp[3 * L.tp4];
+          const unsigned lf = __funnelshift_r(wm, wc, 8), rt = __funnelshift_r(wc, wp, 24);
+          const unsigned v = gt_bytes(__vabsdiffu4(wc, up), kT) | gt_bytes(__vabsdiffu4(wc, dn), kT);
+          const unsigned h = gt_bytes(__vabsdiffu4(wc, lf), kT) | gt_bytes(__vabsdiffu4(wc, rt), kT);
+          unsigned t = v & h & 0x80808080u;
+          if (gi == 0) t &= m_first;
+          if (gi == ng - 1) t &= m_last;
+          const unsigned nib = __umulhi(t, 0x02040810u);  // sign bits 7,15,23,31 -> bits 0..3 (+ junk above)
+          if (it < 8) acc0 = __funnelshift_r(acc0, nib, 4); else acc1 = __funnelshift_r(acc1, nib, 4);
+          if (++gi == ng) { gi = 0; ++row; }
+        }
       }
-      const unsigned m = __ballot_sync(0xffffffffu, ok);
-      if (ok) cand[ncand + __popc(m & ((1u << lane) - 1))] = (uint16_t)k;
-      ncand += __popc(m);
+      // right-align the runs: item `it` at nibble it & 7, pixel j of the word at bit j of the nibble
+      const int n0 = min(cnt, 8), n1 = max(cnt - 8, 0);
+      acc0 = n0 > 0 ? acc0 >> (4 * (8 - n0)) : 0u;
+      acc1 = n1 > 0 ? acc1 >> (4 * (8 - n1)) : 0u;
+      const int mine = __popc(acc0) + __popc(acc1);
+      int incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int vv = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += vv;
+      }
+      int pos = ncand + incl - mine;
+      ncand += __shfl_sync(0xffffffffu, incl, 31);
+      // emit this lane's candidates in row-major order (ascending bit order)
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        unsigned acc = half ? acc1 : acc0;
+        while (acc) {
+          const int b = __ffs(acc) - 1;
+          acc &= acc - 1;
+          const int it = (b >> 2) + 8 * half, jj = b & 3;
+          const int item = a + it;
+          const int r = (int)(((unsigned)item * inv_ng) >> 20), gq = item - r * ng;
+          cand[pos++] = (uint16_t)((r << 8) | (4 * (gw0 + gq) - xs + jj));
+        }
+      }
+      __syncwarp();
     }
-    __syncwarp();
-    // 2. exact score of the candidates
+    // ---- 2. exact score of the candidates ----
     for (int q = lane; q < ncand; q += 32) {
-      const int k = cand[q];
-      const int y = (int)(((unsigned)k * inv_iw) >> 20), x = k - y * iw;
+      const int c = cand[q];
+      const int y = c >> 8, x = c & 255;
       const int s = fast_score(t0 + y * tp + x, tp);
-      if (s > T) score[(y + 1) * score_pitch + (x + 1)] = (uint8_t)s;
+      if (s > T) score[(y + 1) * L.score_pitch + (x + 1)] = (uint8_t)s;
     }
     __syncwarp();
-    // 3. NMS + ordered emission
+    // ---- 3. NMS + ordered emission ----
     for (int q0 = 0; q0 < ncand; q0 += 32) {
       const int q = q0 + lane;
       bool keep = false;
       int s = 0, x = 0, y = 0;
       if (q < ncand) {
-        const int k = cand[q];
-        y = (int)(((unsigned)k * inv_iw) >> 20); x = k - y * iw;
-        const uint8_t* c = score + (y + 1) * score_pitch + (x + 1);
-        s = c[0];
+        const int c = cand[q];
+        y = c >> 8; x = c & 255;
+        const uint8_t* cs = score + (y + 1) * L.score_pitch + (x + 1);
+        s = cs[0];
         if (s > 0) {
-          const int mx = max(max(max(c[-score_pitch - 1], c[-score_pitch]), max(c[-score_pitch + 1], c[-1])),
-                             max(max(c[1], c[score_pitch - 1]), max(c[score_pitch], c[score_pitch + 1])));
+          const int sp = L.score_pitch;
+          const int mx = max(max(max(cs[-sp - 1], cs[-sp]), max(cs[-sp + 1], cs[-1])),
+                             max(max(cs[1], cs[sp - 1]), max(cs[sp], cs[sp + 1])));
           keep = s > mx;
         }
       }
-      const unsigned m = __ballot_sync(0xffffffffu, keep);
+      const unsigned mk = __ballot_sync(0xffffffffu, keep);
       if (keep)  // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
-        out[n_kept + __popc(m & ((1u << lane) - 1))] =
+        out[n_kept + __popc(mk & ((1u << lane) - 1))] =
             (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(s - 1) << 16);
-      n_kept += __popc(m);
+      n_kept += __popc(mk);
     }
     if (n_kept > 0 || T == p.min_th) break;
     T = p.min_th;  // empty at iniThFAST: rerun the cell at minThFAST (:812-816)
+    // scores written at iniTh (none survived NMS, but some may be set) must not leak into the rerun
+    for (int q = lane; q < ncand; q += 32) {
+      const int c = cand[q];
+      score[((c >> 8) + 1) * L.score_pitch + ((c & 255) + 1)] = 0;
+    }
     __syncwarp();
   }
-  if (lane == 0) *out_cnt = (uint32_t)n_kept;  // hi field 0: the list is already the final one
+  if (lane == 0) *out_cnt = (uint32_t)n_kept;
 }
 
-static void fast_smem_layout(const Plan& p, int* tile_pitch, int* tile_rows, int* score_pitch,
-                             int* score_rows, int* cand_cap) {
+static FastLayout fast_smem_layout(const Plan& p) {
   int mw = 0, mh = 0;
   for (int l = 0; l < p.nlevels; ++l) {
     mw = max(mw, p.lv[l].wcell + 6);
     mh = max(mh, p.lv[l].hcell + 6);
   }
-  *tile_pitch = (mw + 3 + 3 + 3) & ~3;  // + alignment offset (<= 3) + word-load overhang
-  *tile_rows = mh;
-  *score_pitch = ((mw - 6 + 2) + 3) & ~3;
-  *score_rows = mh - 6 + 2;
-  *cand_cap = ((mw - 6) * (mh - 6) + 7) & ~7;
+  FastLayout L;
+  L.tp4 = (mw + 3 + 3) / 4 + 1;  // + alignment offset (<= 3), + one word read right of the last group
+  L.tile_rows = mh;
+  L.score_pitch = ((mw - 6 + 2) + 3) & ~3;
+  L.score_rows = mh - 6 + 2;
+  L.cand_cap = ((mw - 6) * (mh - 6) + 7) & ~7;
+  L.per_warp = (L.tp4 * 4 * L.tile_rows + L.score_pitch * L.score_rows + 2 * L.cand_cap + 15) & ~15;
+  return L;
 }
 
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
-  int tp, tr, sp, sr, cc;
-  fast_smem_layout(p, &tp, &tr, &sp, &sr, &cc);
-  const size_t smem = (size_t)kFastWarps * (tp * tr + sp * sr + 2 * cc);
+  const FastLayout L = fast_smem_layout(p);
+  const size_t smem = (size_t)kFastWarps * L.per_warp;
   static size_t configured = 0;
+  if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
   if (smem > 48 * 1024 && smem > configured) {
     ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
@@ -245,7 +307,7 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
   }
   const long long cells = (long long)nframes * p.cells_per_frame;
   const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, tp, tr, sp, sr, cc);
+  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, L);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
