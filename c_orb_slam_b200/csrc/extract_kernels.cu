@@ -118,25 +118,25 @@ __device__ __forceinline__ unsigned gt_bytes(unsigned x, unsigned k127mT) {
   return ((x & 0x7f7f7f7fu) + k127mT) | x;
 }
 
-struct FastLayout { int tp4, tile_rows, score_pitch, score_rows, cand_cap, per_warp; };
+struct FastLayout { int tp4, tile_rows, cand_cap, per_warp; unsigned inv_tp; };
 
 __global__ void __launch_bounds__(kFastWarps * 32)
-fast_cells_kernel(Plan p, Scratch sc, int nframes, FastLayout L) {
+fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long gcell = (long long)blockIdx.x * kFastWarps + warp;
-  if (gcell >= (long long)nframes * p.cells_per_frame) return;
-  const int f = (int)(gcell / p.cells_per_frame);
-  const int cell = (int)(gcell - (long long)f * p.cells_per_frame);
+  const int cell = blockIdx.x * kFastWarps + warp;
+  if (cell >= p.cells_per_frame) return;
+  const int f = blockIdx.y;
   int level = 0;
   while (level + 1 < p.nlevels && cell >= p.lv[level + 1].cell_base) ++level;
   const LevelGeom& g = p.lv[level];
   const int ci = cell - g.cell_base;
   const int i = ci / g.ncols, j = ci - i * g.ncols;
 
+  const int tp4 = L.tp4, tp = tp4 * 4;
   uint8_t* tile = smem + (size_t)warp * L.per_warp;
-  uint8_t* score = tile + L.tp4 * 4 * L.tile_rows;
-  uint16_t* cand = reinterpret_cast<uint16_t*>(score + L.score_pitch * L.score_rows);
+  uint8_t* score = tile + tp * L.tile_rows;  // same pitch as the tile, one ring of zeros around the interior
+  uint16_t* cand = reinterpret_cast<uint16_t*>(score + tp * (L.tile_rows - 4));
 
   // cell ROI (:789-806)
   const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
@@ -157,62 +157,68 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, FastLayout L) {
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
     const int nw = (off + cw + 3) >> 2, wpitch = g.pitch >> 2;
-    const unsigned inv_nw = ((1u << 20) + nw - 1) / nw;
-    for (int k = lane; k < nw * ch; k += 32) {
-      const int r = (int)(((unsigned)k * inv_nw) >> 20), c = k - r * nw;
-      cp_async4(tile32 + r * L.tp4 + c, src + (size_t)r * wpitch + c);
+    if (nw <= 16) {  // half a warp per row
+      const int c = lane & 15;
+      if (c < nw)
+        for (int r = lane >> 4; r < ch; r += 2) cp_async4(tile32 + r * tp4 + c, src + (size_t)r * wpitch + c);
+    } else {
+      const unsigned inv_nw = ((1u << 20) + nw - 1) / nw;
+      for (int k = lane; k < nw * ch; k += 32) {
+        const int r = (int)(((unsigned)k * inv_nw) >> 20), c = k - r * nw;
+        cp_async4(tile32 + r * tp4 + c, src + (size_t)r * wpitch + c);
+      }
     }
     uint32_t* z = reinterpret_cast<uint32_t*>(score);
-    for (int k = lane; k < (L.score_pitch * (ih + 2)) >> 2; k += 32) z[k] = 0;
+    for (int k = lane; k < tp4 * (ih + 2); k += 32) z[k] = 0;
     cp_async_commit_wait_all();
   }
   __syncwarp();
-  const int tp = L.tp4 * 4;
   const int xs = off + 3;                         // tile byte column of interior pixel x = 0
-  const uint8_t* t0 = tile + 3 * tp + xs;         // interior pixel (0,0)
+  const uint8_t* t0 = tile + 3 * tp + xs;         // interior pixel (0,0); candidates are offsets y*tp + x from here
+  uint8_t* s0 = score + tp + 1;                   // score of interior pixel (0,0)
   const int gw0 = xs >> 2;                        // first word group that holds interior pixels
   const int ng = ((xs + iw - 1) >> 2) - gw0 + 1;  // word groups per interior row
-  const unsigned m_first = 0x80808080u << (8 * (xs & 3));
-  const unsigned m_last = 0x80808080u >> (8 * (4 * (gw0 + ng) - (xs + iw)));
-  const int nitems = ih * ng;
-  const unsigned inv_ng = ((1u << 20) + ng - 1) / ng;  // k / ng == (k * inv_ng) >> 20 (k < 2^20 / ng)
+  const int lead = xs & 3;                        // bytes of the first group left of the interior
+  const int tail = (xs + iw) - 4 * (gw0 + ng - 1);  // interior bytes of the last group (1..4)
+  const int S = (ng + 15) >> 4;                   // row segments (1 unless the cell is wider than 64 px)
+  const int seg_len = S == 1 ? ng : (ng + S - 1) / S;
+  const int units = ih * S;
 
   int n_kept = 0;
   int T = p.ini_th;
   for (int pass = 0; pass < 2; ++pass) {
     const unsigned kT = (unsigned)(127 - min(T, 126)) * 0x01010101u;
-    // ---- 1. necessary test, 4 pixels per word, up to 16 consecutive words per lane and round ----
+    // ---- 1. necessary test, 4 pixels per word; a lane walks one row (segment) with a sliding window ----
     int ncand = 0;
-    for (int k0 = 0; k0 < nitems; k0 += 512) {
-      const int nr = min(512, nitems - k0);
-      int m = (nr + 31) >> 5;
-      if (!(m & 1) && m < 16) ++m;  // odd run length: lanes start on different banks
-      const int a = k0 + min(lane * m, nr);
-      const int cnt = min(m, k0 + nr - a);
-      int row = (int)(((unsigned)a * inv_ng) >> 20), gi = a - row * ng;
-      unsigned acc0 = 0, acc1 = 0;
-#pragma unroll
-      for (int it = 0; it < 16; ++it) {
-        if (it < cnt) {
-          const uint32_t* rp = tile32 + (row + 3) * L.tp4 + gw0 + gi;
-          const unsigned wm = rp[-1], wc = rp[0], wp = rp[1];
-          const unsigned up = rp[-3 * L.tp4], dn = rp[3 * L.tp4];
-          const unsigned lf = __funnelshift_r(wm, wc, 8), rt = __funnelshift_r(wc, wp, 24);
-          const unsigned v = gt_bytes(__vabsdiffu4(wc, up), kT) | gt_bytes(__vabsdiffu4(wc, dn), kT);
-          const unsigned h = gt_bytes(__vabsdiffu4(wc, lf), kT) | gt_bytes(__vabsdiffu4(wc, rt), kT);
-          unsigned t = v & h & 0x80808080u;
-          if (gi == 0) t &= m_first;
-          if (gi == ng - 1) t &= m_last;
-          const unsigned nib = __umulhi(t, 0x02040810u);  // sign bits 7,15,23,31 -> bits 0..3 (+ junk above)
-          if (it < 8) acc0 = __funnelshift_r(acc0, nib, 4); else acc1 = __funnelshift_r(acc1, nib, 4);
-          if (++gi == ng) { gi = 0; ++row; }
-        }
+    for (int u0 = 0; u0 < units; u0 += 32) {
+      const int u = u0 + lane;
+      const int uu = min(u, units - 1);  // idle lanes shadow a valid unit, their result is dropped
+      int row = uu, seg = 0;
+      if (S > 1) { row = uu / S; seg = uu - row * S; }
+      const int g0 = seg * seg_len, len = min(seg_len, ng - g0);
+      const uint32_t* rp = tile32 + (row + 3) * tp4 + gw0 + g0;
+      const uint32_t* rup = rp - 3 * tp4;
+      const uint32_t* rdn = rp + 3 * tp4;
+      unsigned wm = rp[-1], wc = rp[0];
+      unsigned acc_lo = 0, acc_hi = 0;
+      for (int it = 0; it < seg_len; ++it) {
+        const unsigned wp = rp[it + 1], up = rup[it], dn = rdn[it];
+        const unsigned lf = __funnelshift_r(wm, wc, 8), rt = __funnelshift_r(wc, wp, 24);
+        const unsigned v = gt_bytes(__vabsdiffu4(wc, up), kT) | gt_bytes(__vabsdiffu4(wc, dn), kT);
+        const unsigned h = gt_bytes(__vabsdiffu4(wc, lf), kT) | gt_bytes(__vabsdiffu4(wc, rt), kT);
+        const unsigned nib = __umulhi(v & h & 0x80808080u, 0x02040810u);  // sign bits 7,15,23,31 -> bits 0..3 (+ junk above)
+        acc_lo = __funnelshift_r(acc_lo, acc_hi, 4);
+        acc_hi = __funnelshift_r(acc_hi, nib, 4);
+        wm = wc; wc = wp;
       }
-      // right-align the runs: item `it` at nibble it & 7, pixel j of the word at bit j of the nibble
-      const int n0 = min(cnt, 8), n1 = max(cnt - 8, 0);
-      acc0 = n0 > 0 ? acc0 >> (4 * (8 - n0)) : 0u;
-      acc1 = n1 > 0 ? acc1 >> (4 * (8 - n1)) : 0u;
-      const int mine = __popc(acc0) + __popc(acc1);
+      // right-align (group k of the segment at nibble k) and drop everything outside the interior
+      unsigned long long acc = (((unsigned long long)acc_hi << 32) | acc_lo) >> (4 * (16 - seg_len));
+      const int first_bit = g0 == 0 ? lead : 0;
+      const int end_bit = g0 + len == ng ? 4 * (len - 1) + tail : 4 * len;
+      acc &= (end_bit >= 64 ? ~0ull : (1ull << end_bit) - 1) & ~((1ull << first_bit) - 1);
+      if (u >= units) acc = 0;
+      unsigned a_lo = (unsigned)acc, a_hi = (unsigned)(acc >> 32);
+      const int mine = __popc(a_lo) + __popc(a_hi);
       int incl = mine;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -221,59 +227,54 @@ fast_cells_kernel(Plan p, Scratch sc, int nframes, FastLayout L) {
       }
       int pos = ncand + incl - mine;
       ncand += __shfl_sync(0xffffffffu, incl, 31);
-      // emit this lane's candidates in row-major order (ascending bit order)
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        unsigned acc = half ? acc1 : acc0;
-        while (acc) {
-          const int b = __ffs(acc) - 1;
-          acc &= acc - 1;
-          const int it = (b >> 2) + 8 * half, jj = b & 3;
-          const int item = a + it;
-          const int r = (int)(((unsigned)item * inv_ng) >> 20), gq = item - r * ng;
-          cand[pos++] = (uint16_t)((r << 8) | (4 * (gw0 + gq) - xs + jj));
-        }
+      // row-major emission: ascending bit order inside the lane, lanes in unit order
+      const int cbase = row * tp + 4 * (gw0 + g0) - xs;  // bit b of acc is the pixel at offset cbase + b
+      while (a_lo) {
+        const int b = __ffs(a_lo) - 1;
+        a_lo &= a_lo - 1;
+        cand[pos++] = (uint16_t)(cbase + b);
+      }
+      while (a_hi) {
+        const int b = __ffs(a_hi) - 1;
+        a_hi &= a_hi - 1;
+        cand[pos++] = (uint16_t)(cbase + 32 + b);
       }
       __syncwarp();
     }
     // ---- 2. exact score of the candidates ----
     for (int q = lane; q < ncand; q += 32) {
       const int c = cand[q];
-      const int y = c >> 8, x = c & 255;
-      const int s = fast_score(t0 + y * tp + x, tp);
-      if (s > T) score[(y + 1) * L.score_pitch + (x + 1)] = (uint8_t)s;
+      const int s = fast_score(t0 + c, tp);
+      if (s > T) s0[c] = (uint8_t)s;
     }
     __syncwarp();
     // ---- 3. NMS + ordered emission ----
     for (int q0 = 0; q0 < ncand; q0 += 32) {
       const int q = q0 + lane;
       bool keep = false;
-      int s = 0, x = 0, y = 0;
+      int s = 0, c = 0;
       if (q < ncand) {
-        const int c = cand[q];
-        y = c >> 8; x = c & 255;
-        const uint8_t* cs = score + (y + 1) * L.score_pitch + (x + 1);
+        c = cand[q];
+        const uint8_t* cs = s0 + c;
         s = cs[0];
         if (s > 0) {
-          const int sp = L.score_pitch;
-          const int mx = max(max(max(cs[-sp - 1], cs[-sp]), max(cs[-sp + 1], cs[-1])),
-                             max(max(cs[1], cs[sp - 1]), max(cs[sp], cs[sp + 1])));
+          const int mx = max(max(max(cs[-tp - 1], cs[-tp]), max(cs[-tp + 1], cs[-1])),
+                             max(max(cs[1], cs[tp - 1]), max(cs[tp], cs[tp + 1])));
           keep = s > mx;
         }
       }
       const unsigned mk = __ballot_sync(0xffffffffu, keep);
-      if (keep)  // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
+      if (keep) {  // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
+        const int y = (int)(((unsigned)c * L.inv_tp) >> 20), x = c - y * tp;
         out[n_kept + __popc(mk & ((1u << lane) - 1))] =
             (uint32_t)(x + 3) | ((uint32_t)(y + 3) << 8) | ((uint32_t)(s - 1) << 16);
+      }
       n_kept += __popc(mk);
     }
     if (n_kept > 0 || T == p.min_th) break;
     T = p.min_th;  // empty at iniThFAST: rerun the cell at minThFAST (:812-816)
     // scores written at iniTh (none survived NMS, but some may be set) must not leak into the rerun
-    for (int q = lane; q < ncand; q += 32) {
-      const int c = cand[q];
-      score[((c >> 8) + 1) * L.score_pitch + ((c & 255) + 1)] = 0;
-    }
+    for (int q = lane; q < ncand; q += 32) s0[cand[q]] = 0;
     __syncwarp();
   }
   if (lane == 0) *out_cnt = (uint32_t)n_kept;
@@ -286,12 +287,12 @@ static FastLayout fast_smem_layout(const Plan& p) {
     mh = max(mh, p.lv[l].hcell + 6);
   }
   FastLayout L;
-  L.tp4 = (mw + 3 + 3) / 4 + 1;  // + alignment offset (<= 3), + one word read right of the last group
+  L.tp4 = ((mw + 3 + 3) / 4 + 1) | 1;  // + alignment offset (<= 3), + one word right of the last group; odd:
+                                        // lanes walk different rows, an odd word pitch keeps them on different banks
   L.tile_rows = mh;
-  L.score_pitch = ((mw - 6 + 2) + 3) & ~3;
-  L.score_rows = mh - 6 + 2;
   L.cand_cap = ((mw - 6) * (mh - 6) + 7) & ~7;
-  L.per_warp = (L.tp4 * 4 * L.tile_rows + L.score_pitch * L.score_rows + 2 * L.cand_cap + 15) & ~15;
+  L.per_warp = (L.tp4 * 4 * (2 * L.tile_rows - 4) + 2 * L.cand_cap + 15) & ~15;  // tile + score (mh-4 rows) + cand
+  L.inv_tp = ((1u << 20) + L.tp4 * 4 - 1) / (L.tp4 * 4);
   return L;
 }
 
@@ -305,9 +306,8 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
                                       (int)smem));
     configured = smem;
   }
-  const long long cells = (long long)nframes * p.cells_per_frame;
-  const unsigned grid = (unsigned)((cells + kFastWarps - 1) / kFastWarps);
-  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, nframes, L);
+  const dim3 grid((p.cells_per_frame + kFastWarps - 1) / kFastWarps, nframes);
+  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, L);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;

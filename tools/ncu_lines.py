@@ -20,11 +20,15 @@ per_inst = len(set(files)) or 1
 sel = groups[inst * per_inst:(inst + 1) * per_inst]
 tot_ex = tot_s = 0.0
 lines = []
-f = lambda x: float(x) if x not in ("", "N/A", "-") else 0.0
+def f(x):
+    try:
+        return float(x)
+    except ValueError:
+        return 0.0
 for fname, hdr, body in sel:
     iex, ismp = hdr.index("Instructions Executed"), hdr.index("# Samples")
     for r in body:
-        if len(r) > ismp and r[0] != "":
+        if len(r) == len(hdr) and r[0] != "":
             lines.append((f(r[ismp]), f(r[iex]), fname.split("/")[-1], r[0], r[1]))
             tot_ex += f(r[iex]); tot_s += f(r[ismp])
 print("instance %d: total warp-inst %.0f samples %.0f" % (inst, tot_ex, tot_s))
