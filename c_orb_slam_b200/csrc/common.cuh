@@ -57,6 +57,7 @@ struct Plan {
 
 // Per-batch device scratch shared by the extraction kernels.
 struct Scratch {
+  const uint2* cell_tab;  // [cells_per_frame] FAST cell ROIs: x | y<<16, cw | ch<<8 | level<<16 (cw == 0: skipped)
   uint32_t* cell_kp;   // [B][cells_per_frame][cell_cap]  lx | ly<<8 | score<<16
   uint32_t* cell_cnt;  // [B][cells_per_frame]            all | hi<<16
   uint64_t* keys;      // [B][keys_per_frame]             quadtree sort keys (global fallback)

@@ -118,7 +118,7 @@ __device__ __forceinline__ unsigned gt_bytes(unsigned x, unsigned k127mT) {
   return ((x & 0x7f7f7f7fu) + k127mT) | x;
 }
 
-struct FastLayout { int tp4, tile_rows, cand_cap, per_warp; unsigned inv_tp; };
+struct FastLayout { int tp4, tile_bytes, score_bytes, cand_cap, per_warp; unsigned inv_tp; };
 
 __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
@@ -127,25 +127,22 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   const int cell = blockIdx.x * kFastWarps + warp;
   if (cell >= p.cells_per_frame) return;
   const int f = blockIdx.y;
-  int level = 0;
-  while (level + 1 < p.nlevels && cell >= p.lv[level + 1].cell_base) ++level;
-  const LevelGeom& g = p.lv[level];
-  const int ci = cell - g.cell_base;
-  const int i = ci / g.ncols, j = ci - i * g.ncols;
+  // cell ROI (:789-806), precomputed on the host: x | y << 16, cw | ch << 8 | level << 16 (cw == 0: skipped cell)
+  const uint2 cd = __ldg(sc.cell_tab + cell);
+  const int ini_x = (int)(cd.x & 0xffffu), ini_y = (int)(cd.x >> 16);
+  const int cw = (int)(cd.y & 0xffu), ch = (int)((cd.y >> 8) & 0xffu);
+  const LevelGeom& g = p.lv[(cd.y >> 16) & 0xffu];
 
   const int tp4 = L.tp4, tp = tp4 * 4;
   uint8_t* tile = smem + (size_t)warp * L.per_warp;
-  uint8_t* score = tile + tp * L.tile_rows;  // same pitch as the tile, one ring of zeros around the interior
-  uint16_t* cand = reinterpret_cast<uint16_t*>(score + tp * (L.tile_rows - 4));
+  uint8_t* score = tile + L.tile_bytes;  // same pitch as the tile, one ring of zeros around the interior
+  uint16_t* cand = reinterpret_cast<uint16_t*>(score + L.score_bytes);
+  uint16_t* corner = cand;  // compacted in place: a round only overwrites entries it has already read
 
-  // cell ROI (:789-806)
-  const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
-  const int max_y = min(ini_y + g.hcell + 6, g.max_by), max_x = min(ini_x + g.wcell + 6, g.max_bx);
-  const int cw = max_x - ini_x, ch = max_y - ini_y;
-  uint32_t* out = sc.cell_kp + ((size_t)f * p.cells_per_frame + cell) * p.cell_cap;
-  uint32_t* out_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + cell;
-  if (ini_y >= g.max_by - 3 || ini_x >= g.max_bx - 6 || cw < 7 || ch < 7) {
-    if (lane == 0) *out_cnt = 0;
+  const size_t cell_slot = (size_t)f * p.cells_per_frame + cell;
+  uint32_t* out = sc.cell_kp + cell_slot * p.cell_cap;
+  if (cw == 0) {
+    if (lane == 0) sc.cell_cnt[cell_slot] = 0;
     return;
   }
   const int iw = cw - 6, ih = ch - 6;  // detectable interior
@@ -155,21 +152,27 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   const int off = (int)(reinterpret_cast<uintptr_t>(img) & 3);
   uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
   {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
-    const int nw = (off + cw + 3) >> 2, wpitch = g.pitch >> 2;
+    const int nw = (off + cw + 3) >> 2;
     if (nw <= 16) {  // half a warp per row
-      const int c = lane & 15;
+      const int c = lane & 15, r0 = lane >> 4;
+      const uint8_t* src = img - off + (size_t)r0 * g.pitch + 4 * c;
+      unsigned dst = (unsigned)__cvta_generic_to_shared(tile32 + r0 * tp4 + c);
+      const int sstep = 2 * g.pitch;
+      const unsigned dstep = 2 * tp;
       if (c < nw)
-        for (int r = lane >> 4; r < ch; r += 2) cp_async4(tile32 + r * tp4 + c, src + (size_t)r * wpitch + c);
+        for (int r = r0; r < ch; r += 2, src += sstep, dst += dstep)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
     } else {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
+      const int wpitch = g.pitch >> 2;
       const unsigned inv_nw = ((1u << 20) + nw - 1) / nw;
       for (int k = lane; k < nw * ch; k += 32) {
         const int r = (int)(((unsigned)k * inv_nw) >> 20), c = k - r * nw;
         cp_async4(tile32 + r * tp4 + c, src + (size_t)r * wpitch + c);
       }
     }
-    uint32_t* z = reinterpret_cast<uint32_t*>(score);
-    for (int k = lane; k < tp4 * (ih + 2); k += 32) z[k] = 0;
+    uint4* z = reinterpret_cast<uint4*>(score);  // 16-byte aligned; zeroing a little past (ih+2) rows is harmless
+    for (int k = lane; k < (tp4 * (ih + 2) + 3) >> 2; k += 32) z[k] = make_uint4(0, 0, 0, 0);
     cp_async_commit_wait_all();
   }
   __syncwarp();
@@ -241,27 +244,37 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
       }
       __syncwarp();
     }
-    // ---- 2. exact score of the candidates ----
-    for (int q = lane; q < ncand; q += 32) {
-      const int c = cand[q];
-      const int s = fast_score(t0 + c, tp);
-      if (s > T) s0[c] = (uint8_t)s;
+    // ---- 2. exact score of the candidates; corners (score > T) go to a second ordered list ----
+    int ncorner = 0;
+    for (int q0 = 0; q0 < ncand; q0 += 32) {
+      const int q = q0 + lane;
+      int c = 0, s = 0;
+      if (q < ncand) {
+        c = cand[q];
+        s = fast_score(t0 + c, tp);
+      }
+      __syncwarp();  // all reads of this round precede the in-place writes below
+      const bool is_corner = s > T;
+      const unsigned mk = __ballot_sync(0xffffffffu, is_corner);
+      if (is_corner) {
+        s0[c] = (uint8_t)s;
+        corner[ncorner + __popc(mk & ((1u << lane) - 1))] = (uint16_t)c;
+      }
+      ncorner += __popc(mk);
     }
     __syncwarp();
     // ---- 3. NMS + ordered emission ----
-    for (int q0 = 0; q0 < ncand; q0 += 32) {
+    for (int q0 = 0; q0 < ncorner; q0 += 32) {
       const int q = q0 + lane;
       bool keep = false;
       int s = 0, c = 0;
-      if (q < ncand) {
-        c = cand[q];
+      if (q < ncorner) {
+        c = corner[q];
         const uint8_t* cs = s0 + c;
         s = cs[0];
-        if (s > 0) {
-          const int mx = max(max(max(cs[-tp - 1], cs[-tp]), max(cs[-tp + 1], cs[-1])),
-                             max(max(cs[1], cs[tp - 1]), max(cs[tp], cs[tp + 1])));
-          keep = s > mx;
-        }
+        const int mx = max(max(max(cs[-tp - 1], cs[-tp]), max(cs[-tp + 1], cs[-1])),
+                           max(max(cs[1], cs[tp - 1]), max(cs[tp], cs[tp + 1])));
+        keep = s > mx;
       }
       const unsigned mk = __ballot_sync(0xffffffffu, keep);
       if (keep) {  // ROI coordinates as cv::FAST reports them (x+3, y+3), response = score-1
@@ -274,10 +287,10 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
     if (n_kept > 0 || T == p.min_th) break;
     T = p.min_th;  // empty at iniThFAST: rerun the cell at minThFAST (:812-816)
     // scores written at iniTh (none survived NMS, but some may be set) must not leak into the rerun
-    for (int q = lane; q < ncand; q += 32) s0[cand[q]] = 0;
+    for (int q = lane; q < ncorner; q += 32) s0[corner[q]] = 0;
     __syncwarp();
   }
-  if (lane == 0) *out_cnt = (uint32_t)n_kept;
+  if (lane == 0) sc.cell_cnt[cell_slot] = (uint32_t)n_kept;
 }
 
 static FastLayout fast_smem_layout(const Plan& p) {
@@ -289,9 +302,12 @@ static FastLayout fast_smem_layout(const Plan& p) {
   FastLayout L;
   L.tp4 = ((mw + 3 + 3) / 4 + 1) | 1;  // + alignment offset (<= 3), + one word right of the last group; odd:
                                         // lanes walk different rows, an odd word pitch keeps them on different banks
-  L.tile_rows = mh;
-  L.cand_cap = ((mw - 6) * (mh - 6) + 7) & ~7;
-  L.per_warp = (L.tp4 * 4 * (2 * L.tile_rows - 4) + 2 * L.cand_cap + 15) & ~15;  // tile + score (mh-4 rows) + cand
+  L.tile_bytes = (L.tp4 * 4 * mh + 15) & ~15;
+  L.score_bytes = (L.tp4 * 4 * (mh - 4) + 15) & ~15;
+  int area = 0;
+  for (int l = 0; l < p.nlevels; ++l) area = max(area, p.lv[l].wcell * p.lv[l].hcell);
+  L.cand_cap = (area + 7) & ~7;
+  L.per_warp = L.tile_bytes + L.score_bytes + 2 * L.cand_cap;  // tile + score + candidate list
   L.inv_tp = ((1u << 20) + L.tp4 * 4 - 1) / (L.tp4 * 4);
   return L;
 }
@@ -684,125 +700,139 @@ int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t 
 // =============================================================================================
 // 4. GaussianBlur 7x7 sigma 2 (separable integer kernel, REFLECT_101 of the w x h image)
 // =============================================================================================
-// Tile 64x64 per block (256 threads).  Raw tile (+3 px halo, word-aligned loads, REFLECT_101 applied
-// to row indices at load time and to the <=3 halo columns in shared memory), horizontal pass with two
-// IDP4A per pixel on funnel-shifted words (8.8 fixed point, u16), vertical pass with a 10-row register
-// window per 4x4 output patch (16.16), one 32-bit store per 4 pixels.
-constexpr int kBlurTW = 64, kBlurTH = 64;
-constexpr int kBlurRawPitch = kBlurTW + 8;     // bytes: [x0-4, x0+TW+4)
-constexpr int kBlurHPitch = kBlurTW + 4;       // u16 elements (+4 pad against bank conflicts)
+// out = (sum_ij k_i k_j p + 32768) >> 16 with k = [18 34 48 56 48 34 18]; every intermediate is an exact
+// integer, so the two 1-D passes commute: the vertical pass runs first, on packed bytes.
+// One block = a band of kBlurR rows over the full width of one level of one frame; a thread owns
+// 4 adjacent columns (one 32-bit word per row, coalesced loads straight from global memory).
+//   vertical:   the word is split into even/odd bytes (2 x u16 lanes per register); with the 7-row
+//               window in registers the 8.8 column sums are 3 IADD + 4 IMAD per register (sum <= 65280
+//               never carries between the 16-bit lanes);
+//   exchange:   (v0,v1),(v2,v3) u16 pairs go to a shared-memory row buffer (kBlurBatch rows per barrier
+//               pair, double buffered); one small pass mirrors the 3 columns left and right (REFLECT_101);
+//   horizontal: 4 IDP2A per pixel on the u16 pairs (16.16), +32768 folded into the accumulator, >>16,
+//               one 32-bit store per thread and row.
+constexpr int kBlurR = 32, kBlurBatch = 8;
 
 __device__ __forceinline__ int reflect101(int p, int len) {
-  // valid for -len < p < 2*len-1 (3-px halo; len >= 4 guaranteed by the plan)
+  // valid for -len < p < 2*len-1
   p = p < 0 ? -p : p;
   return p >= len ? 2 * (len - 1) - p : p;
 }
 
-__global__ void __launch_bounds__(256)
-blur_kernel(Plan p, int tiles_total) {
-  __shared__ __align__(16) uint8_t s_raw[(kBlurTH + 6) * kBlurRawPitch];
-  __shared__ __align__(16) uint16_t s_h[(kBlurTH + 6) * kBlurHPitch];
-  // tile -> (level, tx, ty); tiles of all levels are laid out consecutively per frame
-  int tile = blockIdx.x;
+__device__ __forceinline__ void bar_sync_n(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(1024)
+blur_kernel(Plan p, int bands_total) {
+  extern __shared__ __align__(16) uint16_t s_rows[];  // [2][kBlurBatch][pitch]
+  int band = blockIdx.x;
   const int f = blockIdx.y;
-  int level = 0, tiles_x = 0;
+  int level = 0;
   for (;; ++level) {
-    const LevelGeom& g = p.lv[level];
-    tiles_x = (g.w + kBlurTW - 1) / kBlurTW;
-    const int nt = tiles_x * ((g.h + kBlurTH - 1) / kBlurTH);
-    if (tile < nt || level + 1 == p.nlevels) break;
-    tile -= nt;
+    const int nb = (p.lv[level].h + kBlurR - 1) / kBlurR;
+    if (band < nb || level + 1 == p.nlevels) break;
+    band -= nb;
   }
   const LevelGeom& g = p.lv[level];
-  const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
-  const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
-  const uint8_t* img = g.img + (size_t)f * g.frame_stride;
   const int t = threadIdx.x;
+  const int nt = (g.w + 3) >> 2;             // threads that own columns of this level
+  const int nactive = (nt + 31) & ~31;       // whole warps beyond leave before any barrier
+  if (t >= nactive) return;
+  const int pitch = 4 * (int)blockDim.x + 8; // u16 elements per row buffer: column x lives at index x + 4
+  const int wi = min(t, nt - 1);
+  const int y0 = band * kBlurR;
+  const uint8_t* src = g.img + (size_t)f * g.frame_stride + 4 * wi;
+  uint8_t* dst = g.blur + (size_t)f * g.bframe_stride + 4 * wi;
+  const int h = g.h, w = g.w;
+  auto load_row = [&](int yy) -> unsigned {  // word of input row yy (reflected; far rows of a partial band are clamped)
+    const int sy = reflect101(min(yy, h + 2), h);
+    return __ldg(reinterpret_cast<const unsigned*>(src + (size_t)sy * g.pitch));
+  };
 
-  // ---- raw tile: 18 words per row, rows reflected ----
-  {
-    const int words_in_row = (g.w + 3) >> 2;  // readable words of an image row
-    constexpr int WPR = kBlurRawPitch / 4;
-    for (int k = t; k < (kBlurTH + 6) * WPR; k += 256) {
-      const int r = k / WPR, c = k - r * WPR;
-      const int sy = reflect101(min(y0 + r - 3, g.h + 2), g.h);
-      const int wi = (x0 >> 2) - 1 + c;
-      uint32_t v = 0;
-      if (wi >= 0 && wi < words_in_row) v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)sy * g.pitch) + wi);
-      reinterpret_cast<uint32_t*>(s_raw)[r * WPR + c] = v;
-    }
-  }
-  __syncthreads();
-  // column halo by reflection (tile column c holds image x = x0 - 4 + c)
-  if (x0 == 0 || x0 + kBlurTW + 3 > g.w - 1) {
-    for (int k = t; k < (kBlurTH + 6) * 6; k += 256) {
-      const int r = k / 6, j = k - r * 6;
-      int x;
-      if (j < 3) { if (x0 != 0) continue; x = -1 - j; }
-      else { x = g.w + (j - 3); if (x - (x0 - 4) >= kBlurRawPitch || x < x0 - 4) continue; }
-      const int sx = reflect101(x, g.w);
-      if (sx - (x0 - 4) < 0 || sx - (x0 - 4) >= kBlurRawPitch) continue;
-      s_raw[r * kBlurRawPitch + (x - (x0 - 4))] = s_raw[r * kBlurRawPitch + (sx - (x0 - 4))];
-    }
-    __syncthreads();
-  }
-  // ---- horizontal: 4 output pixels per item from 3 words, 2 dp4a each ----
-  {
-    const uint32_t K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps 0..3
-    const uint32_t K1 = 48u | (34u << 8) | (18u << 16);                // taps 4..6
-    constexpr int GPR = kBlurTW / 4;
-    for (int k = t; k < (kBlurTH + 6) * GPR; k += 256) {
-      const int r = k / GPR, gq = k - r * GPR;
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(s_raw + r * kBlurRawPitch) + gq;
-      const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];  // bytes x-4..x-1 | x..x+3 | x+4..x+7
-      uint32_t h0 = __dp4a(__funnelshift_r(w0, w1, 8), K0, 0u);
-      h0 = __dp4a(__funnelshift_r(w1, w2, 8), K1, h0);
-      uint32_t h1 = __dp4a(__funnelshift_r(w0, w1, 16), K0, 0u);
-      h1 = __dp4a(__funnelshift_r(w1, w2, 16), K1, h1);
-      uint32_t h2 = __dp4a(__funnelshift_r(w0, w1, 24), K0, 0u);
-      h2 = __dp4a(__funnelshift_r(w1, w2, 24), K1, h2);
-      uint32_t h3 = __dp4a(w1, K0, 0u);
-      h3 = __dp4a(w2, K1, h3);
-      uint2 o;
-      o.x = h0 | (h1 << 16);
-      o.y = h2 | (h3 << 16);
-      *reinterpret_cast<uint2*>(s_h + r * kBlurHPitch + gq * 4) = o;
-    }
-  }
-  __syncthreads();
-  // ---- vertical: thread = 4 columns x 4 rows, 10-row window ----
-  {
-    const int cg = t & 15, slab = t >> 4;  // 16 column groups x 16 row slabs
-    const int x = x0 + cg * 4, yb = y0 + slab * 4;
-    if (x < g.w && yb < g.h) {
-      uint32_t col[10][4];
+  unsigned e[7], o[7];
 #pragma unroll
-      for (int r = 0; r < 10; ++r) {
-        const uint2 v = *reinterpret_cast<const uint2*>(s_h + (slab * 4 + r) * kBlurHPitch + cg * 4);
-        col[r][0] = v.x & 0xffffu; col[r][1] = v.x >> 16; col[r][2] = v.y & 0xffffu; col[r][3] = v.y >> 16;
-      }
-      uint8_t* out = g.blur + (size_t)f * g.bframe_stride + (size_t)yb * g.bpitch + x;
+  for (int r = 0; r < 6; ++r) {
+    const unsigned wd = load_row(y0 - 3 + r);
+    e[r] = __byte_perm(wd, 0, 0x4240);  // (b0, 0, b2, 0)
+    o[r] = __byte_perm(wd, 0, 0x4341);  // (b1, 0, b3, 0)
+  }
+  unsigned nxt[kBlurBatch];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        if (yb + r >= g.h) break;
-        uint32_t packed = 0;
+  for (int k = 0; k < kBlurBatch; ++k) nxt[k] = load_row(y0 + 3 + k);
+
+  // IDP2A weights: .lo uses bytes 0,1 and .hi bytes 2,3 of the second operand
+  const unsigned W1 = (18u << 8) | (34u << 16) | (48u << 24);              // (0,k0) | (k1,k2)
+  const unsigned W2 = 56u | (48u << 8) | (34u << 16) | (18u << 24);        // (k3,k4) | (k5,k6)
+  const unsigned W3 = 18u | (34u << 8) | (48u << 16) | (56u << 24);        // (k0,k1) | (k2,k3)
+  const unsigned W4 = 48u | (34u << 8) | (18u << 16);                      // (k4,k5) | (k6,0)
+
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t v = 18u * (col[r][q] + col[r + 6][q]) + 34u * (col[r + 1][q] + col[r + 5][q]) +
-                             48u * (col[r + 2][q] + col[r + 4][q]) + 56u * col[r + 3][q];
-          packed |= ((v + 32768u) >> 16) << (8 * q);
+  for (int b = 0; b < kBlurR / kBlurBatch; ++b) {
+    unsigned cur[kBlurBatch];
+#pragma unroll
+    for (int k = 0; k < kBlurBatch; ++k) cur[k] = nxt[k];
+    if (b + 1 < kBlurR / kBlurBatch) {
+#pragma unroll
+      for (int k = 0; k < kBlurBatch; ++k) nxt[k] = load_row(y0 + 3 + kBlurBatch * (b + 1) + k);
+    }
+    uint16_t* buf = s_rows + (size_t)(b & 1) * kBlurBatch * pitch;
+    // ---- vertical pass of kBlurBatch rows ----
+#pragma unroll
+    for (int k = 0; k < kBlurBatch; ++k) {
+      const int r = kBlurBatch * b + k + 6;  // index of the newest input row of this output row
+      e[r % 7] = __byte_perm(cur[k], 0, 0x4240);
+      o[r % 7] = __byte_perm(cur[k], 0, 0x4341);
+      const unsigned ve = 18u * (e[(r - 6) % 7] + e[r % 7]) + 34u * (e[(r - 5) % 7] + e[(r - 1) % 7]) +
+                          48u * (e[(r - 4) % 7] + e[(r - 2) % 7]) + 56u * e[(r - 3) % 7];  // (v0, v2)
+      const unsigned vo = 18u * (o[(r - 6) % 7] + o[r % 7]) + 34u * (o[(r - 5) % 7] + o[(r - 1) % 7]) +
+                          48u * (o[(r - 4) % 7] + o[(r - 2) % 7]) + 56u * o[(r - 3) % 7];  // (v1, v3)
+      uint2 pr;
+      pr.x = __byte_perm(ve, vo, 0x5410);  // (v0, v1)
+      pr.y = __byte_perm(ve, vo, 0x7632);  // (v2, v3)
+      *reinterpret_cast<uint2*>(buf + k * pitch + 4 + 4 * t) = pr;
+    }
+    bar_sync_n(1, nactive);
+    // ---- REFLECT_101 columns: x = -1-j <- 1+j and x = w+j <- w-2-j (j = 0..2) ----
+    for (int q = t; q < kBlurBatch * 6; q += nactive) {
+      const int k = q / 6, jj = q - 6 * k;
+      uint16_t* row = buf + k * pitch + 4;
+      if (jj < 3) row[-1 - jj] = row[1 + jj]; else row[w + jj - 3] = row[w + 1 - jj];
+    }
+    bar_sync_n(1, nactive);
+    // ---- horizontal pass ----
+    if (t < nt) {
+#pragma unroll
+      for (int k = 0; k < kBlurBatch; ++k) {
+        const int y = y0 + kBlurBatch * b + k;
+        if (y < h) {
+          const uint2* rp = reinterpret_cast<const uint2*>(buf + k * pitch + 4 * t);
+          const uint2 a = rp[0], c = rp[1], d = rp[2];  // (P0,P1) (P2,P3) (P4,P5): columns 4t-4 .. 4t+7
+          unsigned o0 = __dp2a_lo(a.x, W1, 32768u); o0 = __dp2a_hi(a.y, W1, o0); o0 = __dp2a_lo(c.x, W2, o0); o0 = __dp2a_hi(c.y, W2, o0);
+          unsigned o1 = __dp2a_lo(a.y, W3, 32768u); o1 = __dp2a_hi(c.x, W3, o1); o1 = __dp2a_lo(c.y, W4, o1); o1 = __dp2a_hi(d.x, W4, o1);
+          unsigned o2 = __dp2a_lo(a.y, W1, 32768u); o2 = __dp2a_hi(c.x, W1, o2); o2 = __dp2a_lo(c.y, W2, o2); o2 = __dp2a_hi(d.x, W2, o2);
+          unsigned o3 = __dp2a_lo(c.x, W3, 32768u); o3 = __dp2a_hi(c.y, W3, o3); o3 = __dp2a_lo(d.x, W4, o3); o3 = __dp2a_hi(d.y, W4, o3);
+          const unsigned lo = __byte_perm(o0, o1, 0x0062);  // (o0.b2, o1.b2, -, -)
+          const unsigned hi = __byte_perm(o2, o3, 0x0062);
+          *reinterpret_cast<unsigned*>(dst + (size_t)y * g.bpitch) = __byte_perm(lo, hi, 0x5410);
         }
-        *reinterpret_cast<uint32_t*>(out + (size_t)r * g.bpitch) = packed;
       }
     }
   }
 }
 
 int launch_blur(const Plan& p, int nframes, cudaStream_t s) {
-  int tiles = 0;
-  for (int l = 0; l < p.nlevels; ++l)
-    tiles += ((p.lv[l].w + kBlurTW - 1) / kBlurTW) * ((p.lv[l].h + kBlurTH - 1) / kBlurTH);
-  blur_kernel<<<dim3(tiles, nframes), 256, 0, s>>>(p, tiles);
+  int bands = 0;
+  for (int l = 0; l < p.nlevels; ++l) bands += (p.lv[l].h + kBlurR - 1) / kBlurR;
+  const int threads = (((p.lv[0].w + 3) >> 2) + 31) & ~31;
+  if (threads > 1024) return ORB_GPU_ERR_CAPACITY;
+  const size_t smem = (size_t)2 * kBlurBatch * (4 * threads + 8) * sizeof(uint16_t);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    ORB_CUDA_TRY(cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  blur_kernel<<<dim3(bands, nframes), threads, smem, s>>>(p, bands);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;

@@ -73,7 +73,7 @@ struct OrbGpuExtractor {
   Plan plan;
   int plan_w = 0, plan_h = 0, plan_batch = 0;
   std::vector<size_t> lvl_off;  // byte offset of each level inside pyr/blur (per batch capacity)
-  DevBuf pyr, blur, tables, cell_kp, cell_cnt, keys, pay, sel, sel_cnt, cand_cnt, status;
+  DevBuf pyr, blur, tables, cell_tab, cell_kp, cell_cnt, keys, pay, sel, sel_cnt, cand_cnt, status;
   DevBuf out_kps, out_desc, out_n;
   Scratch sc;
   int last_nframes = 0;
@@ -183,7 +183,7 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
   cudaStreamSynchronize(h->stream);
   int rc;
   if ((rc = h->pyr.ensure(pyr_bytes)) || (rc = h->blur.ensure(pyr_bytes)) ||
-      (rc = h->tables.ensure(table_bytes)) ||
+      (rc = h->tables.ensure(table_bytes)) || (rc = h->cell_tab.ensure((size_t)cells * sizeof(uint2))) ||
       (rc = h->cell_kp.ensure((size_t)batch * cells * cell_cap * 4)) ||
       (rc = h->cell_cnt.ensure((size_t)batch * cells * 4)) ||
       (rc = h->keys.ensure((size_t)batch * keys * 8)) || (rc = h->pay.ensure((size_t)batch * keys * 4)) ||
@@ -210,8 +210,24 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
     g.ax0 = (const short*)(g.yofs + g.h); g.ax1 = g.ax0 + g.w;
     g.ay0 = g.ax1 + g.w; g.ay1 = g.ay0 + g.h;
   }
+  // FAST cell ROIs (:789-806): the skip rules differ for rows (maxBorderY-3) and columns (maxBorderX-6)
+  std::vector<uint2> ctab(cells);
+  for (int l = 0; l < L; ++l) {
+    const LevelGeom& g = p.lv[l];
+    for (int i = 0; i < g.nrows; ++i)
+      for (int j = 0; j < g.ncols; ++j) {
+        const int ini_y = kBorder + i * g.hcell, ini_x = kBorder + j * g.wcell;
+        const int max_y = std::min(ini_y + g.hcell + 6, g.max_by), max_x = std::min(ini_x + g.wcell + 6, g.max_bx);
+        int cw = max_x - ini_x, ch = max_y - ini_y;
+        if (ini_y >= g.max_by - 3 || ini_x >= g.max_bx - 6 || cw < 7 || ch < 7) cw = ch = 0;
+        ctab[g.cell_base + i * g.ncols + j] =
+            make_uint2((unsigned)ini_x | ((unsigned)ini_y << 16), (unsigned)cw | ((unsigned)ch << 8) | ((unsigned)l << 16));
+      }
+  }
+  ORB_CUDA_TRY(cudaMemcpyAsync(h->cell_tab.p, ctab.data(), ctab.size() * sizeof(uint2), cudaMemcpyHostToDevice, h->stream));
   ORB_CUDA_TRY(cudaMemcpyAsync(h->tables.p, tab.data(), table_bytes, cudaMemcpyHostToDevice, h->stream));
   ORB_CUDA_TRY(cudaStreamSynchronize(h->stream));  // `tab` dies at scope exit
+  h->sc.cell_tab = (const uint2*)h->cell_tab.p;
   h->sc.cell_kp = (uint32_t*)h->cell_kp.p; h->sc.cell_cnt = (uint32_t*)h->cell_cnt.p;
   h->sc.keys = (uint64_t*)h->keys.p; h->sc.pay = (uint32_t*)h->pay.p;
   h->sc.sel = (uint32_t*)h->sel.p; h->sc.sel_cnt = (int*)h->sel_cnt.p;
@@ -279,7 +295,7 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   if (!h) return ORB_GPU_OK;
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
-  DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
+  DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_tab, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
                     &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);

@@ -34,3 +34,9 @@ for fname, hdr, body in sel:
 print("instance %d: total warp-inst %.0f samples %.0f" % (inst, tot_ex, tot_s))
 for s, e, fn, ln, src in sorted(lines, key=lambda x: -x[0])[:n]:
     print("%6.2f%% smp %6.2f%% exe  %s:%-4s %s" % (100 * s / max(tot_s, 1), 100 * e / max(tot_ex, 1), fn[:12], ln, src.strip()[:100]))
+if len(sys.argv) > 5:  # line ranges "a-b,c-d" -> share of executed instructions
+    for rng in sys.argv[5].split(","):
+        lo, hi = (int(v) for v in rng.split("-"))
+        e = sum(x[1] for x in lines if x[2].startswith("extract") and lo <= int(x[3]) <= hi)
+        sm = sum(x[0] for x in lines if x[2].startswith("extract") and lo <= int(x[3]) <= hi)
+        print("lines %d-%d: %.1f%% exe %.1f%% smp  (%.0f warp-inst)" % (lo, hi, 100 * e / tot_ex, 100 * sm / tot_s, e))
