@@ -14,13 +14,18 @@
 
 namespace orbgpu {
 
-__constant__ int8_t c_pattern[256 * 4];
+// rBRIEF tests (x0, y0, x1, y1) as floats, read by the descriptor kernel with coalesced 16-byte loads
+__device__ float4 g_pattern[256];
 static const int8_t h_pattern[256 * 4] = {
 #include "brief_pattern.inc"
 };
 
 int upload_constants() {
-  ORB_CUDA_TRY(cudaMemcpyToSymbol(c_pattern, h_pattern, sizeof(h_pattern)));
+  float4 pf[256];
+  for (int k = 0; k < 256; ++k)
+    pf[k] = make_float4((float)h_pattern[4 * k], (float)h_pattern[4 * k + 1], (float)h_pattern[4 * k + 2],
+                        (float)h_pattern[4 * k + 3]);
+  ORB_CUDA_TRY(cudaMemcpyToSymbol(g_pattern, pf, sizeof(pf)));
   return ORB_GPU_OK;
 }
 
@@ -863,111 +868,117 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
-constexpr int kOdWarps = 8;
+constexpr int kOdWarps = 8, kOdSlotsPerWarp = 4, kOdSlotsPerBlock = kOdWarps * kOdSlotsPerWarp;
 
-// One warp per output slot (frame, level, rank in the level's selection).
+__device__ __forceinline__ int round_half_even(float v) {
+  // cvRound for |v| < 2^22: adding 1.5 * 2^23 leaves the rounded integer in the mantissa
+  return __float_as_int(__fadd_rn(v, 12582912.f)) - 0x4B400000;
+}
+
+// One block = 32 consecutive output slots (level, rank in the level's selection) of one frame, one warp
+// per slot, 4 slots per warp.  IC_Angle: lane = patch column u, the rows of the disc that contain it
+// are |v| <= umax[|u|] (the disc is symmetric), 31 coalesced byte loads, shuffle reduction.
 __global__ void __launch_bounds__(kOdWarps * 32)
-orient_desc_kernel(Plan p, Scratch sc, int nframes, OrbKeyPoint* __restrict__ kps,
-                   uint8_t* __restrict__ desc, int capacity, int* __restrict__ n_out) {
-  __shared__ char4 s_pat[256];
-  for (int k = threadIdx.x; k < 256; k += blockDim.x)
-    s_pat[k] = make_char4(c_pattern[4 * k], c_pattern[4 * k + 1], c_pattern[4 * k + 2], c_pattern[4 * k + 3]);
+orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
+                   int capacity, int* __restrict__ n_out) {
+  __shared__ float4 s_pat[256];
+  __shared__ int s_cnt[kMaxLevels], s_before[kMaxLevels + 1];
+  const int f = blockIdx.y;
+  s_pat[threadIdx.x] = g_pattern[threadIdx.x];
+  if (threadIdx.x < p.nlevels) s_cnt[threadIdx.x] = sc.sel_cnt[f * p.nlevels + threadIdx.x];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int l = 0; l < p.nlevels; ++l) { s_before[l] = run; run += s_cnt[l]; }
+    s_before[p.nlevels] = run;
+    if (blockIdx.x == 0) n_out[f] = min(run, capacity);
+  }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long gslot = (long long)blockIdx.x * kOdWarps + warp;
-  if (gslot >= (long long)nframes * p.slots_per_frame) return;
-  const int f = (int)(gslot / p.slots_per_frame);
-  const int slot = (int)(gslot - (long long)f * p.slots_per_frame);
-  int level = 0;
-  while (level + 1 < p.nlevels && slot >= p.lv[level + 1].slot_base) ++level;
-  const LevelGeom& g = p.lv[level];
-  const int rank = slot - g.slot_base;
-  const int* cnt = sc.sel_cnt + f * p.nlevels;
-  int before = 0, total = 0;
-  for (int l = 0; l < p.nlevels; ++l) {
-    const int c = cnt[l];
-    if (l < level) before += c;
-    total += c;
-  }
-  if (slot == 0 && lane == 0) n_out[f] = min(total, capacity);
-  if (rank >= cnt[level]) return;
-  const int out_idx = before + rank;
-  if (out_idx >= capacity) {
-    if (lane == 0) *sc.status = ORB_GPU_ERR_CAPACITY;
-    return;
-  }
-  const uint32_t pv = sc.sel[(size_t)f * p.slots_per_frame + slot];
-  const int cx = (int)(pv & 0xfff) + kBorder, cy = (int)((pv >> 12) & 0xfff) + kBorder;
-  const int resp = (int)(pv >> 24);
+  const int u = lane - kHalfPatch;
+  const int vm = lane < 31 ? p.umax[u < 0 ? -u : u] : -1;  // rows |v| <= vm of column u are inside the disc
 
-  // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc; lane = column u+15
-  const uint8_t* img = g.img + (size_t)f * g.frame_stride + (size_t)cy * g.pitch + cx;
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-    const int u = lane - kHalfPatch;
-    const int au = u < 0 ? -u : u;
-    int vals[31];
-#pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v)  // 31 independent loads in flight
-      vals[v + kHalfPatch] = au <= p.umax[v < 0 ? -v : v] ? (int)__ldg(img + v * g.pitch + u) : 0;
+  for (int it = 0; it < kOdSlotsPerWarp; ++it) {
+    const int slot = blockIdx.x * kOdSlotsPerBlock + it * kOdWarps + warp;
+    if (slot >= p.slots_per_frame) break;
+    int level = 0;
+    while (level + 1 < p.nlevels && slot >= p.lv[level + 1].slot_base) ++level;
+    const LevelGeom& g = p.lv[level];
+    const int rank = slot - g.slot_base;
+    if (rank >= s_cnt[level]) continue;
+    const int out_idx = s_before[level] + rank;
+    if (out_idx >= capacity) {
+      if (lane == 0) *sc.status = ORB_GPU_ERR_CAPACITY;
+      continue;
+    }
+    const uint32_t pv = sc.sel[(size_t)f * p.slots_per_frame + slot];
+    const int cx = (int)(pv & 0xfff) + kBorder, cy = (int)((pv >> 12) & 0xfff) + kBorder;
+    const int resp = (int)(pv >> 24);
+
+    // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc (:77-104)
+    const uint8_t* img = g.img + (size_t)f * g.frame_stride;
+    const unsigned o0 = (unsigned)((cy - kHalfPatch) * g.pitch + cx + u);
     int sv = 0, s1 = 0;
 #pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) { sv += vals[v + kHalfPatch]; s1 += v * vals[v + kHalfPatch]; }
-    m10 = u * sv;
-    m01 = s1;
-  }
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+      int val = 0;
+      if ((v < 0 ? -v : v) <= vm) val = (int)__ldg(img + (o0 + (unsigned)((v + kHalfPatch) * g.pitch)));
+      sv += val;
+      s1 += v * val;
+    }
+    int m10 = u * sv, m01 = s1;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-  }
-  const float angle = fast_atan2_deg((float)m01, (float)m10);
+    for (int o = 16; o > 0; o >>= 1) {
+      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-  // steered BRIEF on the blurred level (:106-147)
-  const float rad = __fmul_rn(angle, 0.017453292519943295f);  // (float)(CV_PI/180.f)
-  double sd, cd;
-  sincos((double)rad, &sd, &cd);
-  const float a = (float)cd, b = (float)sd;
-  const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride + (size_t)cy * g.bpitch + cx;
-  uint32_t* drow = reinterpret_cast<uint32_t*>(desc + ((size_t)f * capacity + out_idx) * 32);
-  int t0[8], t1[8];
+    // steered BRIEF on the blurred level (:106-147)
+    const float rad = __fmul_rn(angle, 0.017453292519943295f);  // (float)(CV_PI/180.f)
+    double sd, cd;
+    sincos((double)rad, &sd, &cd);
+    const float a = (float)cd, b = (float)sd;
+    const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
+    const int c0 = cy * g.bpitch + cx;
+    int t0[8], t1[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {  // 16 independent gathers per lane
-    const char4 t = s_pat[32 * k + lane];
-    const float x0 = (float)t.x, y0 = (float)t.y, x1 = (float)t.z, y1 = (float)t.w;
-    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-    t0[k] = __ldg(bl + r0 * g.bpitch + c0);
-    t1[k] = __ldg(bl + r1 * g.bpitch + c1);
-  }
-  uint32_t words[8];
+    for (int k = 0; k < 8; ++k) {  // 16 independent gathers per lane
+      const float4 t = s_pat[32 * k + lane];
+      const int r0 = round_half_even(__fadd_rn(__fmul_rn(t.x, b), __fmul_rn(t.y, a)));
+      const int q0 = round_half_even(__fsub_rn(__fmul_rn(t.x, a), __fmul_rn(t.y, b)));
+      const int r1 = round_half_even(__fadd_rn(__fmul_rn(t.z, b), __fmul_rn(t.w, a)));
+      const int q1 = round_half_even(__fsub_rn(__fmul_rn(t.z, a), __fmul_rn(t.w, b)));
+      t0[k] = __ldg(bl + (unsigned)(c0 + r0 * g.bpitch + q0));
+      t1[k] = __ldg(bl + (unsigned)(c0 + r1 * g.bpitch + q1));
+    }
+    uint32_t mine = 0;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) words[k] = __ballot_sync(0xffffffffu, t0[k] < t1[k]);  // bit = test 32k+lane
-  uint32_t mine = 0;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) mine = lane == k ? words[k] : mine;
-  if (lane < 8) drow[lane] = mine;  // one coalesced 32-byte store
-  if (lane == 0) {
-    OrbKeyPoint kp;
-    const float fx = (float)cx, fy = (float)cy;
-    kp.x = level ? __fmul_rn(fx, g.scale) : fx;  // keypoint->pt *= scale (:1095-1101)
-    kp.y = level ? __fmul_rn(fy, g.scale) : fy;
-    kp.size = g.patch_size;
-    kp.angle = angle;
-    kp.response = (float)resp;
-    kp.octave = level;
-    kp.class_id = -1;
-    kps[(size_t)f * capacity + out_idx] = kp;
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t wk = __ballot_sync(0xffffffffu, t0[k] < t1[k]);  // bit = test 32k+lane
+      mine = lane == k ? wk : mine;
+    }
+    uint32_t* drow = reinterpret_cast<uint32_t*>(desc + ((size_t)f * capacity + out_idx) * 32);
+    if (lane < 8) drow[lane] = mine;  // one coalesced 32-byte store
+    if (lane == 0) {
+      OrbKeyPoint kp;
+      const float fx = (float)cx, fy = (float)cy;
+      kp.x = level ? __fmul_rn(fx, g.scale) : fx;  // keypoint->pt *= scale (:1095-1101)
+      kp.y = level ? __fmul_rn(fy, g.scale) : fy;
+      kp.size = g.patch_size;
+      kp.angle = angle;
+      kp.response = (float)resp;
+      kp.octave = level;
+      kp.class_id = -1;
+      kps[(size_t)f * capacity + out_idx] = kp;
+    }
   }
 }
 
 int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
-  const long long slots = (long long)nframes * p.slots_per_frame;
-  const unsigned grid = (unsigned)((slots + kOdWarps - 1) / kOdWarps);
-  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, nframes, d_kps, d_desc, capacity, d_n_out);
+  const dim3 grid((p.slots_per_frame + kOdSlotsPerBlock - 1) / kOdSlotsPerBlock, nframes);
+  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
