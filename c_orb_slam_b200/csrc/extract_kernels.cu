@@ -32,39 +32,71 @@ int upload_constants() {
 // =============================================================================================
 // 1. pyramid level l from level l-1
 // =============================================================================================
-// One thread produces 4 consecutive destination pixels of one row (one 32-bit store).
-__global__ void __launch_bounds__(256)
+// cv::resize INTER_LINEAR, 8U fixed point:  T = s[x0]*a0 + s[x1]*a1 (11-bit weights),
+// dst = (((b0 * (T0 >> 4)) >> 16) + ((b1 * (T1 >> 4)) >> 16) + 2) >> 2.
+// A thread owns two adjacent destination columns of a band of kRzRows destination rows: its taps
+// are fixed, so per source row it loads the two aligned words that hold them, one PRMT (lane-constant
+// selector) puts the two tap pairs in one register and two IDP2A give T for both columns.  The 16 loads
+// of kRzBatch destination rows are issued together; the second read of a source row (1.67 destination
+// rows share one) hits L1.  No shared-memory staging, loads and stores are coalesced.
+constexpr int kRzRows = 16, kRzBatch = 4;
+
+__global__ void __launch_bounds__(512)
 resize_level_kernel(LevelGeom src, LevelGeom dst) {
-  const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
-  const int y = blockIdx.y * 8 + threadIdx.y;
-  const int f = blockIdx.z;
-  if (x4 >= dst.w || y >= dst.h) return;
-  const int sy0 = dst.yofs[y];
-  const int sy1 = min(sy0 + 1, src.h - 1);
-  const int b0 = dst.ay0[y], b1 = dst.ay1[y];
-  const uint8_t* s0 = src.img + (size_t)f * src.frame_stride + (size_t)sy0 * src.pitch;
-  const uint8_t* s1 = src.img + (size_t)f * src.frame_stride + (size_t)sy1 * src.pitch;
-  uint32_t packed = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int x = min(x4 + k, dst.w - 1);
-    const int x0 = dst.xofs[x];
-    const int x1 = min(x0 + 1, src.w - 1);
-    const int a0 = dst.ax0[x], a1 = dst.ax1[x];
-    const int r0 = (int)s0[x0] * a0 + (int)s0[x1] * a1;
-    const int r1 = (int)s1[x0] * a0 + (int)s1[x1] * a1;
-    const int v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
-    packed |= (uint32_t)(v & 0xff) << (8 * k);
+  __shared__ int s_sy0[kRzRows];
+  __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];
+  const int f = blockIdx.y;
+  const int dy0 = blockIdx.x * kRzRows;
+  if (threadIdx.x < kRzRows) {
+    const int dy = min(dy0 + (int)threadIdx.x, dst.h - 1);  // rows past the image repeat the last one (not stored)
+    s_sy0[threadIdx.x] = dst.yofs[dy];
+    s_b0[threadIdx.x] = (unsigned)dst.ay0[dy] << 16;
+    s_b1[threadIdx.x] = (unsigned)dst.ay1[dy] << 16;
   }
-  uint8_t* d = dst.img + (size_t)f * dst.frame_stride + (size_t)y * dst.pitch + x4;
-  *reinterpret_cast<uint32_t*>(d) = packed;  // pitch is a multiple of 4; the row tail is padding
+  __syncthreads();
+  const int nt = (dst.w + 1) >> 1;
+  const int last_word = (src.pitch >> 2) - 1;
+  const int rstep = src.pitch >> 2;
+  const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
+  uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
+  for (int t = threadIdx.x; t < nt; t += blockDim.x) {
+    const int dxa = 2 * t, dxb = min(dxa + 1, dst.w - 1);
+    const int xa = dst.xofs[dxa], xb = dst.xofs[dxb];
+    const unsigned wa = (unsigned)(unsigned short)dst.ax0[dxa] | ((unsigned)(unsigned short)dst.ax1[dxa] << 16);
+    const unsigned wb = (unsigned)(unsigned short)dst.ax0[dxb] | ((unsigned)(unsigned short)dst.ax1[dxb] << 16);
+    const int wi0 = xa >> 2, wi1 = min(wi0 + 1, last_word);
+    const int oa = xa & 3, ob = xb - 4 * wi0;  // byte offsets of the two tap pairs in the 8-byte window (<= 6)
+    const unsigned sel = (unsigned)oa | ((unsigned)(oa + 1) << 4) | ((unsigned)ob << 8) | ((unsigned)(ob + 1) << 12);
+    uint8_t* drow = dbase + 2 * t;
+#pragma unroll
+    for (int i0 = 0; i0 < kRzRows; i0 += kRzBatch) {
+      unsigned w[kRzBatch][4];
+#pragma unroll
+      for (int k = 0; k < kRzBatch; ++k) {
+        const int sy0 = s_sy0[i0 + k], sy1 = min(sy0 + 1, src.h - 1);
+        const unsigned* r0 = sbase + sy0 * rstep;
+        const unsigned* r1 = sbase + sy1 * rstep;
+        w[k][0] = r0[wi0]; w[k][1] = r0[wi1]; w[k][2] = r1[wi0]; w[k][3] = r1[wi1];
+      }
+#pragma unroll
+      for (int k = 0; k < kRzBatch; ++k) {
+        const unsigned p0 = __byte_perm(w[k][0], w[k][1], sel), p1 = __byte_perm(w[k][2], w[k][3], sel);
+        const unsigned b0 = s_b0[i0 + k], b1 = s_b1[i0 + k];
+        const unsigned va = (__umulhi(b0, __dp2a_lo(wa, p0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wa, p1, 0u) >> 4) + 2u) >> 2;
+        const unsigned vb = (__umulhi(b0, __dp2a_hi(wb, p0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wb, p1, 0u) >> 4) + 2u) >> 2;
+        if (dy0 + i0 + k < dst.h)
+          *reinterpret_cast<unsigned short*>(drow + (size_t)(i0 + k) * dst.pitch) = (unsigned short)(va | (vb << 8));
+      }
+    }
+  }
 }
 
 int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
   const LevelGeom& d = p.lv[level];
-  dim3 block(32, 8);
-  dim3 grid((d.w + 127) / 128, (d.h + 7) / 8, nframes);
-  resize_level_kernel<<<grid, block, 0, s>>>(p.lv[level - 1], d);
+  const int nt = (d.w + 1) >> 1;
+  const int threads = min(512, (nt + 31) & ~31);
+  dim3 grid((d.h + kRzRows - 1) / kRzRows, nframes);
+  resize_level_kernel<<<grid, threads, 0, s>>>(p.lv[level - 1], d);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;

@@ -272,7 +272,7 @@ int orb_gpu_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
                    int max_width, int max_height, int max_batch, int device, OrbGpuExtractor** out) {
   if (!out) return ORB_GPU_ERR_ARG;
   *out = nullptr;
-  if (nfeatures < 1 || nfeatures > 60000 || nlevels < 1 || nlevels > kMaxLevels || !(scaleFactor > 1.0f) ||
+  if (nfeatures < 1 || nfeatures > 60000 || nlevels < 1 || nlevels > kMaxLevels || !(scaleFactor > 1.0f) || scaleFactor > 2.0f ||
       iniThFAST < 1 || iniThFAST > 254 || minThFAST < 1 || minThFAST > iniThFAST || max_width < 1 ||
       max_height < 1 || max_width > kMaxDim || max_height > kMaxDim || max_batch < 1)
     return ORB_GPU_ERR_ARG;
