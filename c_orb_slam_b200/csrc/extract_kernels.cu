@@ -43,40 +43,43 @@ constexpr int kRzRows = 16, kRzBatch = 4;
 
 __global__ void __launch_bounds__(512)
 resize_level_kernel(LevelGeom src, LevelGeom dst) {
-  __shared__ int s_sy0[kRzRows];
-  __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];
+  __shared__ unsigned s_off0[kRzRows], s_off1[kRzRows];  // word offsets of the two source rows
+  __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];      // vertical weights << 16
   const int f = blockIdx.y;
   const int dy0 = blockIdx.x * kRzRows;
+  const int rstep = src.pitch >> 2;
   if (threadIdx.x < kRzRows) {
     const int dy = min(dy0 + (int)threadIdx.x, dst.h - 1);  // rows past the image repeat the last one (not stored)
-    s_sy0[threadIdx.x] = dst.yofs[dy];
+    const int sy0 = dst.yofs[dy];
+    s_off0[threadIdx.x] = (unsigned)(sy0 * rstep);
+    s_off1[threadIdx.x] = (unsigned)(min(sy0 + 1, src.h - 1) * rstep);
     s_b0[threadIdx.x] = (unsigned)dst.ay0[dy] << 16;
     s_b1[threadIdx.x] = (unsigned)dst.ay1[dy] << 16;
   }
   __syncthreads();
   const int nt = (dst.w + 1) >> 1;
-  const int last_word = (src.pitch >> 2) - 1;
-  const int rstep = src.pitch >> 2;
+  const int last_word = rstep - 1;
   const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
   uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
+  const int nrows = min(kRzRows, dst.h - dy0);
   for (int t = threadIdx.x; t < nt; t += blockDim.x) {
     const int dxa = 2 * t, dxb = min(dxa + 1, dst.w - 1);
     const int xa = dst.xofs[dxa], xb = dst.xofs[dxb];
     const unsigned wa = (unsigned)(unsigned short)dst.ax0[dxa] | ((unsigned)(unsigned short)dst.ax1[dxa] << 16);
     const unsigned wb = (unsigned)(unsigned short)dst.ax0[dxb] | ((unsigned)(unsigned short)dst.ax1[dxb] << 16);
-    const int wi0 = xa >> 2, wi1 = min(wi0 + 1, last_word);
+    const int wi0 = xa >> 2;
+    const unsigned* c0 = sbase + wi0;                       // this thread's two word columns
+    const unsigned* c1 = sbase + min(wi0 + 1, last_word);
     const int oa = xa & 3, ob = xb - 4 * wi0;  // byte offsets of the two tap pairs in the 8-byte window (<= 6)
     const unsigned sel = (unsigned)oa | ((unsigned)(oa + 1) << 4) | ((unsigned)ob << 8) | ((unsigned)(ob + 1) << 12);
     uint8_t* drow = dbase + 2 * t;
-#pragma unroll
+#pragma unroll 1
     for (int i0 = 0; i0 < kRzRows; i0 += kRzBatch) {
       unsigned w[kRzBatch][4];
 #pragma unroll
       for (int k = 0; k < kRzBatch; ++k) {
-        const int sy0 = s_sy0[i0 + k], sy1 = min(sy0 + 1, src.h - 1);
-        const unsigned* r0 = sbase + sy0 * rstep;
-        const unsigned* r1 = sbase + sy1 * rstep;
-        w[k][0] = r0[wi0]; w[k][1] = r0[wi1]; w[k][2] = r1[wi0]; w[k][3] = r1[wi1];
+        const unsigned o0 = s_off0[i0 + k], o1 = s_off1[i0 + k];
+        w[k][0] = c0[o0]; w[k][1] = c1[o0]; w[k][2] = c0[o1]; w[k][3] = c1[o1];
       }
 #pragma unroll
       for (int k = 0; k < kRzBatch; ++k) {
@@ -84,8 +87,8 @@ resize_level_kernel(LevelGeom src, LevelGeom dst) {
         const unsigned b0 = s_b0[i0 + k], b1 = s_b1[i0 + k];
         const unsigned va = (__umulhi(b0, __dp2a_lo(wa, p0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wa, p1, 0u) >> 4) + 2u) >> 2;
         const unsigned vb = (__umulhi(b0, __dp2a_hi(wb, p0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wb, p1, 0u) >> 4) + 2u) >> 2;
-        if (dy0 + i0 + k < dst.h)
-          *reinterpret_cast<unsigned short*>(drow + (size_t)(i0 + k) * dst.pitch) = (unsigned short)(va | (vb << 8));
+        if (i0 + k < nrows) *reinterpret_cast<unsigned short*>(drow) = (unsigned short)(va | (vb << 8));
+        drow += dst.pitch;
       }
     }
   }
