@@ -382,6 +382,8 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
 // scans instead of pointer chasing.  Equal-size ties use the creation sequence.
 constexpr int kQtThreads = 256;
 constexpr int kQtSmemKeys = 4096;   // keys sorted in shared memory up to this many, else global
+constexpr int kQtBins = 4096;       // buckets of the shared-memory sort
+constexpr int kQtKpt = kQtSmemKeys / kQtThreads;  // candidates per thread on the shared-memory path
 
 struct QtNode { int start, end; uint32_t prefix; int depth_new; int seq; };  // depth | isnew<<8
 
@@ -495,7 +497,9 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
 
   // shared memory carve-up
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* s_sort = s_keys + kQtSmemKeys;                       // [sort_cap]
+  uint32_t* s_bkt = reinterpret_cast<uint32_t*>(s_keys + kQtSmemKeys);  // [kQtSmemKeys] bucketed (rest-of-code, arrival)
+  uint32_t* s_bin = s_bkt + kQtSmemKeys;                         // [kQtBins / 2 + 4] packed u16 bucket counters / bases
+  uint64_t* s_sort = reinterpret_cast<uint64_t*>(s_bin + kQtBins / 2 + 4);  // [sort_cap]
   QtNode* list_a = reinterpret_cast<QtNode*>(s_sort + sort_cap); // [ncap]
   QtNode* list_b = list_a + ncap;                                // [ncap]
   int* s_nch = reinterpret_cast<int*>(list_b + ncap);            // [ncap] children per split node
@@ -526,38 +530,129 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   uint64_t* keys = (cpad <= kQtSmemKeys) ? s_keys
                                          : sc.keys + (size_t)f * p.keys_per_frame + g.key_base;
   __syncthreads();
-  // one thread per candidate: its cell is the last one whose arrival base is <= the arrival index
-  for (int arrival = t; arrival < C; arrival += T) {
-    int lo = 0, hi = ncells - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (s_cell[mid] <= arrival) lo = mid; else hi = mid - 1;
-    }
-    const int c = lo;
-    const int ci = c / g.ncols, cj = c - ci * g.ncols;
-    const uint32_t e = cell_kp[(size_t)c * p.cell_cap + (arrival - s_cell[c])];
-    const int resp = (e >> 16) & 0xff;
-    const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
-    // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
-    int root = (int)__fdiv_rn((float)x, g.hx);
-    root = min(root, g.n_ini - 1);
-    int ulx = (int)__fmul_rn(g.hx, (float)root), brx = (int)__fmul_rn(g.hx, (float)(root + 1));
-    int uly = 0, bry = g.box_h;
-    uint32_t code = (uint32_t)root << 24;
-#pragma unroll
-    for (int d = 0; d < kCodeDepth; ++d) {
-      const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
-      const int right = x >= mx, below = y >= my;
-      code |= (uint32_t)(right | (below << 1)) << (22 - 2 * d);
-      if (right) ulx = mx; else brx = mx;
-      if (below) uly = my; else bry = my;
-    }
-    pay[arrival] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)resp << 24);
-    keys[arrival] = ((uint64_t)code << 32) | (uint32_t)arrival;
+  // One thread per candidate: its cell is the last one whose arrival base is <= the arrival index.
+  // Candidates are distinct pixels, so their path codes are distinct: the order by code is found with a
+  // bucket sort instead of a comparison network.  Bucket = root and the first d quadrant digits
+  // (n_ini * 4^d <= kQtBins buckets); rank inside the bucket by counting smaller (rest-of-code, arrival).
+  const bool in_smem = cpad <= kQtSmemKeys;
+  int bdepth = 0;
+  while ((g.n_ini << (2 * (bdepth + 1))) <= kQtBins && bdepth + 1 <= kCodeDepth) ++bdepth;
+  const int bshift = 24 - 2 * bdepth;
+  const int nbins = g.n_ini << (2 * bdepth);
+  if (in_smem) {
+    for (int k = t; k < kQtBins / 2 + 1; k += T) s_bin[k] = 0;
+    __syncthreads();
   }
-  for (int k = C + t; k < cpad; k += T) keys[k] = ~0ull;
-  __syncthreads();
-  block_bitonic_sort(keys, cpad);
+  uint32_t my_code[kQtKpt], my_rank[kQtKpt];
+#pragma unroll
+  for (int q = 0; q < kQtKpt; ++q) {
+    const int arrival = t + q * T;
+    my_code[q] = 0; my_rank[q] = 0;
+    if (in_smem ? arrival < C : q == 0) {
+      for (int arr = arrival; arr < C; arr += in_smem ? C : T) {  // shared-memory path: exactly one candidate per slot
+        int lo = 0, hi = ncells - 1;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (s_cell[mid] <= arr) lo = mid; else hi = mid - 1;
+        }
+        const int c = lo;
+        const int ci = c / g.ncols, cj = c - ci * g.ncols;
+        const uint32_t e = cell_kp[(size_t)c * p.cell_cap + (arr - s_cell[c])];
+        const int resp = (e >> 16) & 0xff;
+        const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
+        // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
+        int root = (int)__fdiv_rn((float)x, g.hx);
+        root = min(root, g.n_ini - 1);
+        int ulx = (int)__fmul_rn(g.hx, (float)root), brx = (int)__fmul_rn(g.hx, (float)(root + 1));
+        int uly = 0, bry = g.box_h;
+        uint32_t code = (uint32_t)root << 24;
+#pragma unroll
+        for (int d = 0; d < kCodeDepth; ++d) {
+          const int mx = ulx + ((brx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+          const int right = x >= mx, below = y >= my;
+          code |= (uint32_t)(right | (below << 1)) << (22 - 2 * d);
+          if (right) ulx = mx; else brx = mx;
+          if (below) uly = my; else bry = my;
+        }
+        pay[arr] = (uint32_t)x | ((uint32_t)y << 12) | ((uint32_t)resp << 24);
+        if (in_smem) {
+          const uint32_t bin = code >> bshift;
+          const uint32_t old = atomicAdd(&s_bin[bin >> 1], (bin & 1) ? 0x10000u : 1u);
+          my_code[q] = code;
+          my_rank[q] = (bin & 1) ? old >> 16 : old & 0xffffu;
+        } else {
+          keys[arr] = ((uint64_t)code << 32) | (uint32_t)arr;
+        }
+      }
+    }
+  }
+  if (in_smem) {
+    __syncthreads();
+    // exclusive scan of the packed u16 counters -> bucket bases (entry nbins = C)
+    {
+      const int nwords = (nbins >> 1) + 1;
+      const int chunk = (nwords + T - 1) / T;
+      const int lo = min(t * chunk, nwords), hi = min(lo + chunk, nwords);
+      int sum = 0;
+      for (int k = lo; k < hi; ++k) { const uint32_t v = s_bin[k]; sum += (int)(v & 0xffffu) + (int)(v >> 16); }
+      int incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((t & 31) >= o) incl += v;
+      }
+      if ((t & 31) == 31) s_warp[t >> 5] = incl;
+      __syncthreads();
+      if (t < 32) {
+        const int nw = T >> 5;
+        int w = t < nw ? s_warp[t] : 0, wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_up_sync(0xffffffffu, wi, o);
+          if (t >= o) wi += v;
+        }
+        if (t < nw) s_warp[t] = wi - w;
+      }
+      __syncthreads();
+      int run = s_warp[t >> 5] + incl - sum;
+      for (int k = lo; k < hi; ++k) {
+        const uint32_t v = s_bin[k];
+        const int c0 = (int)(v & 0xffffu), c1 = (int)(v >> 16);
+        s_bin[k] = (uint32_t)run | ((uint32_t)(run + c0) << 16);
+        run += c0 + c1;
+      }
+    }
+    __syncthreads();
+    const uint32_t rem_mask = (1u << bshift) - 1u;
+#pragma unroll
+    for (int q = 0; q < kQtKpt; ++q) {
+      const int arrival = t + q * T;
+      if (arrival < C) {
+        const uint32_t bin = my_code[q] >> bshift;
+        const uint32_t base = (s_bin[bin >> 1] >> ((bin & 1) * 16)) & 0xffffu;
+        s_bkt[base + my_rank[q]] = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < kQtKpt; ++q) {
+      const int arrival = t + q * T;
+      if (arrival < C) {
+        const uint32_t bin = my_code[q] >> bshift;
+        const int bs = (int)((s_bin[bin >> 1] >> ((bin & 1) * 16)) & 0xffffu);
+        const int be = (int)((s_bin[(bin + 1) >> 1] >> (((bin + 1) & 1) * 16)) & 0xffffu);
+        const uint32_t mine = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
+        int rank = 0;
+        for (int k = bs; k < be; ++k) rank += s_bkt[k] < mine;
+        keys[bs + rank] = ((uint64_t)my_code[q] << 32) | (uint32_t)arrival;
+      }
+    }
+    __syncthreads();
+  } else {
+    for (int k = C + t; k < cpad; k += T) keys[k] = ~0ull;
+    __syncthreads();
+    block_bitonic_sort(keys, cpad);
+  }
 
   // ---- initial list: non-empty roots (:543-585) --------------------------------------------
   QtNode* cur = list_a;
@@ -717,7 +812,7 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
   const LevelGeom& g = p.lv[level];
   const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
-  return (size_t)kQtSmemKeys * 8 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
+  return (size_t)kQtSmemKeys * 12 + (size_t)(kQtBins / 2 + 4) * 4 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
          (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 40) * 4 + 64;
 }
 
