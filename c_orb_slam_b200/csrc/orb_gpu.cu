@@ -85,7 +85,34 @@ struct OrbGpuExtractor {
   // optional per-stage CUDA-event timing (bench/roofline)
   bool timing = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  // host-pointer path: frames go through in chunks, H2D of chunk i+1 and D2H of chunk i-1 overlap
+  // the kernels of chunk i (one copy stream per direction, events per chunk)
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  std::vector<cudaEvent_t> ev_in, ev_done;
 };
+
+static const int kHostChunk = 64;  // frames per chunk of the host-pointer path
+
+// Plan / scratch of the frames [f0, ...) of a batch: every per-frame array advanced by f0 frames.
+static Plan plan_at(const Plan& p, int f0) {
+  Plan q = p;
+  for (int l = 0; l < p.nlevels; ++l) {
+    q.lv[l].img += (size_t)f0 * p.lv[l].frame_stride;
+    q.lv[l].blur += (size_t)f0 * p.lv[l].bframe_stride;
+  }
+  return q;
+}
+static Scratch scratch_at(const Scratch& sc, const Plan& p, int f0) {
+  Scratch q = sc;
+  q.cell_kp += (size_t)f0 * p.cells_per_frame * p.cell_cap;
+  q.cell_cnt += (size_t)f0 * p.cells_per_frame;
+  q.keys += (size_t)f0 * p.keys_per_frame;
+  q.pay += (size_t)f0 * p.keys_per_frame;
+  q.sel += (size_t)f0 * p.slots_per_frame;
+  q.sel_cnt += (size_t)f0 * p.nlevels;
+  q.cand_cnt += (size_t)f0 * p.nlevels;
+  return q;
+}
 
 static int build_tables(OrbGpuExtractor* h) {
   const int L = h->nlevels;
@@ -239,22 +266,22 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
 }
 
 // Runs all stages for `nframes` frames whose level-0 images are described by plan.lv[0].
-static int run_pipeline(OrbGpuExtractor* h, const Plan& p, int nframes, OrbKeyPoint* d_kps,
-                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
+static int run_pipeline(OrbGpuExtractor* h, const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
+                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s, bool reset_status = true) {
   int rc;
-  ORB_CUDA_TRY(cudaMemsetAsync(h->sc.status, 0, sizeof(int), s));
+  if (reset_status) ORB_CUDA_TRY(cudaMemsetAsync(sc.status, 0, sizeof(int), s));
   const bool tm = h->timing;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[0], s));
   for (int l = 1; l < p.nlevels; ++l)
     if ((rc = launch_resize_level(p, l, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[1], s));
-  if ((rc = launch_fast_cells(p, h->sc, nframes, s))) return rc;
+  if ((rc = launch_fast_cells(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[2], s));
-  if ((rc = launch_quadtree(p, h->sc, nframes, s))) return rc;
+  if ((rc = launch_quadtree(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[3], s));
   if ((rc = launch_blur(p, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[4], s));
-  if ((rc = launch_orient_desc(p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  if ((rc = launch_orient_desc(p, sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[5], s));
   return ORB_GPU_OK;
 }
@@ -286,7 +313,16 @@ int orb_gpu_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
   cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { set_last_error("cudaStreamCreate", e); delete h; return ORB_GPU_ERR_CUDA; }
   int rc = upload_constants();
-  if (rc) { cudaStreamDestroy(h->stream); delete h; return rc; }
+  if (!rc && (cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking) != cudaSuccess ||
+              cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking) != cudaSuccess)) {
+    set_last_error("copy streams", cudaGetLastError());
+    rc = ORB_GPU_ERR_CUDA;
+  }
+  if (rc) {
+    if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    cudaStreamDestroy(h->stream); delete h; return rc;
+  }
   *out = h;
   return ORB_GPU_OK;
 }
@@ -295,6 +331,10 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   if (!h) return ORB_GPU_OK;
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
+  cudaStreamSynchronize(h->s_h2d); cudaStreamSynchronize(h->s_d2h);
+  for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
+  for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+  cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
   DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_tab, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
                     &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n};
   for (DevBuf* b : bufs) b->release();
@@ -372,7 +412,7 @@ int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, in
                                      d_frames + (size_t)f * frame_stride, stride, width, height,
                                      cudaMemcpyDeviceToDevice, s));
   }
-  if ((rc = run_pipeline(h, p, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  if ((rc = run_pipeline(h, p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
   if (d_status)
     ORB_CUDA_TRY(cudaMemcpyAsync(d_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToDevice, s));
   h->last_nframes = nframes;
@@ -403,27 +443,52 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       return rc;
     const Plan& p = h->plan;
     const LevelGeom& l0 = p.lv[0];
-    const uint8_t* src = frames + (size_t)f0 * frame_stride;
-    if (frame_stride == stride * (size_t)height) {
-      ORB_CUDA_TRY(cudaMemcpy2DAsync(l0.img, l0.pitch, src, stride, width, (size_t)height * nb,
-                                     cudaMemcpyHostToDevice, s));
-    } else {
-      for (int f = 0; f < nb; ++f)
-        ORB_CUDA_TRY(cudaMemcpy2DAsync(l0.img + (size_t)f * l0.frame_stride, l0.pitch,
-                                       src + (size_t)f * frame_stride, stride, width, height,
-                                       cudaMemcpyHostToDevice, s));
+    const int nchunks = (nb + kHostChunk - 1) / kHostChunk;
+    while ((int)h->ev_in.size() < nchunks) {
+      cudaEvent_t a = nullptr, b = nullptr;
+      ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+      ORB_CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+      h->ev_in.push_back(a); h->ev_done.push_back(b);
     }
-    if ((rc = run_pipeline(h, p, nb, (OrbKeyPoint*)h->out_kps.p, (uint8_t*)h->out_desc.p, capacity,
-                           (int*)h->out_n.p, s)))
-      return rc;
+    ORB_CUDA_TRY(cudaMemsetAsync(h->sc.status, 0, sizeof(int), s));
+    // earlier work on the compute stream (a previous call's kernels) must not race the new uploads
+    ORB_CUDA_TRY(cudaEventRecord(h->ev_done[0], s));
+    ORB_CUDA_TRY(cudaStreamWaitEvent(h->s_h2d, h->ev_done[0], 0));
+    for (int c = 0; c < nchunks; ++c) {  // uploads: all queued on the H2D stream, one event per chunk
+      const int c0 = c * kHostChunk, cn = std::min(kHostChunk, nb - c0);
+      const uint8_t* src = frames + (size_t)(f0 + c0) * frame_stride;
+      uint8_t* dst = l0.img + (size_t)c0 * l0.frame_stride;
+      if (frame_stride == stride * (size_t)height) {
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, l0.pitch, src, stride, width, (size_t)height * cn,
+                                       cudaMemcpyHostToDevice, h->s_h2d));
+      } else {
+        for (int f = 0; f < cn; ++f)
+          ORB_CUDA_TRY(cudaMemcpy2DAsync(dst + (size_t)f * l0.frame_stride, l0.pitch,
+                                         src + (size_t)f * frame_stride, stride, width, height,
+                                         cudaMemcpyHostToDevice, h->s_h2d));
+      }
+      ORB_CUDA_TRY(cudaEventRecord(h->ev_in[c], h->s_h2d));
+    }
+    for (int c = 0; c < nchunks; ++c) {  // kernels of chunk c, then its results leave on the D2H stream
+      const int c0 = c * kHostChunk, cn = std::min(kHostChunk, nb - c0);
+      OrbKeyPoint* dk = (OrbKeyPoint*)h->out_kps.p + (size_t)c0 * capacity;
+      uint8_t* dd = (uint8_t*)h->out_desc.p + (size_t)c0 * capacity * 32;
+      int* dn = (int*)h->out_n.p + c0;
+      ORB_CUDA_TRY(cudaStreamWaitEvent(s, h->ev_in[c], 0));
+      if ((rc = run_pipeline(h, plan_at(p, c0), scratch_at(h->sc, p, c0), cn, dk, dd, capacity, dn, s, false)))
+        return rc;
+      ORB_CUDA_TRY(cudaEventRecord(h->ev_done[c], s));
+      ORB_CUDA_TRY(cudaStreamWaitEvent(h->s_d2h, h->ev_done[c], 0));
+      ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0 + c0, dn, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, h->s_d2h));
+      ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)(f0 + c0) * capacity, dk, (size_t)cn * capacity * sizeof(OrbKeyPoint),
+                                   cudaMemcpyDeviceToHost, h->s_d2h));
+      ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)(f0 + c0) * capacity * 32, dd, (size_t)cn * capacity * 32,
+                                   cudaMemcpyDeviceToHost, h->s_d2h));
+    }
     int dev_status = 0;
-    ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0, h->out_n.p, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, s));
-    ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)f0 * capacity, h->out_kps.p,
-                                 (size_t)nb * capacity * sizeof(OrbKeyPoint), cudaMemcpyDeviceToHost, s));
-    ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)f0 * capacity * 32, h->out_desc.p, (size_t)nb * capacity * 32,
-                                 cudaMemcpyDeviceToHost, s));
     ORB_CUDA_TRY(cudaMemcpyAsync(&dev_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToHost, s));
     ORB_CUDA_TRY(cudaStreamSynchronize(s));
+    ORB_CUDA_TRY(cudaStreamSynchronize(h->s_d2h));
     if (dev_status) status_all = dev_status;
     h->last_nframes = nb;
     h->have_result = true;
