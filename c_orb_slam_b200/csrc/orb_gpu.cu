@@ -3,6 +3,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -91,7 +92,13 @@ struct OrbGpuExtractor {
   std::vector<cudaEvent_t> ev_in, ev_done;
 };
 
-static const int kHostChunk = 64;  // frames per chunk of the host-pointer path
+// Frames per chunk of the host-pointer path: a quarter of the batch, between 32 and 128 (small chunks
+// leave the kernels short of blocks, large ones expose the first upload); ORB_GPU_HOST_CHUNK overrides.
+static int host_chunk(int nb) {
+  static const int forced = [] { const char* e = getenv("ORB_GPU_HOST_CHUNK"); return e ? atoi(e) : 0; }();
+  if (forced > 0) return forced;
+  return std::max(32, std::min(128, (nb + 3) / 4));
+}
 
 // Plan / scratch of the frames [f0, ...) of a batch: every per-frame array advanced by f0 frames.
 static Plan plan_at(const Plan& p, int f0) {
@@ -443,6 +450,7 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       return rc;
     const Plan& p = h->plan;
     const LevelGeom& l0 = p.lv[0];
+    const int kHostChunk = host_chunk(nb);
     const int nchunks = (nb + kHostChunk - 1) / kHostChunk;
     while ((int)h->ev_in.size() < nchunks) {
       cudaEvent_t a = nullptr, b = nullptr;
