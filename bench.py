@@ -241,29 +241,16 @@ def run_ours(args):
     hamming = None
     if not args.skip_hamming:
         nq, ndb_total = 4096, args.db_rows
-        lo = ndb_total * rank // world
-        hi = ndb_total * (rank + 1) // world
+        from c_orb_slam_b200 import parallel
+        lo, hi = parallel.shard_range(ndb_total, rank, world)  # contiguous row block of this rank
         g = torch.Generator(device=dev)
         g.manual_seed(7 + rank)
         db = torch.randint(0, 256, (hi - lo, 32), dtype=torch.uint8, device=dev, generator=g)
         g.manual_seed(99)
         q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)
-        part = torch.empty((3, nq), dtype=torch.int32, device=dev)
-        gathered = torch.empty((world, 3, nq), dtype=torch.int32, device=dev)
-        merged = torch.empty((3, nq), dtype=torch.int32, device=dev)
-
         def step_match():
-            rc = L.orb_gpu_match_bruteforce_device(q.data_ptr(), nq, db.data_ptr(), hi - lo, lo, part[0].data_ptr(),
-                                                   part[1].data_ptr(), part[2].data_ptr(), stream)
-            if rc:
-                raise SystemExit("orb_gpu_match_bruteforce_device failed: %d" % rc)
-            if world > 1:
-                dist.all_gather_into_tensor(gathered, part)  # 48 KB per rank over NVLink
-                gt = gathered.permute(1, 0, 2).contiguous()  # [3][world][nq]
-                rc = L.orb_gpu_merge_top2_device(gt[0].data_ptr(), gt[1].data_ptr(), gt[2].data_ptr(), world, nq,
-                                                 merged[0].data_ptr(), merged[1].data_ptr(), merged[2].data_ptr(), stream)
-                if rc:
-                    raise SystemExit("orb_gpu_merge_top2_device failed: %d" % rc)
+            # device match of the local rows (+ one all_gather of [3][nq] int32 and the exact merge kernel if N > 1)
+            return parallel.match_bruteforce_sharded(q, db, lo, stream=stream)
 
         for _ in range(2):
             step_match()

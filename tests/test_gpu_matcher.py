@@ -99,3 +99,26 @@ def test_stereo_match(gpu, oracle):
     bi_g, bd_g = gpu.ORBmatcher().stereo_match(kl, dl, kr, dr, H, sf, 0.0, max_d)
     assert (bi_o >= 0).sum() > 200
     assert np.array_equal(bi_g, bi_o) and np.array_equal(bd_g, bd_o)
+
+
+def test_sharded_bruteforce_merge_on_device(gpu, oracle):
+    """Database split into 3 row shards on one GPU: per-shard device match + merge kernel == whole database
+    (the N>1 path of c_orb_slam_b200.parallel without the all_gather; gloo covers that on CPU)."""
+    import torch
+    from c_orb_slam_b200 import parallel
+    q, db = synth.make_match_set(300, 25003, seed=3)
+    dq = torch.from_numpy(q).cuda()
+    L = gpu.lib()
+    parts = []
+    for r in range(3):
+        lo, hi = parallel.shard_range(len(db), r, 3)
+        parts.append(parallel.match_bruteforce_sharded(dq, torch.from_numpy(db[lo:hi]).cuda(), lo))
+    g = torch.stack(parts).permute(1, 0, 2).contiguous()  # [3][shards][nq]
+    out = torch.empty((3, len(q)), dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert L.orb_gpu_merge_top2_device(g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), 3, len(q),
+                                       out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    oi, ob, os_ = oracle.match_bruteforce(q, db, threads=8)
+    o = out.cpu().numpy()
+    assert np.array_equal(o[0], oi) and np.array_equal(o[1], ob) and np.array_equal(o[2], os_)
