@@ -117,7 +117,7 @@ def run_reference_arm(args):
             "config": {"workload": "TUM 640x480, 1000 features, 8 levels, 1.2, FAST 20/7 (configs[0]); CPU sample of %d frames/step" % sample},
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": desc},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -206,8 +206,16 @@ def run_ours(args):
     stage_bytes = {"pyramid": 926546 + 643332, "fast": P_PIXELS, "blur": 2 * P_PIXELS,
                    "quadtree": 9000 * 12, "orient_desc": 60 * s["nfeatures"]}
     achieved = stage_bytes[top] * B / (acc[top] * 1e-3) / 1e9
+    traffic = None  # DRAM bytes per launch of that kernel from the committed ncu capture (per frame x frames per launch)
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+            per_frame = json.load(f)["bytes_per_frame"].get(top)
+        traffic = per_frame * B if per_frame else None
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                "frac": achieved / hbm, "traffic": None, "peak_kind": peak_kind,
+                "frac": achieved / hbm, "traffic": traffic, "algorithmic_bytes_per_launch": stage_bytes[top] * B,
+                "peak_kind": peak_kind,
                 "stage_ms": acc, "launches_per_step": launches / max(1, args.steps)}
     pipe_gbs = ALGO_BYTES_PER_FRAME * B * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline["pipeline"] = {"achieved": pipe_gbs, "frac": pipe_gbs / hbm, "bytes_per_frame": ALGO_BYTES_PER_FRAME}
@@ -297,12 +305,26 @@ def run_ours(args):
                            "keypoints_per_frame": kp_total / B},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks, "hamming": hamming}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else (NCCL banners, library chatter written to
+    fd 1 from C) was redirected to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
+
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
