@@ -999,6 +999,9 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kOdWarps = 8, kOdSlotsPerWarp = 4, kOdSlotsPerBlock = kOdWarps * kOdSlotsPerWarp;
+constexpr int kOdReach = 18;                      // |rotated tap| <= ceil(13 * sqrt(2)) = 18 < EDGE_THRESHOLD
+constexpr int kOdRows = 2 * kOdReach + 1;         // 37 rows of the blurred level around the keypoint
+constexpr int kOdWords = (kOdRows + 3 + 3) / 4;   // 10 words per row: 37 px + alignment offset (<= 3)
 
 __device__ __forceinline__ int round_half_even(float v) {
   // cvRound for |v| < 2^22: adding 1.5 * 2^23 leaves the rounded integer in the mantissa
@@ -1012,6 +1015,7 @@ __global__ void __launch_bounds__(kOdWarps * 32)
 orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
                    int capacity, int* __restrict__ n_out) {
   __shared__ float4 s_pat[256];
+  __shared__ uint32_t s_tile[kOdWarps][kOdRows * kOdWords];
   __shared__ int s_cnt[kMaxLevels], s_before[kMaxLevels + 1];
   const int f = blockIdx.y;
   s_pat[threadIdx.x] = g_pattern[threadIdx.x];
@@ -1027,6 +1031,7 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int u = lane - kHalfPatch;
   const int vm = lane < 31 ? p.umax[u < 0 ? -u : u] : -1;  // rows |v| <= vm of column u are inside the disc
+  uint32_t* my_tile = s_tile[warp];
 
   for (int it = 0; it < kOdSlotsPerWarp; ++it) {
     const int slot = blockIdx.x * kOdSlotsPerBlock + it * kOdWarps + warp;
@@ -1044,6 +1049,24 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     const uint32_t pv = sc.sel[(size_t)f * p.slots_per_frame + slot];
     const int cx = (int)(pv & 0xfff) + kBorder, cy = (int)((pv >> 12) & 0xfff) + kBorder;
     const int resp = (int)(pv >> 24);
+
+    // The rotated BRIEF taps stay within 18 px of the keypoint (|x|,|y| <= 13): the 37 x 37 window of the
+    // blurred level is staged in shared memory with coalesced word copies (10 words per row, issued now
+    // so they fly during the orientation pass); the 512 byte gathers then hit shared memory, not L1/L2.
+    {
+      const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
+      const int xal = (cx - kOdReach) & ~3;
+      const uint8_t* src = bl + (size_t)(cy - kOdReach) * g.bpitch + xal;
+#pragma unroll
+      for (int i = 0; i < (kOdRows * kOdWords + 31) / 32; ++i) {
+        const int k = lane + 32 * i;
+        if (k < kOdRows * kOdWords) {
+          const int r = k / kOdWords, c = k - r * kOdWords;
+          cp_async4(my_tile + k, src + (size_t)r * g.bpitch + 4 * c);
+        }
+      }
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
 
     // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc (:77-104)
     const uint8_t* img = g.img + (size_t)f * g.frame_stride;
@@ -1069,19 +1092,21 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     double sd, cd;
     sincos((double)rad, &sd, &cd);
     const float a = (float)cd, b = (float)sd;
-    const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
-    const int c0 = cy * g.bpitch + cx;
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncwarp();
+    const uint8_t* tc = reinterpret_cast<const uint8_t*>(my_tile) + kOdReach * (4 * kOdWords) + kOdReach + ((cx - kOdReach) & 3);
     int t0[8], t1[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {  // 16 independent gathers per lane
+    for (int k = 0; k < 8; ++k) {  // 16 gathers per lane from the staged window
       const float4 t = s_pat[32 * k + lane];
       const int r0 = round_half_even(__fadd_rn(__fmul_rn(t.x, b), __fmul_rn(t.y, a)));
       const int q0 = round_half_even(__fsub_rn(__fmul_rn(t.x, a), __fmul_rn(t.y, b)));
       const int r1 = round_half_even(__fadd_rn(__fmul_rn(t.z, b), __fmul_rn(t.w, a)));
       const int q1 = round_half_even(__fsub_rn(__fmul_rn(t.z, a), __fmul_rn(t.w, b)));
-      t0[k] = __ldg(bl + (unsigned)(c0 + r0 * g.bpitch + q0));
-      t1[k] = __ldg(bl + (unsigned)(c0 + r1 * g.bpitch + q1));
+      t0[k] = tc[r0 * (4 * kOdWords) + q0];
+      t1[k] = tc[r1 * (4 * kOdWords) + q1];
     }
+    __syncwarp();  // the window is rewritten by the next slot
     uint32_t mine = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
