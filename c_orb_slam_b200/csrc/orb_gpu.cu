@@ -75,7 +75,7 @@ struct OrbGpuExtractor {
   int plan_w = 0, plan_h = 0, plan_batch = 0;
   std::vector<size_t> lvl_off;  // byte offset of each level inside pyr/blur (per batch capacity)
   DevBuf pyr, blur, tables, cell_tab, cell_kp, cell_cnt, keys, pay, sel, sel_cnt, cand_cnt, status;
-  DevBuf out_kps, out_desc, out_n;
+  DevBuf out_kps, out_desc, out_n, stage;
   Scratch sc;
   int last_nframes = 0;
   bool have_result = false;
@@ -343,7 +343,7 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
   cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
   DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_tab, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
-                    &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n};
+                    &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n, &h->stage};
   for (DevBuf* b : bufs) b->release();
   for (int i = 0; i < 6; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   cudaStreamDestroy(h->stream);
@@ -462,19 +462,17 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
     // earlier work on the compute stream (a previous call's kernels) must not race the new uploads
     ORB_CUDA_TRY(cudaEventRecord(h->ev_done[0], s));
     ORB_CUDA_TRY(cudaStreamWaitEvent(h->s_h2d, h->ev_done[0], 0));
-    for (int c = 0; c < nchunks; ++c) {  // uploads: all queued on the H2D stream, one event per chunk
+    // Uploads are plain 1-D copies of the caller's layout into a staging buffer (a 2-D copy with a row pitch
+    // change runs far below PCIe speed); level 0 then aliases the staging buffer when its rows are 4-byte
+    // aligned, else the frames are repacked on the device.
+    const size_t frame_bytes = stride * (size_t)height;
+    if ((rc = h->stage.ensure((size_t)(nb - 1) * frame_stride + frame_bytes + 16))) return rc;
+    uint8_t* stage = (uint8_t*)h->stage.p;
+    const bool alias = (stride & 3) == 0 && (frame_stride & 3) == 0;
+    for (int c = 0; c < nchunks; ++c) {  // all queued on the H2D stream, one event per chunk
       const int c0 = c * kHostChunk, cn = std::min(kHostChunk, nb - c0);
-      const uint8_t* src = frames + (size_t)(f0 + c0) * frame_stride;
-      uint8_t* dst = l0.img + (size_t)c0 * l0.frame_stride;
-      if (frame_stride == stride * (size_t)height) {
-        ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, l0.pitch, src, stride, width, (size_t)height * cn,
-                                       cudaMemcpyHostToDevice, h->s_h2d));
-      } else {
-        for (int f = 0; f < cn; ++f)
-          ORB_CUDA_TRY(cudaMemcpy2DAsync(dst + (size_t)f * l0.frame_stride, l0.pitch,
-                                         src + (size_t)f * frame_stride, stride, width, height,
-                                         cudaMemcpyHostToDevice, h->s_h2d));
-      }
+      ORB_CUDA_TRY(cudaMemcpyAsync(stage + (size_t)c0 * frame_stride, frames + (size_t)(f0 + c0) * frame_stride,
+                                   (size_t)(cn - 1) * frame_stride + frame_bytes, cudaMemcpyHostToDevice, h->s_h2d));
       ORB_CUDA_TRY(cudaEventRecord(h->ev_in[c], h->s_h2d));
     }
     for (int c = 0; c < nchunks; ++c) {  // kernels of chunk c, then its results leave on the D2H stream
@@ -483,8 +481,18 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       uint8_t* dd = (uint8_t*)h->out_desc.p + (size_t)c0 * capacity * 32;
       int* dn = (int*)h->out_n.p + c0;
       ORB_CUDA_TRY(cudaStreamWaitEvent(s, h->ev_in[c], 0));
-      if ((rc = run_pipeline(h, plan_at(p, c0), scratch_at(h->sc, p, c0), cn, dk, dd, capacity, dn, s, false)))
-        return rc;
+      Plan pc = plan_at(p, c0);
+      if (alias) {
+        pc.lv[0].img = stage + (size_t)c0 * frame_stride;
+        pc.lv[0].pitch = (int)stride;
+        pc.lv[0].frame_stride = (long long)frame_stride;
+      } else {
+        for (int f = 0; f < cn; ++f)
+          ORB_CUDA_TRY(cudaMemcpy2DAsync(pc.lv[0].img + (size_t)f * pc.lv[0].frame_stride, pc.lv[0].pitch,
+                                         stage + (size_t)(c0 + f) * frame_stride, stride, width, height,
+                                         cudaMemcpyDeviceToDevice, s));
+      }
+      if ((rc = run_pipeline(h, pc, scratch_at(h->sc, p, c0), cn, dk, dd, capacity, dn, s, false))) return rc;
       ORB_CUDA_TRY(cudaEventRecord(h->ev_done[c], s));
       ORB_CUDA_TRY(cudaStreamWaitEvent(h->s_d2h, h->ev_done[c], 0));
       ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0 + c0, dn, (size_t)cn * sizeof(int), cudaMemcpyDeviceToHost, h->s_d2h));
@@ -500,7 +508,8 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
     if (dev_status) status_all = dev_status;
     h->last_nframes = nb;
     h->have_result = true;
-    h->last_l0 = l0.img; h->last_l0_pitch = l0.pitch; h->last_l0_stride = l0.frame_stride;
+    if (alias) { h->last_l0 = stage; h->last_l0_pitch = (int)stride; h->last_l0_stride = (long long)frame_stride; }
+    else { h->last_l0 = l0.img; h->last_l0_pitch = l0.pitch; h->last_l0_stride = l0.frame_stride; }
   }
   return status_all;
 }
