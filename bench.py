@@ -64,7 +64,7 @@ class ClockSampler(threading.Thread):
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.02)
+                time.sleep(0.002)
         except Exception as e:  # NVML missing: report nothing rather than guess
             self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
 
@@ -263,19 +263,28 @@ def run_ours(args):
         for _ in range(2):
             step_match()
         barrier()
-        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         hsteps = max(1, min(args.steps, 5))
-        h0.record()
-        for _ in range(hsteps):
-            step_match()
-        h1.record()
-        barrier()
-        hms = max_over_ranks(h0.elapsed_time(h1))
+        hms, hclocks = None, None
+        for attempt in range(2):  # a run that saw a thermal / hardware slowdown is re-measured once
+            hs = ClockSampler(local)
+            hs.start()
+            h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            h0.record()
+            for _ in range(hsteps):
+                step_match()
+            h1.record()
+            barrier()
+            hms = max_over_ranks(h0.elapsed_time(h1))
+            hclocks = hs.result()
+            if not any(r in hclocks["reasons"] for r in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")):
+                break
         gpairs = nq * ndb_total * hsteps / (hms * 1e-3) / 1e9
         popc = orb.popc_peak(local)
         hamming = {"value": gpairs, "unit": "Gpairs/s", "scaling": "strong", "ms_per_step": hms / hsteps,
                    "config": {"workload": "brute-force top-2, %d queries x %d database rows, database sharded over %d GPU(s), "
                                           "top-2 all-gather + exact merge" % (nq, ndb_total, world)},
+                   "clocks": hclocks,
                    "roofline": {"bound": "int-pipe (POPC)", "achieved": gpairs * 8 / world, "peak": popc / 1e9,
                                 "unit": "GPOPC-equivalents/s per GPU (8 per pair)", "frac": gpairs * 8 / world / (popc / 1e9),
                                 "peak_kind": "measured here: dependent-free POPC stream, orb_gpu_popc_peak"}}
