@@ -22,7 +22,10 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("level", "<i4"),
                        ("view_cos", "<f4"), ("valid", "u1"), ("has_obs", "u1"), ("pad", "u1", (2,))])
-assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24
+WINDOW_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("min_level", "<i4"),
+                         ("max_level", "<i4"), ("angle", "<f4"), ("valid", "u1"), ("blocks", "u1"),
+                         ("pad", "u1", (2,))])
+assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24 and WINDOW_DTYPE.itemsize == 32
 
 EXPORTS = [
     "orb_gpu_create", "orb_gpu_destroy", "orb_gpu_extract", "orb_gpu_extract_batch",
@@ -30,7 +33,7 @@ EXPORTS = [
     "orb_gpu_get_scale_tables", "orb_gpu_get_features_per_level", "orb_gpu_get_pyramid",
     "orb_gpu_get_candidates", "orb_gpu_hamming_pairs_device", "orb_gpu_match_bruteforce_device",
     "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
-    "orb_gpu_search_by_projection", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
+    "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
     "orb_gpu_launch_count", "orb_gpu_popc_peak",
 ]
 
@@ -96,6 +99,9 @@ def lib():
                                                    C.c_void_p, C.c_int, _Grid, C.c_void_p, C.c_int, C.c_float,
                                                    C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                                    C.POINTER(C.c_int)]
+        L.orb_gpu_search_windowed.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int, _Grid, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                              C.c_void_p, C.POINTER(C.c_int)]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -297,6 +303,32 @@ class ORBmatcher:
                                                   g, _p(sf), len(sf), th, self.mfNNratio, self.TH_HIGH,
                                                   self.device, _p(blocked), _p(out), C.byref(n)),
                "orb_gpu_search_by_projection")
+        return n.value, out
+
+    def SearchWindowed(self, frame, queries, qdesc, th_accept=None, stereo_gate=False):
+        """Best-only windowed search shared by ORBmatcher::SearchByProjection(Cur, Last, th, bMono)
+        (ORBmatcher.cc:1328-1470; th_accept=TH_HIGH, stereo_gate=True), (Cur, KF, sAlreadyFound, th, ORBdist)
+        (:1472-1599; th_accept=ORBdist) and (KF, Scw, vpPoints, vpMatched, th) (:290-403; th_accept=TH_LOW,
+        no orientation check).  queries: WINDOW_DTYPE [M] computed by the caller like the reference does
+        (projection, radius, level window, source angle).  frame as in SearchByProjection.
+        -> nmatches, match_of_kp [N]; frame['blocked'] is updated in place."""
+        kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
+        kd = np.ascontiguousarray(frame["desc"], np.uint8)
+        ur = frame.get("u_right")
+        ur = None if ur is None else np.ascontiguousarray(ur, np.float32)
+        blocked = frame.get("blocked")
+        if blocked is None:
+            blocked = frame["blocked"] = np.zeros(len(kps), np.uint8)
+        wq = np.ascontiguousarray(queries, WINDOW_DTYPE)
+        qd = np.ascontiguousarray(qdesc, np.uint8)
+        g = _Grid(*[float(v) for v in frame["grid"]])
+        out = np.empty(len(kps), np.int32)
+        n = C.c_int()
+        th_accept = self.TH_HIGH if th_accept is None else int(th_accept)
+        _check(lib().orb_gpu_search_windowed(_p(wq), _p(qd), len(wq), _p(kps), _p(kd), _p(ur), len(kps), g,
+                                             th_accept, int(bool(stereo_gate)), int(self.mbCheckOrientation),
+                                             self.device, _p(blocked), _p(out), C.byref(n)),
+               "orb_gpu_search_windowed")
         return n.value, out
 
     def stereo_match(self, kps_l, desc_l, kps_r, desc_r, n_rows, scale_factors, min_d, max_d):

@@ -10,6 +10,7 @@
 // against the previous round's claims; query i is final after at most i+1 rounds and the loop
 // ends when a round changes nothing, at which point the state equals the sequential result.
 #include <climits>
+#include <vector>
 
 #include "common.cuh"
 
@@ -73,22 +74,20 @@ grid_build_kernel(const OrbKeyPoint* __restrict__ kps, int nk, int nkpad, OrbFra
 // FILL == false: count only.  Entry = kp index | dist << 16 | octave << 25.
 template <bool FILL>
 __global__ void __launch_bounds__(256)
-window_candidates_kernel(const OrbProjQuery* __restrict__ q, const uint4* __restrict__ qdesc, int nq,
+window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __restrict__ qdesc, int nq,
                          const OrbKeyPoint* __restrict__ kps, const uint4* __restrict__ kdesc,
                          const float* __restrict__ u_right, OrbFrameGrid g,
-                         const float* __restrict__ sf, int nlevels, float th,
                          const uint32_t* __restrict__ sorted, const int* __restrict__ cell_start,
                          int* __restrict__ counts, const int* __restrict__ offsets,
                          uint32_t* __restrict__ entries) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= nq) return;
-  const OrbProjQuery p = q[warp];
+  const OrbWindowQuery p = q[warp];
   int n = 0;
-  if (p.valid && p.level >= 0 && p.level < nlevels) {
-    float r = (double)p.view_cos > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos (:131-137)
-    if (th != 1.0f) r = __fmul_rn(r, th);
-    const float rad = __fmul_rn(r, sf[p.level]);
-    const int min_level = p.level - 1, max_level = p.level;
+  if (p.valid) {
+    const float rad = p.radius;
+    const int min_level = p.min_level, max_level = p.max_level;
+    const bool check = min_level > 0 || max_level >= 0;  // bCheckLevels (Frame.cc:348)
     const float bx = __fsub_rn(p.u, g.min_x), by = __fsub_rn(p.v, g.min_y);
     const int c0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(bx, rad), g.inv_w)));
     const int c1 = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(bx, rad), g.inv_w)));
@@ -107,11 +106,11 @@ window_candidates_kernel(const OrbProjQuery* __restrict__ q, const uint4* __rest
             idx = (int)(sorted[e] & 0xffffu);
             const OrbKeyPoint kp = kps[idx];
             oct = kp.octave;
-            ok = oct >= min_level && oct <= max_level &&
-                 fabsf(__fsub_rn(kp.x, p.u)) < rad && fabsf(__fsub_rn(kp.y, p.v)) < rad;
+            ok = fabsf(__fsub_rn(kp.x, p.u)) < rad && fabsf(__fsub_rn(kp.y, p.v)) < rad;
+            if (check && (oct < min_level || (max_level >= 0 && oct > max_level))) ok = false;
             if (ok && u_right) {
               const float ur = u_right[idx];
-              if (ur > 0 && fabsf(__fsub_rn(p.ur, ur)) > rad) ok = false;  // stereo gate (:91-96)
+              if (ur > 0 && fabsf(__fsub_rn(p.ur, ur)) > rad) ok = false;  // stereo gate (:91-96, :1407-1413)
             }
           }
           const unsigned m = __ballot_sync(0xffffffffu, ok);
@@ -146,13 +145,17 @@ __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int
 }
 
 // ---- ordered claim resolution as a fixpoint ---------------------------------------------------
+// TOP2: stable top-2 with the same-level ratio rule of :102-121 (M2); else best-only, accept <= th (M3/M4/M5).
+// check_ori: rotation histogram over the accepted matches, ComputeThreeMaxima (:1601-1642), losers un-matched.
+template <bool TOP2>
 __global__ void __launch_bounds__(1024)
-window_resolve_kernel(const OrbProjQuery* __restrict__ q, int nq, int nk, const int* __restrict__ offsets,
-                      const uint32_t* __restrict__ entries, float nnratio, int th_high,
-                      uint8_t* __restrict__ blocked /*in/out [nk]*/, int* __restrict__ claim_a,
-                      int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
+window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKeyPoint* __restrict__ kps, int nk,
+                      const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
+                      int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
+                      int* __restrict__ claim_a, int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
                       int32_t* __restrict__ match_of_kp, int* __restrict__ nmatches) {
   __shared__ int s_changed, s_count;
+  __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3];
   const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
   int* prev = claim_a;
   int* cur = claim_b;
@@ -163,7 +166,7 @@ window_resolve_kernel(const OrbProjQuery* __restrict__ q, int nq, int nk, const 
     if (t == 0) s_changed = 0;
     __syncthreads();
     for (int i = t; i < nq; i += T)
-      if (prev[i] >= 0 && q[i].has_obs) atomicMin(&minclaim[prev[i]], i);
+      if (prev[i] >= 0 && q[i].blocks) atomicMin(&minclaim[prev[i]], i);
     __syncthreads();
     for (int i = warp; i < nq; i += nwarps) {
       const int beg = offsets[i], end = offsets[i + 1];
@@ -187,15 +190,17 @@ window_resolve_kernel(const OrbProjQuery* __restrict__ q, int nq, int nk, const 
         if (k1 != 0xffffffffu) {
           const int best_dist = (int)(k1 >> 20);
           const uint32_t e1 = entries[beg + (k1 & 0xfffffu)];
-          int best_dist2 = 256, level2 = -1;
-          if (k2 != 0xffffffffu) {
-            best_dist2 = (int)(k2 >> 20);
-            level2 = (int)(entries[beg + (k2 & 0xfffffu)] >> 25);
+          bool ok = best_dist <= th_accept;
+          if (TOP2 && ok) {
+            int best_dist2 = 256, level2 = -1;
+            if (k2 != 0xffffffffu) {
+              best_dist2 = (int)(k2 >> 20);
+              level2 = (int)(entries[beg + (k2 & 0xfffffu)] >> 25);
+            }
+            const int level1 = (int)(e1 >> 25);
+            if (level1 == level2 && (float)best_dist > __fmul_rn(nnratio, (float)best_dist2)) ok = false;
           }
-          const int level1 = (int)(e1 >> 25);
-          if (best_dist <= th_high &&
-              !(level1 == level2 && (float)best_dist > __fmul_rn(nnratio, (float)best_dist2)))
-            result = (int)(e1 & 0xffffu);
+          if (ok) result = (int)(e1 & 0xffffu);
         }
         cur[i] = result;
         if (result != prev[i]) s_changed = 1;
@@ -210,15 +215,57 @@ window_resolve_kernel(const OrbProjQuery* __restrict__ q, int nq, int nk, const 
   // final state: last claimer per keypoint, blocked flags, match count
   for (int k = t; k < nk; k += T) { match_of_kp[k] = -1; }
   if (t == 0) s_count = 0;
+  if (t < ORB_GPU_HISTO_LENGTH) s_hist[t] = 0;
   __syncthreads();
   int local = 0;
   for (int i = t; i < nq; i += T)
     if (prev[i] >= 0) {
       atomicMax(&match_of_kp[prev[i]], i);
-      if (q[i].has_obs) blocked[prev[i]] = 1;
       ++local;
     }
   if (local) atomicAdd(&s_count, local);
+  __syncthreads();
+  // a keypoint keeps the flag of its last claimer (claims by points with blocks == 0 can be overwritten)
+  for (int i = t; i < nq; i += T)
+    if (prev[i] >= 0 && match_of_kp[prev[i]] == i) blocked[prev[i]] = q[i].blocks;
+  if (check_ori) {
+    // rotation histogram (:1432-1441): bin = round(rot / 30), rot in [0, 360)
+    const float factor = __fdiv_rn(1.0f, (float)ORB_GPU_HISTO_LENGTH);
+    for (int i = t; i < nq; i += T)
+      if (prev[i] >= 0) {
+        float rot = __fsub_rn(q[i].angle, kps[prev[i]].angle);
+        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+        int bin = (int)roundf(__fmul_rn(rot, factor));
+        if (bin == ORB_GPU_HISTO_LENGTH) bin = 0;
+        cur[i] = bin;
+        atomicAdd(&s_hist[bin], 1);
+      }
+    __syncthreads();
+    if (t == 0) {  // ComputeThreeMaxima (:1601-1642)
+      int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+      for (int i = 0; i < ORB_GPU_HISTO_LENGTH; ++i) {
+        const int sz = s_hist[i];
+        if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+        else if (sz > max3) { max3 = sz; ind3 = i; }
+      }
+      if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+      else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+      s_keep[0] = ind1; s_keep[1] = ind2; s_keep[2] = ind3;
+    }
+    __syncthreads();
+    local = 0;
+    for (int i = t; i < nq; i += T)
+      if (prev[i] >= 0) {
+        const int bin = cur[i];
+        if (bin != s_keep[0] && bin != s_keep[1] && bin != s_keep[2]) {  // :1456-1464
+          match_of_kp[prev[i]] = -1;
+          blocked[prev[i]] = 0;
+          ++local;
+        }
+      }
+    if (local) atomicSub(&s_count, local);
+  }
   __syncthreads();
   if (t == 0) *nmatches = s_count;
 }
@@ -263,14 +310,11 @@ using namespace orbgpu;
 
 extern "C" {
 
-int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
-                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
-                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
-                                 float th, float nnratio, int th_high, int device, uint8_t* kp_blocked,
-                                 int32_t* match_of_kp, int* nmatches) {
-  if (nq < 0 || nk < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
-      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
-    return ORB_GPU_ERR_ARG;
+// shared body of the windowed searches: uploads, grid, candidates, ordered resolve, downloads
+static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
+                        const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid, bool top2,
+                        float nnratio, int th_accept, int check_ori, int device, uint8_t* kp_blocked,
+                        int32_t* match_of_kp, int* nmatches) {
   *nmatches = 0;
   for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
   if (nq == 0 || nk == 0) return ORB_GPU_OK;
@@ -278,22 +322,21 @@ int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, in
   ORB_CUDA_TRY(cudaSetDevice(device));
   int nkpad = 2;
   while (nkpad < nk) nkpad <<= 1;
-  TmpDevW dq, dqd, dk, dkd, dur, dsf, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn;
+  TmpDevW dq, dqd, dk, dkd, dur, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn;
   int rc;
-  if ((rc = dq.alloc((size_t)nq * sizeof(OrbProjQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbWindowQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
       (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) || (rc = dkd.alloc((size_t)nk * 32)) ||
-      (rc = dur.alloc((size_t)nk * 4)) || (rc = dsf.alloc((size_t)nlevels * 4)) ||
+      (rc = dur.alloc((size_t)nk * 4)) ||
       (rc = dsorted.alloc((size_t)nkpad * 4)) || (rc = dcell.alloc((size_t)(kCells + 1) * 4)) ||
       (rc = dcnt.alloc((size_t)nq * 4)) || (rc = doff.alloc((size_t)(nq + 1) * 4)) ||
       (rc = dblk.alloc((size_t)nk)) || (rc = dca.alloc((size_t)nq * 4)) || (rc = dcb.alloc((size_t)nq * 4)) ||
       (rc = dmin.alloc((size_t)nk * 4)) || (rc = dmatch.alloc((size_t)nk * 4)) || (rc = dn.alloc(4)))
     return rc;
-  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbProjQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbWindowQuery), cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemcpy(dqd.p, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemcpy(dk.p, kps, (size_t)nk * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemcpy(dkd.p, kdesc, (size_t)nk * 32, cudaMemcpyHostToDevice));
   if (u_right) ORB_CUDA_TRY(cudaMemcpy(dur.p, u_right, (size_t)nk * 4, cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(dsf.p, scale_factors, (size_t)nlevels * 4, cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemcpy(dblk.p, kp_blocked, (size_t)nk, cudaMemcpyHostToDevice));
 
   const size_t smem = (size_t)nkpad * 4;
@@ -302,24 +345,65 @@ int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, in
   grid_build_kernel<<<1, 1024, smem>>>(dk.as<OrbKeyPoint>(), nk, nkpad, grid, dsorted.as<uint32_t>(), dcell.as<int>());
   const int blocks = (nq * 32 + 255) / 256;
   const float* ur = u_right ? dur.as<float>() : nullptr;
-  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbProjQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, dsf.as<float>(), nlevels, th, dsorted.as<uint32_t>(), dcell.as<int>(),
-      dcnt.as<int>(), nullptr, nullptr);
+  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), ur, grid, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr, nullptr);
   exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
   int total = 0;
   ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
   if ((rc = dent.alloc((size_t)total * 4))) return rc;
-  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbProjQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, dsf.as<float>(), nlevels, th, dsorted.as<uint32_t>(), dcell.as<int>(),
-      nullptr, doff.as<int>(), dent.as<uint32_t>());
-  window_resolve_kernel<<<1, 1024>>>(dq.as<OrbProjQuery>(), nq, nk, doff.as<int>(), dent.as<uint32_t>(), nnratio,
-      th_high, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(), dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), ur, grid, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(), dent.as<uint32_t>());
+  if (top2)
+    window_resolve_kernel<true><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
+        dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+  else
+    window_resolve_kernel<false><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
+        dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
   count_launch(5);
   ORB_CUDA_TRY(cudaGetLastError());
   ORB_CUDA_TRY(cudaMemcpy(match_of_kp, dmatch.p, (size_t)nk * 4, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(kp_blocked, dblk.p, (size_t)nk, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
   return ORB_GPU_OK;
+}
+
+int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
+                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
+                                 float th, float nnratio, int th_high, int device, uint8_t* kp_blocked,
+                                 int32_t* match_of_kp, int* nmatches) {
+  if (nq < 0 || nk < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
+      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  // window of every map point as the reference computes it on the host (:63-69, RadiusByViewingCos :131-137)
+  std::vector<OrbWindowQuery> wq((size_t)nq);
+  for (int i = 0; i < nq; ++i) {
+    OrbWindowQuery& w = wq[i];
+    w = OrbWindowQuery();
+    const OrbProjQuery& p = q[i];
+    if (!p.valid || p.level < 0 || p.level >= nlevels) continue;
+    float r = (double)p.view_cos > 0.998 ? 2.5f : 4.0f;
+    if (th != 1.0f) r *= th;
+    w.u = p.u; w.v = p.v; w.ur = p.ur;
+    w.radius = r * scale_factors[p.level];
+    w.min_level = p.level - 1; w.max_level = p.level;
+    w.valid = 1; w.blocks = p.has_obs;
+  }
+  return run_windowed(wq.data(), qdesc, nq, kps, kdesc, u_right, nk, grid, true, nnratio, th_high, 0, device,
+                      kp_blocked, match_of_kp, nmatches);
+}
+
+int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
+                            const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid,
+                            int th_accept, int stereo_gate, int check_orientation, int device,
+                            uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches) {
+  if (nq < 0 || nk < 0 || !nmatches || (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) ||
+      (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  return run_windowed(q, qdesc, nq, kps, kdesc, stereo_gate ? u_right : nullptr, nk, grid, false, 0.f, th_accept,
+                      check_orientation, device, kp_blocked, match_of_kp, nmatches);
 }
 
 int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const OrbKeyPoint* kr,

@@ -155,6 +155,32 @@ int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, in
                                  float th, float nnratio, int th_high, int device,
                                  uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches);
 
+/* What the best-only projection searches know about a source point before their candidate loop
+ * (ORBmatcher.cc:1355-1390 / :1497-1527 / :337-362; computed by the caller exactly as the reference does). */
+typedef struct {
+  float u, v;        /* projection into the target frame */
+  float radius;      /* th * mvScaleFactors[level] */
+  float ur;          /* u - mbf*invzc, used by the stereo gate (:1407-1413) */
+  int32_t min_level, max_level; /* GetFeaturesInArea(u, v, radius, minLevel, maxLevel) */
+  float angle;       /* source keypoint angle (rotation histogram, :1432-1441) */
+  uint8_t valid;     /* passed the caller's geometric tests */
+  uint8_t blocks;    /* a match hides the keypoint from later points (Observations()>0 in :1403-1405; 1 elsewhere) */
+  uint8_t pad_[2];
+} OrbWindowQuery;
+
+/* Best-only windowed search with in-order claims and optional rotation consistency:
+ *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono)          src/ORBmatcher.cc:1328-1470
+ *   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)     :1472-1599
+ *   ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)           :290-403
+ * (candidate order of Get FeaturesInArea, bestDist from 256 with strict '<', accept best <= th_accept, claim,
+ * ComputeThreeMaxima :1601-1642 when check_orientation).  Host pointers.  kp_blocked in/out; match_of_kp[nk]
+ * = query index or -1. */
+int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq,
+                            const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
+                            int nk, OrbFrameGrid grid, int th_accept, int stereo_gate,
+                            int check_orientation, int device, uint8_t* kp_blocked,
+                            int32_t* match_of_kp, int* nmatches);
+
 /* Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): for each left keypoint
  * the best right keypoint in its row band within the disparity and octave gates.
  * best_idx_r[nl] = right index or -1, best_dist[nl] = distance (th_high when none). */

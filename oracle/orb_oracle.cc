@@ -492,6 +492,71 @@ int search_by_projection(const ProjQuery* q, const uint8_t* qdesc, int nq, const
   return nmatches;
 }
 
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642)
+void compute_three_maxima(const int* hs, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; ++i) {
+    const int s = hs[i];
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+// Candidate loop, acceptance, claim and rotation consistency of ORBmatcher::SearchByProjection(Cur, Last)
+// (src/ORBmatcher.cc:1385-1467); the (Cur, KF) form (:1527-1597) and the (KF, Scw) form (:363-400) are
+// the same loop with other gates / thresholds.
+int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
+                    const uint8_t* kdesc, const float* u_right, int nk, const FrameGrid& grid,
+                    int th_accept, bool stereo_gate, bool check_orientation, uint8_t* blocked,
+                    int32_t* match_of_kp) {
+  const int HISTO_LENGTH = 30;
+  int nmatches = 0;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  const float factor = 1.0f / HISTO_LENGTH;
+  for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
+  std::vector<int> cand;
+  for (int i = 0; i < nq; ++i) {
+    const WindowQuery& p = q[i];
+    if (!p.valid) continue;
+    grid.features_in_area(kps, p.u, p.v, p.radius, p.min_level, p.max_level, cand);
+    if (cand.empty()) continue;
+    int bestDist = 256, bestIdx2 = -1;
+    for (int i2 : cand) {
+      if (blocked[i2]) continue;  // :1403-1405 / :1541-1542 / :375
+      if (stereo_gate && u_right && u_right[i2] > 0) {
+        const float er = std::fabs(p.ur - u_right[i2]);
+        if (er > p.radius) continue;
+      }
+      const int dist = descriptor_distance(qdesc + (size_t)i * 32, kdesc + (size_t)i2 * 32);
+      if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+    }
+    if (bestDist <= th_accept) {
+      match_of_kp[bestIdx2] = i;
+      blocked[bestIdx2] = p.blocks;
+      ++nmatches;
+      if (check_orientation) {
+        float rot = p.angle - kps[bestIdx2].angle;
+        if (rot < 0.0) rot += 360.0f;
+        int bin = (int)std::round(rot * factor);
+        if (bin == HISTO_LENGTH) bin = 0;
+        rotHist[bin].push_back(bestIdx2);
+      }
+    }
+  }
+  if (check_orientation) {
+    int ind1 = -1, ind2 = -1, ind3 = -1, sizes[HISTO_LENGTH];
+    for (int i = 0; i < HISTO_LENGTH; ++i) sizes[i] = (int)rotHist[i].size();
+    compute_three_maxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; ++i)
+      if (i != ind1 && i != ind2 && i != ind3)
+        for (int idx : rotHist[i]) { match_of_kp[idx] = -1; blocked[idx] = 0; --nmatches; }
+  }
+  return nmatches;
+}
+
 void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint* kr,
                   const uint8_t* dr, int nr, int n_rows, const float* sf, float min_d,
                   float max_d, int th_high, int32_t* best_idx_r, int32_t* best_dist) {

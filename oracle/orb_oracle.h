@@ -100,6 +100,28 @@ int search_by_projection(const ProjQuery* q, const uint8_t* qdesc, int nq, const
                          const FrameGrid& grid, const float* scale_factors, float th,
                          float nnratio, int th_high, uint8_t* kp_blocked, int32_t* match_of_kp);
 
+// The per-source-point quantities the best-only projection searches compute before their candidate loop
+// (M3 ORBmatcher.cc:1355-1390, M4 :1497-1527, M5 :337-362): projection, radius, level window.
+struct WindowQuery {
+  float u, v;          // projected position in the target frame
+  float radius;        // th * mvScaleFactors[level]
+  float ur;            // u - mbf*invzc (stereo gate of M3, :1407-1413)
+  int32_t min_level, max_level;  // GetFeaturesInArea(u, v, radius, minLevel, maxLevel) arguments
+  float angle;         // angle of the source keypoint (rotation histogram, :1432-1441)
+  uint8_t valid;       // the point passed every geometric test of the caller
+  uint8_t blocks;      // its claim hides the keypoint from later points (M3: Observations()>0; M4/M5: always)
+  uint8_t pad_[2];
+};
+// Rotation histogram + ComputeThreeMaxima (ORBmatcher.cc:1601-1642): returns the three kept bins (or -1).
+void compute_three_maxima(const int* histo_sizes, int L, int& ind1, int& ind2, int& ind3);
+// M3/M4/M5: best-only search in a window, accept best <= th_accept, in-order claims, optional rotation
+// consistency (mbCheckOrientation).  kp_blocked in/out; match_of_kp[i] = last query assigned to keypoint i or -1
+// (also -1 when any of its assignments fell in a pruned histogram bin, :1448-1467).  Returns nmatches.
+int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
+                    const uint8_t* kdesc, const float* u_right, int nk, const FrameGrid& grid,
+                    int th_accept, bool stereo_gate, bool check_orientation, uint8_t* kp_blocked,
+                    int32_t* match_of_kp);
+
 // M10: Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549).
 // best_idx_r[i] = right index or -1; best_dist[i] = distance (TH_HIGH if none).
 void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint* kr,

@@ -19,16 +19,17 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("level", "<i4"),
                        ("view_cos", "<f4"), ("valid", "u1"), ("has_obs", "u1")], align=True)
-assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24
+WINDOW_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("min_level", "<i4"),
+                         ("max_level", "<i4"), ("angle", "<f4"), ("valid", "u1"), ("blocks", "u1")], align=True)
+assert KP_DTYPE.itemsize == 28 and PROJ_DTYPE.itemsize == 24 and WINDOW_DTYPE.itemsize == 32
 
 
 def build(force=False):
     """(Re)build the oracle with oracle/Makefile (gcc only; no GPU, no reference build system)."""
-    need = force or not os.path.exists(LIB_PATH)
-    if os.path.isdir("/root/reference") and not os.path.exists(REF_PATH):
-        need = True
-    if need:
-        subprocess.check_call(["make", "-s", "-C", HERE, "all"])
+    # make is incremental (sources vs .so timestamps), so it is simply always consulted
+    if force and os.path.exists(LIB_PATH):
+        os.remove(LIB_PATH)
+    subprocess.check_call(["make", "-s", "-C", HERE, "all"])
 
 
 _lib = None
@@ -227,6 +228,24 @@ def search_by_projection(queries, qdesc, kps, kdesc, u_right, grid, scale_factor
                                         C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
                                         C.c_float(grid[3]), _p(sf), C.c_float(th), C.c_float(nnratio),
                                         th_high, _p(blocked), _p(out))
+    return n, out, blocked
+
+
+def search_windowed(queries, qdesc, kps, kdesc, u_right, grid, th_accept, stereo_gate, check_orientation,
+                    blocked=None):
+    """M3/M4/M5 (best-only windowed search + rotation histogram).  -> nmatches, match_of_kp[nk], blocked_after"""
+    queries = np.ascontiguousarray(queries, WINDOW_DTYPE)
+    qdesc = u8c(qdesc)
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    kdesc = u8c(kdesc)
+    nk = len(kps)
+    blocked = np.zeros(nk, np.uint8) if blocked is None else np.array(blocked, np.uint8)
+    ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+    out = np.empty(nk, np.int32)
+    n = lib().orbo_search_windowed(_p(queries), _p(qdesc), len(queries), _p(kps), _p(kdesc), _p(ur), nk,
+                                   C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
+                                   C.c_float(grid[3]), int(th_accept), int(bool(stereo_gate)),
+                                   int(bool(check_orientation)), _p(blocked), _p(out))
     return n, out, blocked
 
 

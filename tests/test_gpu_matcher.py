@@ -122,3 +122,63 @@ def test_sharded_bruteforce_merge_on_device(gpu, oracle):
     oi, ob, os_ = oracle.match_bruteforce(q, db, threads=8)
     o = out.cpu().numpy()
     assert np.array_equal(o[0], oi) and np.array_equal(o[1], ob) and np.array_equal(o[2], os_)
+
+
+def _window_case(oracle, seed, mode):
+    """Queries of the best-only projection searches as their callers build them (M3: last-frame points,
+    forward / backward / neutral level windows, stereo gate; M4/M5: level +-1 / [l-1, l], no gate)."""
+    W, H = 640, 480
+    ex, kps, desc = _frame_from_extractor(oracle, W, H, seed, 2000)
+    rng = np.random.default_rng(100 + seed)
+    nk, M = len(kps), 1800
+    sf = ex.tables()["scale"]
+    src = rng.integers(0, nk, M)
+    q = np.zeros(M, oracle.WINDOW_DTYPE)
+    near = rng.random(M) < 0.8
+    q["u"] = np.where(near, kps["x"][src] + rng.normal(0, 3, M), rng.uniform(0, W, M)).astype(np.float32)
+    q["v"] = np.where(near, kps["y"][src] + rng.normal(0, 3, M), rng.uniform(0, H, M)).astype(np.float32)
+    lvl = kps["octave"][src]
+    th = {"last_mono": 15.0, "last_forward": 7.0, "last_backward": 7.0, "kf": 10.0, "sim3": 10.0}[mode]
+    q["radius"] = (np.float32(th) * sf[lvl]).astype(np.float32)
+    if mode == "last_forward":
+        q["min_level"], q["max_level"] = lvl, -1
+    elif mode == "last_backward":
+        q["min_level"], q["max_level"] = 0, lvl
+    elif mode == "sim3":
+        q["min_level"], q["max_level"] = lvl - 1, lvl
+    else:
+        q["min_level"], q["max_level"] = lvl - 1, lvl + 1
+    # source angles: mostly a common rotation of ~40 degrees, some outliers -> the histogram prunes
+    rot = np.where(rng.random(M) < 0.85, rng.normal(40, 6, M), rng.uniform(0, 360, M))
+    q["angle"] = np.mod(kps["angle"][src] + rot, 360).astype(np.float32)
+    q["valid"] = rng.random(M) < 0.95
+    q["blocks"] = (rng.random(M) < 0.9) if mode.startswith("last") else 1
+    qdesc = synth.flip_bits(desc[src], rng.integers(0, 70, M), rng)
+    dup = rng.integers(0, M, 300)   # several points aimed at one keypoint: the claim order matters
+    q[dup] = q[(dup + 1) % M]
+    qdesc[dup] = qdesc[(dup + 1) % M]
+    u_right = None
+    if mode in ("last_forward", "last_backward"):
+        u_right = np.where(rng.random(nk) < 0.6, kps["x"] - rng.uniform(1, 40, nk), -1).astype(np.float32)
+        q["ur"] = (q["u"] - rng.uniform(1, 40, M)).astype(np.float32)
+    blocked = (rng.random(nk) < 0.05).astype(np.uint8)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(W), np.float32(48) / np.float32(H))
+    return kps, desc, q, qdesc, u_right, blocked, grid
+
+
+@pytest.mark.parametrize("mode,th_accept,check_ori,seed", [
+    ("last_mono", 100, True, 1), ("last_forward", 100, True, 2), ("last_backward", 100, True, 3),
+    ("kf", 100, True, 4), ("kf", 64, True, 5), ("sim3", 50, False, 6)])
+def test_search_windowed_variants(gpu, oracle, mode, th_accept, check_ori, seed):
+    """M3 / M4 / M5 + M8: best-only windowed search, ordered claims, rotation histogram -- bit-exact."""
+    kps, desc, q, qdesc, u_right, blocked, grid = _window_case(oracle, seed, mode)
+    stereo = u_right is not None
+    n_o, match_o, blocked_o = oracle.search_windowed(q, qdesc, kps, desc, u_right, grid, th_accept, stereo,
+                                                     check_ori, blocked.copy())
+    frame = dict(kps=kps, desc=desc, u_right=u_right, grid=grid, blocked=blocked.copy())
+    qg = np.zeros(len(q), gpu.WINDOW_DTYPE)
+    for f in ("u", "v", "radius", "ur", "min_level", "max_level", "angle", "valid", "blocks"):
+        qg[f] = q[f]
+    n_g, match_g = gpu.ORBmatcher(0.9, checkOri=check_ori).SearchWindowed(frame, qg, qdesc, th_accept, stereo)
+    assert n_o > 100
+    assert n_g == n_o and np.array_equal(match_g, match_o) and np.array_equal(frame["blocked"], blocked_o)
