@@ -7,6 +7,7 @@
 #ifndef ORBMATCHER_GPU_H
 #define ORBMATCHER_GPU_H
 
+#include <cstring>
 #include <vector>
 
 #include "orb_gpu.h"
@@ -52,6 +53,74 @@ int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, fl
     if (match[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[match[i]];  // :123
   return nmatches;
 }
+
+// ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)
+// (src/ORBmatcher.cc:1328-1470).  The projection of every last-frame map point is computed on the host with
+// the reference's own expressions (:1339-1390); the candidate loop, the claims and the rotation histogram
+// (:1392-1467) run in orb_gpu_search_windowed.
+template <class FrameT, class MapPointT>
+int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float th, bool bMono,
+                           bool checkOrientation, int device = 0) {
+  const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat twc = -Rcw.t() * tcw;
+  const cv::Mat Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat tlc = Rlw * twc + tlw;
+  const bool bForward = tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  const bool bBackward = -tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  const int nq = LastFrame.N, nk = CurrentFrame.N;
+  std::vector<OrbWindowQuery> q(nq);
+  std::vector<uint8_t> qdesc((size_t)nq * 32), blocked(nk, 0);
+  for (int i = 0; i < nq; ++i) {
+    OrbWindowQuery& o = q[i];
+    std::memset(&o, 0, sizeof(o));
+    MapPointT* pMP = LastFrame.mvpMapPoints[i];
+    if (!pMP || LastFrame.mvbOutlier[i]) continue;
+    cv::Mat x3Dw = pMP->GetWorldPos();
+    cv::Mat x3Dc = Rcw * x3Dw + tcw;
+    const float xc = x3Dc.at<float>(0), yc = x3Dc.at<float>(1);
+    const float invzc = 1.0 / x3Dc.at<float>(2);
+    if (invzc < 0) continue;
+    const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+    const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+    if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+    if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+    const int nLastOctave = LastFrame.mvKeys[i].octave;
+    o.u = u; o.v = v;
+    o.radius = th * CurrentFrame.mvScaleFactors[nLastOctave];
+    o.ur = u - CurrentFrame.mbf * invzc;
+    if (bForward) { o.min_level = nLastOctave; o.max_level = -1; }            // :1386
+    else if (bBackward) { o.min_level = 0; o.max_level = nLastOctave; }       // :1388
+    else { o.min_level = nLastOctave - 1; o.max_level = nLastOctave + 1; }    // :1390
+    o.angle = LastFrame.mvKeysUn[i].angle;
+    o.valid = 1;
+    o.blocks = pMP->Observations() > 0;                                       // :1403-1405 seen by later points
+    std::memcpy(&qdesc[(size_t)i * 32], pMP->GetDescriptor().ptr(), 32);
+  }
+  for (int i = 0; i < nk; ++i)
+    blocked[i] = CurrentFrame.mvpMapPoints[i] && CurrentFrame.mvpMapPoints[i]->Observations() > 0;
+  std::vector<uint8_t> kdesc((size_t)nk * 32);
+  for (int i = 0; i < nk; ++i) std::memcpy(&kdesc[(size_t)i * 32], CurrentFrame.mDescriptors.ptr(i), 32);
+  OrbFrameGrid g = {FrameT::mnMinX, FrameT::mnMinY, FrameT::mfGridElementWidthInv, FrameT::mfGridElementHeightInv};
+  std::vector<int32_t> match(nk, -1);
+  int nmatches = 0;
+  const int rc = orb_gpu_search_windowed(
+      q.data(), qdesc.data(), nq, reinterpret_cast<const OrbKeyPoint*>(CurrentFrame.mvKeysUn.data()), kdesc.data(),
+      CurrentFrame.mvuRight.empty() ? nullptr : CurrentFrame.mvuRight.data(), nk, g, ORB_GPU_TH_HIGH,
+      /*stereo_gate=*/1, checkOrientation ? 1 : 0, device, blocked.data(), match.data(), &nmatches);
+  if (rc != ORB_GPU_OK) return 0;
+  // keypoints un-matched by the rotation check are reset to NULL by the reference (:1461); they are the ones
+  // that were candidates of this call (blocked flag cleared) and carry no match
+  for (int i = 0; i < nk; ++i)
+    if (match[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[match[i]];
+  return nmatches;
+}
+
+// ORBmatcher::SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>& sAlreadyFound, th, ORBdist) (:1472-1599)
+// and ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (:290-403) build their
+// OrbWindowQuery rows the same way (levels [l-1, l+1] / [l-1, l], blocks = 1, no stereo gate) and call
+// orb_gpu_search_windowed with th_accept = ORBdist / ORB_GPU_TH_LOW (check_orientation = 0 for the latter).
 
 // Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): fills bestIdxR / bestDist
 // per left keypoint; the caller continues with the sub-pixel refinement (:551-640) unchanged.
