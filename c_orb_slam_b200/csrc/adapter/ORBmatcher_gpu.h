@@ -110,10 +110,10 @@ int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float 
       CurrentFrame.mvuRight.empty() ? nullptr : CurrentFrame.mvuRight.data(), nk, g, ORB_GPU_TH_HIGH,
       /*stereo_gate=*/1, checkOrientation ? 1 : 0, device, blocked.data(), match.data(), &nmatches);
   if (rc != ORB_GPU_OK) return 0;
-  // keypoints un-matched by the rotation check are reset to NULL by the reference (:1461); they are the ones
-  // that were candidates of this call (blocked flag cleared) and carry no match
-  for (int i = 0; i < nk; ++i)
+  for (int i = 0; i < nk; ++i) {
     if (match[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[match[i]];
+    else if (match[i] == -2) CurrentFrame.mvpMapPoints[i] = static_cast<MapPointT*>(NULL);  // :1461
+  }
   return nmatches;
 }
 

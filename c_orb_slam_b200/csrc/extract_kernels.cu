@@ -200,6 +200,7 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
       const int sstep = 2 * g.pitch;
       const unsigned dstep = 2 * tp;
       if (c < nw)
+#pragma unroll 4
         for (int r = r0; r < ch; r += 2, src += sstep, dst += dstep)
           asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
     } else {
@@ -998,6 +999,32 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
+// sin and cos of x in [0, 2*pi] in double precision (error ~1e-16, the float rounding of the result is what
+// the descriptor uses: identical to rounding libm's double sincos, without its large-argument slow path).
+// Cody-Waite reduction by pi/2 and the fdlibm kernel polynomials on |r| <= pi/4.
+__device__ __forceinline__ void sincos_0_2pi(double x, double* s, double* c) {
+  const double k = rint(x * 0.63661977236758138);  // 2/pi
+  double r = __fma_rn(-k, 1.5707963267948966, x);
+  r = __fma_rn(-k, 6.123233995736766e-17, r);
+  const double z = r * r;
+  double ps = __fma_rn(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+  ps = __fma_rn(z, ps, 2.75573137070700676789e-06);
+  ps = __fma_rn(z, ps, -1.98412698298579493134e-04);
+  ps = __fma_rn(z, ps, 8.33333333332248946124e-03);
+  ps = __fma_rn(z, ps, -1.66666666666666324348e-01);
+  const double sr = __fma_rn(r * z, ps, r);
+  double pc = __fma_rn(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+  pc = __fma_rn(z, pc, -2.75573143513906633035e-07);
+  pc = __fma_rn(z, pc, 2.48015872894767294178e-05);
+  pc = __fma_rn(z, pc, -1.38888888888741095749e-03);
+  pc = __fma_rn(z, pc, 4.16666666666666019037e-02);
+  const double cr = __fma_rn(z * z, pc, __fma_rn(z, -0.5, 1.0));
+  const int q = (int)k & 3;
+  const double s0 = (q & 1) ? cr : sr, c0 = (q & 1) ? sr : cr;
+  *s = (q & 2) ? -s0 : s0;
+  *c = ((q + 1) & 2) ? -c0 : c0;
+}
+
 constexpr int kOdWarps = 8, kOdSlotsPerWarp = 4, kOdSlotsPerBlock = kOdWarps * kOdSlotsPerWarp;
 constexpr int kOdReach = 18;                      // |rotated tap| <= ceil(13 * sqrt(2)) = 18 < EDGE_THRESHOLD
 constexpr int kOdRows = 2 * kOdReach + 1;         // 37 rows of the blurred level around the keypoint
@@ -1032,6 +1059,8 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   const int u = lane - kHalfPatch;
   const int vm = lane < 31 ? p.umax[u < 0 ? -u : u] : -1;  // rows |v| <= vm of column u are inside the disc
   uint32_t* my_tile = s_tile[warp];
+  const int tile_r = lane / kOdWords, tile_c = lane - tile_r * kOdWords;  // this lane's (row, word) inside a 3-row step
+  const unsigned tile_dst = (unsigned)__cvta_generic_to_shared(my_tile + tile_r * kOdWords + tile_c);
 
   for (int it = 0; it < kOdSlotsPerWarp; ++it) {
     const int slot = blockIdx.x * kOdSlotsPerBlock + it * kOdWarps + warp;
@@ -1056,15 +1085,14 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     {
       const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
       const int xal = (cx - kOdReach) & ~3;
-      const uint8_t* src = bl + (size_t)(cy - kOdReach) * g.bpitch + xal;
+      // 30 lanes copy 3 rows x 10 words per step: one pointer bump per step
+      const uint8_t* src = bl + (size_t)(cy - kOdReach + tile_r) * g.bpitch + xal + 4 * tile_c;
+      unsigned dst = tile_dst;
+      const int step = 3 * g.bpitch;
 #pragma unroll
-      for (int i = 0; i < (kOdRows * kOdWords + 31) / 32; ++i) {
-        const int k = lane + 32 * i;
-        if (k < kOdRows * kOdWords) {
-          const int r = k / kOdWords, c = k - r * kOdWords;
-          cp_async4(my_tile + k, src + (size_t)r * g.bpitch + 4 * c);
-        }
-      }
+      for (int r0 = 0; r0 < kOdRows; r0 += 3, src += step, dst += 3 * kOdWords * 4)
+        if (lane < 30 && r0 + tile_r < kOdRows)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
       asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
 
@@ -1090,7 +1118,7 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     // steered BRIEF on the blurred level (:106-147)
     const float rad = __fmul_rn(angle, 0.017453292519943295f);  // (float)(CV_PI/180.f)
     double sd, cd;
-    sincos((double)rad, &sd, &cd);
+    sincos_0_2pi((double)rad, &sd, &cd);
     const float a = (float)cd, b = (float)sd;
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncwarp();

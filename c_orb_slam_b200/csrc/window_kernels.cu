@@ -259,7 +259,7 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
       if (prev[i] >= 0) {
         const int bin = cur[i];
         if (bin != s_keep[0] && bin != s_keep[1] && bin != s_keep[2]) {  // :1456-1464
-          match_of_kp[prev[i]] = -1;
+          match_of_kp[prev[i]] = -2;  // reset to NULL by the rotation check
           blocked[prev[i]] = 0;
           ++local;
         }

@@ -174,7 +174,7 @@ typedef struct {
  *   ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)           :290-403
  * (candidate order of Get FeaturesInArea, bestDist from 256 with strict '<', accept best <= th_accept, claim,
  * ComputeThreeMaxima :1601-1642 when check_orientation).  Host pointers.  kp_blocked in/out; match_of_kp[nk]
- * = query index or -1. */
+ * = query index, -1 (untouched) or -2 (matched, then reset to NULL by the rotation check, :1461). */
 int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq,
                             const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
                             int nk, OrbFrameGrid grid, int th_accept, int stereo_gate,

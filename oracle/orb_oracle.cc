@@ -552,7 +552,7 @@ int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const Ke
     compute_three_maxima(sizes, HISTO_LENGTH, ind1, ind2, ind3);
     for (int i = 0; i < HISTO_LENGTH; ++i)
       if (i != ind1 && i != ind2 && i != ind3)
-        for (int idx : rotHist[i]) { match_of_kp[idx] = -1; blocked[idx] = 0; --nmatches; }
+        for (int idx : rotHist[i]) { match_of_kp[idx] = -2; blocked[idx] = 0; --nmatches; }  // NULL after :1461
   }
   return nmatches;
 }

@@ -116,7 +116,7 @@ struct WindowQuery {
 void compute_three_maxima(const int* histo_sizes, int L, int& ind1, int& ind2, int& ind3);
 // M3/M4/M5: best-only search in a window, accept best <= th_accept, in-order claims, optional rotation
 // consistency (mbCheckOrientation).  kp_blocked in/out; match_of_kp[i] = last query assigned to keypoint i or -1
-// (also -1 when any of its assignments fell in a pruned histogram bin, :1448-1467).  Returns nmatches.
+// (-2 when any of its assignments fell in a pruned histogram bin: reset to NULL at :1448-1467).  Returns nmatches.
 int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
                     const uint8_t* kdesc, const float* u_right, int nk, const FrameGrid& grid,
                     int th_accept, bool stereo_gate, bool check_orientation, uint8_t* kp_blocked,
