@@ -100,8 +100,8 @@ def lib():
                                                    C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                                    C.POINTER(C.c_int)]
         L.orb_gpu_search_windowed.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
-                                              C.c_int, _Grid, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
-                                              C.c_void_p, C.POINTER(C.c_int)]
+                                              C.c_int, _Grid, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                              C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -305,13 +305,15 @@ class ORBmatcher:
                "orb_gpu_search_by_projection")
         return n.value, out
 
-    def SearchWindowed(self, frame, queries, qdesc, th_accept=None, stereo_gate=False):
+    def SearchWindowed(self, frame, queries, qdesc, th_accept=None, gate=0, inv_level_sigma2=None):
         """Best-only windowed search shared by ORBmatcher::SearchByProjection(Cur, Last, th, bMono)
         (ORBmatcher.cc:1328-1470; th_accept=TH_HIGH, stereo_gate=True), (Cur, KF, sAlreadyFound, th, ORBdist)
         (:1472-1599; th_accept=ORBdist) and (KF, Scw, vpPoints, vpMatched, th) (:290-403; th_accept=TH_LOW,
         no orientation check).  queries: WINDOW_DTYPE [M] computed by the caller like the reference does
         (projection, radius, level window, source angle).  frame as in SearchByProjection.
-        -> nmatches, match_of_kp [N]; frame['blocked'] is updated in place."""
+        gate: 0 none, 1 stereo radius gate (:1407-1413), 2 chi-square gate of Fuse (:904-931, needs
+        inv_level_sigma2).  With blocks = 0 in every query nothing is claimed (the two passes of SearchBySim3).
+        -> nmatches, match_of_kp [N], match_of_query [M]; frame['blocked'] is updated in place."""
         kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
         kd = np.ascontiguousarray(frame["desc"], np.uint8)
         ur = frame.get("u_right")
@@ -320,16 +322,19 @@ class ORBmatcher:
         if blocked is None:
             blocked = frame["blocked"] = np.zeros(len(kps), np.uint8)
         wq = np.ascontiguousarray(queries, WINDOW_DTYPE)
+        sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        outq = np.empty(len(wq), np.int32)
         qd = np.ascontiguousarray(qdesc, np.uint8)
         g = _Grid(*[float(v) for v in frame["grid"]])
         out = np.empty(len(kps), np.int32)
         n = C.c_int()
         th_accept = self.TH_HIGH if th_accept is None else int(th_accept)
         _check(lib().orb_gpu_search_windowed(_p(wq), _p(qd), len(wq), _p(kps), _p(kd), _p(ur), len(kps), g,
-                                             th_accept, int(bool(stereo_gate)), int(self.mbCheckOrientation),
-                                             self.device, _p(blocked), _p(out), C.byref(n)),
+                                             th_accept, int(gate), _p(sig), 0 if sig is None else len(sig),
+                                             int(self.mbCheckOrientation), self.device, _p(blocked), _p(out),
+                                             _p(outq), C.byref(n)),
                "orb_gpu_search_windowed")
-        return n.value, out
+        return n.value, out, outq
 
     def stereo_match(self, kps_l, desc_l, kps_r, desc_r, n_rows, scale_factors, min_d, max_d):
         """Hamming stage of Frame::ComputeStereoMatches (Frame.cc:466-549) -> best_idx_r, best_dist."""

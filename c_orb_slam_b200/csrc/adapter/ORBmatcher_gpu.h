@@ -108,7 +108,7 @@ int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float 
   const int rc = orb_gpu_search_windowed(
       q.data(), qdesc.data(), nq, reinterpret_cast<const OrbKeyPoint*>(CurrentFrame.mvKeysUn.data()), kdesc.data(),
       CurrentFrame.mvuRight.empty() ? nullptr : CurrentFrame.mvuRight.data(), nk, g, ORB_GPU_TH_HIGH,
-      /*stereo_gate=*/1, checkOrientation ? 1 : 0, device, blocked.data(), match.data(), &nmatches);
+      /*gate=*/1, nullptr, 0, checkOrientation ? 1 : 0, device, blocked.data(), match.data(), nullptr, &nmatches);
   if (rc != ORB_GPU_OK) return 0;
   for (int i = 0; i < nk; ++i) {
     if (match[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[match[i]];
@@ -121,6 +121,12 @@ int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float 
 // and ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (:290-403) build their
 // OrbWindowQuery rows the same way (levels [l-1, l+1] / [l-1, l], blocks = 1, no stereo gate) and call
 // orb_gpu_search_windowed with th_accept = ORBdist / ORB_GPU_TH_LOW (check_orientation = 0 for the latter).
+//
+// ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (:825-975): rows with levels [l-1, l], blocks = 0, gate = 2 and
+// pKF->mvInvLevelSigma2, th_accept = ORB_GPU_TH_LOW; the caller walks match_of_query in query order and applies
+// Replace() / AddObservation() exactly as :953-970 do.  Fuse(KeyFrame*, Scw, ...) (:977-1100) is the same with
+// gate = 0.  ORBmatcher::SearchBySim3 (:1102-1326) calls it twice (KF1 points into KF2 and back, blocks = 0,
+// th_accept = ORB_GPU_TH_HIGH) and keeps i where match_of_query2[match_of_query1[i]] == i (:1303-1323).
 
 // Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): fills bestIdxR / bestDist
 // per left keypoint; the caller continues with the sub-pixel refinement (:551-640) unchanged.

@@ -76,7 +76,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(256)
 window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __restrict__ qdesc, int nq,
                          const OrbKeyPoint* __restrict__ kps, const uint4* __restrict__ kdesc,
-                         const float* __restrict__ u_right, OrbFrameGrid g,
+                         const float* __restrict__ u_right, OrbFrameGrid g, int gate,
+                         const float* __restrict__ inv_sigma2,
                          const uint32_t* __restrict__ sorted, const int* __restrict__ cell_start,
                          int* __restrict__ counts, const int* __restrict__ offsets,
                          uint32_t* __restrict__ entries) {
@@ -108,9 +109,20 @@ window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __re
             oct = kp.octave;
             ok = fabsf(__fsub_rn(kp.x, p.u)) < rad && fabsf(__fsub_rn(kp.y, p.v)) < rad;
             if (check && (oct < min_level || (max_level >= 0 && oct > max_level))) ok = false;
-            if (ok && u_right) {
+            if (ok && gate == 1 && u_right) {
               const float ur = u_right[idx];
               if (ur > 0 && fabsf(__fsub_rn(p.ur, ur)) > rad) ok = false;  // stereo gate (:91-96, :1407-1413)
+            }
+            if (ok && gate == 2) {  // chi-square gate of Fuse (:904-931)
+              const float ex = __fsub_rn(p.u, kp.x), ey = __fsub_rn(p.v, kp.y);
+              float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+              double lim = 5.99;
+              if (u_right && u_right[idx] >= 0) {
+                const float er = __fsub_rn(p.ur, u_right[idx]);
+                e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                lim = 7.8;
+              }
+              if ((double)__fmul_rn(e2, inv_sigma2[oct]) > lim) ok = false;
             }
           }
           const unsigned m = __ballot_sync(0xffffffffu, ok);
@@ -153,7 +165,8 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
                       const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
                       int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
                       int* __restrict__ claim_a, int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
-                      int32_t* __restrict__ match_of_kp, int* __restrict__ nmatches) {
+                      int32_t* __restrict__ match_of_kp, int32_t* __restrict__ match_of_query,
+                      int* __restrict__ nmatches) {
   __shared__ int s_changed, s_count;
   __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3];
   const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
@@ -267,6 +280,10 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
     if (local) atomicSub(&s_count, local);
   }
   __syncthreads();
+  for (int i = t; i < nq; i += T) {  // per-query result (-1: none, or un-matched by the rotation check)
+    const int k = prev[i];
+    match_of_query[i] = (k >= 0 && match_of_kp[k] != -2) ? k : -1;
+  }
   if (t == 0) *nmatches = s_count;
 }
 
@@ -313,17 +330,21 @@ extern "C" {
 // shared body of the windowed searches: uploads, grid, candidates, ordered resolve, downloads
 static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
                         const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid, bool top2,
-                        float nnratio, int th_accept, int check_ori, int device, uint8_t* kp_blocked,
-                        int32_t* match_of_kp, int* nmatches) {
+                        float nnratio, int th_accept, int gate, const float* inv_sigma2, int nlevels,
+                        int check_ori, int device, uint8_t* kp_blocked, int32_t* match_of_kp,
+                        int32_t* match_of_query, int* nmatches) {
   *nmatches = 0;
   for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
+  if (match_of_query) for (int i = 0; i < nq; ++i) match_of_query[i] = -1;
   if (nq == 0 || nk == 0) return ORB_GPU_OK;
   if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
   ORB_CUDA_TRY(cudaSetDevice(device));
   int nkpad = 2;
   while (nkpad < nk) nkpad <<= 1;
-  TmpDevW dq, dqd, dk, dkd, dur, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn;
+  TmpDevW dq, dqd, dk, dkd, dur, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn, dsig, dmq;
   int rc;
+  if ((rc = dsig.alloc((size_t)kMaxLevels * 4)) || (rc = dmq.alloc((size_t)nq * 4))) return rc;
+  if (gate == 2) ORB_CUDA_TRY(cudaMemcpy(dsig.p, inv_sigma2, (size_t)nlevels * 4, cudaMemcpyHostToDevice));
   if ((rc = dq.alloc((size_t)nq * sizeof(OrbWindowQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
       (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) || (rc = dkd.alloc((size_t)nk * 32)) ||
       (rc = dur.alloc((size_t)nk * 4)) ||
@@ -346,26 +367,29 @@ static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, c
   const int blocks = (nq * 32 + 255) / 256;
   const float* ur = u_right ? dur.as<float>() : nullptr;
   window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr, nullptr);
+      dkd.as<uint4>(), ur, grid, gate, dsig.as<float>(), dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(),
+      nullptr, nullptr);
   exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
   int total = 0;
   ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
   if ((rc = dent.alloc((size_t)total * 4))) return rc;
   window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(), dent.as<uint32_t>());
+      dkd.as<uint4>(), ur, grid, gate, dsig.as<float>(), dsorted.as<uint32_t>(), dcell.as<int>(), nullptr,
+      doff.as<int>(), dent.as<uint32_t>());
   if (top2)
     window_resolve_kernel<true><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
         dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
-        dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+        dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
   else
     window_resolve_kernel<false><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
         dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
-        dmin.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+        dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
   count_launch(5);
   ORB_CUDA_TRY(cudaGetLastError());
   ORB_CUDA_TRY(cudaMemcpy(match_of_kp, dmatch.p, (size_t)nk * 4, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(kp_blocked, dblk.p, (size_t)nk, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
+  if (match_of_query) ORB_CUDA_TRY(cudaMemcpy(match_of_query, dmq.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
   return ORB_GPU_OK;
 }
 
@@ -391,19 +415,22 @@ int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, in
     w.min_level = p.level - 1; w.max_level = p.level;
     w.valid = 1; w.blocks = p.has_obs;
   }
-  return run_windowed(wq.data(), qdesc, nq, kps, kdesc, u_right, nk, grid, true, nnratio, th_high, 0, device,
-                      kp_blocked, match_of_kp, nmatches);
+  return run_windowed(wq.data(), qdesc, nq, kps, kdesc, u_right, nk, grid, true, nnratio, th_high, 1, nullptr, 0, 0,
+                      device, kp_blocked, match_of_kp, nullptr, nmatches);
 }
 
 int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
                             const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid,
-                            int th_accept, int stereo_gate, int check_orientation, int device,
-                            uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches) {
-  if (nq < 0 || nk < 0 || !nmatches || (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) ||
-      (nq > 0 && (!q || !qdesc)))
+                            int th_accept, int gate, const float* inv_level_sigma2, int nlevels,
+                            int check_orientation, int device, uint8_t* kp_blocked, int32_t* match_of_kp,
+                            int32_t* match_of_query, int* nmatches) {
+  if (nq < 0 || nk < 0 || !nmatches || gate < 0 || gate > 2 ||
+      (gate == 2 && (!inv_level_sigma2 || nlevels < 1 || nlevels > kMaxLevels)) ||
+      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
     return ORB_GPU_ERR_ARG;
-  return run_windowed(q, qdesc, nq, kps, kdesc, stereo_gate ? u_right : nullptr, nk, grid, false, 0.f, th_accept,
-                      check_orientation, device, kp_blocked, match_of_kp, nmatches);
+  return run_windowed(q, qdesc, nq, kps, kdesc, gate ? u_right : nullptr, nk, grid, false, 0.f, th_accept, gate,
+                      inv_level_sigma2, nlevels, check_orientation, device, kp_blocked, match_of_kp,
+                      match_of_query, nmatches);
 }
 
 int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const OrbKeyPoint* kr,

@@ -172,14 +172,20 @@ typedef struct {
  *   ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono)          src/ORBmatcher.cc:1328-1470
  *   ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist)     :1472-1599
  *   ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th)           :290-403
- * (candidate order of Get FeaturesInArea, bestDist from 256 with strict '<', accept best <= th_accept, claim,
- * ComputeThreeMaxima :1601-1642 when check_orientation).  Host pointers.  kp_blocked in/out; match_of_kp[nk]
- * = query index, -1 (untouched) or -2 (matched, then reset to NULL by the rotation check, :1461). */
+ *   ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) / Fuse(KeyFrame*, Scw, ...) search loops  :825-975, :977-1100
+ *   ORBmatcher::SearchBySim3: each of its two passes                                       :1102-1326
+ * (candidate order of GetFeaturesInArea, bestDist from 256 with strict '<', accept best <= th_accept, claim,
+ * ComputeThreeMaxima :1601-1642 when check_orientation).  gate: 0 none; 1 stereo radius gate (:1407-1413:
+ * u_right[i] > 0 and |ur - u_right[i]| > radius -> skip); 2 chi-square gate of Fuse (:904-931:
+ * e2 * inv_level_sigma2[octave] > 5.99, or 7.8 with the right coordinate when u_right[i] >= 0).
+ * Host pointers.  kp_blocked in/out; match_of_kp[nk] = query index, -1 (untouched) or -2 (matched, then reset
+ * to NULL by the rotation check, :1461); match_of_query[nq] (optional) = keypoint chosen by query i or -1. */
 int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq,
                             const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
-                            int nk, OrbFrameGrid grid, int th_accept, int stereo_gate,
-                            int check_orientation, int device, uint8_t* kp_blocked,
-                            int32_t* match_of_kp, int* nmatches);
+                            int nk, OrbFrameGrid grid, int th_accept, int gate,
+                            const float* inv_level_sigma2, int nlevels, int check_orientation,
+                            int device, uint8_t* kp_blocked, int32_t* match_of_kp,
+                            int32_t* match_of_query, int* nmatches);
 
 /* Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): for each left keypoint
  * the best right keypoint in its row band within the disparity and octave gates.

@@ -172,13 +172,14 @@ int orbo_search_by_projection(const ProjQuery* q, const uint8_t* qdesc, int nq, 
 
 int orbo_search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
                          const uint8_t* kdesc, const float* u_right, int nk, float minX, float minY,
-                         float invW, float invH, int th_accept, int stereo_gate, int check_orientation,
-                         uint8_t* kp_blocked, int32_t* match_of_kp) {
+                         float invW, float invH, int th_accept, int gate, const float* inv_level_sigma2,
+                         int check_orientation, uint8_t* kp_blocked, int32_t* match_of_kp,
+                         int32_t* match_of_query) {
   FrameGrid g;
   g.minX = minX; g.minY = minY; g.invW = invW; g.invH = invH;
   g.build(kps, nk);
-  return search_windowed(q, qdesc, nq, kps, kdesc, u_right, nk, g, th_accept, stereo_gate != 0,
-                         check_orientation != 0, kp_blocked, match_of_kp);
+  return search_windowed(q, qdesc, nq, kps, kdesc, u_right, nk, g, th_accept, gate, inv_level_sigma2,
+                         check_orientation != 0, kp_blocked, match_of_kp, match_of_query);
 }
 
 // candidate list of one GetFeaturesInArea query, in the reference's order

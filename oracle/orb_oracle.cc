@@ -510,13 +510,14 @@ void compute_three_maxima(const int* hs, int L, int& ind1, int& ind2, int& ind3)
 // the same loop with other gates / thresholds.
 int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
                     const uint8_t* kdesc, const float* u_right, int nk, const FrameGrid& grid,
-                    int th_accept, bool stereo_gate, bool check_orientation, uint8_t* blocked,
-                    int32_t* match_of_kp) {
+                    int th_accept, int gate, const float* inv_level_sigma2, bool check_orientation,
+                    uint8_t* blocked, int32_t* match_of_kp, int32_t* match_of_query) {
   const int HISTO_LENGTH = 30;
   int nmatches = 0;
   std::vector<int> rotHist[HISTO_LENGTH];
   const float factor = 1.0f / HISTO_LENGTH;
   for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
+  if (match_of_query) for (int i = 0; i < nq; ++i) match_of_query[i] = -1;
   std::vector<int> cand;
   for (int i = 0; i < nq; ++i) {
     const WindowQuery& p = q[i];
@@ -526,14 +527,26 @@ int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const Ke
     int bestDist = 256, bestIdx2 = -1;
     for (int i2 : cand) {
       if (blocked[i2]) continue;  // :1403-1405 / :1541-1542 / :375
-      if (stereo_gate && u_right && u_right[i2] > 0) {
+      if (gate == 1 && u_right && u_right[i2] > 0) {
         const float er = std::fabs(p.ur - u_right[i2]);
         if (er > p.radius) continue;
+      }
+      if (gate == 2) {  // Fuse :904-931
+        const float ex = p.u - kps[i2].x, ey = p.v - kps[i2].y;
+        if (u_right && u_right[i2] >= 0) {
+          const float er = p.ur - u_right[i2];
+          const float e2 = ex * ex + ey * ey + er * er;
+          if (e2 * inv_level_sigma2[kps[i2].octave] > 7.8) continue;
+        } else {
+          const float e2 = ex * ex + ey * ey;
+          if (e2 * inv_level_sigma2[kps[i2].octave] > 5.99) continue;
+        }
       }
       const int dist = descriptor_distance(qdesc + (size_t)i * 32, kdesc + (size_t)i2 * 32);
       if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
     }
     if (bestDist <= th_accept) {
+      if (match_of_query) match_of_query[i] = bestIdx2;
       match_of_kp[bestIdx2] = i;
       blocked[bestIdx2] = p.blocks;
       ++nmatches;
@@ -553,6 +566,9 @@ int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const Ke
     for (int i = 0; i < HISTO_LENGTH; ++i)
       if (i != ind1 && i != ind2 && i != ind3)
         for (int idx : rotHist[i]) { match_of_kp[idx] = -2; blocked[idx] = 0; --nmatches; }  // NULL after :1461
+    if (match_of_query)
+      for (int i = 0; i < nq; ++i)
+        if (match_of_query[i] >= 0 && match_of_kp[match_of_query[i]] == -2) match_of_query[i] = -1;
   }
   return nmatches;
 }

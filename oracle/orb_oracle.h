@@ -117,10 +117,14 @@ void compute_three_maxima(const int* histo_sizes, int L, int& ind1, int& ind2, i
 // M3/M4/M5: best-only search in a window, accept best <= th_accept, in-order claims, optional rotation
 // consistency (mbCheckOrientation).  kp_blocked in/out; match_of_kp[i] = last query assigned to keypoint i or -1
 // (-2 when any of its assignments fell in a pruned histogram bin: reset to NULL at :1448-1467).  Returns nmatches.
+// gate: 0 none; 1 stereo radius gate of M2/M3 (u_right[i] > 0 and |ur - u_right[i]| > radius -> skip);
+// 2 chi-square gate of ORBmatcher::Fuse (:904-931): e2 * inv_level_sigma2[octave] > 5.99 (mono) / 7.8 (stereo,
+// u_right[i] >= 0).  match_of_query[i] (optional) = keypoint chosen by query i or -1 (SearchBySim3 :1190-1227
+// needs the per-source result: its two passes claim nothing and are cross-checked on the host).
 int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const KeyPoint* kps,
                     const uint8_t* kdesc, const float* u_right, int nk, const FrameGrid& grid,
-                    int th_accept, bool stereo_gate, bool check_orientation, uint8_t* kp_blocked,
-                    int32_t* match_of_kp);
+                    int th_accept, int gate, const float* inv_level_sigma2, bool check_orientation,
+                    uint8_t* kp_blocked, int32_t* match_of_kp, int32_t* match_of_query);
 
 // M10: Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549).
 // best_idx_r[i] = right index or -1; best_dist[i] = distance (TH_HIGH if none).

@@ -231,9 +231,10 @@ def search_by_projection(queries, qdesc, kps, kdesc, u_right, grid, scale_factor
     return n, out, blocked
 
 
-def search_windowed(queries, qdesc, kps, kdesc, u_right, grid, th_accept, stereo_gate, check_orientation,
-                    blocked=None):
-    """M3/M4/M5 (best-only windowed search + rotation histogram).  -> nmatches, match_of_kp[nk], blocked_after"""
+def search_windowed(queries, qdesc, kps, kdesc, u_right, grid, th_accept, gate, check_orientation,
+                    blocked=None, inv_level_sigma2=None):
+    """M3/M4/M5 (best-only windowed search + rotation histogram); gate 0 none / 1 stereo radius / 2 chi-square.
+    -> nmatches, match_of_kp[nk], blocked_after[nk], match_of_query[nq]"""
     queries = np.ascontiguousarray(queries, WINDOW_DTYPE)
     qdesc = u8c(qdesc)
     kps = np.ascontiguousarray(kps, KP_DTYPE)
@@ -242,11 +243,13 @@ def search_windowed(queries, qdesc, kps, kdesc, u_right, grid, th_accept, stereo
     blocked = np.zeros(nk, np.uint8) if blocked is None else np.array(blocked, np.uint8)
     ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
     out = np.empty(nk, np.int32)
+    outq = np.empty(len(queries), np.int32)
+    sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
     n = lib().orbo_search_windowed(_p(queries), _p(qdesc), len(queries), _p(kps), _p(kdesc), _p(ur), nk,
                                    C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
-                                   C.c_float(grid[3]), int(th_accept), int(bool(stereo_gate)),
-                                   int(bool(check_orientation)), _p(blocked), _p(out))
-    return n, out, blocked
+                                   C.c_float(grid[3]), int(th_accept), int(gate), _p(sig),
+                                   int(bool(check_orientation)), _p(blocked), _p(out), _p(outq))
+    return n, out, blocked, outq
 
 
 def features_in_area(kps, grid, x, y, r, min_level, max_level):
