@@ -22,6 +22,7 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
 PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("level", "<i4"),
                        ("view_cos", "<f4"), ("valid", "u1"), ("has_obs", "u1"), ("pad", "u1", (2,))])
+BUCKET_DTYPE = np.dtype([("index", "<i4"), ("begin", "<i4"), ("end", "<i4")])
 WINDOW_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("min_level", "<i4"),
                          ("max_level", "<i4"), ("angle", "<f4"), ("valid", "u1"), ("blocks", "u1"),
                          ("pad", "u1", (2,))])
@@ -33,7 +34,8 @@ EXPORTS = [
     "orb_gpu_get_scale_tables", "orb_gpu_get_features_per_level", "orb_gpu_get_pyramid",
     "orb_gpu_get_candidates", "orb_gpu_hamming_pairs_device", "orb_gpu_match_bruteforce_device",
     "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
-    "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
+    "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_search_by_bow",
+    "orb_gpu_search_for_triangulation", "orb_gpu_search_for_initialization", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
     "orb_gpu_launch_count", "orb_gpu_popc_peak",
 ]
 
@@ -102,6 +104,13 @@ def lib():
         L.orb_gpu_search_windowed.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_int, _Grid, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
                                               C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+        vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+        L.orb_gpu_search_by_bow.argtypes = [vp, ci, vp, ci, vp, vp, ci, vp, vp, vp, ci, cf, ci, ci, ci, vp, vp,
+                                            C.POINTER(ci)]
+        L.orb_gpu_search_for_triangulation.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, vp, vp, vp, vp, ci, vp, cf, cf,
+                                                       vp, vp, ci, ci, ci, ci, vp, C.POINTER(ci)]
+        L.orb_gpu_search_for_initialization.argtypes = [vp, vp, ci, vp, vp, vp, ci, _Grid, ci, cf, ci, ci, vp,
+                                                        C.POINTER(ci)]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -335,6 +344,81 @@ class ORBmatcher:
                                              _p(outq), C.byref(n)),
                "orb_gpu_search_windowed")
         return n.value, out, outq
+
+    @staticmethod
+    def bucket_queries(fv1, fv2, keep1):
+        """Walk two DBoW2 feature vectors ({node id: [feature indices]}) the way the reference's two iterators
+        do (src/ORBmatcher.cc:178-266: nodes ascending, equal ids only) and emit one BUCKET_DTYPE row per source
+        feature with keep1[index] set, plus the flat candidate list of frame 2.  Host bookkeeping only."""
+        rows, cand = [], []
+        for node in sorted(set(fv1) & set(fv2)):
+            begin = len(cand)
+            cand.extend(int(j) for j in fv2[node])
+            rows.extend((int(i), begin, len(cand)) for i in fv1[node] if keep1[i])
+        q = np.array(rows, BUCKET_DTYPE) if rows else np.zeros(0, BUCKET_DTYPE)
+        return q, np.asarray(cand, np.int32)
+
+    def SearchByBoW(self, kf, frame, good_mp1, good_mp2=None):
+        """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (ORBmatcher.cc:159-288) when good_mp2 is None, else
+        SearchByBoW(KeyFrame*, KeyFrame*, ...) (:522-655, strict best < TH_LOW).  kf / frame: dict(kps, desc,
+        feat_vec {node: [indices]}); good_mp*: feature holds a map point that is not bad.
+        -> nmatches, match12 [n1], match21 [n2]"""
+        k1 = np.ascontiguousarray(kf["kps"], KP_DTYPE); d1 = np.ascontiguousarray(kf["desc"], np.uint8)
+        k2 = np.ascontiguousarray(frame["kps"], KP_DTYPE); d2 = np.ascontiguousarray(frame["desc"], np.uint8)
+        q, cand = self.bucket_queries(kf["feat_vec"], frame["feat_vec"], np.asarray(good_mp1, bool))
+        skip2 = None if good_mp2 is None else np.ascontiguousarray(~np.asarray(good_mp2, bool), np.uint8)
+        th = self.TH_LOW if good_mp2 is None else self.TH_LOW - 1
+        m12 = np.empty(len(k1), np.int32); m21 = np.empty(len(k2), np.int32)
+        n = C.c_int()
+        _check(lib().orb_gpu_search_by_bow(_p(q), len(q), _p(cand), len(cand), _p(k1), _p(d1), len(k1), _p(k2),
+                                           _p(d2), _p(skip2), len(k2), self.mfNNratio, th,
+                                           int(self.mbCheckOrientation), self.device, _p(m12), _p(m21),
+                                           C.byref(n)), "orb_gpu_search_by_bow")
+        return n.value, m12, m21
+
+    def SearchForTriangulation(self, kf1, kf2, F12, epipole, has_mp1, has_mp2, only_stereo=False):
+        """ORBmatcher::SearchForTriangulation (ORBmatcher.cc:657-823).  kf*: dict(kps, desc, feat_vec, u_right or
+        None); kf2 also scale_factors, level_sigma2.  -> nmatches, match12 [n1]"""
+        k1 = np.ascontiguousarray(kf1["kps"], KP_DTYPE); d1 = np.ascontiguousarray(kf1["desc"], np.uint8)
+        k2 = np.ascontiguousarray(kf2["kps"], KP_DTYPE); d2 = np.ascontiguousarray(kf2["desc"], np.uint8)
+        u1 = kf1.get("u_right"); u2 = kf2.get("u_right")
+        u1 = None if u1 is None else np.ascontiguousarray(u1, np.float32)
+        u2 = None if u2 is None else np.ascontiguousarray(u2, np.float32)
+        keep1 = ~np.asarray(has_mp1, bool)
+        if only_stereo:
+            keep1 &= (u1 >= 0) if u1 is not None else False
+        q, cand = self.bucket_queries(kf1["feat_vec"], kf2["feat_vec"], keep1)
+        skip2 = np.ascontiguousarray(has_mp2, np.uint8)
+        F = np.ascontiguousarray(F12, np.float32).reshape(9)
+        sf = np.ascontiguousarray(kf2["scale_factors"], np.float32)
+        sg = np.ascontiguousarray(kf2["level_sigma2"], np.float32)
+        m12 = np.empty(len(k1), np.int32)
+        n = C.c_int()
+        _check(lib().orb_gpu_search_for_triangulation(
+            _p(q), len(q), _p(cand), len(cand), _p(k1), _p(d1), _p(u1), len(k1), _p(k2), _p(d2), _p(u2), _p(skip2),
+            len(k2), _p(F), float(epipole[0]), float(epipole[1]), _p(sf), _p(sg), len(sf), int(bool(only_stereo)),
+            int(self.mbCheckOrientation), self.device, _p(m12), C.byref(n)), "orb_gpu_search_for_triangulation")
+        return n.value, m12
+
+    def SearchForInitialization(self, f1, f2, prev_matched, window=100):
+        """ORBmatcher::SearchForInitialization (ORBmatcher.cc:405-520).  f1 / f2: dict(kps, desc), f2 also grid;
+        prev_matched float32 [n1, 2] is updated in place from the matches (:514-517).
+        -> nmatches, vnMatches12 [n1]"""
+        k1 = np.ascontiguousarray(f1["kps"], KP_DTYPE); d1 = np.ascontiguousarray(f1["desc"], np.uint8)
+        k2 = np.ascontiguousarray(f2["kps"], KP_DTYPE); d2 = np.ascontiguousarray(f2["desc"], np.uint8)
+        if prev_matched.dtype != np.float32 or prev_matched.shape != (len(k1), 2) or not prev_matched.flags.c_contiguous:
+            raise ValueError("prev_matched must be a C-contiguous float32 [n1, 2] array")
+        g = _Grid(*[float(v) for v in f2["grid"]])
+        m12 = np.empty(len(k1), np.int32)
+        n = C.c_int()
+        _check(lib().orb_gpu_search_for_initialization(_p(k1), _p(d1), len(k1), _p(prev_matched), _p(k2), _p(d2),
+                                                       len(k2), g, int(window), self.mfNNratio,
+                                                       int(self.mbCheckOrientation), self.device, _p(m12),
+                                                       C.byref(n)), "orb_gpu_search_for_initialization")
+        hit = m12 >= 0
+        prev_matched[hit, 0] = k2["x"][m12[hit]]
+        prev_matched[hit, 1] = k2["y"][m12[hit]]
+        return n.value, m12
 
     def stereo_match(self, kps_l, desc_l, kps_r, desc_r, n_rows, scale_factors, min_d, max_d):
         """Hamming stage of Frame::ComputeStereoMatches (Frame.cc:466-549) -> best_idx_r, best_dist."""

@@ -156,6 +156,20 @@ __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int
   for (int k = lo; k < hi; ++k) { out[k] = run; run += in[k]; }
 }
 
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) on the 30 bin sizes
+__device__ inline void three_maxima(const int* hist, int* keep) {
+  int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+  for (int i = 0; i < ORB_GPU_HISTO_LENGTH; ++i) {
+    const int sz = hist[i];
+    if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+    else if (sz > max3) { max3 = sz; ind3 = i; }
+  }
+  if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+  else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+  keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+}
+
 // ---- ordered claim resolution as a fixpoint ---------------------------------------------------
 // TOP2: stable top-2 with the same-level ratio rule of :102-121 (M2); else best-only, accept <= th (M3/M4/M5).
 // check_ori: rotation histogram over the accepted matches, ComputeThreeMaxima (:1601-1642), losers un-matched.
@@ -163,7 +177,7 @@ template <bool TOP2>
 __global__ void __launch_bounds__(1024)
 window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKeyPoint* __restrict__ kps, int nk,
                       const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
-                      int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
+                      int ratio_rule, int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
                       int* __restrict__ claim_a, int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
                       int32_t* __restrict__ match_of_kp, int32_t* __restrict__ match_of_query,
                       int* __restrict__ nmatches) {
@@ -211,7 +225,11 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
               level2 = (int)(entries[beg + (k2 & 0xfffffu)] >> 25);
             }
             const int level1 = (int)(e1 >> 25);
-            if (level1 == level2 && (float)best_dist > __fmul_rn(nnratio, (float)best_dist2)) ok = false;
+            if (ratio_rule == 0) {  // SearchByProjection (:115-116): only between candidates of one level
+              if (level1 == level2 && (float)best_dist > __fmul_rn(nnratio, (float)best_dist2)) ok = false;
+            } else {                // SearchByBoW (:230, :600): strict, against 256 when there is no second
+              ok = (float)best_dist < __fmul_rn(nnratio, (float)best_dist2);
+            }
           }
           if (ok) result = (int)(e1 & 0xffffu);
         }
@@ -254,18 +272,7 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
         atomicAdd(&s_hist[bin], 1);
       }
     __syncthreads();
-    if (t == 0) {  // ComputeThreeMaxima (:1601-1642)
-      int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-      for (int i = 0; i < ORB_GPU_HISTO_LENGTH; ++i) {
-        const int sz = s_hist[i];
-        if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
-        else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
-        else if (sz > max3) { max3 = sz; ind3 = i; }
-      }
-      if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-      else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-      s_keep[0] = ind1; s_keep[1] = ind2; s_keep[2] = ind3;
-    }
+    if (t == 0) three_maxima(s_hist, s_keep);
     __syncthreads();
     local = 0;
     for (int i = t; i < nq; i += T)
@@ -319,6 +326,219 @@ stereo_match_kernel(const OrbKeyPoint* __restrict__ kl, const uint4* __restrict_
     best_idx_r[warp] = ok ? (int)(best & 0xffffu) : -1;
     best_dist[warp] = ok ? d : th_high;
   }
+}
+
+// ---- bucket searches (SearchByBoW x2, SearchForTriangulation): equal vocabulary nodes ----------
+// A query = one feature of frame 1 with the index list of the same node in frame 2 (cand[begin..end), in the
+// node's insertion order).  Entries use the layout of the windowed search (idx | dist << 16, level 0), so the
+// ordered claims are resolved by window_resolve_kernel.
+__global__ void __launch_bounds__(256)
+bucket_entries_kernel(const OrbBucketQuery* __restrict__ q, int nq, const int32_t* __restrict__ cand,
+                      const uint4* __restrict__ d1, const uint4* __restrict__ d2,
+                      const int* __restrict__ offsets, uint32_t* __restrict__ entries) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= nq) return;
+  const OrbBucketQuery Q = q[warp];
+  const int base = offsets[warp];
+  for (int e = Q.begin + lane; e < Q.end; e += 32) {
+    const int idx2 = cand[e];
+    const unsigned d = (unsigned)hamming_rows(d1 + 2 * (size_t)Q.index, d2 + 2 * (size_t)idx2);
+    entries[base + (e - Q.begin)] = (unsigned)idx2 | (d << 16);
+  }
+}
+
+struct TriangulationParams {
+  float F12[9];
+  float ex, ey;
+  float scale2[kMaxLevels], sigma2_2[kMaxLevels];
+  int only_stereo, check_ori, th_low;
+};
+
+// SearchForTriangulation (src/ORBmatcher.cc:657-823): no claims (vbMatched2 is never set, :677), so every
+// query is independent: among the candidates with dist <= TH_LOW that pass the epipole and epipolar-line gates
+// (:742-755, :138-157) the smallest distance wins and, on ties, the LAST one in node order (:737 skips only
+// dist > bestDist).  One block: warp per query, then the rotation histogram (:790-808).
+__global__ void __launch_bounds__(1024)
+triangulation_kernel(const OrbBucketQuery* __restrict__ q, int nq, const int32_t* __restrict__ cand,
+                     const OrbKeyPoint* __restrict__ k1, const uint4* __restrict__ d1,
+                     const float* __restrict__ ur1, const OrbKeyPoint* __restrict__ k2,
+                     const uint4* __restrict__ d2, const float* __restrict__ ur2,
+                     const uint8_t* __restrict__ has_mp2, TriangulationParams P, int* __restrict__ bins,
+                     int32_t* __restrict__ match_of_query, int* __restrict__ nmatches) {
+  __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3], s_count;
+  const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
+  if (t < ORB_GPU_HISTO_LENGTH) s_hist[t] = 0;
+  if (t == 0) s_count = 0;
+  __syncthreads();
+  for (int i = warp; i < nq; i += nwarps) {
+    const OrbBucketQuery Q = q[i];
+    const OrbKeyPoint kp1 = k1[Q.index];
+    const bool stereo1 = ur1 && ur1[Q.index] >= 0;
+    // epipolar line l = x1' F12 (:141-143), one rounding per operation, left to right
+    const float a = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F12[0]), __fmul_rn(kp1.y, P.F12[3])), P.F12[6]);
+    const float b = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F12[1]), __fmul_rn(kp1.y, P.F12[4])), P.F12[7]);
+    const float c = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F12[2]), __fmul_rn(kp1.y, P.F12[5])), P.F12[8]);
+    const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+    unsigned best = 0xffffffffu;  // dist << 20 | (0xfffff - position): smallest distance, then last position
+    for (int e = Q.begin + lane; e < Q.end; e += 32) {
+      const int idx2 = cand[e];
+      if (has_mp2[idx2]) continue;  // :722-726
+      const bool stereo2 = ur2 && ur2[idx2] >= 0;
+      if (P.only_stereo && !stereo2) continue;
+      const int dist = hamming_rows(d1 + 2 * (size_t)Q.index, d2 + 2 * (size_t)idx2);
+      if (dist > P.th_low) continue;
+      const OrbKeyPoint kp2 = k2[idx2];
+      if (!stereo1 && !stereo2) {
+        const float dx = __fsub_rn(P.ex, kp2.x), dy = __fsub_rn(P.ey, kp2.y);
+        if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, P.scale2[kp2.octave])) continue;
+      }
+      const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, kp2.x), __fmul_rn(b, kp2.y)), c);
+      if (den == 0) continue;
+      const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+      if (!((double)dsqr < 3.84 * (double)P.sigma2_2[kp2.octave])) continue;
+      best = min(best, ((unsigned)dist << 20) | (0xfffffu - (unsigned)(e - Q.begin)));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) {
+      int res = -1;
+      if (best != 0xffffffffu) {
+        res = cand[Q.begin + (int)(0xfffffu - (best & 0xfffffu))];
+        atomicAdd(&s_count, 1);
+        if (P.check_ori) {
+          float rot = __fsub_rn(kp1.angle, k2[res].angle);
+          if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+          int bin = (int)roundf(__fmul_rn(rot, __fdiv_rn(1.0f, (float)ORB_GPU_HISTO_LENGTH)));
+          if (bin == ORB_GPU_HISTO_LENGTH) bin = 0;
+          bins[i] = bin;
+          atomicAdd(&s_hist[bin], 1);
+        }
+      }
+      match_of_query[i] = res;
+    }
+  }
+  __syncthreads();
+  if (P.check_ori) {
+    if (t == 0) three_maxima(s_hist, s_keep);
+    __syncthreads();
+    int local = 0;
+    for (int i = t; i < nq; i += T)
+      if (match_of_query[i] >= 0) {
+        const int bin = bins[i];
+        if (bin != s_keep[0] && bin != s_keep[1] && bin != s_keep[2]) { match_of_query[i] = -1; ++local; }
+      }
+    if (local) atomicSub(&s_count, local);
+    __syncthreads();
+  }
+  if (t == 0) *nmatches = s_count;
+}
+
+// SearchForInitialization (src/ORBmatcher.cc:405-520).  A source keypoint (level 0 only) looks in a window of
+// frame 2 around its previously matched position; a target already taken at distance <= dist is invisible
+// (:444-445), otherwise the newcomer steals it (:463-471).  vMatchedDistance[i2] only ever decreases, so the
+// value query i sees equals min{dist_j : j < i accepted on i2}; the sequential result is the fixpoint of
+// "query i evaluates against the accepted choices of all j < i", reached by rounds as in window_resolve_kernel.
+// Accepted choices are kept as per-target linked lists (head[], next[]).
+__global__ void __launch_bounds__(1024)
+init_resolve_kernel(const OrbKeyPoint* __restrict__ kps1, int nq, const OrbKeyPoint* __restrict__ kps2, int nk,
+                    const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
+                    int th_low, int check_ori, int* __restrict__ claim_a, int* __restrict__ claim_b,
+                    int* __restrict__ dist_a, int* __restrict__ dist_b, int* __restrict__ next,
+                    int* __restrict__ head /*[nk]*/, int32_t* __restrict__ match12, int* __restrict__ nmatches) {
+  __shared__ int s_changed, s_count;
+  __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3];
+  const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
+  int *prev = claim_a, *cur = claim_b, *pdist = dist_a, *cdist = dist_b;
+  for (int i = t; i < nq; i += T) prev[i] = -1;
+  __syncthreads();
+  for (int round = 0; round <= nq; ++round) {
+    for (int k = t; k < nk; k += T) head[k] = -1;
+    if (t == 0) s_changed = 0;
+    __syncthreads();
+    for (int i = t; i < nq; i += T)
+      if (prev[i] >= 0) next[i] = atomicExch(&head[prev[i]], i);
+    __syncthreads();
+    for (int i = warp; i < nq; i += nwarps) {
+      const int beg = offsets[i], end = offsets[i + 1];
+      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position)
+      for (int e = beg + lane; e < end; e += 32) {
+        const uint32_t en = entries[e];
+        const int idx = (int)(en & 0xffffu), dist = (int)((en >> 16) & 0x1ffu);
+        int taken = INT_MAX;  // vMatchedDistance[idx] as query i sees it
+        for (int j = head[idx]; j >= 0; j = next[j])
+          if (j < i) taken = min(taken, pdist[j]);
+        if (taken <= dist) continue;  // :444-445
+        const unsigned key = ((unsigned)dist << 20) | (unsigned)(e - beg);
+        if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const unsigned lo = min(k1, o1), hi = max(k1, o1);
+        k2 = min(hi, min(k2, o2));
+        k1 = lo;
+      }
+      if (lane == 0) {
+        int result = -1, rdist = 0;
+        if (k1 != 0xffffffffu) {
+          const int best = (int)(k1 >> 20);
+          const float second = k2 != 0xffffffffu ? (float)(int)(k2 >> 20) : (float)INT_MAX;
+          if (best <= th_low && (float)best < __fmul_rn(second, nnratio)) {  // :459-461
+            result = (int)(entries[beg + (k1 & 0xfffffu)] & 0xffffu);
+            rdist = best;
+          }
+        }
+        cur[i] = result;
+        cdist[i] = rdist;
+        if (result != prev[i]) s_changed = 1;
+      }
+    }
+    __syncthreads();
+    int* tmp = prev; prev = cur; cur = tmp;
+    tmp = pdist; pdist = cdist; cdist = tmp;
+    const int changed = s_changed;
+    __syncthreads();
+    if (!changed) break;
+  }
+  // vnMatches21 = last accepted query per target; everyone else on that target was robbed (:463-467)
+  for (int k = t; k < nk; k += T) head[k] = -1;
+  if (t == 0) s_count = 0;
+  if (t < ORB_GPU_HISTO_LENGTH) s_hist[t] = 0;
+  __syncthreads();
+  for (int i = t; i < nq; i += T)
+    if (prev[i] >= 0) atomicMax(&head[prev[i]], i);
+  __syncthreads();
+  const float factor = __fdiv_rn(1.0f, (float)ORB_GPU_HISTO_LENGTH);
+  int local = 0;
+  for (int i = t; i < nq; i += T) {
+    const int k = prev[i];
+    const bool keeps = k >= 0 && head[k] == i;
+    match12[i] = keeps ? k : -1;
+    local += keeps;
+    if (k >= 0 && check_ori) {  // the histogram also counts matches that were robbed later (:472-481)
+      float rot = __fsub_rn(kps1[i].angle, kps2[k].angle);
+      if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+      int bin = (int)roundf(__fmul_rn(rot, factor));
+      if (bin == ORB_GPU_HISTO_LENGTH) bin = 0;
+      cur[i] = bin;
+      atomicAdd(&s_hist[bin], 1);
+    }
+  }
+  if (local) atomicAdd(&s_count, local);
+  __syncthreads();
+  if (check_ori) {
+    if (t == 0) three_maxima(s_hist, s_keep);
+    __syncthreads();
+    local = 0;
+    for (int i = t; i < nq; i += T)
+      if (match12[i] >= 0) {
+        const int bin = cur[i];
+        if (bin != s_keep[0] && bin != s_keep[1] && bin != s_keep[2]) { match12[i] = -1; ++local; }
+      }
+    if (local) atomicSub(&s_count, local);
+    __syncthreads();
+  }
+  if (t == 0) *nmatches = s_count;
 }
 
 }  // namespace orbgpu
@@ -378,11 +598,11 @@ static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, c
       doff.as<int>(), dent.as<uint32_t>());
   if (top2)
     window_resolve_kernel<true><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dent.as<uint32_t>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
         dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
   else
     window_resolve_kernel<false><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), nnratio, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dent.as<uint32_t>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
         dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
   count_launch(5);
   ORB_CUDA_TRY(cudaGetLastError());
@@ -431,6 +651,197 @@ int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int n
   return run_windowed(q, qdesc, nq, kps, kdesc, gate ? u_right : nullptr, nk, grid, false, 0.f, th_accept, gate,
                       inv_level_sigma2, nlevels, check_orientation, device, kp_blocked, match_of_kp,
                       match_of_query, nmatches);
+}
+
+static int check_bucket_queries(const OrbBucketQuery* q, int nq, int ncand2, int n1, const int32_t* cand2,
+                                int n2, std::vector<int>& offsets) {
+  offsets.assign((size_t)nq + 1, 0);
+  for (int i = 0; i < nq; ++i) {
+    if (q[i].index < 0 || q[i].index >= n1 || q[i].begin < 0 || q[i].end < q[i].begin || q[i].end > ncand2)
+      return ORB_GPU_ERR_ARG;
+    offsets[i + 1] = offsets[i] + (q[i].end - q[i].begin);
+  }
+  for (int i = 0; i < ncand2; ++i)
+    if (cand2[i] < 0 || cand2[i] >= n2) return ORB_GPU_ERR_ARG;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_search_by_bow(const OrbBucketQuery* q, int nq, const int32_t* cand2, int ncand2,
+                          const OrbKeyPoint* kps1, const uint8_t* desc1, int n1, const OrbKeyPoint* kps2,
+                          const uint8_t* desc2, const uint8_t* skip2, int n2, float nnratio, int th_accept,
+                          int check_orientation, int device, int32_t* match12, int32_t* match21,
+                          int* nmatches) {
+  if (nq < 0 || n1 < 0 || n2 < 0 || ncand2 < 0 || !nmatches || (n1 > 0 && !match12) || (n2 > 0 && !match21) ||
+      (nq > 0 && (!q || !kps1 || !desc1)) || (ncand2 > 0 && (!cand2 || !kps2 || !desc2)))
+    return ORB_GPU_ERR_ARG;
+  *nmatches = 0;
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  for (int i = 0; i < n2; ++i) match21[i] = -1;
+  if (nq == 0 || n2 == 0 || ncand2 == 0) return ORB_GPU_OK;
+  if (n2 > 32768) return ORB_GPU_ERR_CAPACITY;
+  std::vector<int> offsets;
+  int rc;
+  if ((rc = check_bucket_queries(q, nq, ncand2, n1, cand2, n2, offsets))) return rc;
+  std::vector<OrbWindowQuery> wq((size_t)nq);
+  for (int i = 0; i < nq; ++i) {
+    wq[i] = OrbWindowQuery();
+    wq[i].angle = kps1[q[i].index].angle;
+    wq[i].valid = 1;
+    wq[i].blocks = 1;
+  }
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  TmpDevW dq, dwq, dc, d1, dk2, d2, doff, dent, dblk, dca, dcb, dmin, dmatch, dmq, dn;
+  const int total = offsets[nq];
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbBucketQuery))) || (rc = dwq.alloc((size_t)nq * sizeof(OrbWindowQuery))) ||
+      (rc = dc.alloc((size_t)ncand2 * 4)) || (rc = d1.alloc((size_t)n1 * 32)) ||
+      (rc = dk2.alloc((size_t)n2 * sizeof(OrbKeyPoint))) || (rc = d2.alloc((size_t)n2 * 32)) ||
+      (rc = doff.alloc((size_t)(nq + 1) * 4)) || (rc = dent.alloc((size_t)total * 4)) || (rc = dblk.alloc((size_t)n2)) ||
+      (rc = dca.alloc((size_t)nq * 4)) || (rc = dcb.alloc((size_t)nq * 4)) || (rc = dmin.alloc((size_t)n2 * 4)) ||
+      (rc = dmatch.alloc((size_t)n2 * 4)) || (rc = dmq.alloc((size_t)nq * 4)) || (rc = dn.alloc(4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbBucketQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dwq.p, wq.data(), (size_t)nq * sizeof(OrbWindowQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dc.p, cand2, (size_t)ncand2 * 4, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(d1.p, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk2.p, kps2, (size_t)n2 * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(d2.p, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(doff.p, offsets.data(), (size_t)(nq + 1) * 4, cudaMemcpyHostToDevice));
+  if (skip2) ORB_CUDA_TRY(cudaMemcpy(dblk.p, skip2, (size_t)n2, cudaMemcpyHostToDevice));
+  else ORB_CUDA_TRY(cudaMemset(dblk.p, 0, (size_t)n2));
+  bucket_entries_kernel<<<(nq * 32 + 255) / 256, 256>>>(dq.as<OrbBucketQuery>(), nq, dc.as<int32_t>(), d1.as<uint4>(),
+                                                        d2.as<uint4>(), doff.as<int>(), dent.as<uint32_t>());
+  window_resolve_kernel<true><<<1, 1024>>>(dwq.as<OrbWindowQuery>(), nq, dk2.as<OrbKeyPoint>(), n2, doff.as<int>(),
+      dent.as<uint32_t>(), nnratio, 1, th_accept, check_orientation, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+      dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
+  count_launch(2);
+  ORB_CUDA_TRY(cudaGetLastError());
+  std::vector<int32_t> mq((size_t)nq);
+  ORB_CUDA_TRY(cudaMemcpy(mq.data(), dmq.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < nq; ++i)
+    if (mq[i] >= 0) { match12[q[i].index] = mq[i]; match21[mq[i]] = q[i].index; }
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_search_for_triangulation(const OrbBucketQuery* q, int nq, const int32_t* cand2, int ncand2,
+                                     const OrbKeyPoint* kps1, const uint8_t* desc1, const float* u_right1, int n1,
+                                     const OrbKeyPoint* kps2, const uint8_t* desc2, const float* u_right2,
+                                     const uint8_t* skip2, int n2, const float* F12, float ex, float ey,
+                                     const float* scale_factors2, const float* level_sigma2_2, int nlevels,
+                                     int only_stereo, int check_orientation, int device, int32_t* match12,
+                                     int* nmatches) {
+  if (nq < 0 || n1 < 0 || n2 < 0 || ncand2 < 0 || !nmatches || (n1 > 0 && !match12) || !F12 || !scale_factors2 ||
+      !level_sigma2_2 || nlevels < 1 || nlevels > kMaxLevels || (nq > 0 && (!q || !kps1 || !desc1)) ||
+      (ncand2 > 0 && (!cand2 || !kps2 || !desc2)))
+    return ORB_GPU_ERR_ARG;
+  *nmatches = 0;
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  if (nq == 0 || n2 == 0 || ncand2 == 0) return ORB_GPU_OK;
+  std::vector<int> offsets;
+  int rc;
+  if ((rc = check_bucket_queries(q, nq, ncand2, n1, cand2, n2, offsets))) return rc;
+  TriangulationParams P;
+  for (int i = 0; i < 9; ++i) P.F12[i] = F12[i];
+  P.ex = ex; P.ey = ey;
+  for (int i = 0; i < kMaxLevels; ++i) {
+    P.scale2[i] = i < nlevels ? scale_factors2[i] : 0.f;
+    P.sigma2_2[i] = i < nlevels ? level_sigma2_2[i] : 0.f;
+  }
+  P.only_stereo = only_stereo; P.check_ori = check_orientation; P.th_low = ORB_GPU_TH_LOW;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  TmpDevW dq, dc, dk1, d1, du1, dk2, d2, du2, dskip, dbins, dmq, dn;
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbBucketQuery))) || (rc = dc.alloc((size_t)ncand2 * 4)) ||
+      (rc = dk1.alloc((size_t)n1 * sizeof(OrbKeyPoint))) || (rc = d1.alloc((size_t)n1 * 32)) ||
+      (rc = du1.alloc((size_t)n1 * 4)) || (rc = dk2.alloc((size_t)n2 * sizeof(OrbKeyPoint))) ||
+      (rc = d2.alloc((size_t)n2 * 32)) || (rc = du2.alloc((size_t)n2 * 4)) || (rc = dskip.alloc((size_t)n2)) ||
+      (rc = dbins.alloc((size_t)nq * 4)) || (rc = dmq.alloc((size_t)nq * 4)) || (rc = dn.alloc(4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbBucketQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dc.p, cand2, (size_t)ncand2 * 4, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk1.p, kps1, (size_t)n1 * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(d1.p, desc1, (size_t)n1 * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk2.p, kps2, (size_t)n2 * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(d2.p, desc2, (size_t)n2 * 32, cudaMemcpyHostToDevice));
+  if (u_right1) ORB_CUDA_TRY(cudaMemcpy(du1.p, u_right1, (size_t)n1 * 4, cudaMemcpyHostToDevice));
+  if (u_right2) ORB_CUDA_TRY(cudaMemcpy(du2.p, u_right2, (size_t)n2 * 4, cudaMemcpyHostToDevice));
+  if (skip2) ORB_CUDA_TRY(cudaMemcpy(dskip.p, skip2, (size_t)n2, cudaMemcpyHostToDevice));
+  else ORB_CUDA_TRY(cudaMemset(dskip.p, 0, (size_t)n2));
+  triangulation_kernel<<<1, 1024>>>(dq.as<OrbBucketQuery>(), nq, dc.as<int32_t>(), dk1.as<OrbKeyPoint>(), d1.as<uint4>(),
+      u_right1 ? du1.as<float>() : nullptr, dk2.as<OrbKeyPoint>(), d2.as<uint4>(), u_right2 ? du2.as<float>() : nullptr,
+      dskip.as<uint8_t>(), P, dbins.as<int>(), dmq.as<int32_t>(), dn.as<int>());
+  count_launch(1);
+  ORB_CUDA_TRY(cudaGetLastError());
+  std::vector<int32_t> mq((size_t)nq);
+  ORB_CUDA_TRY(cudaMemcpy(mq.data(), dmq.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < nq; ++i)
+    if (mq[i] >= 0) match12[q[i].index] = mq[i];
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_search_for_initialization(const OrbKeyPoint* kps1, const uint8_t* desc1, int n1,
+                                      const float* prev_matched, const OrbKeyPoint* kps2, const uint8_t* desc2,
+                                      int n2, OrbFrameGrid grid, int window, float nnratio, int check_orientation,
+                                      int device, int32_t* match12, int* nmatches) {
+  if (n1 < 0 || n2 < 0 || !nmatches || (n1 > 0 && (!kps1 || !desc1 || !prev_matched || !match12)) ||
+      (n2 > 0 && (!kps2 || !desc2)))
+    return ORB_GPU_ERR_ARG;
+  *nmatches = 0;
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  if (n1 == 0 || n2 == 0) return ORB_GPU_OK;
+  if (n2 > 32768) return ORB_GPU_ERR_CAPACITY;
+  const int nq = n1, nk = n2;
+  std::vector<OrbWindowQuery> wq((size_t)nq);
+  for (int i = 0; i < nq; ++i) {
+    OrbWindowQuery& w = wq[i];
+    w = OrbWindowQuery();
+    if (kps1[i].octave > 0) continue;  // :421-423
+    w.u = prev_matched[2 * i]; w.v = prev_matched[2 * i + 1];
+    w.radius = (float)window;
+    w.min_level = kps1[i].octave; w.max_level = kps1[i].octave;  // GetFeaturesInArea(x, y, windowSize, level1, level1)
+    w.valid = 1;
+  }
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int nkpad = 2;
+  while (nkpad < nk) nkpad <<= 1;
+  TmpDevW dq, dqd, dk1, dk, dkd, dsorted, dcell, dcnt, doff, dent, dca, dcb, dda, ddb, dnext, dhead, dmatch, dn;
+  int rc;
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbWindowQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
+      (rc = dk1.alloc((size_t)nq * sizeof(OrbKeyPoint))) || (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) ||
+      (rc = dkd.alloc((size_t)nk * 32)) || (rc = dsorted.alloc((size_t)nkpad * 4)) ||
+      (rc = dcell.alloc((size_t)(kCells + 1) * 4)) || (rc = dcnt.alloc((size_t)nq * 4)) ||
+      (rc = doff.alloc((size_t)(nq + 1) * 4)) || (rc = dca.alloc((size_t)nq * 4)) || (rc = dcb.alloc((size_t)nq * 4)) ||
+      (rc = dda.alloc((size_t)nq * 4)) || (rc = ddb.alloc((size_t)nq * 4)) || (rc = dnext.alloc((size_t)nq * 4)) ||
+      (rc = dhead.alloc((size_t)nk * 4)) || (rc = dmatch.alloc((size_t)nq * 4)) || (rc = dn.alloc(4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, wq.data(), (size_t)nq * sizeof(OrbWindowQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dqd.p, desc1, (size_t)nq * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk1.p, kps1, (size_t)nq * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk.p, kps2, (size_t)nk * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dkd.p, desc2, (size_t)nk * 32, cudaMemcpyHostToDevice));
+  const size_t smem = (size_t)nkpad * 4;
+  if (smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grid_build_kernel<<<1, 1024, smem>>>(dk.as<OrbKeyPoint>(), nk, nkpad, grid, dsorted.as<uint32_t>(), dcell.as<int>());
+  const int blocks = (nq * 32 + 255) / 256;
+  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr,
+      nullptr);
+  exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
+  int total = 0;
+  ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
+  if ((rc = dent.alloc((size_t)total * 4))) return rc;
+  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(),
+      dent.as<uint32_t>());
+  init_resolve_kernel<<<1, 1024>>>(dk1.as<OrbKeyPoint>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
+      dent.as<uint32_t>(), nnratio, ORB_GPU_TH_LOW, check_orientation, dca.as<int>(), dcb.as<int>(), dda.as<int>(),
+      ddb.as<int>(), dnext.as<int>(), dhead.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
+  count_launch(5);
+  ORB_CUDA_TRY(cudaGetLastError());
+  ORB_CUDA_TRY(cudaMemcpy(match12, dmatch.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
 }
 
 int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const OrbKeyPoint* kr,

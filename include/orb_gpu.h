@@ -187,6 +187,54 @@ int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int n
                             int device, uint8_t* kp_blocked, int32_t* match_of_kp,
                             int32_t* match_of_query, int* nmatches);
 
+/* One source feature of a search over equal vocabulary nodes: feature `index` of frame 1 is compared with the
+ * features cand[begin .. end) of frame 2 (the index list of the same DBoW2 node, in its insertion order).  The
+ * caller emits the rows in the reference's visiting order (nodes ascending, then the node's list order) and
+ * drops the features the reference skips before the inner loop (no / bad map point, :194-200, :559-563,
+ * :699-709). */
+typedef struct OrbBucketQuery {
+  int32_t index, begin, end;
+} OrbBucketQuery;
+
+/* Replaces the loops of
+ *   ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)       src/ORBmatcher.cc:159-288
+ *   ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)    src/ORBmatcher.cc:522-655
+ * (top-2 inside the node, accept best <= th_accept and (float)best < nnratio * (float)second, second = 256
+ * when alone; the chosen feature of frame 2 is claimed, :209/:576; rotation histogram :268-285).
+ * th_accept = ORB_GPU_TH_LOW for the first form and ORB_GPU_TH_LOW - 1 for the second (strict '<', :598).
+ * skip2[n2] (optional): features of frame 2 that are never candidates (no / bad map point, :576-580).
+ * match12[n1] = feature of frame 2 matched to feature i of frame 1 or -1; match21[n2] the inverse.  Host
+ * pointers. */
+int orb_gpu_search_by_bow(const OrbBucketQuery* q, int nq, const int32_t* cand2, int ncand2,
+                          const OrbKeyPoint* kps1, const uint8_t* desc1, int n1,
+                          const OrbKeyPoint* kps2, const uint8_t* desc2, const uint8_t* skip2, int n2,
+                          float nnratio, int th_accept, int check_orientation, int device,
+                          int32_t* match12, int32_t* match21, int* nmatches);
+
+/* Replaces the loops of ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823) including
+ * CheckDistEpipolarLine (:138-157).  u_right1/2 optional (NULL = monocular, all < 0); skip2[n2] = feature of
+ * frame 2 already has a map point (:722-726); F12 row-major 3x3; (ex, ey) the epipole in image 2 (:663-670);
+ * scale_factors2 / level_sigma2_2 of key frame 2.  The caller drops sources with a map point and, with
+ * only_stereo, the monocular ones (:699-709).  match12[n1] = feature of frame 2 or -1. */
+int orb_gpu_search_for_triangulation(const OrbBucketQuery* q, int nq, const int32_t* cand2, int ncand2,
+                                     const OrbKeyPoint* kps1, const uint8_t* desc1,
+                                     const float* u_right1, int n1, const OrbKeyPoint* kps2,
+                                     const uint8_t* desc2, const float* u_right2,
+                                     const uint8_t* skip2, int n2, const float* F12, float ex, float ey,
+                                     const float* scale_factors2, const float* level_sigma2_2,
+                                     int nlevels, int only_stereo, int check_orientation, int device,
+                                     int32_t* match12, int* nmatches);
+
+/* Replaces ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) up to :511: level-0 sources, a
+ * `window`-pixel box around prev_matched[i] = (x, y) in frame 2's grid, top-2 from INT_MAX, per-target best
+ * distance table with steal-back, rotation histogram.  match12[n1] = index in frame 2 or -1; the caller updates
+ * vbPrevMatched from it (:514-517). */
+int orb_gpu_search_for_initialization(const OrbKeyPoint* kps1, const uint8_t* desc1, int n1,
+                                      const float* prev_matched, const OrbKeyPoint* kps2,
+                                      const uint8_t* desc2, int n2, OrbFrameGrid grid2, int window,
+                                      float nnratio, int check_orientation, int device,
+                                      int32_t* match12, int* nmatches);
+
 /* Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): for each left keypoint
  * the best right keypoint in its row band within the disparity and octave gates.
  * best_idx_r[nl] = right index or -1, best_dist[nl] = distance (th_high when none). */

@@ -182,6 +182,51 @@ int orbo_search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, con
                          check_orientation != 0, kp_blocked, match_of_kp, match_of_query);
 }
 
+static FeatVec mk_fv(const int32_t* node, const int32_t* start, const int32_t* idx, int n) {
+  FeatVec f; f.node = node; f.start = start; f.idx = idx; f.n_nodes = n; return f;
+}
+
+int orbo_search_by_bow_frame(const int32_t* node1, const int32_t* start1, const int32_t* idx1, int nn1,
+                             const int32_t* node2, const int32_t* start2, const int32_t* idx2, int nn2,
+                             const KeyPoint* kps1, const uint8_t* d1, const uint8_t* good1, int n1,
+                             const KeyPoint* kps2, const uint8_t* d2, int n2, float nnratio, int check_ori,
+                             int32_t* match_of_2) {
+  return search_by_bow_frame(mk_fv(node1, start1, idx1, nn1), mk_fv(node2, start2, idx2, nn2), kps1, d1, good1, n1,
+                             kps2, d2, n2, nnratio, check_ori != 0, match_of_2);
+}
+
+int orbo_search_by_bow_keyframes(const int32_t* node1, const int32_t* start1, const int32_t* idx1, int nn1,
+                                 const int32_t* node2, const int32_t* start2, const int32_t* idx2, int nn2,
+                                 const KeyPoint* kps1, const uint8_t* d1, const uint8_t* good1, int n1,
+                                 const KeyPoint* kps2, const uint8_t* d2, const uint8_t* good2, int n2,
+                                 float nnratio, int check_ori, int32_t* match12) {
+  return search_by_bow_keyframes(mk_fv(node1, start1, idx1, nn1), mk_fv(node2, start2, idx2, nn2), kps1, d1, good1,
+                                 n1, kps2, d2, good2, n2, nnratio, check_ori != 0, match12);
+}
+
+int orbo_search_for_triangulation(const int32_t* node1, const int32_t* start1, const int32_t* idx1, int nn1,
+                                  const int32_t* node2, const int32_t* start2, const int32_t* idx2, int nn2,
+                                  const KeyPoint* kps1, const uint8_t* d1, const float* ur1, const uint8_t* has1,
+                                  int n1, const KeyPoint* kps2, const uint8_t* d2, const float* ur2,
+                                  const uint8_t* has2, int n2, const float* F12, float ex, float ey,
+                                  const float* sf2, const float* sigma2_2, int only_stereo, int check_ori,
+                                  int32_t* match12) {
+  return search_for_triangulation(mk_fv(node1, start1, idx1, nn1), mk_fv(node2, start2, idx2, nn2), kps1, d1, ur1,
+                                  has1, n1, kps2, d2, ur2, has2, n2, F12, ex, ey, sf2, sigma2_2, only_stereo != 0,
+                                  check_ori != 0, match12);
+}
+
+int orbo_search_for_initialization(const KeyPoint* kps1, const uint8_t* d1, int n1, const float* prev_matched,
+                                   const KeyPoint* kps2, const uint8_t* d2, int n2, float minX, float minY,
+                                   float invW, float invH, int window, float nnratio, int check_ori,
+                                   int32_t* match12) {
+  FrameGrid g;
+  g.minX = minX; g.minY = minY; g.invW = invW; g.invH = invH;
+  g.build(kps2, n2);
+  return search_for_initialization(kps1, d1, n1, prev_matched, kps2, d2, n2, g, window, nnratio, check_ori != 0,
+                                   match12);
+}
+
 // candidate list of one GetFeaturesInArea query, in the reference's order
 int orbo_features_in_area(const KeyPoint* kps, int nk, float minX, float minY, float invW,
                           float invH, float x, float y, float r, int minLevel, int maxLevel,

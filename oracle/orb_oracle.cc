@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <climits>
 #include <cmath>
 #include <cstring>
 
@@ -570,6 +571,200 @@ int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const Ke
       for (int i = 0; i < nq; ++i)
         if (match_of_query[i] >= 0 && match_of_kp[match_of_query[i]] == -2) match_of_query[i] = -1;
   }
+  return nmatches;
+}
+
+namespace {
+const int kThLow = 50;  // ORBmatcher::TH_LOW (src/ORBmatcher.cc:37)
+const int kHistoLength = 30;  // ORBmatcher::HISTO_LENGTH (:39)
+
+inline int rot_bin(float a1, float a2) {  // :240-247 and its copies
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)std::round(rot * (1.0f / kHistoLength));
+  if (bin == kHistoLength) bin = 0;
+  return bin;
+}
+
+// the two-iterator walk over equal node ids (:178-266); lower_bound on a std::map == advance to first >= key
+template <class Fn>
+void for_equal_nodes(const FeatVec& a, const FeatVec& b, Fn fn) {
+  int ia = 0, ib = 0;
+  while (ia < a.n_nodes && ib < b.n_nodes) {
+    if (a.node[ia] == b.node[ib]) { fn(ia, ib); ++ia; ++ib; }
+    else if (a.node[ia] < b.node[ib]) { while (ia < a.n_nodes && a.node[ia] < b.node[ib]) ++ia; }
+    else { while (ib < b.n_nodes && b.node[ib] < a.node[ia]) ++ib; }
+  }
+}
+
+// prune every bin but the three maxima; calls drop(element) for the pruned entries, returns how many
+template <class Fn>
+int prune_rotation(std::vector<int>* rotHist, Fn drop) {
+  int ind1 = -1, ind2 = -1, ind3 = -1, sizes[kHistoLength], n = 0;
+  for (int i = 0; i < kHistoLength; ++i) sizes[i] = (int)rotHist[i].size();
+  compute_three_maxima(sizes, kHistoLength, ind1, ind2, ind3);
+  for (int i = 0; i < kHistoLength; ++i) {
+    if (i == ind1 || i == ind2 || i == ind3) continue;
+    for (int e : rotHist[i]) n += drop(e);
+  }
+  return n;
+}
+}  // namespace
+
+int search_by_bow_frame(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                        const uint8_t* good_mp1, int n1, const KeyPoint* kps2, const uint8_t* d2, int n2,
+                        float nnratio, bool check_orientation, int32_t* match_of_2) {
+  (void)n1;
+  for (int i = 0; i < n2; ++i) match_of_2[i] = -1;
+  int nmatches = 0;
+  std::vector<int> rotHist[kHistoLength];
+  for_equal_nodes(fv1, fv2, [&](int a, int b) {
+    for (int iKF = fv1.start[a]; iKF < fv1.start[a + 1]; ++iKF) {
+      const int realIdxKF = fv1.idx[iKF];
+      if (!good_mp1[realIdxKF]) continue;  // :194-200
+      int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+      for (int iF = fv2.start[b]; iF < fv2.start[b + 1]; ++iF) {
+        const int realIdxF = fv2.idx[iF];
+        if (match_of_2[realIdxF] >= 0) continue;  // :209
+        const int dist = descriptor_distance(d1 + (size_t)realIdxKF * 32, d2 + (size_t)realIdxF * 32);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+        else if (dist < bestDist2) { bestDist2 = dist; }
+      }
+      if (bestDist1 <= kThLow && (float)bestDist1 < nnratio * (float)bestDist2) {  // :228-230
+        match_of_2[bestIdxF] = realIdxKF;
+        if (check_orientation) rotHist[rot_bin(kps1[realIdxKF].angle, kps2[bestIdxF].angle)].push_back(bestIdxF);
+        ++nmatches;
+      }
+    }
+  });
+  if (check_orientation)
+    nmatches -= prune_rotation(rotHist, [&](int idxF) { match_of_2[idxF] = -1; return 1; });  // :268-285
+  return nmatches;
+}
+
+int search_by_bow_keyframes(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                            const uint8_t* good_mp1, int n1, const KeyPoint* kps2, const uint8_t* d2,
+                            const uint8_t* good_mp2, int n2, float nnratio, bool check_orientation,
+                            int32_t* match12) {
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  std::vector<uint8_t> matched2((size_t)n2, 0);
+  int nmatches = 0;
+  std::vector<int> rotHist[kHistoLength];
+  for_equal_nodes(fv1, fv2, [&](int a, int b) {
+    for (int i1 = fv1.start[a]; i1 < fv1.start[a + 1]; ++i1) {
+      const int idx1 = fv1.idx[i1];
+      if (!good_mp1[idx1]) continue;  // :559-563
+      int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+      for (int i2 = fv2.start[b]; i2 < fv2.start[b + 1]; ++i2) {
+        const int idx2 = fv2.idx[i2];
+        if (matched2[idx2] || !good_mp2[idx2]) continue;  // :576-580
+        const int dist = descriptor_distance(d1 + (size_t)idx1 * 32, d2 + (size_t)idx2 * 32);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = idx2; }
+        else if (dist < bestDist2) { bestDist2 = dist; }
+      }
+      if (bestDist1 < kThLow && (float)bestDist1 < nnratio * (float)bestDist2) {  // :598-600 (strict)
+        match12[idx1] = bestIdx2;
+        matched2[bestIdx2] = 1;
+        if (check_orientation) rotHist[rot_bin(kps1[idx1].angle, kps2[bestIdx2].angle)].push_back(idx1);
+        ++nmatches;
+      }
+    }
+  });
+  if (check_orientation)
+    nmatches -= prune_rotation(rotHist, [&](int idx1) { match12[idx1] = -1; return 1; });  // :634-652
+  return nmatches;
+}
+
+static bool check_dist_epipolar_line(const KeyPoint& kp1, const KeyPoint& kp2, const float* F12,
+                                     const float* level_sigma2_2) {  // :138-157
+  const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+  const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+  const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+  const float num = a * kp2.x + b * kp2.y + c;
+  const float den = a * a + b * b;
+  if (den == 0) return false;
+  const float dsqr = num * num / den;
+  return dsqr < 3.84 * level_sigma2_2[kp2.octave];
+}
+
+int search_for_triangulation(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                             const float* ur1, const uint8_t* has_mp1, int n1, const KeyPoint* kps2,
+                             const uint8_t* d2, const float* ur2, const uint8_t* has_mp2, int n2,
+                             const float* F12, float ex, float ey, const float* scale_factors2,
+                             const float* level_sigma2_2, bool only_stereo, bool check_orientation,
+                             int32_t* match12) {
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  std::vector<uint8_t> matched2((size_t)n2, 0);  // never set by the reference (:677), kept for the gate at :724
+  int nmatches = 0;
+  std::vector<int> rotHist[kHistoLength];
+  for_equal_nodes(fv1, fv2, [&](int a, int b) {
+    for (int i1 = fv1.start[a]; i1 < fv1.start[a + 1]; ++i1) {
+      const int idx1 = fv1.idx[i1];
+      if (has_mp1[idx1]) continue;  // :699-703
+      const bool bStereo1 = ur1 && ur1[idx1] >= 0;
+      if (only_stereo && !bStereo1) continue;
+      const KeyPoint& kp1 = kps1[idx1];
+      int bestDist = kThLow, bestIdx2 = -1;
+      for (int i2 = fv2.start[b]; i2 < fv2.start[b + 1]; ++i2) {
+        const int idx2 = fv2.idx[i2];
+        if (matched2[idx2] || has_mp2[idx2]) continue;
+        const bool bStereo2 = ur2 && ur2[idx2] >= 0;
+        if (only_stereo && !bStereo2) continue;
+        const int dist = descriptor_distance(d1 + (size_t)idx1 * 32, d2 + (size_t)idx2 * 32);
+        if (dist > kThLow || dist > bestDist) continue;  // :737 (an equal distance replaces the best)
+        const KeyPoint& kp2 = kps2[idx2];
+        if (!bStereo1 && !bStereo2) {
+          const float distex = ex - kp2.x, distey = ey - kp2.y;
+          if (distex * distex + distey * distey < 100 * scale_factors2[kp2.octave]) continue;  // :742-748
+        }
+        if (check_dist_epipolar_line(kp1, kp2, F12, level_sigma2_2)) { bestIdx2 = idx2; bestDist = dist; }
+      }
+      if (bestIdx2 >= 0) {
+        match12[idx1] = bestIdx2;
+        ++nmatches;
+        if (check_orientation) rotHist[rot_bin(kp1.angle, kps2[bestIdx2].angle)].push_back(idx1);
+      }
+    }
+  });
+  if (check_orientation)
+    nmatches -= prune_rotation(rotHist, [&](int idx1) { match12[idx1] = -1; return 1; });  // :790-808
+  return nmatches;
+}
+
+int search_for_initialization(const KeyPoint* kps1, const uint8_t* d1, int n1, const float* prev_matched,
+                              const KeyPoint* kps2, const uint8_t* d2, int n2, const FrameGrid& grid2,
+                              int window, float nnratio, bool check_orientation, int32_t* match12) {
+  int nmatches = 0;
+  for (int i = 0; i < n1; ++i) match12[i] = -1;
+  std::vector<int> rotHist[kHistoLength];
+  std::vector<int> vMatchedDistance((size_t)n2, INT_MAX), vnMatches21((size_t)n2, -1);
+  std::vector<int> cand;
+  for (int i1 = 0; i1 < n1; ++i1) {
+    const int level1 = kps1[i1].octave;
+    if (level1 > 0) continue;  // :421-423
+    grid2.features_in_area(kps2, prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window, level1, level1, cand);
+    if (cand.empty()) continue;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int i2 : cand) {
+      const int dist = descriptor_distance(d1 + (size_t)i1 * 32, d2 + (size_t)i2 * 32);
+      if (vMatchedDistance[i2] <= dist) continue;  // :444-445
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) { bestDist2 = dist; }
+    }
+    if (bestDist <= kThLow && bestDist < (float)bestDist2 * nnratio) {  // :459-461
+      if (vnMatches21[bestIdx2] >= 0) { match12[vnMatches21[bestIdx2]] = -1; --nmatches; }  // steal-back :463-467
+      match12[i1] = bestIdx2;
+      vnMatches21[bestIdx2] = i1;
+      vMatchedDistance[bestIdx2] = bestDist;
+      ++nmatches;
+      if (check_orientation) rotHist[rot_bin(kps1[i1].angle, kps2[bestIdx2].angle)].push_back(i1);
+    }
+  }
+  if (check_orientation)
+    nmatches -= prune_rotation(rotHist, [&](int idx1) {  // :486-509: entries stolen earlier are already -1
+      if (match12[idx1] >= 0) { match12[idx1] = -1; return 1; }
+      return 0;
+    });
   return nmatches;
 }
 

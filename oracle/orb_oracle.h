@@ -126,6 +126,44 @@ int search_windowed(const WindowQuery* q, const uint8_t* qdesc, int nq, const Ke
                     int th_accept, int gate, const float* inv_level_sigma2, bool check_orientation,
                     uint8_t* kp_blocked, int32_t* match_of_kp, int32_t* match_of_query);
 
+// DBoW2::FeatureVector as flat arrays: node ids ascending (std::map order), start[n_nodes + 1] into idx[]
+// (the feature indices of a node in insertion order, Thirdparty/DBoW2/DBoW2/FeatureVector.cpp:28-41).
+struct FeatVec {
+  const int32_t* node;
+  const int32_t* start;
+  const int32_t* idx;
+  int n_nodes;
+};
+
+// M6: ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (src/ORBmatcher.cc:159-288).  good_mp1[i]: key-frame
+// feature i holds a map point that is not bad (:194-200).  match_of_2[n2] = key-frame feature whose map
+// point the frame feature received, or -1.  Returns nmatches.
+int search_by_bow_frame(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                        const uint8_t* good_mp1, int n1, const KeyPoint* kps2, const uint8_t* d2, int n2,
+                        float nnratio, bool check_orientation, int32_t* match_of_2);
+
+// M6: ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...) (:522-655): strict best < TH_LOW (:598).
+// match12[n1] = feature of key frame 2 or -1.
+int search_by_bow_keyframes(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                            const uint8_t* good_mp1, int n1, const KeyPoint* kps2, const uint8_t* d2,
+                            const uint8_t* good_mp2, int n2, float nnratio, bool check_orientation,
+                            int32_t* match12);
+
+// M6: ORBmatcher::SearchForTriangulation (:657-823) with CheckDistEpipolarLine (:138-157).  has_mp*: the
+// feature already has a map point (:699-703, :722-726); F12 row-major 3x3; (ex, ey) the epipole (:663-670).
+int search_for_triangulation(const FeatVec& fv1, const FeatVec& fv2, const KeyPoint* kps1, const uint8_t* d1,
+                             const float* ur1, const uint8_t* has_mp1, int n1, const KeyPoint* kps2,
+                             const uint8_t* d2, const float* ur2, const uint8_t* has_mp2, int n2,
+                             const float* F12, float ex, float ey, const float* scale_factors2,
+                             const float* level_sigma2_2, bool only_stereo, bool check_orientation,
+                             int32_t* match12);
+
+// M7: ORBmatcher::SearchForInitialization (:405-520).  prev_matched[2*i] = (x, y) of vbPrevMatched[i]
+// (not updated here; the caller applies :514-517).  match12[n1] = index in frame 2 or -1.
+int search_for_initialization(const KeyPoint* kps1, const uint8_t* d1, int n1, const float* prev_matched,
+                              const KeyPoint* kps2, const uint8_t* d2, int n2, const FrameGrid& grid2,
+                              int window, float nnratio, bool check_orientation, int32_t* match12);
+
 // M10: Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549).
 // best_idx_r[i] = right index or -1; best_dist[i] = distance (TH_HIGH if none).
 void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint* kr,

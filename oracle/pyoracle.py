@@ -252,6 +252,82 @@ def search_windowed(queries, qdesc, kps, kdesc, u_right, grid, th_accept, gate, 
     return n, out, blocked, outq
 
 
+def flatten_feat_vec(fv):
+    """{node id: [feature indices]} -> (node ids ascending, start[n+1], flat indices), int32: the iteration order of
+    the std::map behind DBoW2::FeatureVector."""
+    nodes = sorted(fv)
+    start = np.zeros(len(nodes) + 1, np.int32)
+    for i, nd in enumerate(nodes):
+        start[i + 1] = start[i] + len(fv[nd])
+    idx = np.fromiter((j for nd in nodes for j in fv[nd]), np.int32, count=int(start[-1]))
+    return np.asarray(nodes, np.int32), start, idx
+
+
+def _fv_args(fv):
+    node, start, idx = flatten_feat_vec(fv)
+    return (node, start, idx), (_p(node), _p(start), _p(idx), len(node))
+
+
+def search_by_bow_frame(fv1, fv2, kps1, d1, good_mp1, kps2, d2, nnratio, check_orientation):
+    """M6 SearchByBoW(KF, Frame) -> nmatches, match_of_2[n2] (key-frame feature index or -1)"""
+    k1, a1 = _fv_args(fv1)
+    k2, a2 = _fv_args(fv2)
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    d1 = u8c(d1); d2 = u8c(d2)
+    g1 = np.ascontiguousarray(good_mp1, np.uint8)
+    out = np.empty(len(kps2), np.int32)
+    n = lib().orbo_search_by_bow_frame(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), len(kps2),
+                                       C.c_float(nnratio), int(bool(check_orientation)), _p(out))
+    return n, out
+
+
+def search_by_bow_keyframes(fv1, fv2, kps1, d1, good_mp1, kps2, d2, good_mp2, nnratio, check_orientation):
+    """M6 SearchByBoW(KF, KF) -> nmatches, match12[n1]"""
+    k1, a1 = _fv_args(fv1)
+    k2, a2 = _fv_args(fv2)
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    d1 = u8c(d1); d2 = u8c(d2)
+    g1 = np.ascontiguousarray(good_mp1, np.uint8); g2 = np.ascontiguousarray(good_mp2, np.uint8)
+    out = np.empty(len(kps1), np.int32)
+    n = lib().orbo_search_by_bow_keyframes(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), _p(g2),
+                                           len(kps2), C.c_float(nnratio), int(bool(check_orientation)), _p(out))
+    return n, out
+
+
+def search_for_triangulation(fv1, fv2, kps1, d1, ur1, has_mp1, kps2, d2, ur2, has_mp2, F12, ex, ey, scale_factors2,
+                             level_sigma2_2, only_stereo, check_orientation):
+    """M6 SearchForTriangulation -> nmatches, match12[n1]"""
+    k1, a1 = _fv_args(fv1)
+    k2, a2 = _fv_args(fv2)
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    d1 = u8c(d1); d2 = u8c(d2)
+    h1 = np.ascontiguousarray(has_mp1, np.uint8); h2 = np.ascontiguousarray(has_mp2, np.uint8)
+    u1 = None if ur1 is None else np.ascontiguousarray(ur1, np.float32)
+    u2 = None if ur2 is None else np.ascontiguousarray(ur2, np.float32)
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf = np.ascontiguousarray(scale_factors2, np.float32)
+    sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+    out = np.empty(len(kps1), np.int32)
+    n = lib().orbo_search_for_triangulation(*a1, *a2, _p(kps1), _p(d1), _p(u1), _p(h1), len(kps1), _p(kps2), _p(d2),
+                                            _p(u2), _p(h2), len(kps2), _p(F), C.c_float(ex), C.c_float(ey), _p(sf),
+                                            _p(sg), int(bool(only_stereo)), int(bool(check_orientation)), _p(out))
+    return n, out
+
+
+def search_for_initialization(kps1, d1, prev_matched, kps2, d2, grid, window, nnratio, check_orientation):
+    """M7 SearchForInitialization -> nmatches, match12[n1] (vbPrevMatched is left to the caller)"""
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    d1 = u8c(d1); d2 = u8c(d2)
+    pm = np.ascontiguousarray(prev_matched, np.float32).reshape(-1)
+    assert len(pm) == 2 * len(kps1)
+    out = np.empty(len(kps1), np.int32)
+    n = lib().orbo_search_for_initialization(_p(kps1), _p(d1), len(kps1), _p(pm), _p(kps2), _p(d2), len(kps2),
+                                             C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
+                                             C.c_float(grid[3]), int(window), C.c_float(nnratio),
+                                             int(bool(check_orientation)), _p(out))
+    return n, out
+
+
 def features_in_area(kps, grid, x, y, r, min_level, max_level):
     kps = np.ascontiguousarray(kps, KP_DTYPE)
     out = np.empty(len(kps) + 1, np.int32)

@@ -126,3 +126,68 @@ def test_matcher_oracle_small(oracle):
     dist = np.unpackbits(q[:, None, :] ^ db[None, :, :], axis=2).sum(2)
     assert np.array_equal(best, dist.min(1)) and np.array_equal(idx, dist.argmin(1))
     assert np.array_equal(second, np.sort(dist, 1)[:, 1])
+
+
+def _kp(oracle, xs, ys, octave=0, angle=0.0):
+    k = np.zeros(len(xs), oracle.KP_DTYPE)
+    k["x"], k["y"], k["octave"], k["angle"] = xs, ys, octave, angle
+    return k
+
+
+def test_oracle_initialization_steal_back(oracle):
+    """Hand cases of SearchForInitialization (src/ORBmatcher.cc:405-520): a later source takes a target only when
+    strictly closer (:444-445); the earlier source is un-matched (:463-467); level > 0 sources never match."""
+    rng = np.random.default_rng(3)
+    target = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    grid = (0.0, 0.0, np.float32(0.1), np.float32(0.1))
+    k2 = _kp(oracle, [100.0], [100.0])
+    k1 = _kp(oracle, [100.0, 101.0, 99.0], [100.0, 100.0, 101.0])
+    prev = np.stack([k1["x"], k1["y"]], 1)
+    for flips, want in (([10, 5, 20], [-1, 0, -1]), ([10, 10, 12], [0, -1, -1]), ([30, 20, 10], [-1, -1, 0]),
+                        ([51, 50, 50], [-1, 0, -1])):
+        d1 = synth.flip_bits(np.repeat(target, 3, 0), flips, rng)
+        n, m12 = oracle.search_for_initialization(k1, d1, prev, k2, target, grid, 100, 0.9, False)
+        assert m12.tolist() == want and n == 1
+    k1["octave"] = [1, 0, 2]
+    d1 = synth.flip_bits(np.repeat(target, 3, 0), [0, 40, 0], rng)
+    n, m12 = oracle.search_for_initialization(k1, d1, prev, k2, target, grid, 100, 0.9, False)
+    assert m12.tolist() == [-1, 0, -1]
+
+
+def test_oracle_bow_claims_and_ratio(oracle):
+    """SearchByBoW hand cases (:159-288, :522-655): a claimed frame feature is invisible to later sources of the
+    node (:209); the ratio test is strict and uses 256 when the node holds one candidate (:230)."""
+    rng = np.random.default_rng(4)
+    base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    d2 = synth.flip_bits(np.repeat(base, 2, 0), [0, 30], rng)          # two frame features in node 3
+    d1 = synth.flip_bits(np.repeat(base, 2, 0), [2, 1], rng)           # both sources prefer frame feature 0
+    k = _kp(oracle, [0.0, 0.0], [0.0, 0.0])
+    fv = {3: [0, 1]}
+    n, m21 = oracle.search_by_bow_frame(fv, fv, k, d1, [1, 1], k, d2, 0.9, False)
+    # source 0 takes feature 0 (2 < 0.9 * ~30); source 1 then only sees feature 1, alone in the node: vs 256
+    assert n == 2 and m21.tolist() == [0, 1]
+    n, m21 = oracle.search_by_bow_frame(fv, fv, k, d1, [0, 1], k, d2, 0.9, False)
+    assert n == 1 and m21.tolist() == [1, -1]
+    n, m21 = oracle.search_by_bow_frame(fv, {4: [0, 1]}, k, d1, [1, 1], k, d2, 0.9, False)
+    assert n == 0
+    # ratio: best 2 vs second ~30 passes at 0.9 but not at 0.05
+    n, _ = oracle.search_by_bow_frame(fv, fv, k, d1, [1, 0], k, d2, 0.05, False)
+    assert n == 0
+
+
+def test_oracle_triangulation_tie_goes_to_last(oracle):
+    """SearchForTriangulation :737 skips only dist > bestDist, so an equal distance later in the node wins."""
+    rng = np.random.default_rng(5)
+    base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    d2 = synth.flip_bits(np.repeat(base, 3, 0), [7, 7, 9], rng)
+    k1 = _kp(oracle, [50.0], [60.0])
+    k2 = _kp(oracle, [10.0, 20.0, 30.0], [60.0, 60.0, 60.0])
+    F = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    one = np.ones(8, np.float32)
+    n, m12 = oracle.search_for_triangulation({1: [0]}, {1: [0, 1, 2]}, k1, base, None, [0], k2, d2, None, [0, 0, 0], F,
+                                             1e6, 1e6, one, one, False, False)
+    assert n == 1 and m12.tolist() == [1]
+    k2["y"][1] = 63.0   # off the epipolar line: 9 > 3.84
+    n, m12 = oracle.search_for_triangulation({1: [0]}, {1: [0, 1, 2]}, k1, base, None, [0], k2, d2, None, [0, 0, 0], F,
+                                             1e6, 1e6, one, one, False, False)
+    assert m12.tolist() == [0]
