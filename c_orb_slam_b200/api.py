@@ -35,7 +35,8 @@ EXPORTS = [
     "orb_gpu_get_candidates", "orb_gpu_hamming_pairs_device", "orb_gpu_match_bruteforce_device",
     "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
     "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_search_by_bow",
-    "orb_gpu_search_for_triangulation", "orb_gpu_search_for_initialization", "orb_gpu_stereo_match", "orb_gpu_version", "orb_gpu_last_error",
+    "orb_gpu_search_for_triangulation", "orb_gpu_search_for_initialization", "orb_gpu_stereo_match",
+    "orb_gpu_compute_stereo_matches", "orb_gpu_stereo_matches_device", "orb_gpu_version", "orb_gpu_last_error",
     "orb_gpu_launch_count", "orb_gpu_popc_peak",
 ]
 
@@ -111,6 +112,9 @@ def lib():
                                                        vp, vp, ci, ci, ci, ci, vp, C.POINTER(ci)]
         L.orb_gpu_search_for_initialization.argtypes = [vp, vp, ci, vp, vp, vp, ci, _Grid, ci, cf, ci, ci, vp,
                                                         C.POINTER(ci)]
+        L.orb_gpu_compute_stereo_matches.argtypes = [vp, ci, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, vp, vp]
+        L.orb_gpu_stereo_matches_device.argtypes = [vp, ci, ci, vp, ci, ci, ci, vp, vp, vp, ci, vp, vp, vp, ci, cf, cf,
+                                                    vp, vp, vp, vp]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -419,6 +423,17 @@ class ORBmatcher:
         prev_matched[hit, 0] = k2["x"][m12[hit]]
         prev_matched[hit, 1] = k2["y"][m12[hit]]
         return n.value, m12
+
+    def ComputeStereoMatches(self, ex_left, ex_right, kps_l, desc_l, kps_r, desc_r, bf, b, frame_l=0, frame_r=0):
+        """Frame::ComputeStereoMatches (src/Frame.cc:466-640) on the pyramids the two ORBextractor objects kept on
+        the device from their last call.  -> mvuRight [nl], mvDepth [nl] (float32, -1 = no match)"""
+        kl = np.ascontiguousarray(kps_l, KP_DTYPE); dl = np.ascontiguousarray(desc_l, np.uint8)
+        kr = np.ascontiguousarray(kps_r, KP_DTYPE); dr = np.ascontiguousarray(desc_r, np.uint8)
+        ur = np.empty(len(kl), np.float32); dp = np.empty(len(kl), np.float32)
+        _check(lib().orb_gpu_compute_stereo_matches(ex_left._h, frame_l, ex_right._h, frame_r, _p(kl), _p(dl), len(kl),
+                                                    _p(kr), _p(dr), len(kr), float(bf), float(b), _p(ur), _p(dp)),
+               "orb_gpu_compute_stereo_matches")
+        return ur, dp
 
     def stereo_match(self, kps_l, desc_l, kps_r, desc_r, n_rows, scale_factors, min_d, max_d):
         """Hamming stage of Frame::ComputeStereoMatches (Frame.cc:466-549) -> best_idx_r, best_dist."""

@@ -145,6 +145,23 @@ int StereoHammingMatches(const FrameT& F, int nRows, float minD, float maxD, std
                               device, bestIdxR.data(), bestDist.data());
 }
 
+// Frame::ComputeStereoMatches (src/Frame.cc:466-640) whole -- Hamming stage, sub-pixel refinement on the
+// pyramids both extractors kept on the device, median filter.  With this the extractors can run with
+// mbDownloadPyramid = false: no image returns to the host for stereo.
+template <class FrameT>
+void ComputeStereoMatches(FrameT& F) {
+  const int nl = F.N, nr = (int)F.mvKeysRight.size();
+  F.mvuRight.assign(nl, -1.0f);
+  F.mvDepth.assign(nl, -1.0f);
+  std::vector<uint8_t> dl((size_t)nl * 32), dr((size_t)nr * 32);
+  for (int i = 0; i < nl; ++i) std::memcpy(&dl[(size_t)i * 32], F.mDescriptors.ptr(i), 32);
+  for (int i = 0; i < nr; ++i) std::memcpy(&dr[(size_t)i * 32], F.mDescriptorsRight.ptr(i), 32);
+  orb_gpu_compute_stereo_matches(F.mpORBextractorLeft->Handle(), 0, F.mpORBextractorRight->Handle(), 0,
+                                 reinterpret_cast<const OrbKeyPoint*>(F.mvKeys.data()), dl.data(), nl,
+                                 reinterpret_cast<const OrbKeyPoint*>(F.mvKeysRight.data()), dr.data(), nr, F.mbf,
+                                 F.mb, F.mvuRight.data(), F.mvDepth.data());
+}
+
 }  // namespace gpu
 }  // namespace ORB_SLAM2
 #endif  // ORBMATCHER_GPU_H

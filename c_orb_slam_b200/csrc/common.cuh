@@ -68,6 +68,25 @@ struct Scratch {
   int* status;         // [1] sticky device-side status (0 or ORB_GPU_ERR_CAPACITY)
 };
 
+// One side of a batch of stereo pairs (stereo_kernels.cu): the unblurred pyramid an extractor left in HBM and
+// the keypoints / descriptors of its frames.  Pair i reads image frame img_frame0 + i*img_frame_step and the
+// keypoint arrays of frame kp_frame0 + i*kp_frame_step ([frame][capacity] layout, n[frame] valid entries).
+struct StereoSide {
+  const uint8_t* img[kMaxLevels];
+  long long frame_stride[kMaxLevels];
+  int pitch[kMaxLevels], w[kMaxLevels], h[kMaxLevels];
+  int img_frame0, img_frame_step, kp_frame0, kp_frame_step;
+  const OrbKeyPoint* kps;
+  const uint8_t* desc;
+  const int* n;
+  int capacity;
+};
+struct StereoParams {
+  float scale[kMaxLevels], inv_scale[kMaxLevels];  // mvScaleFactors / mvInvScaleFactors of the left extractor
+  float min_d, max_d, bf;                          // Frame.cc:496-498; mbf
+  int n_rows;                                      // mvImagePyramid[0].rows (:473)
+};
+
 void count_launch(int n = 1);
 void set_last_error(const char* what, cudaError_t e);
 
@@ -89,6 +108,8 @@ int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoin
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s);
 int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int level, float* d_xyr,
                              int cap, cudaStream_t s);
+int launch_stereo_pairs(const StereoSide& L, const StereoSide& R, const StereoParams& P, int npairs,
+                        int max_left, float* d_u_right, float* d_depth, int* d_sad, cudaStream_t s);
 int upload_constants();
 size_t quadtree_smem_bytes(const Plan& p, int level);
 

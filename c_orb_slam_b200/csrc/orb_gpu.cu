@@ -564,4 +564,109 @@ int orb_gpu_get_candidates(OrbGpuExtractor* h, int frame, int level, float* xyr,
   return rc;
 }
 
+// ---- Frame::ComputeStereoMatches on the pyramids of two extractors (stereo_kernels.cu) ------------
+static int fill_stereo_side(const OrbGpuExtractor* h, StereoSide& s) {
+  if (!h->have_result) return ORB_GPU_ERR_STATE;
+  for (int l = 0; l < kMaxLevels; ++l) {
+    const bool on = l < h->nlevels;
+    const LevelGeom& g = h->plan.lv[on ? l : 0];
+    s.img[l] = !on ? nullptr : (l == 0 ? h->last_l0 : g.img);
+    s.pitch[l] = !on ? 0 : (l == 0 ? h->last_l0_pitch : g.pitch);
+    s.frame_stride[l] = !on ? 0 : (l == 0 ? h->last_l0_stride : g.frame_stride);
+    s.w[l] = on ? g.w : 0;
+    s.h[l] = on ? g.h : 0;
+  }
+  return ORB_GPU_OK;
+}
+
+static int stereo_params(const OrbGpuExtractor* left, const OrbGpuExtractor* right, float bf, float b,
+                         StereoParams& P) {
+  if (left->nlevels != right->nlevels || left->plan.width != right->plan.width ||
+      left->plan.height != right->plan.height || left->scale_factor_f != right->scale_factor_f || !(b > 0))
+    return ORB_GPU_ERR_ARG;
+  for (int l = 0; l < kMaxLevels; ++l) {
+    P.scale[l] = l < left->nlevels ? left->scale[l] : 0.f;
+    P.inv_scale[l] = l < left->nlevels ? left->inv_scale[l] : 0.f;
+  }
+  P.min_d = 0.f;       // Frame.cc:497
+  P.max_d = bf / b;    // :498  (mbf/mb)
+  P.bf = bf;
+  P.n_rows = left->plan.height;   // mvImagePyramid[0].rows (:473)
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_stereo_matches_device(OrbGpuExtractor* left, int frame_l0, int frame_l_step, OrbGpuExtractor* right,
+                                  int frame_r0, int frame_r_step, int npairs, const OrbKeyPoint* d_kps_l,
+                                  const uint8_t* d_desc_l, const int* d_n_l, int capacity_l,
+                                  const OrbKeyPoint* d_kps_r, const uint8_t* d_desc_r, const int* d_n_r,
+                                  int capacity_r, float bf, float b, float* d_u_right, float* d_depth,
+                                  int* d_sad, void* stream) {
+  if (!left || !right || npairs < 1 || !d_kps_l || !d_desc_l || !d_n_l || !d_kps_r || !d_desc_r || !d_n_r ||
+      capacity_l < 1 || capacity_r < 1 || capacity_r > 65535 || !d_u_right || !d_depth || !d_sad)
+    return ORB_GPU_ERR_ARG;
+  const int last_l = frame_l0 + (npairs - 1) * frame_l_step, last_r = frame_r0 + (npairs - 1) * frame_r_step;
+  if (frame_l0 < 0 || frame_r0 < 0 || last_l < 0 || last_r < 0) return ORB_GPU_ERR_ARG;
+  StereoSide L, R;
+  StereoParams P;
+  int rc;
+  if ((rc = fill_stereo_side(left, L)) || (rc = fill_stereo_side(right, R)) ||
+      (rc = stereo_params(left, right, bf, b, P)))
+    return rc;
+  if (std::max(frame_l0, last_l) >= left->last_nframes || std::max(frame_r0, last_r) >= right->last_nframes)
+    return ORB_GPU_ERR_ARG;
+  L.img_frame0 = L.kp_frame0 = frame_l0; L.img_frame_step = L.kp_frame_step = frame_l_step;
+  R.img_frame0 = R.kp_frame0 = frame_r0; R.img_frame_step = R.kp_frame_step = frame_r_step;
+  L.kps = d_kps_l; L.desc = d_desc_l; L.n = d_n_l; L.capacity = capacity_l;
+  R.kps = d_kps_r; R.desc = d_desc_r; R.n = d_n_r; R.capacity = capacity_r;
+  ORB_CUDA_TRY(cudaSetDevice(left->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : left->stream;
+  return launch_stereo_pairs(L, R, P, npairs, capacity_l, d_u_right, d_depth, d_sad, s);
+}
+
+int orb_gpu_compute_stereo_matches(OrbGpuExtractor* left, int frame_l, OrbGpuExtractor* right, int frame_r,
+                                   const OrbKeyPoint* kps_l, const uint8_t* desc_l, int nl,
+                                   const OrbKeyPoint* kps_r, const uint8_t* desc_r, int nr, float bf, float b,
+                                   float* u_right, float* depth) {
+  if (!left || !right || nl < 0 || nr < 0 || nr > 65535 || (nl > 0 && (!kps_l || !desc_l || !u_right || !depth)) ||
+      (nr > 0 && (!kps_r || !desc_r)))
+    return ORB_GPU_ERR_ARG;
+  StereoSide L, R;
+  StereoParams P;
+  int rc;
+  if ((rc = fill_stereo_side(left, L)) || (rc = fill_stereo_side(right, R)) ||
+      (rc = stereo_params(left, right, bf, b, P)))
+    return rc;
+  if (frame_l < 0 || frame_l >= left->last_nframes || frame_r < 0 || frame_r >= right->last_nframes)
+    return ORB_GPU_ERR_ARG;
+  for (int i = 0; i < nl; ++i) { u_right[i] = -1.0f; depth[i] = -1.0f; }
+  if (nl == 0 || nr == 0) return ORB_GPU_OK;
+  ORB_CUDA_TRY(cudaSetDevice(left->device));
+  // both extractors may still be running on their own streams
+  ORB_CUDA_TRY(cudaStreamSynchronize(left->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(right->stream));
+  DevBuf kl, dl, kr, dr, nn, ur, dp, sad;
+  struct Free { DevBuf* b[8]; ~Free() { for (DevBuf* x : b) x->release(); } } guard{{&kl, &dl, &kr, &dr, &nn, &ur, &dp, &sad}};
+  if ((rc = kl.ensure((size_t)nl * sizeof(OrbKeyPoint))) || (rc = dl.ensure((size_t)nl * 32)) ||
+      (rc = kr.ensure((size_t)nr * sizeof(OrbKeyPoint))) || (rc = dr.ensure((size_t)nr * 32)) ||
+      (rc = nn.ensure(8)) || (rc = ur.ensure((size_t)nl * 4)) || (rc = dp.ensure((size_t)nl * 4)) ||
+      (rc = sad.ensure((size_t)nl * 4)))
+    return rc;
+  cudaStream_t s = left->stream;
+  const int counts[2] = {nl, nr};
+  ORB_CUDA_TRY(cudaMemcpyAsync(kl.p, kps_l, (size_t)nl * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice, s));
+  ORB_CUDA_TRY(cudaMemcpyAsync(dl.p, desc_l, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
+  ORB_CUDA_TRY(cudaMemcpyAsync(kr.p, kps_r, (size_t)nr * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice, s));
+  ORB_CUDA_TRY(cudaMemcpyAsync(dr.p, desc_r, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+  ORB_CUDA_TRY(cudaMemcpyAsync(nn.p, counts, 8, cudaMemcpyHostToDevice, s));
+  L.img_frame0 = frame_l; L.img_frame_step = 0; L.kp_frame0 = 0; L.kp_frame_step = 0;
+  R.img_frame0 = frame_r; R.img_frame_step = 0; R.kp_frame0 = 0; R.kp_frame_step = 0;
+  L.kps = (const OrbKeyPoint*)kl.p; L.desc = (const uint8_t*)dl.p; L.n = (const int*)nn.p; L.capacity = nl;
+  R.kps = (const OrbKeyPoint*)kr.p; R.desc = (const uint8_t*)dr.p; R.n = (const int*)nn.p + 1; R.capacity = nr;
+  if ((rc = launch_stereo_pairs(L, R, P, 1, nl, (float*)ur.p, (float*)dp.p, (int*)sad.p, s))) return rc;
+  ORB_CUDA_TRY(cudaMemcpyAsync(u_right, ur.p, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+  ORB_CUDA_TRY(cudaMemcpyAsync(depth, dp.p, (size_t)nl * 4, cudaMemcpyDeviceToHost, s));
+  ORB_CUDA_TRY(cudaStreamSynchronize(s));
+  return ORB_GPU_OK;
+}
+
 }  // extern "C"

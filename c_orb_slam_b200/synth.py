@@ -75,6 +75,27 @@ def make_stereo_pair(width, height, seed):
     return left, np.clip(right.astype(np.int16) + noise, 0, 255).astype(np.uint8)
 
 
+def make_stereo_pair_subpixel(width, height, seed):
+    """left, right: right = left shifted by a fractional disparity per 32-row band in [3, 60] px (linear
+    interpolation between the two neighbouring integer shifts) plus noise: exercises the parabola fit of the
+    sub-pixel stereo refinement."""
+    left = make_frame(width, height, seed)
+    rng = np.random.default_rng(seed + 777)
+    right = np.empty_like(left)
+    for y0 in range(0, height, 32):
+        d = float(rng.uniform(3, 60))
+        d0 = int(np.floor(d))
+        f = d - d0
+        band = left[y0:y0 + 32].astype(np.float32)
+        a = np.roll(band, -d0, axis=1)
+        b = np.roll(band, -(d0 + 1), axis=1)
+        mix = (1 - f) * a + f * b
+        mix[:, width - d0 - 1:] = band[:, -1:]
+        right[y0:y0 + 32] = np.clip(np.rint(mix), 0, 255).astype(np.uint8)
+    noise = rng.integers(-2, 3, right.shape)
+    return left, np.clip(right.astype(np.int16) + noise, 0, 255).astype(np.uint8)
+
+
 def random_descriptors(n, seed=7):
     return np.random.default_rng(seed).integers(0, 256, (n, 32), dtype=np.uint8)
 

@@ -187,6 +187,31 @@ int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int n
                             int device, uint8_t* kp_blocked, int32_t* match_of_kp,
                             int32_t* match_of_query, int* nmatches);
 
+/* Replaces Frame::ComputeStereoMatches (src/Frame.cc:466-640) whole: Hamming stage (:476-549), sub-pixel
+ * refinement (11x11 SAD over 11 shifts + parabola, :551-620) and the median outlier filter (:623-639), run on
+ * the unblurred pyramids (mvImagePyramid, include/ORBextractor.h:85) that `left` and `right` kept in device
+ * memory from their last extract call -- frame_l / frame_r are indices inside those batches (0 for
+ * orb_gpu_extract); left == right is allowed.  kps / desc are the host arrays those calls returned (mvKeys,
+ * mDescriptors, mvKeysRight, mDescriptorsRight).  bf = Frame::mbf, b = Frame::mb (minD = 0, maxD = mbf/mb,
+ * :496-498).  u_right / depth [nl] = mvuRight / mvDepth (-1 where there is no match).  A keypoint whose 11x11
+ * window would leave its level image (cv::Mat::rowRange would throw in the reference) gets no match. */
+int orb_gpu_compute_stereo_matches(OrbGpuExtractor* left, int frame_l, OrbGpuExtractor* right,
+                                   int frame_r, const OrbKeyPoint* kps_l, const uint8_t* desc_l, int nl,
+                                   const OrbKeyPoint* kps_r, const uint8_t* desc_r, int nr, float bf,
+                                   float b, float* u_right, float* depth);
+
+/* The same for `npairs` stereo pairs with everything resident in device memory, asynchronous on `stream`
+ * (NULL = left's stream).  Pair i uses frame frame_l0 + i*frame_l_step of left's last batch and frame
+ * frame_r0 + i*frame_r_step of right's, for the images and for the keypoint arrays alike: d_kps_* / d_desc_* /
+ * d_n_* are the [frame][capacity] outputs of orb_gpu_extract_batch_device.  Outputs: d_u_right / d_depth
+ * [npairs][capacity_l]; d_sad [npairs][capacity_l] int scratch (best SAD or -1). */
+int orb_gpu_stereo_matches_device(OrbGpuExtractor* left, int frame_l0, int frame_l_step,
+                                  OrbGpuExtractor* right, int frame_r0, int frame_r_step, int npairs,
+                                  const OrbKeyPoint* d_kps_l, const uint8_t* d_desc_l, const int* d_n_l,
+                                  int capacity_l, const OrbKeyPoint* d_kps_r, const uint8_t* d_desc_r,
+                                  const int* d_n_r, int capacity_r, float bf, float b, float* d_u_right,
+                                  float* d_depth, int* d_sad, void* stream);
+
 /* One source feature of a search over equal vocabulary nodes: feature `index` of frame 1 is compared with the
  * features cand[begin .. end) of frame 2 (the index list of the same DBoW2 node, in its insertion order).  The
  * caller emits the rows in the reference's visiting order (nodes ascending, then the node's list order) and

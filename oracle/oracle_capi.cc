@@ -248,4 +248,20 @@ void orbo_stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyP
                best_dist);
 }
 
+// levels_*: nlevels dense images (w, h in sizes[2*l], sizes[2*l+1])
+int orbo_stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int32_t* best_idx_r,
+                       const int32_t* best_dist, const uint8_t* const* levels_l, const uint8_t* const* levels_r,
+                       const int32_t* sizes_l, const int32_t* sizes_r, int nlevels, const float* sf,
+                       const float* inv_sf, float min_d, float max_d, float bf, float* u_right, float* depth) {
+  std::vector<Image> pl((size_t)nlevels), pr((size_t)nlevels);
+  for (int l = 0; l < nlevels; ++l) {
+    pl[l].w = sizes_l[2 * l]; pl[l].h = sizes_l[2 * l + 1];
+    pl[l].px.assign(levels_l[l], levels_l[l] + (size_t)pl[l].w * pl[l].h);
+    pr[l].w = sizes_r[2 * l]; pr[l].h = sizes_r[2 * l + 1];
+    pr[l].px.assign(levels_r[l], levels_r[l] + (size_t)pr[l].w * pr[l].h);
+  }
+  return stereo_refine(kl, nl, kr, best_idx_r, best_dist, pl.data(), pr.data(), sf, inv_sf, min_d, max_d, bf,
+                       u_right, depth);
+}
+
 }  // extern "C"

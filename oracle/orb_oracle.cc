@@ -803,4 +803,71 @@ void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint*
   }
 }
 
+int stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int32_t* best_idx_r,
+                  const int32_t* best_dist, const Image* pyr_l, const Image* pyr_r,
+                  const float* sf, const float* inv_sf, float minD, float maxD, float mbf,
+                  float* u_right, float* depth) {
+  const int thOrbDist = (100 + 50) / 2;  // (TH_HIGH+TH_LOW)/2, Frame.cc:471
+  int out_of_image = 0;
+  std::vector<std::pair<int, int>> vDistIdx;
+  for (int iL = 0; iL < nl; ++iL) { u_right[iL] = -1.0f; depth[iL] = -1.0f; }
+  for (int iL = 0; iL < nl; ++iL) {
+    if (best_idx_r[iL] < 0 || !(best_dist[iL] < thOrbDist)) continue;  // :552
+    const KeyPoint& kpL = kl[iL];
+    const float uL = kpL.x;
+    const float uR0 = kr[best_idx_r[iL]].x;
+    const float scaleFactor = inv_sf[kpL.octave];
+    const float scaleduL = std::round(kpL.x * scaleFactor);
+    const float scaledvL = std::round(kpL.y * scaleFactor);
+    const float scaleduR0 = std::round(uR0 * scaleFactor);
+    const int w = 5, L = 5;
+    const Image& imL = pyr_l[kpL.octave];
+    const Image& imR = pyr_r[kpL.octave];
+    const int r0 = (int)(scaledvL - w), r1 = (int)(scaledvL + w + 1);
+    const int c0 = (int)(scaleduL - w), c1 = (int)(scaleduL + w + 1);
+    if (r0 < 0 || r1 > imL.h || c0 < 0 || c1 > imL.w) { ++out_of_image; continue; }  // cv::Mat::rowRange asserts
+    const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+    if (iniu < 0 || endu >= imR.w) continue;  // :575-578
+    if ((int)(scaleduR0 - L - w) < 0 || r1 > imR.h) { ++out_of_image; continue; }
+    float IL[11][11];
+    const float cl = (float)imL.row(r0 + w)[c0 + w];
+    for (int r = 0; r < 11; ++r)
+      for (int c = 0; c < 11; ++c) IL[r][c] = (float)imL.row(r0 + r)[c0 + c] - cl;  // :564-566
+    int bestDist = INT_MAX, bestincR = 0;
+    float vDists[2 * 5 + 1];
+    for (int incR = -L; incR <= +L; ++incR) {
+      const int cr0 = (int)(scaleduR0 + incR - w);
+      const float cr = (float)imR.row(r0 + w)[cr0 + w];
+      double acc = 0;  // cv::norm(IL, IR, NORM_L1) on CV_32F accumulates in double; the terms are integers
+      for (int r = 0; r < 11; ++r)
+        for (int c = 0; c < 11; ++c) acc += std::fabs(IL[r][c] - ((float)imR.row(r0 + r)[cr0 + c] - cr));
+      const float dist = (float)acc;
+      if (dist < bestDist) { bestDist = (int)dist; bestincR = incR; }
+      vDists[L + incR] = dist;
+    }
+    if (bestincR == -L || bestincR == L) continue;
+    const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+    const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+    if (deltaR < -1 || deltaR > 1) continue;
+    float bestuR = sf[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+    float disparity = (uL - bestuR);
+    if (disparity >= minD && disparity < maxD) {
+      if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+      depth[iL] = mbf / disparity;
+      u_right[iL] = bestuR;
+      vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
+    }
+  }
+  if (vDistIdx.empty()) return out_of_image;  // (the reference indexes vDistIdx[0] regardless, :627)
+  std::sort(vDistIdx.begin(), vDistIdx.end());
+  const float median = vDistIdx[vDistIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  for (int i = (int)vDistIdx.size() - 1; i >= 0; --i) {
+    if (vDistIdx[i].first < thDist) break;
+    u_right[vDistIdx[i].second] = -1;
+    depth[vDistIdx[i].second] = -1;
+  }
+  return out_of_image;
+}
+
 }  // namespace orbo

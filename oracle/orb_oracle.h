@@ -171,4 +171,14 @@ void stereo_match(const KeyPoint* kl, const uint8_t* dl, int nl, const KeyPoint*
                   float min_d, float max_d, int th_high, int32_t* best_idx_r,
                   int32_t* best_dist);
 
+// N1: sub-pixel refinement and outlier filter of Frame::ComputeStereoMatches (src/Frame.cc:551-640) on the
+// unblurred pyramids of both extractors (mvImagePyramid).  pyr_l / pyr_r: one Image per level.  Inputs are the
+// Hamming stage's best_idx_r / best_dist.  u_right / depth [nl] as mvuRight / mvDepth (-1 = none).  Returns the
+// number of keypoints whose 11x11 windows left the level image (the reference would throw in cv::Mat::rowRange /
+// colRange there; they are skipped).
+int stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int32_t* best_idx_r,
+                  const int32_t* best_dist, const Image* pyr_l, const Image* pyr_r,
+                  const float* scale_factors, const float* inv_scale_factors, float min_d, float max_d,
+                  float bf, float* u_right, float* depth);
+
 }  // namespace orbo

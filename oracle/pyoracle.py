@@ -353,6 +353,29 @@ def stereo_match(kl, dl, kr, dr, n_rows, scale_factors, min_d, max_d, th_high=10
 # ------------------------------------------------------------------------------------------------
 # The reference's own ORBextractor.cc, compiled verbatim over oracle/opencv_shim (oracle/_ref).
 # ------------------------------------------------------------------------------------------------
+def stereo_refine(kl, kr, best_idx_r, best_dist, levels_l, levels_r, scale_factors, inv_scale_factors, min_d, max_d,
+                  bf):
+    """N1 (Frame.cc:551-640) -> u_right[nl], depth[nl], n_out_of_image.  levels_*: list of 2-D uint8 level images."""
+    kl = np.ascontiguousarray(kl, KP_DTYPE)
+    kr = np.ascontiguousarray(kr, KP_DTYPE)
+    bi = np.ascontiguousarray(best_idx_r, np.int32)
+    bd = np.ascontiguousarray(best_dist, np.int32)
+    ll = [u8c(a) for a in levels_l]
+    lr = [u8c(a) for a in levels_r]
+    n = len(ll)
+    pl = (C.c_void_p * n)(*[a.ctypes.data for a in ll])
+    pr = (C.c_void_p * n)(*[a.ctypes.data for a in lr])
+    sl = np.array([(a.shape[1], a.shape[0]) for a in ll], np.int32)
+    sr = np.array([(a.shape[1], a.shape[0]) for a in lr], np.int32)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    isf = np.ascontiguousarray(inv_scale_factors, np.float32)
+    ur = np.empty(len(kl), np.float32)
+    dp = np.empty(len(kl), np.float32)
+    bad = lib().orbo_stereo_refine(_p(kl), len(kl), _p(kr), _p(bi), _p(bd), pl, pr, _p(sl), _p(sr), n, _p(sf), _p(isf),
+                                   C.c_float(min_d), C.c_float(max_d), C.c_float(bf), _p(ur), _p(dp))
+    return ur, dp, bad
+
+
 def have_ref():
     if not os.path.exists(REF_PATH) and os.path.isdir("/root/reference"):
         try:
