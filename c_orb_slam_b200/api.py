@@ -36,7 +36,9 @@ EXPORTS = [
     "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
     "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_search_by_bow",
     "orb_gpu_search_for_triangulation", "orb_gpu_search_for_initialization", "orb_gpu_stereo_match",
-    "orb_gpu_compute_stereo_matches", "orb_gpu_stereo_matches_device", "orb_gpu_version", "orb_gpu_last_error",
+    "orb_gpu_compute_stereo_matches", "orb_gpu_stereo_matches_device", "orb_gpu_distinctive_descriptors",
+    "orb_gpu_distinctive_descriptors_device", "orb_gpu_vocabulary_create", "orb_gpu_vocabulary_destroy",
+    "orb_gpu_vocabulary_transform", "orb_gpu_vocabulary_transform_device", "orb_gpu_version", "orb_gpu_last_error",
     "orb_gpu_launch_count", "orb_gpu_popc_peak",
 ]
 
@@ -115,6 +117,13 @@ def lib():
         L.orb_gpu_compute_stereo_matches.argtypes = [vp, ci, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, vp, vp]
         L.orb_gpu_stereo_matches_device.argtypes = [vp, ci, ci, vp, ci, ci, ci, vp, vp, vp, ci, vp, vp, vp, ci, cf, cf,
                                                     vp, vp, vp, vp]
+        L.orb_gpu_distinctive_descriptors.argtypes = [vp, vp, ci, ci, vp]
+        L.orb_gpu_distinctive_descriptors_device.argtypes = [vp, vp, ci, ci, vp, vp, vp]
+        L.orb_gpu_vocabulary_create.argtypes = [ci, vp, vp, vp, vp, vp, ci, ci, C.POINTER(vp)]
+        L.orb_gpu_vocabulary_destroy.argtypes = [vp]
+        L.orb_gpu_vocabulary_destroy.restype = None
+        L.orb_gpu_vocabulary_transform.argtypes = [vp, vp, ci, ci, vp, vp, vp]
+        L.orb_gpu_vocabulary_transform_device.argtypes = [vp, vp, ci, ci, vp, vp, vp, vp]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -259,6 +268,56 @@ class ORBextractor:
             _check(lib().orb_gpu_get_candidates(self._h, frame, level, _p(out), n.value, C.byref(n)),
                    "orb_gpu_get_candidates")
         return out
+
+
+class ORBVocabulary:
+    """Device-resident DBoW2 vocabulary (ORB_SLAM2::ORBVocabulary = TemplatedVocabulary<FORB::TDescriptor, FORB>,
+    include/ORBVocabulary.h) for the transform of Frame::ComputeBoW / KeyFrame::ComputeBoW
+    (src/Frame.cc:395-402): TF_IDF weighting, L1 norm (the header line of ORBvoc.txt)."""
+
+    def __init__(self, tree, device=0):
+        self.depth = int(tree["depth"])
+        self._keep = [np.ascontiguousarray(tree["child_begin"], np.int32), np.ascontiguousarray(tree["children"], np.int32),
+                      np.ascontiguousarray(tree["desc"], np.uint8), np.ascontiguousarray(tree["word_id"], np.int32),
+                      np.ascontiguousarray(tree["weight"], np.float64)]
+        self._h = C.c_void_p()
+        _check(lib().orb_gpu_vocabulary_create(len(self._keep[3]), *[_p(a) for a in self._keep], self.depth, device,
+                                               C.byref(self._h)), "orb_gpu_vocabulary_create")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_gpu_vocabulary_destroy(self._h)
+            self._h = None
+
+    def transform_features(self, desc, levelsup=4):
+        """-> word_id uint32 [n], weight float64 [n], node_id uint32 [n] (TemplatedVocabulary.h:1213-1259)"""
+        d = np.ascontiguousarray(desc, np.uint8)
+        n = len(d)
+        w = np.empty(n, np.uint32); v = np.empty(n, np.float64); nd = np.empty(n, np.uint32)
+        _check(lib().orb_gpu_vocabulary_transform(self._h, _p(d), n, int(levelsup), _p(w), _p(v), _p(nd)),
+               "orb_gpu_vocabulary_transform")
+        return w, v, nd
+
+    def transform(self, desc, levelsup=4):
+        """TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1127-1192).
+        -> BowVector as (word ids ascending uint32, values float64), FeatureVector {node id: [feature indices]}.
+        The descent runs on the GPU; the two std::map fills are host bookkeeping in the reference's order."""
+        words, weights, nodes = self.transform_features(desc, levelsup)
+        bow, fv = {}, {}
+        for i in range(len(words)):
+            w = float(weights[i])
+            if w > 0:                                   # not stopped (:1155)
+                k = int(words[i])
+                bow[k] = bow[k] + w if k in bow else w   # BowVector::addWeight
+                fv.setdefault(int(nodes[i]), []).append(i)
+        ids = np.array(sorted(bow), np.uint32)
+        vals = np.array([bow[int(k)] for k in ids], np.float64)
+        norm = 0.0
+        for x in vals:                                  # BowVector::normalize(L1): ascending key order
+            norm += abs(float(x))
+        if norm > 0.0:
+            vals = vals / norm
+        return (ids, vals), fv
 
 
 class ORBmatcher:
@@ -423,6 +482,20 @@ class ORBmatcher:
         prev_matched[hit, 0] = k2["x"][m12[hit]]
         prev_matched[hit, 1] = k2["y"][m12[hit]]
         return n.value, m12
+
+    def ComputeDistinctiveDescriptors(self, desc_lists):
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307) for many map points at once.
+        desc_lists: one [N_p, 32] uint8 array per map point (its observations in mObservations order).
+        -> best index per point (int32; -1 for an empty list); the caller clones that row into mDescriptor."""
+        offs = np.zeros(len(desc_lists) + 1, np.int32)
+        for i, d in enumerate(desc_lists):
+            offs[i + 1] = offs[i] + len(d)
+        flat = (np.concatenate([np.ascontiguousarray(d, np.uint8).reshape(-1, 32) for d in desc_lists])
+                if len(desc_lists) and offs[-1] else np.zeros((0, 32), np.uint8))
+        best = np.empty(len(desc_lists), np.int32)
+        _check(lib().orb_gpu_distinctive_descriptors(_p(flat), _p(offs), len(desc_lists), self.device, _p(best)),
+               "orb_gpu_distinctive_descriptors")
+        return best
 
     def ComputeStereoMatches(self, ex_left, ex_right, kps_l, desc_l, kps_r, desc_r, bf, b, frame_l=0, frame_r=0):
         """Frame::ComputeStereoMatches (src/Frame.cc:466-640) on the pyramids the two ORBextractor objects kept on

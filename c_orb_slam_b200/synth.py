@@ -96,6 +96,55 @@ def make_stereo_pair_subpixel(width, height, seed):
     return left, np.clip(right.astype(np.int16) + noise, 0, 255).astype(np.uint8)
 
 
+def make_vocabulary(k=10, depth=4, seed=1, shuffle_ids=True, stop_frac=0.02):
+    """Synthetic DBoW2 vocabulary tree (the shipped ORBvoc.txt is k = 10, L = 6; it is not in the reference
+    tree): every node's descriptor is its parent's with ~256/(level+2) random bits flipped, so descents are
+    decisive near the root and close calls (equal distances) appear near the leaves.  Branching is k, a few
+    nodes get fewer children.  Node ids are shuffled (children of a node are not contiguous, as in a loaded
+    vocabulary); words are numbered in creation order; weights mimic idf values, a fraction is 0 (stopped).
+    -> dict(child_begin, children, desc, word_id, weight, depth)"""
+    rng = np.random.default_rng(seed)
+    descs = [rng.integers(0, 256, 32, dtype=np.uint8)]
+    kids = [[]]
+    level_nodes = [0]
+    for lv in range(depth):
+        nxt = []
+        for nd in level_nodes:
+            nk = k if rng.random() < 0.9 else int(rng.integers(1, k + 1))
+            for _ in range(nk):
+                d = descs[nd].copy()
+                bits = rng.choice(256, size=max(4, 256 // (lv + 2) // 2), replace=False)
+                for b in bits:
+                    d[b >> 3] ^= np.uint8(1 << (b & 7))
+                descs.append(d)
+                kids.append([])
+                kids[nd].append(len(descs) - 1)
+                nxt.append(len(descs) - 1)
+        level_nodes = nxt
+    n = len(descs)
+    perm = np.arange(n)
+    if shuffle_ids:
+        perm[1:] = rng.permutation(np.arange(1, n))   # new id of old node i; the root stays 0
+    inv = np.argsort(perm)
+    child_begin = np.zeros(n + 1, np.int32)
+    children = []
+    for new in range(n):
+        old = inv[new]
+        children.extend(int(perm[c]) for c in kids[old])
+        child_begin[new + 1] = len(children)
+    desc = np.stack(descs)[inv]
+    word_id = np.full(n, -1, np.int32)
+    weight = np.zeros(n, np.float64)
+    words = 0
+    for old in range(n):                      # creation order
+        if not kids[old]:
+            word_id[perm[old]] = words
+            words += 1
+            weight[perm[old]] = 0.0 if rng.random() < stop_frac else float(np.log(rng.uniform(1.5, 400.0)))
+    return dict(child_begin=child_begin, children=np.asarray(children, np.int32), desc=desc, word_id=word_id,
+                weight=weight, depth=depth, words=words)
+
+
 def random_descriptors(n, seed=7):
     return np.random.default_rng(seed).integers(0, 256, (n, 32), dtype=np.uint8)
 

@@ -212,6 +212,42 @@ int orb_gpu_stereo_matches_device(OrbGpuExtractor* left, int frame_l0, int frame
                                   const int* d_n_r, int capacity_r, float bf, float b, float* d_u_right,
                                   float* d_depth, int* d_sad, void* stream);
 
+/* Replaces the arithmetic of MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307) for a batch of
+ * map points: point p owns the descriptors desc[offsets[p] .. offsets[p+1]) (its observations in the iteration
+ * order of mObservations, bad key frames already dropped, :261-267).  best_idx[p] = position inside that list
+ * of the descriptor with the least median distance to the others -- median = sorted row [0.5*(N-1)], first
+ * minimum wins (:288-301) -- or -1 for a point without descriptors.  At most 1024 observations per point
+ * (ORB_GPU_ERR_CAPACITY beyond).  Host pointers. */
+int orb_gpu_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int npoints, int device,
+                                    int32_t* best_idx);
+/* Device pointers, asynchronous on `stream`; max_obs >= the longest list; *d_status is set to
+ * ORB_GPU_ERR_CAPACITY when a list is longer than 1024 (initialise it to 0). */
+int orb_gpu_distinctive_descriptors_device(const uint8_t* d_desc, const int* d_offsets, int npoints,
+                                           int max_obs, int32_t* d_best_idx, int* d_status, void* stream);
+
+/* ---- vocabulary (DBoW2) ------------------------------------------------------------------- */
+
+/* A DBoW2 vocabulary tree resident in device memory.  Node 0 is the root; node i owns the children
+ * children[child_begin[i] .. child_begin[i+1]) in the order of Node::children
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:148-176); a node without children is a word with word_id /
+ * weight (Node::word_id, Node::weight); depth = m_L. */
+typedef struct OrbGpuVocabulary OrbGpuVocabulary;
+int orb_gpu_vocabulary_create(int n_nodes, const int32_t* child_begin, const int32_t* children,
+                              const uint8_t* node_desc, const int32_t* word_id, const double* weight,
+                              int depth, int device, OrbGpuVocabulary** out);
+void orb_gpu_vocabulary_destroy(OrbGpuVocabulary* v);
+
+/* Replaces TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)
+ * (TemplatedVocabulary.h:1213-1259) for n descriptors -- the Hamming work of Frame::ComputeBoW
+ * (src/Frame.cc:395-402, levelsup = 4).  node_id[i] = ancestor of the word at level depth - levelsup (0 = root
+ * when that is <= 0).  The caller folds (word_id, weight) into the BowVector and (node_id, i) into the
+ * FeatureVector in feature order (:1148-1165).  Host pointers / device pointers + stream. */
+int orb_gpu_vocabulary_transform(const OrbGpuVocabulary* v, const uint8_t* desc, int n, int levelsup,
+                                 uint32_t* word_id, double* weight, uint32_t* node_id);
+int orb_gpu_vocabulary_transform_device(const OrbGpuVocabulary* v, const uint8_t* d_desc, int n,
+                                        int levelsup, uint32_t* d_word_id, double* d_weight,
+                                        uint32_t* d_node_id, void* stream);
+
 /* One source feature of a search over equal vocabulary nodes: feature `index` of frame 1 is compared with the
  * features cand[begin .. end) of frame 2 (the index list of the same DBoW2 node, in its insertion order).  The
  * caller emits the rows in the reference's visiting order (nodes ascending, then the node's list order) and

@@ -264,4 +264,21 @@ int orbo_stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int
                        u_right, depth);
 }
 
+void orbo_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best) {
+  for (int p = 0; p < npoints; ++p)
+    best[p] = distinctive_descriptor(desc + (size_t)offsets[p] * 32, offsets[p + 1] - offsets[p]);
+}
+
+int orbo_voc_transform(int n_nodes, const int32_t* child_begin, const int32_t* children, const uint8_t* node_desc,
+                       const int32_t* word_id, const double* weight, int depth, const uint8_t* features, int n,
+                       int levelsup, uint32_t* f_word, double* f_weight, uint32_t* f_node, uint32_t* bow_id,
+                       double* bow_val, uint32_t* feature_node) {
+  VocTree t;
+  t.n_nodes = n_nodes; t.child_begin = child_begin; t.children = children; t.desc = node_desc;
+  t.word_id = word_id; t.weight = weight; t.depth = depth;
+  for (int i = 0; i < n; ++i)
+    voc_transform_feature(t, features + (size_t)i * 32, levelsup, f_word + i, f_weight + i, f_node + i);
+  return voc_transform(t, features, n, levelsup, bow_id, bow_val, feature_node);
+}
+
 }  // extern "C"

@@ -5,6 +5,7 @@
 #include <chrono>
 #include <climits>
 #include <cmath>
+#include <map>
 #include <cstring>
 
 namespace orbo {
@@ -868,6 +869,73 @@ int stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int32_t*
     depth[vDistIdx[i].second] = -1;
   }
   return out_of_image;
+}
+
+void voc_transform_feature(const VocTree& t, const uint8_t* feature, int levelsup, uint32_t* word_id,
+                           double* weight, uint32_t* nid) {
+  const int nid_level = t.depth - levelsup;
+  if (nid_level <= 0 && nid != NULL) *nid = 0;  // root
+  int final_id = 0, current_level = 0;
+  do {
+    ++current_level;
+    const int32_t* nodes = t.children + t.child_begin[final_id];
+    const int count = t.child_begin[final_id + 1] - t.child_begin[final_id];
+    final_id = nodes[0];
+    double best_d = descriptor_distance(feature, t.desc + (size_t)final_id * 32);  // FORB::distance
+    for (int c = 1; c < count; ++c) {
+      const int id = nodes[c];
+      const double d = descriptor_distance(feature, t.desc + (size_t)id * 32);
+      if (d < best_d) { best_d = d; final_id = id; }
+    }
+    if (nid != NULL && current_level == nid_level) *nid = (uint32_t)final_id;
+  } while (t.child_begin[final_id + 1] > t.child_begin[final_id]);  // !isLeaf()
+  *word_id = (uint32_t)t.word_id[final_id];
+  *weight = t.weight[final_id];
+}
+
+int voc_transform(const VocTree& t, const uint8_t* features, int n, int levelsup, uint32_t* bow_id,
+                  double* bow_val, uint32_t* feature_node) {
+  std::map<uint32_t, double> v;  // BowVector
+  for (int i = 0; i < n; ++i) {
+    uint32_t id = 0, nid = 0;
+    double w = 0;
+    voc_transform_feature(t, features + (size_t)i * 32, levelsup, &id, &w, &nid);
+    feature_node[i] = 0xffffffffu;
+    if (w > 0) {  // not stopped
+      std::map<uint32_t, double>::iterator it = v.find(id);  // BowVector::addWeight (BowVector.cpp:34-46)
+      if (it != v.end()) it->second += w; else v[id] = w;
+      feature_node[i] = nid;  // FeatureVector::addFeature(nid, i_feature)
+    }
+  }
+  double norm = 0.0;  // BowVector::normalize(L1) (BowVector.cpp:62-84)
+  for (auto& kv : v) norm += std::fabs(kv.second);
+  if (norm > 0.0)
+    for (auto& kv : v) kv.second /= norm;
+  int k = 0;
+  for (auto& kv : v) { bow_id[k] = kv.first; bow_val[k] = kv.second; ++k; }
+  return k;
+}
+
+int distinctive_descriptor(const uint8_t* desc, int n) {
+  if (n <= 0) return -1;
+  const size_t N = (size_t)n;
+  std::vector<float> Distances(N * N);  // float Distances[N][N] (:275)
+  for (size_t i = 0; i < N; i++) {
+    Distances[i * N + i] = 0;
+    for (size_t j = i + 1; j < N; j++) {
+      const int distij = descriptor_distance(desc + i * 32, desc + j * 32);
+      Distances[i * N + j] = distij;
+      Distances[j * N + i] = distij;
+    }
+  }
+  int BestMedian = INT_MAX, BestIdx = 0;
+  for (size_t i = 0; i < N; i++) {
+    std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + (i + 1) * N);
+    std::sort(vDists.begin(), vDists.end());
+    const int median = vDists[0.5 * (N - 1)];
+    if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+  }
+  return BestIdx;
 }
 
 }  // namespace orbo

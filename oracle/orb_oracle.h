@@ -181,4 +181,28 @@ int stereo_refine(const KeyPoint* kl, int nl, const KeyPoint* kr, const int32_t*
                   const float* scale_factors, const float* inv_scale_factors, float min_d, float max_d,
                   float bf, float* u_right, float* depth);
 
+// N3: DBoW2 vocabulary tree as flat arrays (node 0 = root; children of node i in Node::children order).
+struct VocTree {
+  int n_nodes;
+  const int32_t* child_begin;  // [n_nodes + 1]
+  const int32_t* children;
+  const uint8_t* desc;         // [n_nodes][32]
+  const int32_t* word_id;      // [n_nodes]
+  const double* weight;        // [n_nodes]
+  int depth;                   // m_L
+};
+// TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1213-1259)
+void voc_transform_feature(const VocTree& t, const uint8_t* feature, int levelsup, uint32_t* word_id,
+                           double* weight, uint32_t* nid);
+// TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1127-1192) for TF_IDF
+// weighting and L1 normalisation (what ORBvoc.txt declares).  bow_id / bow_val: the BowVector in key order,
+// returns its size; feature_node[i] = node of feature i or 0xffffffff when the word is stopped (w <= 0).
+int voc_transform(const VocTree& t, const uint8_t* features, int n, int levelsup, uint32_t* bow_id,
+                  double* bow_val, uint32_t* feature_node);
+
+// N4: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307) for the n descriptors of one map point.
+// Returns BestIdx (:288-301), -1 when n == 0.
+int distinctive_descriptor(const uint8_t* desc, int n);
+
 }  // namespace orbo

@@ -376,6 +376,36 @@ def stereo_refine(kl, kr, best_idx_r, best_dist, levels_l, levels_r, scale_facto
     return ur, dp, bad
 
 
+def distinctive_descriptors(desc_lists):
+    """N4 (MapPoint.cc:242-307) -> best index per map point"""
+    offs = np.zeros(len(desc_lists) + 1, np.int32)
+    for i, d in enumerate(desc_lists):
+        offs[i + 1] = offs[i] + len(d)
+    flat = (np.concatenate([u8c(d).reshape(-1, 32) for d in desc_lists]) if offs[-1] else np.zeros((0, 32), np.uint8))
+    best = np.empty(len(desc_lists), np.int32)
+    lib().orbo_distinctive_descriptors(_p(flat), _p(offs), len(desc_lists), _p(best))
+    return best
+
+
+def voc_transform(tree, features, levelsup=4):
+    """N3: DBoW2 transform (TemplatedVocabulary.h:1127-1259, TF_IDF + L1).  tree: dict(child_begin, children, desc,
+    word_id, weight, depth).  -> per-feature (word, weight, node), BowVector (ids, values), FeatureVector dict"""
+    cb = np.ascontiguousarray(tree["child_begin"], np.int32); ch = np.ascontiguousarray(tree["children"], np.int32)
+    nd = u8c(tree["desc"]); wid = np.ascontiguousarray(tree["word_id"], np.int32)
+    wt = np.ascontiguousarray(tree["weight"], np.float64)
+    f = u8c(features)
+    n = len(f)
+    fw = np.empty(n, np.uint32); fv = np.empty(n, np.float64); fn = np.empty(n, np.uint32)
+    bid = np.empty(max(n, 1), np.uint32); bval = np.empty(max(n, 1), np.float64); node = np.empty(n, np.uint32)
+    k = lib().orbo_voc_transform(len(wid), _p(cb), _p(ch), _p(nd), _p(wid), _p(wt), int(tree["depth"]), _p(f), n,
+                                 int(levelsup), _p(fw), _p(fv), _p(fn), _p(bid), _p(bval), _p(node))
+    featvec = {}
+    for i in range(n):
+        if node[i] != 0xffffffff:
+            featvec.setdefault(int(node[i]), []).append(i)
+    return (fw, fv, fn), (bid[:k].copy(), bval[:k].copy()), featvec
+
+
 def have_ref():
     if not os.path.exists(REF_PATH) and os.path.isdir("/root/reference"):
         try:

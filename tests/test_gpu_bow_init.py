@@ -194,3 +194,26 @@ def test_hand_cases_steal_back_and_ties(gpu, oracle):
     n, m12, m21 = gpu.ORBmatcher(0.05, checkOri=False).SearchByBoW(
         dict(kps=kk, desc=dd1, feat_vec=fv), dict(kps=kk, desc=dd2, feat_vec=fv), [1, 0])
     assert n == 0
+
+
+def test_distinctive_descriptors(gpu, oracle):
+    """N4: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307) batched over map points."""
+    rng = np.random.default_rng(12)
+    lists = []
+    for n in [0, 1, 2, 3, 4, 5, 8, 33, 64, 100, 257, 1024] + rng.integers(2, 40, 300).tolist():
+        base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+        d = synth.flip_bits(np.repeat(base, n, 0), rng.integers(0, 60, n), rng) if n else np.zeros((0, 32), np.uint8)
+        if n > 4:
+            d[rng.integers(0, n)] = d[rng.integers(0, n)]   # equal rows: ties between medians
+        lists.append(d)
+    want = oracle.distinctive_descriptors(lists)
+    got = gpu.ORBmatcher().ComputeDistinctiveDescriptors(lists)
+    assert np.array_equal(got, want)
+    assert got[0] == -1 and got[1] == 0 and (got[2:] >= 0).all()
+    # independent restatement for one point
+    d = lists[9].astype(np.uint8)
+    dist = np.unpackbits(d[:, None, :] ^ d[None, :, :], axis=2).sum(2)
+    med = np.sort(dist, 1)[:, int(0.5 * (len(d) - 1))]
+    assert got[9] == int(np.argmin(med))
+    with pytest.raises(gpu.OrbGpuError):
+        gpu.ORBmatcher().ComputeDistinctiveDescriptors([np.zeros((1025, 32), np.uint8)])
