@@ -34,7 +34,7 @@ EXPORTS = [
     "orb_gpu_get_scale_tables", "orb_gpu_get_features_per_level", "orb_gpu_get_pyramid",
     "orb_gpu_get_candidates", "orb_gpu_hamming_pairs_device", "orb_gpu_match_bruteforce_device",
     "orb_gpu_match_bruteforce", "orb_gpu_merge_top2_device", "orb_gpu_ratio_test_device",
-    "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_search_by_bow",
+    "orb_gpu_search_by_projection", "orb_gpu_search_windowed", "orb_gpu_features_in_area", "orb_gpu_search_by_bow",
     "orb_gpu_search_for_triangulation", "orb_gpu_search_for_initialization", "orb_gpu_stereo_match",
     "orb_gpu_compute_stereo_matches", "orb_gpu_stereo_matches_device", "orb_gpu_distinctive_descriptors",
     "orb_gpu_distinctive_descriptors_device", "orb_gpu_vocabulary_create", "orb_gpu_vocabulary_destroy",
@@ -124,6 +124,7 @@ def lib():
         L.orb_gpu_vocabulary_destroy.restype = None
         L.orb_gpu_vocabulary_transform.argtypes = [vp, vp, ci, ci, vp, vp, vp]
         L.orb_gpu_vocabulary_transform_device.argtypes = [vp, vp, ci, ci, vp, vp, vp, vp]
+        L.orb_gpu_features_in_area.argtypes = [vp, ci, vp, ci, _Grid, ci, vp, vp, ci]
         L.orb_gpu_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                            C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -482,6 +483,23 @@ class ORBmatcher:
         prev_matched[hit, 0] = k2["x"][m12[hit]]
         prev_matched[hit, 1] = k2["y"][m12[hit]]
         return n.value, m12
+
+    def GetFeaturesInArea(self, frame, windows):
+        """Frame::GetFeaturesInArea (src/Frame.cc:327-380) for a batch of windows (WINDOW_DTYPE rows: u, v, radius,
+        min_level, max_level, valid).  -> list of int32 index arrays in the reference's candidate order."""
+        kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
+        wq = np.ascontiguousarray(windows, WINDOW_DTYPE)
+        g = _Grid(*[float(v) for v in frame["grid"]])
+        offs = np.zeros(len(wq) + 1, np.int32)
+        idx = np.empty(max(1, 64 * len(wq)), np.int32)
+        rc = lib().orb_gpu_features_in_area(_p(wq), len(wq), _p(kps), len(kps), g, self.device, _p(offs), _p(idx),
+                                            len(idx))
+        if rc == -2 and offs[-1] > len(idx):
+            idx = np.empty(int(offs[-1]), np.int32)
+            rc = lib().orb_gpu_features_in_area(_p(wq), len(wq), _p(kps), len(kps), g, self.device, _p(offs), _p(idx),
+                                                len(idx))
+        _check(rc, "orb_gpu_features_in_area")
+        return [idx[offs[i]:offs[i + 1]].copy() for i in range(len(wq))]
 
     def ComputeDistinctiveDescriptors(self, desc_lists):
         """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307) for many map points at once.

@@ -653,6 +653,55 @@ int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int n
                       match_of_query, nmatches);
 }
 
+// Candidate lists of GetFeaturesInArea for a batch of windows, in the reference's order (N2; used by tests and by
+// callers that want the lists themselves).
+int orb_gpu_features_in_area(const OrbWindowQuery* q, int nq, const OrbKeyPoint* kps, int nk, OrbFrameGrid grid,
+                             int device, int32_t* offsets, int32_t* indices, int capacity) {
+  if (nq < 0 || nk < 0 || !offsets || capacity < 0 || (capacity > 0 && !indices) || (nq > 0 && !q) || (nk > 0 && !kps))
+    return ORB_GPU_ERR_ARG;
+  for (int i = 0; i <= nq; ++i) offsets[i] = 0;
+  if (nq == 0 || nk == 0) return ORB_GPU_OK;
+  if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int nkpad = 2;
+  while (nkpad < nk) nkpad <<= 1;
+  TmpDevW dq, dqd, dk, dkd, dsorted, dcell, dcnt, doff, dent;
+  int rc;
+  if ((rc = dq.alloc((size_t)nq * sizeof(OrbWindowQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
+      (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) || (rc = dkd.alloc((size_t)nk * 32)) ||
+      (rc = dsorted.alloc((size_t)nkpad * 4)) || (rc = dcell.alloc((size_t)(kCells + 1) * 4)) ||
+      (rc = dcnt.alloc((size_t)nq * 4)) || (rc = doff.alloc((size_t)(nq + 1) * 4)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbWindowQuery), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(dk.p, kps, (size_t)nk * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemset(dqd.p, 0, (size_t)nq * 32));
+  ORB_CUDA_TRY(cudaMemset(dkd.p, 0, (size_t)nk * 32));
+  const size_t smem = (size_t)nkpad * 4;
+  if (smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grid_build_kernel<<<1, 1024, smem>>>(dk.as<OrbKeyPoint>(), nk, nkpad, grid, dsorted.as<uint32_t>(), dcell.as<int>());
+  const int blocks = (nq * 32 + 255) / 256;
+  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr,
+      nullptr);
+  exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
+  ORB_CUDA_TRY(cudaMemcpy(offsets, doff.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost));
+  const int total = offsets[nq];
+  count_launch(3);
+  if (total > capacity) return ORB_GPU_ERR_CAPACITY;  // offsets are valid: the caller can size the buffer
+  if (total == 0) return ORB_GPU_OK;
+  if ((rc = dent.alloc((size_t)total * 4))) return rc;
+  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
+      dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(),
+      dent.as<uint32_t>());
+  count_launch(1);
+  ORB_CUDA_TRY(cudaGetLastError());
+  std::vector<uint32_t> ent((size_t)total);
+  ORB_CUDA_TRY(cudaMemcpy(ent.data(), dent.p, (size_t)total * 4, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < total; ++i) indices[i] = (int32_t)(ent[i] & 0xffffu);
+  return ORB_GPU_OK;
+}
+
 static int check_bucket_queries(const OrbBucketQuery* q, int nq, int ncand2, int n1, const int32_t* cand2,
                                 int n2, std::vector<int>& offsets) {
   offsets.assign((size_t)nq + 1, 0);

@@ -248,6 +248,15 @@ int orb_gpu_vocabulary_transform_device(const OrbGpuVocabulary* v, const uint8_t
                                         int levelsup, uint32_t* d_word_id, double* d_weight,
                                         uint32_t* d_node_id, void* stream);
 
+/* Frame::GetFeaturesInArea / KeyFrame::GetFeaturesInArea (src/Frame.cc:327-380, src/KeyFrame.cc:569-608) over
+ * the 64x48 grid of AssignFeaturesToGrid (:230-245) for nq windows at once: the candidates of window i are
+ * indices[offsets[i] .. offsets[i+1]) in the reference's order (grid column, then row, then insertion order).
+ * Only u, v, radius, min_level, max_level and valid of OrbWindowQuery are read.  offsets has nq+1 entries and is
+ * always filled; ORB_GPU_ERR_CAPACITY when offsets[nq] > capacity.  Host pointers. */
+int orb_gpu_features_in_area(const OrbWindowQuery* q, int nq, const OrbKeyPoint* kps, int nk,
+                             OrbFrameGrid grid, int device, int32_t* offsets, int32_t* indices,
+                             int capacity);
+
 /* One source feature of a search over equal vocabulary nodes: feature `index` of frame 1 is compared with the
  * features cand[begin .. end) of frame 2 (the index list of the same DBoW2 node, in its insertion order).  The
  * caller emits the rows in the reference's visiting order (nodes ascending, then the node's list order) and

@@ -245,3 +245,30 @@ def test_search_by_sim3_two_passes_agree(gpu, oracle):
     a, b = res[0][:n] % n, res[1][:n] % n
     mutual = np.flatnonzero((res[0][:n] >= 0) & (b[a] == np.arange(n)))
     assert mutual.size >= 0
+
+
+def test_features_in_area_order(gpu, oracle):
+    """N2 / M11: the device grid returns every window's candidates in the order of Frame::GetFeaturesInArea
+    (src/Frame.cc:327-380) -- the order the stable top-2 tie-breaks depend on."""
+    W, H = 640, 480
+    _, kps, _ = _frame_from_extractor(oracle, W, H, 21, 2000)
+    rng = np.random.default_rng(21)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(W), np.float32(48) / np.float32(H))
+    M = 400
+    q = np.zeros(M, gpu.WINDOW_DTYPE)
+    q["u"] = rng.uniform(-30, W + 30, M).astype(np.float32)
+    q["v"] = rng.uniform(-30, H + 30, M).astype(np.float32)
+    q["radius"] = rng.choice([3.0, 10.0, 40.0, 100.0, 700.0], M).astype(np.float32)
+    lv = rng.integers(0, 8, M)
+    mode = rng.integers(0, 4, M)
+    q["min_level"] = np.where(mode == 0, -1, np.where(mode == 1, lv, np.where(mode == 2, 0, lv - 1)))
+    q["max_level"] = np.where(mode == 0, -1, np.where(mode == 1, -1, np.where(mode == 2, lv, lv + 1)))
+    q["valid"] = 1
+    got = gpu.ORBmatcher().GetFeaturesInArea(dict(kps=kps, grid=grid), q)
+    total = 0
+    for i in range(M):
+        want = oracle.features_in_area(kps, grid, q["u"][i], q["v"][i], q["radius"][i], int(q["min_level"][i]),
+                                       int(q["max_level"][i]))
+        assert np.array_equal(got[i], want), i
+        total += len(want)
+    assert total > 5000 and any(len(g) == 0 for g in got)
