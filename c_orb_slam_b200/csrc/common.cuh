@@ -99,6 +99,18 @@ void set_last_error(const char* what, cudaError_t e);
     }                                                       \
   } while (0)
 
+// Scratch buffer of one host-pointer call: stream-ordered allocation from the device's default memory pool on
+// the legacy default stream (the stream those calls launch on).  use_cached_pool() raises the pool's release
+// threshold once per device, so after the first call of a given size the allocation is a free-list lookup
+// instead of a cudaMalloc / cudaFree pair (the matcher calls are ~100 us of work behind ~15 buffers).
+int use_cached_pool(int device);
+struct TmpDevW {
+  void* p = nullptr;
+  ~TmpDevW() { if (p) cudaFreeAsync(p, 0); }
+  int alloc(size_t bytes) { ORB_CUDA_TRY(cudaMallocAsync(&p, bytes ? bytes : 16, 0)); return ORB_GPU_OK; }
+  template <class T> T* as() { return (T*)p; }
+};
+
 // ---- launchers implemented in extract_kernels.cu -------------------------------------------
 int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s);
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);

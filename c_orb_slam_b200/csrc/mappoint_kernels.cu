@@ -93,13 +93,13 @@ int orb_gpu_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets,
   const int total = offsets[npoints];
   if (total > 0 && !desc) return ORB_GPU_ERR_ARG;
   if (max_obs > kDistinctMaxObs) return ORB_GPU_ERR_CAPACITY;
-  ORB_CUDA_TRY(cudaSetDevice(device));
-  void *dd = nullptr, *doff = nullptr, *dbest = nullptr, *dst = nullptr;
-  struct Free { void** p[4]; ~Free() { for (void** x : p) if (*x) cudaFree(*x); } } guard{{&dd, &doff, &dbest, &dst}};
-  ORB_CUDA_TRY(cudaMalloc(&dd, (size_t)(total > 0 ? total : 1) * 32));
-  ORB_CUDA_TRY(cudaMalloc(&doff, (size_t)(npoints + 1) * 4));
-  ORB_CUDA_TRY(cudaMalloc(&dbest, (size_t)npoints * 4));
-  ORB_CUDA_TRY(cudaMalloc(&dst, 4));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
+  TmpDevW bd, boff, bbest, bst;
+  int rc0;
+  if ((rc0 = bd.alloc((size_t)(total > 0 ? total : 1) * 32)) || (rc0 = boff.alloc((size_t)(npoints + 1) * 4)) ||
+      (rc0 = bbest.alloc((size_t)npoints * 4)) || (rc0 = bst.alloc(4)))
+    return rc0;
+  void *dd = bd.p, *doff = boff.p, *dbest = bbest.p, *dst = bst.p;
   if (total > 0) ORB_CUDA_TRY(cudaMemcpy(dd, desc, (size_t)total * 32, cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemcpy(doff, offsets, (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice));
   ORB_CUDA_TRY(cudaMemset(dst, 0, 4));

@@ -16,6 +16,18 @@ static std::atomic<long long> g_launches{0};
 static thread_local std::string g_last_error;
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int use_cached_pool(int device) {
+  static std::atomic<unsigned long long> done{0};
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  if (device >= 0 && device < 64 && !(done.load() >> device & 1ull)) {
+    cudaMemPool_t pool;
+    ORB_CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long keep = ~0ull;  // never trim: the scratch of the matcher calls is a few MB
+    ORB_CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    done.fetch_or(1ull << device);
+  }
+  return ORB_GPU_OK;
+}
 void set_last_error(const char* what, cudaError_t e) {
   g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
 }
@@ -640,17 +652,17 @@ int orb_gpu_compute_stereo_matches(OrbGpuExtractor* left, int frame_l, OrbGpuExt
     return ORB_GPU_ERR_ARG;
   for (int i = 0; i < nl; ++i) { u_right[i] = -1.0f; depth[i] = -1.0f; }
   if (nl == 0 || nr == 0) return ORB_GPU_OK;
-  ORB_CUDA_TRY(cudaSetDevice(left->device));
+  { const int rc_pool = use_cached_pool(left->device); if (rc_pool) return rc_pool; }
   // both extractors may still be running on their own streams
   ORB_CUDA_TRY(cudaStreamSynchronize(left->stream));
   ORB_CUDA_TRY(cudaStreamSynchronize(right->stream));
-  DevBuf kl, dl, kr, dr, nn, ur, dp, sad;
-  struct Free { DevBuf* b[8]; ~Free() { for (DevBuf* x : b) x->release(); } } guard{{&kl, &dl, &kr, &dr, &nn, &ur, &dp, &sad}};
-  if ((rc = kl.ensure((size_t)nl * sizeof(OrbKeyPoint))) || (rc = dl.ensure((size_t)nl * 32)) ||
-      (rc = kr.ensure((size_t)nr * sizeof(OrbKeyPoint))) || (rc = dr.ensure((size_t)nr * 32)) ||
-      (rc = nn.ensure(8)) || (rc = ur.ensure((size_t)nl * 4)) || (rc = dp.ensure((size_t)nl * 4)) ||
-      (rc = sad.ensure((size_t)nl * 4)))
+  TmpDevW kl, dl, kr, dr, nn, ur, dp, sad;
+  if ((rc = kl.alloc((size_t)nl * sizeof(OrbKeyPoint))) || (rc = dl.alloc((size_t)nl * 32)) ||
+      (rc = kr.alloc((size_t)nr * sizeof(OrbKeyPoint))) || (rc = dr.alloc((size_t)nr * 32)) ||
+      (rc = nn.alloc(8)) || (rc = ur.alloc((size_t)nl * 4)) || (rc = dp.alloc((size_t)nl * 4)) ||
+      (rc = sad.alloc((size_t)nl * 4)))
     return rc;
+  ORB_CUDA_TRY(cudaStreamSynchronize(0));  // the pool hands the buffers out in legacy-stream order
   cudaStream_t s = left->stream;
   const int counts[2] = {nl, nr};
   ORB_CUDA_TRY(cudaMemcpyAsync(kl.p, kps_l, (size_t)nl * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice, s));

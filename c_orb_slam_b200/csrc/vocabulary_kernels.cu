@@ -120,13 +120,13 @@ int orb_gpu_vocabulary_transform(const OrbGpuVocabulary* v, const uint8_t* desc,
                                  uint32_t* word_id, double* weight, uint32_t* node_id) {
   if (!v || n < 0 || (n > 0 && (!desc || !word_id || !weight || !node_id))) return ORB_GPU_ERR_ARG;
   if (n == 0) return ORB_GPU_OK;
-  ORB_CUDA_TRY(cudaSetDevice(v->device));
-  void *dd = nullptr, *dw = nullptr, *dv = nullptr, *dn = nullptr;
-  struct Free { void** p[4]; ~Free() { for (void** x : p) if (*x) cudaFree(*x); } } guard{{&dd, &dw, &dv, &dn}};
-  ORB_CUDA_TRY(cudaMalloc(&dd, (size_t)n * 32));
-  ORB_CUDA_TRY(cudaMalloc(&dw, (size_t)n * 4));
-  ORB_CUDA_TRY(cudaMalloc(&dv, (size_t)n * 8));
-  ORB_CUDA_TRY(cudaMalloc(&dn, (size_t)n * 4));
+  { const int rc_pool = use_cached_pool(v->device); if (rc_pool) return rc_pool; }
+  TmpDevW bd, bw, bv, bn;
+  int rc0;
+  if ((rc0 = bd.alloc((size_t)n * 32)) || (rc0 = bw.alloc((size_t)n * 4)) || (rc0 = bv.alloc((size_t)n * 8)) ||
+      (rc0 = bn.alloc((size_t)n * 4)))
+    return rc0;
+  void *dd = bd.p, *dw = bw.p, *dv = bv.p, *dn = bn.p;
   ORB_CUDA_TRY(cudaMemcpy(dd, desc, (size_t)n * 32, cudaMemcpyHostToDevice));
   int rc = orb_gpu_vocabulary_transform_device(v, (const uint8_t*)dd, n, levelsup, (uint32_t*)dw, (double*)dv,
                                                (uint32_t*)dn, nullptr);

@@ -19,13 +19,6 @@ namespace orbgpu {
 constexpr int kGridCols = 64, kGridRows = 48;  // FRAME_GRID_COLS/ROWS, include/Frame.h:37-38
 constexpr int kCells = kGridCols * kGridRows;
 
-struct TmpDevW {
-  void* p = nullptr;
-  ~TmpDevW() { if (p) cudaFree(p); }
-  int alloc(size_t bytes) { ORB_CUDA_TRY(cudaMalloc(&p, bytes ? bytes : 16)); return ORB_GPU_OK; }
-  template <class T> T* as() { return (T*)p; }
-};
-
 __device__ __forceinline__ int hamming_rows(const uint4* a, const uint4* b) {
   const uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
   return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
@@ -156,6 +149,36 @@ __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int
   for (int k = lo; k < hi; ++k) { out[k] = run; run += in[k]; }
 }
 
+// ---- the kTopK best candidates of every query, sorted by (distance, position) -------------------
+// The ordered resolution below re-evaluates every query once per round; with its candidates pre-sorted a
+// round costs one thread and a handful of loads per query instead of a warp scan of the whole list.  A query
+// whose kTopK best are all taken falls back to the full scan (rare).  One warp per query, any number of blocks.
+constexpr int kTopK = 8;
+__global__ void __launch_bounds__(256)
+topk_entries_kernel(const int* __restrict__ offsets, const uint32_t* __restrict__ entries, int nq,
+                    uint2* __restrict__ topk /*[nq][kTopK]: (dist << 20 | position, entry)*/) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= nq) return;
+  const int beg = offsets[warp], end = offsets[warp + 1];
+  unsigned last = 0;
+  for (int t = 0; t < kTopK; ++t) {
+    unsigned best = 0xffffffffu;
+    for (int e = beg + lane; e < end; e += 32) {
+      const unsigned key = (((entries[e] >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
+      if ((t == 0 || key > last) && key < best) best = key;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0)
+      topk[(size_t)warp * kTopK + t] = make_uint2(best, best == 0xffffffffu ? 0u : entries[beg + (best & 0xfffffu)]);
+    if (best == 0xffffffffu) {
+      if (lane == 0) for (int u = t + 1; u < kTopK; ++u) topk[(size_t)warp * kTopK + u] = make_uint2(0xffffffffu, 0u);
+      break;
+    }
+    last = best;
+  }
+}
+
 // ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) on the 30 bin sizes
 __device__ inline void three_maxima(const int* hist, int* keep) {
   int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
@@ -176,7 +199,8 @@ __device__ inline void three_maxima(const int* hist, int* keep) {
 template <bool TOP2>
 __global__ void __launch_bounds__(1024)
 window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKeyPoint* __restrict__ kps, int nk,
-                      const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
+                      const int* __restrict__ offsets, const uint32_t* __restrict__ entries,
+                      const uint2* __restrict__ topk, float nnratio,
                       int ratio_rule, int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
                       int* __restrict__ claim_a, int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
                       int32_t* __restrict__ match_of_kp, int32_t* __restrict__ match_of_query,
@@ -195,24 +219,28 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
     for (int i = t; i < nq; i += T)
       if (prev[i] >= 0 && q[i].blocks) atomicMin(&minclaim[prev[i]], i);
     __syncthreads();
-    for (int i = warp; i < nq; i += nwarps) {
+    for (int i = t; i < nq; i += T) {
       const int beg = offsets[i], end = offsets[i + 1];
-      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position)
-      for (int e = beg + lane; e < end; e += 32) {
-        const uint32_t en = entries[e];
-        const int idx = (int)(en & 0xffffu);
+      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position) still free
+      const int nent = end - beg, ntop = min(nent, kTopK);
+      for (int u = 0; u < ntop; ++u) {
+        const uint2 c = topk[(size_t)i * kTopK + u];
+        const int idx = (int)(c.y & 0xffffu);
         if (blocked[idx] || minclaim[idx] < i) continue;  // keypoint already taken (:87-89)
-        const unsigned key = (((en >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
-        if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+        if (k1 == 0xffffffffu) { k1 = c.x; if (!TOP2) break; }
+        else { k2 = c.x; break; }
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
-        const unsigned lo = min(k1, o1), hi = max(k1, o1);
-        k2 = min(hi, min(k2, o2));
-        k1 = lo;
+      if (nent > kTopK && (k1 == 0xffffffffu || (TOP2 && k2 == 0xffffffffu))) {  // the best kTopK did not settle it
+        k1 = k2 = 0xffffffffu;
+        for (int e = beg; e < end; ++e) {
+          const uint32_t en = entries[e];
+          const int idx = (int)(en & 0xffffu);
+          if (blocked[idx] || minclaim[idx] < i) continue;
+          const unsigned key = (((en >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
+          if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+        }
       }
-      if (lane == 0) {
+      {
         int result = -1;
         if (k1 != 0xffffffffu) {
           const int best_dist = (int)(k1 >> 20);
@@ -441,7 +469,8 @@ triangulation_kernel(const OrbBucketQuery* __restrict__ q, int nq, const int32_t
 // Accepted choices are kept as per-target linked lists (head[], next[]).
 __global__ void __launch_bounds__(1024)
 init_resolve_kernel(const OrbKeyPoint* __restrict__ kps1, int nq, const OrbKeyPoint* __restrict__ kps2, int nk,
-                    const int* __restrict__ offsets, const uint32_t* __restrict__ entries, float nnratio,
+                    const int* __restrict__ offsets, const uint32_t* __restrict__ entries,
+                    const uint2* __restrict__ topk, float nnratio,
                     int th_low, int check_ori, int* __restrict__ claim_a, int* __restrict__ claim_b,
                     int* __restrict__ dist_a, int* __restrict__ dist_b, int* __restrict__ next,
                     int* __restrict__ head /*[nk]*/, int32_t* __restrict__ match12, int* __restrict__ nmatches) {
@@ -458,27 +487,33 @@ init_resolve_kernel(const OrbKeyPoint* __restrict__ kps1, int nq, const OrbKeyPo
     for (int i = t; i < nq; i += T)
       if (prev[i] >= 0) next[i] = atomicExch(&head[prev[i]], i);
     __syncthreads();
-    for (int i = warp; i < nq; i += nwarps) {
+    for (int i = t; i < nq; i += T) {
       const int beg = offsets[i], end = offsets[i + 1];
-      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position)
-      for (int e = beg + lane; e < end; e += 32) {
-        const uint32_t en = entries[e];
-        const int idx = (int)(en & 0xffffu), dist = (int)((en >> 16) & 0x1ffu);
+      unsigned k1 = 0xffffffffu, k2 = 0xffffffffu;  // two smallest (dist << 20 | position) still open to query i
+      const int nent = end - beg, ntop = min(nent, kTopK);
+      for (int u = 0; u < ntop; ++u) {
+        const uint2 c = topk[(size_t)i * kTopK + u];
+        const int idx = (int)(c.y & 0xffffu), dist = (int)(c.x >> 20);
         int taken = INT_MAX;  // vMatchedDistance[idx] as query i sees it
         for (int j = head[idx]; j >= 0; j = next[j])
           if (j < i) taken = min(taken, pdist[j]);
         if (taken <= dist) continue;  // :444-445
-        const unsigned key = ((unsigned)dist << 20) | (unsigned)(e - beg);
-        if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+        if (k1 == 0xffffffffu) k1 = c.x; else { k2 = c.x; break; }
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const unsigned o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
-        const unsigned lo = min(k1, o1), hi = max(k1, o1);
-        k2 = min(hi, min(k2, o2));
-        k1 = lo;
+      if (nent > kTopK && k2 == 0xffffffffu) {  // the best kTopK did not settle it: full scan
+        k1 = k2 = 0xffffffffu;
+        for (int e = beg; e < end; ++e) {
+          const uint32_t en = entries[e];
+          const int idx = (int)(en & 0xffffu), dist = (int)((en >> 16) & 0x1ffu);
+          int taken = INT_MAX;
+          for (int j = head[idx]; j >= 0; j = next[j])
+            if (j < i) taken = min(taken, pdist[j]);
+          if (taken <= dist) continue;
+          const unsigned key = ((unsigned)dist << 20) | (unsigned)(e - beg);
+          if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+        }
       }
-      if (lane == 0) {
+      {
         int result = -1, rdist = 0;
         if (k1 != 0xffffffffu) {
           const int best = (int)(k1 >> 20);
@@ -558,7 +593,7 @@ static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, c
   if (match_of_query) for (int i = 0; i < nq; ++i) match_of_query[i] = -1;
   if (nq == 0 || nk == 0) return ORB_GPU_OK;
   if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   int nkpad = 2;
   while (nkpad < nk) nkpad <<= 1;
   TmpDevW dq, dqd, dk, dkd, dur, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn, dsig, dmq;
@@ -596,15 +631,18 @@ static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, c
   window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), ur, grid, gate, dsig.as<float>(), dsorted.as<uint32_t>(), dcell.as<int>(), nullptr,
       doff.as<int>(), dent.as<uint32_t>());
+  TmpDevW dtop;
+  if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
+  topk_entries_kernel<<<blocks, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());
   if (top2)
     window_resolve_kernel<true><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
         dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
   else
     window_resolve_kernel<false><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+        dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
         dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
-  count_launch(5);
+  count_launch(6);
   ORB_CUDA_TRY(cudaGetLastError());
   ORB_CUDA_TRY(cudaMemcpy(match_of_kp, dmatch.p, (size_t)nk * 4, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(kp_blocked, dblk.p, (size_t)nk, cudaMemcpyDeviceToHost));
@@ -662,7 +700,7 @@ int orb_gpu_features_in_area(const OrbWindowQuery* q, int nq, const OrbKeyPoint*
   for (int i = 0; i <= nq; ++i) offsets[i] = 0;
   if (nq == 0 || nk == 0) return ORB_GPU_OK;
   if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   int nkpad = 2;
   while (nkpad < nk) nkpad <<= 1;
   TmpDevW dq, dqd, dk, dkd, dsorted, dcell, dcnt, doff, dent;
@@ -738,7 +776,7 @@ int orb_gpu_search_by_bow(const OrbBucketQuery* q, int nq, const int32_t* cand2,
     wq[i].valid = 1;
     wq[i].blocks = 1;
   }
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   TmpDevW dq, dwq, dc, d1, dk2, d2, doff, dent, dblk, dca, dcb, dmin, dmatch, dmq, dn;
   const int total = offsets[nq];
   if ((rc = dq.alloc((size_t)nq * sizeof(OrbBucketQuery))) || (rc = dwq.alloc((size_t)nq * sizeof(OrbWindowQuery))) ||
@@ -759,10 +797,13 @@ int orb_gpu_search_by_bow(const OrbBucketQuery* q, int nq, const int32_t* cand2,
   else ORB_CUDA_TRY(cudaMemset(dblk.p, 0, (size_t)n2));
   bucket_entries_kernel<<<(nq * 32 + 255) / 256, 256>>>(dq.as<OrbBucketQuery>(), nq, dc.as<int32_t>(), d1.as<uint4>(),
                                                         d2.as<uint4>(), doff.as<int>(), dent.as<uint32_t>());
+  TmpDevW dtop;
+  if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
+  topk_entries_kernel<<<(nq * 32 + 255) / 256, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());
   window_resolve_kernel<true><<<1, 1024>>>(dwq.as<OrbWindowQuery>(), nq, dk2.as<OrbKeyPoint>(), n2, doff.as<int>(),
-      dent.as<uint32_t>(), nnratio, 1, th_accept, check_orientation, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
+      dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 1, th_accept, check_orientation, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
       dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
-  count_launch(2);
+  count_launch(3);
   ORB_CUDA_TRY(cudaGetLastError());
   std::vector<int32_t> mq((size_t)nq);
   ORB_CUDA_TRY(cudaMemcpy(mq.data(), dmq.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
@@ -797,7 +838,7 @@ int orb_gpu_search_for_triangulation(const OrbBucketQuery* q, int nq, const int3
     P.sigma2_2[i] = i < nlevels ? level_sigma2_2[i] : 0.f;
   }
   P.only_stereo = only_stereo; P.check_ori = check_orientation; P.th_low = ORB_GPU_TH_LOW;
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   TmpDevW dq, dc, dk1, d1, du1, dk2, d2, du2, dskip, dbins, dmq, dn;
   if ((rc = dq.alloc((size_t)nq * sizeof(OrbBucketQuery))) || (rc = dc.alloc((size_t)ncand2 * 4)) ||
       (rc = dk1.alloc((size_t)n1 * sizeof(OrbKeyPoint))) || (rc = d1.alloc((size_t)n1 * 32)) ||
@@ -850,7 +891,7 @@ int orb_gpu_search_for_initialization(const OrbKeyPoint* kps1, const uint8_t* de
     w.min_level = kps1[i].octave; w.max_level = kps1[i].octave;  // GetFeaturesInArea(x, y, windowSize, level1, level1)
     w.valid = 1;
   }
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   int nkpad = 2;
   while (nkpad < nk) nkpad <<= 1;
   TmpDevW dq, dqd, dk1, dk, dkd, dsorted, dcell, dcnt, doff, dent, dca, dcb, dda, ddb, dnext, dhead, dmatch, dn;
@@ -883,8 +924,11 @@ int orb_gpu_search_for_initialization(const OrbKeyPoint* kps1, const uint8_t* de
   window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(),
       dent.as<uint32_t>());
+  TmpDevW dtop;
+  if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
+  topk_entries_kernel<<<blocks, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());
   init_resolve_kernel<<<1, 1024>>>(dk1.as<OrbKeyPoint>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-      dent.as<uint32_t>(), nnratio, ORB_GPU_TH_LOW, check_orientation, dca.as<int>(), dcb.as<int>(), dda.as<int>(),
+      dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, ORB_GPU_TH_LOW, check_orientation, dca.as<int>(), dcb.as<int>(), dda.as<int>(),
       ddb.as<int>(), dnext.as<int>(), dhead.as<int>(), dmatch.as<int32_t>(), dn.as<int>());
   count_launch(5);
   ORB_CUDA_TRY(cudaGetLastError());
@@ -901,7 +945,7 @@ int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const
       (nl > 0 && (!kl || !dl || !best_idx_r || !best_dist)) || (nr > 0 && (!kr || !dr)) || nr > 65535)
     return ORB_GPU_ERR_ARG;
   if (nl == 0) return ORB_GPU_OK;
-  ORB_CUDA_TRY(cudaSetDevice(device));
+  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
   TmpDevW a, b, c, d, e, f, g;
   int rc;
   if ((rc = a.alloc((size_t)nl * sizeof(OrbKeyPoint))) || (rc = b.alloc((size_t)nl * 32)) ||

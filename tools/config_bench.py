@@ -84,6 +84,54 @@ dt = timed(stereo_pair, 50, warm=5)
 bi, bd = stereo_pair()
 out["config2_kitti_stereo_pair"] = {"ms_per_pair_host_api": dt * 1e3, "pairs_per_s": 1 / dt,
                                     "left_matches": int((bi >= 0).sum())}
+BF, B_ = np.float32(386.1448), np.float32(386.1448) / np.float32(718.856)
+
+
+def stereo_pair_full():
+    """extraction of both images + the whole Frame::ComputeStereoMatches (Hamming + sub-pixel + median)"""
+    kl, dl = exl(left)
+    kr, dr = exr(right)
+    return m.ComputeStereoMatches(exl, exr, kl, dl, kr, dr, BF, B_)
+
+
+dt = timed(stereo_pair_full, 50, warm=5)
+ur, dp = stereo_pair_full()
+kl, dl = exl(left)
+kr, dr = exr(right)
+dt_sm = timed(lambda: m.ComputeStereoMatches(exl, exr, kl, dl, kr, dr, BF, B_), 50, warm=5)
+out["config2_kitti_stereo_pair_full"] = {"ms_per_pair_host_api": dt * 1e3, "pairs_per_s": 1 / dt,
+                                         "compute_stereo_matches_ms": dt_sm * 1e3, "depth_points": int((ur >= 0).sum())}
+
+# batched stereo on the device: 128 pairs interleaved in one batch (left = 2i, right = 2i+1)
+NP = 128
+cap2 = 2000 + 24
+lr = np.stack([left, right] * NP)
+d_lr = torch.from_numpy(lr).cuda()
+exb = orb.ORBextractor(2000, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=2 * NP)
+dk = torch.empty((2 * NP, cap2, 28), dtype=torch.uint8, device="cuda")
+dd = torch.empty((2 * NP, cap2, 32), dtype=torch.uint8, device="cuda")
+dn = torch.zeros(2 * NP, dtype=torch.int32, device="cuda")
+ds = torch.zeros(1, dtype=torch.int32, device="cuda")
+du = torch.empty((NP, cap2), dtype=torch.float32, device="cuda")
+dz = torch.empty((NP, cap2), dtype=torch.float32, device="cuda")
+dsad = torch.empty((NP, cap2), dtype=torch.int32, device="cuda")
+st = torch.cuda.current_stream().cuda_stream
+
+
+def stereo_batch(with_extract=True):
+    if with_extract:
+        exb.extract_batch_device(d_lr.data_ptr(), 2 * NP, W, H, W, W * H, dk.data_ptr(), dd.data_ptr(), dn.data_ptr(),
+                                 ds.data_ptr(), st)
+    assert L.orb_gpu_stereo_matches_device(exb._h, 0, 2, exb._h, 1, 2, NP, dk.data_ptr(), dd.data_ptr(), dn.data_ptr(),
+                                           cap2, dk.data_ptr(), dd.data_ptr(), dn.data_ptr(), cap2, float(BF),
+                                           float(B_), du.data_ptr(), dz.data_ptr(), dsad.data_ptr(), st) == 0
+
+
+dt_all = timed(stereo_batch, 5, warm=2)
+dt_sm = timed(lambda: stereo_batch(False), 10, warm=2)
+out["config2_kitti_stereo_batch128_device"] = {"pairs_per_s": NP / dt_all, "ms_per_batch": dt_all * 1e3,
+                                               "stereo_matches_ms_per_batch": dt_sm * 1e3,
+                                               "depth_points_per_pair": float((du[0, :int(dn[0])] >= 0).sum())}
 out["config2_kitti_batch256"] = device_batch("kitti", 2000, 256)
 
 # config 3: EuRoC 1024 frames, 1200 features (one GPU's worth; frames shard across GPUs with no collective)
@@ -116,6 +164,38 @@ def sbp():
 dt = timed(sbp, 50, warm=5)
 out["config4_search_by_projection"] = {"ms_per_call_host_api": dt * 1e3, "map_points": M, "keypoints": int(nk),
                                        "matches": int(sbp()[0])}
+
+# P1 / next rows: one call each on realistic sizes (host-pointer C ABI, allocations and copies included)
+rng = np.random.default_rng(5)
+tree = synth.make_vocabulary(10, 5, 1)
+voc = orb.ORBVocabulary(tree)
+dt = timed(lambda: voc.transform_features(desc, 4), 50, warm=5)
+d_desc = torch.from_numpy(np.tile(desc, (64, 1))).cuda()
+nf = d_desc.shape[0]
+dw = torch.empty(nf, dtype=torch.int32, device="cuda"); dv = torch.empty(nf, dtype=torch.float64, device="cuda")
+dnid = torch.empty(nf, dtype=torch.int32, device="cuda")
+dt_dev = timed(lambda: L.orb_gpu_vocabulary_transform_device(voc._h, d_desc.data_ptr(), nf, 4, dw.data_ptr(),
+                                                             dv.data_ptr(), dnid.data_ptr(), st), 20, warm=3)
+out["n3_vocabulary_transform"] = {"nodes": int(len(tree["word_id"])), "features": int(nk),
+                                  "ms_per_frame_host_api": dt * 1e3, "device_features_per_s": nf / dt_dev}
+_, fv1 = voc.transform(desc, 2)
+perm = rng.permutation(nk)
+desc2 = synth.flip_bits(desc[perm], rng.integers(0, 45, nk), rng)
+_, fv2 = voc.transform(desc2, 2)
+good = np.ones(nk, bool)
+mb = orb.ORBmatcher(0.7)
+dt = timed(lambda: mb.SearchByBoW(dict(kps=kps, desc=desc, feat_vec=fv1), dict(kps=kps[perm], desc=desc2, feat_vec=fv2),
+                                  good), 30, warm=3)
+out["m6_search_by_bow"] = {"ms_per_call_host_api": dt * 1e3, "features": int(nk)}
+prev = np.stack([kps["x"], kps["y"]], 1).astype(np.float32)
+k2 = kps[perm].copy()
+dt = timed(lambda: orb.ORBmatcher(0.9).SearchForInitialization(dict(kps=kps, desc=desc), dict(kps=k2, desc=desc2, grid=grid),
+                                                              prev.copy(), 100), 30, warm=3)
+out["m7_search_for_initialization"] = {"ms_per_call_host_api": dt * 1e3, "features": int(nk)}
+lists = [synth.flip_bits(np.repeat(desc[i:i + 1], n, 0), rng.integers(0, 40, n), rng)
+         for i, n in enumerate(rng.integers(2, 30, 2000))]
+dt = timed(lambda: mb.ComputeDistinctiveDescriptors(lists), 10, warm=2)
+out["n4_distinctive_descriptors"] = {"ms_per_2000_points_host_api": dt * 1e3}
 
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 with open(os.path.join(ROOT, "gpurun_out", "configs.json"), "w") as f:
