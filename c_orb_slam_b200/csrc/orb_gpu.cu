@@ -102,6 +102,12 @@ struct OrbGpuExtractor {
   // the kernels of chunk i (one copy stream per direction, events per chunk)
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
   std::vector<cudaEvent_t> ev_in, ev_done;
+  // single-chunk host calls (one frame, a stereo pair, a small batch) are launch-bound: the kernel sequence
+  // is captured into a CUDA graph on the second call with the same geometry and buffers and replayed after
+  std::vector<long long> graph_key, graph_seen;
+  cudaGraphExec_t graph_exec = nullptr;
+  int graph_nlaunch = 0;
+  int plan_generation = 0;
 };
 
 // Frames per chunk of the host-pointer path: a quarter of the batch, between 32 and 128 (small chunks
@@ -110,6 +116,31 @@ static int host_chunk(int nb) {
   static const int forced = [] { const char* e = getenv("ORB_GPU_HOST_CHUNK"); return e ? atoi(e) : 0; }();
   if (forced > 0) return forced;
   return std::max(32, std::min(128, (nb + 3) / 4));
+}
+
+static bool graphs_enabled() {
+  static const bool on = [] { const char* e = getenv("ORB_GPU_NO_GRAPH"); return !(e && atoi(e)); }();
+  return on;
+}
+
+// Chunk boundaries of one host-pointer batch: [0, b1, b2, ..., nb].  ORB_GPU_HOST_SCHEDULE="a,b,c" gives the
+// chunk sizes explicitly (the last one repeats) for experiments.
+static std::vector<int> host_schedule(int nb) {
+  std::vector<int> b(1, 0);
+  static const std::vector<int> forced = [] {
+    std::vector<int> v;
+    const char* e = getenv("ORB_GPU_HOST_SCHEDULE");
+    while (e && *e) { v.push_back(atoi(e)); e = strchr(e, ','); if (e) ++e; }
+    return v;
+  }();
+  if (!forced.empty()) {
+    for (size_t i = 0; b.back() < nb; ++i)
+      b.push_back(std::min(nb, b.back() + std::max(1, forced[std::min(i, forced.size() - 1)])));
+    return b;
+  }
+  const int c = host_chunk(nb);
+  while (b.back() < nb) b.push_back(std::min(nb, b.back() + c));
+  return b;
 }
 
 // Plan / scratch of the frames [f0, ...) of a batch: every per-frame array advanced by f0 frames.
@@ -279,6 +310,7 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
   h->sc.sel = (uint32_t*)h->sel.p; h->sc.sel_cnt = (int*)h->sel_cnt.p;
   h->sc.cand_cnt = (int*)h->cand_cnt.p; h->sc.status = (int*)h->status.p;
   h->plan = p;
+  ++h->plan_generation;
   h->plan_w = w; h->plan_h = ht; h->plan_batch = batch;
   h->have_result = false;
   return ORB_GPU_OK;
@@ -351,6 +383,7 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   cudaStreamSynchronize(h->s_h2d); cudaStreamSynchronize(h->s_d2h);
+  if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
   cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
@@ -462,8 +495,8 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       return rc;
     const Plan& p = h->plan;
     const LevelGeom& l0 = p.lv[0];
-    const int kHostChunk = host_chunk(nb);
-    const int nchunks = (nb + kHostChunk - 1) / kHostChunk;
+    const std::vector<int> bounds = host_schedule(nb);
+    const int nchunks = (int)bounds.size() - 1;
     while ((int)h->ev_in.size() < nchunks) {
       cudaEvent_t a = nullptr, b = nullptr;
       ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -481,14 +514,62 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
     if ((rc = h->stage.ensure((size_t)(nb - 1) * frame_stride + frame_bytes + 16))) return rc;
     uint8_t* stage = (uint8_t*)h->stage.p;
     const bool alias = (stride & 3) == 0 && (frame_stride & 3) == 0;
+    if (nchunks == 1 && !h->timing && graphs_enabled()) {
+      // one chunk: everything in order on the compute stream, kernels replayed from a graph
+      OrbKeyPoint* dk = (OrbKeyPoint*)h->out_kps.p;
+      uint8_t* dd = (uint8_t*)h->out_desc.p;
+      int* dn = (int*)h->out_n.p;
+      ORB_CUDA_TRY(cudaMemcpyAsync(stage, frames + (size_t)f0 * frame_stride, (size_t)(nb - 1) * frame_stride + frame_bytes,
+                                   cudaMemcpyHostToDevice, s));
+      Plan pc = p;
+      if (alias) { pc.lv[0].img = stage; pc.lv[0].pitch = (int)stride; pc.lv[0].frame_stride = (long long)frame_stride; }
+      auto enqueue = [&]() -> int {
+        if (!alias)
+          for (int f = 0; f < nb; ++f)
+            ORB_CUDA_TRY(cudaMemcpy2DAsync(pc.lv[0].img + (size_t)f * pc.lv[0].frame_stride, pc.lv[0].pitch,
+                                           stage + (size_t)f * frame_stride, stride, width, height,
+                                           cudaMemcpyDeviceToDevice, s));
+        return run_pipeline(h, pc, h->sc, nb, dk, dd, capacity, dn, s, false);
+      };
+      const std::vector<long long> key = {nb, width, height, (long long)stride, (long long)frame_stride, capacity,
+                                          h->plan_generation, (long long)(uintptr_t)stage, (long long)(uintptr_t)dk,
+                                          (long long)(uintptr_t)dd, (long long)(uintptr_t)dn};
+      if (h->graph_exec && key == h->graph_key) {
+        ORB_CUDA_TRY(cudaGraphLaunch(h->graph_exec, s));
+        count_launch(h->graph_nlaunch);
+      } else if (key == h->graph_seen) {  // second call with these buffers: capture, then replay from now on
+        if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; }
+        cudaGraph_t g = nullptr;
+        const long long before = g_launches.load();
+        ORB_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+        rc = enqueue();
+        cudaError_t e = cudaStreamEndCapture(s, &g);
+        if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+        if (e != cudaSuccess) { set_last_error("cudaStreamEndCapture", e); return ORB_GPU_ERR_CUDA; }
+        e = cudaGraphInstantiate(&h->graph_exec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) { h->graph_exec = nullptr; set_last_error("cudaGraphInstantiate", e); return ORB_GPU_ERR_CUDA; }
+        h->graph_nlaunch = (int)(g_launches.load() - before);
+        h->graph_key = key;
+        ORB_CUDA_TRY(cudaGraphLaunch(h->graph_exec, s));
+      } else {
+        h->graph_seen = key;
+        if ((rc = enqueue())) return rc;
+      }
+      ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0, dn, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, s));
+      ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)f0 * capacity, dk, (size_t)nb * capacity * sizeof(OrbKeyPoint),
+                                   cudaMemcpyDeviceToHost, s));
+      ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)f0 * capacity * 32, dd, (size_t)nb * capacity * 32,
+                                   cudaMemcpyDeviceToHost, s));
+    } else {
     for (int c = 0; c < nchunks; ++c) {  // all queued on the H2D stream, one event per chunk
-      const int c0 = c * kHostChunk, cn = std::min(kHostChunk, nb - c0);
+      const int c0 = bounds[c], cn = bounds[c + 1] - c0;
       ORB_CUDA_TRY(cudaMemcpyAsync(stage + (size_t)c0 * frame_stride, frames + (size_t)(f0 + c0) * frame_stride,
                                    (size_t)(cn - 1) * frame_stride + frame_bytes, cudaMemcpyHostToDevice, h->s_h2d));
       ORB_CUDA_TRY(cudaEventRecord(h->ev_in[c], h->s_h2d));
     }
     for (int c = 0; c < nchunks; ++c) {  // kernels of chunk c, then its results leave on the D2H stream
-      const int c0 = c * kHostChunk, cn = std::min(kHostChunk, nb - c0);
+      const int c0 = bounds[c], cn = bounds[c + 1] - c0;
       OrbKeyPoint* dk = (OrbKeyPoint*)h->out_kps.p + (size_t)c0 * capacity;
       uint8_t* dd = (uint8_t*)h->out_desc.p + (size_t)c0 * capacity * 32;
       int* dn = (int*)h->out_n.p + c0;
@@ -512,6 +593,7 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
                                    cudaMemcpyDeviceToHost, h->s_d2h));
       ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)(f0 + c0) * capacity * 32, dd, (size_t)cn * capacity * 32,
                                    cudaMemcpyDeviceToHost, h->s_d2h));
+    }
     }
     int dev_status = 0;
     ORB_CUDA_TRY(cudaMemcpyAsync(&dev_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToHost, s));

@@ -21,3 +21,16 @@ t0 = time.perf_counter()
 for _ in range(10): step()
 dt = (time.perf_counter() - t0) / 10
 print("chunk", os.environ.get("ORB_GPU_HOST_CHUNK", "default"), "ms", round(dt * 1e3, 3), "fps", round(B / dt), "kp", int(hn.sum()))
+if os.environ.get("E2E_BW"):
+    d = torch.empty_like(fr, device="cuda")
+    for _ in range(2): d.copy_(fr, non_blocking=True)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(5): d.copy_(fr, non_blocking=True)
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 5
+    print("H2D pinned %.1f MB: %.3f ms = %.1f GB/s" % (fr.numel() / 1e6, dt * 1e3, fr.numel() / dt / 1e9))
+    dk = torch.empty_like(hk, device="cuda")
+    for _ in range(2): hk.copy_(dk, non_blocking=True)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(5): hk.copy_(dk, non_blocking=True)
+    torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 5
+    print("D2H pinned %.1f MB: %.3f ms = %.1f GB/s" % (hk.numel() / 1e6, dt * 1e3, hk.numel() / dt / 1e9))
