@@ -422,6 +422,46 @@ __device__ __forceinline__ int block_exclusive_scan(int* a, int n, int* s_warp /
   return total;
 }
 
+// the same for two arrays at once (one set of barriers): returns total of a, *total_b that of b
+__device__ __forceinline__ int block_exclusive_scan2(int* a, int* b, int n, int* s_warp /*>=66 ints*/, int* total_b) {
+  const int T = blockDim.x, t = threadIdx.x;
+  const int chunk = (n + T - 1) / T;
+  const int lo = min(t * chunk, n), hi = min(lo + chunk, n);
+  int sa = 0, sb = 0;
+  for (int k = lo; k < hi; ++k) { sa += a[k]; sb += b[k]; }
+  int ia = sa, ib = sb;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int va = __shfl_up_sync(0xffffffffu, ia, o), vb = __shfl_up_sync(0xffffffffu, ib, o);
+    if ((t & 31) >= o) { ia += va; ib += vb; }
+  }
+  if ((t & 31) == 31) { s_warp[t >> 5] = ia; s_warp[33 + (t >> 5)] = ib; }
+  __syncthreads();
+  if (t < 32) {
+    const int nw = T >> 5;
+    const int wa = t < nw ? s_warp[t] : 0, wb = t < nw ? s_warp[33 + t] : 0;
+    int xa = wa, xb = wb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int va = __shfl_up_sync(0xffffffffu, xa, o), vb = __shfl_up_sync(0xffffffffu, xb, o);
+      if (t >= o) { xa += va; xb += vb; }
+    }
+    if (t < nw) { s_warp[t] = xa - wa; s_warp[33 + t] = xb - wb; }
+    if (t == nw - 1) { s_warp[32] = xa; s_warp[65] = xb; }
+  }
+  __syncthreads();
+  int ra = s_warp[t >> 5] + ia - sa, rb = s_warp[33 + (t >> 5)] + ib - sb;
+  for (int k = lo; k < hi; ++k) {
+    const int va = a[k], vb = b[k];
+    a[k] = ra; b[k] = rb;
+    ra += va; rb += vb;
+  }
+  const int total = s_warp[32];
+  *total_b = s_warp[65];
+  __syncthreads();
+  return total;
+}
+
 __device__ __forceinline__ void bitonic_step(uint64_t* a, int i, int j, int k) {
   const int l = i | j;
   const uint64_t x = a[i], y = a[l];
@@ -485,7 +525,7 @@ __host__ __device__ __forceinline__ int qt_ncap(int quota, int n_ini) {
 }
 __device__ __forceinline__ int pow2ceil_dev(int v) { return v <= 1 ? 1 : 1 << (32 - __clz(v - 1)); }
 
-__global__ void __launch_bounds__(kQtThreads)
+__global__ void __launch_bounds__(kQtThreads, 3)
 quadtree_kernel(Plan p, Scratch sc, int nframes) {
   extern __shared__ __align__(16) uint8_t smem[];
   // one block per (level, frame); the big levels are scheduled first so the small ones fill the tail
@@ -508,7 +548,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   int* s_sv = s_cb + ncap;                                       // [ncap] survivor flags/ranks
   int* s_bnd = s_sv + ncap;                                      // [3*ncap] rank-ordered scratch
   int* s_cell = s_bnd + 3 * ncap;                                // [ncells+1]
-  int* s_warp = s_cell + ncells + 1;                             // [40]
+  int* s_warp = s_cell + ncells + 1;                             // [72]
   __shared__ int s_misc[8];
 
   const uint32_t* cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
@@ -580,9 +620,9 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
           const uint32_t bin = code >> bshift;
           const uint32_t old = atomicAdd(&s_bin[bin >> 1], (bin & 1) ? 0x10000u : 1u);
           my_code[q] = code;
-          my_rank[q] = (bin & 1) ? old >> 16 : old & 0xffffu;
+          my_rank[q] = ((bin & 1) ? old >> 16 : old & 0xffffu) | ((uint32_t)resp << 24);  // response rides along
         } else {
-          keys[arr] = ((uint64_t)code << 32) | (uint32_t)arr;
+          keys[arr] = ((uint64_t)code << 32) | (uint32_t)arr | ((uint32_t)resp << 24);
         }
       }
     }
@@ -631,7 +671,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
       if (arrival < C) {
         const uint32_t bin = my_code[q] >> bshift;
         const uint32_t base = (s_bin[bin >> 1] >> ((bin & 1) * 16)) & 0xffffu;
-        s_bkt[base + my_rank[q]] = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
+        s_bkt[base + (my_rank[q] & 0xffffu)] = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
       }
     }
     __syncthreads();
@@ -645,7 +685,8 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         const uint32_t mine = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
         int rank = 0;
         for (int k = bs; k < be; ++k) rank += s_bkt[k] < mine;
-        keys[bs + rank] = ((uint64_t)my_code[q] << 32) | (uint32_t)arrival;
+        // low word: arrival | response << 24 (codes are distinct, so the low word never decides the order)
+        keys[bs + rank] = ((uint64_t)my_code[q] << 32) | (uint32_t)arrival | (my_rank[q] & 0xff000000u);
       }
     }
     __syncthreads();
@@ -676,25 +717,24 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   while (true) {
     const int prev_n = n;
     // -- choose the nodes to split and their creation bases --
-    for (int i = t; i < n; i += T) { s_nch[i] = 0; s_cb[i] = 0; s_sv[i] = 1; }
-    __syncthreads();
-    int K = 0;
+    int K = 0, nsurv = 0;
     if (!careful) {
       for (int i = t; i < n; i += T) {
         const QtNode nd = cur[i];
+        int nch = 0, sv = 1;
         if (nd.end - nd.start > 1 && (nd.depth_new & 0xff) < kCodeDepth) {
           int b[5];
           child_bounds(keys, nd, b);
-          s_nch[i] = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
-          s_sv[i] = 0;
+          nch = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
+          sv = 0;
         }
+        s_nch[i] = nch; s_cb[i] = nch; s_sv[i] = sv;
       }
       __syncthreads();
-      for (int i = t; i < n; i += T) s_cb[i] = s_nch[i];
-      __syncthreads();
-      K = block_exclusive_scan(s_cb, n, s_warp);
+      K = block_exclusive_scan2(s_cb, s_sv, n, s_warp, &nsurv);
     } else {
       // expandable nodes of the previous round, largest first, newest first among equals
+      for (int i = t; i < n; i += T) { s_nch[i] = 0; s_cb[i] = 0; s_sv[i] = 1; }
       if (t == 0) s_misc[2] = 0;
       __syncthreads();
       for (int i = t; i < n; i += T) {
@@ -744,10 +784,10 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         s_cb[pos] = r_scan[j];
         s_sv[pos] = 0;
       }
+      __syncthreads();
+      nsurv = block_exclusive_scan(s_sv, n, s_warp);
     }
-    __syncthreads();
     // -- survivors keep their order behind the new children --
-    const int nsurv = block_exclusive_scan(s_sv, n, s_warp);
     if (t == 0) s_misc[4] = 0;
     __syncthreads();
     int n_exp_local = 0;
@@ -792,9 +832,8 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
     // max response, earliest arrival among equals: maximise (resp << 32) | ~arrival
     unsigned long long best = 0;
     for (int k = nd.start + lane; k < nd.end; k += 32) {
-      const uint32_t arrival = (uint32_t)keys[k];
-      const uint32_t pv = pay[arrival];
-      const unsigned long long cand = ((unsigned long long)(pv >> 24) << 32) | (uint32_t)(~arrival);
+      const uint32_t low = (uint32_t)keys[k], arrival = low & 0xffffffu;
+      const unsigned long long cand = ((unsigned long long)(low >> 24) << 32) | (uint32_t)(~arrival);
       best = cand > best ? cand : best;
     }
 #pragma unroll
@@ -814,7 +853,7 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
   const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
   return (size_t)kQtSmemKeys * 12 + (size_t)(kQtBins / 2 + 4) * 4 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
-         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 40) * 4 + 64;
+         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 72) * 4 + 64;
 }
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
@@ -1030,6 +1069,9 @@ constexpr int kOdReach = 18;                      // |rotated tap| <= ceil(13 * 
 constexpr int kOdRows = 2 * kOdReach + 1;         // 37 rows of the blurred level around the keypoint
 constexpr int kOdWords = (kOdRows + 3 + 3) / 4;   // 10 words per row: 37 px + alignment offset (<= 3)
 
+constexpr int kIcRows = 2 * kHalfPatch + 1;       // 31 rows of the level image around the keypoint (IC_Angle)
+constexpr int kIcWords = 9;                       // 31 px + alignment offset (<= 3) -> 9 words; odd: conflict-free rows
+
 __device__ __forceinline__ int round_half_even(float v) {
   // cvRound for |v| < 2^22: adding 1.5 * 2^23 leaves the rounded integer in the mantissa
   return __float_as_int(__fadd_rn(v, 12582912.f)) - 0x4B400000;
@@ -1038,15 +1080,18 @@ __device__ __forceinline__ int round_half_even(float v) {
 // One block = 32 consecutive output slots (level, rank in the level's selection) of one frame, one warp
 // per slot, 4 slots per warp.  IC_Angle: lane = patch column u, the rows of the disc that contain it
 // are |v| <= umax[|u|] (the disc is symmetric), 31 coalesced byte loads, shuffle reduction.
-__global__ void __launch_bounds__(kOdWarps * 32)
+__global__ void __launch_bounds__(kOdWarps * 32, 5)
 orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
                    int capacity, int* __restrict__ n_out) {
   __shared__ float4 s_pat[256];
   __shared__ uint32_t s_tile[kOdWarps][kOdRows * kOdWords];
-  __shared__ int s_cnt[kMaxLevels], s_before[kMaxLevels + 1];
+  __shared__ uint32_t s_ic[kOdWarps][kIcRows * kIcWords];  // unblurred 31-row patch, 9 aligned words per row
+  __shared__ int s_cnt[kMaxLevels], s_before[kMaxLevels + 1], s_base[kMaxLevels];
   const int f = blockIdx.y;
   s_pat[threadIdx.x] = g_pattern[threadIdx.x];
   if (threadIdx.x < p.nlevels) s_cnt[threadIdx.x] = sc.sel_cnt[f * p.nlevels + threadIdx.x];
+  if (threadIdx.x < kMaxLevels)  // first slot of every level (unused levels never match)
+    s_base[threadIdx.x] = threadIdx.x < p.nlevels ? p.lv[threadIdx.x].slot_base : 0x7fffffff;
   __syncthreads();
   if (threadIdx.x == 0) {
     int run = 0;
@@ -1056,17 +1101,34 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int u = lane - kHalfPatch;
-  const int vm = lane < 31 ? p.umax[u < 0 ? -u : u] : -1;  // rows |v| <= vm of column u are inside the disc
+  // IC_Angle with lane = patch row v: the row's 31 pixels as 8 aligned words, columns |u| <= umax[|v|] kept by a
+  // byte mask, m10 / row sum by two IDP.4A per word (weights u = 4k+j-15 as signed bytes / all ones)
+  const int v_row = lane - kHalfPatch;
+  const int dmax = lane < 31 ? p.umax[v_row < 0 ? -v_row : v_row] : -1;
+  uint32_t ic_mask[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int uu = 4 * k + j - kHalfPatch;
+      if ((uu < 0 ? -uu : uu) <= dmax) m |= 0xffu << (8 * j);
+    }
+    ic_mask[k] = m;
+  }
   uint32_t* my_tile = s_tile[warp];
   const int tile_r = lane / kOdWords, tile_c = lane - tile_r * kOdWords;  // this lane's (row, word) inside a 3-row step
   const unsigned tile_dst = (unsigned)__cvta_generic_to_shared(my_tile + tile_r * kOdWords + tile_c);
+  uint32_t* my_ic = s_ic[warp];
+  const int ic_r = lane / kIcWords, ic_c = lane - ic_r * kIcWords;  // (row, word) inside a 3-row step, lanes 0..26
+  const unsigned ic_dst = (unsigned)__cvta_generic_to_shared(my_ic + ic_r * kIcWords + ic_c);
 
   for (int it = 0; it < kOdSlotsPerWarp; ++it) {
     const int slot = blockIdx.x * kOdSlotsPerBlock + it * kOdWarps + warp;
     if (slot >= p.slots_per_frame) break;
     int level = 0;
-    while (level + 1 < p.nlevels && slot >= p.lv[level + 1].slot_base) ++level;
+#pragma unroll
+    for (int l = 1; l < kMaxLevels; ++l) level += slot >= s_base[l];
     const LevelGeom& g = p.lv[level];
     const int rank = slot - g.slot_base;
     if (rank >= s_cnt[level]) continue;
@@ -1082,6 +1144,18 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     // The rotated BRIEF taps stay within 18 px of the keypoint (|x|,|y| <= 13): the 37 x 37 window of the
     // blurred level is staged in shared memory with coalesced word copies (10 words per row, issued now
     // so they fly during the orientation pass); the 512 byte gathers then hit shared memory, not L1/L2.
+    const uint8_t* img = g.img + (size_t)f * g.frame_stride;
+    const int ic_xal = (cx - kHalfPatch) & ~3;
+    {  // unblurred 31 x 36-byte patch for IC_Angle: 27 lanes copy 3 rows x 9 words per step, own commit group
+      const uint8_t* src = img + (size_t)(cy - kHalfPatch + ic_r) * g.pitch + ic_xal + 4 * ic_c;
+      unsigned dst = ic_dst;
+      const int step = 3 * g.pitch;
+#pragma unroll
+      for (int r0 = 0; r0 < kIcRows; r0 += 3, src += step, dst += 3 * kIcWords * 4)
+        if (lane < 27 && r0 + ic_r < kIcRows)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
     {
       const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
       const int xal = (cx - kOdReach) & ~3;
@@ -1097,17 +1171,27 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     }
 
     // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc (:77-104)
-    const uint8_t* img = g.img + (size_t)f * g.frame_stride;
-    const unsigned o0 = (unsigned)((cy - kHalfPatch) * g.pitch + cx + u);
-    int sv = 0, s1 = 0;
+    int m10 = 0, m01 = 0;
+    asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // the unblurred patch has landed (the blurred one may still fly)
+    __syncwarp();
+    if (lane < 31) {
+      const uint32_t* wp = my_ic + lane * kIcWords;
+      const unsigned sh = (unsigned)((cx - kHalfPatch) & 3) * 8;
+      uint32_t w[9];
 #pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-      int val = 0;
-      if ((v < 0 ? -v : v) <= vm) val = (int)__ldg(img + (o0 + (unsigned)((v + kHalfPatch) * g.pitch)));
-      sv += val;
-      s1 += v * val;
+      for (int k = 0; k < 9; ++k) w[k] = wp[k];
+      int srow = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint32_t x = __funnelshift_r(w[k], w[k + 1], sh) & ic_mask[k];
+        // signed weights (4k-15 .. 4k-12) as packed bytes
+        const int wu = (int)(((uint32_t)(uint8_t)(int8_t)(4 * k - 15)) | ((uint32_t)(uint8_t)(int8_t)(4 * k - 14) << 8) |
+                             ((uint32_t)(uint8_t)(int8_t)(4 * k - 13) << 16) | ((uint32_t)(uint8_t)(int8_t)(4 * k - 12) << 24));
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(wu));
+        srow = (int)__dp4a(x, 0x01010101u, (unsigned)srow);
+      }
+      m01 = v_row * srow;
     }
-    int m10 = u * sv, m01 = s1;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       m10 += __shfl_xor_sync(0xffffffffu, m10, o);
