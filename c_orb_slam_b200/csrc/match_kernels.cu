@@ -125,6 +125,119 @@ bruteforce_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// brute force on the tensor cores (legacy IMMA path of sm_100a: mma.sync m16n8k32 s8 x u8 -> s32)
+// ---------------------------------------------------------------------------------------------
+// With the query bits expanded to bytes a' in {-1,+1} and the database bits to bytes b in {0,1},
+//   S = sum_k a'_k * b_k = |q & d| - |~q & d|   and   hamming(q, d) = popc(q) - S,
+// so the 256-bit distance of 16 queries x 8 rows is eight m16n8k32 MMAs and the nearest row of a query is the
+// one with the largest S.  A warp keeps 32 queries as A fragments in registers for the whole slice (64
+// registers), streams the packed rows from L1/L2 (two LDG.128 per thread per 8 rows, prefetched one group
+// ahead), expands nibbles to bytes through a 16-entry shared-memory table (conflict-free: equal nibbles
+// broadcast, different nibbles are different banks) and keeps the top-2 of its four queries as packed keys
+// (S + 256) << 22 | (0x3fffff - row): largest S first, lowest row among equals -- the order of the ascending
+// scan with strict '<' (src/ORBmatcher.cc:216-225).  Measured IMMA rate: 1958 MAC/clk/SM
+// (tools/ubench/imma_rate.cu) = 7.6 pairs/clk/SM, 3.9x the POPC pipe's.
+constexpr int kMmaWarps = 8;                      // 256 queries per block
+constexpr int kMmaQueries = kMmaWarps * 32;
+
+__device__ __forceinline__ void imma_s8u8(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(kMmaWarps * 32, 2)
+bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
+                      long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
+                      int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
+  __shared__ uint32_t s_lut[16];  // nibble -> four bytes of 0/1
+  if (threadIdx.x < 16) s_lut[threadIdx.x] = (threadIdx.x * 0x00204081u) & 0x01010101u;
+  __syncthreads();
+  const int slice = blockIdx.y;
+  const long long row0 = (long long)slice * slice_rows;
+  const int rows = (int)min(slice_rows, ndb - row0);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gid = lane >> 2, tig = lane & 3;
+  const int qbase = blockIdx.x * kMmaQueries + warp * 32;
+
+  // A fragments of this thread: queries qbase + 16*mt + gid (+8), k-steps 0..7; bytes +1 / -1
+  uint32_t a[2][8][4];
+  int pq[4];  // popc of the thread's four queries: (mt, half) -> 2*mt + half
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int qi = min(qbase + 16 * mt + gid + 8 * half, nq - 1);
+      const uint4 lo = __ldg(q + 2 * (size_t)qi), hi = __ldg(q + 2 * (size_t)qi + 1);
+      const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+      int pc = 0;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        pc += __popc(w[ks]);
+        const uint32_t e0 = s_lut[(w[ks] >> (4 * tig)) & 0xfu], e1 = s_lut[(w[ks] >> (16 + 4 * tig)) & 0xfu];
+        a[mt][ks][half] = ((e0 ^ 0x01010101u) * 0xffu) | e0;      // a0 / a1: k = 4*tig .. +3
+        a[mt][ks][2 + half] = ((e1 ^ 0x01010101u) * 0xffu) | e1;  // a2 / a3: k = 16 + 4*tig .. +3
+      }
+      pq[2 * mt + half] = pc;
+    }
+
+  unsigned best[4] = {0, 0, 0, 0}, second[4] = {0, 0, 0, 0};  // key 0 = nothing seen
+  const uint4* src = db + row0 * 2;
+  const int ngroups = (rows + 7) >> 3;
+  const unsigned sh0 = 4 * tig, sh1 = 16 + 4 * tig;
+  uint4 nlo = make_uint4(0, 0, 0, 0), nhi = nlo;
+  if (ngroups > 0 && gid < rows) { nlo = __ldg(src + 2 * (size_t)gid); nhi = __ldg(src + 2 * (size_t)gid + 1); }
+  for (int g = 0; g < ngroups; ++g) {
+    const uint4 lo = nlo, hi = nhi;
+    const int nrow = (g + 1) * 8 + gid;
+    if (nrow < rows) { nlo = __ldg(src + 2 * (size_t)nrow); nhi = __ldg(src + 2 * (size_t)nrow + 1); }
+    const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const uint32_t b0 = s_lut[(w[ks] >> sh0) & 0xfu], b1 = s_lut[(w[ks] >> sh1) & 0xfu];
+      imma_s8u8(c0, a[0][ks], b0, b1);
+      imma_s8u8(c1, a[1][ks], b0, b1);
+    }
+    // columns 2*tig, 2*tig+1 of this group: rows g*8 + 2*tig (+1) of the slice
+    const int col = g * 8 + 2 * tig;
+    const unsigned k0 = col < rows ? (256u << 22) + 0x3fffffu - (unsigned)col : 0u;
+    const unsigned k1 = col + 1 < rows ? (256u << 22) + 0x3fffffu - (unsigned)(col + 1) : 0u;
+    const int sv[8] = {c0[0], c0[1], c0[2], c0[3], c1[0], c1[1], c1[2], c1[3]};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int qslot = (i >> 2) * 2 + ((i >> 1) & 1);           // (mt, half)
+      const unsigned kc = (i & 1) ? k1 : k0;
+      const unsigned key = kc ? (unsigned)(sv[i] * (1 << 22)) + kc : 0u;  // rows past the slice end never count
+      second[qslot] = max(second[qslot], min(best[qslot], key));
+      best[qslot] = max(best[qslot], key);
+    }
+  }
+  // merge the four lanes of a group (they saw different columns of the same queries)
+#pragma unroll
+  for (int o = 1; o <= 2; o <<= 1)
+#pragma unroll
+    for (int s4 = 0; s4 < 4; ++s4) {
+      const unsigned ob = __shfl_xor_sync(0xffffffffu, best[s4], o), os = __shfl_xor_sync(0xffffffffu, second[s4], o);
+      second[s4] = max(max(second[s4], os), min(best[s4], ob));
+      best[s4] = max(best[s4], ob);
+    }
+  if (tig == 0) {
+#pragma unroll
+    for (int s4 = 0; s4 < 4; ++s4) {
+      const int qi = qbase + 16 * (s4 >> 1) + gid + 8 * (s4 & 1);
+      if (qi >= nq) continue;
+      const size_t o = (size_t)slice * nq + qi;
+      const int bd = best[s4] ? pq[s4] - ((int)(best[s4] >> 22) - 256) : 256;
+      const int sd = second[s4] ? pq[s4] - ((int)(second[s4] >> 22) - 256) : 256;
+      o_best[o] = bd;
+      o_second[o] = sd;
+      // a row at distance 256 never beats the initial best of the reference's scan (strict '<')
+      o_idx[o] = (best[s4] && bd < 256) ? (int32_t)(idx_base + row0 + (0x3fffffu - (best[s4] & 0x3fffffu))) : -1;
+    }
+  }
+}
+
 // Exact merge of top-2 partials of disjoint ascending index ranges: scanning
 // shards in ascending order with the reference's update rule applied to (best, second) pairs.
 __global__ void merge_top2_kernel(const int32_t* __restrict__ idx, const int32_t* __restrict__ best,
@@ -228,7 +341,7 @@ struct TmpDev {  // RAII for call-scoped device scratch
   template <class T> T* as() { return (T*)p; }
 };
 
-static int g_bf_variant = 1;   // 0: 8-POPC form, 1: carry-save form (default)
+static int g_bf_variant = 2;   // 0: 8-POPC form, 1: carry-save form, 2: tensor-core (IMMA) form (default)
 static int g_bf_qpt = 2;
 
 template <int QPT, bool CSA>
@@ -243,8 +356,8 @@ extern "C" {
 
 // test/bench knob: choose the inner-loop form (0 = 8 POPC, 1 = carry-save) and queries per thread
 int orb_gpu_set_bruteforce_variant(int csa, int qpt) {
-  if (qpt != 1 && qpt != 2 && qpt != 4) return ORB_GPU_ERR_ARG;
-  g_bf_variant = csa ? 1 : 0;
+  if ((qpt != 1 && qpt != 2 && qpt != 4) || csa < 0 || csa > 2) return ORB_GPU_ERR_ARG;
+  g_bf_variant = csa;
   g_bf_qpt = qpt;
   return ORB_GPU_OK;
 }
@@ -260,7 +373,8 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   ORB_CUDA_TRY(cudaGetDevice(&dev));
   ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int qpt = g_bf_qpt;
-  const int qblocks = (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
+  const bool mma = g_bf_variant == 2;
+  const int qblocks = mma ? (nq + kMmaQueries - 1) / kMmaQueries : (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
   // enough database slices to put ~4 waves of blocks on the chip, each slice a whole number of tiles
   long long nslices = std::max<long long>(1, (4LL * sms * 4 + qblocks - 1) / qblocks);
   long long slice_rows = (ndb + nslices - 1) / nslices;
@@ -277,8 +391,11 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   }
   dim3 grid(qblocks, (unsigned)nslices);
   const uint4* q4 = (const uint4*)d_q; const uint4* db4 = (const uint4*)d_db;
-  const int key = qpt * 2 + g_bf_variant;
+  const int key = mma ? -1 : qpt * 2 + g_bf_variant;
   switch (key) {
+    case -1:
+      bruteforce_mma_kernel<<<grid, kMmaWarps * 32, 0, s>>>(q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps);
+      break;
     case 2: bf_launch<1, false>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
     case 3: bf_launch<1, true>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
     case 4: bf_launch<2, false>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;

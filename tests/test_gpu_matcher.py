@@ -8,7 +8,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("nq,ndb", [(1, 1), (7, 300), (512, 20000), (1000, 70001)])
-@pytest.mark.parametrize("variant", [(0, 1), (1, 2), (1, 4)])
+@pytest.mark.parametrize("variant", [(0, 1), (1, 2), (1, 4), (2, 2)])  # 8-POPC, carry-save x2, tensor-core form
 def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
     q, db = synth.make_match_set(nq, ndb, seed=11)
     gpu.lib().orb_gpu_set_bruteforce_variant(*variant)
@@ -19,7 +19,7 @@ def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
     acc = m.accept(best, second, th=m.TH_HIGH)
     ref = (ob <= 100) & (ob.astype(np.float32) < np.float32(0.9) * os_.astype(np.float32))
     assert np.array_equal(acc, ref)
-    gpu.lib().orb_gpu_set_bruteforce_variant(1, 2)
+    gpu.lib().orb_gpu_set_bruteforce_variant(2, 2)   # back to the default (tensor-core form)
 
 
 def test_bruteforce_empty_and_ties(gpu, oracle):
