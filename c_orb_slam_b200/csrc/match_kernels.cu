@@ -147,17 +147,19 @@ __device__ __forceinline__ void imma_s8u8(int (&c)[4], const uint32_t (&a)[4], u
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+constexpr int kMmaTileRows = 32;                  // database rows expanded per barrier (4 groups of 8)
+
 __global__ void __launch_bounds__(kMmaWarps * 32, 2)
 bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
                       long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
                       int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
-  __shared__ uint32_t s_lut[16];  // nibble -> four bytes of 0/1
-  if (threadIdx.x < 16) s_lut[threadIdx.x] = (threadIdx.x * 0x00204081u) & 0x01010101u;
-  __syncthreads();
+  // expanded B tiles, double buffered: [buffer][group of 8 rows][j = k-step pair][lane] -> (b0,b1 of k-step 2j,
+  // b0,b1 of k-step 2j+1); a warp reads its 16 fragment words of a group with four conflict-free LDS.128
+  __shared__ uint4 s_b[2][kMmaTileRows / 8][4][32];
   const int slice = blockIdx.y;
   const long long row0 = (long long)slice * slice_rows;
   const int rows = (int)min(slice_rows, ndb - row0);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gid = lane >> 2, tig = lane & 3;
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31, gid = lane >> 2, tig = lane & 3;
   const int qbase = blockIdx.x * kMmaQueries + warp * 32;
 
   // A fragments of this thread: queries qbase + 16*mt + gid (+8), k-steps 0..7; bytes +1 / -1
@@ -174,44 +176,75 @@ bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks) {
         pc += __popc(w[ks]);
-        const uint32_t e0 = s_lut[(w[ks] >> (4 * tig)) & 0xfu], e1 = s_lut[(w[ks] >> (16 + 4 * tig)) & 0xfu];
+        const uint32_t e0 = (((w[ks] >> (4 * tig)) & 0xfu) * 0x00204081u) & 0x01010101u;
+        const uint32_t e1 = (((w[ks] >> (16 + 4 * tig)) & 0xfu) * 0x00204081u) & 0x01010101u;
         a[mt][ks][half] = ((e0 ^ 0x01010101u) * 0xffu) | e0;      // a0 / a1: k = 4*tig .. +3
         a[mt][ks][2 + half] = ((e1 ^ 0x01010101u) * 0xffu) | e1;  // a2 / a3: k = 16 + 4*tig .. +3
       }
       pq[2 * mt + half] = pc;
     }
 
+  // expansion duty of this thread: packed word e_ks of row e_row of every tile -> 8 fragment words
+  const int e_row = t >> 3, e_ks = t & 7;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(db + row0 * 2);
+  const int ntiles = (rows + kMmaTileRows - 1) / kMmaTileRows;
+  auto fetch = [&](int tile) -> uint32_t {
+    const int r = tile * kMmaTileRows + e_row;
+    return (tile < ntiles && r < rows) ? __ldg(src + (size_t)r * 8 + e_ks) : 0u;
+  };
+  auto expand = [&](uint32_t w, int buf) {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_b[buf][e_row >> 3][e_ks >> 1][(e_row & 7) * 4]) + (e_ks & 1) * 2;
+#pragma unroll
+    for (int g4 = 0; g4 < 4; ++g4) {  // fragment lane (row, tig = g4): nibbles g4 and 4 + g4
+      uint2 v;
+      v.x = (((w >> (4 * g4)) & 0xfu) * 0x00204081u) & 0x01010101u;
+      v.y = (((w >> (16 + 4 * g4)) & 0xfu) * 0x00204081u) & 0x01010101u;
+      *reinterpret_cast<uint2*>(dst + 4 * g4) = v;
+    }
+  };
+
   unsigned best[4] = {0, 0, 0, 0}, second[4] = {0, 0, 0, 0};  // key 0 = nothing seen
-  const uint4* src = db + row0 * 2;
-  const int ngroups = (rows + 7) >> 3;
-  const unsigned sh0 = 4 * tig, sh1 = 16 + 4 * tig;
-  uint4 nlo = make_uint4(0, 0, 0, 0), nhi = nlo;
-  if (ngroups > 0 && gid < rows) { nlo = __ldg(src + 2 * (size_t)gid); nhi = __ldg(src + 2 * (size_t)gid + 1); }
-  for (int g = 0; g < ngroups; ++g) {
-    const uint4 lo = nlo, hi = nhi;
-    const int nrow = (g + 1) * 8 + gid;
-    if (nrow < rows) { nlo = __ldg(src + 2 * (size_t)nrow); nhi = __ldg(src + 2 * (size_t)nrow + 1); }
-    const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};
+  int thr[4] = {-100000, -100000, -100000, -100000};           // S of the thread's second best per query
+  uint32_t w_next = fetch(0);
+  expand(w_next, 0);
+  w_next = fetch(1);
+  for (int tile = 0; tile < ntiles; ++tile) {
+    const int buf = tile & 1;
+    __syncthreads();  // tile `tile` is expanded; everybody has finished reading the other buffer
+    const uint32_t w_cur = w_next;
+    w_next = fetch(tile + 2);
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      const uint32_t b0 = s_lut[(w[ks] >> sh0) & 0xfu], b1 = s_lut[(w[ks] >> sh1) & 0xfu];
-      imma_s8u8(c0, a[0][ks], b0, b1);
-      imma_s8u8(c1, a[1][ks], b0, b1);
-    }
-    // columns 2*tig, 2*tig+1 of this group: rows g*8 + 2*tig (+1) of the slice
-    const int col = g * 8 + 2 * tig;
-    const unsigned k0 = col < rows ? (256u << 22) + 0x3fffffu - (unsigned)col : 0u;
-    const unsigned k1 = col + 1 < rows ? (256u << 22) + 0x3fffffu - (unsigned)(col + 1) : 0u;
-    const int sv[8] = {c0[0], c0[1], c0[2], c0[3], c1[0], c1[1], c1[2], c1[3]};
+    for (int g = 0; g < kMmaTileRows / 8; ++g) {
+      int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int qslot = (i >> 2) * 2 + ((i >> 1) & 1);           // (mt, half)
-      const unsigned kc = (i & 1) ? k1 : k0;
-      const unsigned key = kc ? (unsigned)(sv[i] * (1 << 22)) + kc : 0u;  // rows past the slice end never count
-      second[qslot] = max(second[qslot], min(best[qslot], key));
-      best[qslot] = max(best[qslot], key);
+      for (int j = 0; j < 4; ++j) {
+        const uint4 v = s_b[buf][g][j][lane];
+        imma_s8u8(c0, a[0][2 * j], v.x, v.y);
+        imma_s8u8(c1, a[1][2 * j], v.x, v.y);
+        imma_s8u8(c0, a[0][2 * j + 1], v.z, v.w);
+        imma_s8u8(c1, a[1][2 * j + 1], v.z, v.w);
+      }
+      // quick reject: a row only matters if its S beats the S of the thread's current second best
+      const bool hit = max(c0[0], c0[1]) > thr[0] || max(c0[2], c0[3]) > thr[1] || max(c1[0], c1[1]) > thr[2] ||
+                       max(c1[2], c1[3]) > thr[3];
+      if (hit) {
+        const int col = tile * kMmaTileRows + g * 8 + 2 * tig;  // rows col, col + 1 of the slice
+        const unsigned k0 = col < rows ? (256u << 22) + 0x3fffffu - (unsigned)col : 0u;
+        const unsigned k1 = col + 1 < rows ? (256u << 22) + 0x3fffffu - (unsigned)(col + 1) : 0u;
+        const int sv[8] = {c0[0], c0[1], c0[2], c0[3], c1[0], c1[1], c1[2], c1[3]};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int qslot = (i >> 2) * 2 + ((i >> 1) & 1);           // (mt, half)
+          const unsigned kc = (i & 1) ? k1 : k0;
+          const unsigned key = kc ? (unsigned)(sv[i] * (1 << 22)) + kc : 0u;  // rows past the slice end never count
+          second[qslot] = max(second[qslot], min(best[qslot], key));
+          best[qslot] = max(best[qslot], key);
+        }
+#pragma unroll
+        for (int s4 = 0; s4 < 4; ++s4) thr[s4] = second[s4] ? (int)(second[s4] >> 22) - 256 : -100000;
+      }
     }
+    if (tile + 1 < ntiles) expand(w_cur, buf ^ 1);
   }
   // merge the four lanes of a group (they saw different columns of the same queries)
 #pragma unroll
