@@ -147,14 +147,15 @@ __device__ __forceinline__ void imma_s8u8(int (&c)[4], const uint32_t (&a)[4], u
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-constexpr int kMmaTileRows = 32;                  // database rows expanded per barrier (4 groups of 8)
+constexpr int kMmaTileRows = 32;                  // database rows expanded per barrier (groups of 8; multiple of 32)
 
 __global__ void __launch_bounds__(kMmaWarps * 32, 2)
 bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
                       long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
                       int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
   // expanded B tiles, double buffered: [buffer][group of 8 rows][j = k-step pair][lane] -> (b0,b1 of k-step 2j,
-  // b0,b1 of k-step 2j+1); a warp reads its 16 fragment words of a group with four conflict-free LDS.128
+  // b0,b1 of k-step 2j+1), lane index XORed with j so that the expanding threads spread over the banks; a warp
+  // reads its 16 fragment words of a group with four conflict-free LDS.128
   __shared__ uint4 s_b[2][kMmaTileRows / 8][4][32];
   const int slice = blockIdx.y;
   const long long row0 = (long long)slice * slice_rows;
@@ -184,41 +185,46 @@ bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       pq[2 * mt + half] = pc;
     }
 
-  // expansion duty of this thread: packed word e_ks of row e_row of every tile -> 8 fragment words
+  // expansion duty of this thread: packed word e_ks of rows e_row and e_row + 32 of every tile -> 2 x 8 fragment words
   const int e_row = t >> 3, e_ks = t & 7;
   const uint32_t* src = reinterpret_cast<const uint32_t*>(db + row0 * 2);
   const int ntiles = (rows + kMmaTileRows - 1) / kMmaTileRows;
-  auto fetch = [&](int tile) -> uint32_t {
-    const int r = tile * kMmaTileRows + e_row;
+  auto fetch = [&](int tile, int h) -> uint32_t {
+    const int r = tile * kMmaTileRows + e_row + 32 * h;
     return (tile < ntiles && r < rows) ? __ldg(src + (size_t)r * 8 + e_ks) : 0u;
   };
-  auto expand = [&](uint32_t w, int buf) {
-    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_b[buf][e_row >> 3][e_ks >> 1][(e_row & 7) * 4]) + (e_ks & 1) * 2;
+  auto expand = [&](uint32_t w, int buf, int h) {
+    const int er = e_row + 32 * h, j = e_ks >> 1;
+    uint32_t* base = reinterpret_cast<uint32_t*>(&s_b[buf][er >> 3][j][0]) + (e_ks & 1) * 2;
 #pragma unroll
     for (int g4 = 0; g4 < 4; ++g4) {  // fragment lane (row, tig = g4): nibbles g4 and 4 + g4
       uint2 v;
       v.x = (((w >> (4 * g4)) & 0xfu) * 0x00204081u) & 0x01010101u;
       v.y = (((w >> (16 + 4 * g4)) & 0xfu) * 0x00204081u) & 0x01010101u;
-      *reinterpret_cast<uint2*>(dst + 4 * g4) = v;
+      *reinterpret_cast<uint2*>(base + 4 * ((((er & 7) * 4) + g4) ^ j)) = v;
     }
   };
 
   unsigned best[4] = {0, 0, 0, 0}, second[4] = {0, 0, 0, 0};  // key 0 = nothing seen
   int thr[4] = {-100000, -100000, -100000, -100000};           // S of the thread's second best per query
-  uint32_t w_next = fetch(0);
-  expand(w_next, 0);
-  w_next = fetch(1);
+  constexpr int kHalves = kMmaTileRows / 32;
+  uint32_t w_next[kHalves];
+#pragma unroll
+  for (int h = 0; h < kHalves; ++h) { w_next[h] = fetch(0, h); expand(w_next[h], 0, h); }
+#pragma unroll
+  for (int h = 0; h < kHalves; ++h) w_next[h] = fetch(1, h);
   for (int tile = 0; tile < ntiles; ++tile) {
     const int buf = tile & 1;
     __syncthreads();  // tile `tile` is expanded; everybody has finished reading the other buffer
-    const uint32_t w_cur = w_next;
-    w_next = fetch(tile + 2);
+    uint32_t w_cur[kHalves];
+#pragma unroll
+    for (int h = 0; h < kHalves; ++h) { w_cur[h] = w_next[h]; w_next[h] = fetch(tile + 2, h); }
 #pragma unroll
     for (int g = 0; g < kMmaTileRows / 8; ++g) {
       int c0[4] = {0, 0, 0, 0}, c1[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const uint4 v = s_b[buf][g][j][lane];
+        const uint4 v = s_b[buf][g][j][lane ^ j];
         imma_s8u8(c0, a[0][2 * j], v.x, v.y);
         imma_s8u8(c1, a[1][2 * j], v.x, v.y);
         imma_s8u8(c0, a[0][2 * j + 1], v.z, v.w);
@@ -244,7 +250,10 @@ bruteforce_mma_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
         for (int s4 = 0; s4 < 4; ++s4) thr[s4] = second[s4] ? (int)(second[s4] >> 22) - 256 : -100000;
       }
     }
-    if (tile + 1 < ntiles) expand(w_cur, buf ^ 1);
+    if (tile + 1 < ntiles) {
+#pragma unroll
+      for (int h = 0; h < kHalves; ++h) expand(w_cur[h], buf ^ 1, h);
+    }
   }
   // merge the four lanes of a group (they saw different columns of the same queries)
 #pragma unroll
@@ -316,6 +325,21 @@ __global__ void popc_peak_kernel(uint32_t seed, int iters, uint32_t* out) {
 #pragma unroll
   for (int k = 0; k < 8; ++k) r += acc[k];
   if (r == 0xffffffffu) out[0] = r;
+}
+
+// tensor-pipe peak probe for the legacy int8 path: eight independent IMMA.16832 accumulation chains per warp
+__global__ void imma_peak_kernel(int iters, int* out) {
+  int c[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0;
+  const uint32_t a[4] = {threadIdx.x * 0x01010101u, threadIdx.x * 0x01010101u + 1, 0x01ff01ffu, 0xff01ff01u};
+  for (int it = 0; it < iters; ++it)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) imma_s8u8(c[i], a, 0x01000101u, 0x00010100u);
+  int r = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+  if (r == 0x7fffffff) out[0] = r;
 }
 
 }  // namespace orbgpu
@@ -468,6 +492,38 @@ int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_
   ORB_CUDA_TRY(cudaMemcpy(idx, o, (size_t)nq * 4, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(best, o + nq, (size_t)nq * 4, cudaMemcpyDeviceToHost));
   ORB_CUDA_TRY(cudaMemcpy(second, o + 2 * (size_t)nq, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  return ORB_GPU_OK;
+}
+
+// multiply-accumulates per second of mma.sync m16n8k32 s8 x u8 (the pipe bruteforce_mma_kernel runs on)
+int orb_gpu_imma_peak(int device, double* mac_per_s) {
+  if (!mac_per_s) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int sms = 148;
+  ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  TmpDev out;
+  int rc = out.alloc(16);
+  if (rc) return rc;
+  cudaEvent_t e0, e1;
+  ORB_CUDA_TRY(cudaEventCreate(&e0));
+  ORB_CUDA_TRY(cudaEventCreate(&e1));
+  const int iters = 1 << 13, blocks = sms * 2, threads = 512;
+  imma_peak_kernel<<<blocks, threads>>>(64, out.as<int>());  // warm-up
+  double bestv = 0;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0);
+    imma_peak_kernel<<<blocks, threads>>>(iters, out.as<int>());
+    cudaEventRecord(e1);
+    ORB_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    bestv = std::max(bestv, (double)blocks * (threads / 32) * iters * 8.0 * (16.0 * 8 * 32) / (ms * 1e-3));
+  }
+  count_launch(4);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  ORB_CUDA_TRY(cudaGetLastError());
+  *mac_per_s = bestv;
   return ORB_GPU_OK;
 }
 

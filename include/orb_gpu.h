@@ -331,6 +331,9 @@ int64_t orb_gpu_launch_count(void);
 /* dependent-free POPC stream on all SMs: returns achieved 32-bit POPC/s (integer-pipe peak
  * denominator for the Hamming roofline; MEASURED_PEAKS.json has no integer figure). */
 int orb_gpu_popc_peak(int device, double* popc_per_s);
+/* Measured multiply-accumulate rate (MAC/s) of mma.sync m16n8k32 s8 x u8 -> s32 (IMMA), the tensor-core path of
+ * the default brute-force kernel: 256 MACs per descriptor pair. */
+int orb_gpu_imma_peak(int device, double* mac_per_s);
 
 #ifdef __cplusplus
 }
