@@ -123,6 +123,10 @@ int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int le
 int launch_stereo_pairs(const StereoSide& L, const StereoSide& R, const StereoParams& P, int npairs,
                         int max_left, float* d_u_right, float* d_depth, int* d_sad, cudaStream_t s);
 int upload_constants();
+// ---- match_tc5_kernels.cu: brute force on tcgen05 (256 queries per block, slices of whole 256-row tiles)
+int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
+                          long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
+                          int32_t* o_second);
 size_t quadtree_smem_bytes(const Plan& p, int level);
 
 }  // namespace orbgpu

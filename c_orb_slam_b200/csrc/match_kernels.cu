@@ -398,7 +398,7 @@ struct TmpDev {  // RAII for call-scoped device scratch
   template <class T> T* as() { return (T*)p; }
 };
 
-static int g_bf_variant = 2;   // 0: 8-POPC form, 1: carry-save form, 2: tensor-core (IMMA) form (default)
+static int g_bf_variant = 2;   // 0: 8-POPC form, 1: carry-save form, 2: mma.sync IMMA form (default), 3: tcgen05 kind::i8 form
 static int g_bf_qpt = 2;
 
 template <int QPT, bool CSA>
@@ -413,7 +413,7 @@ extern "C" {
 
 // test/bench knob: choose the inner-loop form (0 = 8 POPC, 1 = carry-save) and queries per thread
 int orb_gpu_set_bruteforce_variant(int csa, int qpt) {
-  if ((qpt != 1 && qpt != 2 && qpt != 4) || csa < 0 || csa > 2) return ORB_GPU_ERR_ARG;
+  if ((qpt != 1 && qpt != 2 && qpt != 4) || csa < 0 || csa > 3) return ORB_GPU_ERR_ARG;
   g_bf_variant = csa;
   g_bf_qpt = qpt;
   return ORB_GPU_OK;
@@ -430,10 +430,11 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   ORB_CUDA_TRY(cudaGetDevice(&dev));
   ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int qpt = g_bf_qpt;
-  const bool mma = g_bf_variant == 2;
+  const bool mma = g_bf_variant >= 2, tc5 = g_bf_variant == 3;  // both tensor-core forms take 256 queries per block
   const int qblocks = mma ? (nq + kMmaQueries - 1) / kMmaQueries : (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
-  // enough database slices to put ~4 waves of blocks on the chip, each slice a whole number of tiles
-  long long nslices = std::max<long long>(1, (4LL * sms * 4 + qblocks - 1) / qblocks);
+  // enough database slices to put ~4 waves of blocks on the chip (the tcgen05 form runs one block per SM),
+  // each slice a whole number of tiles
+  long long nslices = std::max<long long>(1, (4LL * sms * (tc5 ? 1 : 4) + qblocks - 1) / qblocks);
   long long slice_rows = (ndb + nslices - 1) / nslices;
   slice_rows = std::max<long long>(kBfTile, (slice_rows + kBfTile - 1) / kBfTile * kBfTile);
   slice_rows = std::min<long long>(slice_rows, kBfSliceMax);
@@ -448,8 +449,13 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   }
   dim3 grid(qblocks, (unsigned)nslices);
   const uint4* q4 = (const uint4*)d_q; const uint4* db4 = (const uint4*)d_db;
-  const int key = mma ? -1 : qpt * 2 + g_bf_variant;
+  const int key = tc5 ? -2 : mma ? -1 : qpt * 2 + g_bf_variant;
   switch (key) {
+    case -2: {
+      int rc = launch_bruteforce_tc5(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps);
+      if (rc) return rc;
+      break;
+    }
     case -1:
       bruteforce_mma_kernel<<<grid, kMmaWarps * 32, 0, s>>>(q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps);
       break;
