@@ -278,7 +278,7 @@ def run_ours(args):
                 step_match()
                 evs[k + 1].record()
             barrier()
-            # One step is a single 72 ms kernel; on this pool a step is now and then stretched by 20-50 ms by
+            # One step is a single kernel of several ms; on this pool a step is now and then stretched by 20-50 ms by
             # something outside the process (seen with and without NVML polling, clocks at maximum), so the
             # per-step MEDIAN over the ranks' maxima is reported, with the extremes next to it.
             per_step = [max_over_ranks(evs[k].elapsed_time(evs[k + 1])) for k in range(hsteps)]
@@ -289,18 +289,23 @@ def run_ours(args):
         gpairs = nq * ndb_total * hsteps / (hms * 1e-3) / 1e9
         popc = orb.popc_peak(local)
         imma = orb.imma_peak(local)
+        umma = orb.umma_peak(local)
         hamming = {"value": gpairs, "unit": "Gpairs/s", "scaling": "strong", "ms_per_step": hms / hsteps,
                    "steps": hsteps, "timing": "median of per-step device times (CUDA events, max over ranks)",
                    "ms_per_step_min": min(per_step), "ms_per_step_max": max(per_step),
                    "config": {"workload": "brute-force top-2, %d queries x %d database rows, database sharded over %d GPU(s), "
                                           "top-2 all-gather + exact merge" % (nq, ndb_total, world)},
                    "clocks": hclocks,
-                   # the default kernel runs on the legacy int8 tensor path (IMMA): 256 multiply-accumulates per pair
-                   "roofline": {"bound": "tensor (mma.sync s8 IMMA)", "achieved": gpairs * 256 / world / 1e3,
-                                "peak": imma / 1e12, "unit": "TMAC/s per GPU (256 per pair)",
-                                "frac": gpairs * 1e9 * 256 / world / imma,
-                                "peak_kind": "measured here: independent IMMA.16832 chains, orb_gpu_imma_peak"},
-                   # for reference: the same rate against the POPC pipe the LOP3+POPC kernels are bound by
+                   # the default kernel runs on tcgen05.mma kind::i8 (TMEM accumulators): 256 multiply-accumulates per pair
+                   "roofline": {"bound": "tensor (tcgen05.mma kind::i8)", "achieved": gpairs * 256 / world / 1e3,
+                                "peak": umma / 1e12, "unit": "TMAC/s per GPU (256 per pair)",
+                                "frac": gpairs * 1e9 * 256 / world / umma,
+                                "peak_kind": "measured here: back-to-back M128 N256 K32 kind::i8 MMAs on every SM, orb_gpu_umma_peak"},
+                   # for reference: the same rate against the legacy mma.sync IMMA path (brute-force variant 2) ...
+                   "vs_imma_pipe": {"achieved": gpairs * 256 / world / 1e3, "peak": imma / 1e12,
+                                    "unit": "TMAC/s per GPU", "frac": gpairs * 1e9 * 256 / world / imma,
+                                    "peak_kind": "measured here: independent IMMA.16832 chains, orb_gpu_imma_peak"},
+                   # ... and against the POPC pipe the LOP3+POPC kernels (variants 0, 1) are bound by
                    "vs_popc_pipe": {"achieved": gpairs * 8 / world, "peak": popc / 1e9,
                                     "unit": "GPOPC-equivalents/s per GPU (8 per pair)", "frac": gpairs * 8 / world / (popc / 1e9),
                                     "peak_kind": "measured here: dependent-free POPC stream, orb_gpu_popc_peak"}}

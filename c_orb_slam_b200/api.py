@@ -39,7 +39,7 @@ EXPORTS = [
     "orb_gpu_compute_stereo_matches", "orb_gpu_stereo_matches_device", "orb_gpu_distinctive_descriptors",
     "orb_gpu_distinctive_descriptors_device", "orb_gpu_vocabulary_create", "orb_gpu_vocabulary_destroy",
     "orb_gpu_vocabulary_transform", "orb_gpu_vocabulary_transform_device", "orb_gpu_version", "orb_gpu_last_error",
-    "orb_gpu_launch_count", "orb_gpu_popc_peak", "orb_gpu_imma_peak",
+    "orb_gpu_launch_count", "orb_gpu_popc_peak", "orb_gpu_imma_peak", "orb_gpu_umma_peak",
 ]
 
 STATUS = {0: "OK", -1: "ERR_ARG", -2: "ERR_CAPACITY", -3: "ERR_CUDA", -4: "ERR_STATE"}
@@ -132,6 +132,7 @@ def lib():
         L.orb_gpu_get_stage_ms.argtypes = [C.c_void_p, C.c_void_p]
         L.orb_gpu_popc_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
         L.orb_gpu_imma_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+        L.orb_gpu_umma_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
         L.orb_gpu_set_bruteforce_variant.argtypes = [C.c_int, C.c_int]
         _lib = L
     return _lib
@@ -154,6 +155,13 @@ def imma_peak(device=0):
     """Measured MAC/s of the legacy int8 tensor path (mma.sync m16n8k32) on `device`."""
     v = C.c_double()
     _check(lib().orb_gpu_imma_peak(device, C.byref(v)), "orb_gpu_imma_peak")
+    return v.value
+
+
+def umma_peak(device=0):
+    """Measured MAC/s of tcgen05.mma kind::i8 (M128 N256 K32, the default brute-force kernel's path) on `device`."""
+    v = C.c_double()
+    _check(lib().orb_gpu_umma_peak(device, C.byref(v)), "orb_gpu_umma_peak")
     return v.value
 
 

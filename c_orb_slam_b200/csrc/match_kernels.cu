@@ -398,7 +398,7 @@ struct TmpDev {  // RAII for call-scoped device scratch
   template <class T> T* as() { return (T*)p; }
 };
 
-static int g_bf_variant = 2;   // 0: 8-POPC form, 1: carry-save form, 2: mma.sync IMMA form (default), 3: tcgen05 kind::i8 form
+static int g_bf_variant = 3;   // 0: 8-POPC form, 1: carry-save form, 2: mma.sync IMMA form, 3: tcgen05 kind::i8 form (default)
 static int g_bf_qpt = 2;
 
 template <int QPT, bool CSA>
@@ -440,12 +440,15 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   slice_rows = std::min<long long>(slice_rows, kBfSliceMax);
   nslices = std::max<long long>(1, (ndb + slice_rows - 1) / slice_rows);
   if (nslices > 65535) return ORB_GPU_ERR_CAPACITY;
-  TmpDev part;
+  // per-slice partials: stream-ordered scratch from the device's cached pool (no cudaMalloc / cudaFree and no
+  // host synchronisation in the call; the merge kernel is the last reader and the free is ordered after it)
+  void* part = nullptr;
   int32_t *pi = d_idx, *pb = d_best, *ps = d_second;
   if (nslices > 1) {
-    int rc = part.alloc((size_t)nslices * nq * 3 * sizeof(int32_t));
+    int rc = use_cached_pool(dev);
     if (rc) return rc;
-    pi = part.as<int32_t>(); pb = pi + (size_t)nslices * nq; ps = pb + (size_t)nslices * nq;
+    ORB_CUDA_TRY(cudaMallocAsync(&part, (size_t)nslices * nq * 3 * sizeof(int32_t), s));
+    pi = (int32_t*)part; pb = pi + (size_t)nslices * nq; ps = pb + (size_t)nslices * nq;
   }
   dim3 grid(qblocks, (unsigned)nslices);
   const uint4* q4 = (const uint4*)d_q; const uint4* db4 = (const uint4*)d_db;
@@ -453,7 +456,7 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   switch (key) {
     case -2: {
       int rc = launch_bruteforce_tc5(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps);
-      if (rc) return rc;
+      if (rc) { if (part) cudaFreeAsync(part, s); return rc; }
       break;
     }
     case -1:
@@ -467,13 +470,14 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
     default: bf_launch<4, true>(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps); break;
   }
   count_launch();
-  ORB_CUDA_TRY(cudaGetLastError());
-  if (nslices > 1) {
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && nslices > 1) {
     merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pi, pb, ps, (int)nslices, nq, d_idx, d_best, d_second);
     count_launch();
-    ORB_CUDA_TRY(cudaGetLastError());
-    ORB_CUDA_TRY(cudaStreamSynchronize(s));  // `part` is freed on return
+    e = cudaGetLastError();
   }
+  if (part) cudaFreeAsync(part, s);
+  ORB_CUDA_TRY(e);
   return ORB_GPU_OK;
 }
 

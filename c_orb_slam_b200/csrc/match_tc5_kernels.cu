@@ -11,15 +11,15 @@
 //
 // One block = 256 queries (two M=128 A tiles, expanded once into shared memory) x one slice of the database.
 // Roles (one warp each unless noted):
-//   warps 9..16  expanders: one database row per thread and tile of 256 rows -> 16 STS.128 into the K-major,
+//   warps 9..12  expanders: two database rows per thread and tile of 256 rows -> 32 STS.128 into the K-major,
 //                unswizzled core-matrix layout (8 rows x 16 bytes contiguous; LBO = 4096, SBO = 128)
 //   warp 8       MMA issuer (lane 0): per tile 2 x 8 tcgen05.mma M128 N256 K32 into two TMEM accumulators
-//   warps 0..7   epilogue (set i = warps 4i..4i+3 drains accumulator i): tcgen05.ld 32 columns at a time, max filter against the running second best,
-//                packed (S, row) keys; one query per thread and accumulator
+//   warps 0..7   epilogue (set i = warps 4i..4i+3 drains accumulator i): the 256-column row of the thread's
+//                query comes to registers in four packed tcgen05.ld (three in flight), the accumulator is
+//                handed back as soon as the last one lands, and the rest of the scan (max filter against the
+//                running second best, packed (S, row) keys) overlaps the next MMA into it
 // Pipelines: b_full/b_empty (expanders <-> MMA, 2 stages), acc_full/acc_empty (MMA <-> epilogue, the two
 // accumulators alternate so the epilogue of one overlaps the MMAs of the other).
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace orbgpu {
@@ -27,7 +27,9 @@ namespace orbgpu {
 constexpr int kT5Queries = 256;
 constexpr int kT5TileRows = 256;
 constexpr int kT5EpiWarps = 8;                           // two sets of four: set i drains accumulator i
-constexpr int kT5ExpWarps = 8;
+constexpr int kT5ExpWarps = 4;
+constexpr int kT5ExpThreads = kT5ExpWarps * 32;
+constexpr int kT5RowsPerExp = kT5TileRows / kT5ExpThreads;
 constexpr int kT5Threads = (kT5EpiWarps + 1 + kT5ExpWarps) * 32;
 constexpr uint32_t kT5ATile = 128 * 256;                 // bytes of one expanded A tile
 constexpr uint32_t kT5BStage = kT5TileRows * 256;        // bytes of one expanded B stage
@@ -84,10 +86,11 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
 
 #define T5_R8(v, o) "=r"(v[o]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]), "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7])
 #define T5_RW8(v, o) "+r"(v[o]), "+r"(v[o + 1]), "+r"(v[o + 2]), "+r"(v[o + 3]), "+r"(v[o + 4]), "+r"(v[o + 5]), "+r"(v[o + 6]), "+r"(v[o + 7])
-// 32 consecutive accumulator columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_ld32(uint32_t (&v)[32], uint32_t taddr) {
+// 64 consecutive accumulator columns of this thread's TMEM lane, the low 16 bits of each packed two to a
+// register (column 2r in the low half of register r): |64 * S| <= 16384 fits
+__device__ __forceinline__ void tmem_ld64p(uint32_t (&v)[32], uint32_t taddr) {
   asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
       "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
       : T5_R8(v, 0), T5_R8(v, 8), T5_R8(v, 16), T5_R8(v, 24)
@@ -101,36 +104,61 @@ __device__ __forceinline__ void tmem_wait(uint32_t (&v)[32]) {
                : "memory");
 }
 
-// top-2 update over 32 accumulator columns (database rows col0 .. col0 + 31 of the slice) of one query
-__device__ __forceinline__ void t5_update(const uint32_t (&v)[32], int col0, int rows, unsigned& best,
-                                          unsigned& second, int& thr) {
-  int m4[4];  // four independent chains: the warp is alone on its scheduler, so the chain depth is what it pays
+// packed maximum of 64 accumulator columns (two s16 lanes), a depth-4 tree of three-input maxima
+__device__ __forceinline__ uint32_t t5_rowmax(const uint32_t (&v)[32]) {
+  uint32_t l1[11], l2[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    m4[i] = max((int)v[i], (int)v[4 + i]);
+  for (int i = 0; i < 10; ++i) l1[i] = __vmaxs2(__vmaxs2(v[3 * i], v[3 * i + 1]), v[3 * i + 2]);
+  l1[10] = __vmaxs2(v[30], v[31]);
 #pragma unroll
-    for (int j = 8; j < 32; j += 8) m4[i] = max(m4[i], max((int)v[j + i], (int)v[j + 4 + i]));
-  }
-  const int m = max(max(m4[0], m4[1]), max(m4[2], m4[3]));
-  // a row only matters if 64 * S beats the current second best; the branch is warp-uniform because the
-  // tcgen05.ld that follows is .aligned
-  if (__any_sync(0xffffffffu, m > thr)) {
+  for (int i = 0; i < 3; ++i) l2[i] = __vmaxs2(__vmaxs2(l1[3 * i], l1[3 * i + 1]), l1[3 * i + 2]);
+  l2[3] = __vmaxs2(l1[9], l1[10]);
+  return __vmaxs2(__vmaxs2(__vmaxs2(l2[0], l2[1]), l2[2]), l2[3]);
+}
+// does either half exceed the threshold held in both halves of thr2?
+__device__ __forceinline__ bool t5_hit(uint32_t packed, uint32_t thr2) { return __vmaxs2(packed, thr2) != thr2; }
+
+// exact top-2 merge of 64 accumulator columns into (best, second): keys of the two halves of a register are
+// ordered first, four independent (best, second) pairs take the registers round robin, and the pairs are merged
+// at the end -- straight-line code with a short dependency chain (all lanes run it; it is reached for ~5% of the
+// calls).  CHECK masks the columns past the end of the slice (last tile only).
+__device__ __forceinline__ void t5_merge2(unsigned& b, unsigned& s2, unsigned hi, unsigned lo) {
+  const unsigned t = min(b, hi);
+  s2 = max(max(s2, t), lo);
+  b = max(b, hi);
+}
+template <bool CHECK>
+__device__ __forceinline__ void t5_merge64(const uint32_t (&v)[32], int col0, int rows, unsigned& best,
+                                           unsigned& second) {
+  const unsigned kbase = (256u << 22) + 0x3fffffu - (unsigned)col0;
+  const int lim = rows - col0;
+  unsigned b[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const int col = col0 + j;
-      const unsigned key =
-          col < rows ? (unsigned)((int)v[j] * (1 << 16)) + ((256u << 22) + 0x3fffffu - (unsigned)col) : 0u;
-      second = max(second, min(best, key));
-      best = max(best, key);
+  for (int r = 0; r < 32; ++r) {
+    // (64 * S) << 16 = S << 22: the packed halves are already the key's distance field
+    unsigned k0 = (v[r] << 16) + (kbase - 2 * r), k1 = (v[r] & 0xffff0000u) + (kbase - (2 * r + 1));
+    if (CHECK) {
+      k0 = 2 * r < lim ? k0 : 0u;
+      k1 = 2 * r + 1 < lim ? k1 : 0u;
     }
-    thr = second ? ((int)(second >> 22) - 256) * 64 : -100000;
+    t5_merge2(b[r & 3], s2[r & 3], max(k0, k1), min(k0, k1));
   }
+  t5_merge2(b[0], s2[0], b[1], s2[1]);
+  t5_merge2(b[2], s2[2], b[3], s2[3]);
+  t5_merge2(b[0], s2[0], b[2], s2[2]);
+  t5_merge2(best, second, b[0], s2[0]);
+}
+__device__ __forceinline__ void t5_scan64(const uint32_t (&v)[32], int col0, int rows, unsigned& best,
+                                          unsigned& second, uint32_t& thr2) {
+  if (rows - col0 >= 64) t5_merge64<false>(v, col0, rows, best, second);
+  else t5_merge64<true>(v, col0, rows, best, second);
+  if (second) thr2 = (((second >> 22) * 64u - 16384u) & 0xffffu) * 0x10001u;
 }
 
 __global__ void __launch_bounds__(kT5Threads, 1)
 bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
                       long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
-                      int32_t* __restrict__ o_best, int32_t* __restrict__ o_second, int dbg) {
+                      int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
   extern __shared__ __align__(128) uint8_t t5_smem[];
   uint8_t* s_a = t5_smem;
   uint8_t* s_b = t5_smem + 2 * kT5ATile;
@@ -148,7 +176,7 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
   const int qbase = blockIdx.x * kT5Queries;
 
   if (t == 0) {
-    mbar_init(bar(0), kT5ExpWarps * 32); mbar_init(bar(1), kT5ExpWarps * 32);
+    mbar_init(bar(0), kT5ExpThreads); mbar_init(bar(1), kT5ExpThreads);
     mbar_init(bar(2), 1); mbar_init(bar(3), 1);
     mbar_init(bar(4), 1); mbar_init(bar(5), 1);
     mbar_init(bar(6), 128); mbar_init(bar(7), 128);
@@ -162,26 +190,27 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
   }
   if (warp > kT5EpiWarps) {
     // A operand: query qbase + e as signed weighted bytes (see the header), K-major core matrices
-    const int e = t - (kT5EpiWarps + 1) * 32;
-    const int qi = min(qbase + e, nq - 1);
-    const uint4 lo = __ldg(q + 2 * (size_t)qi), hi = __ldg(q + 2 * (size_t)qi + 1);
-    const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    uint8_t* dst = s_a + (e >> 7) * kT5ATile + (e & 127) * 16;
+    for (int e = t - (kT5EpiWarps + 1) * 32; e < kT5Queries; e += kT5ExpThreads) {
+      const int qi = min(qbase + e, nq - 1);
+      const uint4 lo = __ldg(q + 2 * (size_t)qi), hi = __ldg(q + 2 * (size_t)qi + 1);
+      const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+      uint8_t* dst = s_a + (e >> 7) * kT5ATile + (e & 127) * 16;
+#pragma unroll 2
+      for (int c = 0; c < 16; ++c) {
+        const uint32_t h = (w[c >> 1] >> (16 * (c & 1))) & 0xffffu;
+        uint32_t o[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int c = 0; c < 16; ++c) {
-      const uint32_t h = (w[c >> 1] >> (16 * (c & 1))) & 0xffffu;
-      uint32_t o[4] = {0, 0, 0, 0};
+        for (int b = 0; b < 2; ++b)
 #pragma unroll
-      for (int b = 0; b < 2; ++b)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int wx = 64 >> j, wy = 8 >> j;  // query weights of bits j and 4 + j
-          const uint32_t x = (h >> (8 * b + j)) & 1u ? (uint32_t)wx : (uint32_t)(256 - wx);
-          const uint32_t y = (h >> (8 * b + 4 + j)) & 1u ? (uint32_t)wy : (uint32_t)(256 - wy);
-          o[2 * b] |= x << (8 * j);
-          o[2 * b + 1] |= y << (8 * j);
-        }
-      *reinterpret_cast<uint4*>(dst + c * 2048) = make_uint4(o[0], o[1], o[2], o[3]);
+          for (int j = 0; j < 4; ++j) {
+            const int wx = 64 >> j, wy = 8 >> j;  // query weights of bits j and 4 + j
+            const uint32_t x = (h >> (8 * b + j)) & 1u ? (uint32_t)wx : (uint32_t)(256 - wx);
+            const uint32_t y = (h >> (8 * b + 4 + j)) & 1u ? (uint32_t)wy : (uint32_t)(256 - wy);
+            o[2 * b] |= x << (8 * j);
+            o[2 * b + 1] |= y << (8 * j);
+          }
+        *reinterpret_cast<uint4*>(dst + c * 2048) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -194,29 +223,30 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
     // ---- epilogue: thread = TMEM lane = query qbase + t (warps 0..3: accumulator 0, warps 4..7: accumulator 1)
     const int acc = warp >> 2;
     unsigned best = 0, second = 0;
-    int thr = -100000;
+    uint32_t thr2 = 0x80008000u;  // 64 * S of the running second best in both halves; -32768 = none yet
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * 256;
-    uint32_t va[32], vb[32];
+    // three buffers of 64 packed columns: 13 warps put four on one scheduler, which caps a thread at 128 registers
+    uint32_t va[32], vb[32], vc[32];
     for (int tile = 0; tile < ntiles; ++tile) {
       mbar_wait(bar(4 + acc), tile & 1);
       tc_fence_after();
       const int col0 = tile * kT5TileRows;
-      tmem_ld32(va, taddr);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        tmem_wait(va);
-        tmem_ld32(vb, taddr + (2 * c + 1) * 32);
-        if (!(dbg & 1)) t5_update(va, col0 + 2 * c * 32, rows, best, second, thr);
-        tmem_wait(vb);
-        if (c < 3) {
-          tmem_ld32(va, taddr + (2 * c + 2) * 32);
-        } else {
-          tc_fence_before();
-          mbar_arrive(bar(6 + acc));  // the accumulator is in registers: the next MMA may overwrite it
-        }
-        if (!(dbg & 1)) t5_update(vb, col0 + (2 * c + 1) * 32, rows, best, second, thr);
-        else best += va[3] + vb[5];
-      }
+      tmem_ld64p(va, taddr);
+      tmem_ld64p(vb, taddr + 64);
+      tmem_ld64p(vc, taddr + 128);
+      tmem_wait(va);
+      tmem_wait(vb);
+      tmem_wait(vc);
+      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0, rows, best, second, thr2);
+      tmem_ld64p(va, taddr + 192);  // the fourth quarter lands while the second and third are filtered
+      const bool hb = __any_sync(0xffffffffu, t5_hit(t5_rowmax(vb), thr2));
+      const bool hc = __any_sync(0xffffffffu, t5_hit(t5_rowmax(vc), thr2));
+      tmem_wait(va);
+      tc_fence_before();
+      mbar_arrive(bar(6 + acc));  // the accumulator is in registers: the next MMA into it overlaps the rest of the scan
+      if (hb) t5_scan64(vb, col0 + 64, rows, best, second, thr2);
+      if (hc) t5_scan64(vc, col0 + 128, rows, best, second, thr2);
+      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0 + 192, rows, best, second, thr2);
     }
     const int qi = qbase + t;
     if (qi < nq) {
@@ -244,7 +274,6 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
         for (int acc = 0; acc < 2; ++acc) {
           mbar_wait(bar(6 + acc), (tile & 1) ^ 1);
           tc_fence_after();
-          if (!(dbg & 4))
 #pragma unroll
           for (int k = 0; k < 8; ++k)  // K = 32 bytes = two 16-byte chunks per step
             umma_i8(tmem_base + acc * 256, da[acc] + (uint64_t)(k * (2 * 2048 >> 4)),
@@ -257,34 +286,40 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       if (ntiles > 0) mbar_wait(bar(2 + ((ntiles - 1) & 1)), ((ntiles - 1) >> 1) & 1);
     }
   } else {
-    // ---- expanders: row e of every tile
+    // ---- expanders: rows e, e + 128 of every tile
     const int e = t - (kT5EpiWarps + 1) * 32;
     const uint4* src = db + row0 * 2;
-    auto fetch = [&](int tile, uint4& lo, uint4& hi) {
-      const int r = tile * kT5TileRows + e;
-      if (tile < ntiles && r < rows) { lo = __ldg(src + 2 * (size_t)r); hi = __ldg(src + 2 * (size_t)r + 1); }
-      else { lo = make_uint4(0, 0, 0, 0); hi = lo; }
+    auto fetch = [&](int tile, uint4 (&lo)[kT5RowsPerExp], uint4 (&hi)[kT5RowsPerExp]) {
+#pragma unroll
+      for (int i = 0; i < kT5RowsPerExp; ++i) {
+        const int r = tile * kT5TileRows + e + i * kT5ExpThreads;
+        if (tile < ntiles && r < rows) { lo[i] = __ldg(src + 2 * (size_t)r); hi[i] = __ldg(src + 2 * (size_t)r + 1); }
+        else { lo[i] = make_uint4(0, 0, 0, 0); hi[i] = lo[i]; }
+      }
     };
-    uint4 lo, hi, nlo, nhi;
+    uint4 lo[kT5RowsPerExp], hi[kT5RowsPerExp], nlo[kT5RowsPerExp], nhi[kT5RowsPerExp];
     fetch(0, lo, hi);
     for (int tile = 0; tile < ntiles; ++tile) {
       const int s = tile & 1, u = tile >> 1;
       fetch(tile + 1, nlo, nhi);
       mbar_wait(bar(2 + s), (u & 1) ^ 1);
-      uint8_t* dst = s_b + s * kT5BStage + e * 16;
-      const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-      if (!(dbg & 2))
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const uint32_t x = w[c >> 1], x1 = x >> 1;
-        const uint32_t s0 = (c & 1) ? 0x2222u : 0x0000u, s1 = (c & 1) ? 0x3333u : 0x1111u;  // byte replication
-        *reinterpret_cast<uint4*>(dst + c * 4096) =
-            make_uint4(__byte_perm(x, 0, s0) & 0x08040201u, __byte_perm(x1, 0, s0) & 0x40201008u,
-                       __byte_perm(x, 0, s1) & 0x08040201u, __byte_perm(x1, 0, s1) & 0x40201008u);
+      for (int i = 0; i < kT5RowsPerExp; ++i) {
+        uint8_t* dst = s_b + s * kT5BStage + (e + i * kT5ExpThreads) * 16;
+        const uint32_t w[8] = {lo[i].x, lo[i].y, lo[i].z, lo[i].w, hi[i].x, hi[i].y, hi[i].z, hi[i].w};
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const uint32_t x = w[c >> 1], x1 = x >> 1;
+          const uint32_t s0 = (c & 1) ? 0x2222u : 0x0000u, s1 = (c & 1) ? 0x3333u : 0x1111u;  // byte replication
+          *reinterpret_cast<uint4*>(dst + c * 4096) =
+              make_uint4(__byte_perm(x, 0, s0) & 0x08040201u, __byte_perm(x1, 0, s0) & 0x40201008u,
+                         __byte_perm(x, 0, s1) & 0x08040201u, __byte_perm(x1, 0, s1) & 0x40201008u);
+        }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_arrive(bar(s));
-      lo = nlo; hi = nhi;
+#pragma unroll
+      for (int i = 0; i < kT5RowsPerExp; ++i) { lo[i] = nlo[i]; hi[i] = nhi[i]; }
     }
   }
 
@@ -299,12 +334,80 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
 int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
                           long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
                           int32_t* o_second) {
-  static const int dbg = getenv("ORB_GPU_TC5_DEBUG") ? atoi(getenv("ORB_GPU_TC5_DEBUG")) : 0;  // timing experiments only
   ORB_CUDA_TRY(cudaFuncSetAttribute(bruteforce_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kT5SmemBytes));
   bruteforce_tc5_kernel<<<grid, kT5Threads, kT5SmemBytes, s>>>(q, nq, db, ndb, slice_rows, idx_base, o_idx, o_best,
-                                                              o_second, dbg);
+                                                              o_second);
   return ORB_GPU_OK;
 }
 
+// Peak probe: thread 0 of one block per SM issues `n` M128 N256 K32 kind::i8 MMAs back to back on fixed operands
+// (the shape and operand layout of bruteforce_tc5_kernel) and waits for the commit.
+__global__ void __launch_bounds__(128, 1) umma_peak_kernel(int n) {
+  extern __shared__ __align__(128) uint8_t t5_smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(t5_smem + kT5ATile + kT5BStage);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 1);
+  const int t = threadIdx.x, warp = t >> 5;
+  for (int i = t; i < (int)(kT5ATile + kT5BStage) / 4; i += 128) reinterpret_cast<uint32_t*>(t5_smem)[i] = 0x01010101u;
+  if (t == 0) {
+    mbar_init(smem_u32(bars), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)),
+                 "r"(kT5TmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  if (t == 0) {
+    const uint64_t da = umma_desc(smem_u32(t5_smem), 2048, 128), db = umma_desc(smem_u32(t5_smem + kT5ATile), 4096, 128);
+    for (int i = 0; i < n; ++i) {
+      const int k = i & 7;
+      umma_i8(tmem_base + ((i >> 3) & 1) * 256, da + (uint64_t)(k * 256), db + (uint64_t)(k * 512), i > 15);
+    }
+    umma_commit(smem_u32(bars));
+    mbar_wait(smem_u32(bars), 0);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kT5TmemCols) : "memory");
+  }
+}
+
 }  // namespace orbgpu
+
+extern "C" int orb_gpu_umma_peak(int device, double* mac_per_s) {
+  using namespace orbgpu;
+  if (!mac_per_s) return ORB_GPU_ERR_ARG;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  int sms = 148;
+  ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  const int smem = (int)(kT5ATile + kT5BStage) + 64, n = 8192;
+  ORB_CUDA_TRY(cudaFuncSetAttribute(umma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  cudaEvent_t e0, e1;
+  ORB_CUDA_TRY(cudaEventCreate(&e0));
+  ORB_CUDA_TRY(cudaEventCreate(&e1));
+  umma_peak_kernel<<<sms, 128, smem>>>(n);
+  float best = 1e30f;
+  for (int r = 0; r < 3; ++r) {
+    ORB_CUDA_TRY(cudaEventRecord(e0));
+    umma_peak_kernel<<<sms, 128, smem>>>(n);
+    ORB_CUDA_TRY(cudaEventRecord(e1));
+    ORB_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    ORB_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    best = ms < best ? ms : best;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  ORB_CUDA_TRY(cudaGetLastError());
+  *mac_per_s = (double)sms * n * 128.0 * 256.0 * 32.0 / (best * 1e-3);
+  return ORB_GPU_OK;
+}

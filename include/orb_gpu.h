@@ -313,8 +313,9 @@ int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const
                          int nlevels, float min_d, float max_d, int th_high, int device,
                          int32_t* best_idx_r, int32_t* best_dist);
 
-/* test/bench knob for the brute-force inner loop: csa = 0 (8 POPC per pair) or 1 (carry-save,
- * 4 POPC per pair; default); qpt = queries per thread (1, 2 or 4). */
+/* test/bench knob for the brute-force kernel: csa = 0 (8 POPC per pair), 1 (carry-save, 4 POPC per pair),
+ * 2 (tensor cores through mma.sync m16n8k32 s8 x u8) or 3 (tcgen05.mma kind::i8 with TMEM accumulators; the
+ * default); qpt = queries per thread of forms 0 and 1 (1, 2 or 4).  All forms return identical results. */
 int orb_gpu_set_bruteforce_variant(int csa, int qpt);
 
 /* Per-stage device time of the last extract call on this handle (CUDA events on the stream the
@@ -332,8 +333,11 @@ int64_t orb_gpu_launch_count(void);
  * denominator for the Hamming roofline; MEASURED_PEAKS.json has no integer figure). */
 int orb_gpu_popc_peak(int device, double* popc_per_s);
 /* Measured multiply-accumulate rate (MAC/s) of mma.sync m16n8k32 s8 x u8 -> s32 (IMMA), the tensor-core path of
- * the default brute-force kernel: 256 MACs per descriptor pair. */
+ * brute-force variant 2: 256 MACs per descriptor pair. */
 int orb_gpu_imma_peak(int device, double* mac_per_s);
+/* Measured multiply-accumulate rate (MAC/s) of tcgen05.mma kind::i8 (M128 N256 K32, operands in shared memory,
+ * accumulators in TMEM), the path of the default brute-force kernel (variant 3): 256 MACs per descriptor pair. */
+int orb_gpu_umma_peak(int device, double* mac_per_s);
 
 #ifdef __cplusplus
 }

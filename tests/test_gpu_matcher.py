@@ -8,7 +8,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("nq,ndb", [(1, 1), (7, 300), (512, 20000), (1000, 70001)])
-@pytest.mark.parametrize("variant", [(0, 1), (1, 2), (1, 4), (2, 2)])  # 8-POPC, carry-save x2, tensor-core form
+@pytest.mark.parametrize("variant", [(0, 1), (1, 2), (1, 4), (2, 2), (3, 2)])  # 8-POPC, carry-save x2, mma.sync, tcgen05
 def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
     q, db = synth.make_match_set(nq, ndb, seed=11)
     gpu.lib().orb_gpu_set_bruteforce_variant(*variant)
@@ -19,7 +19,25 @@ def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
     acc = m.accept(best, second, th=m.TH_HIGH)
     ref = (ob <= 100) & (ob.astype(np.float32) < np.float32(0.9) * os_.astype(np.float32))
     assert np.array_equal(acc, ref)
-    gpu.lib().orb_gpu_set_bruteforce_variant(2, 2)   # back to the default (tensor-core form)
+    gpu.lib().orb_gpu_set_bruteforce_variant(3, 2)   # back to the default (tcgen05 form)
+
+
+@pytest.mark.parametrize("variant", [(2, 2), (3, 2)])
+def test_bruteforce_extreme_descriptors(gpu, oracle, variant):
+    """All-zero / all-one descriptors (S = +-256, the ends of the accumulator range), ragged sizes, planted ties."""
+    rng = np.random.default_rng(5)
+    q = synth.random_descriptors(259, 3)
+    q[0] = 0; q[1] = 255; q[2] = 0x0f; q[3] = 0xf0
+    db = synth.random_descriptors(1031, 4)
+    db[5] = 0; db[6] = 255; db[700] = 255; db[701] = 0; db[1030] = q[258]; db[9] = q[258]
+    db[300] = q[7]; db[301] = q[7]; db[302] = q[7] ^ np.uint8(1)
+    gpu.lib().orb_gpu_set_bruteforce_variant(*variant)
+    try:
+        idx, best, second = gpu.ORBmatcher(0.9).match_bruteforce(q, db)
+    finally:
+        gpu.lib().orb_gpu_set_bruteforce_variant(3, 2)
+    oi, ob, os_ = oracle.match_bruteforce(q, db, threads=4)
+    assert np.array_equal(best, ob) and np.array_equal(second, os_) and np.array_equal(idx, oi)
 
 
 def test_bruteforce_empty_and_ties(gpu, oracle):
