@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Device time of the brute-force matcher variants (4096 x 10M): 8-POPC, carry-save, tensor-core (IMMA)."""
+"""Device time of the brute-force matcher variants (4096 x 10M): 8-POPC, carry-save, mma.sync IMMA, tcgen05 kind::i8 (default)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
@@ -11,7 +11,7 @@ ndb = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
 db = torch.randint(0, 256, (ndb, 32), dtype=torch.uint8, device=dev, generator=g)
 q = torch.randint(0, 256, (4096, 32), dtype=torch.uint8, device=dev, generator=g)
 ref = None
-for name, v in (("8-popc", (0, 2)), ("carry-save", (1, 2)), ("imma", (2, 2))):
+for name, v in (("8-popc", (0, 2)), ("carry-save", (1, 2)), ("imma", (2, 2)), ("tcgen05", (3, 2))):
     orb.lib().orb_gpu_set_bruteforce_variant(*v)
     out = parallel.match_bruteforce_sharded(q, db, 0)
     ts = []
