@@ -211,7 +211,7 @@ def run_ours(args):
     achieved = stage_bytes[top] * B / (acc[top] * 1e-3) / 1e9
     traffic = None  # DRAM bytes per launch of that kernel from the committed ncu capture (per frame x frames per launch)
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "traffic_r03.json")) as f:
             per_frame = json.load(f)["bytes_per_frame"].get(top)
         traffic = per_frame * B if per_frame else None
     except Exception:
