@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <vector>
 
+#include <cstdlib>
 #include "common.cuh"
 
 namespace orbgpu {
@@ -432,9 +433,16 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   const int qpt = g_bf_qpt;
   const bool mma = g_bf_variant >= 2, tc5 = g_bf_variant == 3;  // both tensor-core forms take 256 queries per block
   const int qblocks = mma ? (nq + kMmaQueries - 1) / kMmaQueries : (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
-  // enough database slices to put ~4 waves of blocks on the chip (the tcgen05 form runs one block per SM),
-  // each slice a whole number of tiles
-  long long nslices = std::max<long long>(1, (4LL * sms * (tc5 ? 1 : 4) + qblocks - 1) / qblocks);
+  // Database slices.  tcgen05 form (one block per SM): ONE wave of blocks -- every slice restarts the top-2
+  // scan with no threshold, and the ~100 us a block spends in the exact merge before its threshold has
+  // tightened is paid once per wave (measured: 5.56 -> 5.35 ms at 10 M rows, 0.99 -> 0.79 ms at 1.25 M);
+  // more waves only when a slice would exceed the 22-bit row field of the packed keys.  Other forms: ~4 waves
+  // of 4 blocks per SM.  Each slice is a whole number of tiles.
+  static const int env_waves = [] { const char* e = getenv("ORB_GPU_BF_WAVES"); return e ? atoi(e) : 0; }();
+  long long waves = env_waves > 0 ? env_waves : 1;
+  while (tc5 && waves * sms / qblocks * kBfSliceMax < ndb && waves < 65535) ++waves;
+  long long nslices = tc5 ? std::max<long long>(1, waves * sms / qblocks)
+                          : std::max<long long>(1, (16LL * sms + qblocks - 1) / qblocks);
   long long slice_rows = (ndb + nslices - 1) / nslices;
   slice_rows = std::max<long long>(kBfTile, (slice_rows + kBfTile - 1) / kBfTile * kBfTile);
   slice_rows = std::min<long long>(slice_rows, kBfSliceMax);

@@ -148,10 +148,38 @@ __device__ __forceinline__ void t5_merge64(const uint32_t (&v)[32], int col0, in
   t5_merge2(b[0], s2[0], b[2], s2[2]);
   t5_merge2(best, second, b[0], s2[0]);
 }
+// exact top-2 merge of the 16 columns held by registers 8 * J .. 8 * J + 7 (same keys as t5_merge64)
+template <int J>
+__device__ __forceinline__ void t5_merge16(const uint32_t (&v)[32], int col0, unsigned& best, unsigned& second) {
+  const unsigned kbase = (256u << 22) + 0x3fffffu - (unsigned)col0;
+  unsigned b[2] = {0, 0}, s2[2] = {0, 0};
+#pragma unroll
+  for (int r = 8 * J; r < 8 * J + 8; ++r) {
+    const unsigned k0 = (v[r] << 16) + (kbase - 2 * r), k1 = (v[r] & 0xffff0000u) + (kbase - (2 * r + 1));
+    t5_merge2(b[r & 1], s2[r & 1], max(k0, k1), min(k0, k1));
+  }
+  t5_merge2(b[0], s2[0], b[1], s2[1]);
+  t5_merge2(best, second, b[0], s2[0]);
+}
+template <int J>
+__device__ __forceinline__ void t5_scan16(const uint32_t (&v)[32], int col0, unsigned& best, unsigned& second,
+                                          uint32_t thr2) {
+  uint32_t m = __vmaxs2(__vmaxs2(v[8 * J], v[8 * J + 1]), __vmaxs2(v[8 * J + 2], v[8 * J + 3]));
+  m = __vmaxs2(m, __vmaxs2(__vmaxs2(v[8 * J + 4], v[8 * J + 5]), __vmaxs2(v[8 * J + 6], v[8 * J + 7])));
+  if (__any_sync(0xffffffffu, t5_hit(m, thr2))) t5_merge16<J>(v, col0, best, second);
+}
+// A 64-column chunk in which some query of the warp beats its running second best: after the first few thousand
+// rows of a slice that is one column in 64, so the quarter that holds it is found first and only it is merged.
 __device__ __forceinline__ void t5_scan64(const uint32_t (&v)[32], int col0, int rows, unsigned& best,
                                           unsigned& second, uint32_t& thr2) {
-  if (rows - col0 >= 64) t5_merge64<false>(v, col0, rows, best, second);
-  else t5_merge64<true>(v, col0, rows, best, second);
+  if (rows - col0 >= 64) {
+    t5_scan16<0>(v, col0, best, second, thr2);
+    t5_scan16<1>(v, col0, best, second, thr2);
+    t5_scan16<2>(v, col0, best, second, thr2);
+    t5_scan16<3>(v, col0, best, second, thr2);
+  } else {
+    t5_merge64<true>(v, col0, rows, best, second);
+  }
   if (second) thr2 = (((second >> 22) * 64u - 16384u) & 0xffffu) * 0x10001u;
 }
 
