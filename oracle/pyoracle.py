@@ -14,6 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "liborb_oracle.so")
 REF_PATH = os.path.join(HERE, "_ref", "libref_orb.so")
 REF_SEQ_PATH = os.path.join(HERE, "_ref", "libref_orb_seq.so")
+REF_MATCHER_PATH = os.path.join(HERE, "_ref", "libref_matcher.so")   # src/ORBmatcher.cc verbatim over oracle/slam_shim
 
 KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
                      ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
@@ -34,6 +35,31 @@ def build(force=False):
 
 _lib = None
 _ref = None
+_refm = None
+
+
+def have_ref_matcher():
+    return os.path.exists(REF_MATCHER_PATH)
+
+
+def ref_matcher():
+    """The reference's own src/ORBmatcher.cc, compiled verbatim (oracle/Makefile target `refmatch`)."""
+    global _refm
+    if _refm is None:
+        if not have_ref_matcher():
+            raise RuntimeError("oracle/_ref/libref_matcher.so is not built (needs /root/reference)")
+        _refm = C.CDLL(REF_MATCHER_PATH)
+    return _refm
+
+
+def _m(impl, name):
+    """Entry point `name` of the restated oracle (impl="oracle") or of the verbatim reference build
+    (impl="reference"): both take the same flat arrays."""
+    if impl == "oracle":
+        return getattr(lib(), "orbo_" + name)
+    if impl == "reference":
+        return getattr(ref_matcher(), "refm_" + name)
+    raise ValueError(impl)
 
 
 def _p(a):
@@ -193,10 +219,10 @@ def extract_batch(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, thre
     return counts, kps, desc
 
 
-def descriptor_distance(a, b):
+def descriptor_distance(a, b, impl="oracle"):
     a = u8c(a)
     b = u8c(b)
-    return lib().orbo_descriptor_distance(_p(a), _p(b))
+    return _m(impl, "descriptor_distance")(_p(a), _p(b))
 
 
 def match_bruteforce(q, db, threads=1):
@@ -212,7 +238,7 @@ def match_bruteforce(q, db, threads=1):
 
 
 def search_by_projection(queries, qdesc, kps, kdesc, u_right, grid, scale_factors, th, nnratio,
-                         th_high=100, blocked=None):
+                         th_high=100, blocked=None, impl="oracle"):
     """grid = (minX, minY, invW, invH).  -> nmatches, match_of_kp[nk], blocked_after[nk]"""
     queries = np.ascontiguousarray(queries, PROJ_DTYPE)
     qdesc = u8c(qdesc)
@@ -223,7 +249,7 @@ def search_by_projection(queries, qdesc, kps, kdesc, u_right, grid, scale_factor
     ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
     sf = np.ascontiguousarray(scale_factors, np.float32)
     out = np.empty(nk, np.int32)
-    n = lib().orbo_search_by_projection(_p(queries), _p(qdesc), len(queries), _p(kps), _p(kdesc),
+    n = _m(impl, "search_by_projection")(_p(queries), _p(qdesc), len(queries), _p(kps), _p(kdesc),
                                         _p(ur), nk,
                                         C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
                                         C.c_float(grid[3]), _p(sf), C.c_float(th), C.c_float(nnratio),
@@ -268,7 +294,7 @@ def _fv_args(fv):
     return (node, start, idx), (_p(node), _p(start), _p(idx), len(node))
 
 
-def search_by_bow_frame(fv1, fv2, kps1, d1, good_mp1, kps2, d2, nnratio, check_orientation):
+def search_by_bow_frame(fv1, fv2, kps1, d1, good_mp1, kps2, d2, nnratio, check_orientation, impl="oracle"):
     """M6 SearchByBoW(KF, Frame) -> nmatches, match_of_2[n2] (key-frame feature index or -1)"""
     k1, a1 = _fv_args(fv1)
     k2, a2 = _fv_args(fv2)
@@ -276,12 +302,13 @@ def search_by_bow_frame(fv1, fv2, kps1, d1, good_mp1, kps2, d2, nnratio, check_o
     d1 = u8c(d1); d2 = u8c(d2)
     g1 = np.ascontiguousarray(good_mp1, np.uint8)
     out = np.empty(len(kps2), np.int32)
-    n = lib().orbo_search_by_bow_frame(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), len(kps2),
+    n = _m(impl, "search_by_bow_frame")(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), len(kps2),
                                        C.c_float(nnratio), int(bool(check_orientation)), _p(out))
     return n, out
 
 
-def search_by_bow_keyframes(fv1, fv2, kps1, d1, good_mp1, kps2, d2, good_mp2, nnratio, check_orientation):
+def search_by_bow_keyframes(fv1, fv2, kps1, d1, good_mp1, kps2, d2, good_mp2, nnratio, check_orientation,
+                            impl="oracle"):
     """M6 SearchByBoW(KF, KF) -> nmatches, match12[n1]"""
     k1, a1 = _fv_args(fv1)
     k2, a2 = _fv_args(fv2)
@@ -289,13 +316,13 @@ def search_by_bow_keyframes(fv1, fv2, kps1, d1, good_mp1, kps2, d2, good_mp2, nn
     d1 = u8c(d1); d2 = u8c(d2)
     g1 = np.ascontiguousarray(good_mp1, np.uint8); g2 = np.ascontiguousarray(good_mp2, np.uint8)
     out = np.empty(len(kps1), np.int32)
-    n = lib().orbo_search_by_bow_keyframes(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), _p(g2),
+    n = _m(impl, "search_by_bow_keyframes")(*a1, *a2, _p(kps1), _p(d1), _p(g1), len(kps1), _p(kps2), _p(d2), _p(g2),
                                            len(kps2), C.c_float(nnratio), int(bool(check_orientation)), _p(out))
     return n, out
 
 
 def search_for_triangulation(fv1, fv2, kps1, d1, ur1, has_mp1, kps2, d2, ur2, has_mp2, F12, ex, ey, scale_factors2,
-                             level_sigma2_2, only_stereo, check_orientation):
+                             level_sigma2_2, only_stereo, check_orientation, impl="oracle"):
     """M6 SearchForTriangulation -> nmatches, match12[n1]"""
     k1, a1 = _fv_args(fv1)
     k2, a2 = _fv_args(fv2)
@@ -308,20 +335,23 @@ def search_for_triangulation(fv1, fv2, kps1, d1, ur1, has_mp1, kps2, d2, ur2, ha
     sf = np.ascontiguousarray(scale_factors2, np.float32)
     sg = np.ascontiguousarray(level_sigma2_2, np.float32)
     out = np.empty(len(kps1), np.int32)
-    n = lib().orbo_search_for_triangulation(*a1, *a2, _p(kps1), _p(d1), _p(u1), _p(h1), len(kps1), _p(kps2), _p(d2),
+    n = _m(impl, "search_for_triangulation")(*a1, *a2, _p(kps1), _p(d1), _p(u1), _p(h1), len(kps1), _p(kps2), _p(d2),
                                             _p(u2), _p(h2), len(kps2), _p(F), C.c_float(ex), C.c_float(ey), _p(sf),
                                             _p(sg), int(bool(only_stereo)), int(bool(check_orientation)), _p(out))
     return n, out
 
 
-def search_for_initialization(kps1, d1, prev_matched, kps2, d2, grid, window, nnratio, check_orientation):
+def search_for_initialization(kps1, d1, prev_matched, kps2, d2, grid, window, nnratio, check_orientation,
+                              impl="oracle"):
     """M7 SearchForInitialization -> nmatches, match12[n1] (vbPrevMatched is left to the caller)"""
     kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
     d1 = u8c(d1); d2 = u8c(d2)
+    # the verbatim reference updates vbPrevMatched in place (:514-517): it gets the caller's array when that is
+    # a contiguous float32 array, so the caller sees the update
     pm = np.ascontiguousarray(prev_matched, np.float32).reshape(-1)
     assert len(pm) == 2 * len(kps1)
     out = np.empty(len(kps1), np.int32)
-    n = lib().orbo_search_for_initialization(_p(kps1), _p(d1), len(kps1), _p(pm), _p(kps2), _p(d2), len(kps2),
+    n = _m(impl, "search_for_initialization")(_p(kps1), _p(d1), len(kps1), _p(pm), _p(kps2), _p(d2), len(kps2),
                                              C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
                                              C.c_float(grid[3]), int(window), C.c_float(nnratio),
                                              int(bool(check_orientation)), _p(out))

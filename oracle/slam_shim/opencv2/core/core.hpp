@@ -1,0 +1,122 @@
+// TEST INFRASTRUCTURE.  Minimal stand-in for the slice of the OpenCV C++ API that the reference's
+// src/ORBmatcher.cc uses (descriptor matrices of bytes, small float matrices for poses), so that file compiles
+// UNMODIFIED here: OpenCV's C++ headers/libs are absent from the image and the reference does not vendor them.
+// Our own code, not OpenCV's.  Float matrix products accumulate in double and round once to float, like
+// OpenCV's generic GEMM for CV_32F; only the verbatim build sees these values -- the windows the reference
+// derives from them are recorded (slam_shim.h) and handed to the oracle / GPU as inputs.
+#pragma once
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+typedef unsigned char uchar;
+#define CV_8U 0
+#define CV_8UC1 0
+#define CV_32F 5
+
+namespace cv {
+
+template <typename T>
+struct Point_ {
+  T x, y;
+  Point_() : x(0), y(0) {}
+  Point_(T x_, T y_) : x(x_), y(y_) {}
+};
+typedef Point_<float> Point2f;
+
+struct KeyPoint {  // 28 bytes, same field order as cv::KeyPoint
+  Point2f pt;
+  float size, angle, response;
+  int octave, class_id;
+  KeyPoint() : pt(0, 0), size(0), angle(-1), response(0), octave(0), class_id(-1) {}
+};
+
+class Mat {
+ public:
+  int rows = 0, cols = 0;
+  uchar* data = nullptr;
+  size_t step = 0;
+
+  Mat() {}
+  Mat(int r, int c, int type) { create(r, c, type); }
+  void create(int r, int c, int type) {
+    type_ = type;
+    buf_ = std::make_shared<std::vector<uchar>>((size_t)r * c * esz(), 0);
+    data = buf_->data();
+    rows = r; cols = c; step = (size_t)c * esz();
+  }
+  int type() const { return type_; }
+  bool empty() const { return !data || !rows || !cols; }
+  size_t esz() const { return type_ == CV_32F ? 4 : 1; }
+  Mat clone() const {
+    Mat m(rows, cols, type_);
+    for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols * esz());
+    return m;
+  }
+  Mat rowRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * step; m.rows = b - a; return m; }
+  Mat colRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * esz(); m.cols = b - a; return m; }
+  Mat row(int y) const { return rowRange(y, y + 1); }
+  Mat col(int x) const { return colRange(x, x + 1); }
+  template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + (size_t)x * sizeof(T)); }
+  template <typename T> const T& at(int y, int x) const { return *(const T*)(data + (size_t)y * step + (size_t)x * sizeof(T)); }
+  // single index: element i of a row or column vector
+  template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+  template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+  uchar* ptr(int y = 0) { return data + (size_t)y * step; }
+  const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
+  template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
+  template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }
+  Mat t() const {
+    Mat m(cols, rows, CV_32F);
+    for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+    return m;
+  }
+  double dot(const Mat& b) const {  // CV_32F dot product accumulates in double
+    double s = 0;
+    for (int y = 0; y < rows; ++y) for (int x = 0; x < cols; ++x) s += (double)at<float>(y, x) * b.at<float>(y, x);
+    return s;
+  }
+
+ private:
+  int type_ = CV_8U;
+  std::shared_ptr<std::vector<uchar>> buf_;
+};
+
+inline Mat operator*(const Mat& a, const Mat& b) {
+  assert(a.cols == b.rows);
+  Mat m(a.rows, b.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < b.cols; ++x) {
+      double s = 0;
+      for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(y, k) * (double)b.at<float>(k, x);
+      m.at<float>(y, x) = (float)s;
+    }
+  return m;
+}
+template <class F>
+inline Mat mat_map2(const Mat& a, const Mat& b, F f) {
+  assert(a.rows == b.rows && a.cols == b.cols);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = f(a.at<float>(y, x), b.at<float>(y, x));
+  return m;
+}
+template <class F>
+inline Mat mat_map1(const Mat& a, F f) {
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = f(a.at<float>(y, x));
+  return m;
+}
+inline Mat operator+(const Mat& a, const Mat& b) { return mat_map2(a, b, [](float p, float q) { return p + q; }); }
+inline Mat operator-(const Mat& a, const Mat& b) { return mat_map2(a, b, [](float p, float q) { return p - q; }); }
+inline Mat operator-(const Mat& a) { return mat_map1(a, [](float p) { return -p; }); }
+inline Mat operator*(double s, const Mat& a) { return mat_map1(a, [s](float p) { return (float)(p * s); }); }
+inline Mat operator*(const Mat& a, double s) { return s * a; }
+inline Mat operator/(const Mat& a, double s) { return mat_map1(a, [s](float p) { return (float)(p / s); }); }
+inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+
+}  // namespace cv
