@@ -505,3 +505,120 @@ def ref_extract_batch(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, 
     ref().ref_extract_batch(nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th, _p(frames),
                             B, W, H, C.c_size_t(W), C.c_size_t(W * H), threads, _p(counts))
     return counts
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, np.float32)
+
+
+def ref_search_last_frame(cam, Tcw_cur, Tcw_last, kps_cur, d_cur, ur_cur, scale_factors, blocked, kps_last, has_mp,
+                          outlier, world_pos, mp_desc, mp_obs, th, mono, check_orientation):
+    """The reference's SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1328-1470), verbatim.
+    cam = (fx, fy, cx, cy, mbf, mb, minX, minY, maxX, maxY, invW, invH); poses row-major 3x4.
+    -> nmatches, match_of_kp[n_cur] (last-frame feature or -1), windows[n_last] (WINDOW_DTYPE: what it searched)."""
+    cam = _f32(cam); Tc = _f32(Tcw_cur).reshape(12); Tl = _f32(Tcw_last).reshape(12)
+    kc = np.ascontiguousarray(kps_cur, KP_DTYPE); kl = np.ascontiguousarray(kps_last, KP_DTYPE)
+    dc = u8c(d_cur); md = u8c(mp_desc)
+    ur = _f32(ur_cur); sf = _f32(scale_factors)
+    bl = None if blocked is None else np.ascontiguousarray(blocked, np.uint8)
+    hm = np.ascontiguousarray(has_mp, np.uint8); ol = np.ascontiguousarray(outlier, np.uint8)
+    wp = _f32(world_pos); ob = np.ascontiguousarray(mp_obs, np.int32)
+    out = np.empty(len(kc), np.int32)
+    win = np.zeros(len(kl), WINDOW_DTYPE)
+    n = ref_matcher().refm_search_last_frame(_p(cam), _p(Tc), _p(Tl), _p(kc), _p(dc), _p(ur), len(kc), _p(sf), len(sf),
+                                             _p(bl), _p(kl), len(kl), _p(hm), _p(ol), _p(wp), _p(md), _p(ob),
+                                             C.c_float(th), int(bool(mono)), int(bool(check_orientation)), _p(out),
+                                             _p(win))
+    return n, out, win
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(a, np.int32)
+
+
+def _u8(a):
+    return None if a is None else np.ascontiguousarray(a, np.uint8)
+
+
+def ref_search_keyframe_points(cam, Tcw_cur, kps_cur, d_cur, scale_factors, cur_has_mp, kps_kf, has_mp, world_pos,
+                               desc, flags, dist_inv, pred_level, th, orb_dist, check_orientation):
+    """The reference's SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1472-1599), verbatim.
+    flags: bit 0 bad, bit 1 in sAlreadyFound.  -> nmatches, match_of_kp[n_cur], windows[n]"""
+    cam = _f32(cam); Tc = _f32(Tcw_cur).reshape(12)
+    kc = np.ascontiguousarray(kps_cur, KP_DTYPE); kk = np.ascontiguousarray(kps_kf, KP_DTYPE)
+    dc = u8c(d_cur); sf = _f32(scale_factors); ch = _u8(cur_has_mp); hm = _u8(has_mp)
+    wp = _f32(world_pos); ds = u8c(desc); fl = _u8(flags); di = _f32(dist_inv); pl = _i32(pred_level)
+    out = np.empty(len(kc), np.int32)
+    win = np.zeros(len(kk), WINDOW_DTYPE)
+    n = ref_matcher().refm_search_keyframe_points(_p(cam), _p(Tc), _p(kc), _p(dc), len(kc), _p(sf), len(sf), _p(ch),
+                                                  _p(kk), _p(hm), len(kk), _p(wp), _p(ds), _p(fl), _p(di), _p(pl),
+                                                  C.c_float(th), int(orb_dist), int(bool(check_orientation)),
+                                                  _p(out), _p(win))
+    return n, out, win
+
+
+def ref_search_sim3_projection(cam, Scw, kps_kf, d_kf, scale_factors, kf_matched, world_pos, normal, desc, flags,
+                               dist_inv, pred_level, th):
+    """The reference's SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:290-403), verbatim.
+    -> nmatches, match_of_kp[n_kf] (cloud point newly written into vpMatched, or -1), windows[n]"""
+    cam = _f32(cam); S = _f32(Scw).reshape(12)
+    kk = np.ascontiguousarray(kps_kf, KP_DTYPE); dk = u8c(d_kf); sf = _f32(scale_factors); km = _u8(kf_matched)
+    wp = _f32(world_pos); nm = _f32(normal); ds = u8c(desc); fl = _u8(flags); di = _f32(dist_inv); pl = _i32(pred_level)
+    out = np.empty(len(kk), np.int32)
+    win = np.zeros(len(ds), WINDOW_DTYPE)
+    n = ref_matcher().refm_search_sim3_projection(_p(cam), _p(S), _p(kk), _p(dk), len(kk), _p(sf), len(sf), _p(km),
+                                                  len(ds), _p(wp), _p(nm), _p(ds), _p(fl), _p(di), _p(pl), int(th),
+                                                  _p(out), _p(win))
+    return n, out, win
+
+
+def ref_fuse(cam, Tcw, kps_kf, d_kf, ur_kf, scale_factors, level_sigma2, kf_obs, world_pos, normal, desc, flags, obs,
+             dist_inv, pred_level, th):
+    """The reference's Fuse(pKF, vpMapPoints, th) (:825-975), verbatim.  flags: bit 0 bad, bit 1 IsInKeyFrame.
+    -> nFused, match_of_query[n], action[n] (1 add, 2 point replaced by the key frame's, 3 the reverse), windows[n]"""
+    cam = _f32(cam); T = _f32(Tcw).reshape(12)
+    kk = np.ascontiguousarray(kps_kf, KP_DTYPE); dk = u8c(d_kf); ur = _f32(ur_kf); sf = _f32(scale_factors)
+    sg = _f32(level_sigma2); ko = _i32(kf_obs)
+    wp = _f32(world_pos); nm = _f32(normal); ds = u8c(desc); fl = _u8(flags); ob = _i32(obs); di = _f32(dist_inv)
+    pl = _i32(pred_level)
+    mq = np.empty(len(ds), np.int32); act = np.empty(len(ds), np.int32)
+    win = np.zeros(len(ds), WINDOW_DTYPE)
+    n = ref_matcher().refm_fuse(_p(cam), _p(T), _p(kk), _p(dk), _p(ur), len(kk), _p(sf), _p(sg), len(sf), _p(ko),
+                                len(ds), _p(wp), _p(nm), _p(ds), _p(fl), _p(ob), _p(di), _p(pl), C.c_float(th),
+                                _p(mq), _p(act), _p(win))
+    return n, mq, act, win
+
+
+def ref_search_by_sim3(cam, T1w, T2w, s12, R12, t12, scale_factors, kf1, kf2, pre12, th):
+    """The reference's SearchBySim3 (:1102-1326), verbatim.  kf1 / kf2: dict(kps, desc, has_mp, pos, flags, dist_inv,
+    pred_level).  -> nFound, match12[n1], windows12[n1], windows21[n2]"""
+    cam = _f32(cam); a = _f32(T1w).reshape(12); b = _f32(T2w).reshape(12)
+    R = _f32(R12).reshape(9); t = _f32(t12).reshape(3); sf = _f32(scale_factors)
+
+    def side(k):
+        return (np.ascontiguousarray(k["kps"], KP_DTYPE), u8c(k["desc"]), _u8(k["has_mp"]), _f32(k["pos"]),
+                _u8(k["flags"]), _f32(k["dist_inv"]), _i32(k["pred_level"]))
+    s1, s2 = side(kf1), side(kf2)
+    n1, n2 = len(s1[0]), len(s2[0])
+    pre = _i32(pre12)
+    out = np.empty(n1, np.int32)
+    w12 = np.zeros(n1, WINDOW_DTYPE); w21 = np.zeros(n2, WINDOW_DTYPE)
+    n = ref_matcher().refm_search_by_sim3(_p(cam), _p(a), _p(b), C.c_float(s12), _p(R), _p(t), _p(sf), len(sf),
+                                          _p(s1[0]), _p(s1[1]), _p(s1[2]), n1, _p(s1[3]), _p(s1[4]), _p(s1[5]), _p(s1[6]),
+                                          _p(s2[0]), _p(s2[1]), _p(s2[2]), n2, _p(s2[3]), _p(s2[4]), _p(s2[5]), _p(s2[6]),
+                                          _p(pre), C.c_float(th), _p(out), _p(w12), _p(w21))
+    return n, out, w12, w21
+
+
+def ref_fuse_sim3(cam, Scw, kps_kf, d_kf, scale_factors, kf_obs, world_pos, normal, desc, flags, dist_inv, pred_level,
+                  th):
+    """The reference's Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:977-1100), verbatim.
+    -> nFused, match_of_query[n], replace[n], windows[n]"""
+    cam = _f32(cam); S = _f32(Scw).reshape(12)
+    kk = np.ascontiguousarray(kps_kf, KP_DTYPE); dk = u8c(d_kf); sf = _f32(scale_factors); ko = _i32(kf_obs)
+    wp = _f32(world_pos); nm = _f32(normal); ds = u8c(desc); fl = _u8(flags); di = _f32(dist_inv); pl = _i32(pred_level)
+    mq = np.empty(len(ds), np.int32); rp = np.empty(len(ds), np.int32)
+    win = np.zeros(len(ds), WINDOW_DTYPE)
+    n = ref_matcher().refm_fuse_sim3(_p(cam), _p(S), _p(kk), _p(dk), len(kk), _p(sf), len(sf), _p(ko), len(ds), _p(wp),
+                                     _p(nm), _p(ds), _p(fl), _p(di), _p(pl), C.c_float(th), _p(mq), _p(rp), _p(win))
+    return n, mq, rp, win

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <set>
 #include <vector>
 
 #include "ORBmatcher.h"
@@ -313,6 +314,243 @@ int refm_search_last_frame(const float* cam12, const float* Tcw_cur, const float
     }
   for (int i = 0; i < n_cur; ++i) match_of_kp[i] = index_of(pc.index, cur.mvpMapPoints[i]);
   return n;
+}
+
+}  // extern "C"
+
+// ---- projection searches over a cloud of map points ------------------------------------------------------------
+// cloud arrays (n points): world_pos[3n], normal[3n] (may be null), desc[32n], flags[n] (bit 0 bad, bit 1 already
+// found / already in the key frame), obs[n], dist_inv[2n] (min, max distance invariance), pred_level[n].
+namespace {
+struct CloudArgs {
+  int n; const float* world_pos; const float* normal; const uint8_t* desc; const uint8_t* flags; const int32_t* obs;
+  const float* dist_inv; const int32_t* pred_level;
+};
+MapPoint* add_cloud_point(PointCloud& pc, const CloudArgs& c, int i) {
+  MapPoint* p = pc.add(i, c.world_pos + 3 * i, c.normal ? c.normal + 3 * i : nullptr, c.desc + (size_t)i * 32,
+                       c.obs ? c.obs[i] : 1);
+  p->mbBad = c.flags && (c.flags[i] & 1);
+  if (c.dist_inv) { p->min_dist_inv = c.dist_inv[2 * i]; p->max_dist_inv = c.dist_inv[2 * i + 1]; }
+  if (c.pred_level) p->predicted_level = c.pred_level[i];
+  return p;
+}
+void clear_windows(orbo::WindowQuery* w, int n) { if (n) std::memset(w, 0, (size_t)n * sizeof(orbo::WindowQuery)); }
+void reset_log() { ShimLog::get().calls.clear(); ShimLog::get().map_point_reads.clear(); ShimLog::get().last_mp = nullptr; }
+// KeyFrame::SetPose (src/KeyFrame.cc:75-92): Ow = -Rcw^T * tcw
+void set_kf_pose(KeyFrame& k, const float* rt) {
+  k.Tcw = pose44(rt);
+  cv::Mat Rcw = k.Tcw.rowRange(0, 3).colRange(0, 3);
+  cv::Mat tcw = k.Tcw.rowRange(0, 3).col(3);
+  cv::Mat Rwc = Rcw.t();
+  k.Ow = -Rwc * tcw;
+}
+}  // namespace
+
+extern "C" {
+
+// src/ORBmatcher.cc:1472-1599, SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist): the cloud is
+// the key frame's map points by feature (has_mp[i] == 0: none); kps_kf carries the source angles.
+int refm_search_keyframe_points(const float* cam12, const float* Tcw_cur, const orbo::KeyPoint* kps_cur,
+                                const uint8_t* d_cur, int n_cur, const float* scale_factors, int nlevels,
+                                const uint8_t* cur_has_mp, const orbo::KeyPoint* kps_kf, const uint8_t* has_mp,
+                                int n, const float* world_pos, const uint8_t* desc, const uint8_t* flags,
+                                const float* dist_inv, const int32_t* pred_level, float th, int orb_dist,
+                                int check_ori, int32_t* match_of_kp, orbo::WindowQuery* windows) {
+  Camera cam;
+  std::memcpy(&cam, cam12, sizeof(cam));
+  Frame cur;
+  fill_frame(cur, cam, kps_cur, d_cur, nullptr, n_cur, scale_factors, nlevels);
+  cur.mTcw = pose44(Tcw_cur);
+  MapPoint holder;
+  for (int i = 0; i < n_cur; ++i) if (cur_has_mp && cur_has_mp[i]) cur.mvpMapPoints[i] = &holder;
+  std::vector<uint8_t> zero((size_t)std::max(n, 1) * 32, 0);
+  auto kf = make_keyframe(cam, kps_kf, zero.data(), nullptr, n, scale_factors, nullptr, nlevels);
+  CloudArgs c{n, world_pos, nullptr, desc, flags, nullptr, dist_inv, pred_level};
+  PointCloud pc;
+  std::set<MapPoint*> found;
+  clear_windows(windows, n);
+  for (int i = 0; i < n; ++i) {
+    windows[i].angle = kps_kf[i].angle;
+    windows[i].blocks = 1;
+    if (!has_mp[i]) continue;
+    kf->mvpMapPoints[i] = add_cloud_point(pc, c, i);
+    if (flags[i] & 2) found.insert(kf->mvpMapPoints[i]);
+  }
+  reset_log();
+  ORBmatcher matcher(0.9f, check_ori != 0);
+  const int nm = matcher.SearchByProjection(cur, kf.get(), found, th, orb_dist);
+  windows_from_log(pc.index, windows);
+  for (int i = 0; i < n_cur; ++i) match_of_kp[i] = index_of(pc.index, cur.mvpMapPoints[i]);
+  return nm;
+}
+
+// src/ORBmatcher.cc:290-403, SearchByProjection(pKF, Scw, vpPoints, vpMatched, th).  Scw row-major 3x4 (scaled
+// rotation | translation).  kf_matched[i]: vpMatched[i] is already set.  Cloud flag bit 1: the point is one of
+// those already in vpMatched.  match_of_kp[n_kf] = cloud point now in vpMatched[i], or -1.
+int refm_search_sim3_projection(const float* cam12, const float* Scw, const orbo::KeyPoint* kps_kf,
+                                const uint8_t* d_kf, int n_kf, const float* scale_factors, int nlevels,
+                                const uint8_t* kf_matched, int n, const float* world_pos, const float* normal,
+                                const uint8_t* desc, const uint8_t* flags, const float* dist_inv,
+                                const int32_t* pred_level, int th, int32_t* match_of_kp,
+                                orbo::WindowQuery* windows) {
+  Camera cam;
+  std::memcpy(&cam, cam12, sizeof(cam));
+  auto kf = make_keyframe(cam, kps_kf, d_kf, nullptr, n_kf, scale_factors, nullptr, nlevels);
+  CloudArgs c{n, world_pos, normal, desc, flags, nullptr, dist_inv, pred_level};
+  PointCloud pc;
+  std::vector<MapPoint*> points, matched((size_t)n_kf, nullptr);
+  MapPoint holder;
+  std::vector<int> found_points;
+  for (int i = 0; i < n; ++i) {
+    points.push_back(add_cloud_point(pc, c, i));
+    if (flags[i] & 2) found_points.push_back(i);
+  }
+  // already matched key-frame features hold either one of the cloud's "already found" points or a foreign point
+  size_t next = 0;
+  for (int i = 0; i < n_kf; ++i)
+    if (kf_matched[i]) matched[i] = next < found_points.size() ? points[found_points[next++]] : &holder;
+  std::vector<MapPoint*> before = matched;
+  clear_windows(windows, n);
+  for (int i = 0; i < n; ++i) windows[i].blocks = 1;
+  reset_log();
+  ORBmatcher matcher(0.75f, true);
+  const int nm = matcher.SearchByProjection(kf.get(), pose44(Scw), points, matched, th);
+  windows_from_log(pc.index, windows);
+  for (int i = 0; i < n; ++i)
+    if (windows[i].valid) { windows[i].min_level = pred_level[i] - 1; windows[i].max_level = pred_level[i]; }  // :372-375
+  for (int i = 0; i < n_kf; ++i) match_of_kp[i] = matched[i] != before[i] ? index_of(pc.index, matched[i]) : -1;
+  return nm;
+}
+
+// src/ORBmatcher.cc:825-975, Fuse(pKF, vpMapPoints, th).  kf_obs[i] >= 0: key-frame feature i holds a map point
+// with that many observations (-1: none).  Cloud flag bit 1: IsInKeyFrame(pKF).  match_of_query[n] = the
+// key-frame feature the point was fused with (what pKF->GetMapPoint(bestIdx) was asked for), or -1;
+// action[n]: 0 none, 1 AddObservation + AddMapPoint, 2 pMP->Replace(pMPinKF), 3 pMPinKF->Replace(pMP).
+int refm_fuse(const float* cam12, const float* Tcw, const orbo::KeyPoint* kps_kf, const uint8_t* d_kf,
+              const float* ur_kf, int n_kf, const float* scale_factors, const float* level_sigma2, int nlevels,
+              const int32_t* kf_obs, int n, const float* world_pos, const float* normal, const uint8_t* desc,
+              const uint8_t* flags, const int32_t* obs, const float* dist_inv, const int32_t* pred_level, float th,
+              int32_t* match_of_query, int32_t* action, orbo::WindowQuery* windows) {
+  Camera cam;
+  std::memcpy(&cam, cam12, sizeof(cam));
+  auto kf = make_keyframe(cam, kps_kf, d_kf, ur_kf, n_kf, scale_factors, level_sigma2, nlevels);
+  set_kf_pose(*kf, Tcw);
+  PointCloud in_kf;
+  for (int i = 0; i < n_kf; ++i)
+    if (kf_obs[i] >= 0) kf->mvpMapPoints[i] = in_kf.add(i, nullptr, nullptr, nullptr, kf_obs[i]);
+  CloudArgs c{n, world_pos, normal, desc, flags, obs, dist_inv, pred_level};
+  PointCloud pc;
+  std::vector<MapPoint*> points;
+  for (int i = 0; i < n; ++i) {
+    points.push_back(add_cloud_point(pc, c, i));
+    if (flags[i] & 2) points.back()->mObservations[kf.get()] = 0;
+  }
+  clear_windows(windows, n);
+  reset_log();
+  ORBmatcher matcher(0.6f, true);
+  const int nf = matcher.Fuse(kf.get(), points, th);
+  windows_from_log(pc.index, windows);
+  const cv::Mat Rcw = kf->GetRotation(), tcw = kf->GetTranslation();
+  for (int i = 0; i < n; ++i) {
+    match_of_query[i] = -1;
+    action[i] = 0;
+    if (!windows[i].valid) continue;
+    windows[i].min_level = pred_level[i] - 1; windows[i].max_level = pred_level[i];  // :906-909
+    cv::Mat p3Dc = Rcw * points[i]->mWorldPos + tcw;                                 // ur of :869
+    const float invz = 1 / p3Dc.at<float>(2);
+    windows[i].ur = windows[i].u - kf->mbf * invz;
+  }
+  for (const auto& r : ShimLog::get().map_point_reads) {
+    const int i = index_of(pc.index, r.first);
+    if (i >= 0) match_of_query[i] = (int32_t)r.second;
+  }
+  for (int i = 0; i < n; ++i) {
+    if (!points[i]->added.empty()) action[i] = 1;
+    else if (points[i]->replaced_by) action[i] = 2;
+  }
+  for (const auto& q : in_kf.own)
+    if (q->replaced_by) { const int i = index_of(pc.index, q->replaced_by); if (i >= 0 && !action[i]) action[i] = 3; }
+  return nf;
+}
+
+// src/ORBmatcher.cc:1102-1326, SearchBySim3.  Each key frame: pose (row-major 3x4), keypoints, descriptors and the
+// cloud of its map points by feature (has_mp).  pre12[i] >= 0: vpMatches12[i] is already the map point of feature
+// pre12[i] of key frame 2.  Out: match12[n1] (feature of key frame 2 or -1; pre-set entries stay), the windows of
+// both passes.
+int refm_search_by_sim3(const float* cam12, const float* T1w, const float* T2w, float s12, const float* R12,
+                        const float* t12, const float* scale_factors, int nlevels,
+                        const orbo::KeyPoint* kps1, const uint8_t* d1, const uint8_t* has1, int n1,
+                        const float* pos1, const uint8_t* flags1, const float* dist_inv1, const int32_t* lvl1,
+                        const orbo::KeyPoint* kps2, const uint8_t* d2, const uint8_t* has2, int n2,
+                        const float* pos2, const uint8_t* flags2, const float* dist_inv2, const int32_t* lvl2,
+                        const int32_t* pre12, float th, int32_t* match12, orbo::WindowQuery* win12,
+                        orbo::WindowQuery* win21) {
+  Camera cam;
+  std::memcpy(&cam, cam12, sizeof(cam));
+  auto kf1 = make_keyframe(cam, kps1, d1, nullptr, n1, scale_factors, nullptr, nlevels);
+  auto kf2 = make_keyframe(cam, kps2, d2, nullptr, n2, scale_factors, nullptr, nlevels);
+  set_kf_pose(*kf1, T1w);
+  set_kf_pose(*kf2, T2w);
+  // the descriptor a map point reports is that of its own feature
+  CloudArgs c1{n1, pos1, nullptr, d1, flags1, nullptr, dist_inv1, lvl1}, c2{n2, pos2, nullptr, d2, flags2, nullptr, dist_inv2, lvl2};
+  PointCloud pc1, pc2;
+  for (int i = 0; i < n1; ++i) if (has1[i]) kf1->mvpMapPoints[i] = add_cloud_point(pc1, c1, i);
+  for (int i = 0; i < n2; ++i) if (has2[i]) {
+    kf2->mvpMapPoints[i] = add_cloud_point(pc2, c2, i);
+    kf2->mvpMapPoints[i]->mObservations[kf2.get()] = (size_t)i;
+  }
+  std::vector<MapPoint*> m12((size_t)n1, nullptr);
+  for (int i = 0; i < n1; ++i) if (pre12[i] >= 0 && kf2->mvpMapPoints[pre12[i]]) m12[i] = kf2->mvpMapPoints[pre12[i]];
+  clear_windows(win12, n1);
+  clear_windows(win21, n2);
+  reset_log();
+  ORBmatcher matcher(0.75f, true);
+  const int nf = matcher.SearchBySim3(kf1.get(), kf2.get(), m12, s12, float_mat(R12, 3, 3), float_mat(t12, 3, 1), th);
+  windows_from_log(pc1.index, win12);
+  windows_from_log(pc2.index, win21);
+  for (int i = 0; i < n1; ++i) if (win12[i].valid) { win12[i].min_level = lvl1[i] - 1; win12[i].max_level = lvl1[i]; }
+  for (int i = 0; i < n2; ++i) if (win21[i].valid) { win21[i].min_level = lvl2[i] - 1; win21[i].max_level = lvl2[i]; }
+  for (int i = 0; i < n1; ++i) match12[i] = index_of(pc2.index, m12[i]);
+  return nf;
+}
+
+// src/ORBmatcher.cc:977-1100, Fuse(pKF, Scw, vpPoints, th, vpReplacePoint).  kf_obs[i] >= 0: feature i holds a map
+// point.  Cloud flag bit 1: the point is the one key-frame feature (i mod n_kf) already holds (spAlreadyFound).
+// match_of_query[n] = fused key-frame feature or -1; replace[n] = feature whose point went into vpReplacePoint.
+int refm_fuse_sim3(const float* cam12, const float* Scw, const orbo::KeyPoint* kps_kf, const uint8_t* d_kf, int n_kf,
+                   const float* scale_factors, int nlevels, const int32_t* kf_obs, int n, const float* world_pos,
+                   const float* normal, const uint8_t* desc, const uint8_t* flags, const float* dist_inv,
+                   const int32_t* pred_level, float th, int32_t* match_of_query, int32_t* replace,
+                   orbo::WindowQuery* windows) {
+  Camera cam;
+  std::memcpy(&cam, cam12, sizeof(cam));
+  auto kf = make_keyframe(cam, kps_kf, d_kf, nullptr, n_kf, scale_factors, nullptr, nlevels);
+  PointCloud in_kf;
+  for (int i = 0; i < n_kf; ++i)
+    if (kf_obs[i] >= 0) kf->mvpMapPoints[i] = in_kf.add(i, nullptr, nullptr, nullptr, kf_obs[i]);
+  CloudArgs c{n, world_pos, normal, desc, flags, nullptr, dist_inv, pred_level};
+  PointCloud pc;
+  std::vector<MapPoint*> points, repl((size_t)n, nullptr);
+  for (int i = 0; i < n; ++i) {
+    points.push_back(add_cloud_point(pc, c, i));
+    if ((flags[i] & 2) && n_kf) kf->mvpMapPoints[i % n_kf] = points.back();  // the key frame already sees this point
+  }
+  clear_windows(windows, n);
+  reset_log();
+  ORBmatcher matcher(0.8f, true);
+  const int nf = matcher.Fuse(kf.get(), pose44(Scw), points, th, repl);
+  windows_from_log(pc.index, windows);
+  for (int i = 0; i < n; ++i) {
+    match_of_query[i] = -1;
+    replace[i] = repl[i] ? index_of(in_kf.index, repl[i]) : -1;
+    if (repl[i] && replace[i] < 0) replace[i] = -2 - index_of(pc.index, repl[i]);  // a cloud point sitting in the key frame
+    if (windows[i].valid) { windows[i].min_level = pred_level[i] - 1; windows[i].max_level = pred_level[i]; }
+  }
+  for (const auto& r : ShimLog::get().map_point_reads) {
+    const int i = index_of(pc.index, r.first);
+    if (i >= 0) match_of_query[i] = (int32_t)r.second;
+  }
+  return nf;
 }
 
 }  // extern "C"

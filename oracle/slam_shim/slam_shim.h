@@ -38,6 +38,7 @@ struct AreaCall {
 };
 struct ShimLog {
   std::vector<AreaCall> calls;
+  std::vector<std::pair<const MapPoint*, size_t>> map_point_reads;  // KeyFrame::GetMapPoint(idx) by the point in hand
   const MapPoint* last_mp = nullptr;
   static ShimLog& get() { static thread_local ShimLog l; return l; }
 };
@@ -68,8 +69,8 @@ class MapPoint {
   cv::Mat GetDescriptor() { touch(); return mDescriptor.clone(); }
   bool isBad() { touch(); return mbBad; }
   int Observations() { return nObs; }
-  float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }   // src/MapPoint.cc:373-377
-  float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }   // src/MapPoint.cc:379-383
+  float GetMinDistanceInvariance() { return min_dist_inv; }   // 0.8f * mfMinDistance, src/MapPoint.cc:373-377
+  float GetMaxDistanceInvariance() { return max_dist_inv; }   // 1.2f * mfMaxDistance, src/MapPoint.cc:379-383
   int PredictScale(const float&, KeyFrame*) { return predicted_level; }
   int PredictScale(const float&, Frame*) { return predicted_level; }
   bool IsInKeyFrame(KeyFrame* pKF) { return mObservations.count(pKF) != 0; }
@@ -86,7 +87,7 @@ class MapPoint {
   cv::Mat mWorldPos, mNormalVector, mDescriptor;
   bool mbBad = false;
   int nObs = 1, predicted_level = 0;
-  float mfMinDistance = 0, mfMaxDistance = 1e9f;
+  float min_dist_inv = 0, max_dist_inv = 1e9f;
   std::map<KeyFrame*, size_t> mObservations;
   std::vector<std::pair<KeyFrame*, size_t>> added;
   MapPoint* replaced_by = nullptr;
@@ -132,8 +133,15 @@ class KeyFrame {
     for (MapPoint* p : mvpMapPoints) if (p && !p->isBad()) s.insert(p);
     return s;
   }
-  MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
-  void AddMapPoint(MapPoint* pMP, const size_t& idx) { added.push_back(std::make_pair(pMP, idx)); }
+  MapPoint* GetMapPoint(const size_t& idx) {
+    ShimLog& l = ShimLog::get();
+    l.map_point_reads.push_back(std::make_pair(l.last_mp, idx));
+    return mvpMapPoints[idx];
+  }
+  void AddMapPoint(MapPoint* pMP, const size_t& idx) {              // src/KeyFrame.cc:201-205
+    added.push_back(std::make_pair(pMP, idx));
+    mvpMapPoints[idx] = pMP;
+  }
   std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r) const {
     return grid.area(this, x, y, r, -1, -1);
   }

@@ -93,3 +93,295 @@ def test_search_for_initialization_equals_reference(ref, check_ori, window, seed
         assert n_r > 100 and n_o == n_r and np.array_equal(m_o, m_r)
         hit = m_r >= 0
         assert np.array_equal(prev[hit, 0], k2["x"][m_r[hit]]) and np.array_equal(prev[hit, 1], k2["y"][m_r[hit]])
+
+
+# ---- projection searches: the reference projects 3-D points itself; its windows are recorded and replayed ----
+CAM = dict(fx=520.0, fy=516.0, cx=318.6, cy=255.3, W=640, H=480)
+
+
+def _cam_tuple(mbf, mb):
+    c = CAM
+    return (c["fx"], c["fy"], c["cx"], c["cy"], mbf, mb, 0.0, 0.0, float(c["W"]), float(c["H"]),
+            np.float32(64) / np.float32(c["W"]), np.float32(48) / np.float32(c["H"]))
+
+
+def _pose(rng, angle_deg, t):
+    """row-major 3x4 [R | t], rotation by angle_deg about a random axis"""
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax)
+    a = np.deg2rad(angle_deg)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * K @ K
+    return np.concatenate([R, np.asarray(t, float).reshape(3, 1)], 1).astype(np.float32)
+
+
+def _scene(oracle, seed, M=1800, spread=3.0):
+    """Current frame = an extracted synthetic frame; M world points that project (through Tcw) near keypoints of it."""
+    ex = oracle.Extractor(2000, 1.2, 8, 20, 7)
+    kps, desc = ex(synth.make_frame(CAM["W"], CAM["H"], seed))
+    rng = np.random.default_rng(500 + seed)
+    Tcw = _pose(rng, 4.0, rng.normal(0, 0.2, 3))
+    nk = len(kps)
+    src = rng.integers(0, nk, M)
+    near = rng.random(M) < 0.85
+    u = np.where(near, kps["x"][src] + rng.normal(0, spread, M), rng.uniform(-40, CAM["W"] + 40, M))
+    v = np.where(near, kps["y"][src] + rng.normal(0, spread, M), rng.uniform(-40, CAM["H"] + 40, M))
+    z = rng.uniform(2.0, 12.0, M) * np.where(rng.random(M) < 0.03, -1, 1)       # a few points behind the camera
+    Xc = np.stack([(u - CAM["cx"]) / CAM["fx"] * z, (v - CAM["cy"]) / CAM["fy"] * z, z], 1)
+    R, t = Tcw[:, :3].astype(float), Tcw[:, 3].astype(float)
+    Xw = ((Xc - t) @ R).astype(np.float32)                                        # R^T (Xc - t)
+    return ex, rng, kps, desc, Tcw, src, Xw
+
+
+@pytest.mark.parametrize("mode,th,check_ori,seed", [
+    ("mono", 15.0, True, 1), ("mono", 7.0, False, 2), ("forward", 7.0, True, 3), ("backward", 15.0, True, 4),
+    ("neutral_stereo", 7.0, True, 5)])
+def test_search_last_frame_equals_reference(ref, mode, th, check_ori, seed):
+    ex, rng, kps, desc, Tcw, src, Xw = _scene(ref, seed)
+    nk, M = len(kps), len(src)
+    sf = ex.tables()["scale"].astype(np.float32)
+    mb = 0.1
+    # last pose: the current camera moved along its optical axis by dz since the last frame (tlc.z = -dz ... see :1346)
+    dz = {"mono": 0.0, "forward": -0.5, "backward": 0.5, "neutral_stereo": 0.02}[mode]
+    Tlw = Tcw.copy()
+    Tlw[2, 3] -= np.float32(dz)
+    stereo = mode != "mono"
+    ur_cur = np.where(rng.random(nk) < 0.6, kps["x"] - rng.uniform(1, 40, nk), -1).astype(np.float32) if stereo else None
+    kps_last = np.zeros(M, ref.KP_DTYPE)
+    kps_last["octave"] = np.clip(kps["octave"][src] + rng.integers(-1, 2, M), 0, 7)
+    rot = np.where(rng.random(M) < 0.85, rng.normal(40, 6, M), rng.uniform(0, 360, M))
+    kps_last["angle"] = np.mod(kps["angle"][src] + rot, 360).astype(np.float32)
+    has_mp = rng.random(M) < 0.9
+    outlier = rng.random(M) < 0.05
+    mp_obs = (rng.random(M) < 0.9).astype(np.int32)
+    mp_desc = synth.flip_bits(desc[src], rng.integers(0, 70, M), rng)
+    dup = rng.integers(0, M, 300)           # several points aimed at one keypoint: the claim order matters
+    Xw[dup] = Xw[(dup + 1) % M]; mp_desc[dup] = mp_desc[(dup + 1) % M]; kps_last[dup] = kps_last[(dup + 1) % M]
+    blocked = (rng.random(nk) < 0.05).astype(np.uint8)
+    cam = _cam_tuple(mbf=40.0, mb=mb)
+    n_r, m_r, win = ref.ref_search_last_frame(cam, Tcw, Tlw, kps, desc, ur_cur, sf, blocked, kps_last, has_mp, outlier,
+                                              Xw, mp_desc, mp_obs, th, mode == "mono", check_ori)
+    # the reference chose the level window this test expects (:1385-1390)
+    val = win["valid"] == 1
+    assert val.sum() > 1200 and not val[~has_mp].any() and not val[outlier].any()
+    lo, hi, oc = win["min_level"][val], win["max_level"][val], kps_last["octave"][val]
+    if mode == "forward":
+        assert np.array_equal(lo, oc) and (hi == -1).all()
+    elif mode == "backward":
+        assert (lo == 0).all() and np.array_equal(hi, oc)
+    else:
+        assert np.array_equal(lo, oc - 1) and np.array_equal(hi, oc + 1)
+    grid = (0.0, 0.0, cam[10], cam[11])
+    n_o, m_o, _, _ = ref.search_windowed(win, mp_desc, kps, desc, ur_cur, grid, 100, 1 if stereo else 0, check_ori,
+                                         blocked.copy())
+    assert n_r > 100
+    assert n_o == n_r and np.array_equal(np.maximum(m_o, -1), m_r)
+
+
+def _cloud_extras(rng, kps, src, Xw, Tcw):
+    """Per-point quantities the callers' gates read: distance invariance interval, predicted level, normal."""
+    M = len(src)
+    R, t = Tcw[:, :3].astype(float), Tcw[:, 3].astype(float)
+    Ow = -R.T @ t
+    PO = Xw.astype(float) - Ow
+    dist = np.linalg.norm(PO, axis=1)
+    dist_inv = np.stack([dist * rng.uniform(0.3, 1.05, M), dist * rng.uniform(0.95, 3.0, M)], 1).astype(np.float32)
+    pred = np.clip(kps["octave"][src] + rng.integers(0, 2, M), 0, 7).astype(np.int32)
+    normal = PO / dist[:, None]
+    tilt = rng.random(M) < 0.1                                # some seen from behind / too obliquely (:354)
+    normal[tilt] = -normal[tilt]
+    return dist_inv, pred, normal.astype(np.float32)
+
+
+@pytest.mark.parametrize("th,orb_dist,check_ori,seed", [(10.0, 100, True, 11), (3.0, 64, True, 12), (10.0, 100, False, 13)])
+def test_search_keyframe_points_equals_reference(ref, th, orb_dist, check_ori, seed):
+    """Relocalisation: SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1472-1599)."""
+    ex, rng, kps, desc, Tcw, src, Xw = _scene(ref, seed)
+    nk, M = len(kps), len(src)
+    sf = ex.tables()["scale"].astype(np.float32)
+    dist_inv, pred, _ = _cloud_extras(rng, kps, src, Xw, Tcw)
+    kps_kf = np.zeros(M, ref.KP_DTYPE)
+    rot = np.where(rng.random(M) < 0.85, rng.normal(-30, 6, M), rng.uniform(0, 360, M))
+    kps_kf["angle"] = np.mod(kps["angle"][src] + rot, 360).astype(np.float32)
+    has_mp = rng.random(M) < 0.9
+    flags = ((rng.random(M) < 0.05) * 1 + (rng.random(M) < 0.1) * 2).astype(np.uint8)
+    mp_desc = synth.flip_bits(desc[src], rng.integers(0, 70, M), rng)
+    dup = rng.integers(0, M, 300)
+    Xw[dup] = Xw[(dup + 1) % M]; mp_desc[dup] = mp_desc[(dup + 1) % M]; kps_kf[dup] = kps_kf[(dup + 1) % M]
+    pred[dup] = pred[(dup + 1) % M]; dist_inv[dup] = dist_inv[(dup + 1) % M]
+    cur_has = (rng.random(nk) < 0.2).astype(np.uint8)
+    cam = _cam_tuple(0.0, 0.0)
+    n_r, m_r, win = ref.ref_search_keyframe_points(cam, Tcw, kps, desc, sf, cur_has, kps_kf, has_mp, Xw, mp_desc, flags,
+                                                   dist_inv, pred, th, orb_dist, check_ori)
+    val = win["valid"] == 1
+    assert 600 < val.sum() < M and not val[~has_mp].any() and not val[flags != 0].any()
+    assert np.array_equal(win["min_level"][val], pred[val] - 1) and np.array_equal(win["max_level"][val], pred[val] + 1)
+    grid = (0.0, 0.0, cam[10], cam[11])
+    n_o, m_o, _, _ = ref.search_windowed(win, mp_desc, kps, desc, None, grid, orb_dist, 0, check_ori, cur_has.copy())
+    assert n_r > 100 and n_o == n_r and np.array_equal(np.maximum(m_o, -1), m_r)
+
+
+@pytest.mark.parametrize("th,scale,seed", [(10, 1.0, 21), (4, 1.7, 22)])
+def test_search_sim3_projection_equals_reference(ref, th, scale, seed):
+    """Loop closing: SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) (:290-403)."""
+    ex, rng, kps, desc, Tcw, src, Xw = _scene(ref, seed)
+    nk, M = len(kps), len(src)
+    sf = ex.tables()["scale"].astype(np.float32)
+    dist_inv, pred, normal = _cloud_extras(rng, kps, src, Xw, Tcw)
+    Scw = (Tcw.astype(np.float64) * scale).astype(np.float32)          # s * [R | t]
+    flags = ((rng.random(M) < 0.05) * 1 + (rng.random(M) < 0.05) * 2).astype(np.uint8)
+    mp_desc = synth.flip_bits(desc[src], rng.integers(0, 45, M), rng)
+    dup = rng.integers(0, M, 300)
+    Xw[dup] = Xw[(dup + 1) % M]; mp_desc[dup] = mp_desc[(dup + 1) % M]; normal[dup] = normal[(dup + 1) % M]
+    pred[dup] = pred[(dup + 1) % M]; dist_inv[dup] = dist_inv[(dup + 1) % M]
+    kf_matched = (rng.random(nk) < 0.15).astype(np.uint8)
+    cam = _cam_tuple(0.0, 0.0)
+    n_r, m_r, win = ref.ref_search_sim3_projection(cam, Scw, kps, desc, sf, kf_matched, Xw, normal, mp_desc, flags,
+                                                   dist_inv, pred, th)
+    val = win["valid"] == 1
+    assert 500 < val.sum() < M and not val[flags != 0].any()
+    grid = (0.0, 0.0, cam[10], cam[11])
+    n_o, m_o, _, _ = ref.search_windowed(win, mp_desc, kps, desc, None, grid, 50, 0, False, kf_matched.copy())
+    assert n_r > 100 and n_o == n_r and np.array_equal(m_o, m_r)
+
+
+@pytest.mark.parametrize("stereo,th,seed", [(False, 3.0, 31), (True, 3.0, 32), (True, 8.0, 33)])
+def test_fuse_equals_reference(ref, stereo, th, seed):
+    """Local mapping: Fuse(pKF, vpMapPoints, th) (:825-975) -- chi-square gate, no claims, map edits by rule."""
+    ex, rng, kps, desc, Tcw, src, Xw = _scene(ref, seed, spread=1.2)
+    nk, M = len(kps), len(src)
+    sf = ex.tables()["scale"].astype(np.float32)
+    sigma2 = (sf * sf).astype(np.float32)
+    dist_inv, pred, normal = _cloud_extras(rng, kps, src, Xw, Tcw)
+    pred = np.clip(kps["octave"][src] + rng.integers(0, 2, M), 0, 7).astype(np.int32)
+    flags = ((rng.random(M) < 0.05) * 1 + (rng.random(M) < 0.1) * 2).astype(np.uint8)
+    obs = rng.integers(0, 6, M).astype(np.int32)
+    mp_desc = synth.flip_bits(desc[src], rng.integers(0, 45, M), rng)
+    kf_obs = np.where(rng.random(nk) < 0.5, rng.integers(0, 6, nk), -1).astype(np.int32)
+    mbf = 40.0
+    ur_kf = None
+    if stereo:   # right coordinate consistent with some depth for most, so the 3-term error passes sometimes
+        R, t = Tcw[:, :3].astype(float), Tcw[:, 3].astype(float)
+        zc = (Xw.astype(float) @ R.T + t)[:, 2]
+        ur_kf = np.full(nk, -1, np.float32)
+        ur_kf[src] = (kps["x"][src] - mbf / zc + rng.normal(0, 0.7, M)).astype(np.float32)
+        ur_kf[rng.random(nk) < 0.3] = -1
+    cam = _cam_tuple(mbf, 0.08)
+    n_r, mq_r, act, win = ref.ref_fuse(cam, Tcw, kps, desc, ur_kf, sf, sigma2, kf_obs, Xw, normal, mp_desc, flags, obs,
+                                       dist_inv, pred, th)
+    val = win["valid"] == 1
+    assert 500 < val.sum() < M and not val[flags != 0].any()
+    win["blocks"] = 0
+    grid = (0.0, 0.0, cam[10], cam[11])
+    inv_sigma2 = (np.float32(1.0) / sigma2).astype(np.float32)
+    n_o, _, _, mq_o = ref.search_windowed(win, mp_desc, kps, desc, ur_kf, grid, 50, 2, False, np.zeros(nk, np.uint8),
+                                          inv_sigma2)
+    assert n_r > 100 and n_o == n_r and np.array_equal(mq_o, mq_r)
+    # the gate bites, and the map edits follow :955-970 where a key-frame feature is the target of one point only
+    _, _, _, mq_nogate = ref.search_windowed(win, mp_desc, kps, desc, ur_kf, grid, 50, 0, False, np.zeros(nk, np.uint8))
+    assert (mq_nogate >= 0).sum() > (mq_o >= 0).sum()
+    hit = np.flatnonzero(mq_r >= 0)
+    tgt, cnt = np.unique(mq_r[hit], return_counts=True)
+    single = set(tgt[cnt == 1].tolist())
+    for i in hit:
+        k = int(mq_r[i])
+        if k in single:
+            want = 1 if kf_obs[k] < 0 else (2 if kf_obs[k] > obs[i] else 3)
+            assert act[i] == want
+    assert (act[mq_r < 0] == 0).all()
+
+
+@pytest.mark.parametrize("s12,th,seed", [(1.0, 7.5, 41), (1.03, 7.5, 42)])
+def test_search_by_sim3_equals_reference(ref, s12, th, seed):
+    """Loop closing: SearchBySim3 (:1102-1326) = two claim-free passes + mutual agreement."""
+    ex = ref.Extractor(1500, 1.2, 8, 20, 7)
+    kps2, d2 = ex(synth.make_frame(CAM["W"], CAM["H"], 60 + seed))
+    rng = np.random.default_rng(seed)
+    sf = ex.tables()["scale"].astype(np.float32)
+    n2 = len(kps2)
+    n1 = n2
+    perm = rng.permutation(n2)
+    T2w = _pose(rng, 5.0, rng.normal(0, 0.2, 3))
+    T1w = _pose(rng, 3.0, rng.normal(0, 0.2, 3))
+    z = rng.uniform(3.0, 12.0, n1)
+    k2 = kps2[perm]
+    Xc2 = np.stack([(k2["x"] - CAM["cx"]) / CAM["fx"] * z, (k2["y"] - CAM["cy"]) / CAM["fy"] * z, z], 1)
+    R2, t2 = T2w[:, :3].astype(float), T2w[:, 3].astype(float)
+    R1, t1 = T1w[:, :3].astype(float), T1w[:, 3].astype(float)
+    Xw = (Xc2 - t2) @ R2
+    Xc1 = Xw @ R1.T + t1
+    kps1 = np.zeros(n1, ref.KP_DTYPE)
+    kps1["x"] = (CAM["fx"] * Xc1[:, 0] / Xc1[:, 2] + CAM["cx"] + rng.normal(0, 1.5, n1)).astype(np.float32)
+    kps1["y"] = (CAM["fy"] * Xc1[:, 1] / Xc1[:, 2] + CAM["cy"] + rng.normal(0, 1.5, n1)).astype(np.float32)
+    kps1["octave"] = k2["octave"]
+    kps1["angle"] = k2["angle"]
+    d1 = synth.flip_bits(d2[perm], rng.integers(0, 60, n1), rng)
+    R12 = R1 @ R2.T
+    t12 = t1 - R12 @ t2
+    pos1 = Xw.astype(np.float32)
+    pos2 = np.empty((n2, 3), np.float32)
+    pos2[perm] = (Xw + rng.normal(0, 0.01, Xw.shape)).astype(np.float32)
+
+    def extras(n, pos, T, octave):
+        R, t = T[:, :3].astype(float), T[:, 3].astype(float)
+        dist = np.linalg.norm(pos.astype(float) @ R.T + t, axis=1)
+        di = np.stack([dist * rng.uniform(0.3, 1.03, n), dist * rng.uniform(0.97, 3.0, n)], 1).astype(np.float32)
+        return di, np.clip(octave + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    di1, lv1 = extras(n1, pos1, T2w, kps1["octave"])      # points of key frame 1 are predicted in key frame 2
+    di2, lv2 = extras(n2, pos2, T1w, kps2["octave"])
+    kf1 = dict(kps=kps1, desc=d1, has_mp=rng.random(n1) < 0.9, pos=pos1, flags=(rng.random(n1) < 0.05).astype(np.uint8),
+               dist_inv=di1, pred_level=lv1)
+    kf2 = dict(kps=kps2, desc=d2, has_mp=rng.random(n2) < 0.9, pos=pos2, flags=(rng.random(n2) < 0.05).astype(np.uint8),
+               dist_inv=di2, pred_level=lv2)
+    pre12 = np.where(rng.random(n1) < 0.1, perm, -1).astype(np.int32)
+    pre12[(pre12 >= 0) & ~kf2["has_mp"][np.maximum(pre12, 0)]] = -1
+    cam = _cam_tuple(0.0, 0.0)
+    n_r, m12_r, w12, w21 = ref.ref_search_by_sim3(cam, T1w, T2w, s12, R12, t12, sf, kf1, kf2, pre12, th)
+    assert (w12["valid"] == 1).sum() > 500 and (w21["valid"] == 1).sum() > 500
+    assert not (w12["valid"][pre12 >= 0]).any() and not (w21["valid"][pre12[pre12 >= 0]]).any()
+    grid = (0.0, 0.0, cam[10], cam[11])
+    _, _, _, mq1 = ref.search_windowed(w12, d1, kps2, d2, None, grid, 100, 0, False, np.zeros(n2, np.uint8))
+    _, _, _, mq2 = ref.search_windowed(w21, d2, kps1, d1, None, grid, 100, 0, False, np.zeros(n1, np.uint8))
+    want = pre12.copy()
+    found = 0
+    for i1 in range(n1):                                   # the agreement check of :1308-1323
+        j = mq1[i1]
+        if j >= 0 and mq2[j] == i1:
+            want[i1] = j
+            found += 1
+    assert n_r > 100 and found == n_r and np.array_equal(want, m12_r)
+
+
+@pytest.mark.parametrize("th,scale,seed", [(4.0, 1.0, 51), (4.0, 0.8, 52)])
+def test_fuse_sim3_equals_reference(ref, th, scale, seed):
+    """Loop closing: Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:977-1100): no chi-square gate, no claims."""
+    ex, rng, kps, desc, Tcw, src, Xw = _scene(ref, seed)
+    nk, M = len(kps), len(src)
+    sf = ex.tables()["scale"].astype(np.float32)
+    dist_inv, pred, normal = _cloud_extras(rng, kps, src, Xw, Tcw)
+    Scw = (Tcw.astype(np.float64) * scale).astype(np.float32)
+    flags = ((rng.random(M) < 0.05) * 1 + (rng.random(M) < 0.05) * 2).astype(np.uint8)
+    mp_desc = synth.flip_bits(desc[src], rng.integers(0, 45, M), rng)
+    kf_obs = np.where(rng.random(nk) < 0.5, rng.integers(1, 6, nk), -1).astype(np.int32)
+    cam = _cam_tuple(0.0, 0.0)
+    n_r, mq_r, rp, win = ref.ref_fuse_sim3(cam, Scw, kps, desc, sf, kf_obs, Xw, normal, mp_desc, flags, dist_inv, pred, th)
+    val = win["valid"] == 1
+    assert 500 < val.sum() < M and not val[flags != 0].any()
+    win["blocks"] = 0
+    grid = (0.0, 0.0, cam[10], cam[11])
+    n_o, _, _, mq_o = ref.search_windowed(win, mp_desc, kps, desc, None, grid, 50, 0, False, np.zeros(nk, np.uint8))
+    assert n_r > 100 and n_o == n_r and np.array_equal(mq_o, mq_r)
+    # vpReplacePoint names the point the fused feature held before the call: the key frame's own (its feature
+    # index) or, where the wrapper seated an "already found" cloud point i there, -2 - i
+    seat = {}
+    for i in np.flatnonzero(flags & 2):
+        seat[int(i) % nk] = int(i)
+    for i in np.flatnonzero(mq_r >= 0):
+        k = int(mq_r[i])
+        want = -2 - seat[k] if k in seat else (k if kf_obs[k] >= 0 else -1)
+        if k in seat and flags[seat[k]] & 1:
+            want = -1                        # a bad point in the key frame is not reported (:1083-1084)
+        if want == -1 and rp[i] != -1 and k not in seat:      # an earlier point of this call was added to feature k (:1089-1090)
+            assert rp[i] <= -2 and mq_r[-2 - rp[i]] == k and -2 - rp[i] < i
+        else:
+            assert rp[i] == want
+    assert (rp[mq_r < 0] == -1).all()
