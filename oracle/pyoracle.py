@@ -622,3 +622,49 @@ def ref_fuse_sim3(cam, Scw, kps_kf, d_kf, scale_factors, kf_obs, world_pos, norm
     n = ref_matcher().refm_fuse_sim3(_p(cam), _p(S), _p(kk), _p(dk), len(kk), _p(sf), len(sf), _p(ko), len(ds), _p(wp),
                                      _p(nm), _p(ds), _p(fl), _p(di), _p(pl), C.c_float(th), _p(mq), _p(rp), _p(win))
     return n, mq, rp, win
+
+
+# ------------------------------------------------------------------------------------------------
+# The reference's own Frame.cc, compiled verbatim over oracle/slam_shim/frame_shim.h (oracle/_ref/libref_frame.so).
+# ------------------------------------------------------------------------------------------------
+REF_FRAME_PATH = os.path.join(HERE, "_ref", "libref_frame.so")
+_reff = None
+
+
+def have_ref_frame():
+    return os.path.exists(REF_FRAME_PATH)
+
+
+def ref_frame():
+    global _reff
+    if _reff is None:
+        if not have_ref_frame():
+            raise RuntimeError("oracle/_ref/libref_frame.so is not built (needs /root/reference)")
+        _reff = C.CDLL(REF_FRAME_PATH)
+    return _reff
+
+
+def ref_compute_stereo_matches(kl, dl, kr, dr, levels_l, levels_r, scale_factors, inv_scale_factors, mb, mbf):
+    """The reference's Frame::ComputeStereoMatches (src/Frame.cc:466-640), verbatim -> mvuRight[nl], mvDepth[nl], rc
+    (rc = -1: a correlation window left its level image, where OpenCV asserts)."""
+    kl = np.ascontiguousarray(kl, KP_DTYPE); kr = np.ascontiguousarray(kr, KP_DTYPE)
+    dl = u8c(dl); dr = u8c(dr)
+    ll = [u8c(a) for a in levels_l]; lr = [u8c(a) for a in levels_r]
+    n = len(ll)
+    pl = (C.c_void_p * n)(*[a.ctypes.data for a in ll]); pr = (C.c_void_p * n)(*[a.ctypes.data for a in lr])
+    sl = np.array([[a.shape[1], a.shape[0]] for a in ll], np.int32); sr = np.array([[a.shape[1], a.shape[0]] for a in lr], np.int32)
+    sf = _f32(scale_factors); isf = _f32(inv_scale_factors)
+    ur = np.empty(len(kl), np.float32); dp = np.empty(len(kl), np.float32)
+    rc = ref_frame().reff_compute_stereo_matches(_p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), pl, pr, _p(sl), _p(sr), n,
+                                                 _p(sf), _p(isf), C.c_float(mb), C.c_float(mbf), _p(ur), _p(dp))
+    return ur, dp, rc
+
+
+def ref_features_in_area(kps, grid, x, y, r, min_level, max_level):
+    """The reference's Frame::AssignFeaturesToGrid + GetFeaturesInArea (src/Frame.cc:230-245, :327-392), verbatim."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    out = np.empty(len(kps) + 1, np.int32)
+    n = ref_frame().reff_features_in_area(_p(kps), len(kps), C.c_float(grid[0]), C.c_float(grid[1]), C.c_float(grid[2]),
+                                          C.c_float(grid[3]), C.c_float(x), C.c_float(y), C.c_float(r), min_level,
+                                          max_level, _p(out), len(out))
+    return out[:n].copy()

@@ -12,6 +12,7 @@
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <stdexcept>
 #include <vector>
 
 typedef unsigned char uchar;
@@ -58,8 +59,29 @@ class Mat {
     for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols * esz());
     return m;
   }
-  Mat rowRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * step; m.rows = b - a; return m; }
-  Mat colRange(int a, int b) const { Mat m(*this); m.data = data + (size_t)a * esz(); m.cols = b - a; return m; }
+  // OpenCV asserts on ranges that leave the matrix; here they throw, so a caller can report the case
+  Mat rowRange(int a, int b) const {
+    if (a < 0 || b > rows || a > b) throw std::out_of_range("Mat::rowRange");
+    Mat m(*this); m.data = data + (size_t)a * step; m.rows = b - a; return m;
+  }
+  Mat colRange(int a, int b) const {
+    if (a < 0 || b > cols || a > b) throw std::out_of_range("Mat::colRange");
+    Mat m(*this); m.data = data + (size_t)a * esz(); m.cols = b - a; return m;
+  }
+  static Mat ones(int r, int c, int type) {
+    Mat m(r, c, type);
+    for (int y = 0; y < r; ++y) for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.0f;
+    return m;
+  }
+  void convertTo(Mat& dst, int type) const {  // CV_8U -> CV_32F (may be in place)
+    assert(type == CV_32F);
+    Mat m(rows, cols, CV_32F);
+    for (int y = 0; y < rows; ++y)
+      for (int x = 0; x < cols; ++x) m.at<float>(y, x) = type_ == CV_32F ? at<float>(y, x) : (float)at<uchar>(y, x);
+    dst = m;
+  }
+  void copyTo(Mat& dst) const { dst = clone(); }
+  Mat reshape(int /*cn*/) const { return *this; }  // channel views are only passed to undistortPoints (a no-op here)
   Mat row(int y) const { return rowRange(y, y + 1); }
   Mat col(int x) const { return colRange(x, x + 1); }
   template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + (size_t)x * sizeof(T)); }
@@ -118,5 +140,27 @@ inline Mat operator*(double s, const Mat& a) { return mat_map1(a, [s](float p) {
 inline Mat operator*(const Mat& a, double s) { return s * a; }
 inline Mat operator/(const Mat& a, double s) { return mat_map1(a, [s](float p) { return (float)(p / s); }); }
 inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+enum { NORM_L1 = 2 };
+inline double norm(const Mat& a, const Mat& b, int type) {  // CV_32F: float differences, double accumulation
+  assert(type == NORM_L1 && a.rows == b.rows && a.cols == b.cols);
+  double s = 0;
+  for (int y = 0; y < a.rows; ++y) for (int x = 0; x < a.cols; ++x) s += std::fabs(a.at<float>(y, x) - b.at<float>(y, x));
+  return s;
+}
+template <typename T>
+class Mat_ : public Mat {  // only the `(Mat_<float>(3,1) << x, y, z)` initialiser of src/Frame.cc:675
+ public:
+  Mat_(int r, int c) : Mat(r, c, CV_32F) {}
+  struct Init {
+    Mat_* m; int i;
+    Init& operator,(T v) { m->template at<T>(i / m->cols, i % m->cols) = v; ++i; return *this; }
+    operator Mat() const { return *m; }
+  };
+  Init operator<<(T v) { Init in{this, 0}; in, v; return in; }
+};
+// distortion-free cameras only (the callers test mDistCoef.at<float>(0) == 0 first and never get here)
+inline void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) {
+  throw std::logic_error("cv::undistortPoints is not part of the shim");
+}
 
 }  // namespace cv

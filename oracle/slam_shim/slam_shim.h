@@ -10,7 +10,9 @@
 // RECORDED (target, map point last touched, x, y, r, levels): those are the windows the reference derived, and
 // the tests hand them to the restated oracle / the GPU entry points as inputs.
 #pragma once
+#ifndef SLAM_SHIM_REAL_FRAME   // frame_shim.h keeps the reference's own Frame.h
 #define FRAME_H
+#endif
 #define KEYFRAME_H
 #define MAPPOINT_H
 
@@ -96,6 +98,7 @@ class MapPoint {
   void touch() const { ShimLog::get().last_mp = this; }
 };
 
+#ifndef SLAM_SHIM_REAL_FRAME
 class Frame {
  public:
   std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1,
@@ -117,6 +120,8 @@ class Frame {
   std::vector<float> mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
   ShimGrid grid;
 };
+
+#endif  // SLAM_SHIM_REAL_FRAME
 
 class KeyFrame {
  public:

@@ -78,3 +78,28 @@ def test_last_frame_projection_gpu_equals_reference(gpu, ref, mode, seed):
     n_g, m_g, _ = gpu.ORBmatcher(0.9, checkOri=True).SearchWindowed(frame, _to_gpu_queries(gpu, win), mp_desc, 100,
                                                                     1 if stereo else 0)
     assert n_r > 100 and n_g == n_r and np.array_equal(np.maximum(m_g, -1), m_r)
+
+
+def test_compute_stereo_matches_gpu_equals_reference(gpu, oracle):
+    """Whole Frame::ComputeStereoMatches on the device against the reference's own src/Frame.cc (verbatim build)."""
+    if not oracle.have_ref_frame():
+        pytest.skip("oracle/_ref/libref_frame.so not built")
+    BF, FX = np.float32(386.1448), np.float32(718.856)
+    W, H, nfeat = 1241, 376, 2000
+    left, right = synth.make_stereo_pair_subpixel(W, H, 57)
+    exl = gpu.ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=1)
+    exr = gpu.ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=1)
+    kl, dl = exl(left)
+    kr, dr = exr(right)
+    b = np.float32(BF / FX)
+    ur, dp = gpu.ORBmatcher().ComputeStereoMatches(exl, exr, kl, dl, kr, dr, BF, b)
+    oxl = oracle.Extractor(nfeat, 1.2, 8, 20, 7)
+    oxr = oracle.Extractor(nfeat, 1.2, 8, 20, 7)
+    oxl(left); oxr(right)
+    t = oxl.tables()
+    lv_l = [oxl.level_image(l) for l in range(8)]
+    lv_r = [oxr.level_image(l) for l in range(8)]
+    ur_r, dp_r, rc = oracle.ref_compute_stereo_matches(kl, dl, kr, dr, lv_l, lv_r, t["scale"], t["inv_scale"], b, BF)
+    assert rc == 0 and (ur_r >= 0).sum() > 0.2 * len(kl)
+    assert np.array_equal(ur.view(np.uint32), ur_r.view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), dp_r.view(np.uint32))
