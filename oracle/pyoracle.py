@@ -668,3 +668,99 @@ def ref_features_in_area(kps, grid, x, y, r, min_level, max_level):
                                           C.c_float(grid[3]), C.c_float(x), C.c_float(y), C.c_float(r), min_level,
                                           max_level, _p(out), len(out))
     return out[:n].copy()
+
+
+# ------------------------------------------------------------------------------------------------
+# DBoW2 as vendored by the reference, compiled verbatim (oracle/_ref/libref_vocabulary.so).
+# ------------------------------------------------------------------------------------------------
+REF_VOC_PATH = os.path.join(HERE, "_ref", "libref_vocabulary.so")
+_refv = None
+
+
+def have_ref_vocabulary():
+    return os.path.exists(REF_VOC_PATH)
+
+
+def ref_vocabulary_lib():
+    global _refv
+    if _refv is None:
+        if not have_ref_vocabulary():
+            raise RuntimeError("oracle/_ref/libref_vocabulary.so is not built (needs /root/reference)")
+        _refv = C.CDLL(REF_VOC_PATH)
+        _refv.refv_load_text.restype = C.c_void_p
+        _refv.refv_load_text.argtypes = [C.c_char_p]
+        _refv.refv_destroy.argtypes = [C.c_void_p]
+        _refv.refv_size.argtypes = [C.c_void_p]
+    return _refv
+
+
+def tree_as_loaded(tree):
+    """The synthetic tree as TemplatedVocabulary::loadFromTextFile (TemplatedVocabulary.h:1338-1430) rebuilds it from
+    a text file: node ids = line numbers with every parent before its children (the loader appends to m_nodes line by
+    line and indexes the parent, so the file is in top-down order -- breadth first here), children of a node in
+    ascending id order, word ids in ascending node id order."""
+    cb, ch = tree["child_begin"], tree["children"]
+    n = len(tree["word_id"])
+    order = [0]                                   # old ids in breadth-first order
+    for old in order:
+        order.extend(int(c) for c in ch[cb[old]:cb[old + 1]])
+    assert len(order) == n
+    new_of = np.empty(n, np.int64)
+    new_of[order] = np.arange(n)
+    child_begin = np.zeros(n + 1, np.int32)
+    children = []
+    for new, old in enumerate(order):
+        children.extend(sorted(int(new_of[c]) for c in ch[cb[old]:cb[old + 1]]))
+        child_begin[new + 1] = len(children)
+    order = np.asarray(order)
+    leaf = tree["word_id"][order] >= 0
+    word_id = np.full(n, -1, np.int32)
+    word_id[leaf] = np.arange(int(leaf.sum()), dtype=np.int32)
+    return dict(tree, child_begin=child_begin, children=np.asarray(children, np.int32), desc=tree["desc"][order],
+                weight=tree["weight"][order], word_id=word_id)
+
+
+def write_vocabulary_text(tree, k, path):
+    """ORBvoc.txt format: "k L scoring weighting", then one line per node id 1..n-1: parent, is-leaf, 32 bytes, weight.
+    No trailing newline (the reference's eof loop would read an empty record as one more child of the root)."""
+    cb, ch = tree["child_begin"], tree["children"]
+    n = len(tree["word_id"])
+    parent = np.zeros(n, np.int64)
+    for i in range(n):
+        parent[ch[cb[i]:cb[i + 1]]] = i
+    lines = ["%d %d 0 0" % (k, tree["depth"])]      # L1_NORM, TF_IDF (what ORBvoc.txt declares)
+    for i in range(1, n):
+        lines.append("%d %d %s %r" % (parent[i], int(tree["word_id"][i] >= 0),
+                                      " ".join(str(int(b)) for b in tree["desc"][i]), float(tree["weight"][i])))
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+class RefVocabulary:
+    """ORBVocabulary (include/ORBVocabulary.h:31-32) of the verbatim DBoW2 build, loaded from a text file."""
+
+    def __init__(self, path):
+        self._L = ref_vocabulary_lib()
+        self._v = self._L.refv_load_text(path.encode())
+        if not self._v:
+            raise RuntimeError("loadFromTextFile failed: " + path)
+
+    def __del__(self):
+        if getattr(self, "_v", None):
+            self._L.refv_destroy(self._v)
+            self._v = None
+
+    def words(self):
+        return self._L.refv_size(self._v)
+
+    def transform(self, features, levelsup=4):
+        """-> BowVector (ids, values) in key order, FeatureVector dict"""
+        f = u8c(features)
+        n = len(f)
+        bid = np.empty(max(n, 1), np.uint32); bval = np.empty(max(n, 1), np.float64); node = np.empty(n, np.uint32)
+        k = self._L.refv_transform(C.c_void_p(self._v), _p(f), n, int(levelsup), _p(bid), _p(bval), _p(node))
+        featvec = {}
+        for i in range(n):
+            if node[i] != 0xffffffff:
+                featvec.setdefault(int(node[i]), []).append(i)
+        return (bid[:k].copy(), bval[:k].copy()), featvec

@@ -12,7 +12,9 @@
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <sstream>   // OpenCV's core.hpp brings these in; DBoW2's TemplatedVocabulary.h relies on it
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 typedef unsigned char uchar;
@@ -51,6 +53,7 @@ class Mat {
     data = buf_->data();
     rows = r; cols = c; step = (size_t)c * esz();
   }
+  void release() { buf_.reset(); data = nullptr; rows = cols = 0; step = 0; }
   int type() const { return type_; }
   bool empty() const { return !data || !rows || !cols; }
   size_t esz() const { return type_ == CV_32F ? 4 : 1; }
@@ -68,6 +71,7 @@ class Mat {
     if (a < 0 || b > cols || a > b) throw std::out_of_range("Mat::colRange");
     Mat m(*this); m.data = data + (size_t)a * esz(); m.cols = b - a; return m;
   }
+  static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }  // create() zero-fills
   static Mat ones(int r, int c, int type) {
     Mat m(r, c, type);
     for (int y = 0; y < r; ++y) for (int x = 0; x < c; ++x) m.at<float>(y, x) = 1.0f;
@@ -157,6 +161,26 @@ class Mat_ : public Mat {  // only the `(Mat_<float>(3,1) << x, y, z)` initialis
     operator Mat() const { return *m; }
   };
   Init operator<<(T v) { Init in{this, 0}; in, v; return in; }
+};
+// cv::FileStorage / cv::FileNode: the YAML save / load members of DBoW2's TemplatedVocabulary are virtual, so their
+// bodies must compile; nothing here opens a file (the tests load vocabularies with loadFromTextFile).
+class FileNode {
+ public:
+  size_t size() const { return 0; }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](int) const { return FileNode(); }
+  operator int() const { return 0; }
+  operator double() const { return 0; }
+  operator std::string() const { return std::string(); }
+};
+class FileStorage {
+ public:
+  enum { READ = 0, WRITE = 1 };
+  FileStorage(const char*, int) {}
+  bool isOpened() const { return false; }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+  template <class T> FileStorage& operator<<(const T&) { return *this; }
 };
 // distortion-free cameras only (the callers test mDistCoef.at<float>(0) == 0 first and never get here)
 inline void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) {
