@@ -764,3 +764,35 @@ class RefVocabulary:
             if node[i] != 0xffffffff:
                 featvec.setdefault(int(node[i]), []).append(i)
         return (bid[:k].copy(), bval[:k].copy()), featvec
+
+
+# ------------------------------------------------------------------------------------------------
+# The reference's own MapPoint.cc, compiled verbatim with its own MapPoint.h (oracle/_ref/libref_mappoint.so).
+# ------------------------------------------------------------------------------------------------
+REF_MAPPOINT_PATH = os.path.join(HERE, "_ref", "libref_mappoint.so")
+_refp = None
+
+
+def have_ref_mappoint():
+    return os.path.exists(REF_MAPPOINT_PATH)
+
+
+def ref_distinctive_descriptors(desc_lists, bad_lists=None):
+    """The reference's MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307), verbatim, for every list of
+    observed descriptors -> index of the descriptor kept (-1: none).  bad_lists: per observation, its key frame isBad()."""
+    global _refp
+    if _refp is None:
+        if not have_ref_mappoint():
+            raise RuntimeError("oracle/_ref/libref_mappoint.so is not built (needs /root/reference)")
+        _refp = C.CDLL(REF_MAPPOINT_PATH)
+    offs = np.zeros(len(desc_lists) + 1, np.int32)
+    for i, d in enumerate(desc_lists):
+        offs[i + 1] = offs[i] + len(d)
+    flat = (np.concatenate([u8c(d).reshape(-1, 32) for d in desc_lists]) if offs[-1] else np.zeros((0, 32), np.uint8))
+    bad = None
+    if bad_lists is not None:
+        bad = (np.concatenate([np.asarray(b, np.uint8).reshape(-1) for b in bad_lists]) if offs[-1]
+               else np.zeros(0, np.uint8))
+    best = np.empty(len(desc_lists), np.int32)
+    _refp.refp_distinctive_descriptors(_p(flat), _p(bad), _p(offs), len(desc_lists), _p(best))
+    return best
