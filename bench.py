@@ -210,16 +210,32 @@ def run_ours(args):
                    "quadtree": 9000 * 12, "orient_desc": 60 * s["nfeatures"]}
     achieved = stage_bytes[top] * B / (acc[top] * 1e-3) / 1e9
     traffic = None  # DRAM bytes per launch of that kernel from the committed ncu capture (per frame x frames per launch)
+    warp_inst = {}  # warp-level instructions per frame and stage, same capture
     try:
         with open(os.path.join(ROOT, "profiles", "traffic_r03.json")) as f:
-            per_frame = json.load(f)["bytes_per_frame"].get(top)
+            cap_json = json.load(f)
+        per_frame = cap_json["bytes_per_frame"].get(top)
         traffic = per_frame * B if per_frame else None
+        warp_inst = cap_json.get("warp_inst_per_frame", {})
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": hbm, "unit": "GB/s",
                 "frac": achieved / hbm, "traffic": traffic, "algorithmic_bytes_per_launch": stage_bytes[top] * B,
                 "peak_kind": peak_kind,
                 "stage_ms": acc, "launches_per_step": launches / max(1, args.steps)}
+    # What actually bounds these byte-arithmetic kernels is instruction issue: warp instructions per
+    # frame (ncu inst_executed of the committed capture) x frames / live stage time, against 4 warp instructions per
+    # clock per SM at the SM clock sampled during the timed region.
+    if warp_inst and clocks.get("sm_mhz"):
+        props = torch.cuda.get_device_properties(dev)
+        issue_peak = props.multi_processor_count * 4 * clocks["sm_mhz"] * 1e6
+        roofline["issue"] = {
+            "unit": "G warp-inst/s", "peak": issue_peak / 1e9,
+            "peak_kind": "%d SMs x 4 schedulers x %.0f MHz (sampled)" % (props.multi_processor_count, clocks["sm_mhz"]),
+            "per_stage": {k: {"achieved": warp_inst[k] * B / (acc[k] * 1e-3) / 1e9,
+                              "frac": warp_inst[k] * B / (acc[k] * 1e-3) / issue_peak}
+                          for k in acc if k in warp_inst and acc[k] > 0},
+            "source": "profiles/traffic_r03.json (warp_inst_per_frame)"}
     pipe_gbs = ALGO_BYTES_PER_FRAME * B * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline["pipeline"] = {"achieved": pipe_gbs, "frac": pipe_gbs / hbm, "bytes_per_frame": ALGO_BYTES_PER_FRAME}
 

@@ -35,7 +35,10 @@ else:
             "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
             "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
             "launch__shared_mem_per_block_dynamic", "launch__shared_mem_per_block_static",
-            "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "sm__inst_executed.sum",
+            "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "inst_executed",
+            "TPC.TriageCompute.sm__inst_executed_pipe_alu_realtime.avg.pct_of_peak_sustained_elapsed",
+            "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+            "sm__inst_executed.sum",
             "sm__inst_executed_pipe_alu.sum", "sm__inst_executed_pipe_lsu.sum", "sm__inst_executed_pipe_xu.sum"]
     idx = [(w, hdr.index(w)) for w in want if w in hdr]
     out.append("# `ncu --set full --clock-control none --import-source on`, raw page; source: %s" % src)
