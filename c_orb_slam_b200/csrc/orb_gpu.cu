@@ -131,22 +131,42 @@ static bool graphs_enabled() {
   return on;
 }
 
-// Chunk boundaries of one host-pointer batch: [0, b1, b2, ..., nb].  ORB_GPU_HOST_SCHEDULE="a,b,c" gives the
-// chunk sizes explicitly (the last one repeats) for experiments.
-static std::vector<int> host_schedule(int nb) {
+// Chunk boundaries of one host-pointer batch: [0, b1, b2, ..., nb].  The first upload is latency the kernels cannot
+// hide and the last chunk's kernels and download are latency the uploads cannot hide, so the default schedule ramps
+// up at the head and down at the tail.  ORB_GPU_HOST_SCHEDULE="a,b,c/y,z" gives the chunk sizes explicitly for
+// experiments: head a, b, then c repeated, then the tail y, z.
+static std::vector<int> schedule_from(const std::vector<int>& head, const std::vector<int>& tail, int nb) {
   std::vector<int> b(1, 0);
-  static const std::vector<int> forced = [] {
-    std::vector<int> v;
+  int tail_sum = 0;
+  for (int t : tail) tail_sum += t;
+  for (size_t i = 0; b.back() < nb - tail_sum; ++i)
+    b.push_back(std::min(nb - tail_sum, b.back() + std::max(1, head[std::min(i, head.size() - 1)])));
+  for (int t : tail)
+    if (b.back() < nb) b.push_back(std::min(nb, b.back() + std::max(1, t)));
+  if (b.back() < nb) b.push_back(nb);
+  return b;
+}
+static std::vector<int> host_schedule(int nb) {
+  static const std::pair<std::vector<int>, std::vector<int>> forced = [] {
+    std::pair<std::vector<int>, std::vector<int>> v;
     const char* e = getenv("ORB_GPU_HOST_SCHEDULE");
-    while (e && *e) { v.push_back(atoi(e)); e = strchr(e, ','); if (e) ++e; }
+    bool in_tail = false;
+    while (e && *e) {
+      (in_tail ? v.second : v.first).push_back(atoi(e));
+      const char* c = strpbrk(e, ",/");
+      if (!c) break;
+      if (*c == '/') in_tail = true;
+      e = c + 1;
+    }
     return v;
   }();
-  if (!forced.empty()) {
-    for (size_t i = 0; b.back() < nb; ++i)
-      b.push_back(std::min(nb, b.back() + std::max(1, forced[std::min(i, forced.size() - 1)])));
-    return b;
+  if (!forced.first.empty()) {
+    int tail_sum = 0;
+    for (int t : forced.second) tail_sum += t;
+    return schedule_from(forced.first, tail_sum < nb ? forced.second : std::vector<int>(), nb);
   }
   const int c = host_chunk(nb);
+  std::vector<int> b(1, 0);
   while (b.back() < nb) b.push_back(std::min(nb, b.back() + c));
   return b;
 }
