@@ -101,7 +101,7 @@ struct OrbGpuExtractor {
   // host-pointer path: frames go through in chunks, H2D of chunk i+1 and D2H of chunk i-1 overlap
   // the kernels of chunk i (one copy stream per direction, events per chunk)
   cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
-  cudaStream_t s_alt[3] = {nullptr, nullptr, nullptr};  // extra compute streams: chunk c runs on stream c % n
+  cudaStream_t s_alt[7] = {};  // extra compute streams: chunk c runs on stream c % n
   std::vector<cudaEvent_t> ev_in, ev_done;
   // single-chunk host calls (one frame, a stereo pair, a small batch) are launch-bound: the kernel sequence
   // is captured into a CUDA graph on the second call with the same geometry and buffers and replayed after
@@ -123,7 +123,7 @@ static int host_chunk(int nb) {
 }
 static int host_streams() {
   static const int n = [] { const char* e = getenv("ORB_GPU_HOST_STREAMS"); return e ? atoi(e) : 4; }();
-  return std::max(1, std::min(4, n));
+  return std::max(1, std::min(8, n));
 }
 
 static bool graphs_enabled() {
@@ -394,9 +394,9 @@ int orb_gpu_create(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
   int rc = upload_constants();
   if (!rc && (cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking) != cudaSuccess ||
               cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking) != cudaSuccess ||
-              cudaStreamCreateWithFlags(&h->s_alt[0], cudaStreamNonBlocking) != cudaSuccess ||
-              cudaStreamCreateWithFlags(&h->s_alt[1], cudaStreamNonBlocking) != cudaSuccess ||
-              cudaStreamCreateWithFlags(&h->s_alt[2], cudaStreamNonBlocking) != cudaSuccess)) {
+              [&] { for (cudaStream_t& a : h->s_alt)
+                      if (cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking) != cudaSuccess) return true;
+                    return false; }())) {
     set_last_error("copy streams", cudaGetLastError());
     rc = ORB_GPU_ERR_CUDA;
   }
@@ -415,12 +415,12 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   cudaStreamSynchronize(h->s_h2d); cudaStreamSynchronize(h->s_d2h);
-  for (cudaStream_t a : h->s_alt) cudaStreamSynchronize(a);
+  for (cudaStream_t a : h->s_alt) if (a) cudaStreamSynchronize(a);
   if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
   cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
-  for (cudaStream_t a : h->s_alt) cudaStreamDestroy(a);
+  for (cudaStream_t a : h->s_alt) if (a) cudaStreamDestroy(a);
   DevBuf* bufs[] = {&h->pyr, &h->blur, &h->tables, &h->cell_tab, &h->cell_kp, &h->cell_cnt, &h->keys, &h->pay, &h->sel,
                     &h->sel_cnt, &h->cand_cnt, &h->status, &h->out_kps, &h->out_desc, &h->out_n, &h->stage};
   for (DevBuf* b : bufs) b->release();
@@ -617,10 +617,8 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       int* dn = (int*)h->out_n.p + c0;
       const int si = c % host_streams();
       cudaStream_t sc = si ? h->s_alt[si - 1] : s;
-      if (si && c == si) {  // the status reset and earlier work on s precede the first use of an extra stream
-        ORB_CUDA_TRY(cudaEventRecord(h->ev_done[nchunks - 1], s));
-        ORB_CUDA_TRY(cudaStreamWaitEvent(sc, h->ev_done[nchunks - 1], 0));
-      }
+      // ev_in[c] was recorded on the upload stream, which itself waited for the status reset and for earlier work on
+      // the compute stream: the extra streams need no further ordering (and must not wait for chunk 0's kernels)
       ORB_CUDA_TRY(cudaStreamWaitEvent(sc, h->ev_in[c], 0));
       if (timeline) cudaEventRecord(tl[2 + 4 * c], sc);
       Plan pc = plan_at(p, c0);
