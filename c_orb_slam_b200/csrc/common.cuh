@@ -112,6 +112,8 @@ struct TmpDevW {
 };
 
 // ---- launchers implemented in extract_kernels.cu -------------------------------------------
+int launch_repack_rows(const uint8_t* d_frames, size_t stride, size_t frame_stride, int width, int height,
+                       const LevelGeom& l0, int nframes, cudaStream_t s);
 int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s);
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);

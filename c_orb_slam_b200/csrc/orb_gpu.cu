@@ -493,10 +493,7 @@ int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, in
     p.lv[0].frame_stride = (long long)frame_stride;
   } else {
     // rows not 4-byte aligned (e.g. 1241-px KITTI rows): repack into the handle's level-0 buffer
-    for (int f = 0; f < nframes; ++f)
-      ORB_CUDA_TRY(cudaMemcpy2DAsync(p.lv[0].img + (size_t)f * p.lv[0].frame_stride, p.lv[0].pitch,
-                                     d_frames + (size_t)f * frame_stride, stride, width, height,
-                                     cudaMemcpyDeviceToDevice, s));
+    if ((rc = launch_repack_rows(d_frames, stride, frame_stride, width, height, p.lv[0], nframes, s))) return rc;
   }
   if ((rc = run_pipeline(h, p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
   if (d_status)
@@ -558,11 +555,10 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       Plan pc = p;
       if (alias) { pc.lv[0].img = stage; pc.lv[0].pitch = (int)stride; pc.lv[0].frame_stride = (long long)frame_stride; }
       auto enqueue = [&]() -> int {
-        if (!alias)
-          for (int f = 0; f < nb; ++f)
-            ORB_CUDA_TRY(cudaMemcpy2DAsync(pc.lv[0].img + (size_t)f * pc.lv[0].frame_stride, pc.lv[0].pitch,
-                                           stage + (size_t)f * frame_stride, stride, width, height,
-                                           cudaMemcpyDeviceToDevice, s));
+        if (!alias) {
+          const int rr = launch_repack_rows(stage, stride, frame_stride, width, height, pc.lv[0], nb, s);
+          if (rr) return rr;
+        }
         return run_pipeline(h, pc, h->sc, nb, dk, dd, capacity, dn, s, false);
       };
       const std::vector<long long> key = {nb, width, height, (long long)stride, (long long)frame_stride, capacity,
@@ -627,10 +623,9 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
         pc.lv[0].pitch = (int)stride;
         pc.lv[0].frame_stride = (long long)frame_stride;
       } else {
-        for (int f = 0; f < cn; ++f)
-          ORB_CUDA_TRY(cudaMemcpy2DAsync(pc.lv[0].img + (size_t)f * pc.lv[0].frame_stride, pc.lv[0].pitch,
-                                         stage + (size_t)(c0 + f) * frame_stride, stride, width, height,
-                                         cudaMemcpyDeviceToDevice, sc));
+        if ((rc = launch_repack_rows(stage + (size_t)c0 * frame_stride, stride, frame_stride, width, height, pc.lv[0],
+                                     cn, sc)))
+          return rc;
       }
       if ((rc = run_pipeline(h, pc, scratch_at(h->sc, p, c0), cn, dk, dd, capacity, dn, sc, false))) return rc;
       ORB_CUDA_TRY(cudaEventRecord(h->ev_done[c], sc));
