@@ -95,6 +95,31 @@ def cpu_reference_extract(frames, threads):
     return time.perf_counter() - t0, "port", int(counts.sum())
 
 
+def cv2_primitive_bound(frames, threads):
+    """Sanity bound on the speed of the restated OpenCV primitives: the pixel stages of one extraction (7 resizes,
+    FAST over every level at iniThFAST, 8 Gaussian blurs) through the real OpenCV of this image (cv2: SIMD / IPP,
+    `threads` threads).  No cells, retry, quadtree, orientation or descriptors, so a frame here costs LESS than a
+    frame of ORBextractor::operator() over real OpenCV; frames/s, or None when cv2 is missing."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    s = SETTINGS
+    cv2.setNumThreads(threads)
+    fast = cv2.FastFeatureDetector_create(s["ini_th"], True)
+    t0 = time.perf_counter()
+    for img in frames:
+        sf = 1.0
+        level = img
+        for l in range(s["nlevels"]):
+            if l:
+                sf *= s["scale"]
+                level = cv2.resize(level, (int(round(W / sf)), int(round(H / sf))), interpolation=cv2.INTER_LINEAR)
+            fast.detect(level)
+            cv2.GaussianBlur(level, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+    return len(frames) / (time.perf_counter() - t0)
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -339,6 +364,13 @@ def run_ours(args):
                          % (sample, B, cores, max(4, sample // 16) / dt1),
                "note": "ORBextractor.cc verbatim over oracle/opencv_shim (restated OpenCV primitives, not OpenCV's SIMD)"
                        if kind == "reference" else "oracle port"}
+        # how much faster real OpenCV runs the pixel primitives alone (upper bound for a reference built on it)
+        b1 = cv2_primitive_bound(frames_np[:16], 1)
+        bn = cv2_primitive_bound(frames_np[:64], cores)
+        if b1:
+            cpu["cv2_pixel_stages_only"] = {"frames_per_s_1_thread": b1, "frames_per_s_all_threads": bn,
+                                            "what": "7 resizes + FAST(20) on every level + 8 GaussianBlur per frame through "
+                                                    "cv2 (SIMD/IPP); no cells, retry, quadtree, orientation, descriptors"}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
