@@ -300,9 +300,20 @@ def run_ours(args):
         db = torch.randint(0, 256, (hi - lo, 32), dtype=torch.uint8, device=dev, generator=g)
         g.manual_seed(99)
         q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)
+        # N > 1: the per-rank top-2 are exchanged and merged by ONE kernel over NVLink peer memory (Top2Exchange);
+        # ORB_BENCH_EXCHANGE=nccl selects the plain form (NCCL all_gather of [3][nq] int32 + merge kernel)
+        exch, exch_kind = None, "none (one GPU)"
+        if world > 1:
+            exch_kind = "nccl all_gather + merge kernel"
+            if os.environ.get("ORB_BENCH_EXCHANGE", "peer") != "nccl":
+                try:
+                    exch = parallel.Top2Exchange(nq, device=local)
+                    exch_kind = "peer-memory exchange kernel (NVLink stores + system-scope flags, no NCCL on the data path)"
+                except Exception as e:  # e.g. no peer access between the GPUs: the NCCL form is exact as well
+                    exch_kind += " (peer-memory exchange unavailable: %s)" % type(e).__name__
+
         def step_match():
-            # device match of the local rows (+ one all_gather of [3][nq] int32 and the exact merge kernel if N > 1)
-            return parallel.match_bruteforce_sharded(q, db, lo, stream=stream)
+            return parallel.match_bruteforce_sharded(q, db, lo, stream=stream, exchange=exch)
 
         for _ in range(2):
             step_match()
@@ -335,7 +346,8 @@ def run_ours(args):
                    "steps": hsteps, "timing": "median of per-step device times (CUDA events, max over ranks)",
                    "ms_per_step_min": min(per_step), "ms_per_step_max": max(per_step),
                    "config": {"workload": "brute-force top-2, %d queries x %d database rows, database sharded over %d GPU(s), "
-                                          "top-2 all-gather + exact merge" % (nq, ndb_total, world)},
+                                          "exact merge of the per-GPU top-2" % (nq, ndb_total, world),
+                              "exchange": exch_kind},
                    "clocks": hclocks,
                    # the default kernel runs on tcgen05.mma kind::i8 (TMEM accumulators): 256 multiply-accumulates per pair
                    "roofline": {"bound": "tensor (tcgen05.mma kind::i8)", "achieved": gpairs * 256 / world / 1e3,

@@ -100,6 +100,13 @@ def lib():
                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orb_gpu_ratio_test_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float,
                                                 C.c_void_p, C.c_void_p]
+        L.orb_gpu_exchange_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.orb_gpu_exchange_local_handle.argtypes = [C.c_void_p, C.c_void_p]
+        L.orb_gpu_exchange_connect.argtypes = [C.c_void_p, C.c_void_p]
+        L.orb_gpu_exchange_connect_local.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+        L.orb_gpu_exchange_destroy.argtypes = [C.c_void_p]
+        L.orb_gpu_exchange_top2_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orb_gpu_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                                    C.c_void_p, C.c_int, _Grid, C.c_void_p, C.c_int, C.c_float,
                                                    C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,

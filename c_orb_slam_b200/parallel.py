@@ -4,9 +4,12 @@ Two paths shard:
   * extraction -- frames (and stereo pairs) are independent units: rank r takes the contiguous block
     shard_range(nframes, r, world); there is NO collective on the data path;
   * brute-force matching -- the descriptor database is sharded by rows; every rank scans its rows with
-    the queries replicated, one all_gather of the per-rank (idx, best, second) [3][nq] int32 (12*nq bytes per
-    rank) and the exact merge kernel (orb_gpu_merge_top2_device) give the global top-2.  Lowest index wins
-    ties, as in the ascending scan of the reference's update rule (src/ORBmatcher.cc:216-225).
+    the queries replicated; the per-rank (idx, best, second) [3][nq] int32 (12*nq bytes per rank) are exchanged
+    and merged exactly.  Lowest index wins ties, as in the ascending scan of the reference's update rule
+    (src/ORBmatcher.cc:216-225).  Two forms of the exchange: Top2Exchange -- ONE kernel per rank that stores
+    its slice into every rank's gather buffer over NVLink peer memory, signals, waits and merges
+    (orb_gpu_exchange_top2_device; no NCCL on the data path) -- and the plain one: NCCL all_gather +
+    orb_gpu_merge_top2_device.
 Windowed matching is "replicas only" (a call is microseconds of work).
 
 The merge itself runs on the GPU (C ABI); nothing here computes descriptors or distances on the CPU.
@@ -48,9 +51,60 @@ def gather_top2(part, group=None):
     return out.view((world,) + tuple(part.shape))
 
 
-def match_bruteforce_sharded(d_queries, d_db_shard, idx_base, group=None, stream=None):
+class Top2Exchange:
+    """Peer-memory exchange of the per-rank top-2 (one per rank and process).  The constructor allocates this rank's
+    gather buffer and arrival counters, all-gathers the CUDA IPC handles through torch.distributed and maps the
+    peers' buffers; exchange() is then a single kernel launch per call."""
+
+    def __init__(self, nq_max, device=None, group=None):
+        import ctypes as C
+        self._L = lib()
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.nq_max = int(nq_max)
+        h = C.c_void_p()
+        _check(self._L.orb_gpu_exchange_create(self.device, self.rank, self.world, self.nq_max, C.byref(h)),
+               "orb_gpu_exchange_create")
+        self._h = h
+        if self.world > 1:
+            nb = self._L.orb_gpu_exchange_handle_bytes()
+            mine = torch.zeros(nb, dtype=torch.uint8)
+            _check(self._L.orb_gpu_exchange_local_handle(self._h, mine.data_ptr()), "orb_gpu_exchange_local_handle")
+            # the handles are 128 opaque bytes per rank: they go through the process group like any small tensor
+            dev = torch.device("cuda", self.device) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+            allh = torch.empty(self.world * nb, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(allh, mine.to(dev), group=group)
+            allh = allh.cpu().contiguous()
+            _check(self._L.orb_gpu_exchange_connect(self._h, allh.data_ptr()), "orb_gpu_exchange_connect")
+            dist.barrier(group)   # every rank has mapped every buffer before the first store
+
+    def exchange(self, part, stream=None):
+        """part: CUDA int32 [3][nq] (idx, best, second of this rank's rows) -> merged [3][nq], same on every rank."""
+        nq = part.shape[1]
+        out = torch.empty_like(part)
+        st = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+        _check(self._L.orb_gpu_exchange_top2_device(self._h, part[0].data_ptr(), part[1].data_ptr(), part[2].data_ptr(),
+                                                    nq, out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), st),
+               "orb_gpu_exchange_top2_device")
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orb_gpu_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def match_bruteforce_sharded(d_queries, d_db_shard, idx_base, group=None, stream=None, exchange=None):
     """Brute-force top-2 of the replicated queries against a row-sharded database.
     d_queries [nq,32] / d_db_shard [rows,32]: uint8 CUDA tensors; idx_base = global index of the shard's row 0.
+    exchange: a Top2Exchange (peer-memory exchange kernel) or None (NCCL all_gather + merge kernel).
     Returns a CUDA int32 tensor [3][nq] (global idx, best, second), identical on every rank."""
     if not d_queries.is_cuda or not d_db_shard.is_cuda:
         raise RuntimeError("match_bruteforce_sharded needs CUDA tensors: the product path has no CPU fallback")
@@ -64,6 +118,8 @@ def match_bruteforce_sharded(d_queries, d_db_shard, idx_base, group=None, stream
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
         return part
+    if exchange is not None:
+        return exchange.exchange(part, st)
     g = gather_top2(part, group).permute(1, 0, 2).contiguous()  # [3][world][nq], shards in ascending row order
     merged = torch.empty((3, nq), dtype=torch.int32, device=d_queries.device)
     _check(L.orb_gpu_merge_top2_device(g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), world, nq,

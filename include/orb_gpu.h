@@ -125,6 +125,25 @@ int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_
 int orb_gpu_merge_top2_device(const int32_t* d_idx, const int32_t* d_best, const int32_t* d_second,
                               int nshards, int nq, int32_t* d_out_idx, int32_t* d_out_best,
                               int32_t* d_out_second, void* stream);
+/* The same exchange + merge as ONE kernel over NVLink peer memory (no NCCL on the data path): every rank stores
+ * its [3][nq] result into slot `rank` of every rank's gather buffer, signals the peers' arrival counters
+ * (system-scope atomics), waits for its own counters and merges the `world` slots (lowest index wins ties).
+ * One OrbGpuExchange per rank; one process per GPU exchanges the handles of orb_gpu_exchange_local_handle
+ * (orb_gpu_exchange_handle_bytes() bytes each, cudaIpcMemHandle_t inside) by any host-side means and passes all of
+ * them, in rank order, to orb_gpu_exchange_connect; ranks living in one process use orb_gpu_exchange_connect_local.
+ * Every rank must make the same sequence of orb_gpu_exchange_top2_device calls (same nq <= nq_max); a rank that
+ * never arrives makes the others trap after ~4 s instead of hanging.  The reference has no counterpart (it
+ * relocalises through the BoW inverted file, src/KeyFrameDatabase.cc:199-309); config 5 of BASELINE.json defines it. */
+typedef struct OrbGpuExchange OrbGpuExchange;
+int orb_gpu_exchange_create(int device, int rank, int world, int nq_max, OrbGpuExchange** out);
+int orb_gpu_exchange_handle_bytes(void);
+int orb_gpu_exchange_local_handle(OrbGpuExchange* x, uint8_t* handle);
+int orb_gpu_exchange_connect(OrbGpuExchange* x, const uint8_t* handles /* [world][handle_bytes] */);
+int orb_gpu_exchange_connect_local(OrbGpuExchange* const* all, int world);
+int orb_gpu_exchange_destroy(OrbGpuExchange* x);
+int orb_gpu_exchange_top2_device(OrbGpuExchange* x, const int32_t* d_idx, const int32_t* d_best,
+                                 const int32_t* d_second, int nq, int32_t* d_out_idx, int32_t* d_out_best,
+                                 int32_t* d_out_second, void* stream);
 /* accept flags of ORBmatcher.cc:228-230: best <= th && (float)best < nnratio*(float)second */
 int orb_gpu_ratio_test_device(const int32_t* d_best, const int32_t* d_second, int nq, int th,
                               float nnratio, uint8_t* d_accept, void* stream);

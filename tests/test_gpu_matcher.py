@@ -290,3 +290,48 @@ def test_features_in_area_order(gpu, oracle):
         assert np.array_equal(got[i], want), i
         total += len(want)
     assert total > 5000 and any(len(g) == 0 for g in got)
+
+
+def test_peer_memory_exchange_two_ranks_on_one_gpu(gpu, oracle):
+    """orb_gpu_exchange_top2_device: both ranks of a world of 2 live in this process on one GPU (two streams, buffers
+    wired with orb_gpu_exchange_connect_local); five calls in a row reuse the double-buffered gather slots."""
+    import ctypes as C
+    import torch
+    L = gpu.lib()
+    nq, ndb = 1000, 60000
+    hs = (C.c_void_p * 2)()
+    for r in range(2):
+        h = C.c_void_p()
+        assert L.orb_gpu_exchange_create(0, r, 2, 1024, C.byref(h)) == 0
+        hs[r] = h
+    assert L.orb_gpu_exchange_connect_local(hs, 2) == 0
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    try:
+        for call in range(5):
+            q, db = synth.make_match_set(nq, ndb, seed=40 + call)
+            want = np.stack(oracle.match_bruteforce(q, db, threads=4))
+            dq = torch.from_numpy(q).cuda()
+            ddb = torch.from_numpy(db).cuda()
+            cut = ndb // 3 + 17 * call
+            parts, outs = [], []
+            for r, (lo, hi) in enumerate(((0, cut), (cut, ndb))):
+                part = torch.empty((3, nq), dtype=torch.int32, device="cuda")
+                assert L.orb_gpu_match_bruteforce_device(dq.data_ptr(), nq, ddb[lo:hi].data_ptr(), hi - lo, lo,
+                                                         part[0].data_ptr(), part[1].data_ptr(), part[2].data_ptr(),
+                                                         None) == 0
+                parts.append(part)
+            torch.cuda.synchronize()
+            for r in range(2):   # the two kernels wait for each other: they must be on different streams
+                out = torch.empty((3, nq), dtype=torch.int32, device="cuda")
+                p = parts[r]
+                assert L.orb_gpu_exchange_top2_device(hs[r], p[0].data_ptr(), p[1].data_ptr(), p[2].data_ptr(), nq,
+                                                      out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                                                      streams[r].cuda_stream) == 0
+                outs.append(out)
+            torch.cuda.synchronize()
+            for out in outs:
+                assert np.array_equal(out.cpu().numpy(), want)
+    finally:
+        torch.cuda.synchronize()
+        for r in range(2):
+            L.orb_gpu_exchange_destroy(hs[r])
