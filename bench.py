@@ -288,6 +288,29 @@ def run_ours(args):
            "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 4)),
            "ms_per_step": 1e3 * e2e_s / args.steps}
     assert int(h_n.sum().item()) == kp_total, "host and device paths disagree"
+    # the copies alone (same bytes, same pinned buffers, H2D and D2H on two streams, every rank at once): what the
+    # host link leaves for any implementation of the host-pointer call at this N
+    d_in = torch.empty_like(h_frames, device=dev)
+    d_ok, d_od = torch.empty_like(h_kps, device=dev), torch.empty_like(h_desc, device=dev)
+    s_out = torch.cuda.Stream(device=dev)
+
+    def copies():
+        d_in.copy_(h_frames, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            h_kps.copy_(d_ok, non_blocking=True)
+            h_desc.copy_(d_od, non_blocking=True)
+
+    copies()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        copies()
+    torch.cuda.synchronize()
+    copy_s = max_over_ranks(time.perf_counter() - t0) / 5
+    e2e["copies_only_ms_per_step"] = 1e3 * copy_s
+    e2e["copies_only_note"] = ("pinned H2D of the frames + D2H of the outputs alone, all %d rank(s) at once: the host link's "
+                               "bound on this path (%.1f GB/s H2D per GPU)" % (world, B * W * H / copy_s / 1e9))
+    del d_in, d_ok, d_od
 
     # ---- Hamming brute force: 4096 queries x 10M rows, database sharded by rank -----------------
     hamming = None
