@@ -10,6 +10,8 @@
 // (the TU is compiled with -fmad=false) so every operation rounds as in the oracle.
 #include <cfloat>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace orbgpu {
@@ -94,12 +96,90 @@ resize_level_kernel(LevelGeom src, LevelGeom dst) {
   }
 }
 
+// Four destination columns per thread (scaleFactor <= 2: their taps span at most 11 bytes = three aligned words from
+// the thread's first word): per destination row 6 loads instead of 2 x 4, one set of row offsets / weights and one
+// 32-bit store for four pixels.  Columns 0,1 take their tap pairs from words (0,1); columns 2,3 from words (1,2) when
+// column 2 starts in word 1 or later, else from (0,1) as well -- a per-thread constant choice (two selects per row).
+__global__ void __launch_bounds__(256)
+resize_level4_kernel(LevelGeom src, LevelGeom dst) {
+  __shared__ unsigned s_off0[kRzRows], s_off1[kRzRows];
+  __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];
+  const int f = blockIdx.y;
+  const int dy0 = blockIdx.x * kRzRows;
+  const int rstep = src.pitch >> 2;
+  if (threadIdx.x < kRzRows) {
+    const int dy = min(dy0 + (int)threadIdx.x, dst.h - 1);
+    const int sy0 = dst.yofs[dy];
+    s_off0[threadIdx.x] = (unsigned)(sy0 * rstep);
+    s_off1[threadIdx.x] = (unsigned)(min(sy0 + 1, src.h - 1) * rstep);
+    s_b0[threadIdx.x] = (unsigned)dst.ay0[dy] << 16;
+    s_b1[threadIdx.x] = (unsigned)dst.ay1[dy] << 16;
+  }
+  __syncthreads();
+  const int nt = (dst.w + 3) >> 2;
+  const int last_word = rstep - 1;
+  const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
+  uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
+  const int nrows = min(kRzRows, dst.h - dy0);
+  for (int t = threadIdx.x; t < nt; t += blockDim.x) {
+    int x[4];
+    unsigned wt[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int dx = min(4 * t + j, dst.w - 1);
+      x[j] = dst.xofs[dx];
+      wt[j] = (unsigned)(unsigned short)dst.ax0[dx] | ((unsigned)(unsigned short)dst.ax1[dx] << 16);
+    }
+    const int wi0 = x[0] >> 2;
+    const unsigned* c0 = sbase + wi0;
+    const unsigned* c1 = sbase + min(wi0 + 1, last_word);
+    const unsigned* c2 = sbase + min(wi0 + 2, last_word);
+    const int o0 = x[0] - 4 * wi0, o1 = x[1] - 4 * wi0;
+    const bool hi = x[2] - 4 * wi0 >= 4;
+    const int o2 = x[2] - 4 * wi0 - (hi ? 4 : 0), o3 = x[3] - 4 * wi0 - (hi ? 4 : 0);
+    const unsigned sel01 = (unsigned)o0 | ((unsigned)(o0 + 1) << 4) | ((unsigned)o1 << 8) | ((unsigned)(o1 + 1) << 12);
+    const unsigned sel23 = (unsigned)o2 | ((unsigned)(o2 + 1) << 4) | ((unsigned)o3 << 8) | ((unsigned)(o3 + 1) << 12);
+    uint8_t* drow = dbase + 4 * t;
+#pragma unroll 1
+    for (int i0 = 0; i0 < kRzRows; i0 += kRzBatch) {
+      unsigned w[kRzBatch][6];
+#pragma unroll
+      for (int k = 0; k < kRzBatch; ++k) {
+        const unsigned r0 = s_off0[i0 + k], r1 = s_off1[i0 + k];
+        w[k][0] = c0[r0]; w[k][1] = c1[r0]; w[k][2] = c2[r0];
+        w[k][3] = c0[r1]; w[k][4] = c1[r1]; w[k][5] = c2[r1];
+      }
+#pragma unroll
+      for (int k = 0; k < kRzBatch; ++k) {
+        const unsigned pa0 = __byte_perm(w[k][0], w[k][1], sel01), pa1 = __byte_perm(w[k][3], w[k][4], sel01);
+        const unsigned pb0 = __byte_perm(hi ? w[k][1] : w[k][0], hi ? w[k][2] : w[k][1], sel23);
+        const unsigned pb1 = __byte_perm(hi ? w[k][4] : w[k][3], hi ? w[k][5] : w[k][4], sel23);
+        const unsigned b0 = s_b0[i0 + k], b1 = s_b1[i0 + k];
+        const unsigned v0 = (__umulhi(b0, __dp2a_lo(wt[0], pa0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wt[0], pa1, 0u) >> 4) + 2u) >> 2;
+        const unsigned v1 = (__umulhi(b0, __dp2a_hi(wt[1], pa0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wt[1], pa1, 0u) >> 4) + 2u) >> 2;
+        const unsigned v2 = (__umulhi(b0, __dp2a_lo(wt[2], pb0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wt[2], pb1, 0u) >> 4) + 2u) >> 2;
+        const unsigned v3 = (__umulhi(b0, __dp2a_hi(wt[3], pb0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wt[3], pb1, 0u) >> 4) + 2u) >> 2;
+        if (i0 + k < nrows) *reinterpret_cast<unsigned*>(drow) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+        drow += dst.pitch;
+      }
+    }
+  }
+}
+
 int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
   const LevelGeom& d = p.lv[level];
-  const int nt = (d.w + 1) >> 1;
-  const int threads = min(512, (nt + 31) & ~31);
+  static const bool two_col = [] { const char* e = getenv("ORB_GPU_RESIZE2"); return e && atoi(e); }();
   dim3 grid((d.h + kRzRows - 1) / kRzRows, nframes);
-  resize_level_kernel<<<grid, threads, 0, s>>>(p.lv[level - 1], d);
+  // the four-column form needs the three-word tap window (scaleFactor <= 2) and 4-byte aligned destination rows
+  const bool four = !two_col && (long long)p.lv[level - 1].w <= 2LL * d.w + 1 && (d.pitch & 3) == 0 &&
+                    (d.frame_stride & 3) == 0;
+  if (four) {
+    const int nt = (d.w + 3) >> 2;
+    resize_level4_kernel<<<grid, min(256, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d);
+  } else {
+    const int nt = (d.w + 1) >> 1;
+    resize_level_kernel<<<grid, min(512, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d);
+  }
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
