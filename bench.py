@@ -237,7 +237,7 @@ def run_ours(args):
     traffic = None  # DRAM bytes per launch of that kernel from the committed ncu capture (per frame x frames per launch)
     warp_inst = {}  # warp-level instructions per frame and stage, same capture
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r03.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "traffic_r05.json")) as f:
             cap_json = json.load(f)
         per_frame = cap_json["bytes_per_frame"].get(top)
         traffic = per_frame * B if per_frame else None
@@ -260,7 +260,7 @@ def run_ours(args):
             "per_stage": {k: {"achieved": warp_inst[k] * B / (acc[k] * 1e-3) / 1e9,
                               "frac": warp_inst[k] * B / (acc[k] * 1e-3) / issue_peak}
                           for k in acc if k in warp_inst and acc[k] > 0},
-            "source": "profiles/traffic_r03.json (warp_inst_per_frame)"}
+            "source": "profiles/traffic_r05.json (warp_inst_per_frame)"}
     pipe_gbs = ALGO_BYTES_PER_FRAME * B * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline["pipeline"] = {"achieved": pipe_gbs, "frac": pipe_gbs / hbm, "bytes_per_frame": ALGO_BYTES_PER_FRAME}
 
