@@ -140,3 +140,18 @@ def test_device_api_aliased_and_unaligned(gpu, oracle):
             ko, do = ex_o(frames[f])
             assert n[f] == len(ko) and np.array_equal(kps[f, :n[f]], ko) and np.array_equal(desc[f, :n[f]], do)
         assert np.array_equal(ex.pyramid_level(0, 1), frames[1])
+
+
+@pytest.mark.parametrize("W,H,scale,nlevels", [(641, 480, 1.2, 8), (642, 479, 1.2, 8), (643, 481, 1.3, 6),
+                                               (1241, 376, 1.2, 8), (800, 600, 2.0, 4), (640, 480, 1.05, 8)])
+def test_pyramid_levels_pixel_exact_for_odd_widths_and_scales(gpu, oracle, W, H, scale, nlevels):
+    """Every pyramid level, pixel for pixel, for widths of every residue mod 4 (unaligned rows are repacked, the
+    four-column resize stores whole words into the row padding) and for scale factors up to the limit of 2."""
+    img = synth.make_frame(W, H, 77)
+    ex_g = gpu.ORBextractor(400, scale, nlevels, 20, 7, max_width=W, max_height=H)
+    ex_o = oracle.Extractor(400, scale, nlevels, 20, 7)
+    k, d = ex_g(img)
+    ko, do = ex_o(img)
+    for l in range(nlevels):
+        assert np.array_equal(ex_g.pyramid_level(l), ex_o.level_image(l)), l
+    assert np.array_equal(k, ko) and np.array_equal(d, do)
