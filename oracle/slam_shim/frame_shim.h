@@ -6,7 +6,9 @@
 #pragma once
 #define SLAM_SHIM_REAL_FRAME
 #define ORBVOCABULARY_H
+#ifndef SLAM_SHIM_GPU_EXTRACTOR  // frame_gpu_shim.h puts the product's drop-in ORBextractor.h there instead
 #define ORBEXTRACTOR_H
+#endif
 #define CONVERTER_H
 #include <climits>  // INT_MAX reaches the reference's Frame.cc through OpenCV's headers
 
@@ -20,6 +22,7 @@ class ORBVocabulary {  // Frame::ComputeBoW only forwards to it
   void transform(const std::vector<cv::Mat>&, DBoW2::BowVector&, DBoW2::FeatureVector&, int) {}
 };
 
+#ifndef SLAM_SHIM_GPU_EXTRACTOR
 class ORBextractor {  // the image pyramid and the scale tables are what ComputeStereoMatches reads
  public:
   void operator()(const cv::Mat&, const cv::Mat&, std::vector<cv::KeyPoint>&, cv::Mat&) {}
@@ -32,6 +35,8 @@ class ORBextractor {  // the image pyramid and the scale tables are what Compute
   std::vector<cv::Mat> mvImagePyramid;
   std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
 };
+
+#endif  // SLAM_SHIM_GPU_EXTRACTOR
 
 class Converter {
  public:

@@ -187,4 +187,25 @@ inline void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&
   throw std::logic_error("cv::undistortPoints is not part of the shim");
 }
 
+// cv::InputArray / cv::OutputArray as the extractor's operator() takes them (include/ORBextractor.h:59-61)
+class _InputArray {
+ public:
+  _InputArray(const Mat& m) : m_(&m) {}
+  Mat getMat() const { return *m_; }
+  bool empty() const { return m_->empty(); }
+ private:
+  const Mat* m_;
+};
+class _OutputArray {
+ public:
+  _OutputArray(Mat& m) : m_(&m) {}
+  Mat getMat() const { return *m_; }
+  void release() const { m_->release(); }
+  void create(int r, int c, int type) const { m_->create(r, c, type); }
+ private:
+  Mat* m_;
+};
+typedef const _InputArray& InputArray;
+typedef const _OutputArray& OutputArray;
+
 }  // namespace cv
