@@ -335,6 +335,16 @@ def run_ours(args):
                 except Exception as e:  # e.g. no peer access between the GPUs: the NCCL form is exact as well
                     exch_kind += " (peer-memory exchange unavailable: %s)" % type(e).__name__
 
+        if exch is not None:  # the two exchange forms must agree bit for bit on this run's data, else use NCCL
+            same = torch.equal(parallel.match_bruteforce_sharded(q, db, lo, stream=stream, exchange=exch),
+                               parallel.match_bruteforce_sharded(q, db, lo, stream=stream))
+            flag = torch.tensor([int(same)], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) != 1:
+                exch, exch_kind = None, "nccl all_gather + merge kernel (peer-memory exchange DISAGREED and was dropped)"
+            else:
+                exch_kind += "; checked equal to the NCCL form on this run's data"
+
         def step_match():
             return parallel.match_bruteforce_sharded(q, db, lo, stream=stream, exchange=exch)
 
