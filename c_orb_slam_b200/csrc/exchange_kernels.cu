@@ -9,7 +9,7 @@
 //   4. the block merges the `world` slots of the local gather buffer (ld.cg: written by peers, never through L1).
 // No rank waits before it has delivered its own data, so the exchange cannot deadlock as long as every rank makes
 // the call; the gather buffer is double-buffered by call parity (a rank can be at most one call ahead of a peer,
-// because completing a call needs that peer's arrival of the same call).  A wait of seconds traps instead of hanging.
+// because completing a call needs that peer's arrival of the same call).  A wait of ~17 s traps instead of hanging.
 //
 // Peer pointers come from cudaIpcOpenMemHandle (one process per GPU: the handles travel through
 // torch.distributed, c_orb_slam_b200/parallel.py) or are wired directly when all ranks live in one process.
@@ -55,7 +55,7 @@ exchange_top2_kernel(const int32_t* __restrict__ l_idx, const int32_t* __restric
     const long long t0 = clock64();
     for (int r = 0; r < world; ++r)
       while ((int)(ld_acquire_sys(mine + r) - target) < 0)
-        if (clock64() - t0 > (1ll << 33)) __trap();  // ~4 s: a rank never made the call
+        if (clock64() - t0 > (1ll << 35)) __trap();  // ~17 s: a rank never made the call
     __threadfence_system();
   }
   __syncthreads();

@@ -132,7 +132,7 @@ int orb_gpu_merge_top2_device(const int32_t* d_idx, const int32_t* d_best, const
  * (orb_gpu_exchange_handle_bytes() bytes each, cudaIpcMemHandle_t inside) by any host-side means and passes all of
  * them, in rank order, to orb_gpu_exchange_connect; ranks living in one process use orb_gpu_exchange_connect_local.
  * Every rank must make the same sequence of orb_gpu_exchange_top2_device calls (same nq <= nq_max); a rank that
- * never arrives makes the others trap after ~4 s instead of hanging.  The reference has no counterpart (it
+ * never arrives makes the others trap after ~17 s instead of hanging.  The reference has no counterpart (it
  * relocalises through the BoW inverted file, src/KeyFrameDatabase.cc:199-309); config 5 of BASELINE.json defines it. */
 typedef struct OrbGpuExchange OrbGpuExchange;
 int orb_gpu_exchange_create(int device, int rank, int world, int nq_max, OrbGpuExchange** out);
