@@ -376,6 +376,20 @@ class ORBmatcher:
         b = np.asarray(best); s = np.asarray(second)
         return (b <= th) & (b.astype(np.float32) < np.float32(self.mfNNratio) * s.astype(np.float32))
 
+    def accept_device(self, best, second, th=None):
+        """The same flags from the device kernel (orb_gpu_ratio_test_device); best / second: host int32 arrays."""
+        import torch
+        th = self.TH_LOW if th is None else th
+        b = torch.from_numpy(np.ascontiguousarray(best, np.int32)).cuda(self.device)
+        s = torch.from_numpy(np.ascontiguousarray(second, np.int32)).cuda(self.device)
+        out = torch.empty(len(b), dtype=torch.uint8, device=b.device)
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _check(lib().orb_gpu_ratio_test_device(b.data_ptr(), s.data_ptr(), len(b), int(th), self.mfNNratio,
+                                                   out.data_ptr(), st), "orb_gpu_ratio_test_device")
+            torch.cuda.synchronize()
+        return out.cpu().numpy().astype(bool)
+
     def SearchByProjection(self, frame, map_points, th=3.0):
         """ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) (ORBmatcher.cc:45-129).
         frame: dict(kps KP_DTYPE (undistorted), desc [N,32], u_right [N] or None, grid (minX,minY,invW,invH),

@@ -1,9 +1,10 @@
-// Adapters that let the reference's ORBmatcher call sites use the C ABI (include/orb_gpu.h).
-// They are templates over the reference's Frame / MapPoint types so this header does not pull in
-// Frame.h (DBoW2, Eigen, ...): inside ORB-SLAM2, src/ORBmatcher.cc instantiates them with its own
-// classes.  Pointer bookkeeping (F.mvpMapPoints[i] = pMP) stays on the host
-// exactly as in the reference; candidate search, Hamming distances, top-2, ratio test and the
-// ordered claims run on the GPU.
+// Building blocks of the drop-in ORB_SLAM2::ORBmatcher (adapter/ORBmatcher.h, adapter/ORBmatcher.cc): the two
+// Frame-to-Frame projection searches and the stereo helpers as templates over the reference's Frame / MapPoint
+// types, so this header does not pull in Frame.h (DBoW2, Eigen, ...) and can also be instantiated on its own
+// (tests/cpp/dropin_matcher.cc does, with the reference's real Frame).  Pointer bookkeeping
+// (F.mvpMapPoints[i] = pMP) stays on the host exactly as in the reference; candidate search, Hamming distances,
+// top-2, ratio test and the ordered claims run on the GPU.  `device` = CUDA ordinal; `status` (optional) receives
+// the OrbGpuStatus of the C-ABI call.
 #ifndef ORBMATCHER_GPU_H
 #define ORBMATCHER_GPU_H
 
@@ -19,7 +20,7 @@ namespace gpu {
 // (src/ORBmatcher.cc:45-129).  Returns nmatches and assigns F.mvpMapPoints like the reference.
 template <class FrameT, class MapPointT>
 int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, float th, float nnratio,
-                       int device = 0) {
+                       int device = 0, int* status = nullptr) {
   const int nq = (int)vpMapPoints.size(), nk = F.N;
   std::vector<OrbProjQuery> q(nq);
   std::vector<uint8_t> qdesc((size_t)nq * 32), blocked(nk, 0);
@@ -48,6 +49,7 @@ int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, fl
       q.data(), qdesc.data(), nq, reinterpret_cast<const OrbKeyPoint*>(F.mvKeysUn.data()), kdesc.data(),
       F.mvuRight.empty() ? nullptr : F.mvuRight.data(), nk, g, F.mvScaleFactors.data(),
       (int)F.mvScaleFactors.size(), th, nnratio, ORB_GPU_TH_HIGH, device, blocked.data(), match.data(), &nmatches);
+  if (status) *status = rc;
   if (rc != ORB_GPU_OK) return 0;
   for (int i = 0; i < nk; ++i)
     if (match[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[match[i]];  // :123
@@ -60,7 +62,7 @@ int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, fl
 // (:1392-1467) run in orb_gpu_search_windowed.
 template <class FrameT, class MapPointT>
 int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float th, bool bMono,
-                           bool checkOrientation, int device = 0) {
+                           bool checkOrientation, int device = 0, int* status = nullptr) {
   const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
   const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
   const cv::Mat twc = -Rcw.t() * tcw;
@@ -109,6 +111,7 @@ int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float 
       q.data(), qdesc.data(), nq, reinterpret_cast<const OrbKeyPoint*>(CurrentFrame.mvKeysUn.data()), kdesc.data(),
       CurrentFrame.mvuRight.empty() ? nullptr : CurrentFrame.mvuRight.data(), nk, g, ORB_GPU_TH_HIGH,
       /*gate=*/1, nullptr, 0, checkOrientation ? 1 : 0, device, blocked.data(), match.data(), nullptr, &nmatches);
+  if (status) *status = rc;
   if (rc != ORB_GPU_OK) return 0;
   for (int i = 0; i < nk; ++i) {
     if (match[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[match[i]];
@@ -116,17 +119,6 @@ int SearchByProjectionLast(FrameT& CurrentFrame, const FrameT& LastFrame, float 
   }
   return nmatches;
 }
-
-// ORBmatcher::SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>& sAlreadyFound, th, ORBdist) (:1472-1599)
-// and ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (:290-403) build their
-// OrbWindowQuery rows the same way (levels [l-1, l+1] / [l-1, l], blocks = 1, no stereo gate) and call
-// orb_gpu_search_windowed with th_accept = ORBdist / ORB_GPU_TH_LOW (check_orientation = 0 for the latter).
-//
-// ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (:825-975): rows with levels [l-1, l], blocks = 0, gate = 2 and
-// pKF->mvInvLevelSigma2, th_accept = ORB_GPU_TH_LOW; the caller walks match_of_query in query order and applies
-// Replace() / AddObservation() exactly as :953-970 do.  Fuse(KeyFrame*, Scw, ...) (:977-1100) is the same with
-// gate = 0.  ORBmatcher::SearchBySim3 (:1102-1326) calls it twice (KF1 points into KF2 and back, blocks = 0,
-// th_accept = ORB_GPU_TH_HIGH) and keeps i where match_of_query2[match_of_query1[i]] == i (:1303-1323).
 
 // Hamming stage of Frame::ComputeStereoMatches (src/Frame.cc:466-549): fills bestIdxR / bestDist
 // per left keypoint; the caller continues with the sub-pixel refinement (:551-640) unchanged.

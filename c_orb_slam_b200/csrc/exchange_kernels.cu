@@ -13,6 +13,7 @@
 //
 // Peer pointers come from cudaIpcOpenMemHandle (one process per GPU: the handles travel through
 // torch.distributed, c_orb_slam_b200/parallel.py) or are wired directly when all ranks live in one process.
+#include <algorithm>
 #include <cstring>
 #include <vector>
 
@@ -33,14 +34,19 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   return v;
 }
 
+// At most kExMaxBlocks blocks, each striding over the queries: every block's thread 0 waits for ALL blocks of ALL
+// ranks, so the whole grid has to be resident at once -- 64 blocks of 256 threads without shared memory always are
+// (148 SMs), whatever nq_max is.
+constexpr int kExMaxBlocks = 64;
+
 __global__ void __launch_bounds__(256)
 exchange_top2_kernel(const int32_t* __restrict__ l_idx, const int32_t* __restrict__ l_best,
                      const int32_t* __restrict__ l_second, int nq, int nq_max, int rank, int world, int parity,
                      unsigned target, ExPeers peers, int32_t* __restrict__ o_idx, int32_t* __restrict__ o_best,
                      int32_t* __restrict__ o_second) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int stride = gridDim.x * blockDim.x;
   const size_t slot = ((size_t)parity * world + rank) * 3 * (size_t)nq_max;
-  if (i < nq) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nq; i += stride) {
     const int32_t a = l_idx[i], b = l_best[i], c = l_second[i];
     for (int p = 0; p < world; ++p) {
       int32_t* dst = peers.buf[p] + slot;
@@ -59,17 +65,18 @@ exchange_top2_kernel(const int32_t* __restrict__ l_idx, const int32_t* __restric
     __threadfence_system();
   }
   __syncthreads();
-  if (i >= nq) return;
   const int32_t* g = peers.buf[rank] + (size_t)parity * world * 3 * (size_t)nq_max;
-  int b = 256, s = 256, id = -1;
-  for (int r = 0; r < world; ++r) {  // ranks hold ascending row ranges: same rule as merge_top2_kernel
-    const int32_t* e = g + (size_t)r * 3 * nq_max;
-    const int ik = __ldcg(e + i), bk = __ldcg(e + nq_max + i), sk = __ldcg(e + 2 * (size_t)nq_max + i);
-    if (ik < 0) continue;
-    if (bk < b) { s = min(b, sk); b = bk; id = ik; }
-    else s = min(s, bk);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nq; i += stride) {
+    int b = 256, s = 256, id = -1;
+    for (int r = 0; r < world; ++r) {  // ranks hold ascending row ranges: same rule as merge_top2_kernel
+      const int32_t* e = g + (size_t)r * 3 * nq_max;
+      const int ik = __ldcg(e + i), bk = __ldcg(e + nq_max + i), sk = __ldcg(e + 2 * (size_t)nq_max + i);
+      if (ik < 0) continue;
+      if (bk < b) { s = min(b, sk); b = bk; id = ik; }
+      else s = min(s, bk);
+    }
+    o_idx[i] = id; o_best[i] = b; o_second[i] = s;
   }
-  o_idx[i] = id; o_best[i] = b; o_second[i] = s;
 }
 
 }  // namespace orbgpu
@@ -176,7 +183,7 @@ int orb_gpu_exchange_top2_device(OrbGpuExchange* x, const int32_t* d_idx, const 
     return ORB_GPU_ERR_ARG;
   if (!x->connected) return ORB_GPU_ERR_STATE;
   ORB_CUDA_TRY(cudaSetDevice(x->device));
-  const int blocks = (nq + 255) / 256;
+  const int blocks = std::min((nq + 255) / 256, kExMaxBlocks);
   x->arrivals += (unsigned long long)blocks;  // every rank makes the same calls: the target is the same everywhere
   const int parity = (int)(x->calls++ & 1u);
   exchange_top2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_idx, d_best, d_second, nq, x->nq_max, x->rank, x->world,

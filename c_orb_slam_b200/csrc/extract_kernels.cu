@@ -467,13 +467,10 @@ static FastLayout fast_smem_layout(const Plan& p) {
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
   const FastLayout L = fast_smem_layout(p);
   const size_t smem = (size_t)kFastWarps * L.per_warp;
-  static size_t configured = 0;
   if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
-  if (smem > 48 * 1024 && smem > configured) {
-    ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
-    configured = smem;
-  }
+  // the opt-in belongs to the current device's context: set it on every launch rather than cache it process-wide
+  if (smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const dim3 grid((p.cells_per_frame + kFastWarps - 1) / kFastWarps, nframes);
   fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, L);
   count_launch();
@@ -968,15 +965,11 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
 }
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
-  static size_t configured = 0;
   size_t smem = 0;
   for (int l = 0; l < p.nlevels; ++l) smem = max(smem, quadtree_smem_bytes(p, l));
   if (smem > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
-  if (smem > 48 * 1024 && smem > configured) {
-    ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
-    configured = smem;
-  }
+  if (smem > 48 * 1024)  // per device, see launch_fast_cells
+    ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   quadtree_kernel<<<nframes * p.nlevels, kQtThreads, smem, s>>>(p, sc, nframes);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
@@ -1113,11 +1106,8 @@ int launch_blur(const Plan& p, int nframes, cudaStream_t s) {
   const int threads = (((p.lv[0].w + 3) >> 2) + 31) & ~31;
   if (threads > 1024) return ORB_GPU_ERR_CAPACITY;
   const size_t smem = (size_t)2 * kBlurBatch * (4 * threads + 8) * sizeof(uint16_t);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  if (smem > 48 * 1024)  // per device, see launch_fast_cells
     ORB_CUDA_TRY(cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
   blur_kernel<<<dim3(bands, nframes), threads, smem, s>>>(p, bands);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());

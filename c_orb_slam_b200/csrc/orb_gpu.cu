@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <map>
 #include <vector>
 
 #include "common.cuh"
@@ -109,7 +110,28 @@ struct OrbGpuExtractor {
   cudaGraphExec_t graph_exec = nullptr;
   int graph_nlaunch = 0;
   int plan_generation = 0;
+  // blur depends only on the pyramid: it runs on a side stream next to FAST + quadtree and joins before the
+  // descriptors (one side stream and two events per compute stream, created on first use)
+  struct Fork { cudaStream_t side = nullptr; cudaEvent_t forked = nullptr, joined = nullptr; };
+  std::map<cudaStream_t, Fork> forks;
 };
+
+static bool fork_enabled() {
+  static const bool on = [] { const char* e = getenv("ORB_GPU_NO_FORK"); return !(e && atoi(e)); }();
+  return on;
+}
+static int fork_for(OrbGpuExtractor* h, cudaStream_t s, OrbGpuExtractor::Fork** out) {
+  auto it = h->forks.find(s);
+  if (it == h->forks.end()) {
+    OrbGpuExtractor::Fork f;
+    ORB_CUDA_TRY(cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking));
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&f.forked, cudaEventDisableTiming));
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&f.joined, cudaEventDisableTiming));
+    it = h->forks.emplace(s, f).first;
+  }
+  *out = &it->second;
+  return ORB_GPU_OK;
+}
 
 // Frames per chunk of the host-pointer path.  Chunk c runs on compute stream c % 4, so the kernels of up to four
 // chunks interleave on the SMs: one chunk's launch gaps and partial last waves are filled by its neighbours.
@@ -354,11 +376,21 @@ static int run_pipeline(OrbGpuExtractor* h, const Plan& p, const Scratch& sc, in
   for (int l = 1; l < p.nlevels; ++l)
     if ((rc = launch_resize_level(p, l, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[1], s));
+  // per-stage timing needs the stages one after another on `s`; otherwise blur forks off here
+  OrbGpuExtractor::Fork* fk = nullptr;
+  if (!tm && fork_enabled()) {
+    if ((rc = fork_for(h, s, &fk))) return rc;
+    ORB_CUDA_TRY(cudaEventRecord(fk->forked, s));
+    ORB_CUDA_TRY(cudaStreamWaitEvent(fk->side, fk->forked, 0));
+    if ((rc = launch_blur(p, nframes, fk->side))) return rc;
+    ORB_CUDA_TRY(cudaEventRecord(fk->joined, fk->side));
+  }
   if ((rc = launch_fast_cells(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[2], s));
   if ((rc = launch_quadtree(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[3], s));
-  if ((rc = launch_blur(p, nframes, s))) return rc;
+  if (fk) ORB_CUDA_TRY(cudaStreamWaitEvent(s, fk->joined, 0));
+  else if ((rc = launch_blur(p, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[4], s));
   if ((rc = launch_orient_desc(p, sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[5], s));

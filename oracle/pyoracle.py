@@ -52,6 +52,24 @@ def ref_matcher():
     return _refm
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def matcher_library(path):
+    """Inside the block every refm_* call (impl="reference", ref_search_*, ref_fuse*) goes to the library at `path`
+    instead of the verbatim reference build.  tests/cpp/Makefile builds such a library from the same harness
+    (oracle/ref_matcher_wrapper.cc) around the PRODUCT's drop-in ORB_SLAM2::ORBmatcher class, so a test can hand the
+    same flat arrays to the reference's matcher and to the drop-in one."""
+    global _refm
+    keep = _refm
+    _refm = C.CDLL(path)
+    try:
+        yield _refm
+    finally:
+        _refm = keep
+
+
 def _m(impl, name):
     """Entry point `name` of the restated oracle (impl="oracle") or of the verbatim reference build
     (impl="reference"): both take the same flat arrays."""

@@ -8,11 +8,13 @@
 // level range).  Every GetFeaturesInArea call is recorded by the shim; refm_* return those windows as
 // orbo::WindowQuery records, which are then the INPUT of the oracle / GPU call that must reproduce the matches.
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <map>
 #include <memory>
 #include <set>
+#include <thread>
 #include <vector>
 
 #include "ORBmatcher.h"
@@ -24,6 +26,15 @@ float Frame::mnMinX = 0, Frame::mnMaxX = 0, Frame::mnMinY = 0, Frame::mnMaxY = 0
 float Frame::mfGridElementWidthInv = 0, Frame::mfGridElementHeightInv = 0;
 
 namespace {
+
+// seconds spent inside the matcher method of the last refm_* call on this thread (building the stand-in objects from
+// the flat arrays is outside): what bench.py reports as the CPU baseline of a matcher call
+thread_local double g_last_call_seconds = 0.0;
+struct CallTimer {
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  ~CallTimer() { g_last_call_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+};
+#define REFM_TIMED(expr) ([&] { CallTimer timer__; return (expr); }())
 
 struct Camera {  // fx, fy, cx, cy, mbf, mb, minX, minY, maxX, maxY, grid invW, invH
   float fx, fy, cx, cy, mbf, mb, minX, minY, maxX, maxY, invW, invH;
@@ -83,6 +94,7 @@ std::unique_ptr<KeyFrame> make_keyframe(const Camera& c, const orbo::KeyPoint* k
     for (int i = 0; i < nlevels; ++i) k->mvInvLevelSigma2[i] = 1.0f / level_sigma2[i];
   }
   k->grid.build(k->mvKeysUn, c.minX, c.minY, c.invW, c.invH);
+  k->mfGridElementWidthInv = c.invW; k->mfGridElementHeightInv = c.invH;
   return k;
 }
 void fill_featvec(DBoW2::FeatureVector& fv, const int32_t* node, const int32_t* start, const int32_t* idx, int nn) {
@@ -131,6 +143,41 @@ void windows_from_log(const std::map<const MapPoint*, int>& index, orbo::WindowQ
 
 extern "C" {
 
+double refm_last_call_seconds() { return g_last_call_seconds; }
+
+// Brute-force top-2 as config 5 of BASELINE.json defines it, around the matcher's own DescriptorDistance
+// (src/ORBmatcher.cc:1647-1663 in the verbatim build): for each query an ascending scan of the database with the
+// update rule of :216-225.  `threads` host threads split the queries.  The reference has no such loop of its own (it
+// relocalises through the BoW inverted file); this is the CPU baseline bench.py times next to the GPU kernel.
+int refm_bruteforce_top2(const uint8_t* q, int nq, const uint8_t* db, int ndb, int threads, int32_t* idx,
+                         int32_t* best, int32_t* second) {
+  auto header = [](const uint8_t* row) {
+    cv::Mat m;                       // a header over the caller's row, as cv::Mat::row() gives the reference
+    m.rows = 1; m.cols = 32; m.step = 32; m.data = const_cast<uint8_t*>(row);
+    return m;
+  };
+  std::vector<cv::Mat> rows((size_t)ndb);
+  for (int j = 0; j < ndb; ++j) rows[j] = header(db + (size_t)j * 32);
+  CallTimer timer;
+  auto work = [&](int lo, int hi) {
+    for (int i = lo; i < hi; ++i) {
+      const cv::Mat dq = header(q + (size_t)i * 32);
+      int bestDist1 = 256, bestIdx = -1, bestDist2 = 256;
+      for (int j = 0; j < ndb; ++j) {
+        const int dist = ORBmatcher::DescriptorDistance(dq, rows[j]);
+        if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx = j; }
+        else if (dist < bestDist2) { bestDist2 = dist; }
+      }
+      idx[i] = bestIdx; best[i] = bestDist1; second[i] = bestDist2;
+    }
+  };
+  threads = std::max(1, std::min(threads, nq));
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t) pool.emplace_back(work, (int)((long long)nq * t / threads), (int)((long long)nq * (t + 1) / threads));
+  for (auto& t : pool) t.join();
+  return 0;
+}
+
 int refm_descriptor_distance(const uint8_t* a, const uint8_t* b) {
   return ORBmatcher::DescriptorDistance(desc_mat(a, 1), desc_mat(b, 1));
 }
@@ -161,7 +208,7 @@ int refm_search_by_projection(const orbo::ProjQuery* q, const uint8_t* qdesc, in
     vp.push_back(p);
   }
   ORBmatcher matcher(nnratio, true);
-  const int n = matcher.SearchByProjection(F, vp, th);
+  const int n = REFM_TIMED(matcher.SearchByProjection(F, vp, th));
   for (int i = 0; i < nk; ++i) {
     match_of_kp[i] = index_of(pc.index, F.mvpMapPoints[i]);
     kp_blocked[i] = F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0;
@@ -185,7 +232,7 @@ int refm_search_by_bow_frame(const int32_t* node1, const int32_t* start1, const 
   fill_featvec(F.mFeatVec, node2, start2, idx2, nn2);
   std::vector<MapPoint*> matches;
   ORBmatcher matcher(nnratio, check_ori != 0);
-  const int n = matcher.SearchByBoW(kf.get(), F, matches);
+  const int n = REFM_TIMED(matcher.SearchByBoW(kf.get(), F, matches));
   for (int i = 0; i < n2; ++i) match_of_2[i] = index_of(pc.index, matches[i]);
   return n;
 }
@@ -206,7 +253,7 @@ int refm_search_by_bow_keyframes(const int32_t* node1, const int32_t* start1, co
   for (int i = 0; i < n2; ++i) if (good2[i]) kf2->mvpMapPoints[i] = pc2.add(i, nullptr, nullptr, nullptr, 1);
   std::vector<MapPoint*> matches;
   ORBmatcher matcher(nnratio, check_ori != 0);
-  const int n = matcher.SearchByBoW(kf1.get(), kf2.get(), matches);
+  const int n = REFM_TIMED(matcher.SearchByBoW(kf1.get(), kf2.get(), matches));
   for (int i = 0; i < n1; ++i) match12[i] = index_of(pc2.index, matches[i]);
   return n;
 }
@@ -237,7 +284,7 @@ int refm_search_for_triangulation(const int32_t* node1, const int32_t* start1, c
   kf2->Tcw = pose44(ident);
   std::vector<std::pair<size_t, size_t>> pairs;
   ORBmatcher matcher(0.6f, check_ori != 0);
-  const int n = matcher.SearchForTriangulation(kf1.get(), kf2.get(), float_mat(F12, 3, 3), pairs, only_stereo != 0);
+  const int n = REFM_TIMED(matcher.SearchForTriangulation(kf1.get(), kf2.get(), float_mat(F12, 3, 3), pairs, only_stereo != 0));
   for (int i = 0; i < n1; ++i) match12[i] = -1;
   for (const auto& p : pairs) match12[p.first] = (int32_t)p.second;
   return n;
@@ -256,7 +303,7 @@ int refm_search_for_initialization(const orbo::KeyPoint* kps1, const uint8_t* d1
   for (int i = 0; i < n1; ++i) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
   std::vector<int> m12;
   ORBmatcher matcher(nnratio, check_ori != 0);
-  const int n = matcher.SearchForInitialization(F1, F2, prev, m12, window);
+  const int n = REFM_TIMED(matcher.SearchForInitialization(F1, F2, prev, m12, window));
   for (int i = 0; i < n1; ++i) {
     match12[i] = m12[i];
     prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y;
@@ -301,7 +348,7 @@ int refm_search_last_frame(const float* cam12, const float* Tcw_cur, const float
   }
   ShimLog::get().calls.clear();
   ORBmatcher matcher(0.9f, check_ori != 0);
-  const int n = matcher.SearchByProjection(cur, last, th, mono != 0);
+  const int n = REFM_TIMED(matcher.SearchByProjection(cur, last, th, mono != 0));
   windows_from_log(pc.index, windows);
   // ur of :1409 for the stereo gate, from the same expressions on the same matrix stand-in
   const cv::Mat Rcw = cur.mTcw.rowRange(0, 3).colRange(0, 3);
@@ -378,7 +425,7 @@ int refm_search_keyframe_points(const float* cam12, const float* Tcw_cur, const 
   }
   reset_log();
   ORBmatcher matcher(0.9f, check_ori != 0);
-  const int nm = matcher.SearchByProjection(cur, kf.get(), found, th, orb_dist);
+  const int nm = REFM_TIMED(matcher.SearchByProjection(cur, kf.get(), found, th, orb_dist));
   windows_from_log(pc.index, windows);
   for (int i = 0; i < n_cur; ++i) match_of_kp[i] = index_of(pc.index, cur.mvpMapPoints[i]);
   return nm;
@@ -414,7 +461,7 @@ int refm_search_sim3_projection(const float* cam12, const float* Scw, const orbo
   for (int i = 0; i < n; ++i) windows[i].blocks = 1;
   reset_log();
   ORBmatcher matcher(0.75f, true);
-  const int nm = matcher.SearchByProjection(kf.get(), pose44(Scw), points, matched, th);
+  const int nm = REFM_TIMED(matcher.SearchByProjection(kf.get(), pose44(Scw), points, matched, th));
   windows_from_log(pc.index, windows);
   for (int i = 0; i < n; ++i)
     if (windows[i].valid) { windows[i].min_level = pred_level[i] - 1; windows[i].max_level = pred_level[i]; }  // :372-375
@@ -448,7 +495,7 @@ int refm_fuse(const float* cam12, const float* Tcw, const orbo::KeyPoint* kps_kf
   clear_windows(windows, n);
   reset_log();
   ORBmatcher matcher(0.6f, true);
-  const int nf = matcher.Fuse(kf.get(), points, th);
+  const int nf = REFM_TIMED(matcher.Fuse(kf.get(), points, th));
   windows_from_log(pc.index, windows);
   const cv::Mat Rcw = kf->GetRotation(), tcw = kf->GetTranslation();
   for (int i = 0; i < n; ++i) {
@@ -505,7 +552,7 @@ int refm_search_by_sim3(const float* cam12, const float* T1w, const float* T2w, 
   clear_windows(win21, n2);
   reset_log();
   ORBmatcher matcher(0.75f, true);
-  const int nf = matcher.SearchBySim3(kf1.get(), kf2.get(), m12, s12, float_mat(R12, 3, 3), float_mat(t12, 3, 1), th);
+  const int nf = REFM_TIMED(matcher.SearchBySim3(kf1.get(), kf2.get(), m12, s12, float_mat(R12, 3, 3), float_mat(t12, 3, 1), th));
   windows_from_log(pc1.index, win12);
   windows_from_log(pc2.index, win21);
   for (int i = 0; i < n1; ++i) if (win12[i].valid) { win12[i].min_level = lvl1[i] - 1; win12[i].max_level = lvl1[i]; }
@@ -538,7 +585,7 @@ int refm_fuse_sim3(const float* cam12, const float* Scw, const orbo::KeyPoint* k
   clear_windows(windows, n);
   reset_log();
   ORBmatcher matcher(0.8f, true);
-  const int nf = matcher.Fuse(kf.get(), pose44(Scw), points, th, repl);
+  const int nf = REFM_TIMED(matcher.Fuse(kf.get(), pose44(Scw), points, th, repl));
   windows_from_log(pc.index, windows);
   for (int i = 0; i < n; ++i) {
     match_of_query[i] = -1;

@@ -161,6 +161,7 @@ class KeyFrame {
   DBoW2::FeatureVector mFeatVec;
   std::vector<float> mvScaleFactors, mvLevelSigma2, mvInvLevelSigma2;
   const int mnMinX, mnMinY, mnMaxX, mnMaxY;
+  float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;  // include/KeyFrame.h:132-133 (read by the drop-in matcher)
   std::vector<MapPoint*> mvpMapPoints;
   cv::Mat Tcw, Ow;
   std::vector<std::pair<MapPoint*, size_t>> added;

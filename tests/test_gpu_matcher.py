@@ -16,10 +16,46 @@ def test_bruteforce_top2(gpu, oracle, nq, ndb, variant):
     idx, best, second = m.match_bruteforce(q, db)
     oi, ob, os_ = oracle.match_bruteforce(q, db, threads=8)
     assert np.array_equal(best, ob) and np.array_equal(second, os_) and np.array_equal(idx, oi)
-    acc = m.accept(best, second, th=m.TH_HIGH)
+    gpu.lib().orb_gpu_set_bruteforce_variant(3, 2)   # back to the default (tcgen05 form)
+    # the accept flags come from the device kernel (orb_gpu_ratio_test_device), checked against the float rule
+    acc = m.accept_device(best, second, th=m.TH_HIGH)
     ref = (ob <= 100) & (ob.astype(np.float32) < np.float32(0.9) * os_.astype(np.float32))
     assert np.array_equal(acc, ref)
-    gpu.lib().orb_gpu_set_bruteforce_variant(3, 2)   # back to the default (tcgen05 form)
+
+
+def test_hamming_pairs_device_equals_descriptor_distance(gpu, oracle):
+    """M1: orb_gpu_hamming_pairs_device against the reference's own ORBmatcher::DescriptorDistance
+    (src/ORBmatcher.cc:1647-1663, verbatim build) on 10^5 random pairs plus the all-0 / all-1 extremes."""
+    import torch
+    rng = np.random.default_rng(77)
+    n = 100000
+    a = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    b = synth.flip_bits(a, rng.integers(0, 257, n), rng)
+    b[n // 2:] = rng.integers(0, 256, (n - n // 2, 32), dtype=np.uint8)
+    a[0] = 0; b[0] = 0; a[1] = 0; b[1] = 255; a[2] = 255; b[2] = 255; a[3] = 255; b[3] = 0
+    da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert gpu.lib().orb_gpu_hamming_pairs_device(da.data_ptr(), db.data_ptr(), n, out.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    want = np.unpackbits(a ^ b, axis=1).sum(1).astype(np.int32)
+    assert np.array_equal(got, want) and got[1] == 256 and got[3] == 256 and got[0] == 0
+    impl = "reference" if oracle.have_ref_matcher() else "oracle"
+    for i in list(range(8)) + rng.integers(0, n, 2000).tolist():
+        assert oracle.descriptor_distance(a[i], b[i], impl=impl) == got[i]
+    assert gpu.lib().orb_gpu_hamming_pairs_device(da.data_ptr(), db.data_ptr(), 0, out.data_ptr(), st) == 0  # empty
+
+
+@pytest.mark.parametrize("nnratio", [0.6, 0.75, 0.9])
+@pytest.mark.parametrize("th", [50, 100])
+def test_ratio_test_device_all_pairs(gpu, nnratio, th):
+    """orb_gpu_ratio_test_device on all 257 x 257 (best, second) pairs against the float rule of
+    src/ORBmatcher.cc:228-230: best <= th && (float)best < mfNNratio * (float)second."""
+    best, second = [x.ravel().astype(np.int32) for x in np.meshgrid(np.arange(257), np.arange(257), indexing="ij")]
+    acc = gpu.ORBmatcher(nnratio).accept_device(best, second, th=th)
+    want = (best <= th) & (best.astype(np.float32) < np.float32(nnratio) * second.astype(np.float32))
+    assert np.array_equal(acc, want) and want.sum() > 1000
 
 
 @pytest.mark.parametrize("variant", [(2, 2), (3, 2)])
@@ -290,6 +326,55 @@ def test_features_in_area_order(gpu, oracle):
         assert np.array_equal(got[i], want), i
         total += len(want)
     assert total > 5000 and any(len(g) == 0 for g in got)
+
+
+def test_peer_memory_exchange_many_queries(gpu):
+    """65536 queries per call: more query blocks than could ever be resident next to each other with one block per
+    256 queries -- the exchange kernel caps its grid and strides (every block waits for all blocks of all ranks)."""
+    import ctypes as C
+    import torch
+    L = gpu.lib()
+    nq, world = 65536, 2
+    hs = (C.c_void_p * world)()
+    for r in range(world):
+        h = C.c_void_p()
+        assert L.orb_gpu_exchange_create(0, r, world, nq, C.byref(h)) == 0
+        hs[r] = h
+    assert L.orb_gpu_exchange_connect_local(hs, world) == 0
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    rng = np.random.default_rng(3)
+    try:
+        for call in range(3):
+            n = nq - 777 * call
+            parts = []
+            for r in range(world):
+                best = rng.integers(0, 120, n).astype(np.int32)
+                second = (best + rng.integers(0, 40, n)).astype(np.int32)
+                idx = (r * 1000000 + rng.integers(0, 1000000, n)).astype(np.int32)
+                none = rng.random(n) < 0.01
+                idx[none] = -1; best[none] = 256; second[none] = 256
+                parts.append(np.stack([idx, best, second]))
+            b0, b1 = parts[0][1], parts[1][1]
+            first = b0 <= b1                       # rank 0 holds the lower rows: it wins ties
+            want = np.where(first, parts[0], parts[1])
+            want[2] = np.where(first, np.minimum(parts[0][2], b1), np.minimum(parts[1][2], b0))
+            outs = []
+            dparts = [torch.from_numpy(p).cuda() for p in parts]
+            torch.cuda.synchronize()
+            for r in range(world):
+                out = torch.empty((3, n), dtype=torch.int32, device="cuda")
+                p = dparts[r]
+                assert L.orb_gpu_exchange_top2_device(hs[r], p[0].data_ptr(), p[1].data_ptr(), p[2].data_ptr(), n,
+                                                      out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                                                      streams[r].cuda_stream) == 0
+                outs.append(out)
+            torch.cuda.synchronize()
+            for out in outs:
+                assert np.array_equal(out.cpu().numpy(), want)
+    finally:
+        torch.cuda.synchronize()
+        for r in range(world):
+            L.orb_gpu_exchange_destroy(hs[r])
 
 
 def test_peer_memory_exchange_two_ranks_on_one_gpu(gpu, oracle):
