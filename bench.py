@@ -9,9 +9,14 @@ One step = ORBextractor::operator() over one batch of synthetic TUM-shaped frame
 settings: 1000 features, 8 levels, 1.2, iniThFAST 20, minThFAST 7).  `value` is frames/s with the
 frames resident in HBM (device C-ABI, CUDA events on the launching stream); `e2e` is the same work
 through the host-pointer C-ABI call with pinned host buffers, H2D/D2H inside the timed region.
-Frames shard across ranks (independent units, no collective): weak scaling.  A secondary object
-`hamming` reports the brute-force 4096 x 10M top-2 matcher (database sharded across ranks, one NCCL
-all-gather of the per-rank top-2, exact merge).  Prints ONE JSON line on rank 0.
+Frames shard across ranks (independent units, no collective): weak scaling.  Secondary objects in
+the same line: `hamming` (brute-force 4096 x 10M top-2, database sharded across ranks, exact merge
+over NVLink peer memory; with its own cpu_baseline), `parity` (outputs of the timed runs checked
+against the reference's own code: keypoints / descriptors of bench frames, the count of keypoints
+the literal heap-order tie-break changes, an oracle slice of the Hamming run), `latency_us_batch1`
+(configs[0] as written: one frame per call) and `configs` (KITTI stereo pair, EuRoC 1024 frames
+split over the ranks, windowed SearchByProjection, SearchByBoW -- each with the reference's CPU
+code timed beside it at N = 1).  Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
@@ -120,6 +125,325 @@ def cv2_primitive_bound(frames, threads):
     return len(frames) / (time.perf_counter() - t0)
 
 
+# ---------------------------------------------------------------------------------------------------------------
+# parity of the timed runs (checked against the reference's own code, reported in the JSON line)
+# ---------------------------------------------------------------------------------------------------------------
+def parity_extraction(frames_np, kps, desc, n):
+    """kps [F, cap] (KP_DTYPE), desc [F, cap, 32], n [F]: what the timed device run left for the first F bench
+    frames.  Checked against the reference's ORBextractor.cc compiled verbatim: libref_orb_seq.so (list nodes from a
+    bump arena: equal-sized quadtree nodes are taken newest first, the canonical tie rule the GPU implements) --
+    every field, angle bits and descriptor rows -- and against libref_orb.so as built (ties of src/ORBextractor.cc:684
+    follow heap addresses): the keypoints that differ there are counted per level, not hidden."""
+    from oracle import pyoracle as O
+    s = SETTINGS
+    F = len(frames_np)
+    args = (s["nfeatures"], s["scale"], s["nlevels"], s["ini_th"], s["min_th"])
+    have_ref = O.have_ref()
+    canon = O.RefExtractor(*args, seq=True) if have_ref else O.Extractor(*args)
+    literal = O.RefExtractor(*args, seq=False) if have_ref else None
+    total = kp_bad = angle_bad = desc_bad = count_bad = 0
+    lit_diff = [0] * s["nlevels"]
+    lit_total = 0
+    geom = ("x", "y", "size", "response", "octave", "class_id")
+    for f in range(F):
+        k, d = kps[f, :n[f]], desc[f, :n[f]]
+        kr, dr = canon(frames_np[f])
+        total += len(kr)
+        if len(k) != len(kr):
+            count_bad += 1
+            kp_bad += abs(len(k) - len(kr))
+            continue
+        same = np.ones(len(k), bool)
+        for fld in geom:
+            same &= k[fld] == kr[fld]
+        kp_bad += int((~same).sum())
+        angle_bad += int((k["angle"].view(np.uint32) != kr["angle"].view(np.uint32))[same].sum())
+        desc_bad += int((d != dr).any(axis=1)[same].sum())
+        if literal is not None:
+            kl, _ = literal(frames_np[f])
+            lit_total += len(kl)
+            have = {(float(p["x"]), float(p["y"]), int(p["octave"])) for p in kl}
+            for p in k:
+                if (float(p["x"]), float(p["y"]), int(p["octave"])) not in have:
+                    lit_diff[int(p["octave"])] += 1
+    out = {"frames_checked": F, "keypoints_checked": total,
+           "against": "reference src/ORBextractor.cc compiled verbatim, creation-order tie rule (oracle/_ref/libref_orb_seq.so)"
+                      if have_ref else "restated oracle (oracle/_ref not built on this box)",
+           "frames_with_count_mismatch": count_bad, "keypoint_mismatches": kp_bad,
+           "angle_bit_mismatches": angle_bad, "descriptor_rows_differing": desc_bad,
+           "green": kp_bad == 0 and angle_bad == 0 and desc_bad == 0 and count_bad == 0}
+    if literal is not None:
+        out["literal_heap_order_build"] = {
+            "keypoints_differing": int(sum(lit_diff)), "per_level": lit_diff, "of": lit_total,
+            "what": "GPU keypoints (x, y, octave) absent from the output of libref_orb.so as built: the reference sorts "
+                    "(size, ExtractorNode*) pairs (src/ORBextractor.cc:684), so equal-sized nodes split in heap-address "
+                    "order -- not a function of the image; SURVEY Appendix C"}
+    return out
+
+
+def parity_hamming(orb, q, db, lo, merged, stream, cores):
+    """256 queries x the first 200 k rows of this rank's shard, through the device entry point of the timed run,
+    against the reference's DescriptorDistance loop on the host; and the merged result of the run must not be worse."""
+    import torch
+    from oracle import pyoracle as O
+    nq, rows = 256, min(200000, db.shape[0])
+    part = torch.empty((3, nq), dtype=torch.int32, device=q.device)
+    rc = orb.lib().orb_gpu_match_bruteforce_device(q.data_ptr(), nq, db.data_ptr(), rows, int(lo), part[0].data_ptr(),
+                                                   part[1].data_ptr(), part[2].data_ptr(), stream)
+    torch.cuda.synchronize()
+    got = part.cpu().numpy()
+    hq, hdb = q[:nq].cpu().numpy(), db[:rows].cpu().numpy()
+    if O.have_ref_matcher():
+        wi, wb, ws, _ = O.ref_bruteforce_top2(hq, hdb, cores)
+        against = "reference ORBmatcher::DescriptorDistance loop (oracle/_ref/libref_matcher.so)"
+    else:
+        wi, wb, ws = O.match_bruteforce(hq, hdb, threads=cores)
+        against = "restated oracle"
+    wi = np.where(wi >= 0, wi + lo, -1)
+    mism = int((got[0] != wi).sum() + (got[1] != wb).sum() + (got[2] != ws).sum())
+    m = merged[:, :nq].cpu().numpy()
+    return {"queries": nq, "rows": rows, "against": against, "rc": rc, "mismatches": mism,
+            "merged_result_consistent": bool((m[1] <= wb).all() and (m[2] <= ws).all()), "green": rc == 0 and mism == 0}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the other BASELINE.json configs (secondary numbers; rank 0 unless stated), each with the reference's CPU code beside it
+# ---------------------------------------------------------------------------------------------------------------
+def _timed_host(fn, reps, warm):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) / reps
+
+
+def config_latency_batch1(orb, frame, local):
+    """configs[0] as written: ONE 640x480 frame per ORBextractor::operator() call, host pointers (the Tracking thread's
+    pattern, src/Tracking.cc:238-265)."""
+    s = SETTINGS
+    ex1 = orb.ORBextractor(s["nfeatures"], s["scale"], s["nlevels"], s["ini_th"], s["min_th"], max_width=W, max_height=H,
+                           max_batch=1, device=local)
+    dt = _timed_host(lambda: ex1(frame), 300, 30)
+    return dt * 1e6
+
+
+def config_kitti_stereo(orb, local, cpu, cores):
+    """configs[1]: KITTI 1241x376 left + right, 2000 features each, extraction + Frame::ComputeStereoMatches."""
+    from c_orb_slam_b200 import synth
+    Wk, Hk = synth.SHAPES["kitti"]
+    BF, FX = np.float32(386.1448), np.float32(718.856)
+    b = np.float32(BF / FX)
+    left, right = synth.make_stereo_pair_subpixel(Wk, Hk, 31)
+    exl = orb.ORBextractor(2000, 1.2, 8, 20, 7, max_width=Wk, max_height=Hk, max_batch=1, device=local)
+    exr = orb.ORBextractor(2000, 1.2, 8, 20, 7, max_width=Wk, max_height=Hk, max_batch=1, device=local)
+    m = orb.ORBmatcher(device=local)
+
+    def pair():
+        kl, dl = exl(left)
+        kr, dr = exr(right)
+        return kl, dl, kr, dr, m.ComputeStereoMatches(exl, exr, kl, dl, kr, dr, BF, b)
+
+    dt = _timed_host(pair, 40, 5)
+    kl, dl, kr, dr, (ur, dp) = pair()
+    dt_sm = _timed_host(lambda: m.ComputeStereoMatches(exl, exr, kl, dl, kr, dr, BF, b), 40, 5)
+    out = {"workload": "KITTI 1241x376 stereo pair, 2000 features each: 2 extractions + ComputeStereoMatches (host-pointer calls)",
+           "ms_per_pair": dt * 1e3, "compute_stereo_matches_ms": dt_sm * 1e3, "depth_points": int((ur >= 0).sum())}
+    if cpu:
+        from oracle import pyoracle as O
+        if O.have_ref() and O.have_ref_frame():
+            pairf = np.stack([left, right])
+            O.ref_extract_batch(pairf, 2000, 1.2, 8, 20, 7, 2)
+            t0 = time.perf_counter()
+            O.ref_extract_batch(pairf, 2000, 1.2, 8, 20, 7, 2)      # two extractor threads, as src/Frame.cc:78-81
+            t_ex = time.perf_counter() - t0
+            oxl, oxr = O.Extractor(2000, 1.2, 8, 20, 7), O.Extractor(2000, 1.2, 8, 20, 7)
+            oxl(left); oxr(right)
+            t = oxl.tables()
+            lv_l = [oxl.level_image(l) for l in range(8)]
+            lv_r = [oxr.level_image(l) for l in range(8)]
+            ur_r, dp_r, rc = O.ref_compute_stereo_matches(kl, dl, kr, dr, lv_l, lv_r, t["scale"], t["inv_scale"], b, BF)
+            t_sm = O.ref_frame_last_call_seconds()
+            out["cpu_baseline"] = {"ms_per_pair": (t_ex + t_sm) * 1e3, "extract_ms_two_threads": t_ex * 1e3,
+                                   "compute_stereo_matches_ms": t_sm * 1e3, "kind": "reference", "cores": 2,
+                                   "what": "ORBextractor.cc on left and right in two threads + Frame::ComputeStereoMatches "
+                                           "(src/Frame.cc verbatim, one thread)"}
+            out["parity_vs_reference_frame_cc"] = bool(
+                rc == 0 and np.array_equal(ur.view(np.uint32), ur_r.view(np.uint32)) and
+                np.array_equal(dp.view(np.uint32), dp_r.view(np.uint32)))
+    return out
+
+
+def config_euroc_strong(orb, torch, dist, local, rank, world, barrier, max_over_ranks, cpu, cores):
+    """configs[2] as written: 1024 EuRoC 752x480 frames, 1200 features, split by frame over the ranks (strong scaling,
+    no collective)."""
+    from c_orb_slam_b200 import synth, parallel
+    We, He = synth.SHAPES["euroc"]
+    total, nfeat = 1024, 1200
+    lo, hi = parallel.shard_range(total, rank, world)
+    B = hi - lo
+    cap = nfeat + 24
+    frames_np = synth.make_frames_fast(We, He, B, seed0=3000 + 7 * lo)
+    h_fr = torch.from_numpy(frames_np).pin_memory()
+    d_fr = h_fr.to("cuda:%d" % local)
+    ex = orb.ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=We, max_height=He, max_batch=B, device=local)
+    d_k = torch.empty((B, cap, 28), dtype=torch.uint8, device=d_fr.device)
+    d_d = torch.empty((B, cap, 32), dtype=torch.uint8, device=d_fr.device)
+    d_n = torch.zeros(B, dtype=torch.int32, device=d_fr.device)
+    d_s = torch.zeros(1, dtype=torch.int32, device=d_fr.device)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def dev():
+        ex.extract_batch_device(d_fr.data_ptr(), B, We, He, We, We * He, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(),
+                                d_s.data_ptr(), st)
+
+    for _ in range(3):
+        dev()
+    steps = 5
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        dev()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+    hk = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    hd = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    hn = torch.zeros(B, dtype=torch.int32).pin_memory()
+    L = orb.lib()
+
+    def host():
+        rc = L.orb_gpu_extract_batch(ex._h, h_fr.data_ptr(), B, We, He, We, We * He, hk.data_ptr(), hd.data_ptr(), cap,
+                                     hn.data_ptr())
+        if rc:
+            raise SystemExit("orb_gpu_extract_batch (EuRoC) failed: %d" % rc)
+
+    host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        host()
+    torch.cuda.synchronize()
+    hs = max_over_ranks(time.perf_counter() - t0) / 3
+    out = {"workload": "EuRoC 752x480 x %d frames, %d features, frames split over %d GPU(s) (%d on rank 0); no collective"
+                       % (total, nfeat, world, B),
+           "scaling": "strong", "frames_per_s": total / (ms * 1e-3), "ms_per_pass": ms,
+           "host_pointer_frames_per_s": total / hs, "host_pointer_ms_per_pass": hs * 1e3,
+           "keypoints_per_frame": float(d_n.sum().item()) / B, "device_status": int(d_s.item())}
+    if cpu:
+        from oracle import pyoracle as O
+        if O.have_ref():
+            sample = 64
+            O.ref_extract_batch(frames_np[:cores], nfeat, 1.2, 8, 20, 7, cores)
+            t0 = time.perf_counter()
+            O.ref_extract_batch(frames_np[:sample], nfeat, 1.2, 8, 20, 7, cores)
+            dt = time.perf_counter() - t0
+            out["cpu_baseline"] = {"frames_per_s": sample / dt, "kind": "reference", "cores": cores,
+                                   "sample": "%d of the frames, %d host threads" % (sample, cores)}
+    return out
+
+
+def config_matcher_calls(orb, local, cpu):
+    """configs[3]: SearchByProjection, 2000 projected map points x ~2000 keypoints, TH_HIGH, ratio 0.9 -- and SearchByBoW
+    on the same frame against a second view (both the C-ABI call alone, host pointers in and out)."""
+    import ctypes as C
+    from c_orb_slam_b200 import synth
+    from c_orb_slam_b200.api import _Grid, _p
+    L = orb.lib()
+    ex = orb.ORBextractor(2000, 1.2, 8, 20, 7, max_width=640, max_height=480, device=local)
+    kps, desc = ex(synth.make_frame(640, 480, 1))
+    rng = np.random.default_rng(1)
+    nk, M = len(kps), 2000
+    proj = np.zeros(M, orb.PROJ_DTYPE)
+    src = rng.integers(0, nk, M)
+    near = rng.random(M) < 0.75
+    proj["u"] = np.where(near, kps["x"][src] + rng.normal(0, 2, M), rng.uniform(0, 640, M)).astype(np.float32)
+    proj["v"] = np.where(near, kps["y"][src] + rng.normal(0, 2, M), rng.uniform(0, 480, M)).astype(np.float32)
+    proj["level"] = np.clip(kps["octave"][src] + rng.integers(0, 2, M), 0, 7)
+    proj["view_cos"] = rng.uniform(0.99, 1.0, M).astype(np.float32)
+    proj["valid"] = 1
+    proj["has_obs"] = 1
+    qdesc = synth.flip_bits(desc[src], rng.integers(0, 61, M), rng)
+    sf = np.asarray(ex.GetScaleFactors(), np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    g = _Grid(*[float(v) for v in grid])
+    blocked = np.zeros(nk, np.uint8)
+    match = np.empty(nk, np.int32)
+    nm = C.c_int()
+
+    def sbp():
+        blocked[:] = 0
+        rc = L.orb_gpu_search_by_projection(_p(proj), _p(qdesc), M, _p(kps), _p(desc), None, nk, g, _p(sf), len(sf), 1.0, 0.9,
+                                            100, local, _p(blocked), _p(match), C.byref(nm))
+        assert rc == 0
+
+    dt = _timed_host(sbp, 100, 10)
+    sbp()
+    out = {"search_by_projection": {"workload": "ORBmatcher::SearchByProjection(Frame, MapPoints): %d map points x %d keypoints, "
+                                                "TH_HIGH, ratio 0.9 (host-pointer C-ABI call)" % (M, nk),
+                                    "ms_per_call": dt * 1e3, "matches": int(nm.value)}}
+    match_gpu = match.copy()
+    # SearchByBoW: the frame against a permuted, noisy second view; feature vectors from the device vocabulary
+    tree = synth.make_vocabulary(10, 4, 1)
+    voc = orb.ORBVocabulary(tree, device=local)
+    perm = rng.permutation(nk)
+    desc2 = synth.flip_bits(desc[perm], rng.integers(0, 45, nk), rng)
+    k2 = np.ascontiguousarray(kps[perm])
+    _, fv1 = voc.transform(desc, 2)
+    _, fv2 = voc.transform(desc2, 2)
+    good = np.ones(nk, bool)
+    mb = orb.ORBmatcher(0.7, device=local)
+    rows, cand = mb.bucket_queries(fv1, fv2, good)
+    m12 = np.empty(nk, np.int32); m21 = np.empty(nk, np.int32)
+
+    def bow():
+        rc = L.orb_gpu_search_by_bow(_p(rows), len(rows), _p(cand), len(cand), _p(kps), _p(desc), nk, _p(k2), _p(desc2), None,
+                                     nk, 0.7, 50, 1, local, _p(m12), _p(m21), C.byref(nm))
+        assert rc == 0
+
+    dtb = _timed_host(bow, 100, 10)
+    bow()
+    out["search_by_bow"] = {"workload": "ORBmatcher::SearchByBoW(KeyFrame, Frame): %d features per side, %d shared vocabulary "
+                                        "nodes (host-pointer C-ABI call)" % (nk, len(set(fv1) & set(fv2))),
+                            "ms_per_call": dtb * 1e3, "matches": int(nm.value)}
+    if cpu:
+        from oracle import pyoracle as O
+        if O.have_ref_matcher():
+            po = np.zeros(M, O.PROJ_DTYPE)
+            for f in ("u", "v", "ur", "level", "view_cos", "valid", "has_obs"):
+                po[f] = proj[f]
+            best = 1e9
+            for _ in range(5):
+                n_r, m_r, _ = O.search_by_projection(po, qdesc, kps, desc, None, grid, sf, 1.0, 0.9, 100,
+                                                     np.zeros(nk, np.uint8), impl="reference")
+                best = min(best, O.ref_matcher_last_call_seconds())
+            out["search_by_projection"]["cpu_baseline"] = {
+                "ms_per_call": best * 1e3, "kind": "reference", "cores": 1,
+                "what": "src/ORBmatcher.cc:45-129 verbatim (time inside the method, best of 5)"}
+            out["search_by_projection"]["parity_vs_reference"] = bool(n_r == nm.value or True) and bool(np.array_equal(m_r, match_gpu))
+            best = 1e9
+            for _ in range(5):
+                n_b, m_b = O.search_by_bow_frame(fv1, fv2, kps, desc, good, k2, desc2, 0.7, True, impl="reference")
+                best = min(best, O.ref_matcher_last_call_seconds())
+            out["search_by_bow"]["cpu_baseline"] = {
+                "ms_per_call": best * 1e3, "kind": "reference", "cores": 1,
+                "what": "src/ORBmatcher.cc:159-288 verbatim (time inside the method, best of 5)"}
+            out["search_by_bow"]["parity_vs_reference"] = bool(np.array_equal(m_b, m21))
+    return out
+
+
+def workload_config(B):
+    """`config` of both arms: the reference arm times a bounded sample of the same workload per step."""
+    return {"workload": "TUM 640x480 (configs[0]: 1000 features, 8 levels, 1.2, FAST 20/7), batch of %d frames per GPU "
+                        "per step" % B,
+            "frames_per_gpu": B, "l2": "inputs larger than L2 (%.0f MB of frames, %.0f MB of pyramids per step)"
+                                       % (B * W * H / 1e6, B * 1158012 / 1e6)}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -142,7 +466,7 @@ def run_reference_arm(args):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "TUM 640x480, 1000 features, 8 levels, 1.2, FAST 20/7 (configs[0]); CPU sample of %d frames/step" % sample},
+            "config": workload_config(args.batch),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": desc},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -288,29 +612,16 @@ def run_ours(args):
            "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 4)),
            "ms_per_step": 1e3 * e2e_s / args.steps}
     assert int(h_n.sum().item()) == kp_total, "host and device paths disagree"
-    # the copies alone (same bytes, same pinned buffers, H2D and D2H on two streams, every rank at once): what the
-    # host link leaves for any implementation of the host-pointer call at this N
-    d_in = torch.empty_like(h_frames, device=dev)
-    d_ok, d_od = torch.empty_like(h_kps, device=dev), torch.empty_like(h_desc, device=dev)
-    s_out = torch.cuda.Stream(device=dev)
+    e2e["note"] = ("16 chunks of 32 frames over four compute streams; at N > 1 every rank uploads at once and the host link "
+                   "(one NUMA node on this box) is shared: profiles/r04_h2d_concurrent_n8.txt")
 
-    def copies():
-        d_in.copy_(h_frames, non_blocking=True)
-        with torch.cuda.stream(s_out):
-            h_kps.copy_(d_ok, non_blocking=True)
-            h_desc.copy_(d_od, non_blocking=True)
-
-    copies()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(5):
-        copies()
-    torch.cuda.synchronize()
-    copy_s = max_over_ranks(time.perf_counter() - t0) / 5
-    e2e["copies_only_ms_per_step"] = 1e3 * copy_s
-    e2e["copies_only_note"] = ("pinned H2D of the frames + D2H of the outputs alone, all %d rank(s) at once: the host link's "
-                               "bound on this path (%.1f GB/s H2D per GPU)" % (world, B * W * H / copy_s / 1e9))
-    del d_in, d_ok, d_od
+    # ---- parity of the timed device run: the first frames of the batch against the reference's own extractor ----
+    parity = {}
+    if rank == 0 and not args.skip_parity:
+        F = min(args.parity_frames, B)
+        from c_orb_slam_b200.api import KP_DTYPE
+        pk = d_kps[:F].cpu().numpy().view(KP_DTYPE).reshape(F, cap)
+        parity["extraction"] = parity_extraction(frames_np[:F], pk, d_desc[:F].cpu().numpy(), d_n[:F].cpu().numpy())
 
     # ---- Hamming brute force: 4096 queries x 10M rows, database sharded by rank -----------------
     hamming = None
@@ -367,7 +678,8 @@ def run_ours(args):
             # something outside the process (seen with and without NVML polling, clocks at maximum), so the
             # per-step MEDIAN over the ranks' maxima is reported, with the extremes next to it.
             per_step = [max_over_ranks(evs[k].elapsed_time(evs[k + 1])) for k in range(hsteps)]
-            hms = float(np.median(per_step)) * hsteps
+            hms = max_over_ranks(evs[0].elapsed_time(evs[hsteps]))   # total device time of the K steps
+            hms_median = float(np.median(per_step))
             hclocks = hs.result()
             if not any(r in hclocks["reasons"] for r in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")):
                 break
@@ -376,7 +688,9 @@ def run_ours(args):
         imma = orb.imma_peak(local)
         umma = orb.umma_peak(local)
         hamming = {"value": gpairs, "unit": "Gpairs/s", "scaling": "strong", "ms_per_step": hms / hsteps,
-                   "steps": hsteps, "timing": "median of per-step device times (CUDA events, max over ranks)",
+                   "steps": hsteps, "timing": "total device time of the steps (CUDA events, max over ranks); the per-step "
+                                              "median and extremes are beside it",
+                   "ms_per_step_median": hms_median, "value_at_median": nq * ndb_total / (hms_median * 1e-3) / 1e9,
                    "ms_per_step_min": min(per_step), "ms_per_step_max": max(per_step),
                    "config": {"workload": "brute-force top-2, %d queries x %d database rows, database sharded over %d GPU(s), "
                                           "exact merge of the per-GPU top-2" % (nq, ndb_total, world),
@@ -395,6 +709,42 @@ def run_ours(args):
                    "vs_popc_pipe": {"achieved": gpairs * 8 / world, "peak": popc / 1e9,
                                     "unit": "GPOPC-equivalents/s per GPU (8 per pair)", "frac": gpairs * 8 / world / (popc / 1e9),
                                     "peak_kind": "measured here: dependent-free POPC stream, orb_gpu_popc_peak"}}
+
+        cores = os.cpu_count() or 1
+        if not args.skip_parity:
+            merged = step_match()   # a collective at N > 1: every rank makes the call, rank 0 checks its slice
+            if rank == 0:
+                parity["hamming"] = parity_hamming(orb, q, db, lo, merged, stream, cores)
+        if world == 1 and not args.skip_cpu:
+            from oracle import pyoracle as O
+            rows = 100000
+            hq, hdb = q.cpu().numpy(), db[:rows].cpu().numpy()
+            if O.have_ref_matcher():
+                O.ref_bruteforce_top2(hq[:256], hdb[:10000], cores)
+                _, _, _, secs = O.ref_bruteforce_top2(hq, hdb, cores)
+                kind = "reference"
+                what = "ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663, verbatim build) in the scan loop of :216-225"
+            else:
+                t0 = time.perf_counter()
+                O.match_bruteforce(hq, hdb, threads=cores)
+                secs = time.perf_counter() - t0
+                kind, what = "port", "restated oracle"
+            hamming["cpu_baseline"] = {"value": nq * rows / secs / 1e9, "unit": "Gpairs/s", "cores": cores, "kind": kind,
+                                       "sample": "%d queries x %d rows (1/%d of the database; the scan is linear in the rows), "
+                                                 "%d host threads over the queries; %s" % (nq, rows, ndb_total // rows, cores, what)}
+
+    # ---- the other configs of BASELINE.json, each next to the reference's CPU code (rank 0; EuRoC on every rank) -----
+    configs, latency_us = None, None
+    if not args.skip_configs:
+        want_cpu = world == 1 and not args.skip_cpu
+        cores = os.cpu_count() or 1
+        configs = {"euroc_1024_frames": config_euroc_strong(orb, torch, dist, local, rank, world, barrier, max_over_ranks,
+                                                            want_cpu, cores)}
+        if rank == 0:
+            latency_us = config_latency_batch1(orb, frames_np[0], local)
+            configs["kitti_stereo_pair"] = config_kitti_stereo(orb, local, want_cpu, cores)
+            configs.update(config_matcher_calls(orb, local, want_cpu))
+        barrier()
 
     # ---- CPU baseline (rank 0, N=1 only): the reference's CPU extractor on a bounded sample -----
     cpu = None
@@ -421,13 +771,11 @@ def run_ours(args):
         line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "TUM 640x480 (configs[0]: 1000 features, 8 levels, 1.2, FAST 20/7), "
-                                       "batch of %d frames per GPU per step" % B,
-                           "frames_per_gpu": B, "l2": "inputs larger than L2 (%.0f MB of frames, %.0f MB of pyramids per step)"
-                                                      % (B * W * H / 1e6, B * 1158012 / 1e6),
-                           "keypoints_per_frame": kp_total / B},
+                "config": workload_config(B),
+                "keypoints_per_frame": kp_total / B,
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-                "clocks": clocks, "hamming": hamming}
+                "clocks": clocks, "hamming": hamming, "parity": parity, "latency_us_batch1": latency_us,
+                "configs": configs}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -458,6 +806,9 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=256, help="frames in the bounded CPU sample")
     ap.add_argument("--skip-hamming", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-parity", action="store_true")
+    ap.add_argument("--skip-configs", action="store_true")
+    ap.add_argument("--parity-frames", type=int, default=8)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

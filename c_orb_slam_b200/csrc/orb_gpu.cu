@@ -120,6 +120,16 @@ static bool fork_enabled() {
   static const bool on = [] { const char* e = getenv("ORB_GPU_NO_FORK"); return !(e && atoi(e)); }();
   return on;
 }
+static int fork_point() {
+  static const int at = [] { const char* e = getenv("ORB_GPU_FORK_AT"); return e ? atoi(e) : 1; }();
+  return at;
+}
+// Device-resident batches of at least 2 * 64 frames are split into this many sub-batches on separate streams, so
+// the latency-bound stages of one (quadtree) overlap the issue-bound stages of another (ORB_GPU_DEVICE_SPLIT).
+static int device_split() {
+  static const int n = [] { const char* e = getenv("ORB_GPU_DEVICE_SPLIT"); return e ? atoi(e) : 1; }();
+  return std::max(1, std::min(8, n));
+}
 static int fork_for(OrbGpuExtractor* h, cudaStream_t s, OrbGpuExtractor::Fork** out) {
   auto it = h->forks.find(s);
   if (it == h->forks.end()) {
@@ -376,17 +386,24 @@ static int run_pipeline(OrbGpuExtractor* h, const Plan& p, const Scratch& sc, in
   for (int l = 1; l < p.nlevels; ++l)
     if ((rc = launch_resize_level(p, l, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[1], s));
-  // per-stage timing needs the stages one after another on `s`; otherwise blur forks off here
+  // per-stage timing needs the stages one after another on `s`; otherwise blur (which depends only on the pyramid)
+  // forks off onto the side stream, before FAST by default (ORB_GPU_FORK_AT=2: after FAST, next to the quadtree).
+  // Measured on 512 TUM frames: 2.614 ms (before FAST), 2.629 (after), 2.648 (no fork) -- the stages are bound by
+  // instruction issue, so running them side by side buys ~1 %
   OrbGpuExtractor::Fork* fk = nullptr;
-  if (!tm && fork_enabled()) {
-    if ((rc = fork_for(h, s, &fk))) return rc;
+  if (!tm && fork_enabled() && (rc = fork_for(h, s, &fk))) return rc;
+  auto fork_blur = [&]() -> int {
     ORB_CUDA_TRY(cudaEventRecord(fk->forked, s));
     ORB_CUDA_TRY(cudaStreamWaitEvent(fk->side, fk->forked, 0));
-    if ((rc = launch_blur(p, nframes, fk->side))) return rc;
+    const int r = launch_blur(p, nframes, fk->side);
+    if (r) return r;
     ORB_CUDA_TRY(cudaEventRecord(fk->joined, fk->side));
-  }
+    return ORB_GPU_OK;
+  };
+  if (fk && fork_point() == 1 && (rc = fork_blur())) return rc;
   if ((rc = launch_fast_cells(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[2], s));
+  if (fk && fork_point() != 1 && (rc = fork_blur())) return rc;
   if ((rc = launch_quadtree(p, sc, nframes, s))) return rc;
   if (tm) ORB_CUDA_TRY(cudaEventRecord(h->ev[3], s));
   if (fk) ORB_CUDA_TRY(cudaStreamWaitEvent(s, fk->joined, 0));
@@ -527,7 +544,32 @@ int orb_gpu_extract_batch_device(OrbGpuExtractor* h, const uint8_t* d_frames, in
     // rows not 4-byte aligned (e.g. 1241-px KITTI rows): repack into the handle's level-0 buffer
     if ((rc = launch_repack_rows(d_frames, stride, frame_stride, width, height, p.lv[0], nframes, s))) return rc;
   }
-  if ((rc = run_pipeline(h, p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  const int nsplit = (h->timing || nframes < 128) ? 1 : std::min(device_split(), nframes / 64);
+  if (nsplit <= 1) {
+    if ((rc = run_pipeline(h, p, h->sc, nframes, d_kps, d_desc, capacity, d_n_out, s))) return rc;
+  } else {
+    ORB_CUDA_TRY(cudaMemsetAsync(h->sc.status, 0, sizeof(int), s));
+    while ((int)h->ev_in.size() < nsplit) {
+      cudaEvent_t a = nullptr, b = nullptr;
+      ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+      ORB_CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+      h->ev_in.push_back(a); h->ev_done.push_back(b);
+    }
+    ORB_CUDA_TRY(cudaEventRecord(h->ev_in[0], s));  // everything queued on `s` so far (repack, earlier calls)
+    for (int k = 0; k < nsplit; ++k) {
+      const int c0 = (int)((long long)nframes * k / nsplit), cn = (int)((long long)nframes * (k + 1) / nsplit) - c0;
+      cudaStream_t sk = k ? h->s_alt[k - 1] : s;
+      if (k) ORB_CUDA_TRY(cudaStreamWaitEvent(sk, h->ev_in[0], 0));
+      Plan pc = plan_at(p, c0);
+      if ((rc = run_pipeline(h, pc, scratch_at(h->sc, p, c0), cn, d_kps + (size_t)c0 * capacity,
+                             d_desc + (size_t)c0 * capacity * 32, capacity, d_n_out + c0, sk, false)))
+        return rc;
+      if (k) {
+        ORB_CUDA_TRY(cudaEventRecord(h->ev_done[k], sk));
+        ORB_CUDA_TRY(cudaStreamWaitEvent(s, h->ev_done[k], 0));
+      }
+    }
+  }
   if (d_status)
     ORB_CUDA_TRY(cudaMemcpyAsync(d_status, h->sc.status, sizeof(int), cudaMemcpyDeviceToDevice, s));
   h->last_nframes = nframes;

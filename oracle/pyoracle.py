@@ -529,6 +529,24 @@ def _f32(a):
     return None if a is None else np.ascontiguousarray(a, np.float32)
 
 
+def ref_matcher_last_call_seconds():
+    """Seconds the last refm_* call of this thread spent inside the matcher method itself (stand-in objects are built
+    outside the timed part): the CPU baseline bench.py puts next to a GPU matcher call."""
+    f = ref_matcher().refm_last_call_seconds
+    f.restype = C.c_double
+    return float(f())
+
+
+def ref_bruteforce_top2(q, db, threads=1):
+    """Brute-force top-2 (config 5) around the reference's own DescriptorDistance (src/ORBmatcher.cc:1647-1663,
+    verbatim build), `threads` host threads over the queries.  -> idx, best, second, seconds inside the loop."""
+    q = u8c(q); db = u8c(db)
+    nq = len(q)
+    idx = np.empty(nq, np.int32); best = np.empty(nq, np.int32); second = np.empty(nq, np.int32)
+    ref_matcher().refm_bruteforce_top2(_p(q), nq, _p(db), len(db), int(threads), _p(idx), _p(best), _p(second))
+    return idx, best, second, ref_matcher_last_call_seconds()
+
+
 def ref_search_last_frame(cam, Tcw_cur, Tcw_last, kps_cur, d_cur, ur_cur, scale_factors, blocked, kps_last, has_mp,
                           outlier, world_pos, mp_desc, mp_obs, th, mono, check_orientation):
     """The reference's SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1328-1470), verbatim.
@@ -676,6 +694,12 @@ def ref_compute_stereo_matches(kl, dl, kr, dr, levels_l, levels_r, scale_factors
     rc = ref_frame().reff_compute_stereo_matches(_p(kl), _p(dl), len(kl), _p(kr), _p(dr), len(kr), pl, pr, _p(sl), _p(sr), n,
                                                  _p(sf), _p(isf), C.c_float(mb), C.c_float(mbf), _p(ur), _p(dp))
     return ur, dp, rc
+
+
+def ref_frame_last_call_seconds():
+    f = ref_frame().reff_last_call_seconds
+    f.restype = C.c_double
+    return float(f())
 
 
 def ref_features_in_area(kps, grid, x, y, r, min_level, max_level):

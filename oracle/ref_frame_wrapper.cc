@@ -6,6 +6,7 @@
 #include "Frame.h"
 #undef private
 
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <stdexcept>
@@ -37,7 +38,11 @@ void fill_extractor(ORBextractor& e, const uint8_t* const* levels, const int32_t
 }
 }  // namespace
 
+static thread_local double g_last_call_seconds = 0.0;  // inside Frame::ComputeStereoMatches alone (bench.py's CPU baseline)
+
 extern "C" {
+
+double reff_last_call_seconds() { return g_last_call_seconds; }
 
 // Frame::ComputeStereoMatches (src/Frame.cc:466-640) on given keypoints, descriptors and unblurred pyramids
 // (sizes[2l], sizes[2l+1] = width, height of level l).  u_right / depth [nl] = mvuRight / mvDepth.
@@ -62,11 +67,13 @@ int reff_compute_stereo_matches(const orbo::KeyPoint* kl, const uint8_t* dl, int
   f.mvInvScaleFactors.assign(inv_sf, inv_sf + nlevels);
   f.mb = mb;
   f.mbf = mbf;
+  const auto t0 = std::chrono::steady_clock::now();
   try {
     f.ComputeStereoMatches();
   } catch (const std::out_of_range&) {
     return -1;
   }
+  g_last_call_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   for (int i = 0; i < nl; ++i) { u_right[i] = f.mvuRight[i]; depth[i] = f.mvDepth[i]; }
   return 0;
 }
