@@ -387,6 +387,19 @@ def config_matcher_calls(orb, local, cpu):
                                                 "TH_HIGH, ratio 0.9 (host-pointer C-ABI call)" % (M, nk),
                                     "ms_per_call": dt * 1e3, "matches": int(nm.value)}}
     match_gpu = match.copy()
+    # the same search with the frame resident in device memory (orb_gpu_frame_*): only the queries move
+    res = orb.GpuFrame(local).upload(kps, desc, None, grid)
+
+    def sbp_res():
+        blocked[:] = 0
+        rc = L.orb_gpu_frame_search_by_projection(res._h, _p(proj), _p(qdesc), M, _p(sf), len(sf), 1.0, 0.9, 100,
+                                                  _p(blocked), _p(match), C.byref(nm))
+        assert rc == 0
+
+    dtr = _timed_host(sbp_res, 200, 20)
+    sbp_res()
+    out["search_by_projection"]["ms_per_call_resident_frame"] = dtr * 1e3
+    out["search_by_projection"]["resident_equals_host_pointer_call"] = bool(np.array_equal(match, match_gpu))
     # SearchByBoW: the frame against a permuted, noisy second view; feature vectors from the device vocabulary
     tree = synth.make_vocabulary(10, 4, 1)
     voc = orb.ORBVocabulary(tree, device=local)

@@ -40,6 +40,8 @@ EXPORTS = [
     "orb_gpu_distinctive_descriptors_device", "orb_gpu_vocabulary_create", "orb_gpu_vocabulary_destroy",
     "orb_gpu_vocabulary_transform", "orb_gpu_vocabulary_transform_device", "orb_gpu_version", "orb_gpu_last_error",
     "orb_gpu_launch_count", "orb_gpu_popc_peak", "orb_gpu_imma_peak", "orb_gpu_umma_peak",
+    "orb_gpu_frame_create", "orb_gpu_frame_destroy", "orb_gpu_frame_size", "orb_gpu_frame_upload",
+    "orb_gpu_frame_from_device", "orb_gpu_frame_search_by_projection", "orb_gpu_frame_search_windowed",
 ]
 
 STATUS = {0: "OK", -1: "ERR_ARG", -2: "ERR_CAPACITY", -3: "ERR_CUDA", -4: "ERR_STATE"}
@@ -115,6 +117,13 @@ def lib():
                                               C.c_int, _Grid, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
                                               C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
         vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+        L.orb_gpu_frame_create.argtypes = [ci, C.POINTER(vp)]
+        L.orb_gpu_frame_destroy.argtypes = [vp]
+        L.orb_gpu_frame_size.argtypes = [vp]
+        L.orb_gpu_frame_upload.argtypes = [vp, vp, vp, vp, ci, _Grid]
+        L.orb_gpu_frame_from_device.argtypes = [vp, vp, vp, vp, ci, _Grid, vp]
+        L.orb_gpu_frame_search_by_projection.argtypes = [vp, vp, vp, ci, vp, ci, cf, cf, ci, vp, vp, C.POINTER(ci)]
+        L.orb_gpu_frame_search_windowed.argtypes = [vp, vp, vp, ci, ci, ci, vp, ci, ci, vp, vp, vp, C.POINTER(ci)]
         L.orb_gpu_search_by_bow.argtypes = [vp, ci, vp, ci, vp, vp, ci, vp, vp, vp, ci, cf, ci, ci, ci, vp, vp,
                                             C.POINTER(ci)]
         L.orb_gpu_search_for_triangulation.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, vp, vp, vp, vp, ci, vp, cf, cf,
@@ -344,6 +353,37 @@ class ORBVocabulary:
         return (ids, vals), fv
 
 
+class GpuFrame:
+    """The matcher-side data of a Frame / KeyFrame resident in device memory (mvKeysUn, mDescriptors, mvuRight and
+    the 64 x 48 grid of Frame::AssignFeaturesToGrid, src/Frame.cc:230-253): filled once, searched many times."""
+
+    def __init__(self, device=0):
+        self.device = device
+        self._h = C.c_void_p()
+        _check(lib().orb_gpu_frame_create(device, C.byref(self._h)), "orb_gpu_frame_create")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orb_gpu_frame_destroy(self._h)
+            self._h = None
+
+    def __len__(self):
+        return lib().orb_gpu_frame_size(self._h)
+
+    def upload(self, kps, desc, u_right, grid):
+        k = np.ascontiguousarray(kps, KP_DTYPE); d = np.ascontiguousarray(desc, np.uint8)
+        ur = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        _check(lib().orb_gpu_frame_upload(self._h, _p(k), _p(d), _p(ur), len(k), _Grid(*[float(v) for v in grid])),
+               "orb_gpu_frame_upload")
+        return self
+
+    def from_device(self, d_kps_ptr, d_desc_ptr, d_u_right_ptr, n, grid, stream=None):
+        """Device addresses (ints), e.g. one frame of the outputs of ORBextractor.extract_batch_device."""
+        _check(lib().orb_gpu_frame_from_device(self._h, d_kps_ptr, d_desc_ptr, d_u_right_ptr, int(n),
+                                               _Grid(*[float(v) for v in grid]), stream), "orb_gpu_frame_from_device")
+        return self
+
+
 class ORBmatcher:
     """Drop-in for the Hamming-matching surface of ORB_SLAM2::ORBmatcher (include/ORBmatcher.h)."""
 
@@ -396,16 +436,25 @@ class ORBmatcher:
                     scale_factors [L], blocked uint8 [N] (keypoint holds a MapPoint with observations)).
         map_points: dict(proj PROJ_DTYPE [M], desc [M,32]).
         -> nmatches, match_of_kp [N] (map-point index or -1); frame['blocked'] is updated in place."""
+        res = frame.get("resident")      # a GpuFrame: the target stays on the device, only the queries move
+        nk = len(res) if res is not None else len(frame["kps"])
+        sf = np.ascontiguousarray(frame["scale_factors"], np.float32)
+        blocked = frame.get("blocked")
+        if blocked is None:
+            blocked = frame["blocked"] = np.zeros(nk, np.uint8)
+        proj = np.ascontiguousarray(map_points["proj"], PROJ_DTYPE)
+        qd = np.ascontiguousarray(map_points["desc"], np.uint8)
+        if res is not None:
+            out = np.empty(nk, np.int32)
+            n = C.c_int()
+            _check(lib().orb_gpu_frame_search_by_projection(res._h, _p(proj), _p(qd), len(proj), _p(sf), len(sf), th,
+                                                            self.mfNNratio, self.TH_HIGH, _p(blocked), _p(out),
+                                                            C.byref(n)), "orb_gpu_frame_search_by_projection")
+            return n.value, out
         kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
         kd = np.ascontiguousarray(frame["desc"], np.uint8)
         ur = frame.get("u_right")
         ur = None if ur is None else np.ascontiguousarray(ur, np.float32)
-        sf = np.ascontiguousarray(frame["scale_factors"], np.float32)
-        blocked = frame.get("blocked")
-        if blocked is None:
-            blocked = frame["blocked"] = np.zeros(len(kps), np.uint8)
-        proj = np.ascontiguousarray(map_points["proj"], PROJ_DTYPE)
-        qd = np.ascontiguousarray(map_points["desc"], np.uint8)
         g = _Grid(*[float(v) for v in frame["grid"]])
         out = np.empty(len(kps), np.int32)
         n = C.c_int()
@@ -424,17 +473,28 @@ class ORBmatcher:
         gate: 0 none, 1 stereo radius gate (:1407-1413), 2 chi-square gate of Fuse (:904-931, needs
         inv_level_sigma2).  With blocks = 0 in every query nothing is claimed (the two passes of SearchBySim3).
         -> nmatches, match_of_kp [N], match_of_query [M]; frame['blocked'] is updated in place."""
-        kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
-        kd = np.ascontiguousarray(frame["desc"], np.uint8)
-        ur = frame.get("u_right")
-        ur = None if ur is None else np.ascontiguousarray(ur, np.float32)
+        res = frame.get("resident")
+        nk = len(res) if res is not None else len(frame["kps"])
         blocked = frame.get("blocked")
         if blocked is None:
-            blocked = frame["blocked"] = np.zeros(len(kps), np.uint8)
+            blocked = frame["blocked"] = np.zeros(nk, np.uint8)
         wq = np.ascontiguousarray(queries, WINDOW_DTYPE)
         sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
         outq = np.empty(len(wq), np.int32)
         qd = np.ascontiguousarray(qdesc, np.uint8)
+        th_acc = self.TH_HIGH if th_accept is None else int(th_accept)
+        if res is not None:
+            out = np.empty(nk, np.int32)
+            n = C.c_int()
+            _check(lib().orb_gpu_frame_search_windowed(res._h, _p(wq), _p(qd), len(wq), th_acc, int(gate), _p(sig),
+                                                       0 if sig is None else len(sig), int(self.mbCheckOrientation),
+                                                       _p(blocked), _p(out), _p(outq), C.byref(n)),
+                   "orb_gpu_frame_search_windowed")
+            return n.value, out, outq
+        kps = np.ascontiguousarray(frame["kps"], KP_DTYPE)
+        kd = np.ascontiguousarray(frame["desc"], np.uint8)
+        ur = frame.get("u_right")
+        ur = None if ur is None else np.ascontiguousarray(ur, np.float32)
         g = _Grid(*[float(v) for v in frame["grid"]])
         out = np.empty(len(kps), np.int32)
         n = C.c_int()

@@ -9,7 +9,9 @@
 // fixpoint of "query i sees the claims of queries j < i": each round re-evaluates every query
 // against the previous round's claims; query i is final after at most i+1 rounds and the loop
 // ends when a round changes nothing, at which point the state equals the sequential result.
+#include <algorithm>
 #include <climits>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -73,9 +75,13 @@ window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __re
                          const float* __restrict__ inv_sigma2,
                          const uint32_t* __restrict__ sorted, const int* __restrict__ cell_start,
                          int* __restrict__ counts, const int* __restrict__ offsets,
-                         uint32_t* __restrict__ entries) {
+                         uint32_t* __restrict__ entries, int ent_cap, int* __restrict__ overflow) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= nq) return;
+  if (FILL && offsets[nq] > ent_cap) {  // the entry pool is too small: flag it, the host grows the pool and reruns
+    if (warp == 0 && lane == 0) *overflow = 1;
+    return;
+  }
   const OrbWindowQuery p = q[warp];
   int n = 0;
   if (p.valid) {
@@ -156,9 +162,10 @@ __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int
 constexpr int kTopK = 8;
 __global__ void __launch_bounds__(256)
 topk_entries_kernel(const int* __restrict__ offsets, const uint32_t* __restrict__ entries, int nq,
-                    uint2* __restrict__ topk /*[nq][kTopK]: (dist << 20 | position, entry)*/) {
+                    uint2* __restrict__ topk /*[nq][kTopK]: (dist << 20 | position, entry)*/, int ent_cap = INT_MAX) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= nq) return;
+  if (offsets[nq] > ent_cap) return;
   const int beg = offsets[warp], end = offsets[warp + 1];
   unsigned last = 0;
   for (int t = 0; t < kTopK; ++t) {
@@ -201,15 +208,30 @@ __global__ void __launch_bounds__(1024)
 window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKeyPoint* __restrict__ kps, int nk,
                       const int* __restrict__ offsets, const uint32_t* __restrict__ entries,
                       const uint2* __restrict__ topk, float nnratio,
-                      int ratio_rule, int th_accept, int check_ori, uint8_t* __restrict__ blocked /*in/out [nk]*/,
-                      int* __restrict__ claim_a, int* __restrict__ claim_b, int* __restrict__ minclaim /*[nk]*/,
+                      int ratio_rule, int th_accept, int check_ori, uint8_t* blocked_g /*in/out [nk]*/,
+                      int* claim_a, int* claim_b, int* minclaim_g /*[nk]*/,
                       int32_t* __restrict__ match_of_kp, int32_t* __restrict__ match_of_query,
-                      int* __restrict__ nmatches) {
+                      int* __restrict__ nmatches, int use_smem = 0, int ent_cap = INT_MAX) {
+  extern __shared__ __align__(16) int s_dyn[];
   __shared__ int s_changed, s_count;
   __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3];
   const int T = blockDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, nwarps = T >> 5;
+  if (offsets[nq] > ent_cap) return;  // entry pool overflow (flagged by the fill kernel): nothing to resolve yet
+  // The fixpoint rounds touch only the claims, the per-keypoint minimum and the blocked flags: they live in shared
+  // memory when they fit (use_smem: 8 nq + 5 nk + nq bytes), which turns a round from a few L2 round trips into
+  // a few hundred cycles.
   int* prev = claim_a;
   int* cur = claim_b;
+  int* minclaim = minclaim_g;
+  uint8_t* blocked = blocked_g;
+  uint8_t* qblocks = nullptr;
+  if (use_smem) {
+    prev = s_dyn; cur = prev + nq; minclaim = cur + nq;
+    blocked = reinterpret_cast<uint8_t*>(minclaim + nk);
+    qblocks = blocked + ((nk + 3) & ~3);
+    for (int k = t; k < nk; k += T) blocked[k] = blocked_g[k];
+    for (int i = t; i < nq; i += T) qblocks[i] = q[i].blocks;
+  }
   for (int i = t; i < nq; i += T) prev[i] = -1;
   __syncthreads();
   for (int round = 0; round <= nq; ++round) {
@@ -217,7 +239,7 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
     if (t == 0) s_changed = 0;
     __syncthreads();
     for (int i = t; i < nq; i += T)
-      if (prev[i] >= 0 && q[i].blocks) atomicMin(&minclaim[prev[i]], i);
+      if (prev[i] >= 0 && (qblocks ? qblocks[i] : q[i].blocks)) atomicMin(&minclaim[prev[i]], i);
     __syncthreads();
     for (int i = t; i < nq; i += T) {
       const int beg = offsets[i], end = offsets[i + 1];
@@ -319,6 +341,8 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
     const int k = prev[i];
     match_of_query[i] = (k >= 0 && match_of_kp[k] != -2) ? k : -1;
   }
+  if (use_smem)
+    for (int k = t; k < nk; k += T) blocked_g[k] = blocked[k];
   if (t == 0) *nmatches = s_count;
 }
 
@@ -582,85 +606,196 @@ using namespace orbgpu;
 
 extern "C" {
 
-// shared body of the windowed searches: uploads, grid, candidates, ordered resolve, downloads
-static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
-                        const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid, bool top2,
-                        float nnratio, int th_accept, int gate, const float* inv_sigma2, int nlevels,
-                        int check_ori, int device, uint8_t* kp_blocked, int32_t* match_of_kp,
-                        int32_t* match_of_query, int* nmatches) {
+}  // extern "C"
+
+// ---- a frame's matcher-side data resident in device memory ------------------------------------------------------
+// The reference keeps mvKeysUn / mDescriptors / mvuRight and the 64 x 48 grid in the Frame (src/Frame.cc:230-253) and
+// every search reads them there.  OrbGpuFrame is that state on the device: uploaded (or copied from the extractor's
+// device outputs) once, grid sorted once, then any number of searches -- each of which moves only its queries in (one
+// copy from a pinned staging block) and its results out (one copy), with no allocation and one synchronisation.
+namespace {
+
+struct GrowDev {   // device buffer that only grows
+  void* p = nullptr; size_t bytes = 0;
+  int ensure(size_t need) {
+    if (need <= bytes) return ORB_GPU_OK;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    need += need / 2 + 256;
+    ORB_CUDA_TRY(cudaMalloc(&p, need));
+    bytes = need;
+    return ORB_GPU_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+struct GrowPinned {  // pinned host staging block that only grows
+  void* p = nullptr; size_t bytes = 0;
+  int ensure(size_t need) {
+    if (need <= bytes) return ORB_GPU_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; bytes = 0;
+    need += need / 2 + 256;
+    ORB_CUDA_TRY(cudaHostAlloc(&p, need, cudaHostAllocDefault));
+    bytes = need;
+    return ORB_GPU_OK;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+}  // namespace
+
+struct OrbGpuFrame {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  // target: keypoints (undistorted), descriptors, right coordinates, grid
+  int n = 0;
+  bool has_ur = false, grid_built = false;
+  OrbFrameGrid grid{};
+  GrowDev kps, desc, ur, sorted, cell;
+  // workspace of a search
+  GrowDev in, out, cnt, off, ent, top, ca, cb, minc, flag;
+  GrowPinned hin, hout;
+};
+
+namespace {
+
+int frame_build_grid(OrbGpuFrame* f, const OrbKeyPoint* d_kps) {
+  int nkpad = 2;
+  while (nkpad < f->n) nkpad <<= 1;
+  int rc;
+  if ((rc = f->sorted.ensure((size_t)nkpad * 4)) || (rc = f->cell.ensure((size_t)(kCells + 1) * 4))) return rc;
+  const size_t smem = (size_t)nkpad * 4;
+  if (smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grid_build_kernel<<<1, 1024, smem, f->stream>>>(d_kps, f->n, nkpad, f->grid, f->sorted.as<uint32_t>(), f->cell.as<int>());
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  f->grid_built = true;
+  return ORB_GPU_OK;
+}
+
+// One windowed search against the frame's resident target.  `extra_in` bytes at the head of the staging block are the
+// caller's (a transient target for the host-pointer entry points); queries, descriptors, flags follow.
+int frame_search(OrbGpuFrame* f, const OrbWindowQuery* q, const uint8_t* qdesc, int nq, bool top2, float nnratio,
+                 int th_accept, int gate, const float* inv_sigma2, int nlevels, int check_ori, uint8_t* kp_blocked,
+                 int32_t* match_of_kp, int32_t* match_of_query, int* nmatches, const OrbKeyPoint* host_kps = nullptr,
+                 const uint8_t* host_desc = nullptr, const float* host_ur = nullptr) {
+  const int nk = f->n;
   *nmatches = 0;
   for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
   if (match_of_query) for (int i = 0; i < nq; ++i) match_of_query[i] = -1;
   if (nq == 0 || nk == 0) return ORB_GPU_OK;
   if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
-  { const int rc_pool = use_cached_pool(device); if (rc_pool) return rc_pool; }
-  int nkpad = 2;
-  while (nkpad < nk) nkpad <<= 1;
-  TmpDevW dq, dqd, dk, dkd, dur, dsorted, dcell, dcnt, doff, dent, dblk, dca, dcb, dmin, dmatch, dn, dsig, dmq;
+  ORB_CUDA_TRY(cudaSetDevice(f->device));
+  cudaStream_t s = f->stream;
   int rc;
-  if ((rc = dsig.alloc((size_t)kMaxLevels * 4)) || (rc = dmq.alloc((size_t)nq * 4))) return rc;
-  if (gate == 2) ORB_CUDA_TRY(cudaMemcpy(dsig.p, inv_sigma2, (size_t)nlevels * 4, cudaMemcpyHostToDevice));
-  if ((rc = dq.alloc((size_t)nq * sizeof(OrbWindowQuery))) || (rc = dqd.alloc((size_t)nq * 32)) ||
-      (rc = dk.alloc((size_t)nk * sizeof(OrbKeyPoint))) || (rc = dkd.alloc((size_t)nk * 32)) ||
-      (rc = dur.alloc((size_t)nk * 4)) ||
-      (rc = dsorted.alloc((size_t)nkpad * 4)) || (rc = dcell.alloc((size_t)(kCells + 1) * 4)) ||
-      (rc = dcnt.alloc((size_t)nq * 4)) || (rc = doff.alloc((size_t)(nq + 1) * 4)) ||
-      (rc = dblk.alloc((size_t)nk)) || (rc = dca.alloc((size_t)nq * 4)) || (rc = dcb.alloc((size_t)nq * 4)) ||
-      (rc = dmin.alloc((size_t)nk * 4)) || (rc = dmatch.alloc((size_t)nk * 4)) || (rc = dn.alloc(4)))
+  // ---- input block: [transient target: kps | desc | ur] [q | qdesc | blocked | sigma]
+  const bool transient = host_kps != nullptr;
+  const size_t o_kps = 0, o_desc = o_kps + (transient ? up16((size_t)nk * sizeof(OrbKeyPoint)) : 0);
+  const size_t o_ur = o_desc + (transient ? (size_t)nk * 32 : 0);
+  const size_t o_q = o_ur + (transient && host_ur ? up16((size_t)nk * 4) : 0);
+  const size_t o_qd = o_q + (size_t)nq * sizeof(OrbWindowQuery), o_blk = o_qd + (size_t)nq * 32;
+  const size_t o_sig = o_blk + up16((size_t)nk), in_bytes = o_sig + kMaxLevels * 4;
+  // ---- output block: [match_of_kp | match_of_query | blocked | nmatches, total, overflow]
+  const size_t r_mq = (size_t)nk * 4, r_blk = r_mq + (size_t)nq * 4, r_tail = r_blk + up16((size_t)nk), out_bytes = r_tail + 16;
+  if ((rc = f->hin.ensure(in_bytes)) || (rc = f->in.ensure(in_bytes)) || (rc = f->hout.ensure(out_bytes)) ||
+      (rc = f->out.ensure(out_bytes)) || (rc = f->cnt.ensure((size_t)nq * 4)) || (rc = f->off.ensure((size_t)(nq + 1) * 4)) ||
+      (rc = f->top.ensure((size_t)nq * kTopK * sizeof(uint2))) || (rc = f->ca.ensure((size_t)nq * 4)) ||
+      (rc = f->cb.ensure((size_t)nq * 4)) || (rc = f->minc.ensure((size_t)nk * 4)) ||
+      (rc = f->ent.ensure((size_t)std::max(nq * 48, 1 << 16) * 4)))
     return rc;
-  ORB_CUDA_TRY(cudaMemcpy(dq.p, q, (size_t)nq * sizeof(OrbWindowQuery), cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(dqd.p, qdesc, (size_t)nq * 32, cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(dk.p, kps, (size_t)nk * sizeof(OrbKeyPoint), cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(dkd.p, kdesc, (size_t)nk * 32, cudaMemcpyHostToDevice));
-  if (u_right) ORB_CUDA_TRY(cudaMemcpy(dur.p, u_right, (size_t)nk * 4, cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(dblk.p, kp_blocked, (size_t)nk, cudaMemcpyHostToDevice));
-
-  const size_t smem = (size_t)nkpad * 4;
-  if (smem > 48 * 1024)
-    ORB_CUDA_TRY(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  grid_build_kernel<<<1, 1024, smem>>>(dk.as<OrbKeyPoint>(), nk, nkpad, grid, dsorted.as<uint32_t>(), dcell.as<int>());
+  uint8_t* hin = (uint8_t*)f->hin.p;
+  if (transient) {
+    std::memcpy(hin + o_kps, host_kps, (size_t)nk * sizeof(OrbKeyPoint));
+    std::memcpy(hin + o_desc, host_desc, (size_t)nk * 32);
+    if (host_ur) std::memcpy(hin + o_ur, host_ur, (size_t)nk * 4);
+  }
+  std::memcpy(hin + o_q, q, (size_t)nq * sizeof(OrbWindowQuery));
+  std::memcpy(hin + o_qd, qdesc, (size_t)nq * 32);
+  std::memcpy(hin + o_blk, kp_blocked, (size_t)nk);
+  if (gate == 2) std::memcpy(hin + o_sig, inv_sigma2, (size_t)nlevels * 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(f->in.p, hin, in_bytes, cudaMemcpyHostToDevice, s));
+  uint8_t* din = (uint8_t*)f->in.p;
+  const OrbKeyPoint* d_kps = transient ? (const OrbKeyPoint*)(din + o_kps) : f->kps.as<OrbKeyPoint>();
+  const uint4* d_desc = transient ? (const uint4*)(din + o_desc) : f->desc.as<uint4>();
+  const float* d_ur = transient ? (host_ur ? (const float*)(din + o_ur) : nullptr) : (f->has_ur ? f->ur.as<float>() : nullptr);
+  if (!gate) d_ur = nullptr;
+  if (transient || !f->grid_built) { if ((rc = frame_build_grid(f, d_kps))) return rc; }
+  const OrbWindowQuery* d_q = (const OrbWindowQuery*)(din + o_q);
+  const uint4* d_qd = (const uint4*)(din + o_qd);
+  uint8_t* d_blk = din + o_blk;
+  const float* d_sig = (const float*)(din + o_sig);
+  uint8_t* dout = (uint8_t*)f->out.p;
+  int32_t* d_match = (int32_t*)dout;
+  int32_t* d_mq = (int32_t*)(dout + r_mq);
+  int* d_tail = (int*)(dout + r_tail);  // nmatches, total, overflow
+  ORB_CUDA_TRY(cudaMemsetAsync(d_tail, 0, 16, s));
   const int blocks = (nq * 32 + 255) / 256;
-  const float* ur = u_right ? dur.as<float>() : nullptr;
-  window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, gate, dsig.as<float>(), dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(),
-      nullptr, nullptr);
-  exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
-  int total = 0;
-  ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
-  if ((rc = dent.alloc((size_t)total * 4))) return rc;
-  window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
-      dkd.as<uint4>(), ur, grid, gate, dsig.as<float>(), dsorted.as<uint32_t>(), dcell.as<int>(), nullptr,
-      doff.as<int>(), dent.as<uint32_t>());
-  TmpDevW dtop;
-  if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
-  topk_entries_kernel<<<blocks, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());
-  if (top2)
-    window_resolve_kernel<true><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
-        dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
-  else
-    window_resolve_kernel<false><<<1, 1024>>>(dq.as<OrbWindowQuery>(), nq, dk.as<OrbKeyPoint>(), nk, doff.as<int>(),
-        dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 0, th_accept, check_ori, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
-        dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
-  count_launch(6);
-  ORB_CUDA_TRY(cudaGetLastError());
-  ORB_CUDA_TRY(cudaMemcpy(match_of_kp, dmatch.p, (size_t)nk * 4, cudaMemcpyDeviceToHost));
-  ORB_CUDA_TRY(cudaMemcpy(kp_blocked, dblk.p, (size_t)nk, cudaMemcpyDeviceToHost));
-  ORB_CUDA_TRY(cudaMemcpy(nmatches, dn.p, 4, cudaMemcpyDeviceToHost));
-  if (match_of_query) ORB_CUDA_TRY(cudaMemcpy(match_of_query, dmq.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+  // shared-memory state of the resolve kernel: prev, cur [nq], minclaim [nk], blocked [nk], query flags [nq]
+  const size_t rs_smem = (size_t)nq * 8 + (size_t)nk * 4 + up16((size_t)nk) + up16((size_t)nq);
+  const int use_smem = rs_smem <= 200 * 1024;
+  if (use_smem && rs_smem > 48 * 1024) {
+    if (top2) ORB_CUDA_TRY(cudaFuncSetAttribute(window_resolve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
+    else ORB_CUDA_TRY(cudaFuncSetAttribute(window_resolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
+  }
+  window_candidates_kernel<false><<<blocks, 256, 0, s>>>(d_q, d_qd, nq, d_kps, d_desc, d_ur, f->grid, gate, d_sig,
+      f->sorted.as<uint32_t>(), f->cell.as<int>(), f->cnt.as<int>(), nullptr, nullptr, 0, nullptr);
+  exclusive_scan_kernel<<<1, 1024, 0, s>>>(f->cnt.as<int>(), nq, f->off.as<int>());
+  count_launch(2);
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const int ent_cap = (int)std::min<size_t>(f->ent.bytes / 4, (size_t)INT_MAX);
+    window_candidates_kernel<true><<<blocks, 256, 0, s>>>(d_q, d_qd, nq, d_kps, d_desc, d_ur, f->grid, gate, d_sig,
+        f->sorted.as<uint32_t>(), f->cell.as<int>(), nullptr, f->off.as<int>(), f->ent.as<uint32_t>(), ent_cap, d_tail + 2);
+    topk_entries_kernel<<<blocks, 256, 0, s>>>(f->off.as<int>(), f->ent.as<uint32_t>(), nq, f->top.as<uint2>(), ent_cap);
+    if (top2)
+      window_resolve_kernel<true><<<1, 1024, use_smem ? rs_smem : 0, s>>>(d_q, nq, d_kps, nk, f->off.as<int>(),
+          f->ent.as<uint32_t>(), f->top.as<uint2>(), nnratio, 0, th_accept, check_ori, d_blk, f->ca.as<int>(), f->cb.as<int>(),
+          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap);
+    else
+      window_resolve_kernel<false><<<1, 1024, use_smem ? rs_smem : 0, s>>>(d_q, nq, d_kps, nk, f->off.as<int>(),
+          f->ent.as<uint32_t>(), f->top.as<uint2>(), nnratio, 0, th_accept, check_ori, d_blk, f->ca.as<int>(), f->cb.as<int>(),
+          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap);
+    count_launch(3);
+    ORB_CUDA_TRY(cudaGetLastError());
+    // the blocked flags travel back inside the output block
+    ORB_CUDA_TRY(cudaMemcpyAsync(dout + r_blk, d_blk, (size_t)nk, cudaMemcpyDeviceToDevice, s));
+    ORB_CUDA_TRY(cudaMemcpyAsync(d_tail + 1, f->off.as<int>() + nq, 4, cudaMemcpyDeviceToDevice, s));
+    ORB_CUDA_TRY(cudaMemcpyAsync(f->hout.p, dout, out_bytes, cudaMemcpyDeviceToHost, s));
+    ORB_CUDA_TRY(cudaStreamSynchronize(s));
+    const int* tail = (const int*)((const uint8_t*)f->hout.p + r_tail);
+    if (!tail[2]) break;
+    if (attempt == 1) return ORB_GPU_ERR_CAPACITY;
+    if ((rc = f->ent.ensure((size_t)tail[1] * 4))) return rc;  // grow the entry pool to the counted total and rerun
+    ORB_CUDA_TRY(cudaMemsetAsync(d_tail, 0, 16, s));
+  }
+  const uint8_t* hout = (const uint8_t*)f->hout.p;
+  std::memcpy(match_of_kp, hout, (size_t)nk * 4);
+  if (match_of_query) std::memcpy(match_of_query, hout + r_mq, (size_t)nq * 4);
+  std::memcpy(kp_blocked, hout + r_blk, (size_t)nk);
+  *nmatches = *(const int*)(hout + r_tail);
   return ORB_GPU_OK;
 }
 
-int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
-                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
-                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
-                                 float th, float nnratio, int th_high, int device, uint8_t* kp_blocked,
-                                 int32_t* match_of_kp, int* nmatches) {
-  if (nq < 0 || nk < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
-      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
-    return ORB_GPU_ERR_ARG;
-  // window of every map point as the reference computes it on the host (:63-69, RadiusByViewingCos :131-137)
-  std::vector<OrbWindowQuery> wq((size_t)nq);
+// the host-pointer entry points keep one scratch frame per thread and device (transient target, no residency)
+OrbGpuFrame* scratch_frame(int device) {
+  struct Holder {
+    std::vector<OrbGpuFrame*> v;
+    ~Holder() { for (OrbGpuFrame* f : v) orb_gpu_frame_destroy(f); }
+  };
+  static thread_local Holder h;
+  for (OrbGpuFrame* f : h.v) if (f->device == device) return f;
+  OrbGpuFrame* f = nullptr;
+  if (orb_gpu_frame_create(device, &f) != ORB_GPU_OK) return nullptr;
+  h.v.push_back(f);
+  return f;
+}
+
+// window of every map point as the reference computes it on the host (:63-69, RadiusByViewingCos :131-137)
+void proj_to_windows(const OrbProjQuery* q, int nq, const float* scale_factors, int nlevels, float th,
+                     std::vector<OrbWindowQuery>& wq) {
+  wq.resize((size_t)nq);
   for (int i = 0; i < nq; ++i) {
     OrbWindowQuery& w = wq[i];
     w = OrbWindowQuery();
@@ -673,6 +808,133 @@ int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, in
     w.min_level = p.level - 1; w.max_level = p.level;
     w.valid = 1; w.blocks = p.has_obs;
   }
+}
+
+}  // namespace
+
+extern "C" {
+
+int orb_gpu_frame_create(int device, OrbGpuFrame** out) {
+  if (!out) return ORB_GPU_ERR_ARG;
+  *out = nullptr;
+  ORB_CUDA_TRY(cudaSetDevice(device));
+  OrbGpuFrame* f = new OrbGpuFrame();
+  f->device = device;
+  const cudaError_t e = cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { set_last_error("cudaStreamCreate (frame)", e); delete f; return ORB_GPU_ERR_CUDA; }
+  *out = f;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_frame_destroy(OrbGpuFrame* f) {
+  if (!f) return ORB_GPU_OK;
+  cudaSetDevice(f->device);
+  cudaStreamSynchronize(f->stream);
+  for (GrowDev* b : {&f->kps, &f->desc, &f->ur, &f->sorted, &f->cell, &f->in, &f->out, &f->cnt, &f->off, &f->ent, &f->top,
+                     &f->ca, &f->cb, &f->minc, &f->flag})
+    b->release();
+  f->hin.release(); f->hout.release();
+  cudaStreamDestroy(f->stream);
+  delete f;
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_frame_size(const OrbGpuFrame* f) { return f ? f->n : 0; }
+
+int orb_gpu_frame_upload(OrbGpuFrame* f, const OrbKeyPoint* kps, const uint8_t* desc, const float* u_right, int n,
+                         OrbFrameGrid grid) {
+  if (!f || n < 0 || (n > 0 && (!kps || !desc))) return ORB_GPU_ERR_ARG;
+  if (n > 32768) return ORB_GPU_ERR_CAPACITY;
+  ORB_CUDA_TRY(cudaSetDevice(f->device));
+  f->n = n; f->grid = grid; f->has_ur = u_right != nullptr; f->grid_built = false;
+  if (n == 0) return ORB_GPU_OK;
+  int rc;
+  const size_t bk = (size_t)n * sizeof(OrbKeyPoint), bd = (size_t)n * 32, bu = (size_t)n * 4;
+  if ((rc = f->kps.ensure(bk)) || (rc = f->desc.ensure(bd)) || (rc = f->ur.ensure(bu)) ||
+      (rc = f->hin.ensure(up16(bk) + bd + bu)))
+    return rc;
+  uint8_t* h = (uint8_t*)f->hin.p;
+  std::memcpy(h, kps, bk);
+  std::memcpy(h + up16(bk), desc, bd);
+  if (u_right) std::memcpy(h + up16(bk) + bd, u_right, bu);
+  ORB_CUDA_TRY(cudaMemcpyAsync(f->kps.p, h, bk, cudaMemcpyHostToDevice, f->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(f->desc.p, h + up16(bk), bd, cudaMemcpyHostToDevice, f->stream));
+  if (u_right) ORB_CUDA_TRY(cudaMemcpyAsync(f->ur.p, h + up16(bk) + bd, bu, cudaMemcpyHostToDevice, f->stream));
+  if ((rc = frame_build_grid(f, f->kps.as<OrbKeyPoint>()))) return rc;
+  ORB_CUDA_TRY(cudaStreamSynchronize(f->stream));  // the staging block is reused by the next call
+  return ORB_GPU_OK;
+}
+
+int orb_gpu_frame_from_device(OrbGpuFrame* f, const OrbKeyPoint* d_kps, const uint8_t* d_desc, const float* d_u_right,
+                              int n, OrbFrameGrid grid, void* stream) {
+  if (!f || n < 0 || (n > 0 && (!d_kps || !d_desc))) return ORB_GPU_ERR_ARG;
+  if (n > 32768) return ORB_GPU_ERR_CAPACITY;
+  ORB_CUDA_TRY(cudaSetDevice(f->device));
+  f->n = n; f->grid = grid; f->has_ur = d_u_right != nullptr; f->grid_built = false;
+  if (n == 0) return ORB_GPU_OK;
+  int rc;
+  if ((rc = f->kps.ensure((size_t)n * sizeof(OrbKeyPoint))) || (rc = f->desc.ensure((size_t)n * 32)) ||
+      (rc = f->ur.ensure((size_t)n * 4)))
+    return rc;
+  // the producer's stream (the extractor's) must have finished writing: order the copies after it
+  if (stream) ORB_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(f->kps.p, d_kps, (size_t)n * sizeof(OrbKeyPoint), cudaMemcpyDeviceToDevice, f->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(f->desc.p, d_desc, (size_t)n * 32, cudaMemcpyDeviceToDevice, f->stream));
+  if (d_u_right) ORB_CUDA_TRY(cudaMemcpyAsync(f->ur.p, d_u_right, (size_t)n * 4, cudaMemcpyDeviceToDevice, f->stream));
+  return frame_build_grid(f, f->kps.as<OrbKeyPoint>());
+}
+
+int orb_gpu_frame_search_by_projection(OrbGpuFrame* f, const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                       const float* scale_factors, int nlevels, float th, float nnratio, int th_high,
+                                       uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches) {
+  if (!f || nq < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
+      (f->n > 0 && (!kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  std::vector<OrbWindowQuery> wq;
+  proj_to_windows(q, nq, scale_factors, nlevels, th, wq);
+  return frame_search(f, wq.data(), qdesc, nq, true, nnratio, th_high, 1, nullptr, 0, 0, kp_blocked, match_of_kp, nullptr,
+                      nmatches);
+}
+
+int orb_gpu_frame_search_windowed(OrbGpuFrame* f, const OrbWindowQuery* q, const uint8_t* qdesc, int nq, int th_accept,
+                                  int gate, const float* inv_level_sigma2, int nlevels, int check_orientation,
+                                  uint8_t* kp_blocked, int32_t* match_of_kp, int32_t* match_of_query, int* nmatches) {
+  if (!f || nq < 0 || !nmatches || gate < 0 || gate > 2 ||
+      (gate == 2 && (!inv_level_sigma2 || nlevels < 1 || nlevels > kMaxLevels)) ||
+      (f->n > 0 && (!kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  return frame_search(f, q, qdesc, nq, false, 0.f, th_accept, gate, inv_level_sigma2, nlevels, check_orientation,
+                      kp_blocked, match_of_kp, match_of_query, nmatches);
+}
+
+// shared body of the host-pointer windowed searches: a transient target on this thread's scratch frame
+static int run_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int nq, const OrbKeyPoint* kps,
+                        const uint8_t* kdesc, const float* u_right, int nk, OrbFrameGrid grid, bool top2,
+                        float nnratio, int th_accept, int gate, const float* inv_sigma2, int nlevels,
+                        int check_ori, int device, uint8_t* kp_blocked, int32_t* match_of_kp,
+                        int32_t* match_of_query, int* nmatches) {
+  *nmatches = 0;
+  for (int i = 0; i < nk; ++i) match_of_kp[i] = -1;
+  if (match_of_query) for (int i = 0; i < nq; ++i) match_of_query[i] = -1;
+  if (nq == 0 || nk == 0) return ORB_GPU_OK;
+  if (nk > 32768) return ORB_GPU_ERR_CAPACITY;
+  OrbGpuFrame* f = scratch_frame(device);
+  if (!f) return ORB_GPU_ERR_CUDA;
+  f->n = nk; f->grid = grid; f->has_ur = u_right != nullptr; f->grid_built = false;
+  return frame_search(f, q, qdesc, nq, top2, nnratio, th_accept, gate, inv_sigma2, nlevels, check_ori, kp_blocked,
+                      match_of_kp, match_of_query, nmatches, kps, kdesc, u_right);
+}
+
+int orb_gpu_search_by_projection(const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                 const OrbKeyPoint* kps, const uint8_t* kdesc, const float* u_right,
+                                 int nk, OrbFrameGrid grid, const float* scale_factors, int nlevels,
+                                 float th, float nnratio, int th_high, int device, uint8_t* kp_blocked,
+                                 int32_t* match_of_kp, int* nmatches) {
+  if (nq < 0 || nk < 0 || !nmatches || nlevels < 1 || nlevels > kMaxLevels || !scale_factors ||
+      (nk > 0 && (!kps || !kdesc || !kp_blocked || !match_of_kp)) || (nq > 0 && (!q || !qdesc)))
+    return ORB_GPU_ERR_ARG;
+  std::vector<OrbWindowQuery> wq;
+  proj_to_windows(q, nq, scale_factors, nlevels, th, wq);
   return run_windowed(wq.data(), qdesc, nq, kps, kdesc, u_right, nk, grid, true, nnratio, th_high, 1, nullptr, 0, 0,
                       device, kp_blocked, match_of_kp, nullptr, nmatches);
 }
@@ -721,7 +983,7 @@ int orb_gpu_features_in_area(const OrbWindowQuery* q, int nq, const OrbKeyPoint*
   const int blocks = (nq * 32 + 255) / 256;
   window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr,
-      nullptr);
+      nullptr, 0, nullptr);
   exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
   ORB_CUDA_TRY(cudaMemcpy(offsets, doff.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost));
   const int total = offsets[nq];
@@ -731,7 +993,7 @@ int orb_gpu_features_in_area(const OrbWindowQuery* q, int nq, const OrbKeyPoint*
   if ((rc = dent.alloc((size_t)total * 4))) return rc;
   window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(),
-      dent.as<uint32_t>());
+      dent.as<uint32_t>(), INT_MAX, nullptr);
   count_launch(1);
   ORB_CUDA_TRY(cudaGetLastError());
   std::vector<uint32_t> ent((size_t)total);
@@ -916,14 +1178,14 @@ int orb_gpu_search_for_initialization(const OrbKeyPoint* kps1, const uint8_t* de
   const int blocks = (nq * 32 + 255) / 256;
   window_candidates_kernel<false><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), dcnt.as<int>(), nullptr,
-      nullptr);
+      nullptr, 0, nullptr);
   exclusive_scan_kernel<<<1, 1024>>>(dcnt.as<int>(), nq, doff.as<int>());
   int total = 0;
   ORB_CUDA_TRY(cudaMemcpy(&total, doff.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
   if ((rc = dent.alloc((size_t)total * 4))) return rc;
   window_candidates_kernel<true><<<blocks, 256>>>(dq.as<OrbWindowQuery>(), dqd.as<uint4>(), nq, dk.as<OrbKeyPoint>(),
       dkd.as<uint4>(), nullptr, grid, 0, nullptr, dsorted.as<uint32_t>(), dcell.as<int>(), nullptr, doff.as<int>(),
-      dent.as<uint32_t>());
+      dent.as<uint32_t>(), INT_MAX, nullptr);
   TmpDevW dtop;
   if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
   topk_entries_kernel<<<blocks, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());

@@ -206,6 +206,35 @@ int orb_gpu_search_windowed(const OrbWindowQuery* q, const uint8_t* qdesc, int n
                             int device, uint8_t* kp_blocked, int32_t* match_of_kp,
                             int32_t* match_of_query, int* nmatches);
 
+/* ---- frames resident in device memory (matcher side) -----------------------------------------------------------
+ * The reference keeps mvKeysUn, mDescriptors, mvuRight and the 64 x 48 feature grid inside the Frame / KeyFrame
+ * (src/Frame.cc:230-253, include/Frame.h:130-161) and every ORBmatcher search reads them there.  OrbGpuFrame is that
+ * state in device memory: filled once per frame -- from host arrays, or from the device arrays orb_gpu_extract_batch_device
+ * left (no host round trip) -- the grid of AssignFeaturesToGrid built once, then any number of searches.  A search
+ * moves only its queries in and its results out (one copy each way through pinned staging blocks owned by the frame,
+ * no allocation, one synchronisation).  A frame is single-caller like an extractor handle; it owns one stream. */
+typedef struct OrbGpuFrame OrbGpuFrame;
+int orb_gpu_frame_create(int device, OrbGpuFrame** out);
+int orb_gpu_frame_destroy(OrbGpuFrame* f);
+int orb_gpu_frame_size(const OrbGpuFrame* f);
+/* kps = mvKeysUn, desc = mDescriptors [n][32], u_right = mvuRight or NULL (monocular); host pointers. */
+int orb_gpu_frame_upload(OrbGpuFrame* f, const OrbKeyPoint* kps, const uint8_t* desc, const float* u_right, int n,
+                         OrbFrameGrid grid);
+/* The same from device arrays (e.g. frame i of the [frame][capacity] outputs of orb_gpu_extract_batch_device and the
+ * d_u_right row of orb_gpu_stereo_matches_device; the keypoints are taken as undistorted, i.e. a camera without
+ * distortion coefficients as in src/Frame.cc:406-412).  `stream` = the stream that produced them (NULL: already
+ * complete).  The arrays are copied; the caller may reuse them after the call returns. */
+int orb_gpu_frame_from_device(OrbGpuFrame* f, const OrbKeyPoint* d_kps, const uint8_t* d_desc, const float* d_u_right,
+                              int n, OrbFrameGrid grid, void* stream);
+/* orb_gpu_search_by_projection / orb_gpu_search_windowed (below) against a resident frame: same arguments without
+ * the target arrays, same results. */
+int orb_gpu_frame_search_by_projection(OrbGpuFrame* f, const OrbProjQuery* q, const uint8_t* qdesc, int nq,
+                                       const float* scale_factors, int nlevels, float th, float nnratio, int th_high,
+                                       uint8_t* kp_blocked, int32_t* match_of_kp, int* nmatches);
+int orb_gpu_frame_search_windowed(OrbGpuFrame* f, const OrbWindowQuery* q, const uint8_t* qdesc, int nq, int th_accept,
+                                  int gate, const float* inv_level_sigma2, int nlevels, int check_orientation,
+                                  uint8_t* kp_blocked, int32_t* match_of_kp, int32_t* match_of_query, int* nmatches);
+
 /* Replaces Frame::ComputeStereoMatches (src/Frame.cc:466-640) whole: Hamming stage (:476-549), sub-pixel
  * refinement (11x11 SAD over 11 shifts + parabola, :551-620) and the median outlier filter (:623-639), run on
  * the unblurred pyramids (mvImagePyramid, include/ORBextractor.h:85) that `left` and `right` kept in device

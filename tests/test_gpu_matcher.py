@@ -141,6 +141,83 @@ def test_search_by_projection(gpu, oracle, th, stereo, seed):
     assert n_g == n_o and np.array_equal(match_g, match_o) and np.array_equal(frame["blocked"], blocked_o)
 
 
+@pytest.mark.parametrize("th,stereo,seed", [(1.0, False, 1), (5.0, True, 3)])
+def test_search_by_projection_resident_frame(gpu, oracle, th, stereo, seed):
+    """The same search against a frame kept in device memory (orb_gpu_frame_*): uploaded once, searched three times
+    with different blocked flags -- results identical to the oracle and to the host-pointer call."""
+    kps, desc, proj, qdesc, u_right, blocked, grid, sf = _projection_case(oracle, seed, th, stereo)
+    pg = np.zeros(len(proj), gpu.PROJ_DTYPE)
+    for f in ("u", "v", "ur", "level", "view_cos", "valid", "has_obs"):
+        pg[f] = proj[f]
+    res = gpu.GpuFrame().upload(kps, desc, u_right, grid)
+    assert len(res) == len(kps)
+    rng = np.random.default_rng(seed)
+    for rep in range(3):
+        b0 = blocked if rep == 0 else (rng.random(len(kps)) < 0.1 * rep).astype(np.uint8)
+        n_o, match_o, blocked_o = oracle.search_by_projection(proj, qdesc, kps, desc, u_right, grid, sf, th, 0.9, 100,
+                                                              b0.copy())
+        frame = dict(resident=res, scale_factors=sf, blocked=b0.copy())
+        n_g, match_g = gpu.ORBmatcher(0.9).SearchByProjection(frame, dict(proj=pg, desc=qdesc), th)
+        assert n_g == n_o and np.array_equal(match_g, match_o) and np.array_equal(frame["blocked"], blocked_o)
+
+
+@pytest.mark.parametrize("mode,th_accept,check_ori,seed", [
+    ("last_forward", 100, True, 2), ("kf", 64, True, 5), ("sim3", 50, False, 6)])
+def test_search_windowed_resident_frame(gpu, oracle, mode, th_accept, check_ori, seed):
+    kps, desc, q, qdesc, u_right, blocked, grid = _window_case(oracle, seed, mode)
+    gate = 1 if u_right is not None else 0
+    n_o, match_o, blocked_o, mq_o = oracle.search_windowed(q, qdesc, kps, desc, u_right, grid, th_accept, gate,
+                                                           check_ori, blocked.copy())
+    res = gpu.GpuFrame().upload(kps, desc, u_right, grid)
+    for _ in range(2):
+        frame = dict(resident=res, blocked=blocked.copy())
+        n_g, match_g, mq_g = gpu.ORBmatcher(0.9, checkOri=check_ori).SearchWindowed(
+            frame, _to_gpu_queries(gpu, q), qdesc, th_accept, gate)
+        assert n_g == n_o and np.array_equal(match_g, match_o) and np.array_equal(frame["blocked"], blocked_o)
+        assert np.array_equal(mq_g, mq_o)
+
+
+def test_resident_frame_from_extractor_outputs(gpu, oracle):
+    """Keypoints and descriptors go from orb_gpu_extract_batch_device straight into a resident frame (device to
+    device); a search against it equals the search against the same arrays brought through the host."""
+    import torch
+    W, H, nfeat = 640, 480, 2000
+    cap = nfeat + 24
+    img = synth.make_frame(W, H, 77)
+    ex = gpu.ORBextractor(nfeat, 1.2, 8, 20, 7, max_width=W, max_height=H, max_batch=2)
+    d_fr = torch.from_numpy(np.stack([img, img[::-1].copy()])).cuda()
+    d_k = torch.empty((2, cap, 28), dtype=torch.uint8, device="cuda")
+    d_d = torch.empty((2, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(2, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    ex.extract_batch_device(d_fr.data_ptr(), 2, W, H, W, W * H, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), None, st)
+    n = d_n.cpu().numpy()
+    grid = (0.0, 0.0, np.float32(64) / np.float32(W), np.float32(48) / np.float32(H))
+    f = 1
+    res = gpu.GpuFrame().from_device(d_k[f].data_ptr(), d_d[f].data_ptr(), None, int(n[f]), grid, st)
+    kps = d_k[f, :n[f]].cpu().numpy().view(gpu.KP_DTYPE).reshape(-1)
+    desc = d_d[f, :n[f]].cpu().numpy()
+    rng = np.random.default_rng(9)
+    M = 1500
+    src = rng.integers(0, len(kps), M)
+    q = np.zeros(M, oracle.WINDOW_DTYPE)
+    q["u"] = (kps["x"][src] + rng.normal(0, 3, M)).astype(np.float32)
+    q["v"] = (kps["y"][src] + rng.normal(0, 3, M)).astype(np.float32)
+    q["radius"] = 12.0
+    q["min_level"], q["max_level"] = kps["octave"][src] - 1, kps["octave"][src] + 1
+    q["angle"] = kps["angle"][src]
+    q["valid"] = 1
+    q["blocks"] = 1
+    qdesc = synth.flip_bits(desc[src], rng.integers(0, 50, M), rng)
+    m = gpu.ORBmatcher(0.9, checkOri=True)
+    qg = _to_gpu_queries(gpu, q)
+    n_a, match_a, mq_a = m.SearchWindowed(dict(resident=res), qg, qdesc, 100, 0)
+    n_b, match_b, mq_b = m.SearchWindowed(dict(kps=kps, desc=desc, u_right=None, grid=grid), qg, qdesc, 100, 0)
+    n_o, match_o, _, mq_o = oracle.search_windowed(q, qdesc, kps, desc, None, grid, 100, 0, True, np.zeros(len(kps), np.uint8))
+    assert n_a > 500 and n_a == n_b == n_o and np.array_equal(match_a, match_b) and np.array_equal(match_a, match_o)
+    assert np.array_equal(mq_a, mq_o)
+
+
 def test_stereo_match(gpu, oracle):
     W, H = synth.SHAPES["kitti"]
     left, right = synth.make_stereo_pair(W, H, 31)
