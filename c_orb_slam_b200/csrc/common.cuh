@@ -128,7 +128,8 @@ int upload_constants();
 // ---- match_tc5_kernels.cu: brute force on tcgen05 (256 queries per block, slices of whole 256-row tiles)
 int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
                           long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
-                          int32_t* o_second);
+                          int32_t* o_second, unsigned* g_thr, unsigned* g_ticket, int32_t* f_idx, int32_t* f_best,
+                          int32_t* f_second);
 size_t quadtree_smem_bytes(const Plan& p, int level);
 
 }  // namespace orbgpu

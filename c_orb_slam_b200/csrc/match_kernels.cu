@@ -452,18 +452,29 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   // host synchronisation in the call; the merge kernel is the last reader and the free is ordered after it)
   void* part = nullptr;
   int32_t *pi = d_idx, *pb = d_best, *ps = d_second;
+  unsigned *g_thr = nullptr, *g_ticket = nullptr;  // tcgen05 form: shared per-query threshold, slice tickets
   if (nslices > 1) {
     int rc = use_cached_pool(dev);
     if (rc) return rc;
-    ORB_CUDA_TRY(cudaMallocAsync(&part, (size_t)nslices * nq * 3 * sizeof(int32_t), s));
+    const size_t part_bytes = (size_t)nslices * nq * 3 * sizeof(int32_t);
+    const size_t extra = tc5 ? ((size_t)nq + (size_t)qblocks) * sizeof(unsigned) : 0;
+    ORB_CUDA_TRY(cudaMallocAsync(&part, part_bytes + extra, s));
     pi = (int32_t*)part; pb = pi + (size_t)nslices * nq; ps = pb + (size_t)nslices * nq;
+    if (tc5) {
+      static const bool no_share = [] { const char* e = getenv("ORB_GPU_BF_NO_SHARE"); return e && atoi(e); }();
+      g_thr = (unsigned*)((uint8_t*)part + part_bytes);
+      g_ticket = g_thr + nq;
+      ORB_CUDA_TRY(cudaMemsetAsync(g_thr, 0, extra, s));
+      if (no_share) g_thr = nullptr;
+    }
   }
   dim3 grid(qblocks, (unsigned)nslices);
   const uint4* q4 = (const uint4*)d_q; const uint4* db4 = (const uint4*)d_db;
   const int key = tc5 ? -2 : mma ? -1 : qpt * 2 + g_bf_variant;
   switch (key) {
     case -2: {
-      int rc = launch_bruteforce_tc5(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps);
+      int rc = launch_bruteforce_tc5(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps, g_thr, g_ticket, d_idx,
+                                     d_best, d_second);
       if (rc) { if (part) cudaFreeAsync(part, s); return rc; }
       break;
     }
@@ -479,7 +490,7 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   }
   count_launch();
   cudaError_t e = cudaGetLastError();
-  if (e == cudaSuccess && nslices > 1) {
+  if (e == cudaSuccess && nslices > 1 && !tc5) {  // the tcgen05 kernel merges its slices itself (last block per query block)
     merge_top2_kernel<<<(nq + 255) / 256, 256, 0, s>>>(pi, pb, ps, (int)nslices, nq, d_idx, d_best, d_second);
     count_launch();
     e = cudaGetLastError();

@@ -170,8 +170,11 @@ __device__ __forceinline__ void t5_scan16(const uint32_t (&v)[32], int col0, uns
 }
 // A 64-column chunk in which some query of the warp beats its running second best: after the first few thousand
 // rows of a slice that is one column in 64, so the quarter that holds it is found first and only it is merged.
+__device__ __forceinline__ uint32_t t5_thr_of(unsigned field) {  // packed 64 * S of the distance field S + 256
+  return ((field * 64u - 16384u) & 0xffffu) * 0x10001u;
+}
 __device__ __forceinline__ void t5_scan64(const uint32_t (&v)[32], int col0, int rows, unsigned& best,
-                                          unsigned& second, uint32_t& thr2) {
+                                          unsigned& second, uint32_t& thr2, unsigned floor_f) {
   if (rows - col0 >= 64) {
     t5_scan16<0>(v, col0, best, second, thr2);
     t5_scan16<1>(v, col0, best, second, thr2);
@@ -180,13 +183,18 @@ __device__ __forceinline__ void t5_scan64(const uint32_t (&v)[32], int col0, int
   } else {
     t5_merge64<true>(v, col0, rows, best, second);
   }
-  if (second) thr2 = (((second >> 22) * 64u - 16384u) & 0xffffu) * 0x10001u;
+  // the filter is the running second best of this slice or, when it is tighter, what the other slices of the
+  // query block have published (floor_f, already one step looser: a tie with another slice must still get through)
+  if (second || floor_f) thr2 = t5_thr_of(max(second >> 22, floor_f));
 }
 
 __global__ void __launch_bounds__(kT5Threads, 1)
 bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, long long ndb,
                       long long slice_rows, int32_t idx_base, int32_t* __restrict__ o_idx,
-                      int32_t* __restrict__ o_best, int32_t* __restrict__ o_second) {
+                      int32_t* __restrict__ o_best, int32_t* __restrict__ o_second,
+                      unsigned* __restrict__ g_thr /*[nq] shared second-best field of a query over the slices, or null*/,
+                      unsigned* __restrict__ g_ticket /*[query blocks] slices finished*/, int nslices,
+                      int32_t* __restrict__ f_idx, int32_t* __restrict__ f_best, int32_t* __restrict__ f_second) {
   extern __shared__ __align__(128) uint8_t t5_smem[];
   uint8_t* s_a = t5_smem;
   uint8_t* s_b = t5_smem + 2 * kT5ATile;
@@ -252,6 +260,12 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
     const int acc = warp >> 2;
     unsigned best = 0, second = 0;
     uint32_t thr2 = 0x80008000u;  // 64 * S of the running second best in both halves; -32768 = none yet
+    // Every slice of a query block starts its scan cold; the slices publish their running second best per query
+    // (atomicMax on its distance field) and adopt the others' -- less one step, so that a row that only TIES what
+    // another slice holds still arrives (the lowest row wins ties in the final merge).  A row filtered this way is
+    // below two rows of the same query elsewhere: the merged top-2 is unchanged, and the warm-up is shared.
+    unsigned floor_f = 0, published = 0;
+    const bool share = g_thr != nullptr && qbase + t < nq;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * 256;
     // three buffers of 64 packed columns: 13 warps put four on one scheduler, which caps a thread at 128 registers
     uint32_t va[32], vb[32], vc[32];
@@ -265,16 +279,26 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       tmem_wait(va);
       tmem_wait(vb);
       tmem_wait(vc);
-      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0, rows, best, second, thr2);
+      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0, rows, best, second, thr2, floor_f);
       tmem_ld64p(va, taddr + 192);  // the fourth quarter lands while the second and third are filtered
       const bool hb = __any_sync(0xffffffffu, t5_hit(t5_rowmax(vb), thr2));
       const bool hc = __any_sync(0xffffffffu, t5_hit(t5_rowmax(vc), thr2));
       tmem_wait(va);
       tc_fence_before();
       mbar_arrive(bar(6 + acc));  // the accumulator is in registers: the next MMA into it overlaps the rest of the scan
-      if (hb) t5_scan64(vb, col0 + 64, rows, best, second, thr2);
-      if (hc) t5_scan64(vc, col0 + 128, rows, best, second, thr2);
-      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0 + 192, rows, best, second, thr2);
+      if (hb) t5_scan64(vb, col0 + 64, rows, best, second, thr2, floor_f);
+      if (hc) t5_scan64(vc, col0 + 128, rows, best, second, thr2, floor_f);
+      if (__any_sync(0xffffffffu, t5_hit(t5_rowmax(va), thr2))) t5_scan64(va, col0 + 192, rows, best, second, thr2, floor_f);
+      if (share && (tile < 32 || (tile & 7) == 7)) {
+        const unsigned mine = second >> 22;
+        unsigned seen;
+        if (mine > published) { seen = atomicMax(g_thr + qbase + t, mine); published = mine; }
+        else seen = __ldcg(g_thr + qbase + t);
+        if (seen > floor_f + 1) {
+          floor_f = seen - 1;
+          if (floor_f > mine) thr2 = t5_thr_of(floor_f);
+        }
+      }
     }
     const int qi = qbase + t;
     if (qi < nq) {
@@ -288,6 +312,7 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       o_second[o] = sd;
       // a row at distance 256 never beats the initial best of the reference's scan (strict '<')
       o_idx[o] = (best && bd < 256) ? (int32_t)(idx_base + row0 + (0x3fffffu - (best & 0x3fffffu))) : -1;
+      if (nslices > 1) __threadfence();  // the slice's result is visible before this block takes its ticket
     }
   } else if (warp == kT5EpiWarps) {
     // ---- MMA issuer
@@ -357,15 +382,37 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kT5TmemCols) : "memory");
   }
+  // ---- the block that finishes a query block's last slice merges the slices (ascending rows, the reference's
+  // update rule on (best, second) pairs: same as merge_top2_kernel) -- no separate merge launch
+  if (nslices > 1) {
+    if (t == 0) s_tmem[1] = atomicAdd(g_ticket + blockIdx.x, 1u) == (unsigned)(nslices - 1);
+    __syncthreads();
+    if (s_tmem[1] && t < kT5Queries && qbase + t < nq) {
+      __threadfence();
+      const int qi = qbase + t;
+      int b = 256, sd = 256, id = -1;
+      for (int k = 0; k < nslices; ++k) {
+        const size_t o = (size_t)k * nq + qi;
+        const int ik = __ldcg(o_idx + o), bk = __ldcg(o_best + o), sk = __ldcg(o_second + o);
+        if (ik < 0) continue;
+        if (bk < b) { sd = min(b, sk); b = bk; id = ik; }
+        else sd = min(sd, bk);
+      }
+      f_idx[qi] = id; f_best[qi] = b; f_second[qi] = sd;
+    }
+    if (s_tmem[1] && t == 0) g_ticket[blockIdx.x] = 0;  // ready for the next call
+  }
 }
 
 int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
                           long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
-                          int32_t* o_second) {
+                          int32_t* o_second, unsigned* g_thr, unsigned* g_ticket, int32_t* f_idx, int32_t* f_best,
+                          int32_t* f_second) {
   ORB_CUDA_TRY(cudaFuncSetAttribute(bruteforce_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kT5SmemBytes));
   bruteforce_tc5_kernel<<<grid, kT5Threads, kT5SmemBytes, s>>>(q, nq, db, ndb, slice_rows, idx_base, o_idx, o_best,
-                                                              o_second);
+                                                              o_second, g_thr, g_ticket, (int)grid.y, f_idx, f_best,
+                                                              f_second);
   return ORB_GPU_OK;
 }
 

@@ -65,6 +65,62 @@ grid_build_kernel(const OrbKeyPoint* __restrict__ kps, int nk, int nkpad, OrbFra
   }
 }
 
+// ---- the kTopK best candidates of a query, sorted by (distance, position): one warp ------------------------------
+constexpr int kTopK = 8;
+__device__ __forceinline__ void topk_of_query(const uint32_t* entries /*may have been written by this warp*/, int beg,
+                                              int end, uint2* row /*[kTopK]: (dist << 20 | position, entry)*/, int lane) {
+  unsigned last = 0;
+  for (int t = 0; t < kTopK; ++t) {
+    unsigned best = 0xffffffffu;
+    for (int e = beg + lane; e < end; e += 32) {
+      const unsigned key = (((entries[e] >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
+      if ((t == 0 || key > last) && key < best) best = key;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) row[t] = make_uint2(best, best == 0xffffffffu ? 0u : entries[beg + (best & 0xfffffu)]);
+    if (best == 0xffffffffu) {
+      if (lane == 0) for (int u = t + 1; u < kTopK; ++u) row[u] = make_uint2(0xffffffffu, 0u);
+      break;
+    }
+    last = best;
+  }
+}
+
+// exclusive scan of in[0..n) into out[0..n], out[n] = total, by one whole block
+__device__ __forceinline__ int block_scan_counts(const int* in, int n, int* out, int* s_part /*[33]*/) {
+  const int T = blockDim.x, t = threadIdx.x;
+  const int chunk = (n + T - 1) / T, lo = min(t * chunk, n), hi = min(lo + chunk, n);
+  int sum = 0;
+  for (int k = lo; k < hi; ++k) sum += in[k];
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((t & 31) >= o) incl += v;
+  }
+  if ((t & 31) == 31) s_part[t >> 5] = incl;
+  __syncthreads();
+  if (t < 32) {
+    const int nw = T >> 5;
+    const int w = t < nw ? s_part[t] : 0;
+    int wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, wi, o);
+      if (t >= o) wi += v;
+    }
+    if (t < nw) s_part[t] = wi - w;
+    if (t == nw - 1) s_part[32] = wi;
+  }
+  __syncthreads();
+  int run = s_part[t >> 5] + incl - sum;
+  for (int k = lo; k < hi; ++k) { out[k] = run; run += in[k]; }
+  const int total = s_part[32];
+  if (t == 0) out[n] = total;
+  return total;
+}
+
 // ---- candidates of every query, in GetFeaturesInArea order -----------------------------------
 // FILL == false: count only.  Entry = kp index | dist << 16 | octave << 25.
 template <bool FILL>
@@ -75,16 +131,24 @@ window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __re
                          const float* __restrict__ inv_sigma2,
                          const uint32_t* __restrict__ sorted, const int* __restrict__ cell_start,
                          int* __restrict__ counts, const int* __restrict__ offsets,
-                         uint32_t* __restrict__ entries, int ent_cap, int* __restrict__ overflow) {
+                         uint32_t* __restrict__ entries, int ent_cap, int* __restrict__ overflow,
+                         uint2* __restrict__ topk = nullptr /*FILL: also the kTopK best of every query*/,
+                         int* __restrict__ ticket = nullptr /*!FILL: the last block to finish scans the counts ...*/,
+                         int* __restrict__ scan_out = nullptr /*... into these offsets [nq + 1] ...*/,
+                         int* __restrict__ tail = nullptr /*... and resets (nmatches, total, overflow)*/) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= nq) return;
-  if (FILL && offsets[nq] > ent_cap) {  // the entry pool is too small: flag it, the host grows the pool and reruns
-    if (warp == 0 && lane == 0) *overflow = 1;
-    return;
+  const bool active = warp < nq;
+  if (FILL) {
+    if (!active) return;
+    if (offsets[nq] > ent_cap) {  // the entry pool is too small: flag it, the host grows the pool and reruns
+      if (warp == 0 && lane == 0) *overflow = 1;
+      return;
+    }
   }
-  const OrbWindowQuery p = q[warp];
+  OrbWindowQuery p = OrbWindowQuery();
+  if (active) p = q[warp];
   int n = 0;
-  if (p.valid) {
+  if (active && p.valid) {
     const float rad = p.radius;
     const int min_level = p.min_level, max_level = p.max_level;
     const bool check = min_level > 0 || max_level >= 0;  // bCheckLevels (Frame.cc:348)
@@ -134,10 +198,33 @@ window_candidates_kernel(const OrbWindowQuery* __restrict__ q, const uint4* __re
       }
     }
   }
-  if (!FILL && lane == 0) counts[warp] = n;
+  if (FILL) {
+    if (topk) {
+      __syncwarp();
+      topk_of_query(entries, offsets[warp], offsets[warp] + n, topk + (size_t)warp * kTopK, lane);
+    }
+    return;
+  }
+  if (active && lane == 0) counts[warp] = n;
+  if (ticket) {  // every thread of every block gets here
+    __shared__ int s_last, s_part[33];
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      const int total = block_scan_counts(counts, nq, scan_out, s_part);
+      if (threadIdx.x == 0) {
+        if (tail) { tail[0] = 0; tail[1] = total; tail[2] = 0; }
+        *ticket = 0;  // ready for the next call
+      }
+    }
+  }
 }
 
-__global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int n, int* out /*[n+1]*/) {
+__global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int n, int* out /*[n+1]*/,
+                                                              int* tail = nullptr /*[3]: nmatches, total, overflow*/) {
   __shared__ int s_part[1024];
   const int T = blockDim.x, t = threadIdx.x;
   const int chunk = (n + T - 1) / T, lo = min(t * chunk, n), hi = min(lo + chunk, n);
@@ -149,41 +236,24 @@ __global__ void __launch_bounds__(1024) exclusive_scan_kernel(const int* in, int
     int run = 0;
     for (int k = 0; k < T; ++k) { const int v = s_part[k]; s_part[k] = run; run += v; }
     out[n] = run;
+    if (tail) { tail[0] = 0; tail[1] = run; tail[2] = 0; }
   }
   __syncthreads();
   int run = s_part[t];
   for (int k = lo; k < hi; ++k) { out[k] = run; run += in[k]; }
 }
 
-// ---- the kTopK best candidates of every query, sorted by (distance, position) -------------------
+// ---- the kTopK best candidates of every query (stand-alone form for the searches over vocabulary nodes) ---------
 // The ordered resolution below re-evaluates every query once per round; with its candidates pre-sorted a
 // round costs one thread and a handful of loads per query instead of a warp scan of the whole list.  A query
 // whose kTopK best are all taken falls back to the full scan (rare).  One warp per query, any number of blocks.
-constexpr int kTopK = 8;
 __global__ void __launch_bounds__(256)
 topk_entries_kernel(const int* __restrict__ offsets, const uint32_t* __restrict__ entries, int nq,
-                    uint2* __restrict__ topk /*[nq][kTopK]: (dist << 20 | position, entry)*/, int ent_cap = INT_MAX) {
+                    uint2* __restrict__ topk /*[nq][kTopK]*/, int ent_cap = INT_MAX) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= nq) return;
   if (offsets[nq] > ent_cap) return;
-  const int beg = offsets[warp], end = offsets[warp + 1];
-  unsigned last = 0;
-  for (int t = 0; t < kTopK; ++t) {
-    unsigned best = 0xffffffffu;
-    for (int e = beg + lane; e < end; e += 32) {
-      const unsigned key = (((entries[e] >> 16) & 0x1ffu) << 20) | (unsigned)(e - beg);
-      if ((t == 0 || key > last) && key < best) best = key;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-    if (lane == 0)
-      topk[(size_t)warp * kTopK + t] = make_uint2(best, best == 0xffffffffu ? 0u : entries[beg + (best & 0xfffffu)]);
-    if (best == 0xffffffffu) {
-      if (lane == 0) for (int u = t + 1; u < kTopK; ++u) topk[(size_t)warp * kTopK + u] = make_uint2(0xffffffffu, 0u);
-      break;
-    }
-    last = best;
-  }
+  topk_of_query(entries, offsets[warp], offsets[warp + 1], topk + (size_t)warp * kTopK, lane);
 }
 
 // ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642) on the 30 bin sizes
@@ -211,7 +281,8 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
                       int ratio_rule, int th_accept, int check_ori, uint8_t* blocked_g /*in/out [nk]*/,
                       int* claim_a, int* claim_b, int* minclaim_g /*[nk]*/,
                       int32_t* __restrict__ match_of_kp, int32_t* __restrict__ match_of_query,
-                      int* __restrict__ nmatches, int use_smem = 0, int ent_cap = INT_MAX) {
+                      int* __restrict__ nmatches, int use_smem = 0, int ent_cap = INT_MAX,
+                      uint8_t* blocked_out = nullptr /*use_smem only: final flags go here instead of blocked_g*/) {
   extern __shared__ __align__(16) int s_dyn[];
   __shared__ int s_changed, s_count;
   __shared__ int s_hist[ORB_GPU_HISTO_LENGTH], s_keep[3];
@@ -341,8 +412,10 @@ window_resolve_kernel(const OrbWindowQuery* __restrict__ q, int nq, const OrbKey
     const int k = prev[i];
     match_of_query[i] = (k >= 0 && match_of_kp[k] != -2) ? k : -1;
   }
-  if (use_smem)
-    for (int k = t; k < nk; k += T) blocked_g[k] = blocked[k];
+  if (use_smem) {
+    uint8_t* dst = blocked_out ? blocked_out : blocked_g;
+    for (int k = t; k < nk; k += T) dst[k] = blocked[k];
+  }
   if (t == 0) *nmatches = s_count;
 }
 
@@ -731,7 +804,6 @@ int frame_search(OrbGpuFrame* f, const OrbWindowQuery* q, const uint8_t* qdesc, 
   int32_t* d_match = (int32_t*)dout;
   int32_t* d_mq = (int32_t*)(dout + r_mq);
   int* d_tail = (int*)(dout + r_tail);  // nmatches, total, overflow
-  ORB_CUDA_TRY(cudaMemsetAsync(d_tail, 0, 16, s));
   const int blocks = (nq * 32 + 255) / 256;
   // shared-memory state of the resolve kernel: prev, cur [nq], minclaim [nk], blocked [nk], query flags [nq]
   const size_t rs_smem = (size_t)nq * 8 + (size_t)nk * 4 + up16((size_t)nk) + up16((size_t)nq);
@@ -740,35 +812,37 @@ int frame_search(OrbGpuFrame* f, const OrbWindowQuery* q, const uint8_t* qdesc, 
     if (top2) ORB_CUDA_TRY(cudaFuncSetAttribute(window_resolve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
     else ORB_CUDA_TRY(cudaFuncSetAttribute(window_resolve_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
   }
+  // counts, then (in the last block to finish) their scan into offsets and the reset of the result tail
   window_candidates_kernel<false><<<blocks, 256, 0, s>>>(d_q, d_qd, nq, d_kps, d_desc, d_ur, f->grid, gate, d_sig,
-      f->sorted.as<uint32_t>(), f->cell.as<int>(), f->cnt.as<int>(), nullptr, nullptr, 0, nullptr);
-  exclusive_scan_kernel<<<1, 1024, 0, s>>>(f->cnt.as<int>(), nq, f->off.as<int>());
-  count_launch(2);
+      f->sorted.as<uint32_t>(), f->cell.as<int>(), f->cnt.as<int>(), nullptr, nullptr, 0, nullptr, nullptr,
+      f->flag.as<int>(), f->off.as<int>(), d_tail);
+  count_launch(1);
+  uint8_t* d_blk_out = use_smem ? dout + r_blk : nullptr;
   for (int attempt = 0; attempt < 2; ++attempt) {
     const int ent_cap = (int)std::min<size_t>(f->ent.bytes / 4, (size_t)INT_MAX);
     window_candidates_kernel<true><<<blocks, 256, 0, s>>>(d_q, d_qd, nq, d_kps, d_desc, d_ur, f->grid, gate, d_sig,
-        f->sorted.as<uint32_t>(), f->cell.as<int>(), nullptr, f->off.as<int>(), f->ent.as<uint32_t>(), ent_cap, d_tail + 2);
-    topk_entries_kernel<<<blocks, 256, 0, s>>>(f->off.as<int>(), f->ent.as<uint32_t>(), nq, f->top.as<uint2>(), ent_cap);
+        f->sorted.as<uint32_t>(), f->cell.as<int>(), nullptr, f->off.as<int>(), f->ent.as<uint32_t>(), ent_cap, d_tail + 2,
+        f->top.as<uint2>());  // entries and the kTopK best of every query in one pass
     if (top2)
       window_resolve_kernel<true><<<1, 1024, use_smem ? rs_smem : 0, s>>>(d_q, nq, d_kps, nk, f->off.as<int>(),
           f->ent.as<uint32_t>(), f->top.as<uint2>(), nnratio, 0, th_accept, check_ori, d_blk, f->ca.as<int>(), f->cb.as<int>(),
-          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap);
+          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap, d_blk_out);
     else
       window_resolve_kernel<false><<<1, 1024, use_smem ? rs_smem : 0, s>>>(d_q, nq, d_kps, nk, f->off.as<int>(),
           f->ent.as<uint32_t>(), f->top.as<uint2>(), nnratio, 0, th_accept, check_ori, d_blk, f->ca.as<int>(), f->cb.as<int>(),
-          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap);
-    count_launch(3);
+          f->minc.as<int>(), d_match, d_mq, d_tail, use_smem, ent_cap, d_blk_out);
+    count_launch(2);
     ORB_CUDA_TRY(cudaGetLastError());
-    // the blocked flags travel back inside the output block
-    ORB_CUDA_TRY(cudaMemcpyAsync(dout + r_blk, d_blk, (size_t)nk, cudaMemcpyDeviceToDevice, s));
-    ORB_CUDA_TRY(cudaMemcpyAsync(d_tail + 1, f->off.as<int>() + nq, 4, cudaMemcpyDeviceToDevice, s));
+    // the blocked flags travel back inside the output block (the resolve kernel writes them there when its state is
+    // in shared memory)
+    if (!d_blk_out) ORB_CUDA_TRY(cudaMemcpyAsync(dout + r_blk, d_blk, (size_t)nk, cudaMemcpyDeviceToDevice, s));
     ORB_CUDA_TRY(cudaMemcpyAsync(f->hout.p, dout, out_bytes, cudaMemcpyDeviceToHost, s));
     ORB_CUDA_TRY(cudaStreamSynchronize(s));
     const int* tail = (const int*)((const uint8_t*)f->hout.p + r_tail);
     if (!tail[2]) break;
     if (attempt == 1) return ORB_GPU_ERR_CAPACITY;
     if ((rc = f->ent.ensure((size_t)tail[1] * 4))) return rc;  // grow the entry pool to the counted total and rerun
-    ORB_CUDA_TRY(cudaMemsetAsync(d_tail, 0, 16, s));
+    ORB_CUDA_TRY(cudaMemsetAsync(d_tail + 2, 0, 4, s));
   }
   const uint8_t* hout = (const uint8_t*)f->hout.p;
   std::memcpy(match_of_kp, hout, (size_t)nk * 4);
@@ -822,6 +896,10 @@ int orb_gpu_frame_create(int device, OrbGpuFrame** out) {
   f->device = device;
   const cudaError_t e = cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { set_last_error("cudaStreamCreate (frame)", e); delete f; return ORB_GPU_ERR_CUDA; }
+  if (f->flag.ensure(16) != ORB_GPU_OK || cudaMemset(f->flag.p, 0, 16) != cudaSuccess) {  // scan ticket of the count kernel
+    orb_gpu_frame_destroy(f);
+    return ORB_GPU_ERR_CUDA;
+  }
   *out = f;
   return ORB_GPU_OK;
 }
@@ -1062,9 +1140,14 @@ int orb_gpu_search_by_bow(const OrbBucketQuery* q, int nq, const int32_t* cand2,
   TmpDevW dtop;
   if ((rc = dtop.alloc((size_t)nq * kTopK * sizeof(uint2)))) return rc;
   topk_entries_kernel<<<(nq * 32 + 255) / 256, 256>>>(doff.as<int>(), dent.as<uint32_t>(), nq, dtop.as<uint2>());
-  window_resolve_kernel<true><<<1, 1024>>>(dwq.as<OrbWindowQuery>(), nq, dk2.as<OrbKeyPoint>(), n2, doff.as<int>(),
+  // claims, per-keypoint minima and flags of the fixpoint rounds in shared memory when they fit
+  const size_t rs_smem = (size_t)nq * 8 + (size_t)n2 * 4 + (((size_t)n2 + 15) & ~(size_t)15) + (((size_t)nq + 15) & ~(size_t)15);
+  const int use_smem = rs_smem <= 200 * 1024;
+  if (use_smem && rs_smem > 48 * 1024)
+    ORB_CUDA_TRY(cudaFuncSetAttribute(window_resolve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem));
+  window_resolve_kernel<true><<<1, 1024, use_smem ? rs_smem : 0>>>(dwq.as<OrbWindowQuery>(), nq, dk2.as<OrbKeyPoint>(), n2, doff.as<int>(),
       dent.as<uint32_t>(), dtop.as<uint2>(), nnratio, 1, th_accept, check_orientation, dblk.as<uint8_t>(), dca.as<int>(), dcb.as<int>(),
-      dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>());
+      dmin.as<int>(), dmatch.as<int32_t>(), dmq.as<int32_t>(), dn.as<int>(), use_smem);
   count_launch(3);
   ORB_CUDA_TRY(cudaGetLastError());
   std::vector<int32_t> mq((size_t)nq);

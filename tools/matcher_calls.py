@@ -32,6 +32,9 @@ mm = orb.ORBmatcher(0.9)
 for _ in range(reps):
     frame = dict(kps=kps, desc=desc, u_right=None, grid=grid, scale_factors=sf8, blocked=np.zeros(nk, np.uint8))
     mm.SearchByProjection(frame, dict(proj=proj, desc=qdesc), 1.0)
+res = orb.GpuFrame().upload(kps, desc, None, grid)
+for _ in range(reps):   # the same search against a resident frame
+    mm.SearchByProjection(dict(resident=res, scale_factors=sf8, blocked=np.zeros(nk, np.uint8)), dict(proj=proj, desc=qdesc), 1.0)
 perm = rng.permutation(nk)
 desc2 = synth.flip_bits(desc[perm], rng.integers(0, 45, nk), rng)
 k2 = kps[perm].copy()
