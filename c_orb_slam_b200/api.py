@@ -83,6 +83,8 @@ def lib():
         L.orb_gpu_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.orb_gpu_destroy.argtypes = [C.c_void_p]
+        L.orb_gpu_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.POINTER(C.c_int)]
         L.orb_gpu_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t,
                                             C.c_size_t, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orb_gpu_extract_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,

@@ -101,13 +101,13 @@ resize_level_kernel(LevelGeom src, LevelGeom dst) {
 // 32-bit store for four pixels.  Columns 0,1 take their tap pairs from words (0,1); columns 2,3 from words (1,2) when
 // column 2 starts in word 1 or later, else from (0,1) as well -- a per-thread constant choice (two selects per row).
 __global__ void __launch_bounds__(256)
-resize_level4_kernel(LevelGeom src, LevelGeom dst) {
+resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows per block: 4, 8 or 16*/) {
   __shared__ unsigned s_off0[kRzRows], s_off1[kRzRows];
   __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];
   const int f = blockIdx.y;
-  const int dy0 = blockIdx.x * kRzRows;
+  const int dy0 = blockIdx.x * rows;
   const int rstep = src.pitch >> 2;
-  if (threadIdx.x < kRzRows) {
+  if (threadIdx.x < rows) {
     const int dy = min(dy0 + (int)threadIdx.x, dst.h - 1);
     const int sy0 = dst.yofs[dy];
     s_off0[threadIdx.x] = (unsigned)(sy0 * rstep);
@@ -120,7 +120,7 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst) {
   const int last_word = rstep - 1;
   const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
   uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
-  const int nrows = min(kRzRows, dst.h - dy0);
+  const int nrows = min(rows, dst.h - dy0);
   for (int t = threadIdx.x; t < nt; t += blockDim.x) {
     int x[4];
     unsigned wt[4];
@@ -141,7 +141,7 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst) {
     const unsigned sel23 = (unsigned)o2 | ((unsigned)(o2 + 1) << 4) | ((unsigned)o3 << 8) | ((unsigned)(o3 + 1) << 12);
     uint8_t* drow = dbase + 4 * t;
 #pragma unroll 1
-    for (int i0 = 0; i0 < kRzRows; i0 += kRzBatch) {
+    for (int i0 = 0; i0 < rows; i0 += kRzBatch) {
       unsigned w[kRzBatch][6];
 #pragma unroll
       for (int k = 0; k < kRzBatch; ++k) {
@@ -170,12 +170,15 @@ int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
   const LevelGeom& d = p.lv[level];
   static const bool two_col = [] { const char* e = getenv("ORB_GPU_RESIZE2"); return e && atoi(e); }();
   dim3 grid((d.h + kRzRows - 1) / kRzRows, nframes);
+  // a few frames: bands of 4 rows instead of 16, so that one frame's level still spreads over the SMs
+  const int rows4 = (long long)grid.x * nframes >= 2 * 148 ? kRzRows : kRzBatch;
   // the four-column form needs the three-word tap window (scaleFactor <= 2) and 4-byte aligned destination rows
   const bool four = !two_col && (long long)p.lv[level - 1].w <= 2LL * d.w + 1 && (d.pitch & 3) == 0 &&
                     (d.frame_stride & 3) == 0;
   if (four) {
     const int nt = (d.w + 3) >> 2;
-    resize_level4_kernel<<<grid, min(256, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d);
+    grid.x = (d.h + rows4 - 1) / rows4;
+    resize_level4_kernel<<<grid, min(256, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d, rows4);
   } else {
     const int nt = (d.w + 1) >> 1;
     resize_level_kernel<<<grid, min(512, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d);
@@ -275,7 +278,7 @@ __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cell = blockIdx.x * kFastWarps + warp;
+  const int cell = blockIdx.x * (blockDim.x >> 5) + warp;
   if (cell >= p.cells_per_frame) return;
   const int f = blockIdx.y;
   // cell ROI (:789-806), precomputed on the host: x | y << 16, cw | ch << 8 | level << 16 (cw == 0: skipped cell)
@@ -471,8 +474,10 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
   // the opt-in belongs to the current device's context: set it on every launch rather than cache it process-wide
   if (smem > 48 * 1024)
     ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const dim3 grid((p.cells_per_frame + kFastWarps - 1) / kFastWarps, nframes);
-  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(p, sc, L);
+  // a few frames: 2 cells per block instead of 8, so that the cells of one frame fill the SMs
+  const int wpb = (long long)p.cells_per_frame * nframes >= 16 * 148 ? kFastWarps : 2;
+  const dim3 grid((p.cells_per_frame + wpb - 1) / wpb, nframes);
+  fast_cells_kernel<<<grid, wpb * 32, smem * wpb / kFastWarps, s>>>(p, sc, L);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
@@ -655,7 +660,8 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   int* s_cb = s_nch + ncap;                                      // [ncap] creation base
   int* s_sv = s_cb + ncap;                                       // [ncap] survivor flags/ranks
   int* s_bnd = s_sv + ncap;                                      // [3*ncap] rank-ordered scratch
-  int* s_cell = s_bnd + 3 * ncap;                                // [ncells+1]
+  int* s_cbnd = s_bnd + 3 * ncap;                                // [3*ncap] child boundaries found while counting
+  int* s_cell = s_cbnd + 3 * ncap;                               // [ncells+1]
   int* s_warp = s_cell + ncells + 1;                             // [72]
   __shared__ int s_misc[8];
 
@@ -833,6 +839,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         if (nd.end - nd.start > 1 && (nd.depth_new & 0xff) < kCodeDepth) {
           int b[5];
           child_bounds(keys, nd, b);
+          s_cbnd[3 * i] = b[1]; s_cbnd[3 * i + 1] = b[2]; s_cbnd[3 * i + 2] = b[3];  // reused when the node is split
           nch = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
           sv = 0;
         }
@@ -866,6 +873,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         const int pos = (int)((~s_sort[j]) & 0xffff);
         int b[5];
         child_bounds(keys, cur[pos], b);
+        s_cbnd[3 * pos] = b[1]; s_cbnd[3 * pos + 1] = b[2]; s_cbnd[3 * pos + 2] = b[3];
         r_nch[j] = (b[1] > b[0]) + (b[2] > b[1]) + (b[3] > b[2]) + (b[4] > b[3]);
       }
       __syncthreads();
@@ -907,8 +915,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         keep.depth_new &= 0xff;
         nxt[K + s_sv[i]] = keep;
       } else {
-        int b[5];
-        child_bounds(keys, nd, b);
+        const int b[5] = {nd.start, s_cbnd[3 * i], s_cbnd[3 * i + 1], s_cbnd[3 * i + 2], nd.end};
         const int depth = (nd.depth_new & 0xff) + 1;
         const int shift = 24 - 2 * depth;
         int m_idx = s_cb[i];
@@ -961,7 +968,7 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
   const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
   return (size_t)kQtSmemKeys * 12 + (size_t)(kQtBins / 2 + 4) * 4 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
-         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 72) * 4 + 64;
+         (size_t)ncap * 4 * 9 + (size_t)(ncells + 1 + 72) * 4 + 64;
 }
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
@@ -1183,7 +1190,7 @@ __device__ __forceinline__ int round_half_even(float v) {
 // are |v| <= umax[|u|] (the disc is symmetric), 31 coalesced byte loads, shuffle reduction.
 __global__ void __launch_bounds__(kOdWarps * 32, 5)
 orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                   int capacity, int* __restrict__ n_out) {
+                   int capacity, int* __restrict__ n_out, int slots_per_warp) {
   __shared__ float4 s_pat[256];
   __shared__ uint32_t s_tile[kOdWarps][kOdRows * kOdWords];
   __shared__ uint32_t s_ic[kOdWarps][kIcRows * kIcWords];  // unblurred 31-row patch, 9 aligned words per row
@@ -1224,8 +1231,8 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   const int ic_r = lane / kIcWords, ic_c = lane - ic_r * kIcWords;  // (row, word) inside a 3-row step, lanes 0..26
   const unsigned ic_dst = (unsigned)__cvta_generic_to_shared(my_ic + ic_r * kIcWords + ic_c);
 
-  for (int it = 0; it < kOdSlotsPerWarp; ++it) {
-    const int slot = blockIdx.x * kOdSlotsPerBlock + it * kOdWarps + warp;
+  for (int it = 0; it < slots_per_warp; ++it) {
+    const int slot = blockIdx.x * (slots_per_warp * kOdWarps) + it * kOdWarps + warp;
     if (slot >= p.slots_per_frame) break;
     int level = 0;
 #pragma unroll
@@ -1345,8 +1352,10 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
 
 int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
-  const dim3 grid((p.slots_per_frame + kOdSlotsPerBlock - 1) / kOdSlotsPerBlock, nframes);
-  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out);
+  // a few frames: one keypoint slot per warp instead of four (more, shorter blocks)
+  const int spw = (long long)p.slots_per_frame * nframes >= 4 * kOdSlotsPerBlock * 148 ? kOdSlotsPerWarp : 1;
+  const dim3 grid((p.slots_per_frame + spw * kOdWarps - 1) / (spw * kOdWarps), nframes);
+  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out, spw);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;

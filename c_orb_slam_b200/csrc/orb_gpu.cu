@@ -110,6 +110,9 @@ struct OrbGpuExtractor {
   cudaGraphExec_t graph_exec = nullptr;
   int graph_nlaunch = 0;
   int plan_generation = 0;
+  // one- to four-frame host calls go through pinned staging blocks (one async copy each way, exact-size unpack)
+  void* pin_in = nullptr; size_t pin_in_bytes = 0;
+  void* pin_out = nullptr; size_t pin_out_bytes = 0;
   // blur depends only on the pyramid: it runs on a side stream next to FAST + quadtree and joins before the
   // descriptors (one side stream and two events per compute stream, created on first use)
   struct Fork { cudaStream_t side = nullptr; cudaEvent_t forked = nullptr, joined = nullptr; };
@@ -466,6 +469,14 @@ int orb_gpu_destroy(OrbGpuExtractor* h) {
   cudaStreamSynchronize(h->s_h2d); cudaStreamSynchronize(h->s_d2h);
   for (cudaStream_t a : h->s_alt) if (a) cudaStreamSynchronize(a);
   if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+  if (h->pin_in) cudaFreeHost(h->pin_in);
+  if (h->pin_out) cudaFreeHost(h->pin_out);
+  for (auto& kv : h->forks) {
+    cudaStreamSynchronize(kv.second.side);
+    cudaStreamDestroy(kv.second.side);
+    cudaEventDestroy(kv.second.forked);
+    cudaEventDestroy(kv.second.joined);
+  }
   for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
   for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
   cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
@@ -624,8 +635,28 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       OrbKeyPoint* dk = (OrbKeyPoint*)h->out_kps.p;
       uint8_t* dd = (uint8_t*)h->out_desc.p;
       int* dn = (int*)h->out_n.p;
-      ORB_CUDA_TRY(cudaMemcpyAsync(stage, frames + (size_t)f0 * frame_stride, (size_t)(nb - 1) * frame_stride + frame_bytes,
-                                   cudaMemcpyHostToDevice, s));
+      const size_t in_bytes = (size_t)(nb - 1) * frame_stride + frame_bytes;
+      const size_t kp_bytes = (size_t)nb * capacity * sizeof(OrbKeyPoint), de_bytes = (size_t)nb * capacity * 32;
+      const bool pinned = nb <= 4;  // latency path: the caller's (pageable) arrays are copied through pinned staging
+      if (pinned) {
+        const size_t out_bytes = kp_bytes + de_bytes + (size_t)nb * sizeof(int) + 64;
+        if (h->pin_in_bytes < in_bytes) {
+          if (h->pin_in) cudaFreeHost(h->pin_in);
+          h->pin_in = nullptr; h->pin_in_bytes = 0;
+          ORB_CUDA_TRY(cudaHostAlloc(&h->pin_in, in_bytes, cudaHostAllocDefault));
+          h->pin_in_bytes = in_bytes;
+        }
+        if (h->pin_out_bytes < out_bytes) {
+          if (h->pin_out) cudaFreeHost(h->pin_out);
+          h->pin_out = nullptr; h->pin_out_bytes = 0;
+          ORB_CUDA_TRY(cudaHostAlloc(&h->pin_out, out_bytes, cudaHostAllocDefault));
+          h->pin_out_bytes = out_bytes;
+        }
+        std::memcpy(h->pin_in, frames + (size_t)f0 * frame_stride, in_bytes);
+        ORB_CUDA_TRY(cudaMemcpyAsync(stage, h->pin_in, in_bytes, cudaMemcpyHostToDevice, s));
+      } else {
+        ORB_CUDA_TRY(cudaMemcpyAsync(stage, frames + (size_t)f0 * frame_stride, in_bytes, cudaMemcpyHostToDevice, s));
+      }
       Plan pc = p;
       if (alias) { pc.lv[0].img = stage; pc.lv[0].pitch = (int)stride; pc.lv[0].frame_stride = (long long)frame_stride; }
       auto enqueue = [&]() -> int {
@@ -659,6 +690,28 @@ int orb_gpu_extract_batch(OrbGpuExtractor* h, const uint8_t* frames, int nframes
       } else {
         h->graph_seen = key;
         if ((rc = enqueue())) return rc;
+      }
+      if (pinned) {
+        uint8_t* po = (uint8_t*)h->pin_out;
+        int* pn = (int*)(po + kp_bytes + de_bytes);
+        int* pstat = pn + nb;
+        ORB_CUDA_TRY(cudaMemcpyAsync(po, dk, kp_bytes, cudaMemcpyDeviceToHost, s));
+        ORB_CUDA_TRY(cudaMemcpyAsync(po + kp_bytes, dd, de_bytes, cudaMemcpyDeviceToHost, s));
+        ORB_CUDA_TRY(cudaMemcpyAsync(pn, dn, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, s));
+        ORB_CUDA_TRY(cudaMemcpyAsync(pstat, h->sc.status, sizeof(int), cudaMemcpyDeviceToHost, s));
+        ORB_CUDA_TRY(cudaStreamSynchronize(s));
+        for (int f = 0; f < nb; ++f) {  // exactly n_out keypoints and descriptor rows per frame
+          const int n = std::min(pn[f], capacity);
+          n_out[f0 + f] = pn[f];
+          std::memcpy(kps + (size_t)(f0 + f) * capacity, po + (size_t)f * capacity * sizeof(OrbKeyPoint), (size_t)n * sizeof(OrbKeyPoint));
+          std::memcpy(desc + (size_t)(f0 + f) * capacity * 32, po + kp_bytes + (size_t)f * capacity * 32, (size_t)n * 32);
+        }
+        if (*pstat) status_all = *pstat;
+        h->last_nframes = nb;
+        h->have_result = true;
+        if (alias) { h->last_l0 = stage; h->last_l0_pitch = (int)stride; h->last_l0_stride = (long long)frame_stride; }
+        else { h->last_l0 = l0.img; h->last_l0_pitch = l0.pitch; h->last_l0_stride = l0.frame_stride; }
+        continue;
       }
       ORB_CUDA_TRY(cudaMemcpyAsync(n_out + f0, dn, (size_t)nb * sizeof(int), cudaMemcpyDeviceToHost, s));
       ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)f0 * capacity, dk, (size_t)nb * capacity * sizeof(OrbKeyPoint),
