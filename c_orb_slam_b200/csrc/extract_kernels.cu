@@ -660,9 +660,11 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   int* s_cb = s_nch + ncap;                                      // [ncap] creation base
   int* s_sv = s_cb + ncap;                                       // [ncap] survivor flags/ranks
   int* s_bnd = s_sv + ncap;                                      // [3*ncap] rank-ordered scratch
-  int* s_cbnd = s_bnd + 3 * ncap;                                // [3*ncap] child boundaries found while counting
-  int* s_cell = s_cbnd + 3 * ncap;                               // [ncells+1]
+  int* s_cell = s_bnd + 3 * ncap;                                // [ncells+1]
   int* s_warp = s_cell + ncells + 1;                             // [72]
+  // [3*ncap] child boundaries found while counting: in the bucket array, which is dead once the keys are sorted (a
+  // bigger block would cost the third resident block per SM); very large quotas get their own space behind s_warp
+  int* s_cbnd = 3 * ncap <= kQtSmemKeys ? reinterpret_cast<int*>(s_bkt) : s_warp + 72;
   __shared__ int s_misc[8];
 
   const uint32_t* cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
@@ -968,7 +970,7 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
   const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
   return (size_t)kQtSmemKeys * 12 + (size_t)(kQtBins / 2 + 4) * 4 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
-         (size_t)ncap * 4 * 9 + (size_t)(ncells + 1 + 72) * 4 + 64;
+         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 72) * 4 + 64 + (3 * ncap <= kQtSmemKeys ? 0 : (size_t)ncap * 12);
 }
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {

@@ -191,6 +191,7 @@ def test_resident_frame_from_extractor_outputs(gpu, oracle):
     d_n = torch.zeros(2, dtype=torch.int32, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     ex.extract_batch_device(d_fr.data_ptr(), 2, W, H, W, W * H, d_k.data_ptr(), d_d.data_ptr(), d_n.data_ptr(), None, st)
+    torch.cuda.synchronize()   # a NULL stream means the handle's own (non-blocking) stream: the call is asynchronous
     n = d_n.cpu().numpy()
     grid = (0.0, 0.0, np.float32(64) / np.float32(W), np.float32(48) / np.float32(H))
     f = 1
