@@ -89,6 +89,7 @@ struct StereoParams {
 
 void count_launch(int n = 1);
 void set_last_error(const char* what, cudaError_t e);
+void set_last_message(const char* msg);  // what orb_gpu_last_error() returns, for errors that are not CUDA's
 
 #define ORB_CUDA_TRY(expr)                                  \
   do {                                                      \

@@ -8,6 +8,9 @@
 #include <vector>
 
 #include <cstdlib>
+#include <cstdio>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace orbgpu {
@@ -588,3 +591,89 @@ int orb_gpu_popc_peak(int device, double* popc_per_s) {
 }
 
 }  // extern "C"
+
+// =============================================================================================
+// brute force without any allocation (orb_gpu_match_bruteforce_noalloc_device)
+// =============================================================================================
+// The per-slice partial results, the shared per-query thresholds and the slice tickets of the tcgen05 kernel live in
+// this file-scope array instead of a stream-ordered allocation: 1 MiB that every GPU which loads the library holds
+// until the process exits.  All calls share it and it keeps the last call's contents (the words that must start at
+// zero are cleared on the caller's stream before the kernel): two calls that overlap on one GPU race on it.
+static __device__ __align__(256) unsigned char g_bf_noalloc_scratch[ORB_GPU_NOALLOC_SCRATCH_BYTES];
+
+namespace orbgpu {
+// In host code `g_bf_noalloc_scratch` is only a stand-in for the device symbol: its device address is looked up once
+// per device, with that device current, and that pointer is what the kernel gets.
+static int bf_noalloc_scratch(int dev, unsigned char** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static unsigned char* ptr[kMaxDev] = {};
+  if (dev < 0 || dev >= kMaxDev) return ORB_GPU_ERR_ARG;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_bf_noalloc_scratch);  // the current device's copy
+    if (e != cudaSuccess || !p) {
+      set_last_error("cudaGetSymbolAddress(g_bf_noalloc_scratch)", e);
+      return ORB_GPU_ERR_CUDA;
+    }
+    ptr[dev] = (unsigned char*)p;
+  }
+  *out = ptr[dev];
+  return ORB_GPU_OK;
+}
+}  // namespace orbgpu
+
+extern "C" int orb_gpu_match_bruteforce_noalloc_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                                       int32_t idx_base, int32_t* d_idx, int32_t* d_best,
+                                                       int32_t* d_second, void* stream) {
+  if (nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_idx || !d_best || !d_second)) || (ndb > 0 && !d_db))
+    return ORB_GPU_ERR_ARG;
+  if (nq == 0) return ORB_GPU_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  int dev = 0, sms = 148;
+  ORB_CUDA_TRY(cudaGetDevice(&dev));
+  ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // slices as in orb_gpu_match_bruteforce_device (tcgen05 form): one wave of blocks, more only when a slice would
+  // exceed the row field of the packed keys
+  const int qblocks = (nq + kMmaQueries - 1) / kMmaQueries;
+  long long waves = 1;
+  while (waves * sms / qblocks * kBfSliceMax < ndb && waves < 65535) ++waves;
+  long long nslices = std::max<long long>(1, waves * sms / qblocks);
+  long long slice_rows = (ndb + nslices - 1) / nslices;
+  slice_rows = std::max<long long>(kBfTile, (slice_rows + kBfTile - 1) / kBfTile * kBfTile);
+  slice_rows = std::min<long long>(slice_rows, kBfSliceMax);
+  nslices = std::max<long long>(1, (ndb + slice_rows - 1) / slice_rows);
+  if (nslices > 65535) {
+    set_last_message("orb_gpu_match_bruteforce_noalloc_device: database needs more than 65535 slices");
+    return ORB_GPU_ERR_CAPACITY;
+  }
+  int32_t *pi = d_idx, *pb = d_best, *ps = d_second;
+  unsigned *g_thr = nullptr, *g_ticket = nullptr;
+  if (nslices > 1) {
+    const size_t part_bytes = (size_t)nslices * nq * 3 * sizeof(int32_t);
+    const size_t extra = ((size_t)nq + (size_t)qblocks) * sizeof(unsigned);
+    if (part_bytes + extra > (size_t)ORB_GPU_NOALLOC_SCRATCH_BYTES) {
+      char msg[256];
+      snprintf(msg, sizeof(msg), "orb_gpu_match_bruteforce_noalloc_device: %d queries x %lld rows need %zu bytes of scratch "
+               "(%lld slices), the static scratch holds %d: use orb_gpu_match_bruteforce_device", nq, (long long)ndb,
+               part_bytes + extra, nslices, (int)ORB_GPU_NOALLOC_SCRATCH_BYTES);
+      set_last_message(msg);
+      return ORB_GPU_ERR_CAPACITY;
+    }
+    unsigned char* scratch = nullptr;
+    const int rc = bf_noalloc_scratch(dev, &scratch);
+    if (rc) return rc;
+    pi = (int32_t*)scratch; pb = pi + (size_t)nslices * nq; ps = pb + (size_t)nslices * nq;
+    g_thr = (unsigned*)(scratch + part_bytes);
+    g_ticket = g_thr + nq;
+    ORB_CUDA_TRY(cudaMemsetAsync(g_thr, 0, extra, s));  // thresholds and tickets start at zero; the partials are overwritten
+  }
+  dim3 grid(qblocks, (unsigned)nslices);
+  const int rc = launch_bruteforce_tc5(grid, s, (const uint4*)d_q, nq, (const uint4*)d_db, ndb, slice_rows, idx_base, pi, pb,
+                                       ps, g_thr, g_ticket, d_idx, d_best, d_second);
+  if (rc) return rc;
+  count_launch();
+  ORB_CUDA_TRY(cudaGetLastError());
+  return ORB_GPU_OK;
+}

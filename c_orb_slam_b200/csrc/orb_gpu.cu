@@ -32,6 +32,7 @@ int use_cached_pool(int device) {
 void set_last_error(const char* what, cudaError_t e) {
   g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
 }
+void set_last_message(const char* msg) { g_last_error = msg; }
 
 static inline int cv_round(double v) { return (int)std::lrint(v); }  // round-half-even, like cvRound
 static inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }

@@ -119,6 +119,21 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
 /* Host-pointer form (copies in, computes on `device`, copies out). */
 int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int device,
                              int32_t* idx, int32_t* best, int32_t* second);
+/* The same search for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments and bit-identical results; the default (tcgen05) kernel only.  It calls no cudaMalloc / cudaFree /
+ * cudaMallocAsync or any allocating routine: its scratch (per-slice partial results, shared thresholds, slice tickets)
+ * lives in a file-scope device array of ORB_GPU_NOALLOC_SCRATCH_BYTES (1 MiB) that every GPU which loads the library
+ * holds until the process exits.  Needed: slices * nq * 12 + (nq + ceil(nq / 256)) * 4 bytes when the database is cut
+ * into more than one slice, slices = floor(SMs / ceil(nq / 256)) on a database of up to slices * 2^22 rows (e.g.
+ * 4096 queries x 10 M rows on 148 SMs: 9 slices, 0.46 MB); a call that needs more returns ORB_GPU_ERR_CAPACITY with
+ * the sizes in orb_gpu_last_error() and launches nothing.  Every call on a GPU shares that one array, which keeps the
+ * last call's contents (what must start at zero is cleared on `stream` before the kernel): calls that overlap on the
+ * same GPU -- two streams, two threads -- RACE on it; serialise them or use orb_gpu_match_bruteforce_device. */
+#define ORB_GPU_NOALLOC_SCRATCH_BYTES (1 << 20)
+int orb_gpu_match_bruteforce_noalloc_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
+                                            int32_t idx_base, int32_t* d_idx, int32_t* d_best,
+                                            int32_t* d_second, void* stream);
 /* Exact merge of per-shard results of disjoint ascending index ranges (shard s holds rows
  * [base_s, base_s + n_s) with base_s increasing in s): inputs are [nshards][nq].  This is the
  * step that follows the NCCL all-gather when the database is sharded across GPUs. */
