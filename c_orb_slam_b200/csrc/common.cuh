@@ -87,6 +87,23 @@ struct StereoParams {
   int n_rows;                                      // mvImagePyramid[0].rows (:473)
 };
 
+// Peer-memory exchange of the database-sharded brute-force matcher (exchange_kernels.cu): every rank's gather buffer
+// [2][world][3][nq_max] and flag words, mapped into this process (CUDA IPC or same-process pointers).
+constexpr int kExMaxWorld = 16;
+struct ExPeers {
+  int32_t* buf[kExMaxWorld];    // rank r's gather buffer
+  unsigned* flag[kExMaxWorld];  // rank r's flags: [kExMaxWorld] arrival counters of the stand-alone exchange kernel,
+                                // then [world][qb_max] sequence numbers per source rank and query block (fused form)
+};
+// What the tcgen05 brute-force kernel needs to finish a step itself: the block that completes a query block stores the
+// merged triples into every rank's gather buffer, releases the call's sequence number for that query block to every
+// rank, waits for the same from every rank and merges the `world` slots.
+struct FusedExchange {
+  ExPeers peers;
+  int rank, world, nq_max, qb_max, parity;
+  unsigned seq;
+};
+
 void count_launch(int n = 1);
 void set_last_error(const char* what, cudaError_t e);
 void set_last_message(const char* msg);  // what orb_gpu_last_error() returns, for errors that are not CUDA's
@@ -130,7 +147,12 @@ int upload_constants();
 int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
                           long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
                           int32_t* o_second, unsigned* g_thr, unsigned* g_ticket, int32_t* f_idx, int32_t* f_best,
-                          int32_t* f_second);
+                          int32_t* f_second, const FusedExchange* fx = nullptr);
+// brute force over this rank's rows (match_kernels.cu).  With fx, the tcgen05 form and a grid of at most one block per
+// SM the exchange across the ranks happens inside the same launch and *fused = 1; else *fused = 0 and the caller
+// exchanges d_idx / d_best / d_second afterwards.
+int bruteforce_device_impl(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int32_t idx_base, int32_t* d_idx,
+                           int32_t* d_best, int32_t* d_second, cudaStream_t s, const FusedExchange* fx, int* fused);
 size_t quadtree_smem_bytes(const Plan& p, int level);
 
 }  // namespace orbgpu

@@ -21,13 +21,6 @@
 
 namespace orbgpu {
 
-constexpr int kExMaxWorld = 16;
-
-struct ExPeers {
-  int32_t* buf[kExMaxWorld];    // rank r's gather buffer: [2][world][3][nq_max]
-  unsigned* flag[kExMaxWorld];  // rank r's arrival counters: [world]
-};
-
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -91,7 +84,10 @@ struct OrbGpuExchange {
   std::vector<void*> opened;  // IPC mappings to close
   bool connected = false;
   unsigned long long arrivals = 0;  // blocks that have signalled per source rank so far (same on every rank)
-  unsigned calls = 0;
+  unsigned calls = 0;               // exchanges so far, fused or not (the parity of the gather buffer)
+  unsigned fused_calls = 0;         // sequence number of the fused form
+  int qb_max = 0;                   // query blocks of 256 in nq_max
+  size_t flag_words() const { return (size_t)kExMaxWorld + (size_t)world * qb_max; }
 };
 
 extern "C" {
@@ -101,16 +97,17 @@ int orb_gpu_exchange_create(int device, int rank, int world, int nq_max, OrbGpuE
   ORB_CUDA_TRY(cudaSetDevice(device));
   OrbGpuExchange* x = new OrbGpuExchange();
   x->device = device; x->rank = rank; x->world = world; x->nq_max = nq_max;
+  x->qb_max = (nq_max + 255) / 256;
   const size_t bytes = (size_t)2 * world * 3 * nq_max * sizeof(int32_t);
   // plain cudaMalloc: IPC handles cannot be taken from the stream-ordered pool
-  if (cudaMalloc(&x->buf, bytes) != cudaSuccess || cudaMalloc(&x->flag, kExMaxWorld * sizeof(unsigned)) != cudaSuccess) {
+  if (cudaMalloc(&x->buf, bytes) != cudaSuccess || cudaMalloc(&x->flag, x->flag_words() * sizeof(unsigned)) != cudaSuccess) {
     set_last_error("cudaMalloc (exchange)", cudaGetLastError());
     if (x->buf) cudaFree(x->buf);
     delete x;
     return ORB_GPU_ERR_CUDA;
   }
   ORB_CUDA_TRY(cudaMemset(x->buf, 0xff, bytes));
-  ORB_CUDA_TRY(cudaMemset(x->flag, 0, kExMaxWorld * sizeof(unsigned)));
+  ORB_CUDA_TRY(cudaMemset(x->flag, 0, x->flag_words() * sizeof(unsigned)));
   ORB_CUDA_TRY(cudaDeviceSynchronize());
   x->peers.buf[rank] = x->buf;
   x->peers.flag[rank] = x->flag;
@@ -192,6 +189,37 @@ int orb_gpu_exchange_top2_device(OrbGpuExchange* x, const int32_t* d_idx, const 
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
+}
+
+int orb_gpu_exchange_match_bruteforce_device(OrbGpuExchange* x, const uint8_t* d_q, int nq, const uint8_t* d_db,
+                                             int64_t ndb, int32_t idx_base, int32_t* d_idx, int32_t* d_best,
+                                             int32_t* d_second, void* stream) {
+  if (!x || nq < 1 || nq > x->nq_max || !d_q || !d_idx || !d_best || !d_second) return ORB_GPU_ERR_ARG;
+  if (!x->connected) return ORB_GPU_ERR_STATE;
+  ORB_CUDA_TRY(cudaSetDevice(x->device));
+  if (x->world == 1) {
+    int fused = 0;
+    return bruteforce_device_impl(d_q, nq, d_db, ndb, idx_base, d_idx, d_best, d_second, (cudaStream_t)stream, nullptr, &fused);
+  }
+  static const bool no_fuse = [] { const char* e = getenv("ORB_GPU_NO_FUSED_EXCHANGE"); return e && atoi(e); }();
+  FusedExchange fx;
+  fx.peers = x->peers;
+  fx.rank = x->rank; fx.world = x->world; fx.nq_max = x->nq_max; fx.qb_max = x->qb_max;
+  fx.parity = (int)(x->calls & 1u);
+  fx.seq = x->fused_calls + 1;
+  int fused = 0;
+  int rc = bruteforce_device_impl(d_q, nq, d_db, ndb, idx_base, d_idx, d_best, d_second, (cudaStream_t)stream,
+                                  no_fuse ? nullptr : &fx, &fused);
+  if (rc) return rc;
+  if (fused) {  // the match kernel stored, signalled, waited and merged: the step was one launch
+    ++x->calls;
+    ++x->fused_calls;
+    return ORB_GPU_OK;
+  }
+  // shapes the fused form does not take (another kernel form, a grid of more than one wave): match, then the
+  // stand-alone exchange kernel in place.  Every rank takes the same branch: it depends on nq, the database size
+  // class and the SM count only through the grid shape, which the ranks of one box share.
+  return orb_gpu_exchange_top2_device(x, d_idx, d_best, d_second, nq, d_idx, d_best, d_second, stream);
 }
 
 }  // extern "C"

@@ -426,10 +426,20 @@ int orb_gpu_set_bruteforce_variant(int csa, int qpt) {
 int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb,
                                     int32_t idx_base, int32_t* d_idx, int32_t* d_best, int32_t* d_second,
                                     void* stream) {
+  int fused = 0;
+  return orbgpu::bruteforce_device_impl(d_q, nq, d_db, ndb, idx_base, d_idx, d_best, d_second, (cudaStream_t)stream,
+                                        nullptr, &fused);
+}
+
+}  // extern "C"
+
+int orbgpu::bruteforce_device_impl(const uint8_t* d_q, int nq, const uint8_t* d_db, int64_t ndb, int32_t idx_base,
+                                   int32_t* d_idx, int32_t* d_best, int32_t* d_second, cudaStream_t s,
+                                   const FusedExchange* fx, int* fused) {
+  *fused = 0;
   if (nq < 0 || ndb < 0 || (nq > 0 && (!d_q || !d_idx || !d_best || !d_second)) || (ndb > 0 && !d_db))
     return ORB_GPU_ERR_ARG;
   if (nq == 0) return ORB_GPU_OK;
-  cudaStream_t s = (cudaStream_t)stream;
   int dev = 0, sms = 148;
   ORB_CUDA_TRY(cudaGetDevice(&dev));
   ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -456,7 +466,11 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   void* part = nullptr;
   int32_t *pi = d_idx, *pb = d_best, *ps = d_second;
   unsigned *g_thr = nullptr, *g_ticket = nullptr;  // tcgen05 form: shared per-query threshold, slice tickets
-  if (nslices > 1) {
+  // the exchange across ranks rides in the same launch when the tcgen05 grid is at most one block per SM: the (at
+  // most qblocks) blocks that wait for the peers then never keep a block of this grid from running
+  const bool fuse = fx && fx->world > 1 && tc5 && (long long)qblocks * nslices <= sms && qblocks <= fx->qb_max &&
+                    nq <= fx->nq_max;
+  if (nslices > 1 || fuse) {
     int rc = use_cached_pool(dev);
     if (rc) return rc;
     const size_t part_bytes = (size_t)nslices * nq * 3 * sizeof(int32_t);
@@ -477,7 +491,8 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   switch (key) {
     case -2: {
       int rc = launch_bruteforce_tc5(grid, s, q4, nq, db4, ndb, slice_rows, idx_base, pi, pb, ps, g_thr, g_ticket, d_idx,
-                                     d_best, d_second);
+                                     d_best, d_second, fuse ? fx : nullptr);
+      *fused = fuse ? 1 : 0;
       if (rc) { if (part) cudaFreeAsync(part, s); return rc; }
       break;
     }
@@ -502,6 +517,8 @@ int orb_gpu_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d
   ORB_CUDA_TRY(e);
   return ORB_GPU_OK;
 }
+
+extern "C" {
 
 int orb_gpu_match_bruteforce(const uint8_t* q, int nq, const uint8_t* db, int64_t ndb, int device,
                              int32_t* idx, int32_t* best, int32_t* second) {

@@ -20,6 +20,8 @@
 //                running second best, packed (S, row) keys) overlaps the next MMA into it
 // Pipelines: b_full/b_empty (expanders <-> MMA, 2 stages), acc_full/acc_empty (MMA <-> epilogue, the two
 // accumulators alternate so the epilogue of one overlaps the MMAs of the other).
+#include <cstring>
+
 #include "common.cuh"
 
 namespace orbgpu {
@@ -194,7 +196,8 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
                       int32_t* __restrict__ o_best, int32_t* __restrict__ o_second,
                       unsigned* __restrict__ g_thr /*[nq] shared second-best field of a query over the slices, or null*/,
                       unsigned* __restrict__ g_ticket /*[query blocks] slices finished*/, int nslices,
-                      int32_t* __restrict__ f_idx, int32_t* __restrict__ f_best, int32_t* __restrict__ f_second) {
+                      int32_t* __restrict__ f_idx, int32_t* __restrict__ f_best, int32_t* __restrict__ f_second,
+                      FusedExchange fx /*world > 1: finish the step across the ranks here*/) {
   extern __shared__ __align__(128) uint8_t t5_smem[];
   uint8_t* s_a = t5_smem;
   uint8_t* s_b = t5_smem + 2 * kT5ATile;
@@ -312,7 +315,7 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       o_second[o] = sd;
       // a row at distance 256 never beats the initial best of the reference's scan (strict '<')
       o_idx[o] = (best && bd < 256) ? (int32_t)(idx_base + row0 + (0x3fffffu - (best & 0x3fffffu))) : -1;
-      if (nslices > 1) __threadfence();  // the slice's result is visible before this block takes its ticket
+      if (nslices > 1 || fx.world > 1) __threadfence();  // the slice's result is visible before this block takes its ticket
     }
   } else if (warp == kT5EpiWarps) {
     // ---- MMA issuer
@@ -384,21 +387,64 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
   }
   // ---- the block that finishes a query block's last slice merges the slices (ascending rows, the reference's
   // update rule on (best, second) pairs: same as merge_top2_kernel) -- no separate merge launch
-  if (nslices > 1) {
+  if (nslices > 1 || fx.world > 1) {
     if (t == 0) s_tmem[1] = atomicAdd(g_ticket + blockIdx.x, 1u) == (unsigned)(nslices - 1);
     __syncthreads();
-    if (s_tmem[1] && t < kT5Queries && qbase + t < nq) {
+    if (s_tmem[1] && t < kT5Queries) {  // the eight epilogue warps of the last block of this query block
       __threadfence();
       const int qi = qbase + t;
+      const bool live = qi < nq;
       int b = 256, sd = 256, id = -1;
-      for (int k = 0; k < nslices; ++k) {
-        const size_t o = (size_t)k * nq + qi;
-        const int ik = __ldcg(o_idx + o), bk = __ldcg(o_best + o), sk = __ldcg(o_second + o);
-        if (ik < 0) continue;
-        if (bk < b) { sd = min(b, sk); b = bk; id = ik; }
-        else sd = min(sd, bk);
+      if (live)
+        for (int k = 0; k < nslices; ++k) {
+          const size_t o = (size_t)k * nq + qi;
+          const int ik = __ldcg(o_idx + o), bk = __ldcg(o_best + o), sk = __ldcg(o_second + o);
+          if (ik < 0) continue;
+          if (bk < b) { sd = min(b, sk); b = bk; id = ik; }
+          else sd = min(sd, bk);
+        }
+      if (fx.world > 1) {
+        // ---- exchange across the ranks, fused: this rank's merged triples go into slot `rank` of every
+        // rank's gather buffer over NVLink, the query block's sequence number is released to every rank, and once
+        // every rank's number for this query block has arrived the `world` slots are merged in ascending row order.
+        const size_t nqm = (size_t)fx.nq_max;
+        const size_t slot = ((size_t)fx.parity * fx.world + fx.rank) * 3 * nqm;
+        if (live)
+          for (int p = 0; p < fx.world; ++p) {
+            int32_t* dst = fx.peers.buf[p] + slot;
+            dst[qi] = id; dst[nqm + qi] = b; dst[2 * nqm + qi] = sd;
+          }
+        __threadfence_system();
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (t == 0) {
+          const size_t fo = (size_t)kExMaxWorld + (size_t)fx.rank * fx.qb_max + blockIdx.x;
+          for (int p = 0; p < fx.world; ++p)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(fx.peers.flag[p] + fo), "r"(fx.seq) : "memory");
+          const unsigned* mine = fx.peers.flag[fx.rank] + kExMaxWorld + blockIdx.x;
+          const long long t0 = clock64();
+          for (int r = 0; r < fx.world; ++r) {
+            unsigned v;
+            do {
+              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + (size_t)r * fx.qb_max) : "memory");
+              if (clock64() - t0 > (1ll << 35)) __trap();  // ~17 s: a rank never made the call
+            } while ((int)(v - fx.seq) < 0);
+          }
+          __threadfence_system();
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (live) {
+          const int32_t* g = fx.peers.buf[fx.rank] + (size_t)fx.parity * fx.world * 3 * nqm;
+          b = 256; sd = 256; id = -1;
+          for (int r = 0; r < fx.world; ++r) {
+            const int32_t* e = g + (size_t)r * 3 * nqm;
+            const int ik = __ldcg(e + qi), bk = __ldcg(e + nqm + qi), sk = __ldcg(e + 2 * nqm + qi);
+            if (ik < 0) continue;
+            if (bk < b) { sd = min(b, sk); b = bk; id = ik; }
+            else sd = min(sd, bk);
+          }
+        }
       }
-      f_idx[qi] = id; f_best[qi] = b; f_second[qi] = sd;
+      if (live) { f_idx[qi] = id; f_best[qi] = b; f_second[qi] = sd; }
     }
     if (s_tmem[1] && t == 0) g_ticket[blockIdx.x] = 0;  // ready for the next call
   }
@@ -407,12 +453,15 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
 int launch_bruteforce_tc5(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
                           long long slice_rows, int32_t idx_base, int32_t* o_idx, int32_t* o_best,
                           int32_t* o_second, unsigned* g_thr, unsigned* g_ticket, int32_t* f_idx, int32_t* f_best,
-                          int32_t* f_second) {
+                          int32_t* f_second, const FusedExchange* fx) {
   ORB_CUDA_TRY(cudaFuncSetAttribute(bruteforce_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)kT5SmemBytes));
+  FusedExchange f;
+  if (fx) f = *fx;
+  else { memset(&f, 0, sizeof(f)); f.world = 1; }
   bruteforce_tc5_kernel<<<grid, kT5Threads, kT5SmemBytes, s>>>(q, nq, db, ndb, slice_rows, idx_base, o_idx, o_best,
                                                               o_second, g_thr, g_ticket, (int)grid.y, f_idx, f_best,
-                                                              f_second);
+                                                              f_second, f);
   return ORB_GPU_OK;
 }
 

@@ -89,6 +89,19 @@ class Top2Exchange:
                "orb_gpu_exchange_top2_device")
         return out
 
+    def match(self, d_queries, d_db_shard, idx_base, stream=None):
+        """Search this rank's rows and exchange in ONE launch (orb_gpu_exchange_match_bruteforce_device): the block of
+        the match kernel that finishes a query block stores its triples into every rank's gather buffer, signals, waits
+        for the peers and merges.  -> global [3][nq], identical on every rank."""
+        nq = d_queries.shape[0]
+        out = torch.empty((3, nq), dtype=torch.int32, device=d_queries.device)
+        st = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+        _check(self._L.orb_gpu_exchange_match_bruteforce_device(self._h, d_queries.data_ptr(), nq, d_db_shard.data_ptr(),
+                                                                d_db_shard.shape[0], int(idx_base), out[0].data_ptr(),
+                                                                out[1].data_ptr(), out[2].data_ptr(), st),
+               "orb_gpu_exchange_match_bruteforce_device")
+        return out
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.orb_gpu_exchange_destroy(self._h)
@@ -101,16 +114,19 @@ class Top2Exchange:
             pass
 
 
-def match_bruteforce_sharded(d_queries, d_db_shard, idx_base, group=None, stream=None, exchange=None):
+def match_bruteforce_sharded(d_queries, d_db_shard, idx_base, group=None, stream=None, exchange=None, fused=True):
     """Brute-force top-2 of the replicated queries against a row-sharded database.
     d_queries [nq,32] / d_db_shard [rows,32]: uint8 CUDA tensors; idx_base = global index of the shard's row 0.
-    exchange: a Top2Exchange (peer-memory exchange kernel) or None (NCCL all_gather + merge kernel).
+    exchange: a Top2Exchange (peer memory over NVLink: fused into the match kernel by default, fused=False runs the
+    stand-alone exchange kernel after it) or None (NCCL all_gather + merge kernel).
     Returns a CUDA int32 tensor [3][nq] (global idx, best, second), identical on every rank."""
     if not d_queries.is_cuda or not d_db_shard.is_cuda:
         raise RuntimeError("match_bruteforce_sharded needs CUDA tensors: the product path has no CPU fallback")
     L = lib()
     nq = d_queries.shape[0]
     st = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+    if exchange is not None and fused and exchange.world > 1:
+        return exchange.match(d_queries, d_db_shard, idx_base, st)   # search + exchange + merge: one kernel
     part = torch.empty((3, nq), dtype=torch.int32, device=d_queries.device)
     _check(L.orb_gpu_match_bruteforce_device(d_queries.data_ptr(), nq, d_db_shard.data_ptr(), d_db_shard.shape[0],
                                              int(idx_base), part[0].data_ptr(), part[1].data_ptr(),

@@ -159,6 +159,18 @@ int orb_gpu_exchange_destroy(OrbGpuExchange* x);
 int orb_gpu_exchange_top2_device(OrbGpuExchange* x, const int32_t* d_idx, const int32_t* d_best,
                                  const int32_t* d_second, int nq, int32_t* d_out_idx, int32_t* d_out_best,
                                  int32_t* d_out_second, void* stream);
+/* Fused form: the brute-force search over this rank's rows AND the exchange in ONE launch.  The block
+ * of the tcgen05 kernel that finishes the last database slice of a block of 256 queries merges the slices, stores the
+ * triples into every rank's gather buffer over NVLink, releases a per-query-block sequence number to every rank, waits
+ * for the peers' numbers of the same query block and merges the `world` slots -- the exchange of one query block
+ * overlaps the matching of the others, and there is no merge or exchange launch.  Arguments as
+ * orb_gpu_match_bruteforce_device (idx_base = global index of this rank's row 0; ranks hold ascending row ranges);
+ * the outputs are the GLOBAL top-2, identical on every rank.  Every rank makes the same sequence of calls; it may be
+ * mixed with orb_gpu_exchange_top2_device calls.  Shapes the fused form does not take (a non-default kernel form, a
+ * grid of more than one block per SM) run the search and then the stand-alone exchange kernel, same results. */
+int orb_gpu_exchange_match_bruteforce_device(OrbGpuExchange* x, const uint8_t* d_q, int nq, const uint8_t* d_db,
+                                             int64_t ndb, int32_t idx_base, int32_t* d_idx, int32_t* d_best,
+                                             int32_t* d_second, void* stream);
 /* accept flags of ORBmatcher.cc:228-230: best <= th && (float)best < nnratio*(float)second */
 int orb_gpu_ratio_test_device(const int32_t* d_best, const int32_t* d_second, int nq, int th,
                               float nnratio, uint8_t* d_accept, void* stream);

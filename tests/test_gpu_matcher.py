@@ -455,6 +455,65 @@ def test_peer_memory_exchange_many_queries(gpu):
             L.orb_gpu_exchange_destroy(hs[r])
 
 
+@pytest.mark.parametrize("nq,ndb", [(1000, 60000), (256, 9000), (4096, 300000)])
+def test_fused_match_and_exchange_two_ranks_on_one_gpu(gpu, oracle, nq, ndb):
+    """orb_gpu_exchange_match_bruteforce_device: search + exchange + merge in ONE launch per rank.  Both ranks of a
+    world of 2 live in this process on one GPU (two streams); the database is cut at uneven places; five calls in a
+    row reuse the double-buffered gather slots and the per-query-block sequence numbers, the fourth is a plain
+    exchange call in between (the two forms may be mixed).  Every rank must hold the oracle's global top-2."""
+    import ctypes as C
+    import torch
+    L = gpu.lib()
+    before = gpu.launch_count()
+    hs = (C.c_void_p * 2)()
+    for r in range(2):
+        h = C.c_void_p()
+        assert L.orb_gpu_exchange_create(0, r, 2, 4096, C.byref(h)) == 0
+        hs[r] = h
+    assert L.orb_gpu_exchange_connect_local(hs, 2) == 0
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    try:
+        for call in range(5):
+            q, db = synth.make_match_set(nq, ndb, seed=70 + call)
+            want = np.stack(oracle.match_bruteforce(q, db, threads=8))
+            dq, ddb = torch.from_numpy(q).cuda(), torch.from_numpy(db).cuda()
+            cut = ndb // 3 + 23 * call
+            torch.cuda.synchronize()
+            outs = []
+            if call == 3:   # the stand-alone exchange kernel between fused calls
+                parts = []
+                for lo, hi in ((0, cut), (cut, ndb)):
+                    p = torch.empty((3, nq), dtype=torch.int32, device="cuda")
+                    assert L.orb_gpu_match_bruteforce_device(dq.data_ptr(), nq, ddb[lo:hi].data_ptr(), hi - lo, lo,
+                                                             p[0].data_ptr(), p[1].data_ptr(), p[2].data_ptr(), None) == 0
+                    parts.append(p)
+                torch.cuda.synchronize()
+                for r in range(2):
+                    out = torch.empty((3, nq), dtype=torch.int32, device="cuda")
+                    p = parts[r]
+                    assert L.orb_gpu_exchange_top2_device(hs[r], p[0].data_ptr(), p[1].data_ptr(), p[2].data_ptr(), nq,
+                                                          out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(),
+                                                          streams[r].cuda_stream) == 0
+                    outs.append(out)
+            else:
+                launches = gpu.launch_count()
+                for r, (lo, hi) in enumerate(((0, cut), (cut, ndb))):
+                    out = torch.full((3, nq), -9, dtype=torch.int32, device="cuda")
+                    assert L.orb_gpu_exchange_match_bruteforce_device(hs[r], dq.data_ptr(), nq, ddb[lo:hi].data_ptr(), hi - lo,
+                                                                      lo, out[0].data_ptr(), out[1].data_ptr(),
+                                                                      out[2].data_ptr(), streams[r].cuda_stream) == 0
+                    outs.append(out)
+                assert gpu.launch_count() - launches == 2      # one launch per rank: nothing but the match kernel
+            torch.cuda.synchronize()
+            for out in outs:
+                assert np.array_equal(out.cpu().numpy(), want)
+    finally:
+        torch.cuda.synchronize()
+        for r in range(2):
+            L.orb_gpu_exchange_destroy(hs[r])
+    assert gpu.launch_count() > before
+
+
 def test_peer_memory_exchange_two_ranks_on_one_gpu(gpu, oracle):
     """orb_gpu_exchange_top2_device: both ranks of a world of 2 live in this process on one GPU (two streams, buffers
     wired with orb_gpu_exchange_connect_local); five calls in a row reuse the double-buffered gather slots."""
