@@ -136,6 +136,9 @@ int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s);
 int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s);
 int launch_blur(const Plan& p, int nframes, cudaStream_t s);
+// blur_tc_kernels.cu: the levels in level_mask on the tensor cores (TMA in, tcgen05.mma, TMA out)
+bool blur_tc_level_ok(const LevelGeom& g, int nframes);
+int launch_blur_tc(const Plan& p, int nframes, unsigned level_mask, cudaStream_t s);
 int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s);
 int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int level, float* d_xyr,

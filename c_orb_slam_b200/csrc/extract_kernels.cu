@@ -1012,14 +1012,15 @@ __device__ __forceinline__ void bar_sync_n(int id, int nthreads) {
 }
 
 __global__ void __launch_bounds__(1024)
-blur_kernel(Plan p, int bands_total) {
+blur_kernel(Plan p, unsigned level_mask) {
   extern __shared__ __align__(16) uint16_t s_rows[];  // [2][kBlurBatch][pitch]
   int band = blockIdx.x;
   const int f = blockIdx.y;
   int level = 0;
-  for (;; ++level) {
+  for (;; ++level) {  // the bands of the levels in level_mask, in level order
+    if (!(level_mask >> level & 1u)) continue;
     const int nb = (p.lv[level].h + kBlurR - 1) / kBlurR;
-    if (band < nb || level + 1 == p.nlevels) break;
+    if (band < nb) break;
     band -= nb;
   }
   const LevelGeom& g = p.lv[level];
@@ -1109,15 +1110,34 @@ blur_kernel(Plan p, int bands_total) {
   }
 }
 
+// The tensor-core kernel (blur_tc_kernels.cu) takes every level whose buffers TMA can address; the byte-SIMD kernel
+// above takes the rest (a caller's level-0 frames with rows that are not 16-byte aligned or with gaps between frames).
+// ORB_GPU_BLUR=simd forces the byte-SIMD kernel for all levels (A/B measurements).
+static bool blur_tc_enabled() {
+  static const bool on = [] { const char* e = getenv("ORB_GPU_BLUR"); return !(e && !strcmp(e, "simd")); }();
+  return on;
+}
 int launch_blur(const Plan& p, int nframes, cudaStream_t s) {
-  int bands = 0;
-  for (int l = 0; l < p.nlevels; ++l) bands += (p.lv[l].h + kBlurR - 1) / kBlurR;
-  const int threads = (((p.lv[0].w + 3) >> 2) + 31) & ~31;
+  const unsigned all = (p.nlevels >= 32) ? ~0u : ((1u << p.nlevels) - 1u);
+  unsigned tc_mask = 0;
+  if (blur_tc_enabled())
+    for (int l = 0; l < p.nlevels; ++l)
+      if (blur_tc_level_ok(p.lv[l], nframes)) tc_mask |= 1u << l;
+  if (tc_mask) {
+    const int rc = launch_blur_tc(p, nframes, tc_mask, s);
+    if (rc) return rc;
+  }
+  const unsigned rest = all & ~tc_mask;
+  if (!rest) return ORB_GPU_OK;
+  int bands = 0, wmax = 0;
+  for (int l = 0; l < p.nlevels; ++l)
+    if (rest >> l & 1u) { bands += (p.lv[l].h + kBlurR - 1) / kBlurR; wmax = max(wmax, p.lv[l].w); }
+  const int threads = (((wmax + 3) >> 2) + 31) & ~31;
   if (threads > 1024) return ORB_GPU_ERR_CAPACITY;
   const size_t smem = (size_t)2 * kBlurBatch * (4 * threads + 8) * sizeof(uint16_t);
   if (smem > 48 * 1024)  // per device, see launch_fast_cells
     ORB_CUDA_TRY(cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  blur_kernel<<<dim3(bands, nframes), threads, smem, s>>>(p, bands);
+  blur_kernel<<<dim3(bands, nframes), threads, smem, s>>>(p, rest);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
