@@ -10,17 +10,18 @@
 //                     bottom of a frame is folded into T (a tap that leaves the frame adds its weight to the row it
 //                     reflects to, which always lies inside the 7-row window) -- T is rebuilt per strip (7 bytes per row).
 //                     X (136 rows x 256 columns, starting 16 columns left of the chunk: TMA wants 16-byte aligned box starts) comes straight from the pyramid by TMA (cp.async.bulk.tensor, 128-byte
-//                     swizzle) and is the MN-major B operand; rows 134..159 of the K = 160 extent meet zero weights.
+//                     swizzle) and is the MN-major B operand; rows 134..159 of the K = 160 extent meet zero weights (they are whatever follows the tile in shared memory).
 //   horizontal pass = in registers: the epilogue thread of TMEM lane r owns row r, reads its 16-bit column sums
 //                     two to a register (tcgen05.ld pack::16b) and takes the seven taps from neighbouring registers
 //                     (IDP.2A, the +32768 rounding folded into the accumulator).  REFLECT_101 at the left and right
 //                     image border: the three halo byte columns of the tile are patched in shared memory before the
 //                     MMA (the column sums of a reflected column are the reflected column sums).
-//   output          = 32 rows x 224 columns per warp staged in shared memory, written by TMA (the hardware clips the
+//   output          = 32 rows x 112 columns per warp staged in shared memory, written by TMA (the hardware clips the
 //                     columns past the image and the rows past the batch).
 //
-// One persistent block per SM walks strips (all column chunks of a strip share T).  Roles: warps 0..7 epilogue (two
-// sets of four, set i drains accumulator i), warp 8 TMA loads, warp 9 MMA issue + TMEM allocation, warp 10 builds T
+// One persistent block per SM walks strips (all column chunks of a strip share T).  Roles: warps 0..15 epilogue (two
+// sets of eight, set i drains accumulator i: a warp owns 32 rows x 112 columns), warp 16 TMA loads, warp 17 MMA issue +
+// TMEM allocation, warp 18 builds T
 // and patches the halo columns.  Pipelines: x_full (TMA bytes) -> x_ready (patched) -> MMA -> x_empty / acc_full ->
 // epilogue -> acc_empty; t_ready / t_empty for the two T buffers.
 #include <cuda.h>
@@ -42,14 +43,17 @@ constexpr int kBtBoxRows = 136;                   // rows per TMA box
 constexpr int kBtOutCols = 224;                   // output columns per chunk
 constexpr int kBtLead = 16;                       // a tile starts 16 columns left of its first output column: TMA wants the
                                                   // box start 16-byte aligned (the halo itself is 3 columns)
-constexpr int kBtAtom = kBtK * 128;               // bytes of one 128-column swizzle atom column of X
+constexpr int kBtAtom = kBtBoxRows * 128;          // bytes of one 128-column swizzle atom of X (17 KB, 1024-aligned); the K
+                                                  // extent runs 24 rows into whatever follows it -- those meet zero weights
 constexpr int kBtXStage = 2 * kBtAtom;            // one X stage: up to 256 input columns
+constexpr int kBtStages = 3;                      // TMA -> patch -> MMA ring
 constexpr int kBtT = kBtRows * kBtK;              // bytes of one T buffer
-constexpr int kBtOutWarp = 32 * kBtOutCols;       // staging bytes per epilogue warp
-constexpr int kBtEpiWarps = 8;
+constexpr int kBtHalf = kBtOutCols / 2;              // output columns per epilogue warp
+constexpr int kBtOutWarp = 32 * kBtHalf;            // staging bytes per epilogue warp
+constexpr int kBtEpiWarps = 16;
 constexpr int kBtMaxLevels = 8;
 constexpr int kBtThreads = (kBtEpiWarps + 3) * 32;
-constexpr int kBtOffT = 2 * kBtXStage;
+constexpr int kBtOffT = kBtStages * kBtXStage;
 constexpr int kBtOffOut = kBtOffT + 2 * kBtT;
 constexpr int kBtOffBar = kBtOffOut + kBtEpiWarps * kBtOutWarp;
 constexpr int kBtSmem = kBtOffBar + 256 + 1024;   // + alignment slack (the swizzle atoms need 1024-byte alignment)
@@ -68,7 +72,6 @@ struct BlurTcParams {
   CUtensorMap out[kBtMaxLevels];
   BlurTcLevel lv[kBtMaxLevels];
   int nused, nstrips;
-  int dbg;  // bring-up switches (ORB_GPU_BT_DBG): 1 no MMA, 2 no TMA store, 4 no TMEM load, 8 no TMA load, 16 set-up only
 };
 
 __device__ __forceinline__ void umma_u8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
@@ -154,15 +157,18 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
   uint8_t* s_t = sm + kBtOffT;
   uint8_t* s_o = sm + kBtOffOut;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sm + kBtOffBar);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 16);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
   const uint32_t bar0 = smem_u32(bars);
-  // barrier slots: 0,1 x_full  2,3 x_ready  4,5 x_empty  6,7 t_ready  8,9 t_empty  10,11 acc_full  12,13 acc_empty
+  // barrier slots (per X stage / T buffer / accumulator)
+  constexpr int kXFull = 0, kXReady = kBtStages, kXEmpty = 2 * kBtStages, kTReady = 3 * kBtStages, kTEmpty = kTReady + 2,
+                kAccFull = kTEmpty + 2, kAccEmpty = kAccFull + 2, kNumBars = kAccEmpty + 2;
+  static_assert(kNumBars <= 24, "barrier slots");
   auto bar = [&](int i) { return bar0 + 8u * i; };
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
 
   if (t == 0) {
-    for (int i = 0; i < 12; ++i) mbar_init(bar(i), 1);
-    mbar_init(bar(12), 128); mbar_init(bar(13), 128);
+    for (int i = 0; i < kAccEmpty; ++i) mbar_init(bar(i), 1);
+    mbar_init(bar(kAccEmpty), 256); mbar_init(bar(kAccEmpty + 1), 256);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kBtEpiWarps + 1) {
@@ -178,16 +184,17 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *s_tmem;
 
-  // every role walks the same list: strips blockIdx.x, + gridDim.x, ...; the column chunks of a strip in order
+  // every role walks the same list: strips blockIdx.x, + gridDim.x, ...; the column chunks of a strip in order.
+  // Tile number `tile` uses X stage tile % kBtStages and accumulator tile & 1; strip number sn uses T buffer sn & 1.
   auto level_of = [&](int si) { int j = 0; while (j + 1 < P.nused && si >= P.lv[j + 1].strip0) ++j; return j; };
 
-  if (P.dbg & 16) {
-  } else if (warp < kBtEpiWarps) {
+  if (warp < kBtEpiWarps) {
     // ---------------- epilogue: horizontal pass + store ----------------
-    const int g = warp >> 2, q = warp & 3;
-    const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + g * 256;
+    // warps 8 g + 4 hf + q: accumulator g, column half hf (112 output columns), TMEM lane quarter q (32 rows)
+    const int g = warp >> 3, hf = (warp >> 2) & 1, q = warp & 3;
+    const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + g * 256 + hf * kBtHalf + 12;
     uint8_t* stage = s_o + warp * kBtOutWarp;
-    uint8_t* my_row = stage + lane * kBtOutCols;
+    uint8_t* my_row = stage + lane * kBtHalf;
     int tile = 0;
     for (int si = blockIdx.x; si < P.nstrips; si += gridDim.x) {
       const int j = level_of(si);
@@ -195,51 +202,43 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
       const int g0 = (si - L.strip0) * kBtRows;
       for (int c = 0; c < L.nchunks; ++c, ++tile) {
         if ((tile & 1) != g) continue;
-        const int c0 = c * kBtOutCols;
-        const int out_cols = min(kBtOutCols, L.w - c0);
-        const int ngroups = (out_cols + 63) >> 6;
-        mbar_wait(bar(10 + g), (tile >> 1) & 1);
+        const int c0 = c * kBtOutCols + hf * kBtHalf;
+        const int rem = min(kBtHalf, L.w - c0);   // output columns of this warp (<= 0: none)
+        mbar_wait_suspend(bar(kAccFull + g), (tile >> 1) & 1);
         tc_fence_after();
         if (lane == 0) tma_store_wait_read();  // the previous store of this warp has left the staging rows
         __syncwarp();
-        // groups of 64 output columns; group g reads the sums of tile columns 64 g + 12 .. 64 g + 83 (the window of output
-        // i spans tile columns i + 13 .. i + 19).  The fourth group has 32 outputs and stays inside the 256 columns.
-        for (int grp = 0; grp < ngroups; ++grp) {
-          uint32_t p[32], hl[4] = {0, 0, 0, 0};
-          const bool tail = grp == 3;
-          if (!(P.dbg & 4)) {
-            if (!tail) { bt_ld64p(p, taddr + 64 * grp + 12); bt_ld8p(hl, taddr + 64 * grp + 76); }
-            else {
-#pragma unroll
-              for (int i = 16; i < 32; ++i) p[i] = 0;
-              bt_ld32p(p, taddr + 204); bt_ld8p(hl, taddr + 236);
-            }
+        // The window of this warp's output i spans tile columns hf * 112 + i + 13 .. + 19; the registers hold the column
+        // sums from tile column hf * 112 + 12 (first 64 outputs, 4 halo registers) and hf * 112 + 76 (last 48 outputs).
+        if (rem > 0) {
+          uint32_t p[32], hl[4];
+          bt_ld64p(p, taddr);
+          bt_ld8p(hl, taddr + 64);
+          bt_wait(p, hl);
+          uint4* dst = reinterpret_cast<uint4*>(my_row);
+          if (rem <= 64) { tc_fence_before(); mbar_arrive(bar(kAccEmpty + g)); }
+          dst[0] = bt_row16<0, 32>(p, hl);
+          if (rem > 16) dst[1] = bt_row16<1, 32>(p, hl);
+          if (rem > 32) dst[2] = bt_row16<2, 32>(p, hl);
+          if (rem > 48) dst[3] = bt_row16<3, 32>(p, hl);
+          if (rem > 64) {
+            bt_ld64p(p, taddr + 64);
             bt_wait(p, hl);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) p[i] = 0;
-          }
-          if (grp == ngroups - 1) {  // the accumulator is in registers: the MMA of the tile after next may start
             tc_fence_before();
-            mbar_arrive(bar(12 + g));
+            mbar_arrive(bar(kAccEmpty + g));  // the accumulator is in registers: the MMA of the tile after next may start
+            dst[4] = bt_row16<0, 32>(p, hl);
+            if (rem > 80) dst[5] = bt_row16<1, 32>(p, hl);
+            if (rem > 96) dst[6] = bt_row16<2, 32>(p, hl);
           }
-          const int rem = out_cols - 64 * grp;
-          uint4* dst = reinterpret_cast<uint4*>(my_row + 64 * grp);
-          if (!tail) {
-            dst[0] = bt_row16<0, 32>(p, hl);
-            if (rem > 16) dst[1] = bt_row16<1, 32>(p, hl);
-            if (rem > 32) dst[2] = bt_row16<2, 32>(p, hl);
-            if (rem > 48) dst[3] = bt_row16<3, 32>(p, hl);
-          } else {
-            dst[0] = bt_row16<0, 16>(p, hl);
-            if (rem > 16) dst[1] = bt_row16<1, 16>(p, hl);
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&P.out[j], c0, g0 + 32 * q, smem_u32(stage));
+            tma_store_commit();
           }
-        }
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0 && !(P.dbg & 2)) {
-          tma_store_2d(&P.out[j], c0, g0 + 32 * q, smem_u32(stage));
-          tma_store_commit();
+        } else {
+          tc_fence_before();
+          mbar_arrive(bar(kAccEmpty + g));
         }
       }
     }
@@ -253,15 +252,15 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
         const BlurTcLevel L = P.lv[j];
         const int g0 = (si - L.strip0) * kBtRows;
         for (int c = 0; c < L.nchunks; ++c, ++tile) {
-          const int s = tile & 1;
+          const int s = tile % kBtStages, u = tile / kBtStages;
           const int c0 = c * kBtOutCols;
           const int n = (min(kBtOutCols, L.w - c0) + kBtLead + 3 + 15) & ~15;
           const int natoms = n > 128 ? 2 : 1;
-          mbar_wait(bar(4 + s), ((tile >> 1) & 1) ^ 1);
-          if (P.dbg & 8) { mbar_arrive(bar(s)); continue; }
-          mbar_expect_tx(bar(s), (uint32_t)(natoms * kBtBoxRows * 128));
+          mbar_wait_suspend(bar(kXEmpty + s), (u & 1) ^ 1);
+          mbar_expect_tx(bar(kXFull + s), (uint32_t)(natoms * kBtBoxRows * 128));
           for (int a = 0; a < natoms; ++a)
-            tma_load_2d(smem_u32(s_x + s * kBtXStage + a * kBtAtom), &P.in[j], c0 - kBtLead + 128 * a, g0 - 3, bar(s));
+            tma_load_2d(smem_u32(s_x + s * kBtXStage + a * kBtAtom), &P.in[j], c0 - kBtLead + 128 * a, g0 - 3,
+                        bar(kXFull + s));
         }
       }
     }
@@ -273,28 +272,27 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
         const int j = level_of(si);
         const BlurTcLevel L = P.lv[j];
         const int b = sn & 1;
-        mbar_wait(bar(6 + b), (sn >> 1) & 1);
+        mbar_wait_suspend(bar(kTReady + b), (sn >> 1) & 1);
         const uint64_t da = umma_desc(smem_u32(s_t + b * kBtT), 2048, 128);
         for (int c = 0; c < L.nchunks; ++c, ++tile) {
-          const int s = tile & 1, acc = tile & 1, u = tile >> 1;
+          const int s = tile % kBtStages, u = tile / kBtStages, acc = tile & 1;
           const int n = (min(kBtOutCols, L.w - c * kBtOutCols) + kBtLead + 3 + 15) & ~15;
           const uint64_t db = umma_desc_mn128(smem_u32(s_x + s * kBtXStage), kBtAtom, 1024);
           const uint32_t idesc = kBtIdesc | ((uint32_t)(n >> 3) << 17);
-          mbar_wait(bar(2 + s), u & 1);
-          mbar_wait(bar(12 + acc), (u & 1) ^ 1);
+          mbar_wait_suspend(bar(kXReady + s), u & 1);
+          mbar_wait_suspend(bar(kAccEmpty + acc), ((tile >> 1) & 1) ^ 1);
           tc_fence_after();
-          if (!(P.dbg & 1))
 #pragma unroll
           for (int k = 0; k < kBtK / 32; ++k)  // 32 input rows per step: two 16-byte K chunks of T, four 8-row groups of X
             umma_u8(tmem_base + acc * 256, da + (uint64_t)(k * (2 * 2048 >> 4)), db + (uint64_t)(k * (4096 >> 4)), idesc, k > 0);
-          umma_commit(bar(4 + s));
-          umma_commit(bar(10 + acc));
+          umma_commit(bar(kXEmpty + s));
+          umma_commit(bar(kAccFull + acc));
         }
-        umma_commit(bar(8 + b));
+        umma_commit(bar(kTEmpty + b));
       }
       // the last commits must have landed before the block (and its shared memory) goes away
-      if (tile > 0) mbar_wait(bar(4 + ((tile - 1) & 1)), ((tile - 1) >> 1) & 1);
-      if (sn > 0) mbar_wait(bar(8 + ((sn - 1) & 1)), ((sn - 1) >> 1) & 1);
+      if (tile > 0) mbar_wait_suspend(bar(kXEmpty + (tile - 1) % kBtStages), ((tile - 1) / kBtStages) & 1);
+      if (sn > 0) mbar_wait_suspend(bar(kTEmpty + ((sn - 1) & 1)), ((sn - 1) >> 1) & 1);
     }
   } else {
     // ---------------- T builder + halo patcher ----------------
@@ -304,7 +302,7 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
       const BlurTcLevel L = P.lv[j];
       const int g0 = (si - L.strip0) * kBtRows;
       const int b = sn & 1;
-      mbar_wait(bar(8 + b), ((sn >> 1) & 1) ^ 1);
+      mbar_wait_suspend(bar(kTEmpty + b), ((sn >> 1) & 1) ^ 1);
       uint8_t* tb = s_t + b * kBtT;
       for (int r = lane; r < kBtRows; r += 32) {
         const int y = g0 + r, f = y / L.h, yf = y - f * L.h;
@@ -333,26 +331,44 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
       }
       fence_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar(6 + b));
+      if (lane == 0) mbar_arrive(bar(kTReady + b));
       for (int c = 0; c < L.nchunks; ++c, ++tile) {
-        const int s = tile & 1;
+        const int s = tile % kBtStages, u = tile / kBtStages;
         const int c0 = c * kBtOutCols;
         const bool left = c0 == 0, right = c0 + kBtOutCols >= L.w;
-        mbar_wait(bar(s), (tile >> 1) & 1);
+        mbar_wait_suspend(bar(kXFull + s), u & 1);
         if (left || right) {
+          // REFLECT_101 columns: tile columns 13..15 <- 19..17 (image columns -3..-1) and e..e+2 <- e-2..e-4 (image
+          // columns w..w+2).  All source bytes of a lane's rows are read before any is written (the loads overlap).
           uint8_t* xs = s_x + s * kBtXStage;
           const int e = L.w - c0 + kBtLead;  // tile column of image column w
-          for (int k = lane; k < kBtBoxRows; k += 32) {
-            auto at = [&](int n) -> uint8_t* {
-              return xs + (n >> 7) * kBtAtom + k * 128 + (((((n & 127) >> 4) ^ (k & 7)) << 4) | (n & 15));
-            };
-            if (left) { *at(kBtLead - 3) = *at(kBtLead + 3); *at(kBtLead - 2) = *at(kBtLead + 2); *at(kBtLead - 1) = *at(kBtLead + 1); }
-            if (right) { *at(e) = *at(e - 2); *at(e + 1) = *at(e - 3); *at(e + 2) = *at(e - 4); }
+          constexpr int kRowsPerLane = (kBtBoxRows + 31) / 32;
+          uint8_t v[kRowsPerLane][6];
+          auto at = [&](int k, int n) -> uint8_t* {
+            return xs + (n >> 7) * kBtAtom + k * 128 + (((((n & 127) >> 4) ^ (k & 7)) << 4) | (n & 15));
+          };
+#pragma unroll
+          for (int i = 0; i < kRowsPerLane; ++i) {
+            const int k = min(lane + 32 * i, kBtBoxRows - 1);
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+              v[i][m] = left ? *at(k, kBtLead + 3 - m) : (uint8_t)0;
+              v[i][3 + m] = right ? *at(k, e - 2 - m) : (uint8_t)0;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < kRowsPerLane; ++i) {
+            const int k = min(lane + 32 * i, kBtBoxRows - 1);
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+              if (left) *at(k, kBtLead - 3 + m) = v[i][m];
+              if (right) *at(k, e + m) = v[i][3 + m];
+            }
           }
           fence_async_smem();
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar(2 + s));
+        if (lane == 0) mbar_arrive(bar(kXReady + s));
       }
     }
   }
@@ -425,7 +441,6 @@ int launch_blur_tc(const Plan& p, int nframes, unsigned level_mask, cudaStream_t
   ORB_CUDA_TRY(cudaGetDevice(&dev));
   ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   ORB_CUDA_TRY(cudaFuncSetAttribute(blur_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBtSmem));
-  static const int dbg = [] { const char* e = getenv("ORB_GPU_BT_DBG"); return e ? atoi(e) : 0; }();
   for (int l = 0; l < p.nlevels;) {
     BlurTcParams P;
     std::memset(&P, 0, sizeof(P));
@@ -435,7 +450,7 @@ int launch_blur_tc(const Plan& p, int nframes, unsigned level_mask, cudaStream_t
       const LevelGeom& g = p.lv[l];
       const long long rows = (long long)nframes * g.h;
       if ((rc = tensor_map_2d(&P.in[j], g.img, g.w, rows, g.pitch, 128, kBtBoxRows, true)) ||
-          (rc = tensor_map_2d(&P.out[j], g.blur, g.w, rows, g.bpitch, kBtOutCols, 32, false)))
+          (rc = tensor_map_2d(&P.out[j], g.blur, g.w, rows, g.bpitch, kBtHalf, 32, false)))
         return rc;
       P.lv[j].w = g.w; P.lv[j].h = g.h; P.lv[j].rows = (int)rows; P.lv[j].level = l;
       P.lv[j].nchunks = (g.w + kBtOutCols - 1) / kBtOutCols;
@@ -444,7 +459,7 @@ int launch_blur_tc(const Plan& p, int nframes, unsigned level_mask, cudaStream_t
       ++j;
     }
     if (!j) break;
-    P.nused = j; P.nstrips = strips; P.dbg = dbg;
+    P.nused = j; P.nstrips = strips;
     blur_tc_kernel<<<strips < sms ? strips : sms, kBtThreads, kBtSmem, s>>>(P);
     count_launch();
     ORB_CUDA_TRY(cudaGetLastError());

@@ -32,6 +32,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     else if (now - t0 > 6000000000LL) __trap();
   }
 }
+// Same, but the thread may stay suspended in the barrier unit for up to ~`ns` at a time (it resumes as soon as the
+// phase completes): producer / consumer roles that wait long do not take issue slots from the working warps.
+__device__ __forceinline__ void mbar_wait_suspend(uint32_t bar, uint32_t parity, uint32_t ns = 2000) {
+  uint32_t done;
+  long long t0 = 0;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity), "r"(ns)
+        : "memory");
+    if (done) break;
+    const long long now = clock64();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > 6000000000LL) __trap();
+  }
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
