@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
       for (int c = 0; c < L.nchunks; ++c, ++tile) {
         const int s = tile % kBtStages, u = tile / kBtStages;
         const int c0 = c * kBtOutCols;
-        const bool left = c0 == 0, right = c0 + kBtOutCols >= L.w;
+        const bool left = c0 == 0, right = c0 + kBtOutCols + 3 > L.w;  // the tile reaches past column w - 1
         mbar_wait_suspend(bar(kXFull + s), u & 1);
         if (left || right) {
           // REFLECT_101 columns: tile columns 13..15 <- 19..17 (image columns -3..-1) and e..e+2 <- e-2..e-4 (image

@@ -97,30 +97,42 @@ resize_level_kernel(LevelGeom src, LevelGeom dst) {
 }
 
 // Four destination columns per thread (scaleFactor <= 2: their taps span at most 11 bytes = three aligned words from
-// the thread's first word): per destination row 6 loads instead of 2 x 4, one set of row offsets / weights and one
-// 32-bit store for four pixels.  Columns 0,1 take their tap pairs from words (0,1); columns 2,3 from words (1,2) when
+// the thread's first word).  Columns 0,1 take their tap pairs from words (0,1); columns 2,3 from words (1,2) when
 // column 2 starts in word 1 or later, else from (0,1) as well -- a per-thread constant choice (two selects per row).
+// The block walks the SOURCE rows of its band once: the horizontal pass T >> 4 of a source row (3 loads, 2 PRMT,
+// 4 IDP.2A) is kept for the next row, and a destination row is emitted as soon as its lower source row is done --
+// for 1 < scale <= 2 consecutive destination rows start at consecutive or next-but-one source rows, so every source
+// row of the band is needed and each is loaded and filtered once (1.2 per destination row instead of 2).
+constexpr int kRzSrcRows = 2 * kRzRows + 4;
 __global__ void __launch_bounds__(256)
 resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows per block: 4, 8 or 16*/) {
-  __shared__ unsigned s_off0[kRzRows], s_off1[kRzRows];
-  __shared__ unsigned s_b0[kRzRows], s_b1[kRzRows];
+  __shared__ uint2 s_src[kRzSrcRows];  // per source row of the band: word offset, destination rows to emit (e1 | e2 << 8)
+  __shared__ uint2 s_b[kRzRows];       // vertical weights << 16 of a destination row
+  __shared__ int s_ns;
   const int f = blockIdx.y;
   const int dy0 = blockIdx.x * rows;
   const int rstep = src.pitch >> 2;
-  if (threadIdx.x < rows) {
-    const int dy = min(dy0 + (int)threadIdx.x, dst.h - 1);
-    const int sy0 = dst.yofs[dy];
-    s_off0[threadIdx.x] = (unsigned)(sy0 * rstep);
-    s_off1[threadIdx.x] = (unsigned)(min(sy0 + 1, src.h - 1) * rstep);
-    s_b0[threadIdx.x] = (unsigned)dst.ay0[dy] << 16;
-    s_b1[threadIdx.x] = (unsigned)dst.ay1[dy] << 16;
+  const int nrows = min(rows, dst.h - dy0);
+  const int s_begin = dst.yofs[dy0];
+  if (threadIdx.x < kRzSrcRows)
+    s_src[threadIdx.x] = make_uint2((unsigned)(min(s_begin + (int)threadIdx.x, src.h - 1) * rstep), 0xffffu);
+  __syncthreads();
+  if (threadIdx.x < nrows) {
+    const int dy = dy0 + (int)threadIdx.x;
+    const int sy0 = dst.yofs[dy], i0 = sy0 - s_begin;
+    s_b[threadIdx.x] = make_uint2((unsigned)dst.ay0[dy] << 16, (unsigned)dst.ay1[dy] << 16);
+    // e1: emitted after source row i0 + 1 from (previous, current); e2: the last source row serves as both taps
+    // (sy0 == src.h - 1, the reference clamps sy0 + 1)
+    unsigned char* e = reinterpret_cast<unsigned char*>(&s_src[sy0 + 1 <= src.h - 1 ? i0 + 1 : i0].y);
+    e[sy0 + 1 <= src.h - 1 ? 0 : 1] = (unsigned char)threadIdx.x;
+    if ((int)threadIdx.x == nrows - 1) s_ns = min(sy0 + 1, src.h - 1) - s_begin + 1;
   }
   __syncthreads();
+  const int ns = s_ns;
   const int nt = (dst.w + 3) >> 2;
   const int last_word = rstep - 1;
   const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
   uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
-  const int nrows = min(rows, dst.h - dy0);
   for (int t = threadIdx.x; t < nt; t += blockDim.x) {
     int x[4];
     unsigned wt[4];
@@ -131,36 +143,47 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows p
       wt[j] = (unsigned)(unsigned short)dst.ax0[dx] | ((unsigned)(unsigned short)dst.ax1[dx] << 16);
     }
     const int wi0 = x[0] >> 2;
+    const bool hi = x[2] - 4 * wi0 >= 4;
+    // word columns of the two tap windows: (ca, ca + 1) for destination columns 0,1 and (cb, cb + 1) for 2,3
     const unsigned* c0 = sbase + wi0;
     const unsigned* c1 = sbase + min(wi0 + 1, last_word);
     const unsigned* c2 = sbase + min(wi0 + 2, last_word);
     const int o0 = x[0] - 4 * wi0, o1 = x[1] - 4 * wi0;
-    const bool hi = x[2] - 4 * wi0 >= 4;
     const int o2 = x[2] - 4 * wi0 - (hi ? 4 : 0), o3 = x[3] - 4 * wi0 - (hi ? 4 : 0);
     const unsigned sel01 = (unsigned)o0 | ((unsigned)(o0 + 1) << 4) | ((unsigned)o1 << 8) | ((unsigned)(o1 + 1) << 12);
     const unsigned sel23 = (unsigned)o2 | ((unsigned)(o2 + 1) << 4) | ((unsigned)o3 << 8) | ((unsigned)(o3 + 1) << 12);
-    uint8_t* drow = dbase + 4 * t;
+    uint8_t* dcol = dbase + 4 * t;
+    unsigned pv0 = 0, pv1 = 0, pv2 = 0, pv3 = 0;  // T >> 4 of the previous source row
+    auto emit = [&](unsigned k, unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned h0, unsigned h1, unsigned h2,
+                    unsigned h3) {
+      const uint2 bw = s_b[k];
+      const unsigned v0 = (__umulhi(bw.x, a0) + __umulhi(bw.y, h0) + 2u) >> 2;
+      const unsigned v1 = (__umulhi(bw.x, a1) + __umulhi(bw.y, h1) + 2u) >> 2;
+      const unsigned v2 = (__umulhi(bw.x, a2) + __umulhi(bw.y, h2) + 2u) >> 2;
+      const unsigned v3 = (__umulhi(bw.x, a3) + __umulhi(bw.y, h3) + 2u) >> 2;
+      *reinterpret_cast<unsigned*>(dcol + (size_t)k * dst.pitch) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+    };
 #pragma unroll 1
-    for (int i0 = 0; i0 < rows; i0 += kRzBatch) {
-      unsigned w[kRzBatch][6];
+    for (int j0 = 0; j0 < ns; j0 += kRzBatch) {
+      unsigned w[kRzBatch][3], ev[kRzBatch];
 #pragma unroll
       for (int k = 0; k < kRzBatch; ++k) {
-        const unsigned r0 = s_off0[i0 + k], r1 = s_off1[i0 + k];
-        w[k][0] = c0[r0]; w[k][1] = c1[r0]; w[k][2] = c2[r0];
-        w[k][3] = c0[r1]; w[k][4] = c1[r1]; w[k][5] = c2[r1];
+        const uint2 sr = s_src[j0 + k];  // rows past the band repeat the last source row (never emitted)
+        w[k][0] = c0[sr.x]; w[k][1] = c1[sr.x]; w[k][2] = c2[sr.x];
+        ev[k] = sr.y;
       }
 #pragma unroll
       for (int k = 0; k < kRzBatch; ++k) {
-        const unsigned pa0 = __byte_perm(w[k][0], w[k][1], sel01), pa1 = __byte_perm(w[k][3], w[k][4], sel01);
-        const unsigned pb0 = __byte_perm(hi ? w[k][1] : w[k][0], hi ? w[k][2] : w[k][1], sel23);
-        const unsigned pb1 = __byte_perm(hi ? w[k][4] : w[k][3], hi ? w[k][5] : w[k][4], sel23);
-        const unsigned b0 = s_b0[i0 + k], b1 = s_b1[i0 + k];
-        const unsigned v0 = (__umulhi(b0, __dp2a_lo(wt[0], pa0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wt[0], pa1, 0u) >> 4) + 2u) >> 2;
-        const unsigned v1 = (__umulhi(b0, __dp2a_hi(wt[1], pa0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wt[1], pa1, 0u) >> 4) + 2u) >> 2;
-        const unsigned v2 = (__umulhi(b0, __dp2a_lo(wt[2], pb0, 0u) >> 4) + __umulhi(b1, __dp2a_lo(wt[2], pb1, 0u) >> 4) + 2u) >> 2;
-        const unsigned v3 = (__umulhi(b0, __dp2a_hi(wt[3], pb0, 0u) >> 4) + __umulhi(b1, __dp2a_hi(wt[3], pb1, 0u) >> 4) + 2u) >> 2;
-        if (i0 + k < nrows) *reinterpret_cast<unsigned*>(drow) = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
-        drow += dst.pitch;
+        const unsigned pa = __byte_perm(w[k][0], w[k][1], sel01);
+        const unsigned pb = __byte_perm(hi ? w[k][1] : w[k][0], hi ? w[k][2] : w[k][1], sel23);
+        const unsigned h0 = __dp2a_lo(wt[0], pa, 0u) >> 4, h1 = __dp2a_hi(wt[1], pa, 0u) >> 4;
+        const unsigned h2 = __dp2a_lo(wt[2], pb, 0u) >> 4, h3 = __dp2a_hi(wt[3], pb, 0u) >> 4;
+        const unsigned e1 = ev[k] & 0xffu, e2 = ev[k] >> 8;
+        if (j0 + k < ns) {  // uniform: the emit lists are per block
+          if (e1 != 0xffu) emit(e1, pv0, pv1, pv2, pv3, h0, h1, h2, h3);
+          if (e2 != 0xffu) emit(e2, h0, h1, h2, h3, h0, h1, h2, h3);
+        }
+        pv0 = h0; pv1 = h1; pv2 = h2; pv3 = h3;
       }
     }
   }

@@ -155,3 +155,50 @@ def test_pyramid_levels_pixel_exact_for_odd_widths_and_scales(gpu, oracle, W, H,
     for l in range(nlevels):
         assert np.array_equal(ex_g.pyramid_level(l), ex_o.level_image(l)), l
     assert np.array_equal(k, ko) and np.array_equal(d, do)
+
+
+@pytest.mark.parametrize("W,H,scale,nlevels,B", [(640, 480, 1.2, 8, 3), (225, 150, 1.1, 3, 2), (449, 131, 1.2, 4, 5),
+                                                 (1241, 376, 1.2, 8, 2), (752, 480, 1.2, 8, 1), (400, 300, 1.08, 12, 2),
+                                                 (1920, 1080, 1.5, 5, 1)])
+def test_blurred_levels_equal_gaussian_blur_of_the_levels(gpu, oracle, W, H, scale, nlevels, B):
+    """Every blurred level of every frame of a batch == GaussianBlur 7x7 sigma 2 REFLECT_101 (src/ORBextractor.cc:1085-1086)
+    of the unblurred level, pixel for pixel: the tensor-core kernel's stacked frames (REFLECT_101 rows folded into the
+    Toeplitz matrix at every frame boundary), column chunks with one or two image edges, chunks of a few columns, levels
+    shorter than a strip, more than eight levels (two launches) and 1241-px rows (repacked level 0)."""
+    frames = synth.make_frames(W, H, B, seed0=91)
+    ex = gpu.ORBextractor(300, scale, nlevels, 20, 7, max_width=W, max_height=H, max_batch=B)
+    ex.extract_batch(frames)
+    for f in range(B):
+        for l in range(nlevels):
+            want = oracle.gaussian_blur7(ex.pyramid_level(l, f))
+            assert np.array_equal(ex.pyramid_level(l, f, blurred=True), want), (f, l)
+
+
+def test_blur_of_frames_tma_cannot_address(gpu, oracle):
+    """Device frames whose rows are 4-byte but not 16-byte aligned and frames with a gap between them: level 0 goes
+    through the byte-SIMD blur kernel, the other levels through the tensor-core kernel; all equal the oracle."""
+    import torch
+    W, H, B = 636, 200, 3
+    stride, fstride = 644, 644 * 200 + 644
+    buf = torch.zeros(B * fstride + 64, dtype=torch.uint8, device="cuda")
+    frames = synth.make_frames(W, H, B, seed0=17)
+    host = np.zeros(B * fstride + 64, np.uint8)
+    for f in range(B):
+        host[f * fstride:f * fstride + H * stride].reshape(H, stride)[:, :W] = frames[f]
+    buf.copy_(torch.from_numpy(host))
+    ex = gpu.ORBextractor(300, 1.2, 6, 20, 7, max_width=W, max_height=H, max_batch=B)
+    cap = ex.capacity
+    d_kps = torch.empty((B, cap, 28), dtype=torch.uint8, device="cuda")
+    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.empty(B, dtype=torch.int32, device="cuda")
+    ex.extract_batch_device(buf.data_ptr(), B, W, H, stride, fstride, d_kps.data_ptr(), d_desc.data_ptr(), d_n.data_ptr())
+    torch.cuda.synchronize()
+    n = d_n.cpu().numpy()
+    kps = d_kps.cpu().numpy().view(gpu.KP_DTYPE).reshape(B, cap)
+    desc = d_desc.cpu().numpy()
+    ex_o = oracle.Extractor(300, 1.2, 6, 20, 7)
+    for f in range(B):
+        for l in range(6):
+            assert np.array_equal(ex.pyramid_level(l, f, blurred=True), oracle.gaussian_blur7(ex.pyramid_level(l, f))), (f, l)
+        ko, do = ex_o(frames[f])
+        assert n[f] == len(ko) and np.array_equal(kps[f, :n[f]], ko) and np.array_equal(desc[f, :n[f]], do)

@@ -4,7 +4,7 @@
 // 128-byte swizzle, two atoms), compared with the host column sums.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o tma_probe tma_probe.cu      usage: tma_probe <mode> [lbo sbo]
 //   mode 0: TMA load, tensor map in global memory     mode 1: tensor map inside a __grid_constant__ parameter struct
-//   (mode 1 faults with 'illegal instruction' on this driver: the maps of the product live in global memory)
+//   (both work; what faults with 'illegal instruction' is a box whose first column is not a multiple of 16 bytes)
 //   mode 2: TMA load + MMA (MN-major B)
 #include <cuda.h>
 #include <cuda_runtime.h>
