@@ -585,8 +585,11 @@ def run_ours(args):
     achieved = stage_bytes[top] * B / (acc[top] * 1e-3) / 1e9
     traffic = None  # DRAM bytes per launch of that kernel from the committed ncu capture (per frame x frames per launch)
     warp_inst = {}  # warp-level instructions per frame and stage, same capture
+    cap_name = None
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r05.json")) as f:
+        import glob
+        cap_name = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_r*.json")))[-1]  # the newest capture
+        with open(cap_name) as f:
             cap_json = json.load(f)
         per_frame = cap_json["bytes_per_frame"].get(top)
         traffic = per_frame * B if per_frame else None
@@ -609,7 +612,11 @@ def run_ours(args):
             "per_stage": {k: {"achieved": warp_inst[k] * B / (acc[k] * 1e-3) / 1e9,
                               "frac": warp_inst[k] * B / (acc[k] * 1e-3) / issue_peak}
                           for k in acc if k in warp_inst and acc[k] > 0},
-            "source": "profiles/traffic_r05.json (warp_inst_per_frame)"}
+            "source": "profiles/%s (warp_inst_per_frame)" % os.path.basename(cap_name)}
+    # every pixel stage against the HBM roofline: algorithmic bytes of the stage x frames / live stage time
+    roofline["hbm_per_stage"] = {k: {"achieved": stage_bytes[k] * B / (acc[k] * 1e-3) / 1e9,
+                                     "frac": stage_bytes[k] * B / (acc[k] * 1e-3) / 1e9 / hbm}
+                                 for k in ("pyramid", "fast", "blur") if acc.get(k, 0) > 0}
     pipe_gbs = ALGO_BYTES_PER_FRAME * B * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline["pipeline"] = {"achieved": pipe_gbs, "frac": pipe_gbs / hbm, "bytes_per_frame": ALGO_BYTES_PER_FRAME}
 
