@@ -186,7 +186,9 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
 
   // every role walks the same list: strips blockIdx.x, + gridDim.x, ...; the column chunks of a strip in order.
   // Tile number `tile` uses X stage tile % kBtStages and accumulator tile & 1; strip number sn uses T buffer sn & 1.
-  auto level_of = [&](int si) { int j = 0; while (j + 1 < P.nused && si >= P.lv[j + 1].strip0) ++j; return j; };
+  // (strips are visited in ascending order, so the level index only moves forward: a running search from the last one)
+  int lvl = 0;
+  auto level_of = [&](int si) { while (lvl + 1 < P.nused && si >= P.lv[lvl + 1].strip0) ++lvl; return lvl; };
 
   if (warp < kBtEpiWarps) {
     // ---------------- epilogue: horizontal pass + store ----------------

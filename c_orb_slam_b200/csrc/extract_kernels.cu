@@ -497,8 +497,11 @@ int launch_fast_cells(const Plan& p, const Scratch& sc, int nframes, cudaStream_
   // the opt-in belongs to the current device's context: set it on every launch rather than cache it process-wide
   if (smem > 48 * 1024)
     ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  // a few frames: 2 cells per block instead of 8, so that the cells of one frame fill the SMs
-  const int wpb = (long long)p.cells_per_frame * nframes >= 16 * 148 ? kFastWarps : 2;
+  // 2 cells per block: a block's slot is held until its slowest cell is done and cells differ a lot in work, so small
+  // blocks keep more warps resident (measured on 256 TUM frames: 8 warps 0.431 ms, 4: 0.418, 2: 0.414, 1: 0.416), and
+  // the cells of a single frame still fill the SMs.  ORB_GPU_FAST_WPB overrides (1..8).
+  static const int env_wpb = [] { const char* e = getenv("ORB_GPU_FAST_WPB"); return e ? atoi(e) : 0; }();
+  const int wpb = env_wpb > 0 ? min(env_wpb, kFastWarps) : 2;
   const dim3 grid((p.cells_per_frame + wpb - 1) / wpb, nframes);
   fast_cells_kernel<<<grid, wpb * 32, smem * wpb / kFastWarps, s>>>(p, sc, L);
   count_launch();
