@@ -7,6 +7,7 @@
 #define ORBEXTRACTOR_H
 
 #include <cassert>
+#include <cstdio>
 #include <cstring>
 #include <vector>
 
@@ -46,7 +47,11 @@ class ORBextractor {
     int n = 0;
     const int rc = orb_gpu_extract(mHandle, image.data, image.cols, image.rows, (size_t)image.step,
                                    reinterpret_cast<OrbKeyPoint*>(_keypoints.data()), mDesc.data(), capacity, &n);
-    if (rc != ORB_GPU_OK) n = 0;  // the reference has no error channel (void); see orb_gpu_last_error()
+    // The reference has no error channel (void).  ERR_CAPACITY means some level had more candidates than its key
+    // arrays hold: the keypoints of the other levels are valid and are kept; any other failure reports no keypoints.
+    // Either way the status stays in mLastStatus and the message in orb_gpu_last_error().
+    if (rc != ORB_GPU_OK && rc != ORB_GPU_ERR_CAPACITY) n = 0;
+    if (rc != ORB_GPU_OK) std::fprintf(stderr, "ORBextractor (GPU): status %d: %s\n", rc, orb_gpu_last_error());
     mLastStatus = rc;
     _keypoints.resize(n);
     if (n == 0) {
@@ -56,7 +61,7 @@ class ORBextractor {
       cv::Mat d = _descriptors.getMat();
       for (int i = 0; i < n; ++i) std::memcpy(d.ptr(i), &mDesc[(size_t)i * 32], 32);
     }
-    if (mbDownloadPyramid && rc == ORB_GPU_OK) {
+    if (mbDownloadPyramid && (rc == ORB_GPU_OK || rc == ORB_GPU_ERR_CAPACITY)) {
       for (int l = 0; l < nlevels; ++l) {
         int w = 0, h = 0;
         orb_gpu_get_pyramid(mHandle, 0, l, 0, nullptr, 0, &w, &h);
@@ -77,12 +82,17 @@ class ORBextractor {
   bool mbDownloadPyramid = true;        // monocular callers can switch the D2H of the pyramid off
   int mLastStatus = ORB_GPU_OK;
   OrbGpuExtractor* Handle() { return mHandle; }
+  // ---- not in the reference: which GPU this extractor computes on.  New objects take the process-wide default (0
+  // unless changed); SetDevice moves an existing object (its handle is rebuilt on the new device).
+  static int& DefaultDevice() { static int d = 0; return d; }
+  void SetDevice(int device) { if (device != mDevice) { mDevice = device; Recreate(mMaxW, mMaxH); } }
+  int GetDevice() const { return mDevice; }
 
  protected:
   void Recreate(int w, int h) {
     if (mHandle) orb_gpu_destroy(mHandle);
     mHandle = nullptr;
-    mLastStatus = orb_gpu_create(nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, w, h, 1, 0, &mHandle);
+    mLastStatus = orb_gpu_create(nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, w, h, 1, mDevice, &mHandle);
     mMaxW = w; mMaxH = h;
     mvScaleFactor.assign(nlevels, 0.f); mvInvScaleFactor.assign(nlevels, 0.f);
     mvLevelSigma2.assign(nlevels, 0.f); mvInvLevelSigma2.assign(nlevels, 0.f);
@@ -102,6 +112,7 @@ class ORBextractor {
   std::vector<int> mnFeaturesPerLevel;
   std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
   OrbGpuExtractor* mHandle = nullptr;
+  int mDevice = DefaultDevice();
   int mMaxW = 0, mMaxH = 0;
   std::vector<uint8_t> mDesc;
 };

@@ -11,6 +11,8 @@
 #include <cstdio>
 #include <mutex>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace orbgpu {
@@ -402,8 +404,10 @@ struct TmpDev {  // RAII for call-scoped device scratch
   template <class T> T* as() { return (T*)p; }
 };
 
-static int g_bf_variant = 3;   // 0: 8-POPC form, 1: carry-save form, 2: mma.sync IMMA form, 3: tcgen05 kind::i8 form (default)
-static int g_bf_qpt = 2;
+// Which brute-force form runs: 0: 8-POPC form, 1: carry-save form, 2: mma.sync IMMA form, 3: tcgen05 kind::i8 form
+// (default), and the queries per thread of the POPC forms -- ONE atomic word (form | qpt << 8), so a call that races the
+// test / bench setter still sees a consistent pair; all forms give identical results.
+static std::atomic<int> g_bf_form{3 | (2 << 8)};
 
 template <int QPT, bool CSA>
 static void bf_launch(dim3 grid, cudaStream_t s, const uint4* q, int nq, const uint4* db, long long ndb,
@@ -418,8 +422,7 @@ extern "C" {
 // test/bench knob: choose the inner-loop form (0 = 8 POPC, 1 = carry-save) and queries per thread
 int orb_gpu_set_bruteforce_variant(int csa, int qpt) {
   if ((qpt != 1 && qpt != 2 && qpt != 4) || csa < 0 || csa > 3) return ORB_GPU_ERR_ARG;
-  g_bf_variant = csa;
-  g_bf_qpt = qpt;
+  g_bf_form.store(csa | (qpt << 8), std::memory_order_relaxed);
   return ORB_GPU_OK;
 }
 
@@ -443,7 +446,8 @@ int orbgpu::bruteforce_device_impl(const uint8_t* d_q, int nq, const uint8_t* d_
   int dev = 0, sms = 148;
   ORB_CUDA_TRY(cudaGetDevice(&dev));
   ORB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int qpt = g_bf_qpt;
+  const int form = g_bf_form.load(std::memory_order_relaxed);
+  const int qpt = form >> 8, g_bf_variant = form & 0xff;
   const bool mma = g_bf_variant >= 2, tc5 = g_bf_variant == 3;  // both tensor-core forms take 256 queries per block
   const int qblocks = mma ? (nq + kMmaQueries - 1) / kMmaQueries : (nq + kBfThreads * qpt - 1) / (kBfThreads * qpt);
   // Database slices.  tcgen05 form (one block per SM): ONE wave of blocks -- every slice restarts the top-2
