@@ -1220,7 +1220,7 @@ __device__ __forceinline__ void sincos_0_2pi(double x, double* s, double* c) {
   *c = ((q + 1) & 2) ? -c0 : c0;
 }
 
-constexpr int kOdWarps = 8, kOdSlotsPerWarp = 4, kOdSlotsPerBlock = kOdWarps * kOdSlotsPerWarp;
+constexpr int kOdWarps = 8, kOdSlotsPerWarp = 8, kOdSlotsPerBlock = kOdWarps * kOdSlotsPerWarp;
 constexpr int kOdReach = 18;                      // |rotated tap| <= ceil(13 * sqrt(2)) = 18 < EDGE_THRESHOLD
 constexpr int kOdRows = 2 * kOdReach + 1;         // 37 rows of the blurred level around the keypoint
 constexpr int kOdWords = (kOdRows + 3 + 3) / 4;   // 10 words per row: 37 px + alignment offset (<= 3)
@@ -1234,7 +1234,7 @@ __device__ __forceinline__ int round_half_even(float v) {
 }
 
 // One block = 32 consecutive output slots (level, rank in the level's selection) of one frame, one warp
-// per slot, 4 slots per warp.  IC_Angle: lane = patch column u, the rows of the disc that contain it
+// per slot, 8 slots per warp (the pattern copy and the level prefix of a block are shared by 64 keypoints).  IC_Angle: lane = patch column u, the rows of the disc that contain it
 // are |v| <= umax[|u|] (the disc is symmetric), 31 coalesced byte loads, shuffle reduction.
 __global__ void __launch_bounds__(kOdWarps * 32, 5)
 orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
@@ -1279,12 +1279,12 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   const int ic_r = lane / kIcWords, ic_c = lane - ic_r * kIcWords;  // (row, word) inside a 3-row step, lanes 0..26
   const unsigned ic_dst = (unsigned)__cvta_generic_to_shared(my_ic + ic_r * kIcWords + ic_c);
 
+  int level = 0;
   for (int it = 0; it < slots_per_warp; ++it) {
     const int slot = blockIdx.x * (slots_per_warp * kOdWarps) + it * kOdWarps + warp;
     if (slot >= p.slots_per_frame) break;
-    int level = 0;
-#pragma unroll
-    for (int l = 1; l < kMaxLevels; ++l) level += slot >= s_base[l];
+    // the slots a warp visits ascend, so the level only moves forward
+    while (level + 1 < p.nlevels && slot >= s_base[level + 1]) ++level;
     const LevelGeom& g = p.lv[level];
     const int rank = slot - g.slot_base;
     if (rank >= s_cnt[level]) continue;
@@ -1401,7 +1401,8 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
 int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s) {
   // a few frames: one keypoint slot per warp instead of four (more, shorter blocks)
-  const int spw = (long long)p.slots_per_frame * nframes >= 4 * kOdSlotsPerBlock * 148 ? kOdSlotsPerWarp : 1;
+  static const int env_spw = [] { const char* e = getenv("ORB_GPU_OD_SPW"); return e ? atoi(e) : 0; }();
+  const int spw = env_spw > 0 ? env_spw : (long long)p.slots_per_frame * nframes >= 4 * kOdSlotsPerBlock * 148 ? kOdSlotsPerWarp : 1;
   const dim3 grid((p.slots_per_frame + spw * kOdWarps - 1) / (spw * kOdWarps), nframes);
   orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out, spw);
   count_launch();

@@ -303,7 +303,9 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
     if (g.n_ini < 1 || g.n_ini > 255) return ORB_GPU_ERR_ARG;  // portrait shapes: nIni == 0
     g.hx = width / (float)g.n_ini;
     g.quota = h->quota[l];
-    g.key_cap = pow2ceil(std::min<long long>(32768, std::max<long long>(1024, (long long)g.w * g.h / 16)));
+    // candidate capacity of the level: one per 16 pixels (the synthetic textured frames have one per ~150), at most
+    // 2^18 -- a 4096 x 4096 level 0 with one candidate per 64 pixels still fits (keys and payload: 12 bytes each)
+    g.key_cap = pow2ceil(std::min<long long>(262144, std::max<long long>(1024, (long long)g.w * g.h / 16)));
     g.key_base = keys;
     keys += g.key_cap;
     g.slot_base = slots;

@@ -85,3 +85,17 @@ def test_euroc_batch_1024_properties(gpu, oracle):
         for f in ("x", "y", "size", "response", "octave", "angle"):
             assert np.array_equal(ko[f], kg[f]), f
         assert np.array_equal(do, d_d[j, :len(ko)].cpu().numpy())
+
+
+def test_4k_frame_with_more_than_32768_candidates_per_level(gpu, oracle):
+    """A 3840 x 2160 textured frame has ~57 k FAST candidates on level 0 -- more than the 4096 keys the quadtree sorts
+    in shared memory and more than the 32768 its arrays held in round 1: the global-memory key path (bitonic sort)
+    gives the reference's keypoints and descriptors (src/ORBextractor.cc:539-763 on a large level)."""
+    W, H = 3840, 2160
+    img = synth.make_frame(W, H, 5)
+    ex = gpu.ORBextractor(5000, 1.2, 8, 20, 7, max_width=W, max_height=H)
+    k, d = ex(img)
+    ex_o = oracle.Extractor(5000, 1.2, 8, 20, 7)
+    ko, do = ex_o(img)
+    assert len(ex_o.candidates(0)) > 32768
+    assert len(k) == len(ko) and np.array_equal(k, ko) and np.array_equal(d, do)
