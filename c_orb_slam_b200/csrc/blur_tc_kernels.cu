@@ -8,9 +8,11 @@
 //                     D[r][c] = sum_k T[r][k] * X[k][c],  T[r][r + i] = k_i.  The frames of a level are stacked
 //                     (rows of frame f start at f * h), a strip is 128 stacked rows, and REFLECT_101 at the top and
 //                     bottom of a frame is folded into T (a tap that leaves the frame adds its weight to the row it
-//                     reflects to, which always lies inside the 7-row window) -- T is rebuilt per strip (7 bytes per row).
-//                     X (136 rows x 256 columns, starting 16 columns left of the chunk: TMA wants 16-byte aligned box starts) comes straight from the pyramid by TMA (cp.async.bulk.tensor, 128-byte
-//                     swizzle) and is the MN-major B operand; rows 134..159 of the K = 160 extent meet zero weights (they are whatever follows the tile in shared memory).
+//                     reflects to, which always lies inside the 7-row window) -- T is rebuilt per strip (7 bytes per
+//                     row).  X (136 rows x 256 columns, starting 16 columns left of the chunk: TMA wants 16-byte
+//                     aligned box starts) comes straight from the pyramid by TMA (cp.async.bulk.tensor, 128-byte
+//                     swizzle) and is the MN-major B operand; rows 136..159 of the K = 160 extent meet zero weights
+//                     (they are whatever follows the tile in shared memory).
 //   horizontal pass = in registers: the epilogue thread of TMEM lane r owns row r, reads its 16-bit column sums
 //                     two to a register (tcgen05.ld pack::16b) and takes the seven taps from neighbouring registers
 //                     (IDP.2A, the +32768 rounding folded into the accumulator).  REFLECT_101 at the left and right
@@ -21,9 +23,10 @@
 //
 // One persistent block per SM walks strips (all column chunks of a strip share T).  Roles: warps 0..15 epilogue (two
 // sets of eight, set i drains accumulator i: a warp owns 32 rows x 112 columns), warp 16 TMA loads, warp 17 MMA issue +
-// TMEM allocation, warp 18 builds T
-// and patches the halo columns.  Pipelines: x_full (TMA bytes) -> x_ready (patched) -> MMA -> x_empty / acc_full ->
-// epilogue -> acc_empty; t_ready / t_empty for the two T buffers.
+// TMEM allocation, warp 18 builds T and patches the halo columns.  Pipelines: x_full (TMA bytes) -> x_ready (patched)
+// -> MMA -> x_empty / acc_full -> epilogue -> acc_empty; t_ready / t_empty for the two T buffers.
+// Bring-up notes (tools/ubench/tma_probe.cu): a box whose first column is not a multiple of 16 bytes faults with
+// "illegal instruction"; MN-major SWIZZLE_128B descriptors take LBO = bytes between the 128-column atoms, SBO = 1024.
 #include <cuda.h>
 
 #include <cstdlib>
@@ -97,13 +100,6 @@ __device__ __forceinline__ void bt_ld64p(uint32_t (&v)[32], uint32_t taddr) {
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
       "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
       : BT_R8(v, 0), BT_R8(v, 8), BT_R8(v, 16), BT_R8(v, 24)
-      : "r"(taddr));
-}
-__device__ __forceinline__ void bt_ld32p(uint32_t (&v)[32], uint32_t taddr) {  // registers 0..15
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : BT_R8(v, 0), BT_R8(v, 8)
       : "r"(taddr));
 }
 __device__ __forceinline__ void bt_ld8p(uint32_t (&v)[4], uint32_t taddr) {
