@@ -42,7 +42,7 @@ EXPORTS = [
     "orb_gpu_launch_count", "orb_gpu_popc_peak", "orb_gpu_imma_peak", "orb_gpu_umma_peak",
     "orb_gpu_frame_create", "orb_gpu_frame_destroy", "orb_gpu_frame_size", "orb_gpu_frame_upload",
     "orb_gpu_frame_from_device", "orb_gpu_frame_search_by_projection", "orb_gpu_frame_search_windowed",
-    "orb_gpu_match_bruteforce_noalloc_device", "orb_gpu_exchange_match_bruteforce_device",
+    "orb_gpu_match_bruteforce_noalloc_device", "orb_gpu_exchange_match_bruteforce_device", "orb_gpu_set_resize_variant",
 ]
 
 STATUS = {0: "OK", -1: "ERR_ARG", -2: "ERR_CAPACITY", -3: "ERR_CUDA", -4: "ERR_STATE"}

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborb_gpu.so")
-SOURCES = ["orb_gpu.cu", "extract_kernels.cu", "blur_tc_kernels.cu", "match_kernels.cu", "match_tc5_kernels.cu", "exchange_kernels.cu", "window_kernels.cu", "stereo_kernels.cu", "mappoint_kernels.cu", "vocabulary_kernels.cu"]
+SOURCES = ["orb_gpu.cu", "extract_kernels.cu", "blur_tc_kernels.cu", "resize_tc_kernels.cu", "match_kernels.cu", "match_tc5_kernels.cu", "exchange_kernels.cu", "window_kernels.cu", "stereo_kernels.cu", "mappoint_kernels.cu", "vocabulary_kernels.cu"]
 HEADERS = ["common.cuh", "umma.cuh", "brief_pattern.inc", os.path.join("..", "..", "include", "orb_gpu.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-fmad=false",  # float ops must round one by one (parity with the reference's CPU math)

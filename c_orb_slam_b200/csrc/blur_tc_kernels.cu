@@ -383,6 +383,8 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int tensor_map_2d(CUtensorMap* out, const void* base, int w, long long rows, int pitch, int box_w, int box_h,
+                         bool swizzle128);
 static EncodeTiledFn encode_tiled_fn() {
   static EncodeTiledFn fn = [] {
     void* p = nullptr;
@@ -396,6 +398,10 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 
 // u8 matrix [rows][w] with `pitch` bytes per row; box = box_w x box_h
+bool tma_available() { return encode_tiled_fn() != nullptr; }
+int tensor_map_2d_u8(void* out_map, const void* base, int w, long long rows, int pitch, int box_w, int box_h, bool swizzle128) {
+  return tensor_map_2d(reinterpret_cast<CUtensorMap*>(out_map), base, w, rows, pitch, box_w, box_h, swizzle128);
+}
 static int tensor_map_2d(CUtensorMap* out, const void* base, int w, long long rows, int pitch, int box_w, int box_h,
                          bool swizzle128) {
   typedef std::tuple<const void*, int, long long, int, int, int> Key;

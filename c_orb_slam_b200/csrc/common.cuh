@@ -27,6 +27,7 @@ struct LevelGeom {
   // resize tables (level >= 1): source taps and 11-bit weights per destination column/row
   const int* xofs; const short* ax0; const short* ax1;
   const int* yofs; const short* ay0; const short* ay1;
+  const short* yinv;        // [h of level l-1]: destination row with yofs == source row, or -1
   // FAST cell grid (:778-806)
   int ncols, nrows, wcell, hcell;
   int max_bx, max_by;       // maxBorderX/Y = w-16, h-16
@@ -139,6 +140,14 @@ int launch_blur(const Plan& p, int nframes, cudaStream_t s);
 // blur_tc_kernels.cu: the levels in level_mask on the tensor cores (TMA in, tcgen05.mma, TMA out)
 bool blur_tc_level_ok(const LevelGeom& g, int nframes);
 int launch_blur_tc(const Plan& p, int nframes, unsigned level_mask, cudaStream_t s);
+// resize_tc_kernels.cu: level l from l-1 with the horizontal pass on the tensor cores; false / not launched when the
+// level pair does not qualify (TMA alignment, frame gaps, scale factor above ~1.85)
+bool resize_tc_level_ok(const LevelGeom& src, const LevelGeom& dst, int nframes);
+int launch_resize_tc(const LevelGeom& src, const LevelGeom& dst, int nframes, cudaStream_t s);
+int resize_variant();  // 0: byte-SIMD (default), 1: tensor-core form for batches (orb_gpu_set_resize_variant)
+// cached 2-D u8 tensor map (CUtensorMap, 128 bytes) of [rows][w] with `pitch` bytes per row and a box_w x box_h box
+int tensor_map_2d_u8(void* out_map, const void* base, int w, long long rows, int pitch, int box_w, int box_h, bool swizzle128);
+bool tma_available();
 int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoint* d_kps,
                        uint8_t* d_desc, int capacity, int* d_n_out, cudaStream_t s);
 int launch_export_candidates(const Plan& p, const Scratch& sc, int frame, int level, float* d_xyr,

@@ -191,6 +191,10 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows p
 
 int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
   const LevelGeom& d = p.lv[level];
+  // selectable form (orb_gpu_set_resize_variant(1), not the default: measured slower): horizontal pass on
+  // the tensor cores for batches of 8 frames and more when the level pair qualifies
+  if (resize_variant() == 1 && nframes >= 8 && resize_tc_level_ok(p.lv[level - 1], d, nframes))
+    return launch_resize_tc(p.lv[level - 1], d, nframes, s);
   static const bool two_col = [] { const char* e = getenv("ORB_GPU_RESIZE2"); return e && atoi(e); }();
   dim3 grid((d.h + kRzRows - 1) / kRzRows, nframes);
   // a few frames: bands of 4 rows instead of 16, so that one frame's level still spreads over the SMs

@@ -315,7 +315,7 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
     h->lvl_off[l] = pyr_bytes;
     pyr_bytes += align_up((size_t)g.frame_stride * batch, 256);
     tab_off[l] = table_bytes;
-    table_bytes += align_up((size_t)g.w * 8 + (size_t)g.h * 8, 16);
+    table_bytes += align_up((size_t)g.w * 8 + (size_t)g.h * 8 + (l > 0 ? (size_t)p.lv[l - 1].h * 2 : 0), 16);
     if (quadtree_smem_bytes(p, l) > 227 * 1024) return ORB_GPU_ERR_CAPACITY;
   }
   p.cells_per_frame = cells;
@@ -347,11 +347,17 @@ static int ensure_plan(OrbGpuExtractor* h, int w, int ht, int batch) {
     if (l > 0) {
       resize_axis_table(p.lv[l - 1].w, g.w, xofs, ax0, ax1);
       resize_axis_table(p.lv[l - 1].h, g.h, yofs, ay0, ay1);
+      // inverse of yofs for the tensor-core resize: the destination row whose upper source row is s, or -1 (for a
+      // scale factor > 1 every source row is the upper tap of at most one destination row)
+      short* yinv = ay1 + g.h;
+      for (int sy = 0; sy < p.lv[l - 1].h; ++sy) yinv[sy] = -1;
+      for (int dy = 0; dy < g.h; ++dy) yinv[yofs[dy]] = (short)dy;
     }
     uint8_t* dbase = (uint8_t*)h->tables.p + tab_off[l];
     g.xofs = (const int*)dbase; g.yofs = g.xofs + g.w;
     g.ax0 = (const short*)(g.yofs + g.h); g.ax1 = g.ax0 + g.w;
     g.ay0 = g.ax1 + g.w; g.ay1 = g.ay0 + g.h;
+    g.yinv = l > 0 ? g.ay1 + g.h : nullptr;
   }
   // FAST cell ROIs (:789-806): the skip rules differ for rows (maxBorderY-3) and columns (maxBorderX-6)
   std::vector<uint2> ctab(cells);

@@ -392,6 +392,10 @@ int orb_gpu_stereo_match(const OrbKeyPoint* kl, const uint8_t* dl, int nl, const
  * 2 (tensor cores through mma.sync m16n8k32 s8 x u8) or 3 (tcgen05.mma kind::i8 with TMEM accumulators; the
  * default); qpt = queries per thread of forms 0 and 1 (1, 2 or 4).  All forms return identical results. */
 int orb_gpu_set_bruteforce_variant(int csa, int qpt);
+/* Test / bench knob for A2 (ComputePyramid, src/ORBextractor.cc:1107-1132): 0 = the byte-SIMD resize kernel (default),
+ * 1 = the form with the horizontal pass on the tensor cores (tcgen05.mma + TMA) for batches of 8 frames and more.
+ * Identical pixels; the second form is measured slower and kept as evidence. */
+int orb_gpu_set_resize_variant(int variant);
 
 /* Per-stage device time of the last extract call on this handle (CUDA events on the stream the
  * kernels ran on): ms5 = pyramid, FAST, quadtree, blur, orientation+descriptors. */

@@ -202,3 +202,30 @@ def test_blur_of_frames_tma_cannot_address(gpu, oracle):
             assert np.array_equal(ex.pyramid_level(l, f, blurred=True), oracle.gaussian_blur7(ex.pyramid_level(l, f))), (f, l)
         ko, do = ex_o(frames[f])
         assert n[f] == len(ko) and np.array_equal(kps[f, :n[f]], ko) and np.array_equal(desc[f, :n[f]], do)
+
+
+@pytest.mark.parametrize("W,H,scale,nlevels,B", [(640, 480, 1.2, 8, 9), (752, 480, 1.2, 8, 8), (1241, 376, 1.2, 8, 8),
+                                                 (643, 231, 1.3, 5, 11), (400, 300, 1.08, 10, 8), (1920, 1080, 1.5, 4, 8),
+                                                 (800, 600, 1.85, 3, 8)])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_batch_pyramid_levels_pixel_exact(gpu, oracle, W, H, scale, nlevels, B, variant):
+    """Every level of every frame of a batch == cv::resize of the level below (src/ORBextractor.cc:1107-1132), pixel
+    for pixel, for both resize forms: the byte-SIMD kernel (default) and the tensor-core form (stacked frames, strips that
+    cross frame boundaries, partial column chunks, weight matrices rebuilt per chunk, scale factors up to its limit of ~1.85)."""
+    frames = synth.make_frames(W, H, B, seed0=123)
+    ex = gpu.ORBextractor(300, scale, nlevels, 20, 7, max_width=W, max_height=H, max_batch=B)
+    assert gpu.lib().orb_gpu_set_resize_variant(variant) == 0
+    try:
+        ex.extract_batch(frames)
+    finally:
+        gpu.lib().orb_gpu_set_resize_variant(0)
+    for f in range(B):
+        prev = frames[f]
+        for l in range(1, nlevels):
+            got = ex.pyramid_level(l, f)
+            want = oracle.resize_linear(prev, got.shape[1], got.shape[0])
+            if not np.array_equal(got, want):
+                ys, xs = np.nonzero(got != want)
+                raise AssertionError("frame %d level %d: %d mismatches, rows %d..%d cols %d..%d, first (y=%d,x=%d) got %d want %d" % (
+                    f, l, len(ys), ys.min(), ys.max(), xs.min(), xs.max(), ys[0], xs[0], got[ys[0], xs[0]], want[ys[0], xs[0]]))
+            prev = got

@@ -173,6 +173,67 @@ __global__ void __launch_bounds__(128, 1) k_gmap(const CUtensorMap* gm, int x, i
   if (threadIdx.x == 0) mark(3, 1);
 }
 
+// mode 8: horizontal resize pass as MMAs: A = image tile from TMA (K-major, SWIZZLE_128B, two atoms of 128 columns),
+// B = weight matrices [N = 128 destination columns][K = 192 source columns] (K-major, unswizzled core matrices; hi
+// weights x 16 and lo weights), D_hi / D_lo in two 128-column accumulators.  Host check: D_hi + (D_lo >> 4) == T >> 4.
+__global__ void __launch_bounds__(128, 1) k_hres(const CUtensorMap* m, int x, int y, const uint8_t* w_hi, const uint8_t* w_lo,
+                                                 uint32_t a_lbo, int32_t* out) {
+  extern __shared__ uint8_t raw[];
+  uint8_t* sm = raw + (((smem_u32(raw) + 1023u) & ~1023u) - smem_u32(raw));
+  uint8_t* s_a = sm;                       // 2 atoms x 128 rows x 128 B
+  uint8_t* s_w = sm + 2 * 16384;           // 2 x [128][192]: (k>>4)*2048 + (n>>3)*128 + (n&7)*16 + (k&15)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_w + 2 * 128 * 192);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 2);
+  const int t = threadIdx.x, warp = t >> 5;
+  for (int i = t; i < 128 * 192; i += 128) { s_w[i] = w_hi[i]; s_w[128 * 192 + i] = w_lo[i]; }
+  if (t == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar + 1)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(256u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+  if (t == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(2 * 16384) : "memory");
+    for (int a = 0; a < 2; ++a)
+      asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                   ::"r"(smem_u32(s_a + a * 16384)), "l"(m), "r"(smem_u32(bar)), "r"(x + 128 * a), "r"(y) : "memory");
+    mbar_wait(smem_u32(bar), 0);
+    // instruction descriptor: D s32, A u8 K-major, B u8 K-major, N = 128, M = 128
+    const uint32_t idesc = (2u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    for (int half = 0; half < 2; ++half)
+      for (int k = 0; k < 6; ++k) {
+        const uint32_t a_addr = smem_u32(s_a + (k >> 2) * 16384) + (k & 3) * 32;
+        const uint64_t da = (uint64_t)((a_addr & 0x3ffffu) >> 4) | ((uint64_t)(a_lbo >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        const uint32_t b_addr = smem_u32(s_w + half * 128 * 192) + k * 2 * 2048;
+        const uint64_t db = (uint64_t)((b_addr & 0x3ffffu) >> 4) | ((uint64_t)(2048 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(tmem + half * 128), "l"(da), "l"(db), "r"(idesc), "r"(k > 0 ? 1u : 0u) : "memory");
+      }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar + 1)) : "memory");
+  }
+  mbar_wait(smem_u32(bar + 1), 0);
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  for (int c = 0; c < 256; c += 8) {
+    uint32_t v[8];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(tmem + ((uint32_t)(warp * 32) << 16) + c));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    for (int i = 0; i < 8; ++i) out[t * 256 + c + i] = (int32_t)v[i];
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256u) : "memory");
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -204,6 +265,44 @@ int main(int argc, char** argv) {
   CUtensorMap* d_map; CK(cudaMalloc(&d_map, sizeof(m)));
   CK(cudaMemcpy(d_map, &m, sizeof(m), cudaMemcpyHostToDevice));
   auto expect = [&](int k, int n) -> int { const int y = y0 + k, x = x0 + n; return (y < 0 || y >= H || x < 0 || x >= W) ? 0 : img[(size_t)y * W + x]; };
+  if (mode == 8) {
+    // box 128 columns x 128 rows for the A tile
+    const cuuint32_t boxa[2] = {128, 128};
+    CUtensorMap ma;
+    r = ((EncodeTiledFn)fp)(&ma, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, d_img, dims, strides, boxa, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { printf("encode A rc=%d\n", (int)r); return 1; }
+    CUtensorMap* d_ma; CK(cudaMalloc(&d_ma, sizeof(ma))); CK(cudaMemcpy(d_ma, &ma, sizeof(ma), cudaMemcpyHostToDevice));
+    // destination column n takes source columns xo[n], xo[n] + 1 of the tile with 11-bit weights a0 + a1 = 2048
+    std::vector<int> xo(128), a0(128), a1(128);
+    std::vector<uint8_t> whi(128 * 192, 0), wlo(128 * 192, 0);
+    auto at = [](int n, int k) { return (k >> 4) * 2048 + (n >> 3) * 128 + (n & 7) * 16 + (k & 15); };
+    for (int n = 0; n < 128; ++n) {
+      xo[n] = (int)(n * 1.2) + 5; a1[n] = (n * 37) % 2049; a0[n] = 2048 - a1[n];
+      whi[at(n, xo[n])] = (uint8_t)((a0[n] >> 8) * 16); wlo[at(n, xo[n])] = (uint8_t)(a0[n] & 255);
+      whi[at(n, xo[n] + 1)] = (uint8_t)((a1[n] >> 8) * 16); wlo[at(n, xo[n] + 1)] = (uint8_t)(a1[n] & 255);
+    }
+    uint8_t *d_whi, *d_wlo; CK(cudaMalloc(&d_whi, whi.size())); CK(cudaMalloc(&d_wlo, wlo.size()));
+    CK(cudaMemcpy(d_whi, whi.data(), whi.size(), cudaMemcpyHostToDevice)); CK(cudaMemcpy(d_wlo, wlo.data(), wlo.size(), cudaMemcpyHostToDevice));
+    int32_t* d_out; CK(cudaMalloc(&d_out, 128 * 256 * 4));
+    const int smem8 = 2 * 16384 + 2 * 128 * 192 + 1024 + 256;
+    CK(cudaFuncSetAttribute(k_hres, cudaFuncAttributeMaxDynamicSharedMemorySize, smem8));
+    const uint32_t a_lbo = argc > 2 ? atoi(argv[2]) : 16;
+    k_hres<<<1, 128, smem8>>>(d_ma, x0, y0, d_whi, d_wlo, a_lbo, d_out);
+    CK(cudaGetLastError());
+    { cudaError_t e = cudaDeviceSynchronize(); if (e) { printf("mode 8 sync: %s\n", cudaGetErrorString(e)); return 1; } }
+    std::vector<int32_t> out(128 * 256);
+    CK(cudaMemcpy(out.data(), d_out, out.size() * 4, cudaMemcpyDeviceToHost));
+    long bad = 0;
+    for (int rr = 0; rr < 128; ++rr)
+      for (int n = 0; n < 128; ++n) {
+        const int T = a0[n] * expect(rr, xo[n]) + a1[n] * expect(rr, xo[n] + 1);
+        const int got = out[rr * 256 + n] + (out[rr * 256 + 128 + n] >> 4);
+        if (got != (T >> 4)) { if (bad < 6) printf("  (row=%d, n=%d) hi %d lo %d -> %d want %d\n", rr, n, out[rr * 256 + n], out[rr * 256 + 128 + n], got, T >> 4); ++bad; }
+      }
+    printf("mode 8 (A lbo %u): horizontal-pass mismatches: %ld of %d\n", a_lbo, bad, 128 * 128);
+    return 0;
+  }
   if (mode >= 3 && mode <= 6) {
     uint8_t* d_out; CK(cudaMalloc(&d_out, 2 * kAtom));
     int bytes = 4096;
