@@ -201,7 +201,10 @@ static std::vector<int> host_schedule(int nb) {
     for (int t : forced.second) tail_sum += t;
     return schedule_from(forced.first, tail_sum < nb ? forced.second : std::vector<int>(), nb);
   }
+  // default: chunks of c frames with a half-size first chunk (the kernels start after half the upload time) and a
+  // half-size last one (half the tail behind the last upload); measured on 512 TUM frames: 3.45 vs 3.52 ms
   const int c = host_chunk(nb);
+  if (nb >= 4 * c && c >= 16) return schedule_from({c / 2, c}, {c / 2}, nb);
   std::vector<int> b(1, 0);
   while (b.back() < nb) b.push_back(std::min(nb, b.back() + c));
   return b;
