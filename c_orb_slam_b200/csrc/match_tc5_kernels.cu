@@ -21,6 +21,7 @@
 // Pipelines: b_full/b_empty (expanders <-> MMA, 2 stages), acc_full/acc_empty (MMA <-> epilogue, the two
 // accumulators alternate so the epilogue of one overlaps the MMAs of the other).
 #include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 #include "umma.cuh"
@@ -53,6 +54,25 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t da, uint64_t d
 
 #define T5_R8(v, o) "=r"(v[o]), "=r"(v[o + 1]), "=r"(v[o + 2]), "=r"(v[o + 3]), "=r"(v[o + 4]), "=r"(v[o + 5]), "=r"(v[o + 6]), "=r"(v[o + 7])
 #define T5_RW8(v, o) "+r"(v[o]), "+r"(v[o + 1]), "+r"(v[o + 2]), "+r"(v[o + 3]), "+r"(v[o + 4]), "+r"(v[o + 5]), "+r"(v[o + 6]), "+r"(v[o + 7])
+// The issuing warp runs its loop converged and one elected lane issues (elect.sync inside the asm): the control flow
+// around the MMAs stays warp-uniform, so the descriptors are computed and kept in uniform registers.
+__device__ __forceinline__ void umma_i8_elect(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(kT5Idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(bar)
+      : "memory");
+}
 // 64 consecutive accumulator columns of this thread's TMEM lane, the low 16 bits of each packed two to a
 // register (column 2r in the low half of register r): |64 * S| <= 16384 fits
 __device__ __forceinline__ void tmem_ld64p(uint32_t (&v)[32], uint32_t taddr) {
@@ -172,7 +192,8 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
   // barrier slots: 0,1 b_full  2,3 b_empty  4,5 acc_full  6,7 acc_empty
   auto bar = [&](int i) { return bar0 + 8u * i; };
 
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int t = threadIdx.x, lane = t & 31;
+  const int warp = __shfl_sync(0xffffffffu, t >> 5, 0);  // provably warp-uniform: the role branches stay uniform
   const int slice = blockIdx.y;
   const long long row0 = (long long)slice * slice_rows;
   const int rows = (int)min(slice_rows, ndb - row0);
@@ -283,28 +304,36 @@ bruteforce_tc5_kernel(const uint4* __restrict__ q, int nq, const uint4* __restri
       if (nslices > 1 || fx.world > 1) __threadfence();  // the slice's result is visible before this block takes its ticket
     }
   } else if (warp == kT5EpiWarps) {
-    // ---- MMA issuer
-    if (lane == 0) {
-      const uint64_t da[2] = {umma_desc(smem_u32(s_a), 2048, 128), umma_desc(smem_u32(s_a + kT5ATile), 2048, 128)};
-      const uint64_t dbs[2] = {umma_desc(smem_u32(s_b), 4096, 128), umma_desc(smem_u32(s_b + kT5BStage), 4096, 128)};
-      for (int tile = 0; tile < ntiles; ++tile) {
-        const int s = tile & 1, u = tile >> 1;
-        mbar_wait(bar(s), u & 1);
+    // ---- MMA issuer: the whole warp, converged (see umma_i8_elect)
+    {
+      // Every descriptor is base + constant with compile-time stage, accumulator and K step (the tile loop is
+      // unrolled by the two stages).  A descriptor selected at run time goes through ONE uniform register pair
+      // that is rewritten before every MMA, and the rewrite waits until the previous MMA has read it: the tensor
+      // pipe then idles ~40 clk per MMA (tools/ubench/tmem_a_probe.cu).
+      const uint64_t da0 = umma_desc(smem_u32(s_a), 2048, 128), db0 = umma_desc(smem_u32(s_b), 4096, 128);
+      auto issue_tile = [&](auto stage, int tile) {
+        constexpr int s = decltype(stage)::value;
+        mbar_wait(bar(s), (tile >> 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int acc = 0; acc < 2; ++acc) {
-          mbar_wait(bar(6 + acc), (tile & 1) ^ 1);
+          mbar_wait(bar(6 + acc), s ^ 1);
           tc_fence_after();
 #pragma unroll
           for (int k = 0; k < 8; ++k)  // K = 32 bytes = two 16-byte chunks per step
-            umma_i8(tmem_base + acc * 256, da[acc] + (uint64_t)(k * (2 * 2048 >> 4)),
-                    dbs[s] + (uint64_t)(k * (2 * 4096 >> 4)), k > 0);
-          umma_commit(bar(4 + acc));
+            umma_i8_elect(tmem_base + acc * 256, da0 + (uint64_t)((acc * kT5ATile + k * 2 * 2048) >> 4),
+                          db0 + (uint64_t)((s * kT5BStage + k * 2 * 4096) >> 4), k > 0);
+          umma_commit_elect(bar(4 + acc));
         }
-        umma_commit(bar(2 + s));
+        umma_commit_elect(bar(2 + s));
+      };
+      for (int tile = 0; tile < ntiles; tile += 2) {
+        issue_tile(std::integral_constant<int, 0>{}, tile);
+        if (tile + 1 < ntiles) issue_tile(std::integral_constant<int, 1>{}, tile + 1);
       }
       // the last commit must have landed before the block (and its shared memory) goes away
       if (ntiles > 0) mbar_wait(bar(2 + ((ntiles - 1) & 1)), ((ntiles - 1) >> 1) & 1);
+      __syncwarp();
     }
   } else {
     // ---- expanders: rows e, e + 128 of every tile

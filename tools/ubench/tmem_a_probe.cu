@@ -73,16 +73,17 @@ __global__ void __launch_bounds__(128, 1) probe(const uint8_t* a_rows /*[128][64
 
 // Issue rate: lane 0 of one block per SM issues n x 8 MMAs (M128, N, K32) back to back, A from shared memory (mode 0)
 // or from tensor memory (mode 1), two accumulators alternating when 2N + 64 <= 512 columns.
-__global__ void __launch_bounds__(128, 1) rate(int mode, int N, int n, long long* clk) {
+__global__ void __launch_bounds__(128, 1) rate(int mode, int N, int n, long long* clk, int commit_every) {
   extern __shared__ __align__(128) uint8_t sm[];
   uint8_t* s_a = sm;                 // 128 x 256 bytes
   uint8_t* s_b = sm + 32768;         // N x 256 bytes
   uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 32768 + 65536);
-  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 1);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 2);
   const int t = threadIdx.x, warp = t >> 5;
   for (int i = t; i < (32768 + 65536) / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0x01010101u;
   if (t == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar + 1)) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -103,11 +104,14 @@ __global__ void __launch_bounds__(128, 1) rate(int mode, int N, int n, long long
     const long long c0 = clock64();
     // flat loop, one MMA per iteration (an unrolled loop with the mode test inside issues no faster than one MMA per 93 clk)
     const uint32_t kb = (uint32_t)(2 * 16 * N >> 4);
+    const int cmask = commit_every ? commit_every - 1 : 0x7fffffff;
     if (mode == 0) {
       for (int i = 0; i < 8 * n; ++i) {
         const int k = i & 7;
         asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
                      ::"r"(tmem + (two ? ((i >> 3) & 1) * N : 0)), "l"(da + (uint64_t)(k * 256)), "l"(db + (uint64_t)(k * kb)), "r"(idesc), "r"(i > 15 ? 1u : 0u) : "memory");
+        if ((i & cmask) == cmask)  // a commit nobody waits for (the phase just flips)
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar + 1)) : "memory");
       }
     } else {
       for (int i = 0; i < 8 * n; ++i) {
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(128, 1) rate(int mode, int N, int n, long long
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
 }
 
-static void run_rate(int mode, int N, int n = 8192) {
+static void run_rate(int mode, int N, int n = 8192, int commit_every = 0) {
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   const int smem = 32768 + 65536 + 64;
@@ -136,11 +140,11 @@ static void run_rate(int mode, int N, int n = 8192) {
   cudaEventCreate(&e0); cudaEventCreate(&e1);
   static long long* d_clk = nullptr;
   if (!d_clk) cudaMalloc(&d_clk, 8);
-  for (int r = 0; r < 40; ++r) rate<<<sms, 128, smem>>>(mode, N, n, d_clk);
+  for (int r = 0; r < 40; ++r) rate<<<sms, 128, smem>>>(mode, N, n, d_clk, commit_every);
   float best = 1e9f;
   for (int r = 0; r < 12; ++r) {
     cudaEventRecord(e0);
-    rate<<<sms, 128, smem>>>(mode, N, n, d_clk);
+    rate<<<sms, 128, smem>>>(mode, N, n, d_clk, commit_every);
     cudaEventRecord(e1);
     cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms, e0, e1);
@@ -150,9 +154,84 @@ static void run_rate(int mode, int N, int n = 8192) {
   const double mac = (double)sms * n * 8 * 128.0 * N * 32.0 / (best * 1e-3);
   long long clk = 0;
   cudaMemcpy(&clk, d_clk, 8, cudaMemcpyDeviceToHost);
-  printf("rate (%5d x 8 MMAs): A from %s, N = %3d: %.3f ms, %.1f TMAC/s (%.0f Gpairs/s of 256-bit rows), %.1f clk per MMA (ideal %d), %.0f MHz  [%s]\n",
-         n, mode ? "TMEM" : "smem", N, best, mac * 1e-12, mac / 256 * 1e-9, (double)clk / (8.0 * n), N / 2, (double)clk / (best * 1e3),
+  printf("rate (%5d x 8 MMAs, commit every %d): A from %s, N = %3d: %.3f ms, %.1f TMAC/s (%.0f Gpairs/s of 256-bit rows), %.1f clk per MMA (ideal %d), %.0f MHz  [%s]\n",
+         n, commit_every, mode ? "TMEM" : "smem", N, best, mac * 1e-12, mac / 256 * 1e-9, (double)clk / (8.0 * n), N / 2, (double)clk / (best * 1e3),
          cudaGetErrorString(e));
+}
+
+// Issue-cost variants (A in shared memory, two accumulators): FORM 0 = lane 0 alone, 8 MMAs unrolled, descriptors as
+// base + k * step; FORM 1 = the whole warp runs the loop and elect.sync picks the issuing lane inside the asm.
+__device__ __forceinline__ void mma_plain(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void mma_elect(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p, e;\n\telect.sync _|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+               ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
+}
+template <int FORM, int N>
+__global__ void __launch_bounds__(128, 1) rate2(int n, long long* clk) {
+  extern __shared__ __align__(128) uint8_t sm[];
+  uint8_t* s_a = sm;
+  uint8_t* s_b = sm + 32768;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 32768 + 65536);
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bar + 2);
+  const int t = threadIdx.x, warp = t >> 5;
+  for (int i = t; i < (32768 + 65536) / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0x01010101u;
+  if (t == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *s_tmem;
+  constexpr uint32_t idesc = (2u << 4) | (1u << 7) | (((uint32_t)N >> 3) << 17) | ((128u >> 4) << 24);
+  const uint64_t da = (uint64_t)((smem_u32(s_a) & 0x3ffffu) >> 4) | ((uint64_t)(2048 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
+  const uint64_t db = (uint64_t)((smem_u32(s_b) & 0x3ffffu) >> 4) | ((uint64_t)(16 * N >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
+  constexpr uint32_t kb = 2 * 16 * N >> 4;
+  if (FORM == 0 ? t == 0 : warp == 0) {
+    const long long c0 = clock64();
+    for (int i = 0; i < n; i += 2) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (FORM == 0) mma_plain(tmem + h * N, da + (uint64_t)(k * 256), db + (uint64_t)(k * kb), idesc, (i > 0 || k > 0) ? 1u : 0u);
+          else mma_elect(tmem + h * N, da + (uint64_t)(k * 256), db + (uint64_t)(k * kb), idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+    }
+    if (t == 0) {
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+      uint32_t done = 0;
+      while (!done)
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(smem_u32(bar)) : "memory");
+      if (blockIdx.x == 0) *clk = clock64() - c0;
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+}
+template <int FORM, int N>
+static void run_rate2() {
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  const int smem = 32768 + 65536 + 64, n = 8192;
+  cudaFuncSetAttribute(rate2<FORM, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  long long* d_clk; cudaMalloc(&d_clk, 8);
+  for (int r = 0; r < 10; ++r) rate2<FORM, N><<<sms, 128, smem>>>(n, d_clk);
+  const cudaError_t e = cudaDeviceSynchronize();
+  long long clk = 0;
+  cudaMemcpy(&clk, d_clk, 8, cudaMemcpyDeviceToHost);
+  printf("issue form %d (%s), N = %3d: %.1f clk per MMA (tensor time %d)  [%s]\n", FORM, FORM ? "whole warp + elect.sync" : "lane 0, unrolled x16",
+         N, (double)clk / (8.0 * n), N / 2, cudaGetErrorString(e));
+  cudaFree(d_clk);
 }
 
 int main() {
@@ -183,7 +262,9 @@ int main() {
       if (D[m * 64 + n] != want) { if (bad < 6) printf("  (m=%d, n=%d) got %d want %d\n", m, n, D[m * 64 + n], want); ++bad; }
     }
   printf("A-from-TMEM kind::i8: mismatches %ld of %d\n", bad, 128 * 64);
-  for (int N : {256, 240, 224, 192, 128, 64})
+  for (int N : {256, 192})
     for (int mode = 0; mode < 2; ++mode) run_rate(mode, N);
+  for (int ce : {8, 1}) run_rate(0, 256, 8192, ce);
+  run_rate2<0, 64>(); run_rate2<1, 64>(); run_rate2<0, 256>(); run_rate2<1, 256>();
   return 0;
 }
