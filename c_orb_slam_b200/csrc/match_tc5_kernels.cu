@@ -13,7 +13,8 @@
 // Roles (one warp each unless noted):
 //   warps 9..12  expanders: two database rows per thread and tile of 256 rows -> 32 STS.128 into the K-major,
 //                unswizzled core-matrix layout (8 rows x 16 bytes contiguous; LBO = 4096, SBO = 128)
-//   warp 8       MMA issuer (lane 0): per tile 2 x 8 tcgen05.mma M128 N256 K32 into two TMEM accumulators
+//   warp 8       MMA issuer (the warp stays converged, one elected lane issues): per tile 2 x 8 tcgen05.mma
+//                M128 N256 K32 into two TMEM accumulators, every descriptor in its own uniform register pair
 //   warps 0..7   epilogue (set i = warps 4i..4i+3 drains accumulator i): the 256-column row of the thread's
 //                query comes to registers in four packed tcgen05.ld (three in flight), the accumulator is
 //                handed back as soon as the last one lands, and the rest of the scan (max filter against the
