@@ -160,7 +160,8 @@ __global__ void __launch_bounds__(kBtThreads, 1) blur_tc_kernel(const __grid_con
                 kAccFull = kTEmpty + 2, kAccEmpty = kAccFull + 2, kNumBars = kAccEmpty + 2;
   static_assert(kNumBars <= 24, "barrier slots");
   auto bar = [&](int i) { return bar0 + 8u * i; };
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int t = threadIdx.x, lane = t & 31;
+  const int warp = __shfl_sync(0xffffffffu, t >> 5, 0);  // provably warp-uniform: the role branches are uniform branches
 
   if (t == 0) {
     for (int i = 0; i < kAccEmpty; ++i) mbar_init(bar(i), 1);

@@ -304,7 +304,8 @@ struct FastLayout { int tp4, tile_bytes, score_bytes, cand_cap, per_warp; unsign
 __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   extern __shared__ __align__(16) uint8_t smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // provably warp-uniform: per-cell values stay in uniform registers
   const int cell = blockIdx.x * (blockDim.x >> 5) + warp;
   if (cell >= p.cells_per_frame) return;
   const int f = blockIdx.y;
@@ -616,7 +617,7 @@ __device__ __forceinline__ void bitonic_step(uint64_t* a, int i, int j, int k) {
 // of n / nwarps elements: sub-stages whose partner distance stays inside a chunk only need a
 // __syncwarp, so only the few widest sub-stages pay for a block barrier.
 __device__ __forceinline__ void block_bitonic_sort(uint64_t* a, int n /*pow2*/) {
-  const int nwarps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int chunk = n / nwarps;  // nwarps is a power of two
   if (chunk < 2) {               // tiny input: plain block-wide network
     for (int k = 2; k <= n; k <<= 1)
@@ -973,7 +974,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   }
 
   // ---- best response per node, list order (:741-760) ----------------------------------------
-  const int warp = t >> 5, lane = t & 31;
+  const int warp = __shfl_sync(0xffffffffu, t >> 5, 0), lane = t & 31;  // provably warp-uniform: node fields and loop bounds too
   for (int i = warp; i < n; i += T / 32) {
     const QtNode nd = cur[i];
     // max response, earliest arrival among equals: maximise (resp << 32) | ~arrival
@@ -1260,7 +1261,8 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     if (blockIdx.x == 0) n_out[f] = min(run, capacity);
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // provably warp-uniform
   // IC_Angle with lane = patch row v: the row's 31 pixels as 8 aligned words, columns |u| <= umax[|v|] kept by a
   // byte mask, m10 / row sum by two IDP.4A per word (weights u = 4k+j-15 as signed bytes / all ones)
   const int v_row = lane - kHalfPatch;
