@@ -1,7 +1,16 @@
-// Probe for tcgen05.mma kind::i8 with the A operand in tensor memory: A[128][32] (s8) is stored by tcgen05.st
-// (thread = TMEM lane = row, register j = bytes K = 4j .. 4j+3), B[64][32] (u8) sits in shared memory as unswizzled
-// K-major core matrices; D = A * B^T is compared with the host.
-// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -o tmem_a_probe tmem_a_probe.cu
+// Probes around tcgen05.mma kind::i8 issue (B200):
+//  1. A operand in tensor memory: A[128][32] (s8) is stored by tcgen05.st (thread = TMEM lane = row, register j = bytes
+//     K = 4j .. 4j+3), B[64][32] (u8) sits in shared memory as unswizzled K-major core matrices; D = A * B^T is compared
+//     with the host (bit-exact).
+//  2. rate(): one lane per SM issues M128 x N x K32 MMAs back to back, A from shared memory or from tensor memory, with
+//     an optional tcgen05.commit every c MMAs: both operand sources run at N/2 clk per MMA (N >= 192), a commit after
+//     every MMA costs nothing, and any extra instructions in the issuing loop show up directly (the loop, not the tensor
+//     pipe, sets the rate below ~75-135 clk per MMA).
+//  3. rate2<FORM>(): 16 MMAs unrolled with descriptors as base + constant, issued by lane 0 alone (FORM 0) or by the
+//     converged warp with elect.sync inside the asm (FORM 1): 48 clk per MMA at N = 64, 128 at N = 256 -- every
+//     descriptor sits in its own uniform register pair.  A loop that rewrites ONE pair before each MMA (what a
+//     run-time selected descriptor compiles to) measured N/2 + 40 clk per MMA.
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -o tmem_a_probe tmem_a_probe.cu
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
