@@ -4,6 +4,7 @@ The brute-force kernel's tensor pipe ran at 0.89 of its peak while the MMA issue
 with the next descriptor before every tcgen05.mma, and at 0.98 once every descriptor sat in its own pair (DESIGN.md
 section 8, tools/ubench/tmem_a_probe.cu).  That property is a matter of what ptxas emits, so it is pinned here: the
 eight MMAs of a K loop must be eight consecutive UTCIMMA instructions."""
+import functools
 import os
 import re
 import shutil
@@ -15,13 +16,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "c_orb_slam_b200", "liborb_gpu.so")
 
 
-def _sass(kernel_substr):
+@functools.lru_cache(maxsize=None)
+def _dump():
     exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
     if not os.path.exists(exe):
         pytest.skip("cuobjdump not found")
     if not os.path.exists(LIB):
         pytest.skip("library not built")
-    txt = subprocess.run([exe, "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    return subprocess.run([exe, "-sass", LIB], capture_output=True, text=True, check=True).stdout
+
+
+def _sass(kernel_substr):
+    txt = _dump()
     for blk in re.split(r"\n\s*Function : ", txt)[1:]:
         name, body = blk.split("\n", 1)
         if kernel_substr in name:
