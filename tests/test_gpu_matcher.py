@@ -58,6 +58,20 @@ def test_ratio_test_device_all_pairs(gpu, nnratio, th):
     assert np.array_equal(acc, want) and want.sum() > 1000
 
 
+@pytest.mark.parametrize("nq,ndb", [(1, 255), (255, 257), (256, 148 * 256 - 1), (257, 148 * 256 + 1), (300, 148 * 768),
+                                    (513, 49 * 25 * 256), (513, 49 * 25 * 256 + 1), (100, 300001)])
+def test_bruteforce_tcgen05_ragged_slices(gpu, oracle, nq, ndb):
+    """The tcgen05 kernel's MMA issuer walks the tiles of a slice two at a time (one per B stage): slices of one, an odd
+    and an even number of 256-row tiles, last tiles of a single row, query blocks with one live query."""
+    q, db = synth.make_match_set(nq, ndb, seed=nq + ndb)
+    gpu.lib().orb_gpu_set_bruteforce_variant(3, 2)
+    m = gpu.ORBmatcher(0.9)
+    for rep in range(2):  # the second call reuses the slice tickets the first one reset
+        idx, best, second = m.match_bruteforce(q, db)
+        oi, ob, os_ = oracle.match_bruteforce(q, db, threads=8)
+        assert np.array_equal(best, ob) and np.array_equal(second, os_) and np.array_equal(idx, oi)
+
+
 @pytest.mark.parametrize("variant", [(2, 2), (3, 2)])
 def test_bruteforce_extreme_descriptors(gpu, oracle, variant):
     """All-zero / all-one descriptors (S = +-256, the ends of the accumulator range), ragged sizes, planted ties."""
