@@ -534,7 +534,8 @@ struct QtNode { int start, end; uint32_t prefix; int depth_new; int seq; };  // 
 
 __device__ __forceinline__ int block_exclusive_scan(int* a, int n, int* s_warp /*>=33 ints*/) {
   // in-place exclusive scan of a[0..n) by the whole block; returns the total
-  const int T = blockDim.x, t = threadIdx.x;
+  constexpr int T = kQtThreads;  // compile-time block size: the chunk divisions below become shifts
+  const int t = threadIdx.x;
   const int chunk = (n + T - 1) / T;
   const int lo = min(t * chunk, n), hi = min(lo + chunk, n);
   int sum = 0;
@@ -568,7 +569,8 @@ __device__ __forceinline__ int block_exclusive_scan(int* a, int n, int* s_warp /
 
 // the same for two arrays at once (one set of barriers): returns total of a, *total_b that of b
 __device__ __forceinline__ int block_exclusive_scan2(int* a, int* b, int n, int* s_warp /*>=66 ints*/, int* total_b) {
-  const int T = blockDim.x, t = threadIdx.x;
+  constexpr int T = kQtThreads;  // compile-time block size: the chunk divisions below become shifts
+  const int t = threadIdx.x;
   const int chunk = (n + T - 1) / T;
   const int lo = min(t * chunk, n), hi = min(lo + chunk, n);
   int sa = 0, sb = 0;
@@ -617,12 +619,13 @@ __device__ __forceinline__ void bitonic_step(uint64_t* a, int i, int j, int k) {
 // of n / nwarps elements: sub-stages whose partner distance stays inside a chunk only need a
 // __syncwarp, so only the few widest sub-stages pay for a block barrier.
 __device__ __forceinline__ void block_bitonic_sort(uint64_t* a, int n /*pow2*/) {
-  const int nwarps = blockDim.x >> 5, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  constexpr int nwarps = kQtThreads >> 5;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int chunk = n / nwarps;  // nwarps is a power of two
   if (chunk < 2) {               // tiny input: plain block-wide network
     for (int k = 2; k <= n; k <<= 1)
       for (int j = k >> 1; j > 0; j >>= 1) {
-        for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x)
+        for (int t = threadIdx.x; t < (n >> 1); t += kQtThreads)
           bitonic_step(a, ((t & ~(j - 1)) << 1) | (t & (j - 1)), j, k);
         __syncthreads();
       }
@@ -632,7 +635,7 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* a, int n /*pow2*/) 
   for (int k = 2; k <= n; k <<= 1) {
     int j = k >> 1;
     for (; 2 * j > chunk; j >>= 1) {  // partners in different chunks
-      for (int t = threadIdx.x; t < (n >> 1); t += blockDim.x)
+      for (int t = threadIdx.x; t < (n >> 1); t += kQtThreads)
         bitonic_step(a, ((t & ~(j - 1)) << 1) | (t & (j - 1)), j, k);
       __syncthreads();
     }
@@ -744,10 +747,11 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
           if (s_cell[mid] <= arr) lo = mid; else hi = mid - 1;
         }
         const int c = lo;
-        const int ci = c / g.ncols, cj = c - ci * g.ncols;
+        // the cell's origin comes from the FAST cell table (ini = kBorder + index * cell size): no division by ncols
+        const unsigned cxy = __ldg(&sc.cell_tab[g.cell_base + c].x);
         const uint32_t e = cell_kp[(size_t)c * p.cell_cap + (arr - s_cell[c])];
         const int resp = (e >> 16) & 0xff;
-        const int x = (int)(e & 0xff) + cj * g.wcell, y = (int)((e >> 8) & 0xff) + ci * g.hcell;
+        const int x = (int)(e & 0xff) + (int)(cxy & 0xffffu) - kBorder, y = (int)((e >> 8) & 0xff) + (int)(cxy >> 16) - kBorder;
         // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
         int root = (int)__fdiv_rn((float)x, g.hx);
         root = min(root, g.n_ini - 1);
