@@ -672,7 +672,30 @@ __host__ __device__ __forceinline__ int qt_ncap(int quota, int n_ini) {
 }
 __device__ __forceinline__ int pow2ceil_dev(int v) { return v <= 1 ? 1 : 1 << (32 - __clz(v - 1)); }
 
-__global__ void __launch_bounds__(kQtThreads, 3)
+// Shared-memory layout of quadtree_kernel (bytes from the start of dynamic shared memory), the same on both sides:
+//   A  [kQtSmemKeys] u64 sorted keys.  Until the keys are written (the last step of the sort) A holds the packed bucket
+//      counters (s_bin) and, when they fit behind them, the per-cell arrival bases (s_cell): both are dead by then.
+//   B  [kQtSmemKeys] u32 bucketed entries (s_bkt) during the sort; afterwards the node lists, the rank-ordered scratch
+//      and the child boundaries (everything the list simulation needs) overlay it -- B is as large as the larger user.
+//   C  72 ints of warp partials (+ s_cell when a level has too many cells for A).
+// 75 KB of separate arrays (3 blocks per SM) became 51 KB (4 per SM) on the TUM configuration.
+struct QtLayout { int off_b, off_warp, off_cell, total; };
+__host__ __device__ __forceinline__ QtLayout qt_layout(int ncap, int sort_cap, int ncells) {
+  QtLayout L;
+  const int a_bytes = kQtSmemKeys * 8, bin_bytes = (kQtBins / 2 + 4) * 4, cell_bytes = (ncells + 1) * 4;
+  const int overlay = 8 * sort_cap + (int)sizeof(int) * 19 * ncap;  // s_sort, 2 lists of 5 ints, nch/cb/sv, bnd[3], cbnd[3]
+  int b_bytes = kQtSmemKeys * 4 > overlay ? kQtSmemKeys * 4 : overlay;
+  b_bytes = (b_bytes + 15) & ~15;
+  L.off_b = a_bytes;
+  L.off_warp = a_bytes + b_bytes;
+  const bool cell_in_a = bin_bytes + cell_bytes <= a_bytes;
+  L.off_cell = cell_in_a ? bin_bytes : L.off_warp + 72 * 4;
+  L.total = L.off_warp + 72 * 4 + (cell_in_a ? 0 : cell_bytes) + 16;
+  return L;
+}
+static_assert(sizeof(int) * 5 == 20, "QtNode is five ints");
+
+__global__ void __launch_bounds__(kQtThreads, 4)
 quadtree_kernel(Plan p, Scratch sc, int nframes) {
   extern __shared__ __align__(16) uint8_t smem[];
   // one block per (level, frame); the big levels are scheduled first so the small ones fill the tail
@@ -683,22 +706,21 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   const int ncells = g.nrows * g.ncols;
   const int N = g.quota;
 
-  // shared memory carve-up
-  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);
-  uint32_t* s_bkt = reinterpret_cast<uint32_t*>(s_keys + kQtSmemKeys);  // [kQtSmemKeys] bucketed (rest-of-code, arrival)
-  uint32_t* s_bin = s_bkt + kQtSmemKeys;                         // [kQtBins / 2 + 4] packed u16 bucket counters / bases
-  uint64_t* s_sort = reinterpret_cast<uint64_t*>(s_bin + kQtBins / 2 + 4);  // [sort_cap]
-  QtNode* list_a = reinterpret_cast<QtNode*>(s_sort + sort_cap); // [ncap]
-  QtNode* list_b = list_a + ncap;                                // [ncap]
-  int* s_nch = reinterpret_cast<int*>(list_b + ncap);            // [ncap] children per split node
-  int* s_cb = s_nch + ncap;                                      // [ncap] creation base
-  int* s_sv = s_cb + ncap;                                       // [ncap] survivor flags/ranks
-  int* s_bnd = s_sv + ncap;                                      // [3*ncap] rank-ordered scratch
-  int* s_cell = s_bnd + 3 * ncap;                                // [ncells+1]
-  int* s_warp = s_cell + ncells + 1;                             // [72]
-  // [3*ncap] child boundaries found while counting: in the bucket array, which is dead once the keys are sorted (a
-  // bigger block would cost the third resident block per SM); very large quotas get their own space behind s_warp
-  int* s_cbnd = 3 * ncap <= kQtSmemKeys ? reinterpret_cast<int*>(s_bkt) : s_warp + 72;
+  // shared memory carve-up (qt_layout)
+  const QtLayout lay = qt_layout(ncap, sort_cap, ncells);
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem);                    // [kQtSmemKeys]
+  uint32_t* s_bin = reinterpret_cast<uint32_t*>(smem);                     // [kQtBins / 2 + 4] packed u16 bucket counters / bases, in A until the keys are written
+  int* s_cell = reinterpret_cast<int*>(smem + lay.off_cell);              // [ncells+1], in A behind s_bin when it fits
+  uint32_t* s_bkt = reinterpret_cast<uint32_t*>(smem + lay.off_b);         // [kQtSmemKeys] bucketed (rest-of-code, arrival)
+  uint64_t* s_sort = reinterpret_cast<uint64_t*>(smem + lay.off_b);        // [sort_cap]   -- from here on: after the sort
+  QtNode* list_a = reinterpret_cast<QtNode*>(s_sort + sort_cap);          // [ncap]
+  QtNode* list_b = list_a + ncap;                                          // [ncap]
+  int* s_nch = reinterpret_cast<int*>(list_b + ncap);                      // [ncap] children per split node
+  int* s_cb = s_nch + ncap;                                                // [ncap] creation base
+  int* s_sv = s_cb + ncap;                                                 // [ncap] survivor flags/ranks
+  int* s_bnd = s_sv + ncap;                                                // [3*ncap] rank-ordered scratch
+  int* s_cbnd = s_bnd + 3 * ncap;                                          // [3*ncap] child boundaries found while counting
+  int* s_warp = reinterpret_cast<int*>(smem + lay.off_warp);              // [72]
   __shared__ int s_misc[8];
 
   const uint32_t* cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
@@ -836,9 +858,16 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         const uint32_t mine = ((my_code[q] & rem_mask) << 12) | (uint32_t)arrival;
         int rank = 0;
         for (int k = bs; k < be; ++k) rank += s_bkt[k] < mine;
-        // low word: arrival | response << 24 (codes are distinct, so the low word never decides the order)
-        keys[bs + rank] = ((uint64_t)my_code[q] << 32) | (uint32_t)arrival | (my_rank[q] & 0xff000000u);
+        my_rank[q] = (my_rank[q] & 0xff000000u) | (uint32_t)(bs + rank);  // final position (< kQtSmemKeys)
       }
+    }
+    __syncthreads();  // the keys overwrite s_bin (and s_cell): every read of them is behind this barrier
+#pragma unroll
+    for (int q = 0; q < kQtKpt; ++q) {
+      const int arrival = t + q * T;
+      // low word: arrival | response << 24 (codes are distinct, so the low word never decides the order)
+      if (arrival < C)
+        keys[my_rank[q] & 0xffffu] = ((uint64_t)my_code[q] << 32) | (uint32_t)arrival | (my_rank[q] & 0xff000000u);
     }
     __syncthreads();
   } else {
@@ -1004,8 +1033,7 @@ size_t quadtree_smem_bytes(const Plan& p, int level) {
   const LevelGeom& g = p.lv[level];
   const int ncap = qt_ncap(g.quota, g.n_ini);
   const int ncells = g.nrows * g.ncols;
-  return (size_t)kQtSmemKeys * 12 + (size_t)(kQtBins / 2 + 4) * 4 + (size_t)pow2ceil(ncap) * 8 + (size_t)ncap * sizeof(QtNode) * 2 +
-         (size_t)ncap * 4 * 6 + (size_t)(ncells + 1 + 72) * 4 + 64 + (3 * ncap <= kQtSmemKeys ? 0 : (size_t)ncap * 12);
+  return (size_t)qt_layout(ncap, pow2ceil(ncap), ncells).total;
 }
 
 int launch_quadtree(const Plan& p, const Scratch& sc, int nframes, cudaStream_t s) {
