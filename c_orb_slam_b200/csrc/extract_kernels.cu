@@ -723,10 +723,10 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   int* s_warp = reinterpret_cast<int*>(smem + lay.off_warp);              // [72]
   __shared__ int s_misc[8];
 
-  const uint32_t* cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
-  const uint32_t* cell_kp = sc.cell_kp + ((size_t)f * p.cells_per_frame + g.cell_base) * p.cell_cap;
-  uint32_t* pay = sc.pay + (size_t)f * p.keys_per_frame + g.key_base;
-  uint32_t* sel = sc.sel + (size_t)f * p.slots_per_frame + g.slot_base;
+  const uint32_t* __restrict__ cell_cnt = sc.cell_cnt + (size_t)f * p.cells_per_frame + g.cell_base;
+  const uint32_t* __restrict__ cell_kp = sc.cell_kp + ((size_t)f * p.cells_per_frame + g.cell_base) * p.cell_cap;
+  uint32_t* __restrict__ pay = sc.pay + (size_t)f * p.keys_per_frame + g.key_base;
+  uint32_t* __restrict__ sel = sc.sel + (size_t)f * p.slots_per_frame + g.slot_base;
 
   // ---- gather candidates in arrival order (cell row-major, then FAST row-major) -------------
   for (int c = t; c < ncells; c += T) s_cell[c] = (int)cell_cnt[c];
@@ -771,7 +771,7 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
         const int c = lo;
         // the cell's origin comes from the FAST cell table (ini = kBorder + index * cell size): no division by ncols
         const unsigned cxy = __ldg(&sc.cell_tab[g.cell_base + c].x);
-        const uint32_t e = cell_kp[(size_t)c * p.cell_cap + (arr - s_cell[c])];
+        const uint32_t e = __ldg(&cell_kp[(size_t)c * p.cell_cap + (arr - s_cell[c])]);  // written by the FAST kernel: read-only here
         const int resp = (e >> 16) & 0xff;
         const int x = (int)(e & 0xff) + (int)(cxy & 0xffffu) - kBorder, y = (int)((e >> 8) & 0xff) + (int)(cxy >> 16) - kBorder;
         // root: vpIniNodes[kp.pt.x/hX] (:569), then 12 quadrant digits (DivideNode :481-525)
@@ -1022,8 +1022,12 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
       const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
       best = v > best ? v : best;
     }
-    if (lane == 0) sel[i] = pay[~(uint32_t)best];
+    if (lane == 0) s_sv[i] = (int)(~(uint32_t)best);  // arrival index of the node's keypoint
   }
+  // the payload gather in a pass of its own: one global load per node, all in flight at once (inside the loop above
+  // each warp stalled on its load before it could store, ~27 dependent L2 round trips per warp)
+  __syncthreads();
+  for (int i = t; i < n; i += T) sel[i] = pay[s_sv[i]];
   if (t == 0) sc.sel_cnt[f * p.nlevels + level] = n;
 }
 
