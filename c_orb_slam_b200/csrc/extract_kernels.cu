@@ -1007,22 +1007,29 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   }
 
   // ---- best response per node, list order (:741-760) ----------------------------------------
-  const int warp = __shfl_sync(0xffffffffu, t >> 5, 0), lane = t & 31;  // provably warp-uniform: node fields and loop bounds too
-  for (int i = warp; i < n; i += T / 32) {
-    const QtNode nd = cur[i];
-    // max response, earliest arrival among equals: maximise (resp << 32) | ~arrival
-    unsigned long long best = 0;
-    for (int k = nd.start + lane; k < nd.end; k += 32) {
-      const uint32_t low = (uint32_t)keys[k], arrival = low & 0xffffffu;
-      const unsigned long long cand = ((unsigned long long)(low >> 24) << 32) | (uint32_t)(~arrival);
-      best = cand > best ? cand : best;
-    }
+  // Eight lanes per node: the final nodes hold ~C / N candidates each (18 on a TUM level 0), so a whole warp per node
+  // left most lanes idle and paid five 64-bit shuffle steps per node; four nodes now share a warp's instructions.
+  {
+    const int grp = t >> 3, l8 = t & 7;
+    for (int base = 0; base < n; base += T / 8) {  // uniform trip count: the shuffles below are executed by every lane
+      const int i = base + grp;
+      // max response, earliest arrival among equals: maximise (resp << 32) | ~arrival
+      unsigned long long best = 0;
+      if (i < n) {
+        const QtNode nd = cur[i];
+        for (int k = nd.start + l8; k < nd.end; k += 8) {
+          const uint32_t low = (uint32_t)keys[k], arrival = low & 0xffffffu;
+          const unsigned long long cand = ((unsigned long long)(low >> 24) << 32) | (uint32_t)(~arrival);
+          best = cand > best ? cand : best;
+        }
+      }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
-      best = v > best ? v : best;
+      for (int o = 4; o > 0; o >>= 1) {
+        const unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
+        best = v > best ? v : best;
+      }
+      if (i < n && l8 == 0) s_sv[i] = (int)(~(uint32_t)best);  // arrival index of the node's keypoint
     }
-    if (lane == 0) s_sv[i] = (int)(~(uint32_t)best);  // arrival index of the node's keypoint
   }
   // the payload gather in a pass of its own: one global load per node, all in flight at once (inside the loop above
   // each warp stalled on its load before it could store, ~27 dependent L2 round trips per warp)
