@@ -752,8 +752,15 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
   while ((g.n_ini << (2 * (bdepth + 1))) <= kQtBins && bdepth + 1 <= kCodeDepth) ++bdepth;
   const int bshift = 24 - 2 * bdepth;
   const int nbins = g.n_ini << (2 * bdepth);
+  // shared-memory path: the owner cell of every arrival index, written cell by cell into the bucket array (idle until
+  // the scatter below) -- one load per candidate instead of a 9-step binary search over the cell bases
+  uint16_t* s_own = reinterpret_cast<uint16_t*>(s_bkt);
   if (in_smem) {
     for (int k = t; k < kQtBins / 2 + 1; k += T) s_bin[k] = 0;
+    for (int c = t; c < ncells; c += T) {
+      const int ke = s_cell[c + 1];
+      for (int k = s_cell[c]; k < ke; ++k) s_own[k] = (uint16_t)c;
+    }
     __syncthreads();
   }
   uint32_t my_code[kQtKpt], my_rank[kQtKpt];
@@ -763,12 +770,17 @@ quadtree_kernel(Plan p, Scratch sc, int nframes) {
     my_code[q] = 0; my_rank[q] = 0;
     if (in_smem ? arrival < C : q == 0) {
       for (int arr = arrival; arr < C; arr += in_smem ? C : T) {  // shared-memory path: exactly one candidate per slot
-        int lo = 0, hi = ncells - 1;
-        while (lo < hi) {
-          const int mid = (lo + hi + 1) >> 1;
-          if (s_cell[mid] <= arr) lo = mid; else hi = mid - 1;
+        int c;
+        if (in_smem) {
+          c = s_own[arr];
+        } else {
+          int lo = 0, hi = ncells - 1;
+          while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_cell[mid] <= arr) lo = mid; else hi = mid - 1;
+          }
+          c = lo;
         }
-        const int c = lo;
         // the cell's origin comes from the FAST cell table (ini = kBorder + index * cell size): no division by ncols
         const unsigned cxy = __ldg(&sc.cell_tab[g.cell_base + c].x);
         const uint32_t e = __ldg(&cell_kp[(size_t)c * p.cell_cap + (arr - s_cell[c])]);  // written by the FAST kernel: read-only here
