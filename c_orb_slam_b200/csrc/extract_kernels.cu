@@ -8,11 +8,15 @@
 //   orient_desc_kernel    IC_Angle :77-104, computeOrbDescriptor :106-147, output fix-ups
 // Integer stages are bit-exact with the CPU oracle; float stages use explicit _rn intrinsics
 // (the TU is compiled with -fmad=false) so every operation rounds as in the oracle.
+#include <cuda.h>
+
 #include <cfloat>
 
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
+#include "umma.cuh"
 
 namespace orbgpu {
 
@@ -103,19 +107,45 @@ resize_level_kernel(LevelGeom src, LevelGeom dst) {
 // 4 IDP.2A) is kept for the next row, and a destination row is emitted as soon as its lower source row is done --
 // for 1 < scale <= 2 consecutive destination rows start at consecutive or next-but-one source rows, so every source
 // row of the band is needed and each is loaded and filtered once (1.2 per destination row instead of 2).
+//
+// kStaged: the band's source rows (at most kRzSrcRows of them, whole pitch) come to shared memory by TMA first -- one
+// elected thread issues a 256 x kRzSrcRows byte box per 256-byte column chunk, everybody waits on the mbarrier once --
+// and the walk below reads shared memory.  The direct form waits for global loads once per batch of four source rows
+// (30 % of its stall samples on the first use of a loaded word); staged, a block pays the memory latency once and the
+// other blocks of the SM compute meanwhile.
 constexpr int kRzSrcRows = 2 * kRzRows + 4;
+constexpr int kRzChunk = 256;                              // bytes per column chunk = TMA box width
+constexpr int kRzMaxChunks = 5;                            // source pitch <= 1280 bytes
+struct RzStage { CUtensorMap map; int nchunks, src_h, box_h; };  // source level as [frames * h][pitch] bytes, box 256 x box_h
+// box_h = the most source rows a band of kRzRows destination rows can need at this scale (<= kRzSrcRows)
+
+template <bool kStaged>
 __global__ void __launch_bounds__(256)
-resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows per block: 4, 8 or 16*/) {
+resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows per block: 4, 8 or 16*/,
+                     const __grid_constant__ RzStage S) {
+  extern __shared__ __align__(128) uint8_t rz_band[];  // kStaged: [nchunks][box_h][256]
   __shared__ uint2 s_src[kRzSrcRows];  // per source row of the band: word offset, destination rows to emit (e1 | e2 << 8)
   __shared__ uint2 s_b[kRzRows];       // vertical weights << 16 of a destination row
   __shared__ int s_ns;
+  __shared__ __align__(8) uint64_t s_bar;
   const int f = blockIdx.y;
   const int dy0 = blockIdx.x * rows;
   const int rstep = src.pitch >> 2;
   const int nrows = min(rows, dst.h - dy0);
   const int s_begin = dst.yofs[dy0];
-  if (threadIdx.x < kRzSrcRows)
-    s_src[threadIdx.x] = make_uint2((unsigned)(min(s_begin + (int)threadIdx.x, src.h - 1) * rstep), 0xffffu);
+  if (kStaged && threadIdx.x == 0) {
+    const uint32_t bar = smem_u32(&s_bar);
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(bar, (uint32_t)(S.nchunks * S.box_h * kRzChunk));
+    for (int k = 0; k < S.nchunks; ++k)  // rows past the frame (or the tensor) land too and are never read
+      tma_load_2d(smem_u32(rz_band + k * S.box_h * kRzChunk), &S.map, kRzChunk * k, f * S.src_h + s_begin, bar);
+  }
+  if (threadIdx.x < kRzSrcRows) {
+    const int row = min(s_begin + (int)threadIdx.x, src.h - 1);
+    // staged: row of the band (rows past the staged box are table padding that is loaded but never emitted: clamp)
+    s_src[threadIdx.x] = make_uint2(kStaged ? (unsigned)(min(row - s_begin, S.box_h - 1) * (kRzChunk / 4)) : (unsigned)(row * rstep), 0xffffu);
+  }
   __syncthreads();
   if (threadIdx.x < nrows) {
     const int dy = dy0 + (int)threadIdx.x;
@@ -131,8 +161,14 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows p
   const int ns = s_ns;
   const int nt = (dst.w + 3) >> 2;
   const int last_word = rstep - 1;
-  const unsigned* sbase = reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
+  const unsigned* sbase = kStaged ? reinterpret_cast<const unsigned*>(rz_band)
+                                  : reinterpret_cast<const unsigned*>(src.img + (size_t)f * src.frame_stride);
+  // word column wi of the source row lives at chunk wi >> 6, word wi & 63 of the staged band
+  const int chunk_words = kStaged ? S.box_h * (kRzChunk / 4) : 0;
+  auto col = [&](int wi) { return kStaged ? (wi >> 6) * chunk_words + (wi & 63) : wi; };
+  if (kStaged && ns > S.box_h) __trap();  // the host's bound on the band height (launch_resize_level) must hold
   uint8_t* dbase = dst.img + (size_t)f * dst.frame_stride + (size_t)dy0 * dst.pitch;
+  if (kStaged) mbar_wait(smem_u32(&s_bar), 0);
   for (int t = threadIdx.x; t < nt; t += blockDim.x) {
     int x[4];
     unsigned wt[4];
@@ -145,9 +181,9 @@ resize_level4_kernel(LevelGeom src, LevelGeom dst, int rows /*destination rows p
     const int wi0 = x[0] >> 2;
     const bool hi = x[2] - 4 * wi0 >= 4;
     // word columns of the two tap windows: (ca, ca + 1) for destination columns 0,1 and (cb, cb + 1) for 2,3
-    const unsigned* c0 = sbase + wi0;
-    const unsigned* c1 = sbase + min(wi0 + 1, last_word);
-    const unsigned* c2 = sbase + min(wi0 + 2, last_word);
+    const unsigned* c0 = sbase + col(wi0);
+    const unsigned* c1 = sbase + col(min(wi0 + 1, last_word));
+    const unsigned* c2 = sbase + col(min(wi0 + 2, last_word));
     const int o0 = x[0] - 4 * wi0, o1 = x[1] - 4 * wi0;
     const int o2 = x[2] - 4 * wi0 - (hi ? 4 : 0), o3 = x[3] - 4 * wi0 - (hi ? 4 : 0);
     const unsigned sel01 = (unsigned)o0 | ((unsigned)(o0 + 1) << 4) | ((unsigned)o1 << 8) | ((unsigned)(o1 + 1) << 12);
@@ -205,7 +241,28 @@ int launch_resize_level(const Plan& p, int level, int nframes, cudaStream_t s) {
   if (four) {
     const int nt = (d.w + 3) >> 2;
     grid.x = (d.h + rows4 - 1) / rows4;
-    resize_level4_kernel<<<grid, min(256, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d, rows4);
+    const LevelGeom& sl = p.lv[level - 1];
+    // TMA-staged source band: full bands only, 16-byte aligned rows, frames stacked without gaps, <= 5 column chunks
+    static const bool no_stage = [] { const char* e = getenv("ORB_GPU_RESIZE_DIRECT"); return e && atoi(e); }();
+    const int nchunks = (sl.pitch + kRzChunk - 1) / kRzChunk;
+    const bool staged = !no_stage && rows4 == kRzRows && tma_available() && nchunks <= kRzMaxChunks &&
+                        (reinterpret_cast<uintptr_t>(sl.img) & 15) == 0 && (sl.pitch & 15) == 0 &&
+                        (nframes == 1 || sl.frame_stride == (long long)sl.pitch * sl.h);
+    RzStage S;
+    memset(&S, 0, sizeof(S));
+    if (staged) {
+      // source rows of a band: sy(dy0 + 15) - sy(dy0) <= floor(15 * scale) + 1, plus the lower tap row, plus one spare
+      const int box_h = std::min(kRzSrcRows, (int)(15.0 * (double)sl.h / (double)d.h) + 4);
+      int rc = tensor_map_2d_u8(&S.map, sl.img, sl.pitch, (long long)nframes * sl.h, sl.pitch, kRzChunk, box_h, false);
+      if (rc) return rc;
+      S.nchunks = nchunks; S.src_h = sl.h; S.box_h = box_h;
+      const int smem = nchunks * box_h * kRzChunk;
+      if (smem > 48 * 1024)
+        ORB_CUDA_TRY(cudaFuncSetAttribute(resize_level4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      resize_level4_kernel<true><<<grid, min(256, (nt + 31) & ~31), smem, s>>>(sl, d, rows4, S);
+    } else {
+      resize_level4_kernel<false><<<grid, min(256, (nt + 31) & ~31), 0, s>>>(sl, d, rows4, S);
+    }
   } else {
     const int nt = (d.w + 1) >> 1;
     resize_level_kernel<<<grid, min(512, (nt + 31) & ~31), 0, s>>>(p.lv[level - 1], d);
