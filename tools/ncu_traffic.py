@@ -19,6 +19,7 @@ stage_of = {"resize_level": "pyramid", "repack_rows": "pyramid", "fast_cells": "
 byt, inst, us, seen = {}, {}, {}, {}
 for r in rows[2:]:
     name = r[col["Kernel Name"]]
+    name = name[5:] if name.startswith("void ") else name  # templated kernels are listed with their return type
     st = next((v for k, v in stage_of.items() if name.startswith(k)), None)
     if st is None:
         continue
