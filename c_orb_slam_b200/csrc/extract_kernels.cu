@@ -1353,12 +1353,28 @@ __device__ __forceinline__ int round_half_even(float v) {
 // One block = 32 consecutive output slots (level, rank in the level's selection) of one frame, one warp
 // per slot, 8 slots per warp (the pattern copy and the level prefix of a block are shared by 64 keypoints).  IC_Angle: lane = patch column u, the rows of the disc that contain it
 // are |v| <= umax[|u|] (the disc is symmetric), 31 coalesced byte loads, shuffle reduction.
+// kTma: the two windows of a keypoint come by TMA (one 64 x 37 byte box of the blurred level, one 48 x 31 byte box of
+// the level image; boxes start at the 16-byte boundary left of the window, which is what the wider pitches are for)
+// instead of 24 rounds of 4-byte cp.async per keypoint -- a sixth of the kernel's instructions.  A level image that TMA
+// cannot address (caller memory that is unaligned or has gaps between frames) keeps cp.async for its IC patch.
+constexpr int kOdTilePitch = 64, kOdTileBytes = ((kOdTilePitch * kOdRows + 127) / 128) * 128;   // 2432
+constexpr int kIcPitch = 48, kIcBytes = ((kIcPitch * kIcRows + 127) / 128) * 128;               // 1536
+struct OdStage {
+  CUtensorMap tile[kMaxLevels];  // blurred level l as [frames * h][bpitch], box 64 x 37
+  CUtensorMap ic[kMaxLevels];    // level image l as [frames * h][pitch], box 48 x 31
+  unsigned ic_mask;              // levels whose image TMA can address
+};
+
+template <bool kTma>
 __global__ void __launch_bounds__(kOdWarps * 32, 5)
 orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc,
-                   int capacity, int* __restrict__ n_out, int slots_per_warp) {
+                   int capacity, int* __restrict__ n_out, int slots_per_warp, const __grid_constant__ OdStage T) {
   __shared__ float4 s_pat[256];
-  __shared__ uint32_t s_tile[kOdWarps][kOdRows * kOdWords];
-  __shared__ uint32_t s_ic[kOdWarps][kIcRows * kIcWords];  // unblurred 31-row patch, 9 aligned words per row
+  __shared__ __align__(128) uint32_t s_tile[kOdWarps][kTma ? kOdTileBytes / 4 : kOdRows * kOdWords];
+  __shared__ __align__(128) uint32_t s_ic[kOdWarps][kTma ? kIcBytes / 4 : kIcRows * kIcWords];  // unblurred 31-row patch
+  __shared__ __align__(8) uint64_t s_bar[kOdWarps][2];
+  constexpr int kTileWords = kTma ? kOdTilePitch / 4 : kOdWords;  // words per staged row of the blurred window
+  constexpr int kIcRowWords = kTma ? kIcPitch / 4 : kIcWords;     // words per staged row of the IC patch
   __shared__ int s_cnt[kMaxLevels], s_before[kMaxLevels + 1], s_base[kMaxLevels];
   const int f = blockIdx.y;
   s_pat[threadIdx.x] = g_pattern[threadIdx.x];
@@ -1395,7 +1411,16 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
   const unsigned tile_dst = (unsigned)__cvta_generic_to_shared(my_tile + tile_r * kOdWords + tile_c);
   uint32_t* my_ic = s_ic[warp];
   const int ic_r = lane / kIcWords, ic_c = lane - ic_r * kIcWords;  // (row, word) inside a 3-row step, lanes 0..26
-  const unsigned ic_dst = (unsigned)__cvta_generic_to_shared(my_ic + ic_r * kIcWords + ic_c);
+  const unsigned ic_dst = (unsigned)__cvta_generic_to_shared(my_ic + ic_r * kIcRowWords + ic_c);
+  const uint32_t bar_ic = smem_u32(&s_bar[warp][0]), bar_tl = smem_u32(&s_bar[warp][1]);
+  if (kTma) {
+    if (lane == 0) {
+      mbar_init(bar_ic, 1); mbar_init(bar_tl, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+  }
+  uint32_t phase_tl = 0, phase_ic = 0;
 
   int level = 0;
   for (int it = 0; it < slots_per_warp; ++it) {
@@ -1420,17 +1445,27 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     // so they fly during the orientation pass); the 512 byte gathers then hit shared memory, not L1/L2.
     const uint8_t* img = g.img + (size_t)f * g.frame_stride;
     const int ic_xal = (cx - kHalfPatch) & ~3;
-    {  // unblurred 31 x 36-byte patch for IC_Angle: 27 lanes copy 3 rows x 9 words per step, own commit group
+    const bool ic_tma = kTma && ((T.ic_mask >> level) & 1u);
+    if (kTma && lane == 0) {
+      // rows f * h + y of the stacked levels; x rounded down to the 16-byte boundary (TMA's coordinate rule)
+      mbar_expect_tx(bar_tl, (uint32_t)(kOdTilePitch * kOdRows));
+      tma_load_2d(smem_u32(my_tile), &T.tile[level], (cx - kOdReach) & ~15, f * g.h + cy - kOdReach, bar_tl);
+      if (ic_tma) {
+        mbar_expect_tx(bar_ic, (uint32_t)(kIcPitch * kIcRows));
+        tma_load_2d(smem_u32(my_ic), &T.ic[level], (cx - kHalfPatch) & ~15, f * g.h + cy - kHalfPatch, bar_ic);
+      }
+    }
+    if (!ic_tma) {  // unblurred 31 x 36-byte patch for IC_Angle: 27 lanes copy 3 rows x 9 words per step, own commit group
       const uint8_t* src = img + (size_t)(cy - kHalfPatch + ic_r) * g.pitch + ic_xal + 4 * ic_c;
       unsigned dst = ic_dst;
       const int step = 3 * g.pitch;
 #pragma unroll
-      for (int r0 = 0; r0 < kIcRows; r0 += 3, src += step, dst += 3 * kIcWords * 4)
+      for (int r0 = 0; r0 < kIcRows; r0 += 3, src += step, dst += 3 * kIcRowWords * 4)
         if (lane < 27 && r0 + ic_r < kIcRows)
           asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
       asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
-    {
+    if (!kTma) {
       const uint8_t* bl = g.blur + (size_t)f * g.bframe_stride;
       const int xal = (cx - kOdReach) & ~3;
       // 30 lanes copy 3 rows x 10 words per step: one pointer bump per step
@@ -1446,10 +1481,14 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
 
     // IC_Angle: m10 = sum u*I, m01 = sum v*I over the 31-px disc (:77-104)
     int m10 = 0, m01 = 0;
-    asm volatile("cp.async.wait_group 1;\n" ::: "memory");  // the unblurred patch has landed (the blurred one may still fly)
+    // the unblurred patch has landed (the blurred one may still fly)
+    if (ic_tma) { mbar_wait(bar_ic, phase_ic); phase_ic ^= 1u; }
+    else if (kTma) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    else asm volatile("cp.async.wait_group 1;\n" ::: "memory");
     __syncwarp();
     if (lane < 31) {
-      const uint32_t* wp = my_ic + lane * kIcWords;
+      // TMA boxes start at the 16-byte boundary: the window begins ((cx - 15) & 15) bytes into the staged row
+      const uint32_t* wp = my_ic + lane * kIcRowWords + (ic_tma ? ((cx - kHalfPatch) & 15) >> 2 : 0);
       const unsigned sh = (unsigned)((cx - kHalfPatch) & 3) * 8;
       uint32_t w[9];
 #pragma unroll
@@ -1478,9 +1517,11 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
     double sd, cd;
     sincos_0_2pi((double)rad, &sd, &cd);
     const float a = (float)cd, b = (float)sd;
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    if (kTma) { mbar_wait(bar_tl, phase_tl); phase_tl ^= 1u; }
+    else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncwarp();
-    const uint8_t* tc = reinterpret_cast<const uint8_t*>(my_tile) + kOdReach * (4 * kOdWords) + kOdReach + ((cx - kOdReach) & 3);
+    const uint8_t* tc = reinterpret_cast<const uint8_t*>(my_tile) + kOdReach * (4 * kTileWords) + kOdReach +
+                        ((cx - kOdReach) & (kTma ? 15 : 3));
     int t0[8], t1[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {  // 16 gathers per lane from the staged window
@@ -1489,8 +1530,8 @@ orient_desc_kernel(Plan p, Scratch sc, OrbKeyPoint* __restrict__ kps, uint8_t* _
       const int q0 = round_half_even(__fsub_rn(__fmul_rn(t.x, a), __fmul_rn(t.y, b)));
       const int r1 = round_half_even(__fadd_rn(__fmul_rn(t.z, b), __fmul_rn(t.w, a)));
       const int q1 = round_half_even(__fsub_rn(__fmul_rn(t.z, a), __fmul_rn(t.w, b)));
-      t0[k] = tc[r0 * (4 * kOdWords) + q0];
-      t1[k] = tc[r1 * (4 * kOdWords) + q1];
+      t0[k] = tc[r0 * (4 * kTileWords) + q0];
+      t1[k] = tc[r1 * (4 * kTileWords) + q1];
     }
     __syncwarp();  // the window is rewritten by the next slot
     uint32_t mine = 0;
@@ -1522,7 +1563,24 @@ int launch_orient_desc(const Plan& p, const Scratch& sc, int nframes, OrbKeyPoin
   static const int env_spw = [] { const char* e = getenv("ORB_GPU_OD_SPW"); return e ? atoi(e) : 0; }();
   const int spw = env_spw > 0 ? env_spw : (long long)p.slots_per_frame * nframes >= 4 * kOdSlotsPerBlock * 148 ? kOdSlotsPerWarp : 1;
   const dim3 grid((p.slots_per_frame + spw * kOdWarps - 1) / (spw * kOdWarps), nframes);
-  orient_desc_kernel<<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out, spw);
+  // TMA staging of the keypoint windows: every blurred level must be addressable (16-byte aligned base and pitch, frames
+  // stacked without gaps: always true for the handle's own buffers); a level image that is not keeps cp.async
+  static const bool no_tma = [] { const char* e = getenv("ORB_GPU_OD_DIRECT"); return e && atoi(e); }();
+  OdStage T;
+  memset(&T, 0, sizeof(T));
+  bool tma = !no_tma && tma_available();
+  for (int l = 0; tma && l < p.nlevels; ++l) {
+    const LevelGeom& g = p.lv[l];
+    if ((reinterpret_cast<uintptr_t>(g.blur) & 15) || (g.bpitch & 15) ||
+        (nframes > 1 && g.bframe_stride != (long long)g.bpitch * g.h) || g.h < kOdRows) { tma = false; break; }
+    if (tensor_map_2d_u8(&T.tile[l], g.blur, g.bpitch, (long long)nframes * g.h, g.bpitch, kOdTilePitch, kOdRows, false)) { tma = false; break; }
+    const bool ic_ok = (reinterpret_cast<uintptr_t>(g.img) & 15) == 0 && (g.pitch & 15) == 0 &&
+                       (nframes == 1 || g.frame_stride == (long long)g.pitch * g.h);
+    if (ic_ok && tensor_map_2d_u8(&T.ic[l], g.img, g.pitch, (long long)nframes * g.h, g.pitch, kIcPitch, kIcRows, false) == ORB_GPU_OK)
+      T.ic_mask |= 1u << l;
+  }
+  if (tma) orient_desc_kernel<true><<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out, spw, T);
+  else orient_desc_kernel<false><<<grid, kOdWarps * 32, 0, s>>>(p, sc, d_kps, d_desc, capacity, d_n_out, spw, T);
   count_launch();
   ORB_CUDA_TRY(cudaGetLastError());
   return ORB_GPU_OK;
