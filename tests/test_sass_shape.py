@@ -54,3 +54,12 @@ def test_tensor_core_kernels_use_tcgen05_and_tma():
     assert any("UTCIMMA" in i for i in _sass("blur_tc_kernel"))
     assert any(i.startswith("UTMALDG") or " UTMALDG" in i for i in _sass("blur_tc_kernel"))
     assert any("UTMASTG" in i for i in _sass("blur_tc_kernel"))
+
+
+def test_staged_kernels_load_their_windows_by_tma():
+    """resize_level4_kernel<true> (source bands) and orient_desc_kernel<true> (keypoint windows) stage by TMA; their
+    <false> forms, kept for sources TMA cannot address, must not."""
+    assert any("UTMALDG" in i for i in _sass("resize_level4_kernelILb1"))
+    assert not any("UTMALDG" in i for i in _sass("resize_level4_kernelILb0"))
+    assert any("UTMALDG" in i for i in _sass("orient_desc_kernelILb1"))
+    assert not any("UTMALDG" in i for i in _sass("orient_desc_kernelILb0"))
