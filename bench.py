@@ -645,7 +645,7 @@ def run_ours(args):
            "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 4)),
            "ms_per_step": 1e3 * e2e_s / args.steps}
     assert int(h_n.sum().item()) == kp_total, "host and device paths disagree"
-    e2e["note"] = ("chunks of 32 frames (16 first and last) over four compute streams; at N > 1 every rank uploads at once and the host link "
+    e2e["note"] = ("chunks of 3/32 of the batch (48 frames of 512; 16 first, 24 last) over four compute streams; at N > 1 every rank uploads at once and the host link "
                    "(one NUMA node on this box) is shared: profiles/r04_h2d_concurrent_n8.txt")
 
     # ---- parity of the timed device run: the first frames of the batch against the reference's own extractor ----

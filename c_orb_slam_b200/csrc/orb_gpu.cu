@@ -149,13 +149,14 @@ static int fork_for(OrbGpuExtractor* h, cudaStream_t s, OrbGpuExtractor::Fork** 
 
 // Frames per chunk of the host-pointer path.  Chunk c runs on compute stream c % 4, so the kernels of up to four
 // chunks interleave on the SMs: one chunk's launch gaps and partial last waves are filled by its neighbours.
-// Small chunks (1/16 of the batch, 16..64 frames) keep the first upload short and the overlap fine-grained;
-// measured on 512 TUM frames: 4 x 128 frames on one stream 4.09 ms, 16 x 32 on four streams 3.57 ms.
+// Small chunks (3/32 of the batch, 16..64 frames) keep the first upload short and the overlap fine-grained;
+// measured on 512 TUM frames: 4 x 128 frames on one stream 4.09 ms, 16 x 32 on four streams 3.57 ms; with the
+// kernels of the end of round 2 chunks of 48 beat 32 (3.32 vs 3.45 ms: fewer, fuller launches) and 96 loses (3.58).
 // ORB_GPU_HOST_CHUNK / ORB_GPU_HOST_STREAMS override.
 static int host_chunk(int nb) {
   static const int forced = [] { const char* e = getenv("ORB_GPU_HOST_CHUNK"); return e ? atoi(e) : 0; }();
   if (forced > 0) return forced;
-  return std::max(16, std::min(64, (nb + 15) / 16));
+  return std::max(16, std::min(64, (3 * nb + 31) / 32));
 }
 static int host_streams() {
   static const int n = [] { const char* e = getenv("ORB_GPU_HOST_STREAMS"); return e ? atoi(e) : 4; }();
@@ -201,10 +202,11 @@ static std::vector<int> host_schedule(int nb) {
     for (int t : forced.second) tail_sum += t;
     return schedule_from(forced.first, tail_sum < nb ? forced.second : std::vector<int>(), nb);
   }
-  // default: chunks of c frames with a half-size first chunk (the kernels start after half the upload time) and a
-  // half-size last one (half the tail behind the last upload); measured on 512 TUM frames: 3.45 vs 3.52 ms
+  // default: chunks of c frames with a third-size first chunk (the kernels start after a third of the upload time) and
+  // a half-size last one (half the tail behind the last upload); measured on 512 TUM frames (head, body / tail):
+  // 16,48/24 3.32 ms; 16,48/16 3.35; 16,64/16 3.33; 24,48/24 3.33; 16,32/16 3.45; 8,16,32/16,8 3.47; 16,96/16 3.58
   const int c = host_chunk(nb);
-  if (nb >= 4 * c && c >= 16) return schedule_from({c / 2, c}, {c / 2}, nb);
+  if (nb >= 4 * c && c >= 16) return schedule_from({std::max(8, c / 3), c}, {c / 2}, nb);
   std::vector<int> b(1, 0);
   while (b.back() < nb) b.push_back(std::min(nb, b.back() + c));
   return b;
