@@ -392,15 +392,18 @@ fast_cells_kernel(Plan p, Scratch sc, FastLayout L) {
   uint32_t* tile32 = reinterpret_cast<uint32_t*>(tile);
   {
     const int nw = (off + cw + 3) >> 2;
-    if (nw <= 16) {  // half a warp per row
-      const int c = lane & 15, r0 = lane >> 4;
+    if (nw <= 16) {  // two rows per pass (16 lanes each), three when a row is at most 10 words (30 of 32 lanes busy)
+      const bool three = nw <= 10;
+      const int r0 = three ? (lane * 205) >> 11 : lane >> 4;  // lane / 10 for lane < 32
+      const int c = three ? lane - 10 * r0 : lane & 15;
+      const int rpp = three ? 3 : 2;
       const uint8_t* src = img - off + (size_t)r0 * g.pitch + 4 * c;
       unsigned dst = (unsigned)__cvta_generic_to_shared(tile32 + r0 * tp4 + c);
-      const int sstep = 2 * g.pitch;
-      const unsigned dstep = 2 * tp;
-      if (c < nw)
+      const int sstep = rpp * g.pitch;
+      const unsigned dstep = rpp * tp;
+      if (c < nw && r0 < rpp)
 #pragma unroll 4
-        for (int r = r0; r < ch; r += 2, src += sstep, dst += dstep)
+        for (int r = r0; r < ch; r += rpp, src += sstep, dst += dstep)
           asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
     } else {
       const uint32_t* src = reinterpret_cast<const uint32_t*>(img - off);
